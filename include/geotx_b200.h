@@ -1,0 +1,105 @@
+/* geotx_b200 -- C ABI of the B200-native GeoTransformer geometric-attention hot path.
+ *
+ * Drop-in boundary.  The reference's own native boundary is a pybind11 torch extension
+ * (/root/reference/setup.py:7-22, geotransformer/extensions/pybind.cpp:6-18) whose functions take tensors,
+ * validate them with CHECK_* macros (extensions/common/torch_helper.h:6-35), allocate nothing on the caller's
+ * behalf beyond their outputs and run on the caller's thread.  This library keeps those conventions but with a
+ * plain C signature: device pointers + sizes + a CUDA stream; no torch types.  The caller owns every buffer.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless named host_*; tensors are dense row-major (contiguous);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is enqueued on it,
+ *     nothing synchronises, nothing is allocated;
+ *   - return value: 0 on success, a negative GEOTX_E_* code otherwise; geotx_last_error() gives the text
+ *     (thread-local).  There is no CPU fallback: a machine without an sm_100 GPU gets GEOTX_E_CUDA.
+ *
+ * Each entry point names the reference code it replaces (paths relative to /root/reference/geotransformer/).
+ */
+#ifndef GEOTX_B200_H
+#define GEOTX_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GEOTX_OK 0
+#define GEOTX_E_ARG (-1)   /* invalid argument (shape, k, alignment, unsupported hidden_dim ...) */
+#define GEOTX_E_CUDA (-2)  /* CUDA runtime error (text in geotx_last_error) */
+
+#define GEOTX_MAX_ANGLE_K 7
+
+/* dtype tags for buffers that may be stored in either precision */
+#define GEOTX_F32 0
+#define GEOTX_BF16 1
+
+const char* geotx_last_error(void);
+int geotx_abi_version(void);
+
+/* Bytes of caller-provided scratch needed by geotx_gse_knn for B clouds of n points and k neighbours
+ * (packed float4 points + k reference vectors per point).  The scratch is an OUTPUT of geotx_gse_knn and an
+ * INPUT of geotx_gse_indices / geotx_gse_embed (it holds p and p_knn - p in the kernels' layout). */
+int64_t geotx_gse_geometry_bytes(int B, int n, int k);
+
+/* modules/geotransformer/geotransformer.py:38,42 (+ modules/ops/pairwise_distance.py:4-31):
+ * knn[b,i,:] = indices of the k+1 smallest sqrt(d2(i,:)), first dropped.  Bit-exact with the reference's
+ * torch-CPU fp32 result on tie-free rows; exact ties resolve to the smaller index.
+ *   points   f32 [B,n,3]        knn_out  i64 [B,n,k]        geometry  scratch, geotx_gse_geometry_bytes() */
+int geotx_gse_knn(const float* points, int B, int n, int k, int64_t* knn_out, void* geometry, void* stream);
+
+/* geotransformer.py:25-55 get_embedding_indices:  d_idx f32 [B,n,n], a_idx f32 [B,n,n,k]. */
+int geotx_gse_indices(const void* geometry, int B, int n, int k, float sigma_d, float factor_a,
+                      float* d_idx, float* a_idx, void* stream);
+
+/* One-time (per weight update) repack of proj_d / proj_a into the bf16, 128B-swizzled, K-chunked shared-memory
+ * image the tcgen05 kernel bulk-copies.  w_d, w_a f32 [C,C] (nn.Linear layout [out,in]); b_d, b_a f32 [C].
+ * packed: geotx_gse_packed_weight_bytes(C) bytes. */
+int64_t geotx_gse_packed_weight_bytes(int C);
+int geotx_gse_pack_weights(const float* w_d, const float* b_d, const float* w_a, const float* b_a, int C,
+                           void* packed, void* stream);
+
+/* geotransformer.py:57-72 GeometricStructureEmbedding.forward + positional_embedding.py:18-34:
+ *   E[b,i,j,:] = W_d s(d_ij/sigma_d) + b_d + reduce_k (W_a s(angle_ijk*factor_a) + b_a),  reduce = max | mean
+ * with the sinusoids generated in registers and contracted on tcgen05 (bf16 operands, fp32 accumulation);
+ * the (B,n,n,k,C) intermediate of the reference is never formed.
+ *   div_term f32 [C/2] (the module's registered buffer)      out  [B,n,n,C] in out_dtype (GEOTX_F32|GEOTX_BF16)
+ * C must be 128 or 256 for this entry point.  row_begin/row_count select a slab of query rows i of every cloud
+ * (whole cloud: 0, n); out then has shape [B,row_count,n,C].  Slabs let a caller bound the size of E when
+ * n is large (E is n*n*C*2 bytes per cloud) and stream slab by slab through geotx_rpe_scores. */
+int geotx_gse_embed(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                    const float* div_term, const void* packed_weights, int C, float sigma_d, float factor_a,
+                    int reduce_mean, int out_dtype, void* out, void* stream);
+
+/* Same contract, any even C, fp32 CUDA-core arithmetic with accurate sin/cos (no tensor cores): the
+ * high-precision path (<=1e-5 of the reference) used for small hidden sizes and as the on-device cross-check. */
+int geotx_gse_embed_fp32(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                         const float* div_term,
+                         const float* w_d, const float* b_d, const float* w_a, const float* b_a,
+                         int C, float sigma_d, float factor_a, int reduce_mean, int out_dtype, void* out,
+                         void* stream);
+
+/* modules/transformer/rpe_transformer.py:54-56 with proj_p folded into the query:
+ *   scores_p[b,h,i,j] = sum_c qt[b,h,i,c] * E[b,i,j,c],   qt[b,h,i,:] = W_p[h]^T q[b,h,i,:]
+ * (the q . b_p term is constant over j and cancels in the softmax).  E is streamed from HBM exactly once.
+ *   qt f32, element (b,h,i,c) at qt[b*qt_stride_b + h*qt_stride_h + i*C + c] (strides in elements; a dense
+ *      [B,H,n,C] tensor has qt_stride_b = H*n*C, qt_stride_h = n*C)
+ *   E [B,row_count,m,C] (e_dtype): the slab of query rows [row_begin,row_begin+row_count)
+ *   scores_p f32 [B,H,n,m] (only the slab's rows are written)
+ * Tensor-core path: e_dtype bf16, C in {128,256}, H <= 8; anything else takes a slower generic kernel. */
+int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, const void* E, int e_dtype,
+                     int B, int H, int n, int m, int C, int row_begin, int row_count, float* scores_p,
+                     void* stream);
+
+/* rpe_transformer.py:57-70 / vanilla_transformer.py:54-68: softmax((q k^T + scores_p) * scale [masked]) v.
+ *   q f32 [B,n,H*c] (token-major, heads interleaved as in 'b n (h c)'), k,v f32 [B,m,H*c],
+ *   scores_p f32 [B,H,n,m] or NULL, key_mask u8 [B,m] or NULL (non-zero = ignore),
+ *   out f32 [B,n,H*c].  c (per-head dim) in {32, 64}. */
+int geotx_attention(const float* q, const float* k, const float* v, const float* scores_p,
+                    const uint8_t* key_mask, int B, int H, int n, int m, int c, float scale, float* out,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GEOTX_B200_H */

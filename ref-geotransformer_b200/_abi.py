@@ -1,0 +1,66 @@
+"""ctypes binding of lib/libgeotx_b200.so -- the C ABI declared in include/geotx_b200.h.
+
+There is no fallback of any kind: if the library is missing or a call fails, a RuntimeError is raised
+(the reference's own extension reports errors the same way, TORCH_CHECK -> RuntimeError,
+/root/reference/geotransformer/extensions/common/torch_helper.h:6-35)."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'lib', 'libgeotx_b200.so')
+
+_p = ctypes.c_void_p
+_i = ctypes.c_int
+_f = ctypes.c_float
+_i64 = ctypes.c_int64
+
+# name -> (restype, argtypes); must list every symbol include/geotx_b200.h declares (tests check that)
+SIGNATURES = {
+    'geotx_last_error': (ctypes.c_char_p, []),
+    'geotx_abi_version': (_i, []),
+    'geotx_gse_geometry_bytes': (_i64, [_i, _i, _i]),
+    'geotx_gse_knn': (_i, [_p, _i, _i, _i, _p, _p, _p]),
+    'geotx_gse_indices': (_i, [_p, _i, _i, _i, _f, _f, _p, _p, _p]),
+    'geotx_gse_packed_weight_bytes': (_i64, [_i]),
+    'geotx_gse_pack_weights': (_i, [_p, _p, _p, _p, _i, _p, _p]),
+    'geotx_gse_embed': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
+    'geotx_gse_embed_fp32': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
+    'geotx_rpe_scores': (_i, [_p, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
+    'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p]),
+}
+
+GEOTX_F32 = 0
+GEOTX_BF16 = 1
+
+_lib = None
+launch_count = 0  # kernels-launching ABI calls made through this binding (bench.py reports it)
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f'{LIB_PATH} not found: the CUDA library has not been built (run `python -c "import '
+                f'__graft_entry__ as g; g.build()"`).  ref-geotransformer_b200 has no CPU / PyTorch fallback.')
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().geotx_last_error().decode('utf-8', 'replace')
+        raise RuntimeError(f'{what} failed (code {rc}): {msg}')
+
+
+def call(name, *args):
+    global launch_count
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    check(rc, name)
+    launch_count += 1

@@ -1,0 +1,64 @@
+// Shared device helpers for the GeoTransformer hot-path kernels (sm_100a only).
+//
+// Numerics contract: the squared distance must reproduce the reference's torch-CPU
+// fp32 op sequence bit for bit, because the k-NN indices derived from it are compared bit-exactly:
+//     xy = fma(x2, y2, fma(x1, y1, x0*y0))        /root/reference/.../ops/pairwise_distance.py:23 (MKL sgemm K=3)
+//     sq = (x0*x0 + x1*x1) + x2*x2                 pairwise_distance.py:27-28 (no fma)
+//     d2 = max(0, (sq_i - 2*xy) + sq_j)            pairwise_distance.py:29-30 (left to right)
+// All of it is written with explicit round-to-nearest intrinsics so that nvcc can never contract it.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#define GEOTX_MAX_K 7  // angle_k <= 7 (k+1 <= 8 candidates kept per row)
+
+namespace geotx {
+
+__device__ __forceinline__ float sq_norm_ref(float x, float y, float z) {
+    return __fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z));
+}
+
+// p = (x, y, z, sq_norm_ref(x,y,z))
+__device__ __forceinline__ float sqdist_ref(const float4& pi, const float4& pj) {
+    float xy = __fmaf_rn(pi.z, pj.z, __fmaf_rn(pi.y, pj.y, __fmul_rn(pi.x, pj.x)));
+    float d2 = __fadd_rn(__fsub_rn(pi.w, __fmul_rn(2.0f, xy)), pj.w);
+    return fmaxf(d2, 0.0f);
+}
+
+// geotransformer.py:47-52: angle between ref = p_knn - p_i and anc = p_j - p_i, atan2(|ref x anc|, ref . anc)
+__device__ __forceinline__ float triplet_angle(float rx, float ry, float rz, float ax, float ay, float az) {
+    float cx = __fsub_rn(__fmul_rn(ry, az), __fmul_rn(rz, ay));
+    float cy = __fsub_rn(__fmul_rn(rz, ax), __fmul_rn(rx, az));
+    float cz = __fsub_rn(__fmul_rn(rx, ay), __fmul_rn(ry, ax));
+    float s = sqrtf(cx * cx + cy * cy + cz * cz);
+    float c = rx * ax + ry * ay + rz * az;
+    return atan2f(s, c);
+}
+
+// The four embedding arguments of one (i, j) pair: x[0..k-1] = angle_kk * factor_a, x[k] = dist / sigma_d.
+// refv: k float4 per point (p_knn - p_i, .w unused), written by the k-NN kernel.
+template <int MAXK>
+__device__ __forceinline__ void pair_arguments(const float4& pi, const float4& pj, const float4* __restrict__ refv_i,
+                                               int k, float sigma_d, float factor_a, float* x /*MAXK+1*/) {
+    float ax = __fsub_rn(pj.x, pi.x), ay = __fsub_rn(pj.y, pi.y), az = __fsub_rn(pj.z, pi.z);
+#pragma unroll
+    for (int kk = 0; kk < MAXK; ++kk) {
+        if (kk < k) {
+            float4 r = __ldg(refv_i + kk);
+            x[kk] = __fmul_rn(triplet_angle(r.x, r.y, r.z, ax, ay, az), factor_a);
+        }
+    }
+    x[MAXK] = __fdiv_rn(__fsqrt_rn(sqdist_ref(pi, pj)), sigma_d);
+}
+
+// ---- small PTX wrappers -------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
+}  // namespace geotx

@@ -1,0 +1,377 @@
+// K2: fused GeometricStructureEmbedding on tcgen05 / TMEM  (sm_100a).
+//
+// Replaces /root/reference/geotransformer/modules/geotransformer/geotransformer.py:57-72 together with
+// /root/reference/geotransformer/modules/transformer/positional_embedding.py:18-34:
+//     E[i,j,:] = W_d s(d_ij/sigma_d) + b_d + reduce_kk ( W_a s(angle_ijkk*factor_a) + b_a )
+// The reference materialises s(.) as an (n,n,k,C) fp32 tensor (51 GB at n=4096) plus several copies.  Here one
+// CTA owns a tile of 128 consecutive (i,j) pairs; for each of the k+1 "slots" (k angles, 1 distance) the producer
+// warps generate the 128 x C sinusoid rows in registers (MUFU sin/cos), pack them to bf16 and store them into a
+// 128B-swizzled K-major shared-memory stage; one thread issues tcgen05.mma (M=128, N=C, K=16) against the
+// matching K-chunk of W_a / W_d, which the TMA unit bulk-copies (pre-swizzled image, see pack_weights_kernel)
+// into the same stage; accumulators ping-pong between two TMEM buffers; the epilogue warps pull each finished
+// accumulator out of TMEM once, keep the running max over k in registers, add the distance term and the
+// biases and write E (bf16 or fp32) straight to HBM.  Nothing of size n*n*k*C ever exists.
+//
+// Warp roles (640 threads): warps 0-7 producers, 8-15 epilogue (TMEM lane quarter = warp % 4, column half =
+// (warp-8)/4), 16 MMA issuer, 17 weight loader (bulk async copy), 18 TMEM allocator, 19 idle.
+#include "geotx_common.cuh"
+#include "sm100_ptx.cuh"
+#include "host_util.h"
+
+namespace geotx {
+
+constexpr int TILE_M = 128;
+constexpr int KCHUNK = 64;                     // bf16 elements per 128-byte swizzled row
+constexpr int A_STAGE_BYTES = TILE_M * 128;    // 16 KB
+constexpr int NUM_PRODUCER_WARPS = 8;
+constexpr int NUM_EPILOGUE_WARPS = 8;
+constexpr int K2_THREADS = 640;
+
+template <int C>
+struct K2Cfg {
+    static constexpr int KCH = C / KCHUNK;            // K chunks per slot
+    static constexpr int B_STAGE_BYTES = C * 128;      // C weight rows x 64 bf16
+    static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    static constexpr int NSTAGE = (C == 256) ? 4 : 6;
+    static constexpr int TMEM_COLS = 2 * C;            // two fp32 accumulators of C columns
+    static constexpr int COLS_PER_THREAD = C / 2;
+    static constexpr int SMEM_BYTES = NSTAGE * STAGE_BYTES + C * 4 /*bias*/ + (C / 2) * 4 /*div_term*/ +
+                                      (2 * NSTAGE + 4) * 8 /*barriers*/ + 16 + 1024 /*alignment slack*/;
+};
+
+// ------------------------------------------------------------------------------------------------------------
+// Weight repack: W (C x C fp32, [out][in]) -> bf16 image  [kc = in/64][out row][64 in]  with the 16-byte chunk
+// index of every 128-byte row XOR-ed by (row & 7)  (the SWIZZLE_128B pattern tcgen05 expects for a K-major tile
+// whose base is 1024-byte aligned).  Image order in `packed`: W_a, W_d, then fp32 (b_d + b_a)[C].
+// ------------------------------------------------------------------------------------------------------------
+__global__ void pack_weights_kernel(const float* __restrict__ w_d, const float* __restrict__ b_d,
+                                    const float* __restrict__ w_a, const float* __restrict__ b_a, int C,
+                                    uint8_t* __restrict__ packed) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int total = 2 * C * C;
+    if (t < total) {
+        int which = t / (C * C);  // 0: W_a, 1: W_d
+        int r = t - which * C * C;
+        int o = r / C, i = r - o * C;
+        const float* w = which == 0 ? w_a : w_d;
+        int kc = i >> 6, kk = i & 63, g = kk >> 3, e = kk & 7;
+        size_t off = (size_t)which * C * C * 2 + (size_t)kc * C * 128 + (size_t)o * 128 + ((g ^ (o & 7)) << 4) + e * 2;
+        *(__nv_bfloat16*)(packed + off) = __float2bfloat16_rn(w[(size_t)o * C + i]);
+    }
+    if (t < C) ((float*)(packed + (size_t)4 * C * C))[t] = b_d[t] + b_a[t];
+}
+
+struct K2Params {
+    const float4* pts4;
+    const float4* refv;
+    const float* div_term;
+    const uint8_t* packed;
+    void* out;
+    long long pairs_total;  // B * row_count * n
+    int n, k, row_begin, row_count;
+    int num_tiles;
+    float sigma_d, factor_a;
+    int reduce_mean, out_bf16;
+};
+
+template <int C>
+__global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
+    using Cfg = K2Cfg<C>;
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte alignment: required by the 128B swizzle atoms of the UMMA descriptors
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* stages = smem;
+    float* s_bias = (float*)(smem + Cfg::NSTAGE * Cfg::STAGE_BYTES);
+    float* s_div = s_bias + C;
+    uint64_t* bars = (uint64_t*)(s_div + C / 2);
+    uint32_t* s_tmem = (uint32_t*)(bars + 2 * Cfg::NSTAGE + 4);
+
+    const uint32_t bar_full = smem_u32(bars);                       // [NSTAGE]
+    const uint32_t bar_empty = bar_full + 8 * Cfg::NSTAGE;          // [NSTAGE]
+    const uint32_t bar_acc_full = bar_empty + 8 * Cfg::NSTAGE;      // [2]
+    const uint32_t bar_acc_empty = bar_acc_full + 16;               // [2]
+    const uint32_t stages_u32 = smem_u32(stages);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int k = prm.k;
+    const int slots = k + 1;
+
+    // ---- one-time setup ----
+    for (int t = threadIdx.x; t < C; t += K2_THREADS)
+        s_bias[t] = ((const float*)(prm.packed + (size_t)4 * C * C))[t];
+    for (int t = threadIdx.x; t < C / 2; t += K2_THREADS) s_div[t] = prm.div_term[t];
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < Cfg::NSTAGE; ++s) {
+            ptx::mbar_init(bar_full + 8 * s, NUM_PRODUCER_WARPS + 1);
+            ptx::mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            ptx::mbar_init(bar_acc_full + 8 * b, 1);
+            ptx::mbar_init(bar_acc_empty + 8 * b, NUM_EPILOGUE_WARPS);
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 18) ptx::tmem_alloc(smem_u32(s_tmem), Cfg::TMEM_COLS);
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem_base = *s_tmem;
+
+    if (warp < NUM_PRODUCER_WARPS) {
+        // =============================== PRODUCERS: sinusoid rows -> swizzled smem ===============================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        const int row = threadIdx.x & (TILE_M - 1);
+        const int half = threadIdx.x >> 7;  // which 4 of the 8 sixteen-byte chunks of a 128-byte row
+        const long long per_b = (long long)prm.row_count * prm.n;
+        const float4* s_div4 = (const float4*)s_div;
+        uint32_t q = 0;  // running chunk counter (stage ring position)
+        for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
+            float x[GEOTX_MAX_K + 1];
+#pragma unroll
+            for (int s = 0; s <= GEOTX_MAX_K; ++s) x[s] = 0.f;
+            const long long p = (long long)tile * TILE_M + row;
+            if (p < prm.pairs_total) {
+                const long long b = p / per_b;
+                const long long rem = p - b * per_b;
+                const int i = prm.row_begin + (int)(rem / prm.n);
+                const int j = (int)(rem % prm.n);
+                const float4 pi = __ldg(prm.pts4 + b * prm.n + i);
+                const float4 pj = __ldg(prm.pts4 + b * prm.n + j);
+                pair_arguments<GEOTX_MAX_K>(pi, pj, prm.refv + (b * prm.n + i) * k, k, prm.sigma_d, prm.factor_a, x);
+            }
+            for (int s = 0; s < slots; ++s) {
+                float xv = x[GEOTX_MAX_K];  // slot k = distance
+#pragma unroll
+                for (int t = 0; t < GEOTX_MAX_K; ++t)
+                    if (s == t && s < k) xv = x[t];
+#pragma unroll 1
+                for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
+                    const uint32_t stage = q % Cfg::NSTAGE;
+                    const uint32_t phase = (q / Cfg::NSTAGE) & 1;
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    const uint32_t a_row = stages_u32 + stage * Cfg::STAGE_BYTES + row * 128;
+#pragma unroll
+                    for (int gg = 0; gg < 4; ++gg) {
+                        const int g = half * 4 + gg;
+                        const float4 w = s_div4[kc * 8 + g];  // 4 frequencies = 8 bf16 = one 16-byte chunk
+                        // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
+                        const float o0 = __fmul_rn(xv, w.x), o1 = __fmul_rn(xv, w.y);
+                        const float o2 = __fmul_rn(xv, w.z), o3 = __fmul_rn(xv, w.w);
+                        uint32_t v0 = pack_bf16x2(__sinf(o0), __cosf(o0));
+                        uint32_t v1 = pack_bf16x2(__sinf(o1), __cosf(o1));
+                        uint32_t v2 = pack_bf16x2(__sinf(o2), __cosf(o2));
+                        uint32_t v3 = pack_bf16x2(__sinf(o3), __cosf(o3));
+                        const uint32_t addr = a_row + ((g ^ (row & 7)) << 4);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v0), "r"(v1),
+                                     "r"(v2), "r"(v3)
+                                     : "memory");
+                    }
+                    ptx::fence_proxy_async_smem();  // make the st.shared visible to the tensor core (async proxy)
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(bar_full + 8 * stage);
+                }
+            }
+        }
+    } else if (warp < NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS) {
+        // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 184;");
+        constexpr int NCOL = Cfg::COLS_PER_THREAD;
+        const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 belong to this warp
+        const int colhalf = (warp - NUM_PRODUCER_WARPS) >> 2;
+        const int row = quarter * 32 + lane;
+        const int groups = prm.reduce_mean ? 2 : slots;
+        const float inv_k = 1.0f / (float)k;
+        float run[NCOL];
+        uint32_t gc = 0;  // running accumulation-group counter (TMEM buffer ring position)
+        for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
+            for (int g = 0; g < groups; ++g, ++gc) {
+                const uint32_t buf = gc & 1, phase = (gc >> 1) & 1;
+                ptx::mbar_wait(bar_acc_full + 8 * buf, phase);
+                ptx::tc_fence_after_sync();
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * C + colhalf * NCOL;
+#pragma unroll
+                for (int c0 = 0; c0 < NCOL; c0 += 16) {
+                    uint32_t v[16];
+                    ptx::tmem_ld16(taddr + c0, v);
+                    ptx::tmem_ld_wait();
+                    if (prm.reduce_mean) {
+#pragma unroll
+                        for (int c = 0; c < 16; ++c)
+                            run[c0 + c] = (g == 0) ? __uint_as_float(v[c]) * inv_k : run[c0 + c] + __uint_as_float(v[c]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) {
+                            const float a = __uint_as_float(v[c]);
+                            run[c0 + c] = (g == 0) ? a : ((g < k) ? fmaxf(run[c0 + c], a) : run[c0 + c] + a);
+                        }
+                    }
+                }
+                ptx::tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(bar_acc_empty + 8 * buf);
+            }
+            // E = (W_d s_d + max_k W_a s_a) + (b_d + b_a)
+            const long long p = (long long)tile * TILE_M + row;
+            if (p < prm.pairs_total) {
+                const float4* bias4 = (const float4*)(s_bias + colhalf * NCOL);
+                if (prm.out_bf16) {
+                    uint4* dst = (uint4*)((__nv_bfloat16*)prm.out + p * C + colhalf * NCOL);
+#pragma unroll
+                    for (int c = 0; c < NCOL; c += 8) {
+                        const float4 b0 = bias4[c / 4], b1 = bias4[c / 4 + 1];
+                        uint4 o;
+                        o.x = pack_bf16x2(run[c] + b0.x, run[c + 1] + b0.y);
+                        o.y = pack_bf16x2(run[c + 2] + b0.z, run[c + 3] + b0.w);
+                        o.z = pack_bf16x2(run[c + 4] + b1.x, run[c + 5] + b1.y);
+                        o.w = pack_bf16x2(run[c + 6] + b1.z, run[c + 7] + b1.w);
+                        dst[c / 8] = o;
+                    }
+                } else {
+                    float4* dst = (float4*)((float*)prm.out + p * C + colhalf * NCOL);
+#pragma unroll
+                    for (int c = 0; c < NCOL; c += 4) {
+                        const float4 b0 = bias4[c / 4];
+                        dst[c / 4] = make_float4(run[c] + b0.x, run[c + 1] + b0.y, run[c + 2] + b0.z, run[c + 3] + b0.w);
+                    }
+                }
+            }
+        }
+    } else {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+        if (warp == 16) {
+            // =============================== MMA ISSUER (one thread) ============================================
+            if (lane == 0) {
+                constexpr uint32_t idesc = ptx::umma_idesc_bf16(TILE_M, C);
+                uint32_t q = 0, gc = 0;
+                for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
+                    for (int s = 0; s < slots; ++s) {
+                        const bool first = prm.reduce_mean ? (s == 0 || s == k) : true;
+                        const bool last = prm.reduce_mean ? (s == k - 1 || s == k) : true;
+                        const uint32_t buf = gc & 1;
+                        if (first) {
+                            ptx::mbar_wait(bar_acc_empty + 8 * buf, ((gc >> 1) & 1) ^ 1);
+                            ptx::tc_fence_after_sync();
+                        }
+                        const uint32_t tmem_d = tmem_base + buf * C;
+                        for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
+                            const uint32_t stage = q % Cfg::NSTAGE;
+                            ptx::mbar_wait(bar_full + 8 * stage, (q / Cfg::NSTAGE) & 1);
+                            ptx::tc_fence_after_sync();
+                            const uint32_t a_addr = stages_u32 + stage * Cfg::STAGE_BYTES;
+                            const uint64_t adesc = ptx::umma_desc_sw128(a_addr);
+                            const uint64_t bdesc = ptx::umma_desc_sw128(a_addr + A_STAGE_BYTES);
+#pragma unroll
+                            for (int ks = 0; ks < KCHUNK / 16; ++ks) {
+                                // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzled row: +2 (16-B units)
+                                ptx::umma_bf16(tmem_d, adesc + 2 * ks, bdesc + 2 * ks, idesc,
+                                               (uint32_t)(!(first && kc == 0 && ks == 0)));
+                            }
+                            ptx::umma_commit(bar_empty + 8 * stage);  // stage reusable once these MMAs retire
+                        }
+                        if (last) {
+                            ptx::umma_commit(bar_acc_full + 8 * buf);
+                            ++gc;
+                        }
+                    }
+                }
+            }
+        } else if (warp == 17) {
+            // =============================== WEIGHT LOADER (TMA unit bulk copies) ================================
+            if (lane == 0) {
+                uint32_t q = 0;
+                for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
+                    for (int s = 0; s < slots; ++s) {
+                        const uint8_t* img = prm.packed + (s < k ? 0 : (size_t)2 * C * C);  // W_a | W_d
+                        for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
+                            const uint32_t stage = q % Cfg::NSTAGE;
+                            ptx::mbar_wait(bar_empty + 8 * stage, ((q / Cfg::NSTAGE) & 1) ^ 1);
+                            ptx::mbar_arrive_expect_tx(bar_full + 8 * stage, Cfg::B_STAGE_BYTES);
+                            ptx::bulk_g2s(stages_u32 + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES,
+                                          img + (size_t)kc * Cfg::B_STAGE_BYTES, Cfg::B_STAGE_BYTES,
+                                          bar_full + 8 * stage);
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    // ---- teardown ----
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 18) {
+        ptx::tc_fence_after_sync();
+        ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+}  // namespace geotx
+
+// ---- C ABI --------------------------------------------------------------------------------------------------
+using namespace geotx;
+
+extern "C" int64_t geotx_gse_packed_weight_bytes(int C) {
+    if (C <= 0 || C % 64 != 0) return 0;
+    return (int64_t)4 * C * C + (int64_t)4 * C;
+}
+
+extern "C" int geotx_gse_pack_weights(const float* w_d, const float* b_d, const float* w_a, const float* b_a, int C,
+                                      void* packed, void* stream) {
+    GEOTX_REQUIRE(w_d && b_d && w_a && b_a && packed, "geotx_gse_pack_weights: null pointer");
+    GEOTX_REQUIRE(C == 128 || C == 256, "geotx_gse_pack_weights: hidden_dim %d not supported by the tcgen05 path "
+                  "(128 or 256); use geotx_gse_embed_fp32", C);
+    GEOTX_REQUIRE(((uintptr_t)packed & 15) == 0, "geotx_gse_pack_weights: packed must be 16-byte aligned");
+    int total = 2 * C * C;
+    pack_weights_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w_d, b_d, w_a, b_a, C,
+                                                                               (uint8_t*)packed);
+    return launch_status("geotx_gse_pack_weights");
+}
+
+template <int C>
+static int launch_k2(const K2Params& prm, cudaStream_t st) {
+    using Cfg = K2Cfg<C>;
+    static int num_sms = 0;
+    if (num_sms == 0) {
+        int dev = 0;
+        int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+        if (rc) return rc;
+        rc = check_cuda(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
+        if (rc) return rc;
+        rc = check_cuda(cudaFuncSetAttribute(gse_embed_tc_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::SMEM_BYTES), "cudaFuncSetAttribute(gse_embed_tc_kernel)");
+        if (rc) { num_sms = 0; return rc; }
+    }
+    int grid = prm.num_tiles < num_sms ? prm.num_tiles : num_sms;  // persistent: one CTA per SM
+    gse_embed_tc_kernel<C><<<grid, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
+    return launch_status("geotx_gse_embed");
+}
+
+extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                               const float* div_term, const void* packed_weights, int C, float sigma_d,
+                               float factor_a, int reduce_mean, int out_dtype, void* out, void* stream) {
+    GEOTX_REQUIRE(geometry && div_term && packed_weights && out, "geotx_gse_embed: null pointer");
+    GEOTX_REQUIRE(B > 0 && n > 0 && k >= 1 && k <= GEOTX_MAX_ANGLE_K, "geotx_gse_embed: bad sizes");
+    GEOTX_REQUIRE(C == 128 || C == 256, "geotx_gse_embed: hidden_dim %d not supported by the tcgen05 path (128 or "
+                  "256); use geotx_gse_embed_fp32", C);
+    GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed: bad row slab");
+    GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16, "geotx_gse_embed: bad out_dtype");
+    GEOTX_REQUIRE(((uintptr_t)out & 15) == 0 && ((uintptr_t)packed_weights & 15) == 0,
+                  "geotx_gse_embed: out / packed_weights must be 16-byte aligned");
+    K2Params prm;
+    prm.pts4 = (const float4*)geometry;
+    prm.refv = prm.pts4 + (size_t)B * n;
+    prm.div_term = div_term;
+    prm.packed = (const uint8_t*)packed_weights;
+    prm.out = out;
+    prm.pairs_total = (long long)B * row_count * n;
+    prm.n = n; prm.k = k; prm.row_begin = row_begin; prm.row_count = row_count;
+    long long tiles = (prm.pairs_total + TILE_M - 1) / TILE_M;
+    GEOTX_REQUIRE(tiles < 2147483647LL, "geotx_gse_embed: too many pairs");
+    prm.num_tiles = (int)tiles;
+    prm.sigma_d = sigma_d; prm.factor_a = factor_a;
+    prm.reduce_mean = reduce_mean ? 1 : 0;
+    prm.out_bf16 = out_dtype == GEOTX_BF16;
+    if (C == 256) return launch_k2<256>(prm, (cudaStream_t)stream);
+    return launch_k2<128>(prm, (cudaStream_t)stream);
+}

@@ -1,0 +1,396 @@
+"""Host-side mirror of the reference's module API for the hot path.
+
+Same class names, constructor signatures, forward signatures, error behaviour and state_dict keys as
+/root/reference/geotransformer/modules/geotransformer/geotransformer.py and
+/root/reference/geotransformer/modules/transformer/{rpe_transformer,vanilla_transformer,output_layer,
+conditional_transformer,positional_embedding}.py, so `load_state_dict(strict=True)` of a reference checkpoint
+works and the classes drop into `GeoTransformer.forward` (experiments/*/model.py:35-45,135-140).
+
+The heavy math runs in the sm_100a kernels behind include/geotx_b200.h (see ops.py).  The small dense layers
+(C x C Linears, LayerNorm, ReLU: <0.5 % of the path's flops) are issued through torch on
+the same stream.  Forward-only: calling with autograd enabled on anything that requires grad raises."""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+_ACTIVATIONS = {  # geotransformer/modules/layers/factory.py:18-27,71-80
+    'ReLU': nn.ReLU, 'LeakyReLU': nn.LeakyReLU, 'ELU': nn.ELU, 'GELU': nn.GELU, 'Sigmoid': nn.Sigmoid,
+    'Softplus': nn.Softplus, 'Tanh': nn.Tanh, 'Identity': nn.Identity,
+}
+
+
+def build_act_layer(act_cfg):
+    if act_cfg is None:
+        return nn.Identity()
+    if isinstance(act_cfg, str):
+        name, kwargs = act_cfg, {}
+    else:
+        kwargs = dict(act_cfg)
+        name = kwargs.pop('type')
+    assert name in _ACTIVATIONS, f'Illegal activation: {name}.'
+    if name == 'LeakyReLU' and 'negative_slope' not in kwargs:
+        kwargs['negative_slope'] = 0.2
+    return _ACTIVATIONS[name](**kwargs)
+
+
+def build_dropout_layer(p, **kwargs):
+    # factory.py:48-53.  Dropout only acts in training mode, and this implementation is forward/inference-only,
+    # so a non-zero p is kept as an nn.Dropout module (identity under eval()) for API parity.
+    if p is None or p == 0:
+        return nn.Identity()
+    return nn.Dropout(p=p, **kwargs)
+
+
+def _forward_only_guard(module, *tensors):
+    if not torch.is_grad_enabled():
+        return
+    needs = any(t is not None and t.requires_grad for t in tensors) or \
+        any(p.requires_grad for p in module.parameters())
+    if needs:
+        raise RuntimeError(
+            f'{type(module).__name__} (ref-geotransformer_b200) is forward-only: its CUDA kernels define no backward. '
+            'Call it under torch.no_grad() (as the reference tester does, engine/single_tester.py:42-43) or '
+            'freeze the parameters and inputs.')
+
+
+class SinusoidalPositionalEmbedding(nn.Module):
+    """positional_embedding.py:8-34.  Only the `div_term` buffer matters on the fused path (the kernels read it
+    instead of recomputing it); forward() is kept for API parity and runs as plain device ops."""
+
+    def __init__(self, d_model):
+        super().__init__()
+        if d_model % 2 != 0:
+            raise ValueError(f'Sinusoidal positional encoding with odd d_model: {d_model}')
+        self.d_model = d_model
+        div_indices = torch.arange(0, d_model, 2).float()
+        div_term = torch.exp(div_indices * (-math.log(10000.0) / d_model))
+        self.register_buffer('div_term', div_term)
+
+    def forward(self, emb_indices):
+        shape = emb_indices.shape
+        omegas = emb_indices.reshape(-1, 1) * self.div_term.view(1, -1)
+        return torch.stack([torch.sin(omegas), torch.cos(omegas)], dim=2).view(*shape, self.d_model).detach()
+
+
+class GeometricStructureEmbedding(nn.Module):
+    """geotransformer.py:9-72.  `precision`: 'bf16' = tcgen05 kernel (hidden_dim 128/256), 'fp32' = CUDA-core
+    kernel (any even hidden_dim); 'auto' picks bf16 when the hidden size allows it."""
+
+    def __init__(self, hidden_dim, sigma_d, sigma_a, angle_k, reduction_a='max', precision='auto'):
+        super().__init__()
+        self.sigma_d = sigma_d
+        self.sigma_a = sigma_a
+        self.factor_a = 180.0 / (self.sigma_a * math.pi)
+        self.angle_k = angle_k
+        self.embedding = SinusoidalPositionalEmbedding(hidden_dim)
+        self.proj_d = nn.Linear(hidden_dim, hidden_dim)
+        self.proj_a = nn.Linear(hidden_dim, hidden_dim)
+        self.reduction_a = reduction_a
+        if self.reduction_a not in ['max', 'mean']:
+            raise ValueError(f'Unsupported reduction mode: {self.reduction_a}.')
+        if precision not in ('auto', 'bf16', 'fp32'):
+            raise ValueError(f'Unsupported precision: {precision}.')
+        self.hidden_dim = hidden_dim
+        self.precision = precision
+        self._packed = None
+        self._packed_key = None
+
+    def _use_tensor_cores(self):
+        ok = self.hidden_dim in (128, 256)
+        if self.precision == 'bf16' and not ok:
+            raise RuntimeError(f"precision='bf16' needs hidden_dim 128 or 256, got {self.hidden_dim}")
+        return ok and self.precision != 'fp32'
+
+    def _packed_weights(self):
+        ts = (self.proj_d.weight, self.proj_d.bias, self.proj_a.weight, self.proj_a.bias)
+        key = tuple((t.data_ptr(), t._version) for t in ts)
+        if self._packed is None or key != self._packed_key:
+            self._packed = ops.gse_pack_weights(*[t.detach().contiguous() for t in ts])
+            self._packed_key = key
+        return self._packed
+
+    @torch.no_grad()
+    def geometry(self, points):
+        return ops.gse_knn(points.contiguous(), self.angle_k)
+
+    @torch.no_grad()
+    def get_embedding_indices(self, points):
+        geom = self.geometry(points)
+        return ops.gse_indices(geom, self.sigma_d, self.factor_a)
+
+    def embed(self, geom, out_dtype, row_begin=0, row_count=None, out=None):
+        mean = self.reduction_a == 'mean'
+        if self._use_tensor_cores():
+            return ops.gse_embed(geom, self.embedding.div_term, self._packed_weights(), self.hidden_dim, self.sigma_d,
+                                 self.factor_a, mean, out_dtype, row_begin, row_count, out)
+        return ops.gse_embed_fp32(geom, self.embedding.div_term, self.proj_d.weight.detach(),
+                                  self.proj_d.bias.detach(), self.proj_a.weight.detach(), self.proj_a.bias.detach(),
+                                  self.sigma_d, self.factor_a, mean, out_dtype, row_begin, row_count, out)
+
+    def forward(self, points, out_dtype=torch.float32):
+        """(B,n,3) -> (B,n,n,C).  Standalone calls return fp32 like the reference; GeometricTransformer asks for
+        the bf16 storage format internally."""
+        _forward_only_guard(self, points)
+        return self.embed(self.geometry(points), out_dtype)
+
+
+class AttentionOutput(nn.Module):
+    """output_layer.py:6-21."""
+
+    def __init__(self, d_model, dropout=None, activation_fn='ReLU'):
+        super().__init__()
+        self.expand = nn.Linear(d_model, d_model * 2)
+        self.activation = build_act_layer(activation_fn)
+        self.squeeze = nn.Linear(d_model * 2, d_model)
+        self.dropout = build_dropout_layer(dropout)
+        self.norm = nn.LayerNorm(d_model)
+
+    def forward(self, input_states):
+        hidden_states = self.squeeze(self.activation(self.expand(input_states)))
+        hidden_states = self.dropout(hidden_states)
+        return self.norm(input_states + hidden_states)
+
+
+def _dense_scores(q, k, num_heads, scores_p, key_weights, key_masks, attention_factors, attention_masks):
+    """Materialised attention matrix for the optional modifiers the fused kernel does not cover
+    (rpe_transformer.py:59-66 / vanilla_transformer.py:55-64); unreachable from GeometricTransformer."""
+    B, n, D = q.shape
+    c = D // num_heads
+    qh = q.view(B, n, num_heads, c).permute(0, 2, 1, 3)
+    kh = k.view(B, -1, num_heads, c).permute(0, 2, 1, 3)
+    scores = torch.matmul(qh, kh.transpose(-1, -2))
+    if scores_p is not None:
+        scores = scores + scores_p
+    scores = scores / c ** 0.5
+    if attention_factors is not None:
+        scores = attention_factors.unsqueeze(1) * scores
+    if key_weights is not None:
+        scores = scores * key_weights.unsqueeze(1).unsqueeze(1)
+    if key_masks is not None:
+        scores = scores.masked_fill(key_masks.unsqueeze(1).unsqueeze(1), float('-inf'))
+    if attention_masks is not None:
+        scores = scores.masked_fill(attention_masks, float('-inf'))
+    return F.softmax(scores, dim=-1)
+
+
+class _FusedAttentionBase(nn.Module):
+    need_scores = False  # set True to also return the (B,H,N,M) attention matrix like the reference does
+
+    def _attend(self, q, k, v, scores_p, key_weights, key_masks, attention_factors, attention_masks=None):
+        dense = self.need_scores or key_weights is not None or attention_factors is not None or \
+            attention_masks is not None or (self.training and isinstance(self.dropout, nn.Dropout))
+        if not dense:
+            return ops.attention(q, k, v, self.num_heads, scores_p, key_masks), None
+        scores = _dense_scores(q, k, self.num_heads, scores_p, key_weights, key_masks, attention_factors,
+                               attention_masks)
+        B, m, D = v.shape
+        vh = v.view(B, m, self.num_heads, D // self.num_heads).permute(0, 2, 1, 3)
+        hidden = torch.matmul(self.dropout(scores), vh)
+        return hidden.permute(0, 2, 1, 3).reshape(B, -1, D), scores
+
+
+class RPEMultiHeadAttention(_FusedAttentionBase):
+    """rpe_transformer.py:18-72.  proj_p is folded into the query (exact):
+    sum_c q_c (W_p e + b_p)_c = (W_p^T q) . e + q . b_p, and the second term is constant over keys so it cancels
+    in the softmax.  proj_p.bias therefore only exists for state_dict parity (and for need_scores=False paths it
+    has no effect on any output, as in exact arithmetic for the reference)."""
+
+    def __init__(self, d_model, num_heads, dropout=None):
+        super().__init__()
+        if d_model % num_heads != 0:
+            raise ValueError('`d_model` ({}) must be a multiple of `num_heads` ({}).'.format(d_model, num_heads))
+        self.d_model = d_model
+        self.num_heads = num_heads
+        self.d_model_per_head = d_model // num_heads
+        self.proj_q = nn.Linear(self.d_model, self.d_model)
+        self.proj_k = nn.Linear(self.d_model, self.d_model)
+        self.proj_v = nn.Linear(self.d_model, self.d_model)
+        self.proj_p = nn.Linear(self.d_model, self.d_model)
+        self.dropout = build_dropout_layer(dropout)
+
+    def folded_query(self, q):
+        """q (B,N,H*c) -> qt view of logical shape (B,H,N,C): qt[b,h,i,:] = W_p[h]^T q[b,h,i,:]."""
+        B, n, D = q.shape
+        H, c = self.num_heads, self.d_model_per_head
+        wp = self.proj_p.weight.view(H, c, D)                          # rows h*c..h*c+c of proj_p.weight
+        qh = q.view(B * n, H, c).transpose(0, 1)                       # (H, B*n, c)
+        qt = torch.bmm(qh, wp)                                         # (H, B*n, C)
+        return qt.view(H, B, n, D).permute(1, 0, 2, 3)                 # logical (B,H,N,C), no copy
+
+    def forward(self, input_q, input_k, input_v, embed_qk, key_weights=None, key_masks=None, attention_factors=None):
+        """embed_qk: (B,N,M,C) bf16 or fp32 embedding E (from GeometricStructureEmbedding)."""
+        _forward_only_guard(self, input_q, input_k, input_v, embed_qk)
+        q = self.proj_q(input_q)
+        k = self.proj_k(input_k)
+        v = self.proj_v(input_v)
+        scores_p = ops.rpe_scores(self.folded_query(q), embed_qk.contiguous())
+        return self._attend(q, k, v, scores_p, key_weights, key_masks, attention_factors)
+
+
+class MultiHeadAttention(_FusedAttentionBase):
+    """vanilla_transformer.py:15-70."""
+
+    def __init__(self, d_model, num_heads, dropout=None):
+        super().__init__()
+        if d_model % num_heads != 0:
+            raise ValueError('`d_model` ({}) must be a multiple of `num_heads` ({}).'.format(d_model, num_heads))
+        self.d_model = d_model
+        self.num_heads = num_heads
+        self.d_model_per_head = d_model // num_heads
+        self.proj_q = nn.Linear(self.d_model, self.d_model)
+        self.proj_k = nn.Linear(self.d_model, self.d_model)
+        self.proj_v = nn.Linear(self.d_model, self.d_model)
+        self.dropout = build_dropout_layer(dropout)
+
+    def forward(self, input_q, input_k, input_v, key_weights=None, key_masks=None, attention_factors=None,
+                attention_masks=None):
+        _forward_only_guard(self, input_q, input_k, input_v)
+        q = self.proj_q(input_q)
+        k = self.proj_k(input_k)
+        v = self.proj_v(input_v)
+        return self._attend(q, k, v, None, key_weights, key_masks, attention_factors, attention_masks)
+
+
+class RPEAttentionLayer(nn.Module):
+    """rpe_transformer.py:75-104."""
+
+    def __init__(self, d_model, num_heads, dropout=None):
+        super().__init__()
+        self.attention = RPEMultiHeadAttention(d_model, num_heads, dropout=dropout)
+        self.linear = nn.Linear(d_model, d_model)
+        self.dropout = build_dropout_layer(dropout)
+        self.norm = nn.LayerNorm(d_model)
+
+    def forward(self, input_states, memory_states, position_states, memory_weights=None, memory_masks=None,
+                attention_factors=None):
+        hidden_states, attention_scores = self.attention(
+            input_states, memory_states, memory_states, position_states,
+            key_weights=memory_weights, key_masks=memory_masks, attention_factors=attention_factors)
+        hidden_states = self.dropout(self.linear(hidden_states))
+        return self.norm(hidden_states + input_states), attention_scores
+
+
+class RPETransformerLayer(nn.Module):
+    """rpe_transformer.py:107-131."""
+
+    def __init__(self, d_model, num_heads, dropout=None, activation_fn='ReLU'):
+        super().__init__()
+        self.attention = RPEAttentionLayer(d_model, num_heads, dropout=dropout)
+        self.output = AttentionOutput(d_model, dropout=dropout, activation_fn=activation_fn)
+
+    def forward(self, input_states, memory_states, position_states, memory_weights=None, memory_masks=None,
+                attention_factors=None):
+        hidden_states, attention_scores = self.attention(
+            input_states, memory_states, position_states,
+            memory_weights=memory_weights, memory_masks=memory_masks, attention_factors=attention_factors)
+        return self.output(hidden_states), attention_scores
+
+
+class AttentionLayer(nn.Module):
+    """vanilla_transformer.py:73-102."""
+
+    def __init__(self, d_model, num_heads, dropout=None):
+        super().__init__()
+        self.attention = MultiHeadAttention(d_model, num_heads, dropout=dropout)
+        self.linear = nn.Linear(d_model, d_model)
+        self.dropout = build_dropout_layer(dropout)
+        self.norm = nn.LayerNorm(d_model)
+
+    def forward(self, input_states, memory_states, memory_weights=None, memory_masks=None, attention_factors=None,
+                attention_masks=None):
+        hidden_states, attention_scores = self.attention(
+            input_states, memory_states, memory_states, key_weights=memory_weights, key_masks=memory_masks,
+            attention_factors=attention_factors, attention_masks=attention_masks)
+        hidden_states = self.dropout(self.linear(hidden_states))
+        return self.norm(hidden_states + input_states), attention_scores
+
+
+class TransformerLayer(nn.Module):
+    """vanilla_transformer.py:105-129."""
+
+    def __init__(self, d_model, num_heads, dropout=None, activation_fn='ReLU'):
+        super().__init__()
+        self.attention = AttentionLayer(d_model, num_heads, dropout=dropout)
+        self.output = AttentionOutput(d_model, dropout=dropout, activation_fn=activation_fn)
+
+    def forward(self, input_states, memory_states, memory_weights=None, memory_masks=None, attention_factors=None,
+                attention_masks=None):
+        hidden_states, attention_scores = self.attention(
+            input_states, memory_states, memory_weights=memory_weights, memory_masks=memory_masks,
+            attention_factors=attention_factors, attention_masks=attention_masks)
+        return self.output(hidden_states), attention_scores
+
+
+def _check_block_type(block):
+    if block not in ['self', 'cross']:
+        raise ValueError('Unsupported block type "{}".'.format(block))
+
+
+class RPEConditionalTransformer(nn.Module):
+    """conditional_transformer.py:73-117."""
+
+    def __init__(self, blocks, d_model, num_heads, dropout=None, activation_fn='ReLU', return_attention_scores=False,
+                 parallel=False):
+        super().__init__()
+        self.blocks = blocks
+        layers = []
+        for block in self.blocks:
+            _check_block_type(block)
+            if block == 'self':
+                layers.append(RPETransformerLayer(d_model, num_heads, dropout=dropout, activation_fn=activation_fn))
+            else:
+                layers.append(TransformerLayer(d_model, num_heads, dropout=dropout, activation_fn=activation_fn))
+        self.layers = nn.ModuleList(layers)
+        self.return_attention_scores = return_attention_scores
+        self.parallel = parallel
+
+    def forward(self, feats0, feats1, embeddings0, embeddings1, masks0=None, masks1=None):
+        for layer in self.layers:
+            layer.attention.attention.need_scores = bool(self.return_attention_scores)
+        attention_scores = []
+        for i, block in enumerate(self.blocks):
+            if block == 'self':
+                feats0, scores0 = self.layers[i](feats0, feats0, embeddings0, memory_masks=masks0)
+                feats1, scores1 = self.layers[i](feats1, feats1, embeddings1, memory_masks=masks1)
+            elif self.parallel:
+                new_feats0, scores0 = self.layers[i](feats0, feats1, memory_masks=masks1)
+                new_feats1, scores1 = self.layers[i](feats1, feats0, memory_masks=masks0)
+                feats0, feats1 = new_feats0, new_feats1
+            else:  # sequential: the second call sees the UPDATED feats0 (conditional_transformer.py:110-111)
+                feats0, scores0 = self.layers[i](feats0, feats1, memory_masks=masks1)
+                feats1, scores1 = self.layers[i](feats1, feats0, memory_masks=masks0)
+            if self.return_attention_scores:
+                attention_scores.append([scores0, scores1])
+        if self.return_attention_scores:
+            return feats0, feats1, attention_scores
+        return feats0, feats1
+
+
+class GeometricTransformer(nn.Module):
+    """geotransformer.py:75-155.  Extra keyword `precision` ('auto' | 'bf16' | 'fp32') selects the embedding
+    kernel and the storage type of E (bf16 / fp32); everything else is the reference signature."""
+
+    def __init__(self, input_dim, output_dim, hidden_dim, num_heads, blocks, sigma_d, sigma_a, angle_k, dropout=None,
+                 activation_fn='ReLU', reduction_a='max', precision='auto'):
+        super().__init__()
+        self.embedding = GeometricStructureEmbedding(hidden_dim, sigma_d, sigma_a, angle_k, reduction_a=reduction_a,
+                                                     precision=precision)
+        self.in_proj = nn.Linear(input_dim, hidden_dim)
+        self.transformer = RPEConditionalTransformer(blocks, hidden_dim, num_heads, dropout=dropout,
+                                                     activation_fn=activation_fn)
+        self.out_proj = nn.Linear(hidden_dim, output_dim)
+
+    def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
+        _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
+        e_dtype = torch.bfloat16 if self.embedding._use_tensor_cores() else torch.float32
+        ref_embeddings = self.embedding.embed(self.embedding.geometry(ref_points), e_dtype)
+        src_embeddings = self.embedding.embed(self.embedding.geometry(src_points), e_dtype)
+        ref_feats = self.in_proj(ref_feats)
+        src_feats = self.in_proj(src_feats)
+        ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
+                                                masks0=ref_masks, masks1=src_masks)
+        return self.out_proj(ref_feats), self.out_proj(src_feats)

@@ -1,0 +1,164 @@
+"""Tensor-level wrappers over the C ABI (include/geotx_b200.h).  torch is used for device memory and the
+current CUDA stream only; every function launches hand-written sm_100a kernels and raises RuntimeError on any
+non-CUDA / wrongly-typed input (no CPU fallback, same policy as the reference's CHECK_* macros,
+/root/reference/geotransformer/extensions/common/torch_helper.h:6-35)."""
+import ctypes
+
+import torch
+
+from . import _abi
+
+GEOTX_F32 = _abi.GEOTX_F32
+GEOTX_BF16 = _abi.GEOTX_BF16
+_DT = {torch.float32: GEOTX_F32, torch.bfloat16: GEOTX_BF16}
+
+
+def _check(t, name, dtype=None, dims=None):
+    if not isinstance(t, torch.Tensor):
+        raise RuntimeError(f'{name} must be a torch.Tensor')
+    if not t.is_cuda:
+        raise RuntimeError(f'{name} must be a CUDA tensor (ref-geotransformer_b200 has no CPU path)')
+    if not t.is_contiguous():
+        raise RuntimeError(f'{name} must be contiguous')
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f'{name} must be {dtype}, got {t.dtype}')
+    if dims is not None and t.dim() != dims:
+        raise RuntimeError(f'{name} must have {dims} dims, got shape {tuple(t.shape)}')
+    return t
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Geometry:
+    """Packed points + k-NN reference vectors of B clouds (the scratch geotx_gse_knn fills)."""
+    __slots__ = ('buf', 'B', 'n', 'k', 'knn')
+
+    def __init__(self, buf, B, n, k, knn):
+        self.buf, self.B, self.n, self.k, self.knn = buf, B, n, k, knn
+
+
+def gse_knn(points, k):
+    """points (B,n,3) fp32 -> Geometry (with .knn (B,n,k) int64).  geotransformer.py:38-42."""
+    _check(points, 'points', torch.float32, 3)
+    B, n, three = points.shape
+    if three != 3:
+        raise RuntimeError(f'points must be (B, n, 3), got {tuple(points.shape)}')
+    lib = _abi.load()
+    nbytes = lib.geotx_gse_geometry_bytes(B, n, k)
+    buf = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=points.device)
+    knn = torch.empty(B, n, k, dtype=torch.int64, device=points.device)
+    _abi.call('geotx_gse_knn', _p(points), B, n, k, _p(knn), _p(buf), _stream())
+    return Geometry(buf, B, n, k, knn)
+
+
+def gse_indices(geom, sigma_d, factor_a):
+    """-> d_idx (B,n,n), a_idx (B,n,n,k) fp32.  geotransformer.py:25-55."""
+    dev = geom.buf.device
+    d_idx = torch.empty(geom.B, geom.n, geom.n, dtype=torch.float32, device=dev)
+    a_idx = torch.empty(geom.B, geom.n, geom.n, geom.k, dtype=torch.float32, device=dev)
+    _abi.call('geotx_gse_indices', _p(geom.buf), geom.B, geom.n, geom.k, float(sigma_d), float(factor_a),
+              _p(d_idx), _p(a_idx), _stream())
+    return d_idx, a_idx
+
+
+def gse_pack_weights(w_d, b_d, w_a, b_a):
+    for t, nme in ((w_d, 'proj_d.weight'), (b_d, 'proj_d.bias'), (w_a, 'proj_a.weight'), (b_a, 'proj_a.bias')):
+        _check(t, nme, torch.float32)
+    C = w_d.shape[0]
+    lib = _abi.load()
+    nbytes = lib.geotx_gse_packed_weight_bytes(C)
+    if nbytes <= 0:
+        raise RuntimeError(f'hidden_dim {C} is not supported by the tcgen05 embedding kernel')
+    packed = torch.empty(nbytes, dtype=torch.uint8, device=w_d.device)
+    _abi.call('geotx_gse_pack_weights', _p(w_d), _p(b_d), _p(w_a), _p(b_a), C, _p(packed), _stream())
+    return packed
+
+
+def _slab(geom, row_begin, row_count):
+    row_count = geom.n - row_begin if row_count is None else row_count
+    return row_begin, row_count
+
+
+def gse_embed(geom, div_term, packed, C, sigma_d, factor_a, reduce_mean=False, out_dtype=torch.bfloat16,
+              row_begin=0, row_count=None, out=None):
+    """tcgen05 path.  -> E (B,row_count,n,C).  geotransformer.py:57-72."""
+    _check(div_term, 'div_term', torch.float32, 1)
+    row_begin, row_count = _slab(geom, row_begin, row_count)
+    if out is None:
+        out = torch.empty(geom.B, row_count, geom.n, C, dtype=out_dtype, device=geom.buf.device)
+    else:
+        _check(out, 'out', out_dtype)
+    _abi.call('geotx_gse_embed', _p(geom.buf), geom.B, geom.n, geom.k, row_begin, row_count, _p(div_term),
+              _p(packed), C, float(sigma_d), float(factor_a), int(bool(reduce_mean)), _DT[out_dtype], _p(out),
+              _stream())
+    return out
+
+
+def gse_embed_fp32(geom, div_term, w_d, b_d, w_a, b_a, sigma_d, factor_a, reduce_mean=False,
+                   out_dtype=torch.float32, row_begin=0, row_count=None, out=None):
+    """CUDA-core fp32 path, any even hidden size."""
+    for t, nme in ((w_d, 'proj_d.weight'), (b_d, 'proj_d.bias'), (w_a, 'proj_a.weight'), (b_a, 'proj_a.bias'),
+                   (div_term, 'div_term')):
+        _check(t, nme, torch.float32)
+    C = w_d.shape[0]
+    row_begin, row_count = _slab(geom, row_begin, row_count)
+    if out is None:
+        out = torch.empty(geom.B, row_count, geom.n, C, dtype=out_dtype, device=geom.buf.device)
+    _abi.call('geotx_gse_embed_fp32', _p(geom.buf), geom.B, geom.n, geom.k, row_begin, row_count, _p(div_term),
+              _p(w_d), _p(b_d), _p(w_a), _p(b_a), C, float(sigma_d), float(factor_a), int(bool(reduce_mean)),
+              _DT[out_dtype], _p(out), _stream())
+    return out
+
+
+def rpe_scores(qt, E, n=None, row_begin=0, out=None):
+    """qt: folded query, logical shape (B,H,n,C) fp32 (may be a permuted view with unit channel stride and
+    row stride C);  E (B,row_count,m,C) bf16|fp32  ->  scores_p (B,H,n,m) fp32 (slab rows written).
+    rpe_transformer.py:54-56 with proj_p folded."""
+    if not (isinstance(qt, torch.Tensor) and qt.is_cuda and qt.dtype == torch.float32 and qt.dim() == 4):
+        raise RuntimeError('qt must be a 4-d fp32 CUDA tensor')
+    B, H, nq, C = qt.shape
+    if qt.stride(3) != 1 or qt.stride(2) != C:
+        qt = qt.contiguous()
+    _check(E, 'E', None, 4)
+    if E.dtype not in _DT:
+        raise RuntimeError(f'E must be fp32 or bf16, got {E.dtype}')
+    Bq, row_count, m, Ce = E.shape
+    if Bq != B or Ce != C:
+        raise RuntimeError(f'shape mismatch: qt {tuple(qt.shape)} vs E {tuple(E.shape)}')
+    n = nq if n is None else n
+    if out is None:
+        out = torch.empty(B, H, n, m, dtype=torch.float32, device=E.device)
+    _abi.call('geotx_rpe_scores', _p(qt), qt.stride(0), qt.stride(1), _p(E), _DT[E.dtype], B, H, n, m, C,
+              row_begin, row_count, _p(out), _stream())
+    return out
+
+
+def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None):
+    """q (B,n,H*c), k,v (B,m,H*c) fp32 token-major -> (B,n,H*c).  softmax((q k^T + scores_p)*scale) v.
+    rpe_transformer.py:57-70, vanilla_transformer.py:54-68."""
+    _check(q, 'q', torch.float32, 3)
+    _check(k, 'k', torch.float32, 3)
+    _check(v, 'v', torch.float32, 3)
+    B, n, D = q.shape
+    m = k.shape[1]
+    c = D // num_heads
+    if scores_p is not None:
+        _check(scores_p, 'scores_p', torch.float32, 4)
+        if tuple(scores_p.shape) != (B, num_heads, n, m):
+            raise RuntimeError(f'scores_p must be {(B, num_heads, n, m)}, got {tuple(scores_p.shape)}')
+    mask_u8 = None
+    if key_mask is not None:
+        if tuple(key_mask.shape) != (B, m):
+            raise RuntimeError(f'key_mask must be {(B, m)}, got {tuple(key_mask.shape)}')
+        mask_u8 = _check(key_mask.to(torch.uint8).contiguous(), 'key_mask')
+    scale = 1.0 / (c ** 0.5) if scale is None else scale
+    out = torch.empty_like(q)
+    _abi.call('geotx_attention', _p(q), _p(k), _p(v), _p(scores_p), _p(mask_u8), B, num_heads, n, m, c,
+              float(scale), _p(out), _stream())
+    return out

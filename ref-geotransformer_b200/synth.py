@@ -1,0 +1,77 @@
+"""Synthetic inputs for the hot path: seeded, shaped like the reference's three
+experiment configs (experiments/*/config.py:103-113).  Used by tests, bench.py and smoke()."""
+import math
+
+import numpy as np
+import torch
+
+SEED = 7351  # experiments/*/config.py:13
+
+CONFIGS = {
+    # name: GeometricTransformer ctor args (experiments/*/config.py:103-113, ModelNet :123-133)
+    '3dmatch': dict(input_dim=1024, output_dim=256, hidden_dim=256, num_heads=4,
+                    blocks=['self', 'cross'] * 3, sigma_d=0.2, sigma_a=15, angle_k=3, reduction_a='max'),
+    'kitti': dict(input_dim=2048, output_dim=256, hidden_dim=128, num_heads=4,
+                  blocks=['self', 'cross'] * 3, sigma_d=4.8, sigma_a=15, angle_k=3, reduction_a='max'),
+    'modelnet': dict(input_dim=512, output_dim=256, hidden_dim=256, num_heads=4,
+                     blocks=['self', 'cross'] * 3, sigma_d=0.2, sigma_a=15, angle_k=3, reduction_a='max'),
+}
+
+
+def _rotation(gen, max_deg):
+    axis = torch.randn(3, generator=gen, dtype=torch.float64)
+    axis = axis / axis.norm()
+    ang = (torch.rand(1, generator=gen, dtype=torch.float64).item()) * math.radians(max_deg)
+    kx = torch.tensor([[0, -axis[2], axis[1]], [axis[2], 0, -axis[0]], [-axis[1], axis[0], 0]], dtype=torch.float64)
+    return torch.eye(3, dtype=torch.float64) + math.sin(ang) * kx + (1 - math.cos(ang)) * (kx @ kx)
+
+
+def make_cloud(shape, n, gen):
+    if shape == '3dmatch':
+        s = 3.0 * (n / 1024.0) ** (1.0 / 3.0)  # ~0.3 m superpoint spacing
+        return torch.rand(n, 3, generator=gen) * s
+    if shape == 'kitti':
+        return torch.rand(n, 3, generator=gen) * torch.tensor([160.0, 160.0, 8.0]) - torch.tensor([80.0, 80.0, 4.0])
+    if shape == 'modelnet':
+        return torch.rand(n, 3, generator=gen)
+    raise ValueError(shape)
+
+
+def make_pair(shape='3dmatch', n=1024, m=None, seed=SEED, input_dim=None):
+    """Returns ref_points (1,n,3), src_points (1,m,3), ref_feats (1,n,Din), src_feats (1,m,Din), fp32 CPU."""
+    m = n if m is None else m
+    din = CONFIGS[shape]['input_dim'] if input_dim is None else input_dim
+    gen = torch.Generator().manual_seed(seed)
+    ref = make_cloud(shape, n, gen)
+    perm = torch.randperm(n, generator=gen)[:m]
+    rot = _rotation(gen, 45.0)
+    trans = (torch.rand(3, generator=gen, dtype=torch.float64) - 0.5)
+    src = (ref[perm].double() @ rot.T + trans).float() + torch.randn(m, 3, generator=gen) * 0.01
+    ref_feats = torch.randn(n, din, generator=gen)
+    src_feats = torch.randn(m, din, generator=gen)
+    return ref[None].contiguous(), src[None].contiguous(), ref_feats[None].contiguous(), src_feats[None].contiguous()
+
+
+def tie_free(points, k=3):
+    """Precondition for bit-exact k-NN parity.  torch.topk leaves the order of exact ties
+    unspecified, so parity with the reference is only defined when the reference's own fp32 distances
+    (sqrt(max(0, x2 - 2xy + y2)), pairwise_distance.py:22-30) are strictly increasing over the first k+2
+    sorted neighbours of every row.  points: (n,3) fp32 CPU tensor."""
+    x = points.float()
+    n = x.shape[0]
+    sq = torch.sum(x ** 2, dim=-1)
+    d = torch.sqrt((sq.unsqueeze(-1) - 2 * torch.matmul(x, x.t()) + sq.unsqueeze(-2)).clamp(min=0.0))
+    kk = min(k + 2, n)
+    part = d.topk(kk, dim=1, largest=False)[0]
+    return bool((part[:, 1:] > part[:, :-1]).all())
+
+
+def make_tie_free_pair(shape='3dmatch', n=1024, m=None, seed=SEED, input_dim=None, k=3, max_tries=64):
+    """make_pair, bumping the seed by 1000 until both clouds satisfy tie_free ("else bump the
+    seed and record it").  Returns (ref_points, src_points, ref_feats, src_feats, seed_used)."""
+    for t in range(max_tries):
+        s = seed + 1000 * t
+        out = make_pair(shape, n, m, s, input_dim)
+        if tie_free(out[0][0], k) and tie_free(out[1][0], k):
+            return out + (s,)
+    raise RuntimeError('no tie-free seed found')

@@ -1,0 +1,149 @@
+"""CPU tests of the host-side mirror of the reference interface and of the C-ABI library surface."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from load_reference import load_reference, reference_available
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _expected_keys(blocks):
+    keys = ['embedding.embedding.div_term', 'embedding.proj_d.weight', 'embedding.proj_d.bias',
+            'embedding.proj_a.weight', 'embedding.proj_a.bias', 'in_proj.weight', 'in_proj.bias']
+    for i, b in enumerate(blocks):
+        p = f'transformer.layers.{i}.'
+        for nm in ['proj_q', 'proj_k', 'proj_v'] + (['proj_p'] if b == 'self' else []):
+            keys += [p + f'attention.attention.{nm}.weight', p + f'attention.attention.{nm}.bias']
+        for nm in ['attention.linear', 'attention.norm', 'output.expand', 'output.squeeze', 'output.norm']:
+            keys += [p + nm + '.weight', p + nm + '.bias']
+    return keys + ['out_proj.weight', 'out_proj.bias']
+
+
+@pytest.mark.parametrize('shape', ['3dmatch', 'kitti', 'modelnet'])
+def test_state_dict_keys_and_shapes(pkg, oracle, shape):
+    cfg = dict(pkg.synth.CONFIGS[shape])
+    m = pkg.GeometricTransformer(**cfg)
+    sd = m.state_dict()
+    assert list(sd.keys()) == _expected_keys(cfg['blocks'])
+    assert len(sd) == 111
+    ref_sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    assert {k: tuple(v.shape) for k, v in sd.items()} == {k: tuple(v.shape) for k, v in ref_sd.items()}
+    m.load_state_dict(ref_sd, strict=True)
+    if shape == '3dmatch':
+        assert sum(p.numel() for p in m.parameters()) == 3819776  # SURVEY.md 8b [measured]
+
+
+@pytest.mark.skipif(not reference_available(), reason='/root/reference not present (GPU box)')
+def test_state_dict_round_trip_with_reference(pkg):
+    GT, GSE = load_reference()
+    cfg = dict(pkg.synth.CONFIGS['3dmatch'])
+    args = (cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['num_heads'], cfg['blocks'], cfg['sigma_d'],
+            cfg['sigma_a'], cfg['angle_k'])
+    ref = GT(*args)
+    new = pkg.GeometricTransformer(*args)
+    new.load_state_dict(ref.state_dict(), strict=True)
+    ref.load_state_dict(new.state_dict(), strict=True)
+    assert list(ref.state_dict().keys()) == list(new.state_dict().keys())
+    # same construction order => same default init under the same seed
+    torch.manual_seed(7351)
+    a = GT(*args).state_dict()
+    torch.manual_seed(7351)
+    b = pkg.GeometricTransformer(*args).state_dict()
+    assert all(torch.equal(a[k], b[k]) for k in a)
+
+
+def test_constructor_errors_match_reference(pkg):
+    with pytest.raises(ValueError, match='Unsupported reduction mode'):
+        pkg.GeometricStructureEmbedding(256, 0.2, 15, 3, reduction_a='sum')
+    with pytest.raises(ValueError, match='odd d_model'):
+        pkg.SinusoidalPositionalEmbedding(255)
+    with pytest.raises(ValueError, match='must be a multiple of `num_heads`'):
+        pkg.RPEMultiHeadAttention(256, 3)
+    with pytest.raises(ValueError, match='must be a multiple of `num_heads`'):
+        pkg.MultiHeadAttention(100, 3)
+    with pytest.raises(ValueError, match='Unsupported block type'):
+        pkg.RPEConditionalTransformer(['self', 'mixed'], 256, 4)
+    with pytest.raises(AssertionError):
+        pkg.AttentionOutput(64, activation_fn='Swish')
+
+
+def test_forward_only_and_no_cpu_fallback(pkg):
+    m = pkg.GeometricTransformer(16, 16, 32, 2, ['self', 'cross'], 0.2, 15, 3)
+    x = (torch.rand(1, 8, 3), torch.rand(1, 8, 3), torch.rand(1, 8, 16), torch.rand(1, 8, 16))
+    with pytest.raises(RuntimeError, match='forward-only'):
+        m(*x)
+    with torch.no_grad():
+        with pytest.raises(RuntimeError, match='CUDA tensor'):
+            m(*x)
+        with pytest.raises(RuntimeError, match='CUDA tensor'):
+            m.embedding.get_embedding_indices(x[0])
+
+
+def test_folded_query_identity_fp64(pkg, oracle):
+    """sum_c q_c (W_p e + b_p)_c = (W_p^T q).e + q.b_p, and the bias term cancels in softmax."""
+    torch.manual_seed(0)
+    B, n, m, C, H = 2, 7, 9, 32, 4
+    att = pkg.RPEMultiHeadAttention(C, H).double()
+    sd = {'a.' + k: v for k, v in att.state_dict().items()}
+    x = torch.randn(B, n, C, dtype=torch.float64)
+    mem = torch.randn(B, m, C, dtype=torch.float64)
+    E = torch.randn(B, n, m, C, dtype=torch.float64)
+    hidden_ref, scores_ref = oracle.multi_head_attention(x, mem, mem, sd, 'a.', H, embed_qk=E)
+    with torch.no_grad():
+        q = att.proj_q(x)
+        k = att.proj_k(mem)
+        qt = att.folded_query(q)  # (B,H,n,C) view
+        assert qt.shape == (B, H, n, C) and qt.stride(3) == 1 and qt.stride(2) == C
+        scores_p = torch.einsum('bhnc,bnmc->bhnm', qt, E)
+        c = C // H
+        qh = q.view(B, n, H, c).permute(0, 2, 1, 3)
+        kh = k.view(B, m, H, c).permute(0, 2, 1, 3)
+        scores = torch.softmax((qh @ kh.transpose(-1, -2) + scores_p) / c ** 0.5, dim=-1)
+    assert (scores - scores_ref).abs().max().item() < 1e-13
+    # dropping proj_p.bias changes nothing
+    sd2 = dict(sd)
+    sd2['a.proj_p.bias'] = torch.zeros_like(sd['a.proj_p.bias'])
+    _, scores_nb = oracle.multi_head_attention(x, mem, mem, sd2, 'a.', H, embed_qk=E)
+    assert (scores_nb - scores_ref).abs().max().item() < 1e-13
+
+
+def test_abi_library_exports_every_declared_symbol(pkg):
+    header = open(os.path.join(ROOT, 'include', 'geotx_b200.h')).read()
+    header = re.sub(r'/\*.*?\*/', '', header, flags=re.S)
+    declared = sorted(set(re.findall(r'\b(geotx_[a-z0-9_]+)\s*\(', header)))
+    assert len(declared) >= 11
+    assert sorted(pkg._abi.SIGNATURES.keys()) == declared
+    lib = ctypes.CDLL(pkg._abi.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), f'{name} declared in include/geotx_b200.h but not exported'
+    loaded = pkg._abi.load()
+    assert loaded.geotx_abi_version() == 1
+    assert loaded.geotx_gse_geometry_bytes(2, 100, 3) == 16 * 2 * 100 * 4
+    assert loaded.geotx_gse_packed_weight_bytes(256) == 4 * 256 * 256 + 4 * 256
+    assert loaded.geotx_gse_packed_weight_bytes(100) == 0
+
+
+def test_abi_argument_errors_without_gpu(pkg):
+    """Argument validation happens before any CUDA call, so it is testable on a CPU-only box."""
+    lib = pkg._abi.load()
+    buf = ctypes.create_string_buffer(4096)
+    p = ctypes.cast(buf, ctypes.c_void_p)
+    assert lib.geotx_gse_knn(p, 1, 3, 3, p, p, None) == -1  # n < k+1, as torch.topk raises in the reference
+    assert b'out of range' in lib.geotx_last_error()
+    assert lib.geotx_gse_knn(p, 1, 10, 9, p, p, None) == -1
+    assert lib.geotx_gse_embed(p, 1, 8, 3, 0, 8, p, p, 64, 0.2, 1.0, 0, 1, p, None) == -1
+    assert b'hidden_dim' in lib.geotx_last_error()
+    assert lib.geotx_attention(p, p, p, None, None, 1, 4, 8, 8, 48, 0.1, p, None) == -1
+
+
+def test_synthetic_inputs_are_deterministic(pkg):
+    a = pkg.synth.make_pair('3dmatch', 64, 50, seed=1)
+    b = pkg.synth.make_pair('3dmatch', 64, 50, seed=1)
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
+    assert a[0].shape == (1, 64, 3) and a[1].shape == (1, 50, 3) and a[2].shape == (1, 64, 1024)
+    pts = torch.tensor([[0., 0, 0], [1, 0, 0], [-1, 0, 0], [0, 2, 0], [0, 0, 3], [5, 5, 5]])
+    assert not pkg.synth.tie_free(pts)  # two neighbours at exactly distance 1
