@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py -- registration pairs/sec through GeometricTransformer.forward (GSE embedding + RPE attention).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload 3dmatch_1024]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one forward of the hot path over one synthetic registration pair of the workload (BASELINE.json
+configs[1]: 3DMatch stage-4 config, N = M = 1024 superpoints, random-init weights, seed 7351).  Rank r works on its
+own pairs (pair sharding, no collective on the path; one NCCL all_gather of the outputs at the end).
+Prints ONE JSON line on rank 0.
+
+  value     pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e       pairs/s through the public module call with HOST (pinned) inputs and a host read of the outputs
+  roofline  the fused embedding kernel (geotx_gse_embed, tcgen05): algorithmic flops / CUDA-event time, per launch
+  cpu_baseline  the oracle (CPU restatement of the reference's formulation) on this box's host cores
+
+--impl reference times that CPU oracle alone (rank 0 only)."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (synth shape / config, n, m)
+    '3dmatch_1024': ('3dmatch', 1024, 1024),   # BASELINE.json configs[1]  (the metric's configuration)
+    'kitti_2048': ('kitti', 2048, 2048),       # configs[2]
+    'modelnet_717': ('modelnet', 717, 717),    # configs[0]
+    '3dmatch_512': ('3dmatch', 512, 512),
+    '3dmatch_2048': ('3dmatch', 2048, 2048),
+    '3dmatch_4096': ('3dmatch', 4096, 4096),   # configs[3] sweep point named by north_star
+}
+METRIC = 'registration pairs/sec (embed+RPE-attn) at N superpoints'
+UNIT = 'pairs/s'
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            p = json.load(f)
+        return dict(tensor_sustained=float(p['bf16_tflops_sustained']), tensor_burst=float(p['bf16_tflops']),
+                    hbm=float(p['hbm_gbs']), source='measured')
+    except Exception:
+        return dict(tensor_sustained=1400.0, tensor_burst=1590.0, hbm=6650.0, source='fallback')
+
+
+def flops_gse(n, C, k):
+    """algorithmic flops of one GSE call (one cloud): 2 n^2 C^2 (1+k)."""
+    return 2.0 * n * n * C * C * (1 + k)
+
+
+def flops_pair(n, m, cfg):
+    """SURVEY.md 8d F_min (proj_p folded, E stored)."""
+    C, H, k = cfg['hidden_dim'], cfg['num_heads'], cfg['angle_k']
+    Ls = sum(b == 'self' for b in cfg['blocks'])
+    Lc = len(cfg['blocks']) - Ls
+    f = 0.0
+    for x in (n, m):
+        f += flops_gse(x, C, k) + Ls * (16 * x * C * C + 2 * x * C * C + 2 * x * x * C * H + 4 * x * x * C)
+        f += 2 * x * cfg['input_dim'] * C + 2 * x * C * cfg['output_dim']
+    f += Lc * ((12 * n * C * C + 4 * m * C * C + 4 * n * m * C) + (12 * m * C * C + 4 * n * C * C + 4 * n * m * C))
+    return f
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
+                                          '--format=csv,noheader,nounits', '-lms', '200'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(',')]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith('active'):
+                    reasons.add(nm)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU legs (oracle): test infrastructure used only as the timed baseline
+# ------------------------------------------------------------------------------------------------------------
+def cpu_setup(workload):
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import geotx_oracle as oracle
+    import pkgpath
+    import importlib.util
+    spec = importlib.util.spec_from_file_location('geotx_synth', os.path.join(pkgpath.PKG_DIR, 'synth.py'))
+    synth = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(synth)
+    shape, n, m = WORKLOADS[workload]
+    cfg = dict(synth.CONFIGS[shape])
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    inputs = synth.make_pair(shape, n, m, seed=synth.SEED)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    return oracle, cfg, sd, inputs, n, m, cores
+
+
+def cpu_sample_seconds(oracle, cfg, sd, inputs, rows):
+    t0 = time.perf_counter()
+    oracle.sampled_forward(sd, cfg, *inputs, rows=rows)
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(workload, budget_s=25.0):
+    """Bounded CPU baseline beside the GPU number (rank 0, N=1 only)."""
+    oracle, cfg, sd, inputs, n, m, cores = cpu_setup(workload)
+    rows = min(64, n)
+    cpu_sample_seconds(oracle, cfg, sd, inputs, min(16, n))  # warm the thread pool / allocator
+    t = cpu_sample_seconds(oracle, cfg, sd, inputs, rows)
+    est_full = t * n / rows
+    if est_full <= budget_s:
+        t0 = time.perf_counter()
+        oracle.geometric_transformer_chunked(sd, cfg, *inputs, rows=128)
+        t_full = time.perf_counter() - t0
+        return {'value': 1.0 / t_full, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                'sample': f'1 full pair ({workload}), row-chunked oracle (128 rows), {t_full:.2f} s'}
+    rows2 = max(rows, min(n, int(rows * budget_s / max(t, 1e-3) / 2)))
+    t2 = cpu_sample_seconds(oracle, cfg, sd, inputs, rows2)
+    return {'value': (rows2 / n) / t2, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+            'sample': f'{rows2} of {n} query rows of every block of 1 pair ({workload}), {t2:.2f} s, scaled by n/rows'}
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    oracle, cfg, sd, inputs, n, m, cores = cpu_setup(args.workload)
+    rows = min(128, n)
+    for _ in range(args.warmup):
+        cpu_sample_seconds(oracle, cfg, sd, inputs, rows)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_sample_seconds(oracle, cfg, sd, inputs, rows)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = (rows / n) / dt
+    sample = f'each step = {rows} of {n} query rows of every block of 1 pair, scaled by n/rows'
+    print(json.dumps({
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': cfg['hidden_dim'],
+                   'note': 'CPU oracle port of the reference formulation (reference is pure PyTorch; /root/reference '
+                           'does not travel to the GPU box), all host threads'},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }))
+
+
+# ------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import pkgpath
+    pkg = pkgpath.load_package()
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py needs a CUDA device: ref-geotransformer_b200 has no CPU path')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    pkg._abi.load()
+
+    shape, n, m = WORKLOADS[args.workload]
+    cfg = dict(pkg.synth.CONFIGS[shape])
+    C, k = cfg['hidden_dim'], cfg['angle_k']
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    torch.manual_seed(pkg.synth.SEED)
+    model = pkg.GeometricTransformer(**cfg).to(dev).eval()  # default nn.Linear init under seed 7351 = oracle init
+
+    # a small rotation of distinct pairs per rank; E (n*n*C*2 bytes per cloud) alone exceeds the 126 MB L2
+    n_pairs = 4
+    host = [pkg.synth.make_pair(shape, n, m, seed=pkg.synth.SEED + rank * 101 + p) for p in range(n_pairs)]
+    host = [tuple(t.pin_memory() for t in pr) for pr in host]
+    resident = [tuple(t.to(dev) for t in pr) for pr in host]
+    h2d = sum(t.numel() * t.element_size() for t in host[0])
+    out_host = [torch.empty(1, x, cfg['output_dim']).pin_memory() for x in (n, m)]
+    d2h = sum(t.numel() * t.element_size() for t in out_host)
+
+    # CUDA-event bracket around every launch of the dominant kernel (fused embedding, K2)
+    k2_events = []
+    orig_embed = model.embedding.embed
+
+    def timed_embed(*a, **kw):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = orig_embed(*a, **kw)
+        e1.record()
+        k2_events.append((e0, e1))
+        return out
+    model.embedding.embed = timed_embed
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    last = None
+    with torch.no_grad():
+        for s in range(max(args.warmup, 3)):
+            last = model(*resident[s % n_pairs])
+        barrier()
+        k2_events.clear()
+        launches0 = pkg._abi.launch_count
+        sampler = ClockSampler(local) if rank == 0 else None
+        if sampler:
+            sampler.start()
+        t_start, t_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_start.record()
+        for s in range(args.steps):
+            last = model(*resident[s % n_pairs])
+        if world > 1:  # the one collective of the job: gather the outputs of the last pair of every rank
+            gathered = pkg.dist.gather_pair_outputs([torch.cat(last, dim=1)[0]], world)
+        t_stop.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = t_start.elapsed_time(t_stop)
+        launches = pkg._abi.launch_count - launches0
+        k2_ms = [a.elapsed_time(b) for a, b in k2_events]
+
+        # ---- end to end: host (pinned) inputs -> device -> forward -> host outputs, every step ----
+        dbuf = tuple(torch.empty_like(t, device=dev) for t in host[0])
+        model.embedding.embed = orig_embed
+        for s in range(2):
+            for d, h in zip(dbuf, host[s % n_pairs]):
+                d.copy_(h, non_blocking=True)
+            o = model(*dbuf)
+        barrier()
+        w0 = time.perf_counter()
+        for s in range(args.steps):
+            for d, h in zip(dbuf, host[s % n_pairs]):
+                d.copy_(h, non_blocking=True)
+            o = model(*dbuf)
+            out_host[0].copy_(o[0], non_blocking=True)
+            out_host[1].copy_(o[1], non_blocking=True)
+            torch.cuda.synchronize()  # the caller reads the result on the host
+        barrier()
+        e2e_s = time.perf_counter() - w0
+
+    tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = tt.tolist()
+    if rank == 0:
+        peaks = measured_peaks()
+        value = world * args.steps / (ms * 1e-3)
+        k2_avg_ms = sum(k2_ms) / max(len(k2_ms), 1)
+        k2_flops = (flops_gse(n, C, k) + flops_gse(m, C, k)) / 2.0
+        achieved = k2_flops / (k2_avg_ms * 1e-3) / 1e12 if k2_ms else 0.0
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+            'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': C, 'num_heads': cfg['num_heads'],
+                       'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1,
+                       'l2': f'inputs larger than L2: E is {n * n * C * 2 / 1e6:.0f} MB per cloud, '
+                             f'{n_pairs} distinct pairs rotated',
+                       'sharding': f'by pair over {world} GPU(s); one all_gather of outputs'},
+            'e2e': {'value': world * args.steps / (e2e_ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
+                    'd2h_bytes_per_step': d2h},
+            'gpu_launches': launches,
+            'roofline': {'kernel': 'gse_embed_tc_kernel (geotx_gse_embed)', 'bound': 'tensor', 'achieved': achieved,
+                         'peak': peaks['tensor_sustained'], 'unit': 'TFLOP/s',
+                         'frac': achieved / peaks['tensor_sustained'], 'traffic': None,
+                         'peak_source': peaks['source'] + ' bf16 sustained (kernel timed inside the step)',
+                         'frac_of_burst_peak': achieved / peaks['tensor_burst'],
+                         'flops_per_launch': k2_flops, 'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
+                         'share_of_step': sum(k2_ms) / ms if ms else None},
+            'pair_tflops': flops_pair(n, m, cfg) / 1e12,
+            'pair_tensor_frac': flops_pair(n, m, cfg) * value / world / 1e12 / peaks['tensor_sustained'],
+            'clocks': clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line['cpu_baseline'] = cpu_baseline(args.workload)
+        else:
+            line['cpu_baseline'] = None
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--workload', default='3dmatch_1024', choices=sorted(WORKLOADS))
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == '__main__':
+    main()

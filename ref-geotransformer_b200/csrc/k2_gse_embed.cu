@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
         }
     } else if (warp < NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS) {
         // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 184;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
         constexpr int NCOL = Cfg::COLS_PER_THREAD;
         const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 belong to this warp
         const int colhalf = (warp - NUM_PRODUCER_WARPS) >> 2;

@@ -1,0 +1,79 @@
+"""-m gpu: GeometricTransformer.forward end to end through the drop-in module (C ABI underneath) against golden
+outputs written by the reference itself (tests/golden/make_golden.py) and against the oracle."""
+import pytest
+import torch
+
+from gpu_common import DEV, TOL_BF16, TOL_FP32, build_model, rel, sd_from_npz
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('tag', ['tiny_max', 'tiny_mean'])
+def test_tiny_fp32_path_vs_reference_golden(pkg, golden, tag):
+    """hidden 32, 2 heads (c=16), n=40 / m=33: fp32 embedding kernel + TF32 attention."""
+    z = golden(f'{tag}.npz')
+    cfg = eval(str(z['cfg']))
+    model = build_model(pkg, cfg, sd_from_npz(z))
+    with torch.no_grad():
+        o0, o1 = model(*[torch.from_numpy(z[k]).to(DEV) for k in ('ref_points', 'src_points', 'ref_feats', 'src_feats')])
+    e0, e1 = rel(o0, z['out_ref']), rel(o1, z['out_src'])
+    print(f'{tag}: {e0:.3e} {e1:.3e}')
+    assert e0 <= 2e-3 and e1 <= 2e-3  # TF32 attention contractions bound this path
+
+
+@pytest.mark.parametrize('name', ['3dmatch_n192', 'kitti_n256', 'modelnet_n128'])
+def test_shipped_configs_vs_reference_golden(pkg, oracle, golden, name):
+    z = golden(f'{name}.npz')
+    cfg = eval(str(z['cfg']))
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    rp, sp, rf, sf, _ = pkg.synth.make_tie_free_pair(str(z['shape']), int(z['n']), int(z['m']), seed=int(z['seed']))
+    model = build_model(pkg, cfg, sd)
+    with torch.no_grad():
+        o0, o1 = model(rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV))
+    e0, e1 = rel(o0, z['out_ref']), rel(o1, z['out_src'])
+    print(f'{name}: {e0:.3e} {e1:.3e}')
+    assert e0 <= TOL_BF16 and e1 <= TOL_BF16
+
+
+@pytest.mark.parametrize('name', ['modelnet_n717_out', '3dmatch_n1024_out'])
+def test_baseline_sizes_vs_reference_golden(pkg, oracle, golden, name):
+    """BASELINE.json configs[0] (ModelNet 717) and configs[1] (3DMatch 1024): full outputs of the reference."""
+    z = golden(f'{name}.npz')
+    cfg = eval(str(z['cfg']))
+    n = int(z['n'])
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    rp, sp, rf, sf, _ = pkg.synth.make_tie_free_pair(str(z['shape']), n, n, seed=int(z['seed']))
+    model = build_model(pkg, cfg, sd)
+    with torch.no_grad():
+        o0, o1 = model(rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV))
+    e0, e1 = rel(o0, z['out_ref']), rel(o1, z['out_src'])
+    print(f'{name}: {e0:.3e} {e1:.3e}')
+    assert e0 <= TOL_BF16 and e1 <= TOL_BF16
+
+
+def test_masks_batch_and_fp32_precision_vs_oracle(pkg, oracle):
+    """B = 2, n != m, key masks on both clouds (rpe_transformer.py:63-64), precision='fp32' override."""
+    cfg = dict(pkg.synth.CONFIGS['kitti'])
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    g = torch.Generator().manual_seed(9)
+    rp, sp = torch.rand(2, 90, 3, generator=g) * 40, torch.rand(2, 70, 3, generator=g) * 40
+    rf, sf = torch.randn(2, 90, cfg['input_dim'], generator=g), torch.randn(2, 70, cfg['input_dim'], generator=g)
+    rm, sm = torch.rand(2, 90, generator=g) < 0.2, torch.rand(2, 70, generator=g) < 0.2
+    e0, e1 = oracle.geometric_transformer(sd, cfg, rp, sp, rf, sf, rm, sm)
+    for precision, tol in (('auto', TOL_BF16), ('fp32', 3e-3)):
+        model = build_model(pkg, cfg, sd, precision)
+        with torch.no_grad():
+            o0, o1 = model(rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV), rm.to(DEV), sm.to(DEV))
+        r0, r1 = rel(o0, e0), rel(o1, e1)
+        print(f'masks {precision}: {r0:.3e} {r1:.3e}')
+        assert r0 <= tol and r1 <= tol
+
+
+def test_forward_only_guard_and_cpu_rejection(pkg, oracle):
+    cfg = dict(pkg.synth.CONFIGS['modelnet'])
+    model = pkg.GeometricTransformer(**cfg).to(DEV)
+    rp, sp, rf, sf = pkg.synth.make_pair('modelnet', 32, 32)
+    with pytest.raises(RuntimeError, match='forward-only'):
+        model(rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV))
+    with torch.no_grad(), pytest.raises(RuntimeError, match='CUDA tensor'):
+        pkg.GeometricTransformer(**cfg)(rp, sp, rf, sf)

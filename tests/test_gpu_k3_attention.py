@@ -1,0 +1,77 @@
+"""-m gpu: K3 (folded relative-position scores + flash attention) through the C ABI.  Floating-point kernels: compared
+with a plain torch fp32 evaluation of the reference formula (rpe_transformer.py:51-70, vanilla_transformer.py:50-68)
+computed on the CPU by the oracle."""
+import pytest
+import torch
+
+from gpu_common import DEV, rel
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(g, *shape):
+    return torch.randn(*shape, generator=g)
+
+
+@pytest.mark.parametrize('C,H,n,m', [(256, 4, 97, 97), (128, 4, 130, 130), (256, 8, 64, 64), (64, 2, 50, 50)])
+@pytest.mark.parametrize('e_dtype', [torch.bfloat16, torch.float32])
+def test_rpe_scores_folded_query(pkg, C, H, n, m, e_dtype):
+    """scores_p[b,h,i,j] = (W_p[h]^T q[b,h,i]) . E[b,i,j]  ==  einsum(q, proj_p(E)) - q.b_p  (SURVEY.md 8a-7)."""
+    g = torch.Generator().manual_seed(C + n)
+    B, c = 2, C // H
+    q = _rand(g, B, n, C)
+    E = _rand(g, B, n, m, C)
+    wp, bp = _rand(g, C, C) / C ** 0.5, _rand(g, C)
+    Eq = E.to(e_dtype).float()  # the kernel sees the stored precision of E
+    p = torch.nn.functional.linear(Eq, wp, bp).view(B, n, m, H, c).permute(0, 3, 1, 2, 4)
+    qh = q.view(B, n, H, c).permute(0, 2, 1, 3)
+    exp = torch.einsum('bhnc,bhnmc->bhnm', qh, p) - torch.einsum('bhnc,hc->bhn', qh, bp.view(H, c)).unsqueeze(-1)
+    att = pkg.RPEMultiHeadAttention(C, H).to(DEV)
+    with torch.no_grad():
+        att.proj_p.weight.copy_(wp)
+        att.proj_p.bias.copy_(bp)
+        qt = att.folded_query(q.to(DEV))
+        got = pkg.ops.rpe_scores(qt, E.to(DEV).to(e_dtype))
+        # slab interface: rows [10, 40) only
+        part = torch.zeros_like(got)
+        pkg.ops.rpe_scores(qt, E[:, 10:40].contiguous().to(DEV).to(e_dtype), n=n, row_begin=10, out=part)
+    assert rel(got, exp) <= 5e-5
+    assert torch.equal(part[:, :, 10:40], got[:, :, 10:40]) and float(part[:, :, :10].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize('c,H,n,m', [(64, 4, 200, 160), (32, 4, 77, 300), (64, 4, 64, 64), (16, 2, 33, 65)])
+@pytest.mark.parametrize('with_p,with_mask', [(False, False), (True, False), (True, True), (False, True)])
+def test_attention_vs_torch(pkg, oracle, c, H, n, m, with_p, with_mask):
+    """softmax((q k^T + scores_p)/sqrt(c) [mask]) v ; TF32 tensor-core contractions -> 2e-3."""
+    g = torch.Generator().manual_seed(c * 1000 + n)
+    B, D = 2, H * c
+    q, k, v = _rand(g, B, n, D), _rand(g, B, m, D), _rand(g, B, m, D)
+    sp = _rand(g, B, H, n, m) * 3.0 if with_p else None
+    mask = (torch.rand(B, m, generator=g) < 0.3) if with_mask else None
+    if mask is not None:
+        mask[:, 0] = False
+    qh, kh, vh = (t.view(B, -1, H, c).permute(0, 2, 1, 3) for t in (q, k, v))
+    s = torch.einsum('bhnc,bhmc->bhnm', qh, kh)
+    if sp is not None:
+        s = s + sp
+    s = s / c ** 0.5
+    if mask is not None:
+        s = s.masked_fill(mask[:, None, None], float('-inf'))
+    exp = torch.matmul(torch.softmax(s, -1), vh).permute(0, 2, 1, 3).reshape(B, n, D)
+    got = pkg.ops.attention(q.to(DEV), k.to(DEV), v.to(DEV), H, None if sp is None else sp.to(DEV),
+                            None if mask is None else mask.to(DEV))
+    assert rel(got, exp) <= 2e-3
+
+
+def test_attention_all_keys_masked_is_nan_like_torch(pkg):
+    q = torch.randn(1, 8, 64)
+    got = pkg.ops.attention(q.to(DEV), q.to(DEV), q.to(DEV), 2, None, torch.ones(1, 8, dtype=torch.bool).to(DEV))
+    assert torch.isnan(got).all()  # torch.softmax over a row of -inf is NaN too (rpe_transformer.py:63-65)
+
+
+def test_attention_rejects_cpu_and_bad_head_dim(pkg):
+    q = torch.randn(1, 8, 96)
+    with pytest.raises(RuntimeError, match='CUDA tensor'):
+        pkg.ops.attention(q, q, q, 2)
+    with pytest.raises(RuntimeError, match='per-head dim'):
+        pkg.ops.attention(q.to(DEV), q.to(DEV), q.to(DEV), 2)  # c = 48
