@@ -71,6 +71,11 @@ int geotx_gse_embed(const void* geometry, int B, int n, int k, int row_begin, in
                     const float* div_term, const void* packed_weights, int C, float sigma_d, float factor_a,
                     int reduce_mean, int out_dtype, void* out, void* stream);
 
+/* Debug aid (synchronises the device): the tcgen05 kernel's mbarrier waits are bounded; a wait that times out
+ * records {0x80000000 | role<<24 | ring position, barrier smem address, parity, block} and the launch finishes with
+ * undefined output instead of hanging the GPU.  Copies the record to host_out4 (all zero = healthy) and clears it. */
+int geotx_watchdog_status(uint32_t* host_out4);
+
 /* Same contract, any even C, fp32 CUDA-core arithmetic with accurate sin/cos (no tensor cores): the
  * high-precision path (<=1e-5 of the reference) used for small hidden sizes and as the on-device cross-check. */
 int geotx_gse_embed_fp32(const void* geometry, int B, int n, int k, int row_begin, int row_count,

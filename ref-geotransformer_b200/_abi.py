@@ -24,6 +24,7 @@ SIGNATURES = {
     'geotx_gse_packed_weight_bytes': (_i64, [_i]),
     'geotx_gse_pack_weights': (_i, [_p, _p, _p, _p, _i, _p, _p]),
     'geotx_gse_embed': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
+    'geotx_watchdog_status': (_i, [_p]),
     'geotx_gse_embed_fp32': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
     'geotx_rpe_scores': (_i, [_p, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
     'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p]),
@@ -53,6 +54,17 @@ def load():
             fn.argtypes = args
         _lib = lib
     return _lib
+
+
+def watchdog():
+    """Reads and clears the tcgen05 kernel's protocol watchdog (synchronises).  Returns None when healthy."""
+    rec = (ctypes.c_uint32 * 4)()
+    check(load().geotx_watchdog_status(rec), 'geotx_watchdog_status')
+    if rec[0] == 0:
+        return None
+    roles = {1: 'producer<-empty', 2: 'epilogue<-acc_full', 3: 'mma<-acc_empty', 4: 'mma<-full', 5: 'loader<-empty'}
+    return dict(role=roles.get((rec[0] >> 24) & 0x7f, '?'), ring_pos=rec[0] & 0xFFFFFF, barrier=hex(rec[1]),
+                parity=rec[2], block=rec[3])
 
 
 def check(rc, what):

@@ -32,7 +32,9 @@ __device__ __forceinline__ float triplet_angle(float rx, float ry, float rz, flo
     float cy = __fsub_rn(__fmul_rn(rz, ax), __fmul_rn(rx, az));
     float cz = __fsub_rn(__fmul_rn(rx, ay), __fmul_rn(ry, ax));
     float s = sqrtf(cx * cx + cy * cy + cz * cz);
-    float c = rx * ax + ry * ay + rz * az;
+    // torch.sum starts from +0, so an all-zero dot product (j == i: anc = 0) is +0 even when the products are -0;
+    // atan2(0, -0) would be pi instead of the reference's 0.  "+ 0.0f" maps -0 to +0 and changes nothing else.
+    float c = __fadd_rn(rx * ax + ry * ay + rz * az, 0.0f);
     return atan2f(s, c);
 }
 

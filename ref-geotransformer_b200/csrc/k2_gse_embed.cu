@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
                 for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
                     const uint32_t stage = q % Cfg::NSTAGE;
                     const uint32_t phase = (q / Cfg::NSTAGE) & 1;
-                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, (1u << 24) | (q & 0xFFFFFF));
                     const uint32_t a_row = stages_u32 + stage * Cfg::STAGE_BYTES + row * 128;
 #pragma unroll
                     for (int gg = 0; gg < 4; ++gg) {
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
         for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
             for (int g = 0; g < groups; ++g, ++gc) {
                 const uint32_t buf = gc & 1, phase = (gc >> 1) & 1;
-                ptx::mbar_wait(bar_acc_full + 8 * buf, phase);
+                ptx::mbar_wait(bar_acc_full + 8 * buf, phase, (2u << 24) | (gc & 0xFFFFFF));
                 ptx::tc_fence_after_sync();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * C + colhalf * NCOL;
 #pragma unroll
@@ -250,13 +250,13 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
                         const bool last = prm.reduce_mean ? (s == k - 1 || s == k) : true;
                         const uint32_t buf = gc & 1;
                         if (first) {
-                            ptx::mbar_wait(bar_acc_empty + 8 * buf, ((gc >> 1) & 1) ^ 1);
+                            ptx::mbar_wait(bar_acc_empty + 8 * buf, ((gc >> 1) & 1) ^ 1, (3u << 24) | (gc & 0xFFFFFF));
                             ptx::tc_fence_after_sync();
                         }
                         const uint32_t tmem_d = tmem_base + buf * C;
                         for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
                             const uint32_t stage = q % Cfg::NSTAGE;
-                            ptx::mbar_wait(bar_full + 8 * stage, (q / Cfg::NSTAGE) & 1);
+                            ptx::mbar_wait(bar_full + 8 * stage, (q / Cfg::NSTAGE) & 1, (4u << 24) | (q & 0xFFFFFF));
                             ptx::tc_fence_after_sync();
                             const uint32_t a_addr = stages_u32 + stage * Cfg::STAGE_BYTES;
                             const uint64_t adesc = ptx::umma_desc_sw128(a_addr);
@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
                         const uint8_t* img = prm.packed + (s < k ? 0 : (size_t)2 * C * C);  // W_a | W_d
                         for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
                             const uint32_t stage = q % Cfg::NSTAGE;
-                            ptx::mbar_wait(bar_empty + 8 * stage, ((q / Cfg::NSTAGE) & 1) ^ 1);
+                            ptx::mbar_wait(bar_empty + 8 * stage, ((q / Cfg::NSTAGE) & 1) ^ 1, (5u << 24) | (q & 0xFFFFFF));
                             ptx::mbar_arrive_expect_tx(bar_full + 8 * stage, Cfg::B_STAGE_BYTES);
                             ptx::bulk_g2s(stages_u32 + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES,
                                           img + (size_t)kc * Cfg::B_STAGE_BYTES, Cfg::B_STAGE_BYTES,
@@ -310,6 +310,17 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
 
 // ---- C ABI --------------------------------------------------------------------------------------------------
 using namespace geotx;
+
+extern "C" int geotx_watchdog_status(uint32_t* host_out4) {
+    GEOTX_REQUIRE(host_out4, "geotx_watchdog_status: null pointer");
+    int rc = check_cuda(cudaMemcpyFromSymbol(host_out4, ptx::g_watchdog, 16), "cudaMemcpyFromSymbol(g_watchdog)");
+    if (rc) return rc;
+    if (host_out4[0]) {
+        const uint32_t zero[4] = {0, 0, 0, 0};
+        rc = check_cuda(cudaMemcpyToSymbol(ptx::g_watchdog, zero, 16), "cudaMemcpyToSymbol(g_watchdog)");
+    }
+    return rc;
+}
 
 extern "C" int64_t geotx_gse_packed_weight_bytes(int C) {
     if (C <= 0 || C % 64 != 0) return 0;
