@@ -1,26 +1,31 @@
-// K2: fused GeometricStructureEmbedding on tcgen05 / TMEM  (sm_100a).
+// K2: fused GeometricStructureEmbedding on tcgen05 / TMEM, CTA-pair (cta_group::2) version  (sm_100a).
 //
 // Replaces /root/reference/geotransformer/modules/geotransformer/geotransformer.py:57-72 together with
 // /root/reference/geotransformer/modules/transformer/positional_embedding.py:18-34:
 //     E[i,j,:] = W_d s(d_ij/sigma_d) + b_d + reduce_kk ( W_a s(angle_ijkk*factor_a) + b_a )
-// The reference materialises s(.) as an (n,n,k,C) fp32 tensor (51 GB at n=4096) plus several copies.  Here one
-// CTA owns a tile of 128 consecutive (i,j) pairs; for each of the k+1 "slots" (k angles, 1 distance) the producer
-// warps generate the 128 x C sinusoid rows in registers (MUFU sin/cos), pack them to bf16 and store them into a
-// 128B-swizzled K-major shared-memory stage; one thread issues tcgen05.mma (M=128, N=C, K=16) against the
-// matching K-chunk of W_a / W_d, which the TMA unit bulk-copies (pre-swizzled image, see pack_weights_kernel)
-// into the same stage; accumulators ping-pong between two TMEM buffers; the epilogue warps pull each finished
-// accumulator out of TMEM once, keep the running max over k in registers, add the distance term and the
-// biases and write E (bf16 or fp32) straight to HBM.  Nothing of size n*n*k*C ever exists.
+// The reference materialises s(.) as an (n,n,k,C) fp32 tensor (51 GB at n=4096) plus several copies.  Here a
+// cluster of two CTAs (one SM pair) owns 256 consecutive (i,j) pairs, 128 per CTA.  For each of the k+1 "slots"
+// (k angles, 1 distance) the producer warps of each CTA generate their 128 x C sinusoid rows in registers
+// (MUFU sin/cos), pack them to bf16 and store them into a 128B-swizzled K-major shared-memory stage.  The weights
+// never move after the prologue: each CTA keeps ITS HALF of the output channels of W_a and W_d resident in shared
+// memory (2 x C*C bytes), which is exactly how tcgen05.mma.cta_group::2 wants the B operand split, so one thread of
+// the leader CTA issues M=256 x N=C x K=16 MMAs whose A rows come from both CTAs' stages and whose B rows come from
+// both CTAs' resident weights; each CTA's TMEM receives its own 128 rows x C columns.  Accumulators ping-pong between
+// two TMEM buffers; the epilogue warps pull each finished accumulator out of TMEM once, keep the running max over k in
+// registers, add the distance term and the biases and write E (bf16 or fp32) straight to HBM.  Nothing of size
+// n*n*k*C ever exists, and no weight byte is re-read from L2 after the first microseconds.
 //
-// Warp roles (640 threads): warps 0-7 producers, 8-15 epilogue (TMEM lane quarter = warp % 4, column half =
-// (warp-8)/4), 16 MMA issuer, 17 weight loader (bulk async copy), 18 TMEM allocator, 19 idle.
+// Warp roles (640 threads per CTA): warps 0-7 producers, 8-15 epilogue (TMEM lane quarter = warp % 4, column half =
+// (warp-8)/4), 16 MMA issuer (leader CTA only), 17 weight loader (one bulk copy at start), 18 TMEM allocator, 19 idle.
+// Cross-CTA signalling: producers / epilogue warps of the peer CTA arrive remotely on the leader's mbarriers
+// (mapa + mbarrier.arrive.release.cluster); tcgen05.commit multicasts "stage free" / "accumulator ready" to both.
 #include "geotx_common.cuh"
 #include "sm100_ptx.cuh"
 #include "host_util.h"
 
 namespace geotx {
 
-constexpr int TILE_M = 128;
+constexpr int TILE_M = 128;                    // pairs per CTA per tile (256 per cluster)
 constexpr int KCHUNK = 64;                     // bf16 elements per 128-byte swizzled row
 constexpr int A_STAGE_BYTES = TILE_M * 128;    // 16 KB
 constexpr int NUM_PRODUCER_WARPS = 8;
@@ -29,20 +34,22 @@ constexpr int K2_THREADS = 640;
 
 template <int C>
 struct K2Cfg {
-    static constexpr int KCH = C / KCHUNK;            // K chunks per slot
-    static constexpr int B_STAGE_BYTES = C * 128;      // C weight rows x 64 bf16
-    static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    static constexpr int NSTAGE = (C == 256) ? 4 : 6;
-    static constexpr int TMEM_COLS = 2 * C;            // two fp32 accumulators of C columns
+    static constexpr int KCH = C / KCHUNK;               // K chunks per slot
+    static constexpr int W_CHUNK_BYTES = (C / 2) * 128;  // this CTA's C/2 weight rows x 64 bf16
+    static constexpr int W_HALF_BYTES = KCH * W_CHUNK_BYTES;  // = C*C bytes: one matrix, this CTA's half of the rows
+    static constexpr int NSTAGE = (C == 256) ? 5 : 8;
+    static constexpr int TMEM_COLS = 2 * C;              // two fp32 accumulators of C columns (per CTA)
     static constexpr int COLS_PER_THREAD = C / 2;
-    static constexpr int SMEM_BYTES = NSTAGE * STAGE_BYTES + C * 4 /*bias*/ + (C / 2) * 4 /*div_term*/ +
-                                      (2 * NSTAGE + 4) * 8 /*barriers*/ + 16 + 1024 /*alignment slack*/;
+    static constexpr int NBAR = 2 * NSTAGE + 5;
+    static constexpr int SMEM_BYTES = 2 * W_HALF_BYTES + NSTAGE * A_STAGE_BYTES + C * 4 /*bias*/ +
+                                      (C / 2) * 4 /*div_term*/ + NBAR * 8 + 16 + 1024 /*alignment slack*/;
 };
 
 // ------------------------------------------------------------------------------------------------------------
-// Weight repack: W (C x C fp32, [out][in]) -> bf16 image  [kc = in/64][out row][64 in]  with the 16-byte chunk
-// index of every 128-byte row XOR-ed by (row & 7)  (the SWIZZLE_128B pattern tcgen05 expects for a K-major tile
-// whose base is 1024-byte aligned).  Image order in `packed`: W_a, W_d, then fp32 (b_d + b_a)[C].
+// Weight repack: W (C x C fp32, [out][in]) -> bf16 image  [half = out/(C/2)][kc = in/64][row = out%(C/2)][64 in]
+// with the 16-byte chunk index of every 128-byte row XOR-ed by (row & 7)  (the SWIZZLE_128B pattern tcgen05 expects
+// for a K-major tile whose base is 1024-byte aligned).  CTA rank r of a pair bulk-copies half r of both matrices.
+// Image order in `packed`: W_a, W_d, then fp32 (b_d + b_a)[C].
 // ------------------------------------------------------------------------------------------------------------
 __global__ void pack_weights_kernel(const float* __restrict__ w_d, const float* __restrict__ b_d,
                                     const float* __restrict__ w_a, const float* __restrict__ b_a, int C,
@@ -54,8 +61,11 @@ __global__ void pack_weights_kernel(const float* __restrict__ w_d, const float* 
         int r = t - which * C * C;
         int o = r / C, i = r - o * C;
         const float* w = which == 0 ? w_a : w_d;
+        int hc = C / 2;
+        int half = o / hc, row = o - half * hc;
         int kc = i >> 6, kk = i & 63, g = kk >> 3, e = kk & 7;
-        size_t off = (size_t)which * C * C * 2 + (size_t)kc * C * 128 + (size_t)o * 128 + ((g ^ (o & 7)) << 4) + e * 2;
+        size_t off = (size_t)which * C * C * 2 + (size_t)half * C * C + (size_t)kc * hc * 128 + (size_t)row * 128 +
+                     ((g ^ (row & 7)) << 4) + e * 2;
         *(__nv_bfloat16*)(packed + off) = __float2bfloat16_rn(w[(size_t)o * C + i]);
     }
     if (t < C) ((float*)(packed + (size_t)4 * C * C))[t] = b_d[t] + b_a[t];
@@ -69,31 +79,44 @@ struct K2Params {
     void* out;
     long long pairs_total;  // B * row_count * n
     int n, k, row_begin, row_count;
-    int num_tiles;
+    int num_tile_pairs;     // ceil(ceil(pairs_total / 128) / 2)
     float sigma_d, factor_a;
     int reduce_mean, out_bf16;
 };
 
+// watchdog tags: role << 24 | ring position
+constexpr uint32_t WD_PRODUCER = 1u << 24, WD_EPILOGUE = 2u << 24, WD_MMA_ACC = 3u << 24, WD_MMA_FULL = 4u << 24,
+                   WD_WEIGHTS = 6u << 24;
+
 template <int C>
-__global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(K2_THREADS, 1)
+gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     using Cfg = K2Cfg<C>;
     extern __shared__ uint8_t smem_raw[];
-    // 1024-byte alignment: required by the 128B swizzle atoms of the UMMA descriptors
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint8_t* stages = smem;
-    float* s_bias = (float*)(smem + Cfg::NSTAGE * Cfg::STAGE_BYTES);
+    // 1024-byte alignment: required by the 128B swizzle atoms of the UMMA descriptors.  The dynamic smem base is the
+    // same in both CTAs of the pair, so every offset below is valid in the peer as well.
+    // (offset arithmetic on smem_raw, not an integer round trip, so that ptxas keeps LDS/STS instead of generic LD/ST)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t* s_w = smem;                                   // [W_a half][W_d half], each KCH x (C/2 rows x 128 B)
+    uint8_t* stages = smem + 2 * Cfg::W_HALF_BYTES;        // NSTAGE x 16 KB
+    float* s_bias = (float*)(stages + Cfg::NSTAGE * A_STAGE_BYTES);
     float* s_div = s_bias + C;
     uint64_t* bars = (uint64_t*)(s_div + C / 2);
-    uint32_t* s_tmem = (uint32_t*)(bars + 2 * Cfg::NSTAGE + 4);
+    uint32_t* s_tmem = (uint32_t*)(bars + Cfg::NBAR);
 
-    const uint32_t bar_full = smem_u32(bars);                       // [NSTAGE]
-    const uint32_t bar_empty = bar_full + 8 * Cfg::NSTAGE;          // [NSTAGE]
-    const uint32_t bar_acc_full = bar_empty + 8 * Cfg::NSTAGE;      // [2]
-    const uint32_t bar_acc_empty = bar_acc_full + 16;               // [2]
+    const uint32_t bar_full = smem_u32(bars);                       // [NSTAGE]  leader: 16 warp arrivals
+    const uint32_t bar_empty = bar_full + 8 * Cfg::NSTAGE;          // [NSTAGE]  each CTA: 1 (multicast commit)
+    const uint32_t bar_acc_full = bar_empty + 8 * Cfg::NSTAGE;      // [2]       each CTA: 1 (multicast commit)
+    const uint32_t bar_acc_empty = bar_acc_full + 16;               // [2]       leader: 16 warp arrivals
+    const uint32_t bar_w = bar_acc_empty + 16;                      // [1]       each CTA: own weight copy
     const uint32_t stages_u32 = smem_u32(stages);
+    const uint32_t w_u32 = smem_u32(s_w);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1;
+    const int num_clusters = gridDim.x >> 1;
     const int k = prm.k;
     const int slots = k + 1;
 
@@ -103,18 +126,34 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
     for (int t = threadIdx.x; t < C / 2; t += K2_THREADS) s_div[t] = prm.div_term[t];
     if (threadIdx.x == 0) {
         for (int s = 0; s < Cfg::NSTAGE; ++s) {
-            ptx::mbar_init(bar_full + 8 * s, NUM_PRODUCER_WARPS + 1);
+            ptx::mbar_init(bar_full + 8 * s, 2 * NUM_PRODUCER_WARPS);
             ptx::mbar_init(bar_empty + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(bar_acc_full + 8 * b, 1);
-            ptx::mbar_init(bar_acc_empty + 8 * b, NUM_EPILOGUE_WARPS);
+            ptx::mbar_init(bar_acc_empty + 8 * b, 2 * NUM_EPILOGUE_WARPS);
         }
+        ptx::mbar_init(bar_w, 1);
         ptx::fence_barrier_init();
     }
-    if (warp == 18) ptx::tmem_alloc(smem_u32(s_tmem), Cfg::TMEM_COLS);
-    ptx::tc_fence_before_sync();
+    if (warp == 18) ptx::tmem_alloc_pair(smem_u32(s_tmem), Cfg::TMEM_COLS);
     __syncthreads();
+    if (warp == 17 && lane == 0) {
+        // resident weights: this CTA's half of the output channels of W_a and W_d (TMA unit bulk copies)
+        ptx::mbar_arrive_expect_tx(bar_w, 2 * Cfg::W_HALF_BYTES);
+#pragma unroll 1
+        for (int which = 0; which < 2; ++which) {
+            const uint8_t* src = prm.packed + (size_t)which * 2 * C * C + (size_t)rank * Cfg::W_HALF_BYTES;
+#pragma unroll 1
+            for (int kc = 0; kc < Cfg::KCH; ++kc)
+                ptx::bulk_g2s(w_u32 + which * Cfg::W_HALF_BYTES + kc * Cfg::W_CHUNK_BYTES,
+                              src + (size_t)kc * Cfg::W_CHUNK_BYTES, Cfg::W_CHUNK_BYTES, bar_w);
+        }
+    }
+    ptx::mbar_wait(bar_w, 0, WD_WEIGHTS);
+    __syncwarp();  // barrier.cluster.*.aligned needs converged warps
+    ptx::tc_fence_before_sync();
+    ptx::cluster_sync();  // peer's barriers initialised, peer's weights resident, both TMEM allocations done
     ptx::tc_fence_after_sync();
     const uint32_t tmem_base = *s_tmem;
 
@@ -125,12 +164,13 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
         const int half = threadIdx.x >> 7;  // which 4 of the 8 sixteen-byte chunks of a 128-byte row
         const long long per_b = (long long)prm.row_count * prm.n;
         const float4* s_div4 = (const float4*)s_div;
+        const uint32_t full_leader = ptx::map_to_cta(bar_full, 0);
         uint32_t q = 0;  // running chunk counter (stage ring position)
-        for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
+        for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
             float x[GEOTX_MAX_K + 1];
 #pragma unroll
             for (int s = 0; s <= GEOTX_MAX_K; ++s) x[s] = 0.f;
-            const long long p = (long long)tile * TILE_M + row;
+            const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
             if (p < prm.pairs_total) {
                 const long long b = p / per_b;
                 const long long rem = p - b * per_b;
@@ -149,8 +189,9 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
                 for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
                     const uint32_t stage = q % Cfg::NSTAGE;
                     const uint32_t phase = (q / Cfg::NSTAGE) & 1;
-                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, (1u << 24) | (q & 0xFFFFFF));
-                    const uint32_t a_row = stages_u32 + stage * Cfg::STAGE_BYTES + row * 128;
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (q & 0xFFFFFF));
+                    const uint32_t a_row = stages_u32 + stage * A_STAGE_BYTES + row * 128;
+#ifndef K2_DBG_NO_PRODUCE
 #pragma unroll
                     for (int gg = 0; gg < 4; ++gg) {
                         const int g = half * 4 + gg;
@@ -158,62 +199,82 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
                         // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
                         const float o0 = __fmul_rn(xv, w.x), o1 = __fmul_rn(xv, w.y);
                         const float o2 = __fmul_rn(xv, w.z), o3 = __fmul_rn(xv, w.w);
+#ifdef K2_DBG_NO_SINCOS  // timing experiments only (tools/k2_variants.sh)
+                        uint32_t v0 = pack_bf16x2(o0, o0 + 1.f), v1 = pack_bf16x2(o1, o1 + 1.f);
+                        uint32_t v2 = pack_bf16x2(o2, o2 + 1.f), v3 = pack_bf16x2(o3, o3 + 1.f);
+#else
                         uint32_t v0 = pack_bf16x2(__sinf(o0), __cosf(o0));
                         uint32_t v1 = pack_bf16x2(__sinf(o1), __cosf(o1));
                         uint32_t v2 = pack_bf16x2(__sinf(o2), __cosf(o2));
                         uint32_t v3 = pack_bf16x2(__sinf(o3), __cosf(o3));
+#endif
                         const uint32_t addr = a_row + ((g ^ (row & 7)) << 4);
                         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v0), "r"(v1),
                                      "r"(v2), "r"(v3)
                                      : "memory");
                     }
+#endif
+#ifndef K2_DBG_NO_FENCE
                     ptx::fence_proxy_async_smem();  // make the st.shared visible to the tensor core (async proxy)
+#endif
                     __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(bar_full + 8 * stage);
+                    if (lane == 0) ptx::mbar_arrive_cluster(full_leader + 8 * stage);
                 }
             }
         }
     } else if (warp < NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS) {
         // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");
         constexpr int NCOL = Cfg::COLS_PER_THREAD;
         const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 belong to this warp
         const int colhalf = (warp - NUM_PRODUCER_WARPS) >> 2;
         const int row = quarter * 32 + lane;
         const int groups = prm.reduce_mean ? 2 : slots;
         const float inv_k = 1.0f / (float)k;
+        const uint32_t acc_empty_leader = ptx::map_to_cta(bar_acc_empty, 0);
         float run[NCOL];
         uint32_t gc = 0;  // running accumulation-group counter (TMEM buffer ring position)
-        for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
+        for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
             for (int g = 0; g < groups; ++g, ++gc) {
                 const uint32_t buf = gc & 1, phase = (gc >> 1) & 1;
-                ptx::mbar_wait(bar_acc_full + 8 * buf, phase, (2u << 24) | (gc & 0xFFFFFF));
+                ptx::mbar_wait(bar_acc_full + 8 * buf, phase, WD_EPILOGUE | (gc & 0xFFFFFF));
                 ptx::tc_fence_after_sync();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * C + colhalf * NCOL;
+#ifndef K2_DBG_NO_EPI_LD
 #pragma unroll
-                for (int c0 = 0; c0 < NCOL; c0 += 16) {
-                    uint32_t v[16];
-                    ptx::tmem_ld16(taddr + c0, v);
+                for (int c0 = 0; c0 < NCOL; c0 += 8) {
+                    uint32_t v[8];
+                    ptx::tmem_ld8(taddr + c0, v);
                     ptx::tmem_ld_wait();
                     if (prm.reduce_mean) {
 #pragma unroll
-                        for (int c = 0; c < 16; ++c)
+                        for (int c = 0; c < 8; ++c)
                             run[c0 + c] = (g == 0) ? __uint_as_float(v[c]) * inv_k : run[c0 + c] + __uint_as_float(v[c]);
                     } else {
 #pragma unroll
-                        for (int c = 0; c < 16; ++c) {
+                        for (int c = 0; c < 8; ++c) {
                             const float a = __uint_as_float(v[c]);
                             run[c0 + c] = (g == 0) ? a : ((g < k) ? fmaxf(run[c0 + c], a) : run[c0 + c] + a);
                         }
                     }
                 }
+#else
+                if (g == 0) {
+#pragma unroll
+                    for (int c = 0; c < NCOL; ++c) run[c] = (float)(c + lane);
+                }
+#endif
                 ptx::tc_fence_before_sync();
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(bar_acc_empty + 8 * buf);
+                if (lane == 0) ptx::mbar_arrive_cluster(acc_empty_leader + 8 * buf);
             }
             // E = (W_d s_d + max_k W_a s_a) + (b_d + b_a)
-            const long long p = (long long)tile * TILE_M + row;
+            const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
+#ifdef K2_DBG_NO_EPI_STORE
+            if (p < prm.pairs_total && run[0] == 123.456f) {
+#else
             if (p < prm.pairs_total) {
+#endif
                 const float4* bias4 = (const float4*)(s_bias + colhalf * NCOL);
                 if (prm.out_bf16) {
                     uint4* dst = (uint4*)((__nv_bfloat16*)prm.out + p * C + colhalf * NCOL);
@@ -238,71 +299,54 @@ __global__ void __launch_bounds__(K2_THREADS, 1) gse_embed_tc_kernel(const __gri
             }
         }
     } else {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
-        if (warp == 16) {
-            // =============================== MMA ISSUER (one thread) ============================================
-            if (lane == 0) {
-                constexpr uint32_t idesc = ptx::umma_idesc_bf16(TILE_M, C);
-                uint32_t q = 0, gc = 0;
-                for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
-                    for (int s = 0; s < slots; ++s) {
-                        const bool first = prm.reduce_mean ? (s == 0 || s == k) : true;
-                        const bool last = prm.reduce_mean ? (s == k - 1 || s == k) : true;
-                        const uint32_t buf = gc & 1;
-                        if (first) {
-                            ptx::mbar_wait(bar_acc_empty + 8 * buf, ((gc >> 1) & 1) ^ 1, (3u << 24) | (gc & 0xFFFFFF));
-                            ptx::tc_fence_after_sync();
-                        }
-                        const uint32_t tmem_d = tmem_base + buf * C;
-                        for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
-                            const uint32_t stage = q % Cfg::NSTAGE;
-                            ptx::mbar_wait(bar_full + 8 * stage, (q / Cfg::NSTAGE) & 1, (4u << 24) | (q & 0xFFFFFF));
-                            ptx::tc_fence_after_sync();
-                            const uint32_t a_addr = stages_u32 + stage * Cfg::STAGE_BYTES;
-                            const uint64_t adesc = ptx::umma_desc_sw128(a_addr);
-                            const uint64_t bdesc = ptx::umma_desc_sw128(a_addr + A_STAGE_BYTES);
-#pragma unroll
-                            for (int ks = 0; ks < KCHUNK / 16; ++ks) {
-                                // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzled row: +2 (16-B units)
-                                ptx::umma_bf16(tmem_d, adesc + 2 * ks, bdesc + 2 * ks, idesc,
-                                               (uint32_t)(!(first && kc == 0 && ks == 0)));
-                            }
-                            ptx::umma_commit(bar_empty + 8 * stage);  // stage reusable once these MMAs retire
-                        }
-                        if (last) {
-                            ptx::umma_commit(bar_acc_full + 8 * buf);
-                            ++gc;
-                        }
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 16 && rank == 0 && lane == 0) {
+            // =============================== MMA ISSUER (one thread of the leader CTA) ===========================
+            constexpr uint32_t idesc = ptx::umma_idesc_bf16(2 * TILE_M, C);
+            uint32_t q = 0, gc = 0;
+            for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
+                for (int s = 0; s < slots; ++s) {
+                    const bool first = prm.reduce_mean ? (s == 0 || s == k) : true;
+                    const bool last = prm.reduce_mean ? (s == k - 1 || s == k) : true;
+                    const uint32_t buf = gc & 1;
+                    if (first) {
+                        ptx::mbar_wait(bar_acc_empty + 8 * buf, ((gc >> 1) & 1) ^ 1, WD_MMA_ACC | (gc & 0xFFFFFF));
+                        ptx::tc_fence_after_sync();
                     }
-                }
-            }
-        } else if (warp == 17) {
-            // =============================== WEIGHT LOADER (TMA unit bulk copies) ================================
-            if (lane == 0) {
-                uint32_t q = 0;
-                for (int tile = blockIdx.x; tile < prm.num_tiles; tile += gridDim.x) {
-                    for (int s = 0; s < slots; ++s) {
-                        const uint8_t* img = prm.packed + (s < k ? 0 : (size_t)2 * C * C);  // W_a | W_d
-                        for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
-                            const uint32_t stage = q % Cfg::NSTAGE;
-                            ptx::mbar_wait(bar_empty + 8 * stage, ((q / Cfg::NSTAGE) & 1) ^ 1, (5u << 24) | (q & 0xFFFFFF));
-                            ptx::mbar_arrive_expect_tx(bar_full + 8 * stage, Cfg::B_STAGE_BYTES);
-                            ptx::bulk_g2s(stages_u32 + stage * Cfg::STAGE_BYTES + A_STAGE_BYTES,
-                                          img + (size_t)kc * Cfg::B_STAGE_BYTES, Cfg::B_STAGE_BYTES,
-                                          bar_full + 8 * stage);
+                    const uint32_t tmem_d = tmem_base + buf * C;
+                    const uint32_t w_mat = w_u32 + (s < k ? 0 : Cfg::W_HALF_BYTES);  // W_a | W_d
+                    for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
+                        const uint32_t stage = q % Cfg::NSTAGE;
+                        ptx::mbar_wait(bar_full + 8 * stage, (q / Cfg::NSTAGE) & 1, WD_MMA_FULL | (q & 0xFFFFFF));
+                        ptx::tc_fence_after_sync();
+                        const uint64_t adesc = ptx::umma_desc_sw128(stages_u32 + stage * A_STAGE_BYTES);
+                        const uint64_t bdesc = ptx::umma_desc_sw128(w_mat + kc * Cfg::W_CHUNK_BYTES);
+#ifndef K2_DBG_NO_MMA
+#pragma unroll
+                        for (int ks = 0; ks < KCHUNK / 16; ++ks) {
+                            // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzled row: +2 (16-B units)
+                            ptx::umma_bf16_pair(tmem_d, adesc + 2 * ks, bdesc + 2 * ks, idesc,
+                                                (uint32_t)(!(first && kc == 0 && ks == 0)));
                         }
+#endif
+                        ptx::umma_commit_pair(bar_empty + 8 * stage, 3);  // stage reusable in both CTAs
+                    }
+                    if (last) {
+                        ptx::umma_commit_pair(bar_acc_full + 8 * buf, 3);
+                        ++gc;
                     }
                 }
             }
         }
     }
 
-    // ---- teardown ----
+    // ---- teardown: nobody may leave while the peer can still read our smem / arrive on our barriers ----
+    __syncwarp();  // reconverge the single-thread roles: barrier.cluster.*.aligned needs converged warps
     ptx::tc_fence_before_sync();
-    __syncthreads();
+    ptx::cluster_sync();
     if (warp == 18) {
         ptx::tc_fence_after_sync();
-        ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+        ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
     }
 }
 
@@ -353,8 +397,10 @@ static int launch_k2(const K2Params& prm, cudaStream_t st) {
                                              Cfg::SMEM_BYTES), "cudaFuncSetAttribute(gse_embed_tc_kernel)");
         if (rc) { num_sms = 0; return rc; }
     }
-    int grid = prm.num_tiles < num_sms ? prm.num_tiles : num_sms;  // persistent: one CTA per SM
-    gse_embed_tc_kernel<C><<<grid, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
+    // persistent: one CTA pair per SM pair (cluster of 2, same TPC)
+    int clusters = num_sms / 2;
+    if (prm.num_tile_pairs < clusters) clusters = prm.num_tile_pairs;
+    gse_embed_tc_kernel<C><<<2 * clusters, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
     return launch_status("geotx_gse_embed");
 }
 
@@ -379,7 +425,7 @@ extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int ro
     prm.n = n; prm.k = k; prm.row_begin = row_begin; prm.row_count = row_count;
     long long tiles = (prm.pairs_total + TILE_M - 1) / TILE_M;
     GEOTX_REQUIRE(tiles < 2147483647LL, "geotx_gse_embed: too many pairs");
-    prm.num_tiles = (int)tiles;
+    prm.num_tile_pairs = (int)((tiles + 1) / 2);
     prm.sigma_d = sigma_d; prm.factor_a = factor_a;
     prm.reduce_mean = reduce_mean ? 1 : 0;
     prm.out_bf16 = out_dtype == GEOTX_BF16;

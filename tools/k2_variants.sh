@@ -1,0 +1,15 @@
+#!/bin/bash
+# Builds timing-experiment variants of the library (K2_DBG_* switches; wrong results by design) into tools/bin/variants.
+set -e
+cd "$(dirname "$0")/.."
+mkdir -p tools/bin/variants
+SRC=ref-geotransformer_b200/csrc
+for v in "$@"; do
+  flags=""
+  for f in $(echo $v | tr '+' ' '); do flags="$flags -DK2_DBG_$f"; done
+  nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Xcompiler -fPIC -shared $flags \
+    $SRC/abi.cu $SRC/k1_knn.cu $SRC/k2_gse_embed_fp32.cu $SRC/k2_gse_embed.cu $SRC/k3_rpe_scores.cu $SRC/k3_attention.cu \
+    -o tools/bin/variants/lib_$v.so -lcudart &
+done
+wait
+ls tools/bin/variants
