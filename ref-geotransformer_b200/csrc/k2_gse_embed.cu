@@ -19,6 +19,7 @@
 // (warp-8)/4), 16 MMA issuer (leader CTA only), 17 weight loader (one bulk copy at start), 18 TMEM allocator, 19 idle.
 // Cross-CTA signalling: producers / epilogue warps of the peer CTA arrive remotely on the leader's mbarriers
 // (mapa + mbarrier.arrive.release.cluster); tcgen05.commit multicasts "stage free" / "accumulator ready" to both.
+#include <cuda_fp16.h>
 #include "geotx_common.cuh"
 #include "sm100_ptx.cuh"
 #include "host_util.h"
@@ -159,7 +160,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
 
     if (warp < NUM_PRODUCER_WARPS) {
         // =============================== PRODUCERS: sinusoid rows -> swizzled smem ===============================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
         const int row = threadIdx.x & (TILE_M - 1);
         const int half = threadIdx.x >> 7;  // which 4 of the 8 sixteen-byte chunks of a 128-byte row
         const long long per_b = (long long)prm.row_count * prm.n;
@@ -189,28 +190,37 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
                     const uint32_t stage = q % Cfg::NSTAGE;
                     const uint32_t phase = (q / Cfg::NSTAGE) & 1;
-                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (q & 0xFFFFFF));
-                    const uint32_t a_row = stages_u32 + stage * A_STAGE_BYTES + row * 128;
+                    // 16 frequencies (4 sixteen-byte chunks of this row) are generated in registers BEFORE the stage
+                    // is known to be free: the MUFU work never waits on the ring.
+                    uint32_t v[4][4];
 #ifndef K2_DBG_NO_PRODUCE
+                    float4 w[4];
+#pragma unroll
+                    for (int gg = 0; gg < 4; ++gg) w[gg] = s_div4[kc * 8 + half * 4 + gg];
 #pragma unroll
                     for (int gg = 0; gg < 4; ++gg) {
-                        const int g = half * 4 + gg;
-                        const float4 w = s_div4[kc * 8 + g];  // 4 frequencies = 8 bf16 = one 16-byte chunk
                         // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
-                        const float o0 = __fmul_rn(xv, w.x), o1 = __fmul_rn(xv, w.y);
-                        const float o2 = __fmul_rn(xv, w.z), o3 = __fmul_rn(xv, w.w);
+                        const float o0 = __fmul_rn(xv, w[gg].x), o1 = __fmul_rn(xv, w[gg].y);
+                        const float o2 = __fmul_rn(xv, w[gg].z), o3 = __fmul_rn(xv, w[gg].w);
 #ifdef K2_DBG_NO_SINCOS  // timing experiments only (tools/k2_variants.sh)
-                        uint32_t v0 = pack_bf16x2(o0, o0 + 1.f), v1 = pack_bf16x2(o1, o1 + 1.f);
-                        uint32_t v2 = pack_bf16x2(o2, o2 + 1.f), v3 = pack_bf16x2(o3, o3 + 1.f);
+                        v[gg][0] = pack_bf16x2(o0, o0 + 1.f); v[gg][1] = pack_bf16x2(o1, o1 + 1.f);
+                        v[gg][2] = pack_bf16x2(o2, o2 + 1.f); v[gg][3] = pack_bf16x2(o3, o3 + 1.f);
 #else
-                        uint32_t v0 = pack_bf16x2(__sinf(o0), __cosf(o0));
-                        uint32_t v1 = pack_bf16x2(__sinf(o1), __cosf(o1));
-                        uint32_t v2 = pack_bf16x2(__sinf(o2), __cosf(o2));
-                        uint32_t v3 = pack_bf16x2(__sinf(o3), __cosf(o3));
+                        v[gg][0] = pack_bf16x2(__sinf(o0), __cosf(o0));
+                        v[gg][1] = pack_bf16x2(__sinf(o1), __cosf(o1));
+                        v[gg][2] = pack_bf16x2(__sinf(o2), __cosf(o2));
+                        v[gg][3] = pack_bf16x2(__sinf(o3), __cosf(o3));
 #endif
-                        const uint32_t addr = a_row + ((g ^ (row & 7)) << 4);
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v0), "r"(v1),
-                                     "r"(v2), "r"(v3)
+                    }
+#endif
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (q & 0xFFFFFF));
+#ifndef K2_DBG_NO_PRODUCE
+                    const uint32_t a_row = stages_u32 + stage * A_STAGE_BYTES + row * 128;
+#pragma unroll
+                    for (int gg = 0; gg < 4; ++gg) {
+                        const uint32_t addr = a_row + (((half * 4 + gg) ^ (row & 7)) << 4);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v[gg][0]),
+                                     "r"(v[gg][1]), "r"(v[gg][2]), "r"(v[gg][3])
                                      : "memory");
                     }
 #endif
@@ -224,78 +234,92 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         }
     } else if (warp < NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS) {
         // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");
+        // The running reduction over the k angle slots is kept as packed f16x2 (11-bit mantissa: 4x finer than the bf16
+        // the result is stored in), which halves its register footprint -- the registers go to the producers.
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
         constexpr int NCOL = Cfg::COLS_PER_THREAD;
         const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 belong to this warp
         const int colhalf = (warp - NUM_PRODUCER_WARPS) >> 2;
         const int row = quarter * 32 + lane;
         const int groups = prm.reduce_mean ? 2 : slots;
-        const float inv_k = 1.0f / (float)k;
+        const float inv_k = prm.reduce_mean ? 1.0f / (float)k : 1.0f;
         const uint32_t acc_empty_leader = ptx::map_to_cta(bar_acc_empty, 0);
-        float run[NCOL];
+        __half2 run[NCOL / 2];
         uint32_t gc = 0;  // running accumulation-group counter (TMEM buffer ring position)
         for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
+            const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
             for (int g = 0; g < groups; ++g, ++gc) {
                 const uint32_t buf = gc & 1, phase = (gc >> 1) & 1;
                 ptx::mbar_wait(bar_acc_full + 8 * buf, phase, WD_EPILOGUE | (gc & 0xFFFFFF));
                 ptx::tc_fence_after_sync();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * C + colhalf * NCOL;
+                if (g < groups - 1) {
+                    // angle groups: running max (or the single pre-summed group of 'mean')
 #ifndef K2_DBG_NO_EPI_LD
 #pragma unroll
-                for (int c0 = 0; c0 < NCOL; c0 += 8) {
-                    uint32_t v[8];
-                    ptx::tmem_ld8(taddr + c0, v);
-                    ptx::tmem_ld_wait();
-                    if (prm.reduce_mean) {
+                    for (int c0 = 0; c0 < NCOL; c0 += 16) {
+                        uint32_t v[16];
+                        ptx::tmem_ld16(taddr + c0, v);
+                        ptx::tmem_ld_wait();
 #pragma unroll
-                        for (int c = 0; c < 8; ++c)
-                            run[c0 + c] = (g == 0) ? __uint_as_float(v[c]) * inv_k : run[c0 + c] + __uint_as_float(v[c]);
-                    } else {
+                        for (int c = 0; c < 16; c += 2) {
+                            const __half2 a = __floats2half2_rn(__uint_as_float(v[c]) * inv_k,
+                                                                __uint_as_float(v[c + 1]) * inv_k);
+                            run[(c0 + c) / 2] = (g == 0) ? a : __hmax2(run[(c0 + c) / 2], a);
+                        }
+                    }
+#else
+                    if (g == 0) {
 #pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            const float a = __uint_as_float(v[c]);
-                            run[c0 + c] = (g == 0) ? a : ((g < k) ? fmaxf(run[c0 + c], a) : run[c0 + c] + a);
+                        for (int c = 0; c < NCOL / 2; ++c) run[c] = __floats2half2_rn((float)(c + lane), 1.f);
+                    }
+#endif
+                } else {
+                    // distance group: E = (W_d s_d) + reduce_k(W_a s_a) + (b_d + b_a), straight to HBM in 32-byte pieces
+                    const float4* bias4 = (const float4*)(s_bias + colhalf * NCOL);
+#ifdef K2_DBG_NO_EPI_STORE
+                    const bool do_store = p < prm.pairs_total && __low2float(run[0]) == 123.456f;
+#else
+                    const bool do_store = p < prm.pairs_total;
+#endif
+#pragma unroll
+                    for (int c0 = 0; c0 < NCOL; c0 += 16) {
+                        float e[16];
+#ifndef K2_DBG_NO_EPI_LD
+                        uint32_t v[16];
+                        ptx::tmem_ld16(taddr + c0, v);
+                        ptx::tmem_ld_wait();
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) e[c] = __uint_as_float(v[c]);
+#else
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) e[c] = 1.f;
+#endif
+#pragma unroll
+                        for (int c = 0; c < 16; c += 4) {
+                            const float4 bb = bias4[(c0 + c) / 4];
+                            const float2 r0 = __half22float2(run[(c0 + c) / 2]);
+                            const float2 r1 = __half22float2(run[(c0 + c) / 2 + 1]);
+                            e[c] += r0.x + bb.x; e[c + 1] += r0.y + bb.y;
+                            e[c + 2] += r1.x + bb.z; e[c + 3] += r1.y + bb.w;
+                        }
+                        if (do_store) {
+                            if (prm.out_bf16) {
+                                uint32_t o[8];
+#pragma unroll
+                                for (int c = 0; c < 8; ++c) o[c] = pack_bf16x2(e[2 * c], e[2 * c + 1]);
+                                st_global_v8((__nv_bfloat16*)prm.out + p * C + colhalf * NCOL + c0, o);
+                            } else {
+                                float* dst = (float*)prm.out + p * C + colhalf * NCOL + c0;
+                                st_global_v8(dst, (const uint32_t*)e);
+                                st_global_v8(dst + 8, (const uint32_t*)e + 8);
+                            }
                         }
                     }
                 }
-#else
-                if (g == 0) {
-#pragma unroll
-                    for (int c = 0; c < NCOL; ++c) run[c] = (float)(c + lane);
-                }
-#endif
                 ptx::tc_fence_before_sync();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive_cluster(acc_empty_leader + 8 * buf);
-            }
-            // E = (W_d s_d + max_k W_a s_a) + (b_d + b_a)
-            const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
-#ifdef K2_DBG_NO_EPI_STORE
-            if (p < prm.pairs_total && run[0] == 123.456f) {
-#else
-            if (p < prm.pairs_total) {
-#endif
-                const float4* bias4 = (const float4*)(s_bias + colhalf * NCOL);
-                if (prm.out_bf16) {
-                    uint4* dst = (uint4*)((__nv_bfloat16*)prm.out + p * C + colhalf * NCOL);
-#pragma unroll
-                    for (int c = 0; c < NCOL; c += 8) {
-                        const float4 b0 = bias4[c / 4], b1 = bias4[c / 4 + 1];
-                        uint4 o;
-                        o.x = pack_bf16x2(run[c] + b0.x, run[c + 1] + b0.y);
-                        o.y = pack_bf16x2(run[c + 2] + b0.z, run[c + 3] + b0.w);
-                        o.z = pack_bf16x2(run[c + 4] + b1.x, run[c + 5] + b1.y);
-                        o.w = pack_bf16x2(run[c + 6] + b1.z, run[c + 7] + b1.w);
-                        dst[c / 8] = o;
-                    }
-                } else {
-                    float4* dst = (float4*)((float*)prm.out + p * C + colhalf * NCOL);
-#pragma unroll
-                    for (int c = 0; c < NCOL; c += 4) {
-                        const float4 b0 = bias4[c / 4];
-                        dst[c / 4] = make_float4(run[c] + b0.x, run[c + 1] + b0.y, run[c + 2] + b0.z, run[c + 3] + b0.w);
-                    }
-                }
             }
         }
     } else {
@@ -413,8 +437,8 @@ extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int ro
                   "256); use geotx_gse_embed_fp32", C);
     GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed: bad row slab");
     GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16, "geotx_gse_embed: bad out_dtype");
-    GEOTX_REQUIRE(((uintptr_t)out & 15) == 0 && ((uintptr_t)packed_weights & 15) == 0,
-                  "geotx_gse_embed: out / packed_weights must be 16-byte aligned");
+    GEOTX_REQUIRE(((uintptr_t)out & 31) == 0 && ((uintptr_t)packed_weights & 15) == 0,
+                  "geotx_gse_embed: out must be 32-byte and packed_weights 16-byte aligned");
     K2Params prm;
     prm.pts4 = (const float4*)geometry;
     prm.refv = prm.pts4 + (size_t)B * n;
