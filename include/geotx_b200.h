@@ -99,10 +99,14 @@ int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, 
 /* rpe_transformer.py:57-70 / vanilla_transformer.py:54-68: softmax((q k^T + scores_p) * scale [masked]) v.
  *   q f32 [B,n,H*c] (token-major, heads interleaved as in 'b n (h c)'), k,v f32 [B,m,H*c],
  *   scores_p f32 [B,H,n,m] or NULL, key_mask u8 [B,m] or NULL (non-zero = ignore),
- *   out f32 [B,n,H*c].  c (per-head dim) in {32, 64}. */
+ *   out f32 [B,n,H*c].  c (per-head dim) in {16, 32, 64}.
+ *   workspace: geotx_attention_workspace_bytes() bytes of scratch, or NULL.  With a workspace the key range is split
+ *   over several CTAs per (query tile, head) (partial softmax states merged by a second kernel), which is what keeps
+ *   148 SMs busy when n is about a thousand; with NULL one CTA walks all keys.  Same result up to fp32 rounding. */
+int64_t geotx_attention_workspace_bytes(int B, int H, int n, int m, int c);
 int geotx_attention(const float* q, const float* k, const float* v, const float* scores_p,
                     const uint8_t* key_mask, int B, int H, int n, int m, int c, float scale, float* out,
-                    void* stream);
+                    void* workspace, void* stream);
 
 #ifdef __cplusplus
 }

@@ -27,14 +27,15 @@ SIGNATURES = {
     'geotx_watchdog_status': (_i, [_p]),
     'geotx_gse_embed_fp32': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
     'geotx_rpe_scores': (_i, [_p, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
-    'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p]),
+    'geotx_attention_workspace_bytes': (_i64, [_i, _i, _i, _i, _i]),
+    'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p]),
 }
 
 GEOTX_F32 = 0
 GEOTX_BF16 = 1
 
 # kernels each entry point enqueues (bench.py's gpu_launches is counted from this)
-KERNELS_PER_CALL = {'geotx_gse_knn': 2}
+KERNELS_PER_CALL = {'geotx_gse_knn': 2, 'geotx_attention': 2}  # attention: + merge kernel when the keys are split
 
 _lib = None
 launch_count = 0  # hand-written kernels launched through this binding so far

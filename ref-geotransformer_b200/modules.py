@@ -45,6 +45,24 @@ def build_dropout_layer(p, **kwargs):
     return nn.Dropout(p=p, **kwargs)
 
 
+class _dense_precision:
+    """The small dense layers (C x C Linears; <0.5 % of the path's flops) go through cuBLASLt.  On the bf16 / tensor-core
+    path they run as TF32 tensor-core GEMMs (10-bit mantissa, fp32 accumulate; the module's outputs stay within 1e-4 of
+    the reference); with precision='fp32' they stay exact fp32.  Restores the caller's global setting on exit."""
+
+    def __init__(self, allow_tf32):
+        self.allow = allow_tf32
+
+    def __enter__(self):
+        self.prev = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = self.allow
+        return self
+
+    def __exit__(self, *exc):
+        torch.backends.cuda.matmul.allow_tf32 = self.prev
+        return False
+
+
 def _forward_only_guard(module, *tensors):
     if not torch.is_grad_enabled():
         return
@@ -386,11 +404,13 @@ class GeometricTransformer(nn.Module):
 
     def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
         _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
-        e_dtype = torch.bfloat16 if self.embedding._use_tensor_cores() else torch.float32
+        tc = self.embedding._use_tensor_cores()
+        e_dtype = torch.bfloat16 if tc else torch.float32
         ref_embeddings = self.embedding.embed(self.embedding.geometry(ref_points), e_dtype)
         src_embeddings = self.embedding.embed(self.embedding.geometry(src_points), e_dtype)
-        ref_feats = self.in_proj(ref_feats)
-        src_feats = self.in_proj(src_feats)
-        ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
-                                                masks0=ref_masks, masks1=src_masks)
-        return self.out_proj(ref_feats), self.out_proj(src_feats)
+        with _dense_precision(allow_tf32=tc):
+            ref_feats = self.in_proj(ref_feats)
+            src_feats = self.in_proj(src_feats)
+            ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
+                                                    masks0=ref_masks, masks1=src_masks)
+            return self.out_proj(ref_feats), self.out_proj(src_feats)

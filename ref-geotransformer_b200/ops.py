@@ -139,7 +139,7 @@ def rpe_scores(qt, E, n=None, row_begin=0, out=None):
     return out
 
 
-def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None):
+def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None, split_keys=True):
     """q (B,n,H*c), k,v (B,m,H*c) fp32 token-major -> (B,n,H*c).  softmax((q k^T + scores_p)*scale) v.
     rpe_transformer.py:57-70, vanilla_transformer.py:54-68."""
     _check(q, 'q', torch.float32, 3)
@@ -159,6 +159,8 @@ def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None):
         mask_u8 = _check(key_mask.to(torch.uint8).contiguous(), 'key_mask')
     scale = 1.0 / (c ** 0.5) if scale is None else scale
     out = torch.empty_like(q)
+    ws_bytes = _abi.load().geotx_attention_workspace_bytes(B, num_heads, n, m, c)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device) if (ws_bytes > 0 and split_keys) else None
     _abi.call('geotx_attention', _p(q), _p(k), _p(v), _p(scores_p), _p(mask_u8), B, num_heads, n, m, c,
-              float(scale), _p(out), _stream())
+              float(scale), _p(out), _p(ws), _stream())
     return out
