@@ -11,6 +11,7 @@
 // accumulate, rows of the A fragment = heads).  The folded query is split into bf16 hi + lo parts so that its
 // rounding does not add to the error budget (E itself is the only bf16-rounded operand).
 #include "geotx_common.cuh"
+#include "sm100_ptx.cuh"
 #include "host_util.h"
 
 namespace geotx {
@@ -33,82 +34,135 @@ __device__ __forceinline__ uint4 ldg_stream16(const void* p) {
     return r;
 }
 
-// grid.x = ceil(rows * nsplit / K3A_WARPS); warp -> (slab row r, j-split sp).
+// Streaming structure: the kernel is HBM-bound, so what matters is bytes in flight, not registers.  Every warp owns a
+// private ring of K3A_STAGES shared-memory stages and is its own producer: lane 0 asks the TMA unit (cp.async.bulk) for
+// the next 16 key rows of E (16 x 2C bytes, contiguous in HBM) while the warp contracts the previous ones, completion
+// signalled on a per-stage mbarrier.  8 warps x 3 stages x 8 KB keep ~190 KB per SM in flight (Little's law needs ~40).
+// One bulk copy per chunk: per-row copies into a padded (conflict-free) layout were TMA-issue-bound (72 % of HBM peak);
+// the unpadded layout costs a 2-way bank conflict on the fragment reads, which need <1/4 of the smem bandwidth anyway.
+// Work is split into chunks of 16 keys of one query row; each warp takes a contiguous range of chunks (persistent grid,
+// one CTA per SM), reloading its folded-query fragments only when the row changes.
+//
 // Channel permutation: lane (g = lane/4, t = lane%4) owns channels 32 s + 8 t + [0,8) of E row j0+g for every s;
 // the two k16 steps of chunk s use the 8 channels as k-slots {2t,2t+1 | 2t+8,2t+9}.  Any fixed permutation of
 // the contraction index is legal as long as A (the folded query) uses the same one, which it does.
-template <int C>
-__global__ void __launch_bounds__(K3A_WARPS * 32)
-rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qsh, const __nv_bfloat16* __restrict__ E, int H, int n, int m,
-                       int row_begin, int row_count, int rows_total, int nsplit, int jchunk,
-                       float* __restrict__ scores) {
-    constexpr int S = C / 32;
-    const int lane = threadIdx.x & 31;
-    const int g = lane >> 2, t = lane & 3;
-    const int wid = blockIdx.x * K3A_WARPS + (threadIdx.x >> 5);
-    const int r = wid / nsplit;
-    if (r >= rows_total) return;
-    const int sp = wid - r * nsplit;
-    const int b = r / row_count;
-    const int il = r - b * row_count;   // row inside the slab
-    const int i = row_begin + il;       // query row in the cloud
+constexpr int K3A_STAGES = 3;
+constexpr int K3A_KEYS = 16;  // keys per chunk / stage
 
-    // A fragments: folded query of (b, h = g, i), hi/lo bf16 split
-    uint32_t ah[S][4], al[S][4];
-    if (g < H) {
-        const float* qrow = qt + (size_t)b * qsb + (size_t)g * qsh + (size_t)i * C + 8 * t;
-#pragma unroll
-        for (int s = 0; s < S; ++s) {
-            const float4 u = __ldg((const float4*)(qrow + 32 * s));
-            const float4 v = __ldg((const float4*)(qrow + 32 * s + 4));
-            const float f[8] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float h0 = __bfloat162float(__float2bfloat16_rn(f[2 * e]));
-                const float h1 = __bfloat162float(__float2bfloat16_rn(f[2 * e + 1]));
-                ah[s][e] = pack_bf16x2(h0, h1);
-                al[s][e] = pack_bf16x2(f[2 * e] - h0, f[2 * e + 1] - h1);
-            }
-        }
-    } else {
-#pragma unroll
-        for (int s = 0; s < S; ++s)
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { ah[s][e] = 0u; al[s][e] = 0u; }
+template <int C>
+struct K3ACfg {
+    static constexpr int ROW_BYTES = 2 * C;
+    static constexpr int PITCH = ROW_BYTES;  // one bulk copy per chunk; the 2-way bank conflict of the reads is free here
+    static constexpr int STAGE_BYTES = K3A_KEYS * PITCH;
+    static constexpr int SMEM_BYTES = K3A_WARPS * K3A_STAGES * STAGE_BYTES + K3A_WARPS * K3A_STAGES * 8 + 128;
+};
+
+template <int C>
+__global__ void __launch_bounds__(K3A_WARPS * 32, 1)
+rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qsh, const __nv_bfloat16* __restrict__ E,
+                       int H, int n, int m, int row_begin, int row_count, long long chunks_total, int chunks_per_row,
+                       long long chunks_per_warp, float* __restrict__ scores) {
+    using Cfg = K3ACfg<C>;
+    constexpr int S = C / 32;
+    extern __shared__ __align__(128) uint8_t k3a_smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    uint8_t* ring = k3a_smem + (size_t)warp * K3A_STAGES * Cfg::STAGE_BYTES;
+    const uint32_t ring_u32 = smem_u32(ring);
+    const uint32_t bars = smem_u32(k3a_smem + (size_t)K3A_WARPS * K3A_STAGES * Cfg::STAGE_BYTES) + warp * K3A_STAGES * 8;
+
+    const long long wid = (long long)blockIdx.x * K3A_WARPS + warp;
+    const long long c_begin = wid * chunks_per_warp;
+    long long c_end = c_begin + chunks_per_warp;
+    if (c_end > chunks_total) c_end = chunks_total;
+    if (lane == 0) {
+        for (int s = 0; s < K3A_STAGES; ++s) ptx::mbar_init(bars + 8 * s, 1);
+        ptx::fence_barrier_init();
+    }
+    __syncwarp();
+    if (c_begin >= c_end) return;
+
+    // lane 0: ask the TMA unit for chunk c (up to 16 key rows of one query row) into stage c % K3A_STAGES
+    auto issue = [&](long long c) {
+        const long long r = c / chunks_per_row;
+        const int j0 = (int)(c - r * chunks_per_row) * K3A_KEYS;
+        const int keys = min(K3A_KEYS, m - j0);
+        const uint32_t st = (uint32_t)((c - c_begin) % K3A_STAGES);
+        const uint32_t dst = ring_u32 + st * Cfg::STAGE_BYTES;
+        const uint8_t* src = (const uint8_t*)E + ((size_t)r * m + j0) * Cfg::ROW_BYTES;
+        ptx::mbar_arrive_expect_tx(bars + 8 * st, (uint32_t)keys * Cfg::ROW_BYTES);
+        ptx::bulk_g2s(dst, src, (uint32_t)keys * Cfg::ROW_BYTES, bars + 8 * st);
+    };
+    if (lane == 0) {
+        for (int s = 0; s < K3A_STAGES; ++s)
+            if (c_begin + s < c_end) issue(c_begin + s);
     }
 
-    const __nv_bfloat16* Erow = E + ((size_t)r * m) * C + 8 * t;  // E slab is [B*row_count][m][C]
-    float* srow = scores + (((size_t)b * H + g) * n + i) * m;
-    const int j_begin = sp * jchunk;
-    const int j_end = min(m, j_begin + jchunk);
-
-    for (int j0 = j_begin; j0 < j_end; j0 += 16) {
-        uint4 e0[S], e1[S];
-        const int ja = j0 + g, jb = j0 + 8 + g;
-        const bool va = ja < j_end, vb = jb < j_end;
+    uint32_t ah[S][4], al[S][4];
+    long long cur_row = -1;
+    float* srow = nullptr;
+    for (long long c = c_begin; c < c_end; ++c) {
+        const long long r = c / chunks_per_row;
+        const int j0 = (int)(c - r * chunks_per_row) * K3A_KEYS;
+        if (r != cur_row) {
+            // A fragments: folded query of (b, h = g, i), hi/lo bf16 split
+            cur_row = r;
+            const int b = (int)(r / row_count);
+            const int i = row_begin + (int)(r - (long long)b * row_count);
+            srow = scores + (((size_t)b * H + g) * n + i) * m;
+            if (g < H) {
+                const float* qrow = qt + (size_t)b * qsb + (size_t)g * qsh + (size_t)i * C + 8 * t;
 #pragma unroll
-        for (int s = 0; s < S; ++s) {
-            e0[s] = va ? ldg_stream16(Erow + (size_t)ja * C + 32 * s) : make_uint4(0, 0, 0, 0);
-            e1[s] = vb ? ldg_stream16(Erow + (size_t)jb * C + 32 * s) : make_uint4(0, 0, 0, 0);
+                for (int s = 0; s < S; ++s) {
+                    const float4 u = __ldg((const float4*)(qrow + 32 * s));
+                    const float4 v = __ldg((const float4*)(qrow + 32 * s + 4));
+                    const float f[8] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float h0 = __bfloat162float(__float2bfloat16_rn(f[2 * e]));
+                        const float h1 = __bfloat162float(__float2bfloat16_rn(f[2 * e + 1]));
+                        ah[s][e] = pack_bf16x2(h0, h1);
+                        al[s][e] = pack_bf16x2(f[2 * e] - h0, f[2 * e + 1] - h1);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int s = 0; s < S; ++s)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) { ah[s][e] = 0u; al[s][e] = 0u; }
+            }
         }
+        const uint32_t idx = (uint32_t)(c - c_begin);
+        const uint32_t st = idx % K3A_STAGES;
+        ptx::mbar_wait(bars + 8 * st, (idx / K3A_STAGES) & 1);
+        const uint32_t base = ring_u32 + st * Cfg::STAGE_BYTES + 16 * t;
+        // two independent accumulator chains per key group (hi and lo parts) keep the mma pipe busy
         float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f};
+        float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int s = 0; s < S; ++s) {
-            mma_bf16_16816(c0, ah[s][0], ah[s][1], e0[s].x, e0[s].y);
-            mma_bf16_16816(c0, al[s][0], al[s][1], e0[s].x, e0[s].y);
-            mma_bf16_16816(c0, ah[s][2], ah[s][3], e0[s].z, e0[s].w);
-            mma_bf16_16816(c0, al[s][2], al[s][3], e0[s].z, e0[s].w);
-            mma_bf16_16816(c1, ah[s][0], ah[s][1], e1[s].x, e1[s].y);
-            mma_bf16_16816(c1, al[s][0], al[s][1], e1[s].x, e1[s].y);
-            mma_bf16_16816(c1, ah[s][2], ah[s][3], e1[s].z, e1[s].w);
-            mma_bf16_16816(c1, al[s][2], al[s][3], e1[s].z, e1[s].w);
+            uint4 e0, e1;
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(e0.x), "=r"(e0.y), "=r"(e0.z), "=r"(e0.w) : "r"(base + g * Cfg::PITCH + 64 * s));
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(e1.x), "=r"(e1.y), "=r"(e1.z), "=r"(e1.w) : "r"(base + (g + 8) * Cfg::PITCH + 64 * s));
+            mma_bf16_16816(c0, ah[s][0], ah[s][1], e0.x, e0.y);
+            mma_bf16_16816(d0, al[s][0], al[s][1], e0.x, e0.y);
+            mma_bf16_16816(c1, ah[s][0], ah[s][1], e1.x, e1.y);
+            mma_bf16_16816(d1, al[s][0], al[s][1], e1.x, e1.y);
+            mma_bf16_16816(c0, ah[s][2], ah[s][3], e0.z, e0.w);
+            mma_bf16_16816(d0, al[s][2], al[s][3], e0.z, e0.w);
+            mma_bf16_16816(c1, ah[s][2], ah[s][3], e1.z, e1.w);
+            mma_bf16_16816(d1, al[s][2], al[s][3], e1.z, e1.w);
         }
+        __syncwarp();  // every lane has consumed the stage (its values fed the mma above): safe to refill it
+        if (lane == 0 && c + K3A_STAGES < c_end) issue(c + K3A_STAGES);
         if (g < H) {  // C fragment rows 0..7 = heads; columns 2t, 2t+1 = keys j0+2t, j0+2t+1
             const int ka = j0 + 2 * t, kb = j0 + 8 + 2 * t;
-            if (ka < j_end) srow[ka] = c0[0];
-            if (ka + 1 < j_end) srow[ka + 1] = c0[1];
-            if (kb < j_end) srow[kb] = c1[0];
-            if (kb + 1 < j_end) srow[kb + 1] = c1[1];
+            if (ka < m) srow[ka] = c0[0] + d0[0];
+            if (ka + 1 < m) srow[ka + 1] = c0[1] + d0[1];
+            if (kb < m) srow[kb] = c1[0] + d1[0];
+            if (kb + 1 < m) srow[kb + 1] = c1[1] + d1[1];
         }
     }
 }
@@ -151,22 +205,34 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
     const bool fast = e_dtype == GEOTX_BF16 && (C == 128 || C == 256) && H <= 8 &&
                       (((uintptr_t)E | (uintptr_t)qt) & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0;
     if (fast) {
-        // enough warps to keep ~32 resident per SM even for short clouds; each warp gets a contiguous key range
-        int nsplit = (int)((148LL * 64 + rows - 1) / rows);
-        int max_split = (m + 63) / 64;
-        if (nsplit > max_split) nsplit = max_split;
-        if (nsplit < 1) nsplit = 1;
-        int jchunk = (((m + nsplit - 1) / nsplit) + 15) / 16 * 16;
-        nsplit = (m + jchunk - 1) / jchunk;
-        long long warps = rows * nsplit;
-        long long blocks = (warps + K3A_WARPS - 1) / K3A_WARPS;
-        GEOTX_REQUIRE(blocks < 2147483647LL && rows < 2147483647LL, "geotx_rpe_scores: problem too large");
+        static int num_sms = 0;
+        if (num_sms == 0) {
+            int dev = 0;
+            int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+            if (rc) return rc;
+            rc = check_cuda(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
+            if (rc) return rc;
+            rc = check_cuda(cudaFuncSetAttribute(rpe_scores_bf16_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 K3ACfg<256>::SMEM_BYTES), "cudaFuncSetAttribute(rpe_scores<256>)");
+            if (!rc) rc = check_cuda(cudaFuncSetAttribute(rpe_scores_bf16_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                          K3ACfg<128>::SMEM_BYTES), "cudaFuncSetAttribute(rpe_scores<128>)");
+            if (rc) { num_sms = 0; return rc; }
+        }
+        // persistent: one CTA per SM, every warp streams a contiguous range of 16-key chunks
+        const int chunks_per_row = (m + K3A_KEYS - 1) / K3A_KEYS;
+        const long long chunks_total = rows * chunks_per_row;
+        long long ctas = (chunks_total + K3A_WARPS - 1) / K3A_WARPS;
+        if (ctas > num_sms) ctas = num_sms;
+        const long long warps = ctas * K3A_WARPS;
+        const long long chunks_per_warp = (chunks_total + warps - 1) / warps;
         if (C == 256)
-            rpe_scores_bf16_kernel<256><<<(unsigned)blocks, K3A_WARPS * 32, 0, st>>>(
-                qt, qt_stride_b, qt_stride_h, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, (int)rows, nsplit, jchunk, scores_p);
+            rpe_scores_bf16_kernel<256><<<(unsigned)ctas, K3A_WARPS * 32, K3ACfg<256>::SMEM_BYTES, st>>>(
+                qt, qt_stride_b, qt_stride_h, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
+                chunks_per_row, chunks_per_warp, scores_p);
         else
-            rpe_scores_bf16_kernel<128><<<(unsigned)blocks, K3A_WARPS * 32, 0, st>>>(
-                qt, qt_stride_b, qt_stride_h, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, (int)rows, nsplit, jchunk, scores_p);
+            rpe_scores_bf16_kernel<128><<<(unsigned)ctas, K3A_WARPS * 32, K3ACfg<128>::SMEM_BYTES, st>>>(
+                qt, qt_stride_b, qt_stride_h, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
+                chunks_per_row, chunks_per_warp, scores_p);
     } else {
         long long pairs = rows * m;
         long long blocks = (pairs + 7) / 8;
