@@ -63,6 +63,27 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     return r;
 }
 
+// sin(y), cos(y) on the FMA pipe (no MUFU): y = k*pi + r with k = rint(y/pi) by the 1.5*2^23 trick, |r| <= pi/2,
+// degree-7 odd / degree-6 even least-squares polynomials on Chebyshev nodes (max error 1e-6 / 8e-6 on the reduced
+// range), sign (-1)^k applied through the sign bit.  End-to-end |error| <= 1.1e-5 for |y| <= 60 (tools/ fit script in
+// DESIGN.md), i.e. 200x below the bf16 rounding the result goes through.  13 FMA-pipe + 3 ALU instructions per pair;
+// the fused embedding kernel uses it for half of the frequencies because MUFU (16/clk/SM) is its co-bottleneck.
+__device__ __forceinline__ void sincos_fma(float y, float& s, float& c) {
+    const float t = __fmaf_rn(y, 0.31830987f, 12582912.0f);
+    const float k = t - 12582912.0f;
+    const float r = __fmaf_rn(k, -3.14159274f, y);
+    const uint32_t sign = __float_as_uint(t) << 31;  // parity of k
+    const float r2 = r * r;
+    float sp = __fmaf_rn(r2, -1.848342508e-4f, 8.312028833e-3f);
+    sp = __fmaf_rn(r2, sp, -0.1666564941f);
+    const float sv = __fmaf_rn(r * r2, sp, r);
+    float cp = __fmaf_rn(r2, -1.275219372e-3f, 4.150512442e-2f);
+    cp = __fmaf_rn(r2, cp, -0.4999339879f);
+    const float cv = __fmaf_rn(r2, cp, 1.0f);
+    s = __uint_as_float(__float_as_uint(sv) ^ sign);
+    c = __uint_as_float(__float_as_uint(cv) ^ sign);
+}
+
 // 32-byte store (STG.256, sm_100): a full sector per thread, so row-strided writers do not emit half sectors
 __device__ __forceinline__ void st_global_v8(void* p, const uint32_t* v) {
     asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]),

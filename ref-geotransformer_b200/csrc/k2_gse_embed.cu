@@ -15,8 +15,9 @@
 // registers, add the distance term and the biases and write E (bf16 or fp32) straight to HBM.  Nothing of size
 // n*n*k*C ever exists, and no weight byte is re-read from L2 after the first microseconds.
 //
-// Warp roles (640 threads per CTA): warps 0-7 producers, 8-15 epilogue (TMEM lane quarter = warp % 4, column half =
-// (warp-8)/4), 16 MMA issuer (leader CTA only), 17 weight loader (one bulk copy at start), 18 TMEM allocator, 19 idle.
+// Warp roles (896 threads per CTA): warps 0-15 producers, 16-23 epilogue (TMEM lane quarter = warp % 4, column half =
+// (warp-16)/4), 24 MMA issuer (leader CTA only), 25 weight loader (one bulk copy at start), 26 TMEM allocator, 27 idle.
+// Register budget (setmaxnreg, 64512 in the CTA's pool): producers 56, epilogue 104, the rest 40.
 // Cross-CTA signalling: producers / epilogue warps of the peer CTA arrive remotely on the leader's mbarriers
 // (mapa + mbarrier.arrive.release.cluster); tcgen05.commit multicasts "stage free" / "accumulator ready" to both.
 #include <cuda_fp16.h>
@@ -29,9 +30,14 @@ namespace geotx {
 constexpr int TILE_M = 128;                    // pairs per CTA per tile (256 per cluster)
 constexpr int KCHUNK = 64;                     // bf16 elements per 128-byte swizzled row
 constexpr int A_STAGE_BYTES = TILE_M * 128;    // 16 KB
-constexpr int NUM_PRODUCER_WARPS = 8;
+constexpr int NUM_PRODUCER_WARPS = 16;  // 4 per SM sub-partition: the per-chunk fence / barrier latencies overlap
+constexpr int GROUPS_PER_THREAD = 8 * 128 / (NUM_PRODUCER_WARPS * 32);  // 16-byte chunks of its row a thread builds
 constexpr int NUM_EPILOGUE_WARPS = 8;
-constexpr int K2_THREADS = 640;
+constexpr int WARP_MMA = NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS, WARP_LOADER = WARP_MMA + 1, WARP_ALLOC = WARP_MMA + 2;
+constexpr int K2_THREADS = (WARP_MMA + 4) * 32;
+#ifndef K2_MUFU_GROUPS
+#define K2_MUFU_GROUPS GROUPS_PER_THREAD  // of each thread's 4 frequency groups per chunk: this many on MUFU, the rest on the FMA pipe
+#endif
 
 template <int C>
 struct K2Cfg {
@@ -137,9 +143,9 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         ptx::mbar_init(bar_w, 1);
         ptx::fence_barrier_init();
     }
-    if (warp == 18) ptx::tmem_alloc_pair(smem_u32(s_tmem), Cfg::TMEM_COLS);
+    if (warp == WARP_ALLOC) ptx::tmem_alloc_pair(smem_u32(s_tmem), Cfg::TMEM_COLS);
     __syncthreads();
-    if (warp == 17 && lane == 0) {
+    if (warp == WARP_LOADER && lane == 0) {
         // resident weights: this CTA's half of the output channels of W_a and W_d (TMA unit bulk copies)
         ptx::mbar_arrive_expect_tx(bar_w, 2 * Cfg::W_HALF_BYTES);
 #pragma unroll 1
@@ -160,15 +166,18 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
 
     if (warp < NUM_PRODUCER_WARPS) {
         // =============================== PRODUCERS: sinusoid rows -> swizzled smem ===============================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
         const int row = threadIdx.x & (TILE_M - 1);
-        const int half = threadIdx.x >> 7;  // which 4 of the 8 sixteen-byte chunks of a 128-byte row
+        const int part = threadIdx.x >> 7;  // which GROUPS_PER_THREAD of the 8 sixteen-byte chunks of a 128-byte row
         const long long per_b = (long long)prm.row_count * prm.n;
         const float4* s_div4 = (const float4*)s_div;
         const uint32_t full_leader = ptx::map_to_cta(bar_full, 0);
         uint32_t q = 0;  // running chunk counter (stage ring position)
-        for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
-            float x[GEOTX_MAX_K + 1];
+        float x[GEOTX_MAX_K + 1];
+        uint32_t v[GROUPS_PER_THREAD][4];  // this thread's share of its row (4 frequencies per 16-byte chunk)
+
+        // the k+1 scalar arguments of this thread's pair in tile pair tp
+        auto load_x = [&](int tp) {
 #pragma unroll
             for (int s = 0; s <= GEOTX_MAX_K; ++s) x[s] = 0.f;
             const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
@@ -181,56 +190,77 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 const float4 pj = __ldg(prm.pts4 + b * prm.n + j);
                 pair_arguments<GEOTX_MAX_K>(pi, pj, prm.refv + (b * prm.n + i) * k, k, prm.sigma_d, prm.factor_a, x);
             }
-            for (int s = 0; s < slots; ++s) {
-                float xv = x[GEOTX_MAX_K];  // slot k = distance
+        };
+        // chunk ci of a tile = K-chunk (ci % KCH) of slot (ci / KCH); slot k = distance, slots < k = angles
+        auto generate = [&](int ci) {
+#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_GEN)
+            const int s = ci / Cfg::KCH, kc = ci - s * Cfg::KCH;
+            float xv = x[GEOTX_MAX_K];
 #pragma unroll
-                for (int t = 0; t < GEOTX_MAX_K; ++t)
-                    if (s == t && s < k) xv = x[t];
-#pragma unroll 1
-                for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
-                    const uint32_t stage = q % Cfg::NSTAGE;
-                    const uint32_t phase = (q / Cfg::NSTAGE) & 1;
-                    // 16 frequencies (4 sixteen-byte chunks of this row) are generated in registers BEFORE the stage
-                    // is known to be free: the MUFU work never waits on the ring.
-                    uint32_t v[4][4];
-#ifndef K2_DBG_NO_PRODUCE
-                    float4 w[4];
+            for (int t = 0; t < GEOTX_MAX_K; ++t)
+                if (s == t && s < k) xv = x[t];
+            float4 w[GROUPS_PER_THREAD];
 #pragma unroll
-                    for (int gg = 0; gg < 4; ++gg) w[gg] = s_div4[kc * 8 + half * 4 + gg];
+            for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) w[gg] = s_div4[kc * 8 + part * GROUPS_PER_THREAD + gg];
 #pragma unroll
-                    for (int gg = 0; gg < 4; ++gg) {
-                        // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
-                        const float o0 = __fmul_rn(xv, w[gg].x), o1 = __fmul_rn(xv, w[gg].y);
-                        const float o2 = __fmul_rn(xv, w[gg].z), o3 = __fmul_rn(xv, w[gg].w);
+            for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
+                // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
+                const float o0 = __fmul_rn(xv, w[gg].x), o1 = __fmul_rn(xv, w[gg].y);
+                const float o2 = __fmul_rn(xv, w[gg].z), o3 = __fmul_rn(xv, w[gg].w);
 #ifdef K2_DBG_NO_SINCOS  // timing experiments only (tools/k2_variants.sh)
-                        v[gg][0] = pack_bf16x2(o0, o0 + 1.f); v[gg][1] = pack_bf16x2(o1, o1 + 1.f);
-                        v[gg][2] = pack_bf16x2(o2, o2 + 1.f); v[gg][3] = pack_bf16x2(o3, o3 + 1.f);
+                v[gg][0] = pack_bf16x2(o0, o0 + 1.f); v[gg][1] = pack_bf16x2(o1, o1 + 1.f);
+                v[gg][2] = pack_bf16x2(o2, o2 + 1.f); v[gg][3] = pack_bf16x2(o3, o3 + 1.f);
 #else
-                        v[gg][0] = pack_bf16x2(__sinf(o0), __cosf(o0));
-                        v[gg][1] = pack_bf16x2(__sinf(o1), __cosf(o1));
-                        v[gg][2] = pack_bf16x2(__sinf(o2), __cosf(o2));
-                        v[gg][3] = pack_bf16x2(__sinf(o3), __cosf(o3));
-#endif
-                    }
-#endif
-                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (q & 0xFFFFFF));
-#ifndef K2_DBG_NO_PRODUCE
-                    const uint32_t a_row = stages_u32 + stage * A_STAGE_BYTES + row * 128;
-#pragma unroll
-                    for (int gg = 0; gg < 4; ++gg) {
-                        const uint32_t addr = a_row + (((half * 4 + gg) ^ (row & 7)) << 4);
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v[gg][0]),
-                                     "r"(v[gg][1]), "r"(v[gg][2]), "r"(v[gg][3])
-                                     : "memory");
-                    }
-#endif
-#ifndef K2_DBG_NO_FENCE
-                    ptx::fence_proxy_async_smem();  // make the st.shared visible to the tensor core (async proxy)
-#endif
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive_cluster(full_leader + 8 * stage);
+                if (gg < K2_MUFU_GROUPS) {  // MUFU.SIN / MUFU.COS (XU pipe, 16 results / clk / SM)
+                    v[gg][0] = pack_bf16x2(__sinf(o0), __cosf(o0));
+                    v[gg][1] = pack_bf16x2(__sinf(o1), __cosf(o1));
+                    v[gg][2] = pack_bf16x2(__sinf(o2), __cosf(o2));
+                    v[gg][3] = pack_bf16x2(__sinf(o3), __cosf(o3));
+                } else {                    // polynomial on the FMA pipe: takes the other half of the load off MUFU
+                    float s0, c0, s1, c1, s2, c2, s3, c3;
+                    sincos_fma(o0, s0, c0); sincos_fma(o1, s1, c1); sincos_fma(o2, s2, c2); sincos_fma(o3, s3, c3);
+                    v[gg][0] = pack_bf16x2(s0, c0); v[gg][1] = pack_bf16x2(s1, c1);
+                    v[gg][2] = pack_bf16x2(s2, c2); v[gg][3] = pack_bf16x2(s3, c3);
                 }
+#endif
             }
+#endif
+        };
+
+        const int chunks_per_tile = slots * Cfg::KCH;
+        int tp = cluster_id;
+        if (tp < prm.num_tile_pairs) { load_x(tp); generate(0); }
+        while (tp < prm.num_tile_pairs) {
+#pragma unroll 1
+            for (int ci = 0; ci < chunks_per_tile; ++ci, ++q) {
+                const uint32_t stage = q % Cfg::NSTAGE;
+                const uint32_t phase = (q / Cfg::NSTAGE) & 1;
+                ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (q & 0xFFFFFF));
+#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_STS)
+                const uint32_t a_row = stages_u32 + stage * A_STAGE_BYTES + row * 128;
+#pragma unroll
+                for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
+                    const uint32_t addr = a_row + (((part * GROUPS_PER_THREAD + gg) ^ (row & 7)) << 4);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v[gg][0]),
+                                 "r"(v[gg][1]), "r"(v[gg][2]), "r"(v[gg][3])
+                                 : "memory");
+                }
+#endif
+                // Software pipeline: the MUFU work of the NEXT chunk runs while this chunk's stores drain, so the
+                // proxy fence below finds them complete and the XU pipe never idles across the hand-over.
+                if (ci + 1 < chunks_per_tile) {
+                    generate(ci + 1);
+                } else if (tp + num_clusters < prm.num_tile_pairs) {
+                    load_x(tp + num_clusters);
+                    generate(0);
+                }
+#ifndef K2_DBG_NO_FENCE
+                ptx::fence_proxy_async_smem();  // make the st.shared visible to the tensor core (async proxy)
+#endif
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive_cluster(full_leader + 8 * stage);
+            }
+            tp += num_clusters;
         }
     } else if (warp < NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS) {
         // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================
@@ -324,7 +354,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         }
     } else {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == 16 && rank == 0 && lane == 0) {
+        if (warp == WARP_MMA && rank == 0 && lane == 0) {
             // =============================== MMA ISSUER (one thread of the leader CTA) ===========================
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(2 * TILE_M, C);
             uint32_t q = 0, gc = 0;
@@ -368,7 +398,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     __syncwarp();  // reconverge the single-thread roles: barrier.cluster.*.aligned needs converged warps
     ptx::tc_fence_before_sync();
     ptx::cluster_sync();
-    if (warp == 18) {
+    if (warp == WARP_ALLOC) {
         ptx::tc_fence_after_sync();
         ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
     }
