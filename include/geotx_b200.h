@@ -87,17 +87,19 @@ int geotx_gse_embed_fp32(const void* geometry, int B, int n, int k, int row_begi
 /* modules/transformer/rpe_transformer.py:54-56 with proj_p folded into the query:
  *   scores_p[b,h,i,j] = sum_c qt[b,h,i,c] * E[b,i,j,c],   qt[b,h,i,:] = W_p[h]^T q[b,h,i,:]
  * (the q . b_p term is constant over j and cancels in the softmax).  E is streamed from HBM exactly once.
- *   qt f32, element (b,h,i,c) at qt[b*qt_stride_b + h*qt_stride_h + i*C + c] (strides in elements; a dense
- *      [B,H,n,C] tensor has qt_stride_b = H*n*C, qt_stride_h = n*C)
+ *   qt f32, element (b,h,i,c) at qt[b*qt_stride_b + h*qt_stride_h + i*qt_stride_n + c] (strides in elements; a dense
+ *      [B,H,n,C] tensor has qt_stride_b = H*n*C, qt_stride_h = n*C, qt_stride_n = C; the strided form lets qt be a
+ *      column block of one fused projection GEMM output)
  *   E [B,row_count,m,C] (e_dtype): the slab of query rows [row_begin,row_begin+row_count)
  *   scores_p f32 [B,H,n,m] (only the slab's rows are written)
  * Tensor-core path: e_dtype bf16, C in {128,256}, H <= 8; anything else takes a slower generic kernel. */
-int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, const void* E, int e_dtype,
+int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n, const void* E, int e_dtype,
                      int B, int H, int n, int m, int C, int row_begin, int row_count, float* scores_p,
                      void* stream);
 
 /* rpe_transformer.py:57-70 / vanilla_transformer.py:54-68: softmax((q k^T + scores_p) * scale [masked]) v.
- *   q f32 [B,n,H*c] (token-major, heads interleaved as in 'b n (h c)'), k,v f32 [B,m,H*c],
+ *   q f32 [B,n,H*c] (token-major, heads interleaved as in 'b n (h c)'), k,v f32 [B,m,H*c]; ld_q / ld_k / ld_v are the
+ *   token (row) strides in floats (H*c when dense; larger when q,k,v are column blocks of a fused projection output),
  *   scores_p f32 [B,H,n,m] or NULL, key_mask u8 [B,m] or NULL (non-zero = ignore),
  *   out f32 [B,n,H*c].  c (per-head dim) in {16, 32, 64}.
  *   workspace: geotx_attention_workspace_bytes() bytes of scratch, or NULL.  With a workspace the key range is split
@@ -105,8 +107,14 @@ int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, 
  *   148 SMs busy when n is about a thousand; with NULL one CTA walks all keys.  Same result up to fp32 rounding. */
 int64_t geotx_attention_workspace_bytes(int B, int H, int n, int m, int c);
 int geotx_attention(const float* q, const float* k, const float* v, const float* scores_p,
-                    const uint8_t* key_mask, int B, int H, int n, int m, int c, float scale, float* out,
-                    void* workspace, void* stream);
+                    const uint8_t* key_mask, int B, int H, int n, int m, int c, int ld_q, int ld_k, int ld_v,
+                    float scale, float* out, void* workspace, void* stream);
+
+/* out = LayerNorm(x + residual) over the last dimension (rpe_transformer.py:103, vanilla_transformer.py:101,
+ * output_layer.py:20; torch.nn.LayerNorm semantics: biased variance, eps inside the root).  residual may be NULL.
+ *   x, residual, out f32 [rows, C]; gamma, beta f32 [C]; C a multiple of 4, <= 1024. */
+int geotx_add_layernorm(const float* x, const float* residual, const float* gamma, const float* beta, int64_t rows,
+                        int C, float eps, float* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -26,9 +26,10 @@ SIGNATURES = {
     'geotx_gse_embed': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
     'geotx_watchdog_status': (_i, [_p]),
     'geotx_gse_embed_fp32': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
-    'geotx_rpe_scores': (_i, [_p, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
+    'geotx_rpe_scores': (_i, [_p, _i64, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
     'geotx_attention_workspace_bytes': (_i64, [_i, _i, _i, _i, _i]),
-    'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _p, _p, _p]),
+    'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _f, _p, _p, _p]),
+    'geotx_add_layernorm': (_i, [_p, _p, _p, _p, _i64, _i, _f, _p, _p]),
 }
 
 GEOTX_F32 = 0

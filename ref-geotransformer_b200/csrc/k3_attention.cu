@@ -52,7 +52,7 @@ struct AttSmem {
 template <int DH>
 __global__ void __launch_bounds__(ATT_THREADS)
 attention_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
-                 const float* __restrict__ scores_p, const uint8_t* __restrict__ key_mask, int H, int n, int m,
+                 const float* __restrict__ scores_p, const uint8_t* __restrict__ key_mask, int H, int n, int m, int ldq, int ldk, int ldv,
                  float scale_log2e, float* __restrict__ out, float* __restrict__ ws, int tiles_per_split) {
     using SM = AttSmem<DH>;
     constexpr int PITCH = SM::PITCH;
@@ -79,10 +79,10 @@ attention_kernel(const float* __restrict__ q, const float* __restrict__ k, const
         for (int idx = threadIdx.x; idx < ATT_BK * (DH / 4); idx += ATT_THREADS) {
             const int row = idx / (DH / 4), c4 = idx - row * (DH / 4);
             const int j = j0 + row;
-            const size_t off = ((size_t)b * m + min(j, m - 1)) * ld + h * DH + 4 * c4;
+            const size_t tok = (size_t)b * m + min(j, m - 1);
             const uint32_t nbytes = j < m ? 16u : 0u;
-            cp_async16(ks_u32 + (row * PITCH + 4 * c4) * 4, k + off, nbytes);  // PITCH % 4 == 0: 16-byte aligned
-            cp_async16(vs_u32 + (row * PITCH + 4 * c4) * 4, v + off, nbytes);
+            cp_async16(ks_u32 + (row * PITCH + 4 * c4) * 4, k + tok * ldk + h * DH + 4 * c4, nbytes);  // PITCH % 4 == 0
+            cp_async16(vs_u32 + (row * PITCH + 4 * c4) * 4, v + tok * ldv + h * DH + 4 * c4, nbytes);
         }
         if (threadIdx.x < ATT_BK) {
             const int j = j0 + threadIdx.x;
@@ -97,8 +97,8 @@ attention_kernel(const float* __restrict__ q, const float* __restrict__ k, const
     // Q fragments (A operand, row-major 16 x 8 per k-step): a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4)
     uint32_t qa[KS][4];
     {
-        const float* q_r0 = q + ((size_t)b * n + min(r0, n - 1)) * ld + h * DH;
-        const float* q_r1 = q + ((size_t)b * n + min(r1, n - 1)) * ld + h * DH;
+        const float* q_r0 = q + ((size_t)b * n + min(r0, n - 1)) * ldq + h * DH;
+        const float* q_r1 = q + ((size_t)b * n + min(r1, n - 1)) * ldq + h * DH;
 #pragma unroll
         for (int ks = 0; ks < KS; ++ks) {
             qa[ks][0] = to_tf32(__ldg(q_r0 + 8 * ks + t));
@@ -286,8 +286,8 @@ extern "C" int64_t geotx_attention_workspace_bytes(int B, int H, int n, int m, i
 
 template <int DH>
 static int launch_attention(const float* q, const float* k, const float* v, const float* scores_p,
-                            const uint8_t* key_mask, int B, int H, int n, int m, float sl2, float* out, float* ws,
-                            cudaStream_t st) {
+                            const uint8_t* key_mask, int B, int H, int n, int m, int ldq, int ldk, int ldv, float sl2,
+                            float* out, float* ws, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
         int rc = check_cuda(cudaFuncSetAttribute(attention_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -298,8 +298,8 @@ static int launch_attention(const float* q, const float* k, const float* v, cons
     int splits = 1, tps = (m + ATT_BK - 1) / ATT_BK;
     if (ws) attention_plan(B, H, n, m, &splits, &tps);
     dim3 grid((n + ATT_BQ - 1) / ATT_BQ, B * H, splits);
-    attention_kernel<DH><<<grid, ATT_THREADS, AttSmem<DH>::BYTES, st>>>(q, k, v, scores_p, key_mask, H, n, m, sl2, out,
-                                                                         ws, tps);
+    attention_kernel<DH><<<grid, ATT_THREADS, AttSmem<DH>::BYTES, st>>>(q, k, v, scores_p, key_mask, H, n, m, ldq, ldk,
+                                                                         ldv, sl2, out, ws, tps);
     if (splits > 1) {
         const long long rows = (long long)B * H * n;
         const long long blocks = (rows * DH + 255) / 256;
@@ -309,8 +309,8 @@ static int launch_attention(const float* q, const float* k, const float* v, cons
 }
 
 extern "C" int geotx_attention(const float* q, const float* k, const float* v, const float* scores_p,
-                               const uint8_t* key_mask, int B, int H, int n, int m, int c, float scale, float* out,
-                               void* workspace, void* stream) {
+                               const uint8_t* key_mask, int B, int H, int n, int m, int c, int ld_q, int ld_k,
+                               int ld_v, float scale, float* out, void* workspace, void* stream) {
     GEOTX_REQUIRE(q && k && v && out, "geotx_attention: null pointer");
     GEOTX_REQUIRE(B > 0 && H > 0 && n > 0 && m > 0, "geotx_attention: bad sizes");
     GEOTX_REQUIRE(c == 16 || c == 32 || c == 64, "geotx_attention: per-head dim %d not supported (16, 32, 64)", c);
@@ -318,10 +318,12 @@ extern "C" int geotx_attention(const float* q, const float* k, const float* v, c
                   "geotx_attention: q/k/v/out/workspace must be 16-byte aligned");
     GEOTX_REQUIRE(scores_p == nullptr || ((uintptr_t)scores_p & 7) == 0, "geotx_attention: scores_p must be 8-byte aligned");
     GEOTX_REQUIRE((long long)B * H <= 65535, "geotx_attention: B*H too large");
+    GEOTX_REQUIRE(ld_q >= H * c && ld_k >= H * c && ld_v >= H * c && ld_q % 4 == 0 && ld_k % 4 == 0 && ld_v % 4 == 0,
+                  "geotx_attention: row strides must be >= H*c and multiples of 4 floats");
     const float sl2 = scale * 1.4426950408889634f;
     cudaStream_t st = (cudaStream_t)stream;
     float* ws = (float*)workspace;
-    if (c == 64) return launch_attention<64>(q, k, v, scores_p, key_mask, B, H, n, m, sl2, out, ws, st);
-    if (c == 32) return launch_attention<32>(q, k, v, scores_p, key_mask, B, H, n, m, sl2, out, ws, st);
-    return launch_attention<16>(q, k, v, scores_p, key_mask, B, H, n, m, sl2, out, ws, st);
+    if (c == 64) return launch_attention<64>(q, k, v, scores_p, key_mask, B, H, n, m, ld_q, ld_k, ld_v, sl2, out, ws, st);
+    if (c == 32) return launch_attention<32>(q, k, v, scores_p, key_mask, B, H, n, m, ld_q, ld_k, ld_v, sl2, out, ws, st);
+    return launch_attention<16>(q, k, v, scores_p, key_mask, B, H, n, m, ld_q, ld_k, ld_v, sl2, out, ws, st);
 }

@@ -59,7 +59,8 @@ struct K3ACfg {
 
 template <int C>
 __global__ void __launch_bounds__(K3A_WARPS * 32, 1)
-rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qsh, const __nv_bfloat16* __restrict__ E,
+rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qsh, long long qsn,
+                       const __nv_bfloat16* __restrict__ E,
                        int H, int n, int m, int row_begin, int row_count, long long chunks_total, int chunks_per_row,
                        long long chunks_per_warp, float* __restrict__ scores) {
     using Cfg = K3ACfg<C>;
@@ -111,7 +112,7 @@ rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qs
             const int i = row_begin + (int)(r - (long long)b * row_count);
             srow = scores + (((size_t)b * H + g) * n + i) * m;
             if (g < H) {
-                const float* qrow = qt + (size_t)b * qsb + (size_t)g * qsh + (size_t)i * C + 8 * t;
+                const float* qrow = qt + (size_t)b * qsb + (size_t)g * qsh + (size_t)i * qsn + 8 * t;
 #pragma unroll
                 for (int s = 0; s < S; ++s) {
                     const float4 u = __ldg((const float4*)(qrow + 32 * s));
@@ -170,7 +171,7 @@ rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qs
 // Generic fp32-arithmetic variant (any C, E in fp32 or bf16): one warp per (slab row, key), lanes stride channels.
 template <typename ET>
 __global__ void __launch_bounds__(256)
-rpe_scores_generic_kernel(const float* __restrict__ qt, long long qsb, long long qsh, const ET* __restrict__ E, int H, int n, int m, int C,
+rpe_scores_generic_kernel(const float* __restrict__ qt, long long qsb, long long qsh, long long qsn, const ET* __restrict__ E, int H, int n, int m, int C,
                           int row_begin, int row_count, long long pairs_total, float* __restrict__ scores) {
     const int lane = threadIdx.x & 31;
     const long long p = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -181,7 +182,7 @@ rpe_scores_generic_kernel(const float* __restrict__ qt, long long qsb, long long
     const int i = row_begin + (int)(r - (long long)b * row_count);
     const ET* e = E + p * C;
     for (int h = 0; h < H; ++h) {
-        const float* q = qt + (size_t)b * qsb + (size_t)h * qsh + (size_t)i * C;
+        const float* q = qt + (size_t)b * qsb + (size_t)h * qsh + (size_t)i * qsn;
         float acc = 0.f;
         for (int c = lane; c < C; c += 32) acc = fmaf(q[c], (float)e[c], acc);
 #pragma unroll
@@ -194,7 +195,7 @@ rpe_scores_generic_kernel(const float* __restrict__ qt, long long qsb, long long
 
 using namespace geotx;
 
-extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, const void* E, int e_dtype, int B, int H, int n, int m, int C,
+extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n, const void* E, int e_dtype, int B, int H, int n, int m, int C,
                                 int row_begin, int row_count, float* scores_p, void* stream) {
     GEOTX_REQUIRE(qt && E && scores_p, "geotx_rpe_scores: null pointer");
     GEOTX_REQUIRE(B > 0 && H > 0 && n > 0 && m > 0 && C > 0, "geotx_rpe_scores: bad sizes");
@@ -203,7 +204,7 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
     cudaStream_t st = (cudaStream_t)stream;
     const long long rows = (long long)B * row_count;
     const bool fast = e_dtype == GEOTX_BF16 && (C == 128 || C == 256) && H <= 8 &&
-                      (((uintptr_t)E | (uintptr_t)qt) & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0;
+                      (((uintptr_t)E | (uintptr_t)qt) & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0 && qt_stride_n % 4 == 0;
     if (fast) {
         static int num_sms = 0;
         if (num_sms == 0) {
@@ -227,11 +228,11 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
         const long long chunks_per_warp = (chunks_total + warps - 1) / warps;
         if (C == 256)
             rpe_scores_bf16_kernel<256><<<(unsigned)ctas, K3A_WARPS * 32, K3ACfg<256>::SMEM_BYTES, st>>>(
-                qt, qt_stride_b, qt_stride_h, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
+                qt, qt_stride_b, qt_stride_h, qt_stride_n, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
                 chunks_per_row, chunks_per_warp, scores_p);
         else
             rpe_scores_bf16_kernel<128><<<(unsigned)ctas, K3A_WARPS * 32, K3ACfg<128>::SMEM_BYTES, st>>>(
-                qt, qt_stride_b, qt_stride_h, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
+                qt, qt_stride_b, qt_stride_h, qt_stride_n, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
                 chunks_per_row, chunks_per_warp, scores_p);
     } else {
         long long pairs = rows * m;
@@ -239,10 +240,10 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
         GEOTX_REQUIRE(blocks < 2147483647LL, "geotx_rpe_scores: problem too large");
         if (e_dtype == GEOTX_BF16)
             rpe_scores_generic_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(
-                qt, qt_stride_b, qt_stride_h, (const __nv_bfloat16*)E, H, n, m, C, row_begin, row_count, pairs, scores_p);
+                qt, qt_stride_b, qt_stride_h, qt_stride_n, (const __nv_bfloat16*)E, H, n, m, C, row_begin, row_count, pairs, scores_p);
         else
             rpe_scores_generic_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(
-                qt, qt_stride_b, qt_stride_h, (const float*)E, H, n, m, C, row_begin, row_count, pairs, scores_p);
+                qt, qt_stride_b, qt_stride_h, qt_stride_n, (const float*)E, H, n, m, C, row_begin, row_count, pairs, scores_p);
     }
     return launch_status("geotx_rpe_scores");
 }

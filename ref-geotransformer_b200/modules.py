@@ -230,6 +230,27 @@ class RPEMultiHeadAttention(_FusedAttentionBase):
         self.proj_p = nn.Linear(self.d_model, self.d_model)
         self.dropout = build_dropout_layer(dropout)
 
+    def fused_qkvp(self):
+        """One projection for the whole layer: rows [W_q; W_k; W_v; W_qp] with W_qp[h] = W_p[h]^T W_q[h], so that
+        x -> (q | k | v | folded query of every head) is a single (C -> 3C + H*C) GEMM.  The fold is exact algebra
+        (formed in fp64, stored fp32); rebuilt whenever one of the source parameters changes."""
+        ps = (self.proj_q.weight, self.proj_q.bias, self.proj_k.weight, self.proj_k.bias, self.proj_v.weight,
+              self.proj_v.bias, self.proj_p.weight)
+        key = tuple((t.data_ptr(), t._version) for t in ps)
+        if getattr(self, '_fused_key', None) != key:
+            H, c, C = self.num_heads, self.d_model_per_head, self.d_model
+            wp = self.proj_p.weight.detach().double().view(H, c, C)
+            wq = self.proj_q.weight.detach().double().view(H, c, C)
+            bq = self.proj_q.bias.detach().double().view(H, c)
+            w_qp = torch.einsum('hcd,hci->hdi', wp, wq).reshape(H * C, C)
+            b_qp = torch.einsum('hcd,hc->hd', wp, bq).reshape(H * C)
+            w = torch.cat([self.proj_q.weight.detach().double(), self.proj_k.weight.detach().double(),
+                           self.proj_v.weight.detach().double(), w_qp]).float().contiguous()
+            b = torch.cat([self.proj_q.bias.detach().double(), self.proj_k.bias.detach().double(),
+                           self.proj_v.bias.detach().double(), b_qp]).float().contiguous()
+            self._fused, self._fused_key = (w, b), key
+        return self._fused
+
     def folded_query(self, q):
         """q (B,N,H*c) -> qt view of logical shape (B,H,N,C): qt[b,h,i,:] = W_p[h]^T q[b,h,i,:]."""
         B, n, D = q.shape
@@ -263,6 +284,16 @@ class MultiHeadAttention(_FusedAttentionBase):
         self.proj_k = nn.Linear(self.d_model, self.d_model)
         self.proj_v = nn.Linear(self.d_model, self.d_model)
         self.dropout = build_dropout_layer(dropout)
+
+    def fused_kv(self):
+        """[W_k; W_v] as one (C -> 2C) projection of the memory tokens."""
+        ps = (self.proj_k.weight, self.proj_k.bias, self.proj_v.weight, self.proj_v.bias)
+        key = tuple((t.data_ptr(), t._version) for t in ps)
+        if getattr(self, '_fused_key', None) != key:
+            w = torch.cat([self.proj_k.weight.detach(), self.proj_v.weight.detach()]).contiguous()
+            b = torch.cat([self.proj_k.bias.detach(), self.proj_v.bias.detach()]).contiguous()
+            self._fused, self._fused_key = (w, b), key
+        return self._fused
 
     def forward(self, input_q, input_k, input_v, key_weights=None, key_masks=None, attention_factors=None,
                 attention_masks=None):
@@ -366,7 +397,77 @@ class RPEConditionalTransformer(nn.Module):
         self.return_attention_scores = return_attention_scores
         self.parallel = parallel
 
+    # ---- fused schedule (same math, fewer and larger launches) ------------------------------------------------
+    # Both clouds share every layer's weights, so all token-wise work of a 'self' block (one fused q|k|v|folded-query
+    # projection, the output Linear, the two residual LayerNorms, the C->2C->C FFN) runs once over the concatenated
+    # tokens of both clouds; only the two attention cores see the clouds separately.  'cross' blocks keep the
+    # reference's sequential dependency (conditional_transformer.py:110-111).  Used when nothing asks for the
+    # materialised attention matrix; otherwise the layer-by-layer path below runs.
+    def _fused_ok(self, feats0, feats1):
+        if self.return_attention_scores or feats0.shape[0] != 1 or feats0.dim() != 3:
+            return False
+        C = feats0.shape[-1]
+        if C % 4 or C > 1024:
+            return False
+        for layer in self.layers:
+            att = layer.attention.attention
+            if att.d_model_per_head not in (16, 32, 64):
+                return False
+            if self.training and any(isinstance(m, nn.Dropout) for m in layer.modules()):
+                return False
+        return True
+
+    @staticmethod
+    def _post_attention(layer, hidden, x_in, out=None):
+        """rpe_transformer.py:101-103 / vanilla_transformer.py:99-101 + output_layer.py:15-21 on (1, T, C) tokens."""
+        al, ao = layer.attention, layer.output
+        h = F.linear(hidden, al.linear.weight, al.linear.bias)
+        x1 = ops.add_layernorm(h, x_in, al.norm.weight, al.norm.bias, al.norm.eps)
+        T, C = x1.shape[1], x1.shape[2]
+        if isinstance(ao.activation, nn.ReLU):
+            e = torch._addmm_activation(ao.expand.bias, x1.view(T, C), ao.expand.weight.t())  # bias + ReLU epilogue
+        else:
+            e = ao.activation(F.linear(x1.view(T, C), ao.expand.weight, ao.expand.bias))
+        sq = F.linear(e, ao.squeeze.weight, ao.squeeze.bias).view(1, T, C)
+        return ops.add_layernorm(sq, x1, ao.norm.weight, ao.norm.bias, ao.norm.eps, out=out)
+
+    def _forward_fused(self, feats0, feats1, embeddings0, embeddings1, masks0, masks1):
+        N, C = feats0.shape[1], feats0.shape[2]
+        x = torch.cat([feats0, feats1], dim=1)  # (1, N+M, C); cloud slices of it are contiguous views
+        T = x.shape[1]
+        for i, block in enumerate(self.blocks):
+            layer = self.layers[i]
+            att = layer.attention.attention
+            H = att.num_heads
+            if block == 'self':
+                w, b = att.fused_qkvp()
+                y = F.linear(x, w, b)  # (1, T, 3C + H*C): q | k | v | folded query per head
+                hidden = x.new_empty(1, T, C)
+                for lo, hi, emb, mask in ((0, N, embeddings0, masks0), (N, T, embeddings1, masks1)):
+                    qt = y[:, lo:hi, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
+                    scores_p = ops.rpe_scores(qt, emb.contiguous())
+                    ops.attention(y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask,
+                                  out=hidden[:, lo:hi])
+                x = self._post_attention(layer, hidden, x)
+            else:
+                x_new = torch.empty_like(x)
+                wkv, bkv = att.fused_kv()
+                order = ((0, N, N, T, masks1), (N, T, 0, N, masks0))  # (query cloud, memory cloud, memory mask)
+                for step, (qlo, qhi, mlo, mhi, mask) in enumerate(order):
+                    # sequential: the second step reads the UPDATED first cloud; parallel=True reads the old one
+                    mem_src = x_new if (step == 1 and not self.parallel) else x
+                    q = F.linear(x[:, qlo:qhi], att.proj_q.weight, att.proj_q.bias)
+                    kv = F.linear(mem_src[:, mlo:mhi], wkv, bkv)
+                    hidden = ops.attention(q, kv[:, :, :C], kv[:, :, C:], H, None, mask)
+                    self._post_attention(layer, hidden, x[:, qlo:qhi], out=x_new[:, qlo:qhi])
+                x = x_new
+        return x[:, :N], x[:, N:]
+
     def forward(self, feats0, feats1, embeddings0, embeddings1, masks0=None, masks1=None):
+        if self._fused_ok(feats0, feats1):
+            _forward_only_guard(self, feats0, feats1, embeddings0, embeddings1)
+            return self._forward_fused(feats0.contiguous(), feats1.contiguous(), embeddings0, embeddings1, masks0,
+                                       masks1)
         for layer in self.layers:
             layer.attention.attention.need_scores = bool(self.return_attention_scores)
         attention_scores = []
@@ -413,6 +514,12 @@ class GeometricTransformer(nn.Module):
             src_feats = self.in_proj(src_feats)
             ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
                                                     masks0=ref_masks, masks1=src_masks)
+            if ref_feats.shape[0] == 1 and ref_feats.data_ptr() + ref_feats.numel() * 4 == src_feats.data_ptr():
+                # the fused schedule returns two slices of one (1, N+M, C) buffer: project them in one GEMM
+                n = ref_feats.shape[1]
+                both = torch.as_strided(ref_feats, (1, n + src_feats.shape[1], ref_feats.shape[2]), ref_feats.stride())
+                out = self.out_proj(both)
+                return out[:, :n], out[:, n:]
             return self.out_proj(ref_feats), self.out_proj(src_feats)
 
 

@@ -116,14 +116,27 @@ def gse_embed_fp32(geom, div_term, w_d, b_d, w_a, b_a, sigma_d, factor_a, reduce
     return out
 
 
+def _row_strided(t, name):
+    """(B, tokens, D) fp32 CUDA view with unit channel stride, 16-byte aligned rows: returns (tensor, row stride).
+    Column blocks of a fused projection output qualify; anything else is made contiguous."""
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.dim() == 3):
+        raise RuntimeError(f'{name} must be a 3-d fp32 CUDA tensor (ref-geotransformer_b200 has no CPU path)')
+    B, n, D = t.shape
+    ok = t.stride(2) == 1 and t.stride(1) % 4 == 0 and t.stride(1) >= D and t.data_ptr() % 16 == 0 and \
+        (B == 1 or t.stride(0) == n * t.stride(1))
+    if not ok:
+        t = t.contiguous()
+    return t, t.stride(1)
+
+
 def rpe_scores(qt, E, n=None, row_begin=0, out=None):
-    """qt: folded query, logical shape (B,H,n,C) fp32 (may be a permuted view with unit channel stride and
-    row stride C);  E (B,row_count,m,C) bf16|fp32  ->  scores_p (B,H,n,m) fp32 (slab rows written).
+    """qt: folded query, logical shape (B,H,n,C) fp32 (any view with unit channel stride);
+    E (B,row_count,m,C) bf16|fp32  ->  scores_p (B,H,n,m) fp32 (slab rows written).
     rpe_transformer.py:54-56 with proj_p folded."""
     if not (isinstance(qt, torch.Tensor) and qt.is_cuda and qt.dtype == torch.float32 and qt.dim() == 4):
         raise RuntimeError('qt must be a 4-d fp32 CUDA tensor')
     B, H, nq, C = qt.shape
-    if qt.stride(3) != 1 or qt.stride(2) != C:
+    if qt.stride(3) != 1 or any(st % 4 for st in qt.stride()[:3]) or qt.data_ptr() % 16:
         qt = qt.contiguous()
     _check(E, 'E', None, 4)
     if E.dtype not in _DT:
@@ -134,17 +147,17 @@ def rpe_scores(qt, E, n=None, row_begin=0, out=None):
     n = nq if n is None else n
     if out is None:
         out = torch.empty(B, H, n, m, dtype=torch.float32, device=E.device)
-    _abi.call('geotx_rpe_scores', _p(qt), qt.stride(0), qt.stride(1), _p(E), _DT[E.dtype], B, H, n, m, C,
+    _abi.call('geotx_rpe_scores', _p(qt), qt.stride(0), qt.stride(1), qt.stride(2), _p(E), _DT[E.dtype], B, H, n, m, C,
               row_begin, row_count, _p(out), _stream())
     return out
 
 
-def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None, split_keys=True):
-    """q (B,n,H*c), k,v (B,m,H*c) fp32 token-major -> (B,n,H*c).  softmax((q k^T + scores_p)*scale) v.
-    rpe_transformer.py:57-70, vanilla_transformer.py:54-68."""
-    _check(q, 'q', torch.float32, 3)
-    _check(k, 'k', torch.float32, 3)
-    _check(v, 'v', torch.float32, 3)
+def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None, split_keys=True, out=None):
+    """q (B,n,H*c), k,v (B,m,H*c) fp32 token-major (dense or column blocks of a wider row-major matrix)
+    -> (B,n,H*c) dense.  softmax((q k^T + scores_p)*scale) v.  rpe_transformer.py:57-70, vanilla_transformer.py:54-68."""
+    q, ldq = _row_strided(q, 'q')
+    k, ldk = _row_strided(k, 'k')
+    v, ldv = _row_strided(v, 'v')
     B, n, D = q.shape
     m = k.shape[1]
     c = D // num_heads
@@ -158,9 +171,31 @@ def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None, spli
             raise RuntimeError(f'key_mask must be {(B, m)}, got {tuple(key_mask.shape)}')
         mask_u8 = _check(key_mask.to(torch.uint8).contiguous(), 'key_mask')
     scale = 1.0 / (c ** 0.5) if scale is None else scale
-    out = torch.empty_like(q)
+    if out is None:
+        out = torch.empty(B, n, D, dtype=torch.float32, device=q.device)
+    elif tuple(_check(out, 'out', torch.float32, 3).shape) != (B, n, D):
+        raise RuntimeError(f'out must be {(B, n, D)}, got {tuple(out.shape)}')
     ws_bytes = _abi.load().geotx_attention_workspace_bytes(B, num_heads, n, m, c)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device) if (ws_bytes > 0 and split_keys) else None
-    _abi.call('geotx_attention', _p(q), _p(k), _p(v), _p(scores_p), _p(mask_u8), B, num_heads, n, m, c,
+    _abi.call('geotx_attention', _p(q), _p(k), _p(v), _p(scores_p), _p(mask_u8), B, num_heads, n, m, c, ldq, ldk, ldv,
               float(scale), _p(out), _p(ws), _stream())
+    return out
+
+
+def add_layernorm(x, residual, weight, bias, eps=1e-5, out=None):
+    """LayerNorm(x + residual) over the last dim in one pass (residual may be None).  fp32, C % 4 == 0, C <= 1024."""
+    _check(x, 'x', torch.float32)
+    if residual is not None:
+        _check(residual, 'residual', torch.float32)
+        if residual.shape != x.shape:
+            raise RuntimeError(f'residual shape {tuple(residual.shape)} != x shape {tuple(x.shape)}')
+    _check(weight, 'weight', torch.float32, 1)
+    _check(bias, 'bias', torch.float32, 1)
+    C = x.shape[-1]
+    if out is None:
+        out = torch.empty_like(x)
+    elif _check(out, 'out', torch.float32).shape != x.shape:
+        raise RuntimeError(f'out shape {tuple(out.shape)} != x shape {tuple(x.shape)}')
+    _abi.call('geotx_add_layernorm', _p(x), _p(residual), _p(weight), _p(bias), x.numel() // C, C, float(eps), _p(out),
+              _stream())
     return out

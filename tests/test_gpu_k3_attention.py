@@ -79,3 +79,33 @@ def test_attention_rejects_cpu_and_bad_head_dim(pkg):
         pkg.ops.attention(q, q, q, 2)
     with pytest.raises(RuntimeError, match='per-head dim'):
         pkg.ops.attention(q.to(DEV), q.to(DEV), q.to(DEV), 2)  # c = 48
+
+
+@pytest.mark.parametrize('rows,C', [(1, 256), (77, 128), (300, 32), (5, 1024)])
+def test_add_layernorm_vs_torch(pkg, rows, C):
+    """K4: LayerNorm(x + residual) (rpe_transformer.py:103, output_layer.py:20) against torch fp32 on the CPU."""
+    g = torch.Generator().manual_seed(rows + C)
+    x, r = torch.randn(1, rows, C, generator=g) * 3, torch.randn(1, rows, C, generator=g)
+    w, b = torch.randn(C, generator=g), torch.randn(C, generator=g)
+    exp = torch.nn.functional.layer_norm(x + r, (C,), w, b, 1e-5)
+    got = pkg.ops.add_layernorm(x.to(DEV), r.to(DEV), w.to(DEV), b.to(DEV), 1e-5)
+    assert rel(got, exp) <= 2e-6
+    exp1 = torch.nn.functional.layer_norm(x, (C,), w, b, 1e-5)
+    assert rel(pkg.ops.add_layernorm(x.to(DEV), None, w.to(DEV), b.to(DEV)), exp1) <= 2e-6
+    with pytest.raises(RuntimeError, match='multiple of 4'):
+        pkg.ops.add_layernorm(torch.randn(2, 6, device=DEV), None, torch.ones(6, device=DEV), torch.ones(6, device=DEV))
+
+
+def test_strided_operands_of_a_fused_projection(pkg):
+    """q | k | v | folded query taken as column blocks of one wider row-major matrix (no copies)."""
+    g = torch.Generator().manual_seed(5)
+    B, n, H, c = 1, 150, 4, 64
+    C = H * c
+    y = torch.randn(B, n, 3 * C + H * C, generator=g).to(DEV)
+    E = torch.randn(B, n, n, C, generator=g).to(DEV).to(torch.bfloat16)
+    q, k, v = y[:, :, :C], y[:, :, C:2 * C], y[:, :, 2 * C:3 * C]
+    qt = y[:, :, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)
+    sp = pkg.ops.rpe_scores(qt, E)
+    assert torch.equal(sp, pkg.ops.rpe_scores(qt.contiguous(), E))
+    got = pkg.ops.attention(q, k, v, H, sp)
+    assert torch.equal(got, pkg.ops.attention(q.contiguous(), k.contiguous(), v.contiguous(), H, sp))

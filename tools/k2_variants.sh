@@ -8,7 +8,7 @@ for v in "$@"; do
   flags=""
   for f in $(echo $v | tr '+' ' '); do flags="$flags -DK2_DBG_$f"; done
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Xcompiler -fPIC -shared $flags \
-    $SRC/abi.cu $SRC/k1_knn.cu $SRC/k2_gse_embed_fp32.cu $SRC/k2_gse_embed.cu $SRC/k3_rpe_scores.cu $SRC/k3_attention.cu \
+    $SRC/abi.cu $SRC/k1_knn.cu $SRC/k2_gse_embed_fp32.cu $SRC/k2_gse_embed.cu $SRC/k3_rpe_scores.cu $SRC/k3_attention.cu $SRC/k4_add_layernorm.cu \
     -o tools/bin/variants/lib_$v.so -lcudart &
 done
 wait
