@@ -54,6 +54,18 @@ __device__ __forceinline__ void pair_arguments(const float4& pi, const float4& p
     x[MAXK] = __fdiv_rn(__fsqrt_rn(sqdist_ref(pi, pj)), sigma_d);
 }
 
+// One of the k+1 embedding arguments of a pair: s < k -> angle s * factor_a, s == k -> dist / sigma_d (same arithmetic
+// as pair_arguments; lets cooperating threads split the arguments of a pair between them).
+__device__ __forceinline__ float pair_argument_one(const float4& pi, const float4& pj, const float4* __restrict__ refv_i,
+                                                   int k, int s, float sigma_d, float factor_a) {
+    if (s < k) {
+        const float ax = __fsub_rn(pj.x, pi.x), ay = __fsub_rn(pj.y, pi.y), az = __fsub_rn(pj.z, pi.z);
+        const float4 r = __ldg(refv_i + s);
+        return __fmul_rn(triplet_angle(r.x, r.y, r.z, ax, ay, az), factor_a);
+    }
+    return __fdiv_rn(__fsqrt_rn(sqdist_ref(pi, pj)), sigma_d);
+}
+
 // ---- small PTX wrappers -------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

@@ -31,7 +31,8 @@ constexpr int TILE_M = 128;                    // pairs per CTA per tile (256 pe
 constexpr int KCHUNK = 64;                     // bf16 elements per 128-byte swizzled row
 constexpr int A_STAGE_BYTES = TILE_M * 128;    // 16 KB
 constexpr int NUM_PRODUCER_WARPS = 16;  // 4 per SM sub-partition: the per-chunk fence / barrier latencies overlap
-constexpr int GROUPS_PER_THREAD = 8 * 128 / (NUM_PRODUCER_WARPS * 32);  // 16-byte chunks of its row a thread builds
+constexpr int PARTS = NUM_PRODUCER_WARPS * 32 / 128;  // producer threads per row
+constexpr int GROUPS_PER_THREAD = 8 / PARTS;  // 16-byte chunks of its row a thread builds
 constexpr int NUM_EPILOGUE_WARPS = 8;
 constexpr int WARP_MMA = NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS, WARP_LOADER = WARP_MMA + 1, WARP_ALLOC = WARP_MMA + 2;
 constexpr int K2_THREADS = (WARP_MMA + 4) * 32;
@@ -49,7 +50,8 @@ struct K2Cfg {
     static constexpr int COLS_PER_THREAD = C / 2;
     static constexpr int NBAR = 2 * NSTAGE + 5;
     static constexpr int SMEM_BYTES = 2 * W_HALF_BYTES + NSTAGE * A_STAGE_BYTES + C * 4 /*bias*/ +
-                                      (C / 2) * 4 /*div_term*/ + NBAR * 8 + 16 + 1024 /*alignment slack*/;
+                                      (C / 2) * 4 /*div_term*/ + 2 * TILE_M * 8 * 4 /*pair arguments*/ + NBAR * 8 + 16 +
+                                      1024 /*alignment slack*/;
 };
 
 // ------------------------------------------------------------------------------------------------------------
@@ -108,7 +110,8 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     uint8_t* stages = smem + 2 * Cfg::W_HALF_BYTES;        // NSTAGE x 16 KB
     float* s_bias = (float*)(stages + Cfg::NSTAGE * A_STAGE_BYTES);
     float* s_div = s_bias + C;
-    uint64_t* bars = (uint64_t*)(s_div + C / 2);
+    float* s_args = s_div + C / 2;                         // [2][128 rows][8] pair arguments
+    uint64_t* bars = (uint64_t*)(s_args + 2 * TILE_M * 8);
     uint32_t* s_tmem = (uint32_t*)(bars + Cfg::NBAR);
 
     const uint32_t bar_full = smem_u32(bars);                       // [NSTAGE]  leader: 16 warp arrivals
@@ -177,9 +180,12 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         uint32_t v[GROUPS_PER_THREAD][4];  // this thread's share of its row (4 frequencies per 16-byte chunk)
 
         // the k+1 scalar arguments of this thread's pair in tile pair tp
+        // The four producer threads of a row split its arguments between them (atan2f is ~1/3 of a producer's
+        // instructions if every thread evaluates all k of them) and exchange them through a double-buffered table:
+        // one named barrier over the producer warps per tile.
+        int xbuf = 0;
         auto load_x = [&](int tp) {
-#pragma unroll
-            for (int s = 0; s <= GEOTX_MAX_K; ++s) x[s] = 0.f;
+            float* xs = s_args + xbuf * (TILE_M * 8);
             const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
             if (p < prm.pairs_total) {
                 const long long b = p / per_b;
@@ -188,17 +194,27 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 const int j = (int)(rem % prm.n);
                 const float4 pi = __ldg(prm.pts4 + b * prm.n + i);
                 const float4 pj = __ldg(prm.pts4 + b * prm.n + j);
-                pair_arguments<GEOTX_MAX_K>(pi, pj, prm.refv + (b * prm.n + i) * k, k, prm.sigma_d, prm.factor_a, x);
+                for (int s = part; s < slots; s += PARTS)
+                    xs[row * 8 + s] = pair_argument_one(pi, pj, prm.refv + (b * prm.n + i) * k, k, s, prm.sigma_d,
+                                                        prm.factor_a);
+            } else {
+                for (int s = part; s < slots; s += PARTS) xs[row * 8 + s] = 0.f;
             }
+            asm volatile("bar.sync 1, %0;" ::"n"(NUM_PRODUCER_WARPS * 32) : "memory");
+            const float4 lo = *(const float4*)(xs + row * 8), hi = *(const float4*)(xs + row * 8 + 4);
+            const float all[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+            for (int s = 0; s <= GEOTX_MAX_K; ++s) x[s] = all[s];  // x[s]: angle s for s < k, distance at s == k
+            xbuf ^= 1;
         };
         // chunk ci of a tile = K-chunk (ci % KCH) of slot (ci / KCH); slot k = distance, slots < k = angles
         auto generate = [&](int ci) {
 #if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_GEN)
             const int s = ci / Cfg::KCH, kc = ci - s * Cfg::KCH;
-            float xv = x[GEOTX_MAX_K];
+            float xv = x[0];
 #pragma unroll
-            for (int t = 0; t < GEOTX_MAX_K; ++t)
-                if (s == t && s < k) xv = x[t];
+            for (int t = 1; t <= GEOTX_MAX_K; ++t)
+                if (s == t) xv = x[t];
             float4 w[GROUPS_PER_THREAD];
 #pragma unroll
             for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) w[gg] = s_div4[kc * 8 + part * GROUPS_PER_THREAD + gg];
