@@ -35,6 +35,8 @@ WORKLOADS = {
     '3dmatch_2048': ('3dmatch', 2048, 2048),
     '3dmatch_4096': ('3dmatch', 4096, 4096),   # configs[3] sweep point named by north_star
 }
+# dram__bytes_read.sum + dram__bytes_write.sum of one gse_embed_tc_kernel launch (ncu --set full, profiles/r01_ncu_k2_*)
+K2_NCU_TRAFFIC_BYTES = {'3dmatch_1024': 483.9e6}
 METRIC = 'registration pairs/sec (embed+RPE-attn) at N superpoints'
 UNIT = 'pairs/s'
 
@@ -319,7 +321,8 @@ def run_b200(args):
             'gpu_launches': launches,
             'roofline': {'kernel': 'gse_embed_tc_kernel (geotx_gse_embed)', 'bound': 'tensor', 'achieved': achieved,
                          'peak': peaks['tensor_sustained'], 'unit': 'TFLOP/s',
-                         'frac': achieved / peaks['tensor_sustained'], 'traffic': None,
+                         'frac': achieved / peaks['tensor_sustained'],
+                         'traffic': K2_NCU_TRAFFIC_BYTES.get(args.workload),
                          'peak_source': peaks['source'] + ' bf16 sustained (kernel timed inside the step)',
                          'frac_of_burst_peak': achieved / peaks['tensor_burst'],
                          'flops_per_launch': k2_flops, 'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
