@@ -97,7 +97,7 @@ struct K2Params {
 constexpr uint32_t WD_PRODUCER = 1u << 24, WD_EPILOGUE = 2u << 24, WD_MMA_ACC = 3u << 24, WD_MMA_FULL = 4u << 24,
                    WD_WEIGHTS = 6u << 24;
 
-template <int C>
+template <int C, bool MEAN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(K2_THREADS, 1)
 gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     using Cfg = K2Cfg<C>;
@@ -175,15 +175,15 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         const long long per_b = (long long)prm.row_count * prm.n;
         const float4* s_div4 = (const float4*)s_div;
         const uint32_t full_leader = ptx::map_to_cta(bar_full, 0);
-        uint32_t q = 0;  // running chunk counter (stage ring position)
-        float x[GEOTX_MAX_K + 1];
+        uint32_t stage = 0, phase = 0;  // stage ring position of the next chunk and the parity of its pass
         uint32_t v[GROUPS_PER_THREAD][4];  // this thread's share of its row (4 frequencies per 16-byte chunk)
 
         // the k+1 scalar arguments of this thread's pair in tile pair tp
         // The four producer threads of a row split its arguments between them (atan2f is ~1/3 of a producer's
-        // instructions if every thread evaluates all k of them) and exchange them through a double-buffered table:
-        // one named barrier over the producer warps per tile.
+        // instructions if every thread evaluates all k of them) and exchange them through a double-buffered table
+        // [buffer][slot][row] (conflict-free both ways): one named barrier over the producer warps per tile.
         int xbuf = 0;
+        const float* x_row = s_args + row;  // + slot * TILE_M: arguments of the tile being generated
         auto load_x = [&](int tp) {
             float* xs = s_args + xbuf * (TILE_M * 8);
             const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
@@ -195,26 +195,20 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 const float4 pi = __ldg(prm.pts4 + b * prm.n + i);
                 const float4 pj = __ldg(prm.pts4 + b * prm.n + j);
                 for (int s = part; s < slots; s += PARTS)
-                    xs[row * 8 + s] = pair_argument_one(pi, pj, prm.refv + (b * prm.n + i) * k, k, s, prm.sigma_d,
-                                                        prm.factor_a);
+                    xs[s * TILE_M + row] = pair_argument_one(pi, pj, prm.refv + (b * prm.n + i) * k, k, s,
+                                                             prm.sigma_d, prm.factor_a);
             } else {
-                for (int s = part; s < slots; s += PARTS) xs[row * 8 + s] = 0.f;
+                for (int s = part; s < slots; s += PARTS) xs[s * TILE_M + row] = 0.f;
             }
             asm volatile("bar.sync 1, %0;" ::"n"(NUM_PRODUCER_WARPS * 32) : "memory");
-            const float4 lo = *(const float4*)(xs + row * 8), hi = *(const float4*)(xs + row * 8 + 4);
-            const float all[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-#pragma unroll
-            for (int s = 0; s <= GEOTX_MAX_K; ++s) x[s] = all[s];  // x[s]: angle s for s < k, distance at s == k
+            x_row = xs + row;
             xbuf ^= 1;
         };
         // chunk ci of a tile = K-chunk (ci % KCH) of slot (ci / KCH); slot k = distance, slots < k = angles
         auto generate = [&](int ci) {
 #if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_GEN)
             const int s = ci / Cfg::KCH, kc = ci - s * Cfg::KCH;
-            float xv = x[0];
-#pragma unroll
-            for (int t = 1; t <= GEOTX_MAX_K; ++t)
-                if (s == t) xv = x[t];
+            const float xv = x_row[s * TILE_M];  // angle s for s < k, distance at s == k
             float4 w[GROUPS_PER_THREAD];
 #pragma unroll
             for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) w[gg] = s_div4[kc * 8 + part * GROUPS_PER_THREAD + gg];
@@ -248,10 +242,8 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         if (tp < prm.num_tile_pairs) { load_x(tp); generate(0); }
         while (tp < prm.num_tile_pairs) {
 #pragma unroll 1
-            for (int ci = 0; ci < chunks_per_tile; ++ci, ++q) {
-                const uint32_t stage = q % Cfg::NSTAGE;
-                const uint32_t phase = (q / Cfg::NSTAGE) & 1;
-                ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (q & 0xFFFFFF));
+            for (int ci = 0; ci < chunks_per_tile; ++ci) {
+                ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)ci);
 #if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_STS)
                 const uint32_t a_row = stages_u32 + stage * A_STAGE_BYTES + row * 128;
 #pragma unroll
@@ -275,6 +267,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
 #endif
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive_cluster(full_leader + 8 * stage);
+                if (++stage == Cfg::NSTAGE) { stage = 0; phase ^= 1; }
             }
             tp += num_clusters;
         }
@@ -287,8 +280,8 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 belong to this warp
         const int colhalf = (warp - NUM_PRODUCER_WARPS) >> 2;
         const int row = quarter * 32 + lane;
-        const int groups = prm.reduce_mean ? 2 : slots;
-        const float inv_k = prm.reduce_mean ? 1.0f / (float)k : 1.0f;
+        const int groups = MEAN ? 2 : slots;
+        const float inv_k = 1.0f / (float)k;  // 'mean': the k angle slots are summed by the MMA into one accumulator
         const uint32_t acc_empty_leader = ptx::map_to_cta(bar_acc_empty, 0);
         __half2 run[NCOL / 2];
         uint32_t gc = 0;  // running accumulation-group counter (TMEM buffer ring position)
@@ -296,7 +289,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
             const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
             for (int g = 0; g < groups; ++g, ++gc) {
                 const uint32_t buf = gc & 1, phase = (gc >> 1) & 1;
-                ptx::mbar_wait(bar_acc_full + 8 * buf, phase, WD_EPILOGUE | (gc & 0xFFFFFF));
+                ptx::mbar_wait_backoff(bar_acc_full + 8 * buf, phase, WD_EPILOGUE | (gc & 0xFFFFFF));
                 ptx::tc_fence_after_sync();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * C + colhalf * NCOL;
                 if (g < groups - 1) {
@@ -309,8 +302,9 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                         ptx::tmem_ld_wait();
 #pragma unroll
                         for (int c = 0; c < 16; c += 2) {
-                            const __half2 a = __floats2half2_rn(__uint_as_float(v[c]) * inv_k,
-                                                                __uint_as_float(v[c + 1]) * inv_k);
+                            const __half2 a = MEAN ? __floats2half2_rn(__uint_as_float(v[c]) * inv_k,
+                                                                       __uint_as_float(v[c + 1]) * inv_k)
+                                                   : __floats2half2_rn(__uint_as_float(v[c]), __uint_as_float(v[c + 1]));
                             run[(c0 + c) / 2] = (g == 0) ? a : __hmax2(run[(c0 + c) / 2], a);
                         }
                     }
@@ -370,14 +364,16 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         }
     } else {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == WARP_MMA && rank == 0 && lane == 0) {
-            // =============================== MMA ISSUER (one thread of the leader CTA) ===========================
+        if (warp == WARP_MMA && rank == 0) {
+            // =============================== MMA ISSUER (leader CTA) ============================================
+            // The whole warp walks the loop (uniform control flow, operands in uniform registers); one elected lane
+            // issues the tcgen05 instructions.
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(2 * TILE_M, C);
-            uint32_t q = 0, gc = 0;
+            uint32_t stage = 0, phase = 0, gc = 0;
             for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
                 for (int s = 0; s < slots; ++s) {
-                    const bool first = prm.reduce_mean ? (s == 0 || s == k) : true;
-                    const bool last = prm.reduce_mean ? (s == k - 1 || s == k) : true;
+                    const bool first = MEAN ? (s == 0 || s == k) : true;
+                    const bool last = MEAN ? (s == k - 1 || s == k) : true;
                     const uint32_t buf = gc & 1;
                     if (first) {
                         ptx::mbar_wait(bar_acc_empty + 8 * buf, ((gc >> 1) & 1) ^ 1, WD_MMA_ACC | (gc & 0xFFFFFF));
@@ -385,26 +381,27 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                     }
                     const uint32_t tmem_d = tmem_base + buf * C;
                     const uint32_t w_mat = w_u32 + (s < k ? 0 : Cfg::W_HALF_BYTES);  // W_a | W_d
-                    for (int kc = 0; kc < Cfg::KCH; ++kc, ++q) {
-                        const uint32_t stage = q % Cfg::NSTAGE;
-                        ptx::mbar_wait(bar_full + 8 * stage, (q / Cfg::NSTAGE) & 1, WD_MMA_FULL | (q & 0xFFFFFF));
+                    for (int kc = 0; kc < Cfg::KCH; ++kc) {
+                        ptx::mbar_wait(bar_full + 8 * stage, phase, WD_MMA_FULL | (uint32_t)(s * Cfg::KCH + kc));
                         ptx::tc_fence_after_sync();
                         const uint64_t adesc = ptx::umma_desc_sw128(stages_u32 + stage * A_STAGE_BYTES);
                         const uint64_t bdesc = ptx::umma_desc_sw128(w_mat + kc * Cfg::W_CHUNK_BYTES);
+                        if (ptx::elect_one()) {
 #ifndef K2_DBG_NO_MMA
 #pragma unroll
-                        for (int ks = 0; ks < KCHUNK / 16; ++ks) {
-                            // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzled row: +2 (16-B units)
-                            ptx::umma_bf16_pair(tmem_d, adesc + 2 * ks, bdesc + 2 * ks, idesc,
-                                                (uint32_t)(!(first && kc == 0 && ks == 0)));
-                        }
+                            for (int ks = 0; ks < KCHUNK / 16; ++ks) {
+                                // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzled row: +2 (16-B units)
+                                ptx::umma_bf16_pair(tmem_d, adesc + 2 * ks, bdesc + 2 * ks, idesc,
+                                                    (uint32_t)(!(first && kc == 0 && ks == 0)));
+                            }
 #endif
-                        ptx::umma_commit_pair(bar_empty + 8 * stage, 3);  // stage reusable in both CTAs
+                            ptx::umma_commit_pair(bar_empty + 8 * stage, 3);  // stage reusable in both CTAs
+                            if (last && kc == Cfg::KCH - 1) ptx::umma_commit_pair(bar_acc_full + 8 * buf, 3);
+                        }
+                        __syncwarp();
+                        if (++stage == Cfg::NSTAGE) { stage = 0; phase ^= 1; }
                     }
-                    if (last) {
-                        ptx::umma_commit_pair(bar_acc_full + 8 * buf, 3);
-                        ++gc;
-                    }
+                    if (last) ++gc;
                 }
             }
         }
@@ -463,14 +460,17 @@ static int launch_k2(const K2Params& prm, cudaStream_t st) {
         if (rc) return rc;
         rc = check_cuda(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
         if (rc) return rc;
-        rc = check_cuda(cudaFuncSetAttribute(gse_embed_tc_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        rc = check_cuda(cudaFuncSetAttribute(gse_embed_tc_kernel<C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::SMEM_BYTES), "cudaFuncSetAttribute(gse_embed_tc_kernel)");
+        if (!rc) rc = check_cuda(cudaFuncSetAttribute(gse_embed_tc_kernel<C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                      Cfg::SMEM_BYTES), "cudaFuncSetAttribute(gse_embed_tc_kernel)");
         if (rc) { num_sms = 0; return rc; }
     }
     // persistent: one CTA pair per SM pair (cluster of 2, same TPC)
     int clusters = num_sms / 2;
     if (prm.num_tile_pairs < clusters) clusters = prm.num_tile_pairs;
-    gse_embed_tc_kernel<C><<<2 * clusters, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
+    if (prm.reduce_mean) gse_embed_tc_kernel<C, true><<<2 * clusters, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
+    else gse_embed_tc_kernel<C, false><<<2 * clusters, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
     return launch_status("geotx_gse_embed");
 }
 

@@ -57,6 +57,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_
     }
 }
 
+// Same, for waits that are expected to be long (an epilogue warp waiting for the next accumulator): sleeps between
+// polls so that the spinning warp does not take issue slots from the warps it is waiting for.
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity, uint32_t tag = 0) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(64);
+        if ((++spins & 63u) == 0u) {
+            if (*(volatile unsigned int*)&g_watchdog[0] != 0u) return;
+            if (clock64() - t0 > 4000000000LL) { watchdog_trip(tag, bar, parity); return; }
+        }
+    }
+}
+
 // ---------------- proxy / tcgen05 fences ----------------
 // generic-proxy st.shared  ->  async proxy (tcgen05.mma / bulk copy) visibility
 __device__ __forceinline__ void fence_proxy_async_smem() {
@@ -115,6 +130,21 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* v) {
                  : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// One lane of a converged warp.  Single-thread instructions (tcgen05.mma / commit) are issued as
+//   if (elect_one()) { ... }
+// from warp-UNIFORM control flow: the operands then stay in uniform registers.  Issued from a `lane == 0` branch the
+// compiler treats every operand as divergent and wraps each UTCHMMA in an R2UR broadcast loop (~17 instructions per
+// MMA on the single issuing thread, which is the serial bottleneck of the whole pipeline).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
 
 // ---------------- UMMA (tcgen05.mma, cta_group::1, kind::f16) ----------------
 // Shared-memory matrix descriptor for a K-major operand tile stored as rows of 128 bytes (64 bf16) with the

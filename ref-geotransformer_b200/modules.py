@@ -10,12 +10,17 @@ The heavy math runs in the sm_100a kernels behind include/geotx_b200.h (see ops.
 (C x C Linears, LayerNorm, ReLU: <0.5 % of the path's flops) are issued through torch on
 the same stream.  Forward-only: calling with autograd enabled on anything that requires grad raises."""
 import math
+import os
 
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
 from . import ops
+
+# slab of E (bytes) written by the embedding kernel and consumed from L2 by the first block's scores kernel; the
+# B200 L2 is 126 MB.  Measured sweep in DESIGN.md section 5.
+DEFAULT_L2_SLAB_BYTES = 0
 
 _ACTIVATIONS = {  # geotransformer/modules/layers/factory.py:18-27,71-80
     'ReLU': nn.ReLU, 'LeakyReLU': nn.LeakyReLU, 'ELU': nn.ELU, 'GELU': nn.GELU, 'Sigmoid': nn.Sigmoid,
@@ -379,6 +384,43 @@ def _check_block_type(block):
         raise ValueError('Unsupported block type "{}".'.format(block))
 
 
+class StreamedEmbedding:
+    """E of one cloud, produced slab by slab together with the FIRST 'self' block's scores_p.
+
+    The first 'self' block's folded query depends only on in_proj(feats), not on E, so E need not exist before the
+    transformer starts: the embedding kernel writes a slab of query rows (sized to stay inside the L2 cache) and the
+    scores kernel consumes that slab straight away, while its lines are still L2-resident.  That removes one of the
+    three full HBM reads of E (one per 'self' block); the slab still drains to HBM for the later blocks.
+    `slab_bytes` = 0 produces E in one launch (the scores kernel then reads it from HBM as in the later blocks)."""
+
+    def __init__(self, embedding, geom, dtype, slab_bytes):
+        self.embedding, self.geom, self.dtype, self.slab_bytes = embedding, geom, dtype, slab_bytes
+        self.E = None
+
+    def materialise(self):
+        if self.E is None:
+            self.E = self.embedding.embed(self.geom, self.dtype)
+        return self.E
+
+    def first_scores(self, qt):
+        """qt (1,H,n,C) -> scores_p (1,H,n,n) of the first 'self' block; E is complete afterwards."""
+        if self.E is not None:
+            return ops.rpe_scores(qt, self.E)
+        n, C = self.geom.n, self.embedding.hidden_dim
+        row_bytes = n * C * (2 if self.dtype == torch.bfloat16 else 4)
+        rows = n if self.slab_bytes <= 0 else max(1, min(n, self.slab_bytes // row_bytes))
+        if rows >= n or self.geom.B != 1:
+            return ops.rpe_scores(qt, self.materialise())
+        E = torch.empty(1, n, n, C, dtype=self.dtype, device=qt.device)
+        scores_p = torch.empty(1, qt.shape[1], n, n, dtype=torch.float32, device=qt.device)
+        for r0 in range(0, n, rows):
+            rc = min(rows, n - r0)
+            self.embedding.embed(self.geom, self.dtype, r0, rc, out=E[:, r0:r0 + rc])
+            ops.rpe_scores(qt, E[:, r0:r0 + rc], n=n, row_begin=r0, out=scores_p)
+        self.E = E
+        return scores_p
+
+
 class RPEConditionalTransformer(nn.Module):
     """conditional_transformer.py:73-117."""
 
@@ -433,6 +475,7 @@ class RPEConditionalTransformer(nn.Module):
 
     def _forward_fused(self, feats0, feats1, embeddings0, embeddings1, masks0, masks1):
         N, C = feats0.shape[1], feats0.shape[2]
+        embs = [embeddings0, embeddings1]
         x = torch.cat([feats0, feats1], dim=1)  # (1, N+M, C); cloud slices of it are contiguous views
         T = x.shape[1]
         for i, block in enumerate(self.blocks):
@@ -443,9 +486,14 @@ class RPEConditionalTransformer(nn.Module):
                 w, b = att.fused_qkvp()
                 y = F.linear(x, w, b)  # (1, T, 3C + H*C): q | k | v | folded query per head
                 hidden = x.new_empty(1, T, C)
-                for lo, hi, emb, mask in ((0, N, embeddings0, masks0), (N, T, embeddings1, masks1)):
+                for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
+                    emb = embs[which]
                     qt = y[:, lo:hi, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
-                    scores_p = ops.rpe_scores(qt, emb.contiguous())
+                    if isinstance(emb, StreamedEmbedding):
+                        scores_p = emb.first_scores(qt)  # the first block interleaves with the embedding kernel
+                        embs[which] = emb.E
+                    else:
+                        scores_p = ops.rpe_scores(qt, emb.contiguous())
                     ops.attention(y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask,
                                   out=hidden[:, lo:hi])
                 x = self._post_attention(layer, hidden, x)
@@ -464,10 +512,18 @@ class RPEConditionalTransformer(nn.Module):
         return x[:, :N], x[:, N:]
 
     def forward(self, feats0, feats1, embeddings0, embeddings1, masks0=None, masks1=None):
+        streamed = [e for e in (embeddings0, embeddings1) if isinstance(e, StreamedEmbedding)]
         if self._fused_ok(feats0, feats1):
-            _forward_only_guard(self, feats0, feats1, embeddings0, embeddings1)
+            _forward_only_guard(self, feats0, feats1, *[e for e in (embeddings0, embeddings1)
+                                                         if not isinstance(e, StreamedEmbedding)])
+            if 'self' not in self.blocks:
+                for e in streamed:
+                    e.materialise()
             return self._forward_fused(feats0.contiguous(), feats1.contiguous(), embeddings0, embeddings1, masks0,
                                        masks1)
+        if streamed:
+            embeddings0 = embeddings0.materialise() if isinstance(embeddings0, StreamedEmbedding) else embeddings0
+            embeddings1 = embeddings1.materialise() if isinstance(embeddings1, StreamedEmbedding) else embeddings1
         for layer in self.layers:
             layer.attention.attention.need_scores = bool(self.return_attention_scores)
         attention_scores = []
@@ -502,13 +558,17 @@ class GeometricTransformer(nn.Module):
         self.transformer = RPEConditionalTransformer(blocks, hidden_dim, num_heads, dropout=dropout,
                                                      activation_fn=activation_fn)
         self.out_proj = nn.Linear(hidden_dim, output_dim)
+        # slab of E kept L2-resident between the embedding kernel and the first block's scores kernel (0 = off)
+        self.l2_slab_bytes = int(os.environ.get('GEOTX_L2_SLAB_BYTES', DEFAULT_L2_SLAB_BYTES))
 
     def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
         _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
         tc = self.embedding._use_tensor_cores()
         e_dtype = torch.bfloat16 if tc else torch.float32
-        ref_embeddings = self.embedding.embed(self.embedding.geometry(ref_points), e_dtype)
-        src_embeddings = self.embedding.embed(self.embedding.geometry(src_points), e_dtype)
+        ref_embeddings = StreamedEmbedding(self.embedding, self.embedding.geometry(ref_points), e_dtype,
+                                           self.l2_slab_bytes)
+        src_embeddings = StreamedEmbedding(self.embedding, self.embedding.geometry(src_points), e_dtype,
+                                           self.l2_slab_bytes)
         with _dense_precision(allow_tf32=tc):
             ref_feats = self.in_proj(ref_feats)
             src_feats = self.in_proj(src_feats)
