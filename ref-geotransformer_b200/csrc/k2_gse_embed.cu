@@ -31,13 +31,24 @@ constexpr int TILE_M = 128;                    // pairs per CTA per tile (256 pe
 constexpr int KCHUNK = 64;                     // bf16 elements per 128-byte swizzled row
 constexpr int A_STAGE_BYTES = TILE_M * 128;    // 16 KB
 constexpr int NUM_PRODUCER_WARPS = 16;  // 4 per SM sub-partition: the per-chunk fence / barrier latencies overlap
-constexpr int PARTS = NUM_PRODUCER_WARPS * 32 / 128;  // producer threads per row
-constexpr int GROUPS_PER_THREAD = 8 / PARTS;  // 16-byte chunks of its row a thread builds
+constexpr int ARG_PARTS = NUM_PRODUCER_WARPS * 32 / 128;  // producer threads per row of a tile (argument split)
+// The producer warps form K2_PGROUPS groups that build alternate chunks (group g: chunks g, g + G, ...).  A warp's
+// fixed per-chunk latencies (empty-barrier wait, argument / frequency loads, proxy fence, arrive) are then paid once
+// per G chunk periods and overlap the MUFU work of the other groups; with one group every warp pays them every chunk
+// and the XU pipe idles half of the time (ncu: 46 % busy).
+#ifndef K2_PGROUPS
+#define K2_PGROUPS 2
+#endif
+constexpr int PGROUPS = K2_PGROUPS;
+constexpr int WARPS_PER_PGROUP = NUM_PRODUCER_WARPS / PGROUPS;
+constexpr int PARTS = WARPS_PER_PGROUP * 32 / 128;  // threads of one group per row (1, 2 or 4)
+constexpr int GROUPS_PER_THREAD = 8 / PARTS;        // 16-byte pieces of its 128-byte row a thread builds
+static_assert(PGROUPS == 1 || PGROUPS == 2 || PGROUPS == 4, "producer groups");
 constexpr int NUM_EPILOGUE_WARPS = 8;
 constexpr int WARP_MMA = NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS, WARP_LOADER = WARP_MMA + 1, WARP_ALLOC = WARP_MMA + 2;
 constexpr int K2_THREADS = (WARP_MMA + 4) * 32;
 #ifndef K2_MUFU_GROUPS
-#define K2_MUFU_GROUPS GROUPS_PER_THREAD  // of each thread's 4 frequency groups per chunk: this many on MUFU, the rest on the FMA pipe
+#define K2_MUFU_GROUPS GROUPS_PER_THREAD  // of a thread's 16-byte pieces per chunk: this many on MUFU, the rest on the FMA pipe
 #endif
 
 template <int C>
@@ -136,7 +147,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     for (int t = threadIdx.x; t < C / 2; t += K2_THREADS) s_div[t] = prm.div_term[t];
     if (threadIdx.x == 0) {
         for (int s = 0; s < Cfg::NSTAGE; ++s) {
-            ptx::mbar_init(bar_full + 8 * s, 2 * NUM_PRODUCER_WARPS);
+            ptx::mbar_init(bar_full + 8 * s, 2 * WARPS_PER_PGROUP);
             ptx::mbar_init(bar_empty + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
@@ -171,17 +182,20 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         // =============================== PRODUCERS: sinusoid rows -> swizzled smem ===============================
         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
         const int row = threadIdx.x & (TILE_M - 1);
-        const int part = threadIdx.x >> 7;  // which GROUPS_PER_THREAD of the 8 sixteen-byte chunks of a 128-byte row
+        const int argpart = threadIdx.x >> 7;     // which of its row's k+1 arguments this thread evaluates
+        const int pgroup = argpart / PARTS;       // producer group: builds chunks pgroup, pgroup + PGROUPS, ...
+        const int part = argpart - pgroup * PARTS;  // which GROUPS_PER_THREAD of the 8 sixteen-byte pieces of a row
         const long long per_b = (long long)prm.row_count * prm.n;
         const float4* s_div4 = (const float4*)s_div;
         const uint32_t full_leader = ptx::map_to_cta(bar_full, 0);
-        uint32_t stage = 0, phase = 0;  // stage ring position of the next chunk and the parity of its pass
-        uint32_t v[GROUPS_PER_THREAD][4];  // this thread's share of its row (4 frequencies per 16-byte chunk)
+        const uint32_t a_row = stages_u32 + row * 128;
+        const int sw = row & 7;  // 128-byte swizzle: 16-byte piece index XOR (row mod 8)
+        // stage ring position of this group's next chunk and the parity of its pass
+        uint32_t stage = pgroup % Cfg::NSTAGE, phase = 0;
 
-        // the k+1 scalar arguments of this thread's pair in tile pair tp
-        // The four producer threads of a row split its arguments between them (atan2f is ~1/3 of a producer's
-        // instructions if every thread evaluates all k of them) and exchange them through a double-buffered table
-        // [buffer][slot][row] (conflict-free both ways): one named barrier over the producer warps per tile.
+        // The k+1 scalar arguments of a pair: the four producer threads of a row split them (atan2f is ~1/3 of a
+        // producer's instructions if every thread evaluates all k of them) and exchange them through a
+        // double-buffered table [buffer][slot][row] (conflict-free both ways): one named barrier per tile.
         int xbuf = 0;
         const float* x_row = s_args + row;  // + slot * TILE_M: arguments of the tile being generated
         auto load_x = [&](int tp) {
@@ -194,82 +208,72 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 const int j = (int)(rem % prm.n);
                 const float4 pi = __ldg(prm.pts4 + b * prm.n + i);
                 const float4 pj = __ldg(prm.pts4 + b * prm.n + j);
-                for (int s = part; s < slots; s += PARTS)
+                for (int s = argpart; s < slots; s += ARG_PARTS)
                     xs[s * TILE_M + row] = pair_argument_one(pi, pj, prm.refv + (b * prm.n + i) * k, k, s,
                                                              prm.sigma_d, prm.factor_a);
             } else {
-                for (int s = part; s < slots; s += PARTS) xs[s * TILE_M + row] = 0.f;
+                for (int s = argpart; s < slots; s += ARG_PARTS) xs[s * TILE_M + row] = 0.f;
             }
             asm volatile("bar.sync 1, %0;" ::"n"(NUM_PRODUCER_WARPS * 32) : "memory");
             x_row = xs + row;
             xbuf ^= 1;
         };
-        // chunk ci of a tile = K-chunk (ci % KCH) of slot (ci / KCH); slot k = distance, slots < k = angles
-        auto generate = [&](int ci) {
-#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_GEN)
-            const int s = ci / Cfg::KCH, kc = ci - s * Cfg::KCH;
-            const float xv = x_row[s * TILE_M];  // angle s for s < k, distance at s == k
-            float4 w[GROUPS_PER_THREAD];
-#pragma unroll
-            for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) w[gg] = s_div4[kc * 8 + part * GROUPS_PER_THREAD + gg];
-#pragma unroll
-            for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
-                // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
-                const float o0 = __fmul_rn(xv, w[gg].x), o1 = __fmul_rn(xv, w[gg].y);
-                const float o2 = __fmul_rn(xv, w[gg].z), o3 = __fmul_rn(xv, w[gg].w);
-#ifdef K2_DBG_NO_SINCOS  // timing experiments only (tools/k2_variants.sh)
-                v[gg][0] = pack_bf16x2(o0, o0 + 1.f); v[gg][1] = pack_bf16x2(o1, o1 + 1.f);
-                v[gg][2] = pack_bf16x2(o2, o2 + 1.f); v[gg][3] = pack_bf16x2(o3, o3 + 1.f);
-#else
-                if (gg < K2_MUFU_GROUPS) {  // MUFU.SIN / MUFU.COS (XU pipe, 16 results / clk / SM)
-                    v[gg][0] = pack_bf16x2(__sinf(o0), __cosf(o0));
-                    v[gg][1] = pack_bf16x2(__sinf(o1), __cosf(o1));
-                    v[gg][2] = pack_bf16x2(__sinf(o2), __cosf(o2));
-                    v[gg][3] = pack_bf16x2(__sinf(o3), __cosf(o3));
-                } else {                    // polynomial on the FMA pipe: takes the other half of the load off MUFU
-                    float s0, c0, s1, c1, s2, c2, s3, c3;
-                    sincos_fma(o0, s0, c0); sincos_fma(o1, s1, c1); sincos_fma(o2, s2, c2); sincos_fma(o3, s3, c3);
-                    v[gg][0] = pack_bf16x2(s0, c0); v[gg][1] = pack_bf16x2(s1, c1);
-                    v[gg][2] = pack_bf16x2(s2, c2); v[gg][3] = pack_bf16x2(s3, c3);
-                }
-#endif
-            }
-#endif
-        };
 
         const int chunks_per_tile = slots * Cfg::KCH;
-        int tp = cluster_id;
-        if (tp < prm.num_tile_pairs) { load_x(tp); generate(0); }
-        while (tp < prm.num_tile_pairs) {
+        int ci = pgroup;  // this group's next chunk of the current tile (chunk = K-chunk ci % KCH of slot ci / KCH)
+        for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
+            load_x(tp);
 #pragma unroll 1
-            for (int ci = 0; ci < chunks_per_tile; ++ci) {
-                ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)ci);
-#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_STS)
-                const uint32_t a_row = stages_u32 + stage * A_STAGE_BYTES + row * 128;
+            for (; ci < chunks_per_tile; ci += PGROUPS) {
+                const int s = ci / Cfg::KCH, kc = ci - s * Cfg::KCH;
+                uint32_t v[GROUPS_PER_THREAD][4];  // this thread's share of its row (4 frequencies per 16-byte piece)
+#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_GEN)
+                const float xv = x_row[s * TILE_M];  // angle s for s < k, distance at s == k
 #pragma unroll
                 for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
-                    const uint32_t addr = a_row + (((part * GROUPS_PER_THREAD + gg) ^ (row & 7)) << 4);
+                    // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
+                    const float4 w = s_div4[kc * 8 + part * GROUPS_PER_THREAD + gg];
+                    const float o0 = __fmul_rn(xv, w.x), o1 = __fmul_rn(xv, w.y);
+                    const float o2 = __fmul_rn(xv, w.z), o3 = __fmul_rn(xv, w.w);
+#ifdef K2_DBG_NO_SINCOS  // timing experiments only (tools/k2_variants.sh)
+                    v[gg][0] = pack_bf16x2(o0, o0 + 1.f); v[gg][1] = pack_bf16x2(o1, o1 + 1.f);
+                    v[gg][2] = pack_bf16x2(o2, o2 + 1.f); v[gg][3] = pack_bf16x2(o3, o3 + 1.f);
+#else
+                    if (gg < K2_MUFU_GROUPS) {  // MUFU.SIN / MUFU.COS (XU pipe, 16 results / clk / SM)
+                        v[gg][0] = pack_bf16x2(__sinf(o0), __cosf(o0));
+                        v[gg][1] = pack_bf16x2(__sinf(o1), __cosf(o1));
+                        v[gg][2] = pack_bf16x2(__sinf(o2), __cosf(o2));
+                        v[gg][3] = pack_bf16x2(__sinf(o3), __cosf(o3));
+                    } else {                    // polynomial on the FMA pipe (experiment: not faster)
+                        float s0, c0, s1, c1, s2, c2, s3, c3;
+                        sincos_fma(o0, s0, c0); sincos_fma(o1, s1, c1); sincos_fma(o2, s2, c2); sincos_fma(o3, s3, c3);
+                        v[gg][0] = pack_bf16x2(s0, c0); v[gg][1] = pack_bf16x2(s1, c1);
+                        v[gg][2] = pack_bf16x2(s2, c2); v[gg][3] = pack_bf16x2(s3, c3);
+                    }
+#endif
+                }
+#endif
+                // the row is built in registers BEFORE the wait: the stage is normally free by then
+                ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)ci);
+#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_STS)
+                const uint32_t a_dst = a_row + stage * A_STAGE_BYTES;
+#pragma unroll
+                for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
+                    const uint32_t addr = a_dst + (((part * GROUPS_PER_THREAD + gg) ^ sw) << 4);
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v[gg][0]),
                                  "r"(v[gg][1]), "r"(v[gg][2]), "r"(v[gg][3])
                                  : "memory");
                 }
 #endif
-                // Software pipeline: the MUFU work of the NEXT chunk runs while this chunk's stores drain, so the
-                // proxy fence below finds them complete and the XU pipe never idles across the hand-over.
-                if (ci + 1 < chunks_per_tile) {
-                    generate(ci + 1);
-                } else if (tp + num_clusters < prm.num_tile_pairs) {
-                    load_x(tp + num_clusters);
-                    generate(0);
-                }
 #ifndef K2_DBG_NO_FENCE
                 ptx::fence_proxy_async_smem();  // make the st.shared visible to the tensor core (async proxy)
 #endif
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive_cluster(full_leader + 8 * stage);
-                if (++stage == Cfg::NSTAGE) { stage = 0; phase ^= 1; }
+                stage += PGROUPS;
+                if (stage >= Cfg::NSTAGE) { stage -= Cfg::NSTAGE; phase ^= 1; }
             }
-            tp += num_clusters;
+            ci -= chunks_per_tile;
         }
     } else if (warp < NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS) {
         // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================

@@ -6,7 +6,10 @@ mkdir -p tools/bin/variants
 SRC=ref-geotransformer_b200/csrc
 for v in "$@"; do
   flags=""
-  for f in $(echo $v | tr '+' ' '); do flags="$flags -DK2_DBG_$f"; done
+  # NAME -> -DK2_DBG_NAME ; NAME=VALUE -> -DK2_NAME=VALUE (e.g. PGROUPS=2)
+  for f in $(echo $v | tr '+' ' '); do
+    case $f in *=*) flags="$flags -DK2_$f";; *) flags="$flags -DK2_DBG_$f";; esac
+  done
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Xcompiler -fPIC -shared $flags \
     $SRC/abi.cu $SRC/k1_knn.cu $SRC/k2_gse_embed_fp32.cu $SRC/k2_gse_embed.cu $SRC/k3_rpe_scores.cu $SRC/k3_attention.cu $SRC/k4_add_layernorm.cu \
     -o tools/bin/variants/lib_$v.so -lcudart &
