@@ -33,6 +33,7 @@ extern "C" {
 /* dtype tags for buffers that may be stored in either precision */
 #define GEOTX_F32 0
 #define GEOTX_BF16 1
+#define GEOTX_F16 2 /* IEEE half: the default storage format of E (11-bit significand, finite-saturated) */
 
 const char* geotx_last_error(void);
 int geotx_abi_version(void);

@@ -34,6 +34,7 @@ SIGNATURES = {
 
 GEOTX_F32 = 0
 GEOTX_BF16 = 1
+GEOTX_F16 = 2
 
 # kernels each entry point enqueues (bench.py's gpu_launches is counted from this)
 KERNELS_PER_CALL = {'geotx_gse_knn': 2, 'geotx_attention': 2}  # attention: + merge kernel when the keys are split

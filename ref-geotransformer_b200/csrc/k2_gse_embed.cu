@@ -101,7 +101,7 @@ struct K2Params {
     int n, k, row_begin, row_count;
     int num_tile_pairs;     // ceil(ceil(pairs_total / 128) / 2)
     float sigma_d, factor_a;
-    int reduce_mean, out_bf16;
+    int reduce_mean, out_dtype;
 };
 
 // watchdog tags: role << 24 | ring position
@@ -348,7 +348,12 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                             e[c + 2] += r1.x + bb.z; e[c + 3] += r1.y + bb.w;
                         }
                         if (do_store) {
-                            if (prm.out_bf16) {
+                            if (prm.out_dtype == GEOTX_F16) {  // default storage format of E: 11-bit significand
+                                __half2 o[8];
+#pragma unroll
+                                for (int c = 0; c < 8; ++c) o[c] = __floats2half2_rn(e[2 * c], e[2 * c + 1]);
+                                st_global_v8((__half*)prm.out + p * C + colhalf * NCOL + c0, (const uint32_t*)o);
+                            } else if (prm.out_dtype == GEOTX_BF16) {
                                 uint32_t o[8];
 #pragma unroll
                                 for (int c = 0; c < 8; ++c) o[c] = pack_bf16x2(e[2 * c], e[2 * c + 1]);
@@ -486,7 +491,8 @@ extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int ro
     GEOTX_REQUIRE(C == 128 || C == 256, "geotx_gse_embed: hidden_dim %d not supported by the tcgen05 path (128 or "
                   "256); use geotx_gse_embed_fp32", C);
     GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed: bad row slab");
-    GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16, "geotx_gse_embed: bad out_dtype");
+    GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16 || out_dtype == GEOTX_F16,
+                  "geotx_gse_embed: bad out_dtype");
     GEOTX_REQUIRE(((uintptr_t)out & 31) == 0 && ((uintptr_t)packed_weights & 15) == 0,
                   "geotx_gse_embed: out must be 32-byte and packed_weights 16-byte aligned");
     K2Params prm;
@@ -502,7 +508,7 @@ extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int ro
     prm.num_tile_pairs = (int)((tiles + 1) / 2);
     prm.sigma_d = sigma_d; prm.factor_a = factor_a;
     prm.reduce_mean = reduce_mean ? 1 : 0;
-    prm.out_bf16 = out_dtype == GEOTX_BF16;
+    prm.out_dtype = out_dtype;
     if (C == 256) return launch_k2<256>(prm, (cudaStream_t)stream);
     return launch_k2<128>(prm, (cudaStream_t)stream);
 }

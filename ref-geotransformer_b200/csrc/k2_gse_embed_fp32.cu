@@ -3,6 +3,7 @@
 // /root/reference/geotransformer/modules/transformer/positional_embedding.py:18-34 for ANY even hidden size.
 // This is the high-precision path (small hidden sizes, on-device cross-check of the tcgen05 kernel); the
 // throughput path is k2_gse_embed.cu.  Neither ever materialises the reference's (B,n,n,k,C) tensor.
+#include <cuda_fp16.h>
 #include "geotx_common.cuh"
 #include "host_util.h"
 
@@ -17,7 +18,7 @@ __global__ void gse_embed_fp32_kernel(const float4* __restrict__ pts4, const flo
                                       const float* __restrict__ div_term, const float* __restrict__ w_d,
                                       const float* __restrict__ b_d, const float* __restrict__ w_a,
                                       const float* __restrict__ b_a, int C, float sigma_d, float factor_a,
-                                      int reduce_mean, int out_bf16, void* __restrict__ out) {
+                                      int reduce_mean, int out_dtype, void* __restrict__ out) {
     extern __shared__ float smem[];
     float* xs = smem;                    // [F32_PAIRS][8]
     float* sv = smem + F32_PAIRS * 8;    // [F32_PAIRS][k+1][C]
@@ -98,7 +99,8 @@ __global__ void gse_embed_fp32_kernel(const float4* __restrict__ pts4, const flo
                 if (q < k) red = fmaxf(red, acc_a[p][q] + ba);
         }
         float e = (acc_d[p] + bd) + red;  // geotransformer.py:70
-        if (out_bf16) ((__nv_bfloat16*)out)[pp * C + c] = __float2bfloat16_rn(e);
+        if (out_dtype == GEOTX_BF16) ((__nv_bfloat16*)out)[pp * C + c] = __float2bfloat16_rn(e);
+        else if (out_dtype == GEOTX_F16) ((__half*)out)[pp * C + c] = __float2half_rn(e);
         else ((float*)out)[pp * C + c] = e;
     }
 }
@@ -115,7 +117,8 @@ extern "C" int geotx_gse_embed_fp32(const void* geometry, int B, int n, int k, i
     GEOTX_REQUIRE(B > 0 && n > 0 && k >= 1 && k <= GEOTX_MAX_ANGLE_K, "geotx_gse_embed_fp32: bad sizes");
     GEOTX_REQUIRE(C >= 2 && C % 2 == 0 && C <= 1024, "geotx_gse_embed_fp32: hidden_dim %d must be even and <= 1024", C);
     GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed_fp32: bad row slab");
-    GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16, "geotx_gse_embed_fp32: bad out_dtype");
+    GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16 || out_dtype == GEOTX_F16,
+                  "geotx_gse_embed_fp32: bad out_dtype");
     const float4* pts4 = (const float4*)geometry;
     const float4* refv = pts4 + (size_t)B * n;
     long long pairs = (long long)B * row_count * n;
@@ -128,6 +131,6 @@ extern "C" int geotx_gse_embed_fp32(const void* geometry, int B, int n, int k, i
     if (rc) return rc;
     gse_embed_fp32_kernel<<<(unsigned)blocks, C, smem, (cudaStream_t)stream>>>(
         pts4, refv, n, k, row_begin, row_count, pairs, div_term, w_d, b_d, w_a, b_a, C, sigma_d, factor_a,
-        reduce_mean, out_dtype == GEOTX_BF16, out);
+        reduce_mean, out_dtype, out);
     return launch_status("geotx_gse_embed_fp32");
 }

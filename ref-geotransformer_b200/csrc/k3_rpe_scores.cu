@@ -7,9 +7,10 @@
 //     scores_p[b,h,i,j] = (W_p[h]^T q[b,h,i]) . E[b,i,j,:]  (+ q.b_p, constant over j: cancels in the softmax)
 // so each layer reads E exactly once and never forms p.  The kernel is HBM-bound on E (2 n m C bytes in bf16):
 // every warp streams rows E[b,i,j0..j0+7,:] with 16-byte loads (8 rows x 64 contiguous bytes per instruction)
-// and contracts them against the folded query of row i on the tensor cores (mma.sync m16n8k16, bf16 in / fp32
-// accumulate, rows of the A fragment = heads).  The folded query is split into bf16 hi + lo parts so that its
-// rounding does not add to the error budget (E itself is the only bf16-rounded operand).
+// and contracts them against the folded query of row i on the tensor cores (mma.sync m16n8k16, 16-bit in / fp32
+// accumulate, rows of the A fragment = heads).  The folded query is split into hi + lo 16-bit parts so that its
+// rounding does not add to the error budget (E itself is the only 16-bit-rounded operand).
+#include <cuda_fp16.h>
 #include "geotx_common.cuh"
 #include "sm100_ptx.cuh"
 #include "host_util.h"
@@ -18,12 +19,39 @@ namespace geotx {
 
 constexpr int K3A_WARPS = 8;
 
-__device__ __forceinline__ void mma_bf16_16816(float* c, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+// 16-bit storage formats of E: both are contracted with fp32 accumulation; F16 = IEEE half (the format the embedding
+// kernel writes by default: 11-bit significand), otherwise bfloat16.
+template <bool F16>
+__device__ __forceinline__ void mma_16816(float* c, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
     // rows 8..15 of A are zero (a1 = a3 = 0): only H <= 8 heads are populated
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1));
+    if (F16)
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+            : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+            : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1));
+    else
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+            : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+            : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1));
+}
+// hi + lo split of two fp32 values into the 16-bit format (hi = rounded value, lo = rounded remainder)
+template <bool F16>
+__device__ __forceinline__ void split_hi_lo(float x, float y, uint32_t& hi, uint32_t& lo) {
+    if (F16) {
+        // saturate instead of overflowing to inf (|q| > 65504 does not occur with sane weights, but inf * 0 = NaN)
+        const float xs = fminf(fmaxf(x, -65504.f), 65504.f), ys = fminf(fmaxf(y, -65504.f), 65504.f);
+        const __half2 h = __floats2half2_rn(xs, ys);
+        const float2 hf = __half22float2(h);
+        const __half2 l = __floats2half2_rn(xs - hf.x, ys - hf.y);
+        hi = *(const uint32_t*)&h;
+        lo = *(const uint32_t*)&l;
+    } else {
+        const float h0 = __bfloat162float(__float2bfloat16_rn(x));
+        const float h1 = __bfloat162float(__float2bfloat16_rn(y));
+        hi = pack_bf16x2(h0, h1);
+        lo = pack_bf16x2(x - h0, y - h1);
+    }
 }
 
 __device__ __forceinline__ uint4 ldg_stream16(const void* p) {
@@ -57,10 +85,10 @@ struct K3ACfg {
     static constexpr int SMEM_BYTES = K3A_WARPS * K3A_STAGES * STAGE_BYTES + K3A_WARPS * K3A_STAGES * 8 + 128;
 };
 
-template <int C>
+template <int C, bool F16>
 __global__ void __launch_bounds__(K3A_WARPS * 32, 1)
-rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qsh, long long qsn,
-                       const __nv_bfloat16* __restrict__ E,
+rpe_scores_tc_kernel(const float* __restrict__ qt, long long qsb, long long qsh, long long qsn,
+                       const void* __restrict__ E,
                        int H, int n, int m, int row_begin, int row_count, long long chunks_total, int chunks_per_row,
                        long long chunks_per_warp, float* __restrict__ scores) {
     using Cfg = K3ACfg<C>;
@@ -106,7 +134,7 @@ rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qs
         const long long r = c / chunks_per_row;
         const int j0 = (int)(c - r * chunks_per_row) * K3A_KEYS;
         if (r != cur_row) {
-            // A fragments: folded query of (b, h = g, i), hi/lo bf16 split
+            // A fragments: folded query of (b, h = g, i), hi/lo split in E's 16-bit format
             cur_row = r;
             const int b = (int)(r / row_count);
             const int i = row_begin + (int)(r - (long long)b * row_count);
@@ -119,12 +147,7 @@ rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qs
                     const float4 v = __ldg((const float4*)(qrow + 32 * s + 4));
                     const float f[8] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w};
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float h0 = __bfloat162float(__float2bfloat16_rn(f[2 * e]));
-                        const float h1 = __bfloat162float(__float2bfloat16_rn(f[2 * e + 1]));
-                        ah[s][e] = pack_bf16x2(h0, h1);
-                        al[s][e] = pack_bf16x2(f[2 * e] - h0, f[2 * e + 1] - h1);
-                    }
+                    for (int e = 0; e < 4; ++e) split_hi_lo<F16>(f[2 * e], f[2 * e + 1], ah[s][e], al[s][e]);
                 }
             } else {
 #pragma unroll
@@ -147,14 +170,14 @@ rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qs
                          : "=r"(e0.x), "=r"(e0.y), "=r"(e0.z), "=r"(e0.w) : "r"(base + g * Cfg::PITCH + 64 * s));
             asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
                          : "=r"(e1.x), "=r"(e1.y), "=r"(e1.z), "=r"(e1.w) : "r"(base + (g + 8) * Cfg::PITCH + 64 * s));
-            mma_bf16_16816(c0, ah[s][0], ah[s][1], e0.x, e0.y);
-            mma_bf16_16816(d0, al[s][0], al[s][1], e0.x, e0.y);
-            mma_bf16_16816(c1, ah[s][0], ah[s][1], e1.x, e1.y);
-            mma_bf16_16816(d1, al[s][0], al[s][1], e1.x, e1.y);
-            mma_bf16_16816(c0, ah[s][2], ah[s][3], e0.z, e0.w);
-            mma_bf16_16816(d0, al[s][2], al[s][3], e0.z, e0.w);
-            mma_bf16_16816(c1, ah[s][2], ah[s][3], e1.z, e1.w);
-            mma_bf16_16816(d1, al[s][2], al[s][3], e1.z, e1.w);
+            mma_16816<F16>(c0, ah[s][0], ah[s][1], e0.x, e0.y);
+            mma_16816<F16>(d0, al[s][0], al[s][1], e0.x, e0.y);
+            mma_16816<F16>(c1, ah[s][0], ah[s][1], e1.x, e1.y);
+            mma_16816<F16>(d1, al[s][0], al[s][1], e1.x, e1.y);
+            mma_16816<F16>(c0, ah[s][2], ah[s][3], e0.z, e0.w);
+            mma_16816<F16>(d0, al[s][2], al[s][3], e0.z, e0.w);
+            mma_16816<F16>(c1, ah[s][2], ah[s][3], e1.z, e1.w);
+            mma_16816<F16>(d1, al[s][2], al[s][3], e1.z, e1.w);
         }
         __syncwarp();  // every lane has consumed the stage (its values fed the mma above): safe to refill it
         if (lane == 0 && c + K3A_STAGES < c_end) issue(c + K3A_STAGES);
@@ -167,6 +190,10 @@ rpe_scores_bf16_kernel(const float* __restrict__ qt, long long qsb, long long qs
         }
     }
 }
+
+__device__ __forceinline__ float to_f32(float x) { return x; }
+__device__ __forceinline__ float to_f32(__nv_bfloat16 x) { return __bfloat162float(x); }
+__device__ __forceinline__ float to_f32(__half x) { return __half2float(x); }
 
 // Generic fp32-arithmetic variant (any C, E in fp32 or bf16): one warp per (slab row, key), lanes stride channels.
 template <typename ET>
@@ -184,7 +211,7 @@ rpe_scores_generic_kernel(const float* __restrict__ qt, long long qsb, long long
     for (int h = 0; h < H; ++h) {
         const float* q = qt + (size_t)b * qsb + (size_t)h * qsh + (size_t)i * qsn;
         float acc = 0.f;
-        for (int c = lane; c < C; c += 32) acc = fmaf(q[c], (float)e[c], acc);
+        for (int c = lane; c < C; c += 32) acc = fmaf(q[c], to_f32(e[c]), acc);
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
         if (lane == 0) scores[(((size_t)b * H + h) * n + i) * m + j] = acc;
@@ -200,10 +227,10 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
     GEOTX_REQUIRE(qt && E && scores_p, "geotx_rpe_scores: null pointer");
     GEOTX_REQUIRE(B > 0 && H > 0 && n > 0 && m > 0 && C > 0, "geotx_rpe_scores: bad sizes");
     GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_rpe_scores: bad row slab");
-    GEOTX_REQUIRE(e_dtype == GEOTX_F32 || e_dtype == GEOTX_BF16, "geotx_rpe_scores: bad e_dtype");
+    GEOTX_REQUIRE(e_dtype == GEOTX_F32 || e_dtype == GEOTX_BF16 || e_dtype == GEOTX_F16, "geotx_rpe_scores: bad e_dtype");
     cudaStream_t st = (cudaStream_t)stream;
     const long long rows = (long long)B * row_count;
-    const bool fast = e_dtype == GEOTX_BF16 && (C == 128 || C == 256) && H <= 8 &&
+    const bool fast = e_dtype != GEOTX_F32 && (C == 128 || C == 256) && H <= 8 &&
                       (((uintptr_t)E | (uintptr_t)qt) & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0 && qt_stride_n % 4 == 0;
     if (fast) {
         static int num_sms = 0;
@@ -213,10 +240,12 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
             if (rc) return rc;
             rc = check_cuda(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
             if (rc) return rc;
-            rc = check_cuda(cudaFuncSetAttribute(rpe_scores_bf16_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 K3ACfg<256>::SMEM_BYTES), "cudaFuncSetAttribute(rpe_scores<256>)");
-            if (!rc) rc = check_cuda(cudaFuncSetAttribute(rpe_scores_bf16_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                          K3ACfg<128>::SMEM_BYTES), "cudaFuncSetAttribute(rpe_scores<128>)");
+            const void* kernels[4] = {(const void*)rpe_scores_tc_kernel<256, false>, (const void*)rpe_scores_tc_kernel<256, true>,
+                                      (const void*)rpe_scores_tc_kernel<128, false>, (const void*)rpe_scores_tc_kernel<128, true>};
+            for (int i = 0; i < 4 && !rc; ++i)
+                rc = check_cuda(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     i < 2 ? K3ACfg<256>::SMEM_BYTES : K3ACfg<128>::SMEM_BYTES),
+                                "cudaFuncSetAttribute(rpe_scores_tc_kernel)");
             if (rc) { num_sms = 0; return rc; }
         }
         // persistent: one CTA per SM, every warp streams a contiguous range of 16-key chunks
@@ -226,14 +255,14 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
         if (ctas > num_sms) ctas = num_sms;
         const long long warps = ctas * K3A_WARPS;
         const long long chunks_per_warp = (chunks_total + warps - 1) / warps;
-        if (C == 256)
-            rpe_scores_bf16_kernel<256><<<(unsigned)ctas, K3A_WARPS * 32, K3ACfg<256>::SMEM_BYTES, st>>>(
-                qt, qt_stride_b, qt_stride_h, qt_stride_n, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
-                chunks_per_row, chunks_per_warp, scores_p);
-        else
-            rpe_scores_bf16_kernel<128><<<(unsigned)ctas, K3A_WARPS * 32, K3ACfg<128>::SMEM_BYTES, st>>>(
-                qt, qt_stride_b, qt_stride_h, qt_stride_n, (const __nv_bfloat16*)E, H, n, m, row_begin, row_count, chunks_total,
-                chunks_per_row, chunks_per_warp, scores_p);
+        const bool f16 = e_dtype == GEOTX_F16;
+#define GEOTX_K3A_LAUNCH(CC, FF)                                                                                      \
+    rpe_scores_tc_kernel<CC, FF><<<(unsigned)ctas, K3A_WARPS * 32, K3ACfg<CC>::SMEM_BYTES, st>>>(                        \
+        qt, qt_stride_b, qt_stride_h, qt_stride_n, E, H, n, m, row_begin, row_count, chunks_total, chunks_per_row,      \
+        chunks_per_warp, scores_p)
+        if (C == 256) { if (f16) GEOTX_K3A_LAUNCH(256, true); else GEOTX_K3A_LAUNCH(256, false); }
+        else          { if (f16) GEOTX_K3A_LAUNCH(128, true); else GEOTX_K3A_LAUNCH(128, false); }
+#undef GEOTX_K3A_LAUNCH
     } else {
         long long pairs = rows * m;
         long long blocks = (pairs + 7) / 8;
@@ -241,6 +270,9 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
         if (e_dtype == GEOTX_BF16)
             rpe_scores_generic_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(
                 qt, qt_stride_b, qt_stride_h, qt_stride_n, (const __nv_bfloat16*)E, H, n, m, C, row_begin, row_count, pairs, scores_p);
+        else if (e_dtype == GEOTX_F16)
+            rpe_scores_generic_kernel<__half><<<(unsigned)blocks, 256, 0, st>>>(
+                qt, qt_stride_b, qt_stride_h, qt_stride_n, (const __half*)E, H, n, m, C, row_begin, row_count, pairs, scores_p);
         else
             rpe_scores_generic_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(
                 qt, qt_stride_b, qt_stride_h, qt_stride_n, (const float*)E, H, n, m, C, row_begin, row_count, pairs, scores_p);

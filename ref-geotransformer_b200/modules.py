@@ -121,6 +121,7 @@ class GeometricStructureEmbedding(nn.Module):
         self.precision = precision
         self._packed = None
         self._packed_key = None
+        self._e_bound = math.inf
 
     def _use_tensor_cores(self):
         ok = self.hidden_dim in (128, 256)
@@ -132,9 +133,21 @@ class GeometricStructureEmbedding(nn.Module):
         ts = (self.proj_d.weight, self.proj_d.bias, self.proj_a.weight, self.proj_a.bias)
         key = tuple((t.data_ptr(), t._version) for t in ts)
         if self._packed is None or key != self._packed_key:
-            self._packed = ops.gse_pack_weights(*[t.detach().contiguous() for t in ts])
+            w_d, b_d, w_a, b_a = [t.detach().contiguous() for t in ts]
+            self._packed = ops.gse_pack_weights(w_d, b_d, w_a, b_a)
+            # |sin|, |cos| <= 1, so |E_c| <= ||W_d[c,:]||_1 + ||W_a[c,:]||_1 + |b_d[c] + b_a[c]| whatever the points are
+            self._e_bound = float((w_d.abs().sum(1) + w_a.abs().sum(1) + (b_d + b_a).abs()).max())
             self._packed_key = key
         return self._packed
+
+    def storage_dtype(self):
+        """Format E is stored in between the embedding kernel and the 'self' blocks: IEEE half (11-bit significand)
+        when the weights cannot push |E| out of its range (the bound above, checked when the weights are packed),
+        else bfloat16; fp32 on the CUDA-core path."""
+        if not self._use_tensor_cores():
+            return torch.float32
+        self._packed_weights()
+        return torch.float16 if self._e_bound < 3.0e4 else torch.bfloat16
 
     @torch.no_grad()
     def geometry(self, points):
@@ -156,7 +169,7 @@ class GeometricStructureEmbedding(nn.Module):
 
     def forward(self, points, out_dtype=torch.float32):
         """(B,n,3) -> (B,n,n,C).  Standalone calls return fp32 like the reference; GeometricTransformer asks for
-        the bf16 storage format internally."""
+        the 16-bit storage format (storage_dtype()) internally."""
         _forward_only_guard(self, points)
         return self.embed(self.geometry(points), out_dtype)
 
@@ -266,7 +279,7 @@ class RPEMultiHeadAttention(_FusedAttentionBase):
         return qt.view(H, B, n, D).permute(1, 0, 2, 3)                 # logical (B,H,N,C), no copy
 
     def forward(self, input_q, input_k, input_v, embed_qk, key_weights=None, key_masks=None, attention_factors=None):
-        """embed_qk: (B,N,M,C) bf16 or fp32 embedding E (from GeometricStructureEmbedding)."""
+        """embed_qk: (B,N,M,C) fp16, bf16 or fp32 embedding E (from GeometricStructureEmbedding)."""
         _forward_only_guard(self, input_q, input_k, input_v, embed_qk)
         q = self.proj_q(input_q)
         k = self.proj_k(input_k)
@@ -407,7 +420,7 @@ class StreamedEmbedding:
         if self.E is not None:
             return ops.rpe_scores(qt, self.E)
         n, C = self.geom.n, self.embedding.hidden_dim
-        row_bytes = n * C * (2 if self.dtype == torch.bfloat16 else 4)
+        row_bytes = n * C * (4 if self.dtype == torch.float32 else 2)
         rows = n if self.slab_bytes <= 0 else max(1, min(n, self.slab_bytes // row_bytes))
         if rows >= n or self.geom.B != 1:
             return ops.rpe_scores(qt, self.materialise())
@@ -547,7 +560,8 @@ class RPEConditionalTransformer(nn.Module):
 
 class GeometricTransformer(nn.Module):
     """geotransformer.py:75-155.  Extra keyword `precision` ('auto' | 'bf16' | 'fp32') selects the embedding
-    kernel and the storage type of E (bf16 / fp32); everything else is the reference signature."""
+    kernel ('bf16' = tcgen05 with bf16 operands, fp32 accumulation; E stored as fp16, or bf16 if the weights could
+    overflow it) or the fp32 CUDA-core kernel (E stored as fp32); everything else is the reference signature."""
 
     def __init__(self, input_dim, output_dim, hidden_dim, num_heads, blocks, sigma_d, sigma_a, angle_k, dropout=None,
                  activation_fn='ReLU', reduction_a='max', precision='auto'):
@@ -564,7 +578,7 @@ class GeometricTransformer(nn.Module):
     def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
         _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
         tc = self.embedding._use_tensor_cores()
-        e_dtype = torch.bfloat16 if tc else torch.float32
+        e_dtype = self.embedding.storage_dtype()
         ref_embeddings = StreamedEmbedding(self.embedding, self.embedding.geometry(ref_points), e_dtype,
                                            self.l2_slab_bytes)
         src_embeddings = StreamedEmbedding(self.embedding, self.embedding.geometry(src_points), e_dtype,

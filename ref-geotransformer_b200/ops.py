@@ -10,7 +10,8 @@ from . import _abi
 
 GEOTX_F32 = _abi.GEOTX_F32
 GEOTX_BF16 = _abi.GEOTX_BF16
-_DT = {torch.float32: GEOTX_F32, torch.bfloat16: GEOTX_BF16}
+GEOTX_F16 = _abi.GEOTX_F16
+_DT = {torch.float32: GEOTX_F32, torch.bfloat16: GEOTX_BF16, torch.float16: GEOTX_F16}
 
 
 def _check(t, name, dtype=None, dims=None):
@@ -85,7 +86,7 @@ def _slab(geom, row_begin, row_count):
     return row_begin, row_count
 
 
-def gse_embed(geom, div_term, packed, C, sigma_d, factor_a, reduce_mean=False, out_dtype=torch.bfloat16,
+def gse_embed(geom, div_term, packed, C, sigma_d, factor_a, reduce_mean=False, out_dtype=torch.float16,
               row_begin=0, row_count=None, out=None):
     """tcgen05 path.  -> E (B,row_count,n,C).  geotransformer.py:57-72."""
     _check(div_term, 'div_term', torch.float32, 1)
@@ -131,7 +132,7 @@ def _row_strided(t, name):
 
 def rpe_scores(qt, E, n=None, row_begin=0, out=None):
     """qt: folded query, logical shape (B,H,n,C) fp32 (any view with unit channel stride);
-    E (B,row_count,m,C) bf16|fp32  ->  scores_p (B,H,n,m) fp32 (slab rows written).
+    E (B,row_count,m,C) fp16|bf16|fp32  ->  scores_p (B,H,n,m) fp32 (slab rows written).
     rpe_transformer.py:54-56 with proj_p folded."""
     if not (isinstance(qt, torch.Tensor) and qt.is_cuda and qt.dtype == torch.float32 and qt.dim() == 4):
         raise RuntimeError('qt must be a 4-d fp32 CUDA tensor')
@@ -140,7 +141,7 @@ def rpe_scores(qt, E, n=None, row_begin=0, out=None):
         qt = qt.contiguous()
     _check(E, 'E', None, 4)
     if E.dtype not in _DT:
-        raise RuntimeError(f'E must be fp32 or bf16, got {E.dtype}')
+        raise RuntimeError(f'E must be fp32, fp16 or bf16, got {E.dtype}')
     Bq, row_count, m, Ce = E.shape
     if Bq != B or Ce != C:
         raise RuntimeError(f'shape mismatch: qt {tuple(qt.shape)} vs E {tuple(E.shape)}')

@@ -49,7 +49,7 @@ def test_shipped_configs_vs_reference_golden(pkg, oracle, golden, name, precisio
 
 @pytest.mark.parametrize('C,reduction', [(128, 'max'), (256, 'mean'), (256, 'max')])
 def test_tensor_core_kernel_vs_oracle(pkg, oracle, C, reduction):
-    """Ragged n (tile tail), B = 2, k = 2, both reductions, bf16 and fp32 outputs, row slabs."""
+    """Ragged n (tile tail), B = 2, k = 2, both reductions, f16 / bf16 / fp32 outputs, row slabs."""
     cfg = dict(hidden_dim=C, sigma_d=0.3, sigma_a=10, angle_k=2, reduction_a=reduction)
     sd = oracle.init_state_dict(8, 8, C, [], seed=5)
     g = torch.Generator().manual_seed(C)
@@ -60,10 +60,14 @@ def test_tensor_core_kernel_vs_oracle(pkg, oracle, C, reduction):
         geom = m.geometry(pts.to(DEV))
         e32 = m.embed(geom, torch.float32)
         e16 = m.embed(geom, torch.bfloat16)
+        eh = m.embed(geom, torch.float16)
         slab = m.embed(geom, torch.float32, row_begin=40, row_count=77)
+    assert m.storage_dtype() == torch.float16  # default nn.Linear init is far inside the half range
     assert rel(e32, exp) <= 8e-3
     assert rel(e16, exp) <= 1e-2
+    assert rel(eh, exp) <= 8e-3
     assert torch.equal(slab, e32[:, 40:117]), 'row slabs must reproduce the whole-cloud result bit for bit'
+    assert torch.equal(eh, e32.to(torch.float16)), 'f16 output is the rounded fp32 output'
     assert torch.equal(e16, e32.to(torch.bfloat16)), 'bf16 output is the rounded fp32 output'
 
 
@@ -107,3 +111,20 @@ def test_embed_rejects_bad_arguments(pkg, oracle):
     assert rel(e, exp) <= TOL_FP32
     with pytest.raises(RuntimeError, match='forward-only'):
         m(pts.to(DEV))  # grad enabled + parameters require grad
+
+
+def test_storage_format_falls_back_to_bf16_when_half_could_overflow(pkg, oracle):
+    """|E_c| <= ||W_d[c]||_1 + ||W_a[c]||_1 + |b|: with weights scaled far beyond any checkpoint the module must pick
+    bf16 storage (same exponent range as fp32) and still match the oracle."""
+    cfg = dict(hidden_dim=128, sigma_d=0.3, sigma_a=10, angle_k=3, reduction_a='max')
+    sd = oracle.init_state_dict(8, 8, 128, [], seed=11)
+    sd = {k: (v * 40000.0 if k.endswith('proj_d.weight') else v) for k, v in sd.items()}
+    g = torch.Generator().manual_seed(3)
+    pts = torch.rand(1, 150, 3, generator=g) * 2.0
+    exp = oracle.gse(pts, sd, 'embedding.', cfg['sigma_d'], cfg['sigma_a'], cfg['angle_k'], 'max')
+    m = _gse(pkg, cfg, sd, 'bf16')
+    assert m.storage_dtype() == torch.bfloat16
+    with torch.no_grad():
+        e = m.embed(m.geometry(pts.to(DEV)), m.storage_dtype())
+    assert torch.isfinite(e).all()
+    assert rel(e, exp) <= 1e-2

@@ -14,7 +14,7 @@ def _rand(g, *shape):
 
 
 @pytest.mark.parametrize('C,H,n,m', [(256, 4, 97, 97), (128, 4, 130, 130), (256, 8, 64, 64), (64, 2, 50, 50)])
-@pytest.mark.parametrize('e_dtype', [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize('e_dtype', [torch.float16, torch.bfloat16, torch.float32])
 def test_rpe_scores_folded_query(pkg, C, H, n, m, e_dtype):
     """scores_p[b,h,i,j] = (W_p[h]^T q[b,h,i]) . E[b,i,j]  ==  einsum(q, proj_p(E)) - q.b_p  (SURVEY.md 8a-7)."""
     g = torch.Generator().manual_seed(C + n)

@@ -13,6 +13,7 @@ pkg = pkgpath.load_package()
 if len(sys.argv) > 1:
     pkg._abi.LIB_PATH = os.path.abspath(sys.argv[1])
 dev = 'cuda:0'
+DT = {'f16': torch.float16, 'bf16': torch.bfloat16, 'f32': torch.float32}[os.environ.get('K2_DTYPE', 'f16')]
 CASES = ((256, 1024, 0.2), (256, 2048, 0.2), (128, 2048, 4.8))
 if os.environ.get('K2_CASE'):
     CASES = (CASES[int(os.environ['K2_CASE'])],)
@@ -22,15 +23,15 @@ for C, n, sd in CASES:
     pts = (torch.rand(1, n, 3) * (3.0 if C == 256 else 100.0)).to(dev)
     with torch.no_grad():
         geom = m.geometry(pts)
-        out = torch.empty(1, n, n, C, dtype=torch.bfloat16, device=dev)
+        out = torch.empty(1, n, n, C, dtype=DT, device=dev)
         for _ in range(3):
-            m.embed(geom, torch.bfloat16, out=out)
+            m.embed(geom, DT, out=out)
         torch.cuda.synchronize()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         reps = 10
         ev[0].record()
         for _ in range(reps):
-            m.embed(geom, torch.bfloat16, out=out)
+            m.embed(geom, DT, out=out)
         ev[1].record()
         torch.cuda.synchronize()
     ms = ev[0].elapsed_time(ev[1]) / reps

@@ -30,7 +30,7 @@ for C, n in ((256, 1024), (256, 2048), (128, 2048)):
     torch.manual_seed(0)
     att = pkg.RPEMultiHeadAttention(C, H).to(dev)
     x = torch.randn(1, n, C, device=dev)
-    Es = [torch.randn(1, n, n, C, device=dev).to(torch.bfloat16) for _ in range(2)]  # rotate: each > L2
+    Es = [torch.randn(1, n, n, C, device=dev).to(torch.float16) for _ in range(2)]  # rotate: each > L2
     with torch.no_grad():
         q = att.proj_q(x)
         k = att.proj_k(x)
