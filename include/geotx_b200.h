@@ -103,13 +103,15 @@ int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, 
  *   token (row) strides in floats (H*c when dense; larger when q,k,v are column blocks of a fused projection output),
  *   scores_p f32 [B,H,n,m] or NULL, key_mask u8 [B,m] or NULL (non-zero = ignore),
  *   out f32 [B,n,H*c].  c (per-head dim) in {16, 32, 64}.
- *   workspace: geotx_attention_workspace_bytes() bytes of scratch, or NULL.  With a workspace the key range is split
- *   over several CTAs per (query tile, head) (partial softmax states merged by a second kernel), which is what keeps
- *   148 SMs busy when n is about a thousand; with NULL one CTA walks all keys.  Same result up to fp32 rounding. */
-int64_t geotx_attention_workspace_bytes(int B, int H, int n, int m, int c);
+ *   split_keys != 0: when the grid would otherwise be small (n about a thousand gives only 64 (query tile, head)
+ *   pairs for 148 SMs) the key range is split over the 2, 4 or 8 CTAs of a thread-block cluster, which merge their
+ *   partial softmax states through distributed shared memory (no workspace, no second launch).  split_keys == 0: one
+ *   CTA walks all keys of its query tile.  Same result up to fp32 rounding.
+ *   Arithmetic: q, k, v and the softmax weights enter the two contractions as IEEE half (11-bit significand, values
+ *   saturated to +-65504); accumulation, logits, scores_p, softmax and the output are fp32. */
 int geotx_attention(const float* q, const float* k, const float* v, const float* scores_p,
                     const uint8_t* key_mask, int B, int H, int n, int m, int c, int ld_q, int ld_k, int ld_v,
-                    float scale, float* out, void* workspace, void* stream);
+                    float scale, float* out, int split_keys, void* stream);
 
 /* out = LayerNorm(x + residual) over the last dimension (rpe_transformer.py:103, vanilla_transformer.py:101,
  * output_layer.py:20; torch.nn.LayerNorm semantics: biased variance, eps inside the root).  residual may be NULL.

@@ -27,8 +27,7 @@ SIGNATURES = {
     'geotx_watchdog_status': (_i, [_p]),
     'geotx_gse_embed_fp32': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
     'geotx_rpe_scores': (_i, [_p, _i64, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
-    'geotx_attention_workspace_bytes': (_i64, [_i, _i, _i, _i, _i]),
-    'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _f, _p, _p, _p]),
+    'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _f, _p, _i, _p]),
     'geotx_add_layernorm': (_i, [_p, _p, _p, _p, _i64, _i, _f, _p, _p]),
 }
 
@@ -37,7 +36,7 @@ GEOTX_BF16 = 1
 GEOTX_F16 = 2
 
 # kernels each entry point enqueues (bench.py's gpu_launches is counted from this)
-KERNELS_PER_CALL = {'geotx_gse_knn': 2, 'geotx_attention': 2}  # attention: + merge kernel when the keys are split
+KERNELS_PER_CALL = {'geotx_gse_knn': 2}  # pack_points + knn
 
 _lib = None
 launch_count = 0  # hand-written kernels launched through this binding so far

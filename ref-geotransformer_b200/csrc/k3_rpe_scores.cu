@@ -40,12 +40,9 @@ template <bool F16>
 __device__ __forceinline__ void split_hi_lo(float x, float y, uint32_t& hi, uint32_t& lo) {
     if (F16) {
         // saturate instead of overflowing to inf (|q| > 65504 does not occur with sane weights, but inf * 0 = NaN)
-        const float xs = fminf(fmaxf(x, -65504.f), 65504.f), ys = fminf(fmaxf(y, -65504.f), 65504.f);
-        const __half2 h = __floats2half2_rn(xs, ys);
-        const float2 hf = __half22float2(h);
-        const __half2 l = __floats2half2_rn(xs - hf.x, ys - hf.y);
-        hi = *(const uint32_t*)&h;
-        lo = *(const uint32_t*)&l;
+        asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(y), "f"(x));
+        const float2 hf = __half22float2(*(const __half2*)&hi);
+        asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(y - hf.y), "f"(x - hf.x));
     } else {
         const float h0 = __bfloat162float(__float2bfloat16_rn(x));
         const float h1 = __bfloat162float(__float2bfloat16_rn(y));

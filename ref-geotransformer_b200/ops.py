@@ -176,10 +176,8 @@ def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None, spli
         out = torch.empty(B, n, D, dtype=torch.float32, device=q.device)
     elif tuple(_check(out, 'out', torch.float32, 3).shape) != (B, n, D):
         raise RuntimeError(f'out must be {(B, n, D)}, got {tuple(out.shape)}')
-    ws_bytes = _abi.load().geotx_attention_workspace_bytes(B, num_heads, n, m, c)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device) if (ws_bytes > 0 and split_keys) else None
     _abi.call('geotx_attention', _p(q), _p(k), _p(v), _p(scores_p), _p(mask_u8), B, num_heads, n, m, c, ldq, ldk, ldv,
-              float(scale), _p(out), _p(ws), _stream())
+              float(scale), _p(out), int(bool(split_keys)), _stream())
     return out
 
 

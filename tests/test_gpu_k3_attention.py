@@ -61,7 +61,7 @@ def test_attention_vs_torch(pkg, oracle, c, H, n, m, with_p, with_mask):
     got = pkg.ops.attention(q.to(DEV), k.to(DEV), v.to(DEV), H, None if sp is None else sp.to(DEV),
                             None if mask is None else mask.to(DEV))
     assert rel(got, exp) <= 2e-3
-    # without a workspace one CTA walks every key tile: same math, no split/merge
+    # split_keys=False: one CTA walks every key tile: same math, no cluster split/merge
     one = pkg.ops.attention(q.to(DEV), k.to(DEV), v.to(DEV), H, None if sp is None else sp.to(DEV),
                             None if mask is None else mask.to(DEV), split_keys=False)
     assert rel(one, exp) <= 2e-3 and rel(one, got) <= 1e-3  # P is rounded to TF32 against a different running max

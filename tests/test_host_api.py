@@ -137,7 +137,7 @@ def test_abi_argument_errors_without_gpu(pkg):
     assert lib.geotx_gse_knn(p, 1, 10, 9, p, p, None) == -1
     assert lib.geotx_gse_embed(p, 1, 8, 3, 0, 8, p, p, 64, 0.2, 1.0, 0, 1, p, None) == -1
     assert b'hidden_dim' in lib.geotx_last_error()
-    assert lib.geotx_attention(p, p, p, None, None, 1, 4, 8, 8, 48, 192, 192, 192, 0.1, p, None, None) == -1
+    assert lib.geotx_attention(p, p, p, None, None, 1, 4, 8, 8, 48, 192, 192, 192, 0.1, p, 1, None) == -1
 
 
 def test_synthetic_inputs_are_deterministic(pkg):
