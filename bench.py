@@ -36,7 +36,7 @@ WORKLOADS = {
     '3dmatch_4096': ('3dmatch', 4096, 4096),   # configs[3] sweep point named by north_star
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of one gse_embed_tc_kernel launch (ncu --set full, profiles/r01_ncu_k2_*)
-K2_NCU_TRAFFIC_BYTES = {'3dmatch_1024': 483.9e6}
+K2_NCU_TRAFFIC_BYTES = {"3dmatch_1024": 483.98e6}  # profiles/r01_ncu_k2_v4.txt
 METRIC = 'registration pairs/sec (embed+RPE-attn) at N superpoints'
 UNIT = 'pairs/s'
 
