@@ -313,6 +313,16 @@ class MultiHeadAttention(_FusedAttentionBase):
             self._fused, self._fused_key = (w, b), key
         return self._fused
 
+    def fused_qkv(self):
+        """[W_q; W_k; W_v] as one (C -> 3C) projection (a 'cross' block projects every token of both clouds once)."""
+        ps = (self.proj_q.weight, self.proj_q.bias) + tuple(self.fused_kv())
+        key = tuple((t.data_ptr(), t._version) for t in ps)
+        if getattr(self, '_fused3_key', None) != key:
+            w = torch.cat([self.proj_q.weight.detach(), ps[2]]).contiguous()
+            b = torch.cat([self.proj_q.bias.detach(), ps[3]]).contiguous()
+            self._fused3, self._fused3_key = (w, b), key
+        return self._fused3
+
     def forward(self, input_q, input_k, input_v, key_weights=None, key_masks=None, attention_factors=None,
                 attention_masks=None):
         _forward_only_guard(self, input_q, input_k, input_v)
@@ -489,7 +499,11 @@ class RPEConditionalTransformer(nn.Module):
     def _forward_fused(self, feats0, feats1, embeddings0, embeddings1, masks0, masks1):
         N, C = feats0.shape[1], feats0.shape[2]
         embs = [embeddings0, embeddings1]
-        x = torch.cat([feats0, feats1], dim=1)  # (1, N+M, C); cloud slices of it are contiguous views
+        if feats0.data_ptr() + feats0.numel() * feats0.element_size() == feats1.data_ptr():
+            # GeometricTransformer.forward projects both clouds into one buffer: view it, do not copy
+            x = torch.as_strided(feats0, (1, N + feats1.shape[1], C), feats0.stride())
+        else:
+            x = torch.cat([feats0, feats1], dim=1)  # (1, N+M, C); cloud slices of it are contiguous views
         T = x.shape[1]
         for i, block in enumerate(self.blocks):
             layer = self.layers[i]
@@ -511,15 +525,22 @@ class RPEConditionalTransformer(nn.Module):
                                   out=hidden[:, lo:hi])
                 x = self._post_attention(layer, hidden, x)
             else:
+                # One q|k|v projection of ALL tokens serves both steps' queries (each step queries with the OLD tokens
+                # of its cloud) and the first step's memory (the old second cloud); only the second step's memory --
+                # the UPDATED first cloud, conditional_transformer.py:110-111 -- needs its own k|v projection
+                # (parallel=True reads the old one: no second projection at all).
                 x_new = torch.empty_like(x)
-                wkv, bkv = att.fused_kv()
+                w3, b3 = att.fused_qkv()
+                y = F.linear(x, w3, b3)  # (1, T, 3C): q | k | v
                 order = ((0, N, N, T, masks1), (N, T, 0, N, masks0))  # (query cloud, memory cloud, memory mask)
                 for step, (qlo, qhi, mlo, mhi, mask) in enumerate(order):
-                    # sequential: the second step reads the UPDATED first cloud; parallel=True reads the old one
-                    mem_src = x_new if (step == 1 and not self.parallel) else x
-                    q = F.linear(x[:, qlo:qhi], att.proj_q.weight, att.proj_q.bias)
-                    kv = F.linear(mem_src[:, mlo:mhi], wkv, bkv)
-                    hidden = ops.attention(q, kv[:, :, :C], kv[:, :, C:], H, None, mask)
+                    if step == 1 and not self.parallel:
+                        wkv, bkv = att.fused_kv()
+                        kv = F.linear(x_new[:, mlo:mhi], wkv, bkv)
+                        k_mem, v_mem = kv[:, :, :C], kv[:, :, C:]
+                    else:
+                        k_mem, v_mem = y[:, mlo:mhi, C:2 * C], y[:, mlo:mhi, 2 * C:]
+                    hidden = ops.attention(y[:, qlo:qhi, :C], k_mem, v_mem, H, None, mask)
                     self._post_attention(layer, hidden, x[:, qlo:qhi], out=x_new[:, qlo:qhi])
                 x = x_new
         return x[:, :N], x[:, N:]
@@ -575,17 +596,47 @@ class GeometricTransformer(nn.Module):
         # slab of E kept L2-resident between the embedding kernel and the first block's scores kernel (0 = off)
         self.l2_slab_bytes = int(os.environ.get('GEOTX_L2_SLAB_BYTES', DEFAULT_L2_SLAB_BYTES))
 
+    def _side_stream(self, device):
+        streams = self.__dict__.setdefault('_side_streams', {})
+        if device not in streams:
+            streams[device] = torch.cuda.Stream(device)
+        return streams[device]
+
     def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
         _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
+        if not all(isinstance(t, torch.Tensor) and t.is_cuda for t in (ref_points, src_points, ref_feats, src_feats)):
+            raise RuntimeError('GeometricTransformer (ref-geotransformer_b200) needs CUDA tensor inputs: there is no '
+                               'CPU path')
         tc = self.embedding._use_tensor_cores()
         e_dtype = self.embedding.storage_dtype()
-        ref_embeddings = StreamedEmbedding(self.embedding, self.embedding.geometry(ref_points), e_dtype,
-                                           self.l2_slab_bytes)
-        src_embeddings = StreamedEmbedding(self.embedding, self.embedding.geometry(src_points), e_dtype,
-                                           self.l2_slab_bytes)
+        # The second cloud's k-NN + packing and its in_proj run on a side stream next to the first cloud's: all four
+        # are small launches (~25 us of latency-bound work each) that leave most of the GPU idle on their own.
+        cur = torch.cuda.current_stream(ref_points.device)
+        side = self._side_stream(ref_points.device)
+        one_buffer = ref_feats.dim() == 3 and ref_feats.shape[0] == 1 and src_feats.shape[0] == 1
         with _dense_precision(allow_tf32=tc):
-            ref_feats = self.in_proj(ref_feats)
-            src_feats = self.in_proj(src_feats)
+            if one_buffer:  # both clouds' tokens side by side: the transformer's fused schedule wants exactly this
+                N, M = ref_feats.shape[1], src_feats.shape[1]
+                x = ref_feats.new_empty(1, N + M, self.in_proj.out_features)
+                w_t = self.in_proj.weight.t()
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                src_geom = self.embedding.geometry(src_points)
+                if one_buffer:
+                    torch.addmm(self.in_proj.bias, src_feats[0], w_t, out=x[0, N:])
+                else:
+                    src_proj = self.in_proj(src_feats)
+            ref_geom = self.embedding.geometry(ref_points)
+            if one_buffer:
+                torch.addmm(self.in_proj.bias, ref_feats[0], w_t, out=x[0, :N])
+                ref_feats, src_feats = x[:, :N], x[:, N:]
+            else:
+                ref_feats, src_feats = self.in_proj(ref_feats), src_proj
+            cur.wait_stream(side)
+            for t in (src_geom.buf, src_geom.knn) + (() if one_buffer else (src_feats,)):
+                t.record_stream(cur)  # allocated on the side stream, consumed (and later freed) on this one
+            ref_embeddings = StreamedEmbedding(self.embedding, ref_geom, e_dtype, self.l2_slab_bytes)
+            src_embeddings = StreamedEmbedding(self.embedding, src_geom, e_dtype, self.l2_slab_bytes)
             ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
                                                     masks0=ref_masks, masks1=src_masks)
             if ref_feats.shape[0] == 1 and ref_feats.data_ptr() + ref_feats.numel() * 4 == src_feats.data_ptr():
