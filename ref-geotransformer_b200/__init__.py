@@ -5,13 +5,13 @@ GeometricStructureEmbedding) and /root/reference/geotransformer/modules/transfor
 RPETransformerLayer, TransformerLayer, SinusoidalPositionalEmbedding, ...).  Import via pkgpath.load_package()."""
 from . import _abi, dist, ops, synth  # noqa: F401
 from .modules import (  # noqa: F401
-    AttentionLayer, AttentionOutput, GeometricStructureEmbedding, GeometricTransformer, GraphedGeometricTransformer,
+    AttentionLayer, AttentionOutput, GeometricStructureEmbedding, GeometricTransformer, GraphedGeometricTransformer, PipelinedGeometricTransformer,
     MultiHeadAttention,
     RPEAttentionLayer, RPEConditionalTransformer, RPEMultiHeadAttention, RPETransformerLayer,
     SinusoidalPositionalEmbedding, TransformerLayer, build_act_layer, build_dropout_layer)
 
 __all__ = [
-    'GeometricTransformer', 'GraphedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
+    'GeometricTransformer', 'GraphedGeometricTransformer', 'PipelinedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
     'AttentionOutput', 'SinusoidalPositionalEmbedding', 'ops', 'synth',
 ]

@@ -690,3 +690,63 @@ class GraphedGeometricTransformer:
                 s.copy_(t, non_blocking=True)
         self.graph.replay()
         return self.static_out
+
+
+class PipelinedGeometricTransformer:
+    """Registration pairs that ARRIVE IN HOST MEMORY and whose features are wanted back in host memory.
+
+    At n ~ 1k a pair's inputs are 8.4 MB (two (n, 1024) fp32 feature matrices): ~0.35 ms over PCIe against 2.1 ms of
+    compute, so a serial copy -> forward -> copy loop leaves the GPU idle for 15 % of the time.  `depth` CUDA-graph
+    instances of the forward (each with its own static buffers) are kept in flight instead: the upload of pair p+1 and
+    the download of pair p-1 run on copy streams while pair p computes.
+
+        pipe = PipelinedGeometricTransformer(model, ref_points, src_points, ref_feats, src_feats)  # example DEVICE inputs
+        for ref_out, src_out in pipe.map(host_pairs):    # iterable of 4-tuples of (pinned) host tensors
+            ...                                          # pinned host tensors, valid until `depth` more results
+
+    Results come back in order and are bit-identical to `model(...)` on the same inputs."""
+
+    def __init__(self, model, ref_points, src_points, ref_feats, src_feats, depth=2):
+        if depth < 1:
+            raise ValueError('depth must be >= 1')
+        self.slots = []
+        for _ in range(depth):
+            g = GraphedGeometricTransformer(model, ref_points, src_points, ref_feats, src_feats)
+            host_out = tuple(torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in g.static_out)
+            ev = {k: torch.cuda.Event() for k in ('h2d', 'compute', 'd2h')}
+            self.slots.append((g, host_out, ev))
+        self.copy_in, self.copy_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+    @torch.no_grad()
+    def map(self, pairs):
+        compute = torch.cuda.current_stream()
+        depth = len(self.slots)
+        pending = []  # slots whose results have not been handed out yet, oldest first
+        for p, pair in enumerate(pairs):
+            g, host_out, ev = self.slots[p % depth]
+            if len(pending) == depth:  # this slot's previous result must be handed out before its buffers are reused
+                done = pending.pop(0)
+                done[2]['d2h'].synchronize()
+                yield done[1]
+            if len(pair) != 4:
+                raise RuntimeError('each pair is (ref_points, src_points, ref_feats, src_feats)')
+            self.copy_in.wait_event(ev['compute'])  # the slot's last replay no longer reads its static inputs
+            with torch.cuda.stream(self.copy_in):
+                for s, t in zip(g.static_in, pair):
+                    if s.shape != t.shape:
+                        raise RuntimeError(f'pipeline was captured for shape {tuple(s.shape)}, got {tuple(t.shape)}')
+                    s.copy_(t, non_blocking=True)
+                ev['h2d'].record(self.copy_in)
+            compute.wait_event(ev['h2d'])
+            compute.wait_event(ev['d2h'])  # the slot's last download no longer reads its static outputs
+            g.graph.replay()
+            ev['compute'].record(compute)
+            self.copy_out.wait_event(ev['compute'])
+            with torch.cuda.stream(self.copy_out):
+                for h, o in zip(host_out, g.static_out):
+                    h.copy_(o, non_blocking=True)
+                ev['d2h'].record(self.copy_out)
+            pending.append((g, host_out, ev))
+        for done in pending:
+            done[2]['d2h'].synchronize()
+            yield done[1]

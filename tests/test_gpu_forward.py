@@ -96,3 +96,24 @@ def test_l2_slab_interleave_is_bit_identical(pkg, oracle, slab_rows):
         b0, b1 = model(*args)
     assert torch.equal(a0, b0) and torch.equal(a1, b1)
     assert pkg._abi.watchdog() is None
+
+
+def test_pipelined_host_to_host_serving_matches_direct_forward(pkg, oracle):
+    """PipelinedGeometricTransformer: 5 distinct host pairs through 2 graph instances with overlapped copies come back
+    in order and bit-identical to model(...) on the same inputs."""
+    cfg = dict(pkg.synth.CONFIGS['3dmatch'])
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    model = build_model(pkg, cfg, sd)
+    n, m = 160, 96
+    host = [tuple(t.pin_memory() for t in pkg.synth.make_pair('3dmatch', n, m, seed=20 + p)) for p in range(5)]
+    with torch.no_grad():
+        want = [tuple(o.cpu() for o in model(*[t.to(DEV) for t in pr])) for pr in host]
+    pipe = pkg.PipelinedGeometricTransformer(model, *[t.to(DEV) for t in host[0]], depth=2)
+    got = [tuple(o.clone() for o in out) for out in pipe.map(host)]
+    assert len(got) == 5
+    for w, g in zip(want, got):
+        assert torch.equal(w[0], g[0]) and torch.equal(w[1], g[1])
+    # a second pass reuses the slots
+    again = [tuple(o.clone() for o in out) for out in pipe.map(host[::-1])]
+    for w, g in zip(want[::-1], again):
+        assert torch.equal(w[0], g[0]) and torch.equal(w[1], g[1])
