@@ -232,10 +232,10 @@ def run_b200(args):
     k2_events = []
     orig_embed = model.embedding.embed
 
-    def timed_embed(geom, out_dtype, row_begin=0, row_count=None, out=None):
+    def timed_embed(geom, out_dtype, row_begin=0, row_count=None, out=None, qt=None):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        res = orig_embed(geom, out_dtype, row_begin, row_count, out)
+        res = orig_embed(geom, out_dtype, row_begin, row_count, out, qt=qt)
         e1.record()
         rows = geom.n - row_begin if row_count is None else row_count
         k2_events.append((e0, e1, flops_gse(geom.n, C, k) * rows / geom.n))  # a launch covers `rows` query rows
@@ -318,7 +318,7 @@ def run_b200(args):
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
             'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': C, 'num_heads': cfg['num_heads'],
                        'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1, 'launch': 'one CUDA graph replay per step',
-                       'l2_slab_bytes': model.l2_slab_bytes,
+                       'l2_slab_bytes': model.l2_slab_bytes, 'first_block_scores_fused_into_embedding': bool(model.fuse_scores),
                        'l2': f'inputs larger than L2: E is {n * n * C * 2 / 1e6:.0f} MB per cloud, '
                              f'{n_pairs} distinct pairs rotated',
                        'sharding': f'by pair over {world} GPU(s); one all_gather of outputs'},

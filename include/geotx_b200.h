@@ -72,6 +72,19 @@ int geotx_gse_embed(const void* geometry, int B, int n, int k, int row_begin, in
                     const float* div_term, const void* packed_weights, int C, float sigma_d, float factor_a,
                     int reduce_mean, int out_dtype, void* out, void* stream);
 
+/* geotx_gse_embed that ALSO emits the additive attention scores of the first 'self' block from the accumulator,
+ * before E is rounded for storage (rpe_transformer.py:54-56 with proj_p folded, see geotx_rpe_scores):
+ *   scores_p[b,h,i,j] = sum_c qt[b,h,i,c] * E[b,i,j,c]      for the slab's rows i, all j
+ * This removes one of the block-wise HBM reads of E (the first block's folded query depends only on the input
+ * features, not on E, so it is available before E exists).  qt is addressed exactly as in geotx_rpe_scores
+ * (element strides over batch, head, row; 16-byte aligned, strides multiples of 4); H <= 4; scores_p f32 [B,H,n,n].
+ * Fused when n is a multiple of 128 and k <= 3 (a tile of 128 pairs then shares its query row, whose folded query is
+ * staged in shared memory); otherwise the call runs geotx_gse_embed followed by geotx_rpe_scores. */
+int geotx_gse_embed_scores(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                           const float* div_term, const void* packed_weights, int C, float sigma_d, float factor_a,
+                           int reduce_mean, int out_dtype, void* out, const float* qt, int64_t qt_stride_b,
+                           int64_t qt_stride_h, int64_t qt_stride_n, int H, float* scores_p, void* stream);
+
 /* Debug aid (synchronises the device): the tcgen05 kernel's mbarrier waits are bounded; a wait that times out
  * records {0x80000000 | role<<24 | ring position, barrier smem address, parity, block} and the launch finishes with
  * undefined output instead of hanging the GPU.  Copies the record to host_out4 (all zero = healthy) and clears it. */

@@ -24,6 +24,7 @@ SIGNATURES = {
     'geotx_gse_packed_weight_bytes': (_i64, [_i]),
     'geotx_gse_pack_weights': (_i, [_p, _p, _p, _p, _i, _p, _p]),
     'geotx_gse_embed': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
+    'geotx_gse_embed_scores': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _i, _f, _f, _i, _i, _p, _p, _i64, _i64, _i64, _i, _p, _p]),
     'geotx_watchdog_status': (_i, [_p]),
     'geotx_gse_embed_fp32': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
     'geotx_rpe_scores': (_i, [_p, _i64, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),

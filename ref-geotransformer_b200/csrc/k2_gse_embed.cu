@@ -17,7 +17,7 @@
 //
 // Warp roles (896 threads per CTA): warps 0-15 producers, 16-23 epilogue (TMEM lane quarter = warp % 4, column half =
 // (warp-16)/4), 24 MMA issuer (leader CTA only), 25 weight loader (one bulk copy at start), 26 TMEM allocator, 27 idle.
-// Register budget (setmaxnreg, 64512 in the CTA's pool): producers 56, epilogue 104, the rest 40.
+// Register budget (setmaxnreg, 64512 in the CTA's pool): producers 56, epilogue 120, the rest 40.
 // Cross-CTA signalling: producers / epilogue warps of the peer CTA arrive remotely on the leader's mbarriers
 // (mapa + mbarrier.arrive.release.cluster); tcgen05.commit multicasts "stage free" / "accumulator ready" to both.
 #include <cuda_fp16.h>
@@ -61,7 +61,8 @@ struct K2Cfg {
     static constexpr int COLS_PER_THREAD = C / 2;
     static constexpr int NBAR = 2 * NSTAGE + 5;
     static constexpr int SMEM_BYTES = 2 * W_HALF_BYTES + NSTAGE * A_STAGE_BYTES + C * 4 /*bias*/ +
-                                      (C / 2) * 4 /*div_term*/ + 2 * TILE_M * 8 * 4 /*pair arguments*/ + NBAR * 8 + 16 +
+                                      (C / 2) * 4 /*div_term*/ + 2 * TILE_M * 8 * 4 /*pair arguments*/ +
+                                      TILE_M * 4 * 4 /*score partials*/ + NBAR * 8 + 16 +
                                       1024 /*alignment slack*/;
 };
 
@@ -102,13 +103,18 @@ struct K2Params {
     int num_tile_pairs;     // ceil(ceil(pairs_total / 128) / 2)
     float sigma_d, factor_a;
     int reduce_mean, out_dtype;
+    // optional fused first-block scores (geotx_gse_embed_scores): scores[b,h,i,j] = qt[b,h,i,:] . E[b,i,j,:]
+    const float* qt;
+    long long qt_sb, qt_sh, qt_sn;  // element strides of qt over (batch, head, query row)
+    float* scores;                  // [B,H,n,n] fp32
+    int H;
 };
 
 // watchdog tags: role << 24 | ring position
 constexpr uint32_t WD_PRODUCER = 1u << 24, WD_EPILOGUE = 2u << 24, WD_MMA_ACC = 3u << 24, WD_MMA_FULL = 4u << 24,
                    WD_WEIGHTS = 6u << 24;
 
-template <int C, bool MEAN>
+template <int C, bool MEAN, bool SCORES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(K2_THREADS, 1)
 gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     using Cfg = K2Cfg<C>;
@@ -121,8 +127,11 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     uint8_t* stages = smem + 2 * Cfg::W_HALF_BYTES;        // NSTAGE x 16 KB
     float* s_bias = (float*)(stages + Cfg::NSTAGE * A_STAGE_BYTES);
     float* s_div = s_bias + C;
-    float* s_args = s_div + C / 2;                         // [2][128 rows][8] pair arguments
-    uint64_t* bars = (uint64_t*)(s_args + 2 * TILE_M * 8);
+    float* s_args = s_div + C / 2;                         // [2][slots][128 rows] pair arguments (8 KB reserved: k <= 7)
+    float* s_qt = s_args + TILE_M * 8;                     // [4 heads][C] folded query row of the tile (fused scores;
+                                                           //  upper half of the same 8 KB: needs slots <= 4)
+    float* s_xch = s_args + 2 * TILE_M * 8;                // [128 rows][4 heads] score partials of the upper column half
+    uint64_t* bars = (uint64_t*)(s_xch + TILE_M * 4);
     uint32_t* s_tmem = (uint32_t*)(bars + Cfg::NBAR);
 
     const uint32_t bar_full = smem_u32(bars);                       // [NSTAGE]  leader: 16 warp arrivals
@@ -199,7 +208,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         int xbuf = 0;
         const float* x_row = s_args + row;  // + slot * TILE_M: arguments of the tile being generated
         auto load_x = [&](int tp) {
-            float* xs = s_args + xbuf * (TILE_M * 8);
+            float* xs = s_args + xbuf * (TILE_M * slots);
             const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
             if (p < prm.pairs_total) {
                 const long long b = p / per_b;
@@ -279,7 +288,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================
         // The running reduction over the k angle slots is kept as packed f16x2 (11-bit mantissa: 4x finer than the bf16
         // the result is stored in), which halves its register footprint -- the registers go to the producers.
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 120;");
         constexpr int NCOL = Cfg::COLS_PER_THREAD;
         const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 belong to this warp
         const int colhalf = (warp - NUM_PRODUCER_WARPS) >> 2;
@@ -291,6 +300,26 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
         uint32_t gc = 0;  // running accumulation-group counter (TMEM buffer ring position)
         for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
             const long long p = ((long long)tp * 2 + rank) * TILE_M + row;
+            // fused scores (host guarantees n % 128 == 0 and slots <= 4): the 128 pairs of a tile share the query row
+            // (b, i); its folded query [H][C] is staged in shared memory by the 8 epilogue warps at tile start.
+            float sc[4] = {0.f, 0.f, 0.f, 0.f};
+            long long s_off = 0;
+            if (SCORES) {
+                const long long p0 = ((long long)tp * 2 + rank) * TILE_M;
+                if (p0 < prm.pairs_total) {
+                    const long long per_b = (long long)prm.row_count * prm.n;
+                    const long long b = p0 / per_b;
+                    const long long rem = p0 - b * per_b;
+                    const int i = prm.row_begin + (int)(rem / prm.n);
+                    const int j = (int)(rem % prm.n) + row;
+                    s_off = ((b * prm.H) * prm.n + i) * (long long)prm.n + j;
+                    const int te = (warp - NUM_PRODUCER_WARPS) * 32 + lane;  // 0..255
+                    const int h = te / (C / 4), c4 = te - h * (C / 4);
+                    if (h < prm.H)
+                        *(float4*)(s_qt + h * C + 4 * c4) =
+                            __ldg((const float4*)(prm.qt + b * prm.qt_sb + h * prm.qt_sh + (long long)i * prm.qt_sn) + c4);
+                }
+            }
             for (int g = 0; g < groups; ++g, ++gc) {
                 const uint32_t buf = gc & 1, phase = (gc >> 1) & 1;
                 ptx::mbar_wait_backoff(bar_acc_full + 8 * buf, phase, WD_EPILOGUE | (gc & 0xFFFFFF));
@@ -321,6 +350,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 } else {
                     // distance group: E = (W_d s_d) + reduce_k(W_a s_a) + (b_d + b_a), straight to HBM in 32-byte pieces
                     const float4* bias4 = (const float4*)(s_bias + colhalf * NCOL);
+                    if (SCORES) asm volatile("bar.sync 6, 256;" ::: "memory");  // the tile's folded query is staged
 #ifdef K2_DBG_NO_EPI_STORE
                     const bool do_store = p < prm.pairs_total && __low2float(run[0]) == 123.456f;
 #else
@@ -347,6 +377,23 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                             e[c] += r0.x + bb.x; e[c + 1] += r0.y + bb.y;
                             e[c + 2] += r1.x + bb.z; e[c + 3] += r1.y + bb.w;
                         }
+                        if (SCORES) {
+                            // broadcast reads (every lane the same address): one wavefront each
+#pragma unroll
+                            for (int h = 0; h < 4; ++h) {
+                                if (h < prm.H) {
+                                    const float4* q4 = (const float4*)(s_qt + h * C + colhalf * NCOL + c0);
+#pragma unroll
+                                    for (int u = 0; u < 4; ++u) {
+                                        const float4 qv = q4[u];
+                                        sc[h] = fmaf(qv.x, e[4 * u], sc[h]);
+                                        sc[h] = fmaf(qv.y, e[4 * u + 1], sc[h]);
+                                        sc[h] = fmaf(qv.z, e[4 * u + 2], sc[h]);
+                                        sc[h] = fmaf(qv.w, e[4 * u + 3], sc[h]);
+                                    }
+                                }
+                            }
+                        }
                         if (do_store) {
                             if (prm.out_dtype == GEOTX_F16) {  // default storage format of E: 11-bit significand
                                 __half2 o[8];
@@ -369,6 +416,22 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 ptx::tc_fence_before_sync();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive_cluster(acc_empty_leader + 8 * buf);
+            }
+            if (SCORES) {
+                // the two warps of a lane quarter hold the two column halves of the same 32 rows: add them through
+                // shared memory (named barrier 2 + quarter over those 64 threads) and write scores[b,h,i,j]
+                float4* x4 = (float4*)(s_xch + row * 4);
+                if (colhalf == 1) *x4 = make_float4(sc[0], sc[1], sc[2], sc[3]);
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + quarter) : "memory");
+                if (colhalf == 0 && p < prm.pairs_total) {
+                    const float4 o = *x4;
+                    const float tot[4] = {sc[0] + o.x, sc[1] + o.y, sc[2] + o.z, sc[3] + o.w};
+                    const long long head_stride = (long long)prm.n * prm.n;
+#pragma unroll
+                    for (int h = 0; h < 4; ++h)
+                        if (h < prm.H) prm.scores[s_off + h * head_stride] = tot[h];
+                }
+                asm volatile("bar.sync 6, 256;" ::: "memory");  // partials and the staged query consumed: reusable
             }
         }
     } else {
@@ -463,38 +526,43 @@ template <int C>
 static int launch_k2(const K2Params& prm, cudaStream_t st) {
     using Cfg = K2Cfg<C>;
     static int num_sms = 0;
+    const void* kernels[4] = {(const void*)gse_embed_tc_kernel<C, false, false>, (const void*)gse_embed_tc_kernel<C, true, false>,
+                              (const void*)gse_embed_tc_kernel<C, false, true>, (const void*)gse_embed_tc_kernel<C, true, true>};
     if (num_sms == 0) {
         int dev = 0;
         int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
         if (rc) return rc;
         rc = check_cuda(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
         if (rc) return rc;
-        rc = check_cuda(cudaFuncSetAttribute(gse_embed_tc_kernel<C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             Cfg::SMEM_BYTES), "cudaFuncSetAttribute(gse_embed_tc_kernel)");
-        if (!rc) rc = check_cuda(cudaFuncSetAttribute(gse_embed_tc_kernel<C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                      Cfg::SMEM_BYTES), "cudaFuncSetAttribute(gse_embed_tc_kernel)");
+        for (int i = 0; i < 4 && !rc; ++i)
+            rc = check_cuda(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES),
+                            "cudaFuncSetAttribute(gse_embed_tc_kernel)");
         if (rc) { num_sms = 0; return rc; }
     }
     // persistent: one CTA pair per SM pair (cluster of 2, same TPC)
     int clusters = num_sms / 2;
     if (prm.num_tile_pairs < clusters) clusters = prm.num_tile_pairs;
-    if (prm.reduce_mean) gse_embed_tc_kernel<C, true><<<2 * clusters, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
-    else gse_embed_tc_kernel<C, false><<<2 * clusters, K2_THREADS, Cfg::SMEM_BYTES, st>>>(prm);
+    const int which = (prm.reduce_mean ? 1 : 0) + (prm.scores ? 2 : 0);
+    K2Params p = prm;
+    void* args[1] = {&p};
+    int rc = check_cuda(cudaLaunchKernel(kernels[which], dim3(2 * clusters), dim3(K2_THREADS), args, Cfg::SMEM_BYTES, st),
+                        "cudaLaunchKernel(gse_embed_tc_kernel)");
+    if (rc) return rc;
     return launch_status("geotx_gse_embed");
 }
 
-extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int row_begin, int row_count,
-                               const float* div_term, const void* packed_weights, int C, float sigma_d,
-                               float factor_a, int reduce_mean, int out_dtype, void* out, void* stream) {
-    GEOTX_REQUIRE(geometry && div_term && packed_weights && out, "geotx_gse_embed: null pointer");
-    GEOTX_REQUIRE(B > 0 && n > 0 && k >= 1 && k <= GEOTX_MAX_ANGLE_K, "geotx_gse_embed: bad sizes");
-    GEOTX_REQUIRE(C == 128 || C == 256, "geotx_gse_embed: hidden_dim %d not supported by the tcgen05 path (128 or "
-                  "256); use geotx_gse_embed_fp32", C);
-    GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed: bad row slab");
-    GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16 || out_dtype == GEOTX_F16,
-                  "geotx_gse_embed: bad out_dtype");
+static int gse_embed_common(const char* who, const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                            const float* div_term, const void* packed_weights, int C, float sigma_d, float factor_a,
+                            int reduce_mean, int out_dtype, void* out, const float* qt, int64_t qt_stride_b,
+                            int64_t qt_stride_h, int64_t qt_stride_n, int H, float* scores_p, void* stream) {
+    GEOTX_REQUIRE(geometry && div_term && packed_weights && out, "%s: null pointer", who);
+    GEOTX_REQUIRE(B > 0 && n > 0 && k >= 1 && k <= GEOTX_MAX_ANGLE_K, "%s: bad sizes", who);
+    GEOTX_REQUIRE(C == 128 || C == 256, "%s: hidden_dim %d not supported by the tcgen05 path (128 or "
+                  "256); use geotx_gse_embed_fp32", who, C);
+    GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "%s: bad row slab", who);
+    GEOTX_REQUIRE(out_dtype == GEOTX_F32 || out_dtype == GEOTX_BF16 || out_dtype == GEOTX_F16, "%s: bad out_dtype", who);
     GEOTX_REQUIRE(((uintptr_t)out & 31) == 0 && ((uintptr_t)packed_weights & 15) == 0,
-                  "geotx_gse_embed: out must be 32-byte and packed_weights 16-byte aligned");
+                  "%s: out must be 32-byte and packed_weights 16-byte aligned", who);
     K2Params prm;
     prm.pts4 = (const float4*)geometry;
     prm.refv = prm.pts4 + (size_t)B * n;
@@ -504,11 +572,45 @@ extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int ro
     prm.pairs_total = (long long)B * row_count * n;
     prm.n = n; prm.k = k; prm.row_begin = row_begin; prm.row_count = row_count;
     long long tiles = (prm.pairs_total + TILE_M - 1) / TILE_M;
-    GEOTX_REQUIRE(tiles < 2147483647LL, "geotx_gse_embed: too many pairs");
+    GEOTX_REQUIRE(tiles < 2147483647LL, "%s: too many pairs", who);
     prm.num_tile_pairs = (int)((tiles + 1) / 2);
     prm.sigma_d = sigma_d; prm.factor_a = factor_a;
     prm.reduce_mean = reduce_mean ? 1 : 0;
     prm.out_dtype = out_dtype;
+    prm.qt = qt; prm.qt_sb = qt_stride_b; prm.qt_sh = qt_stride_h; prm.qt_sn = qt_stride_n;
+    prm.scores = scores_p; prm.H = H;
     if (C == 256) return launch_k2<256>(prm, (cudaStream_t)stream);
     return launch_k2<128>(prm, (cudaStream_t)stream);
+}
+
+extern "C" int geotx_gse_embed(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                               const float* div_term, const void* packed_weights, int C, float sigma_d,
+                               float factor_a, int reduce_mean, int out_dtype, void* out, void* stream) {
+    return gse_embed_common("geotx_gse_embed", geometry, B, n, k, row_begin, row_count, div_term, packed_weights, C,
+                            sigma_d, factor_a, reduce_mean, out_dtype, out, nullptr, 0, 0, 0, 0, nullptr, stream);
+}
+
+extern "C" int geotx_gse_embed_scores(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                                      const float* div_term, const void* packed_weights, int C, float sigma_d,
+                                      float factor_a, int reduce_mean, int out_dtype, void* out, const float* qt,
+                                      int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n, int H,
+                                      float* scores_p, void* stream) {
+    GEOTX_REQUIRE(qt && scores_p, "geotx_gse_embed_scores: null pointer");
+    GEOTX_REQUIRE(H >= 1 && H <= 4, "geotx_gse_embed_scores: %d heads not supported by the fused scores (1..4); use "
+                  "geotx_gse_embed + geotx_rpe_scores", H);
+    GEOTX_REQUIRE(((uintptr_t)qt & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0 && qt_stride_n % 4 == 0,
+                  "geotx_gse_embed_scores: qt must be 16-byte aligned with strides that are multiples of 4 floats");
+    if (n % TILE_M != 0 || k > 3) {
+        // tiles would straddle query rows (or the argument table needs the staging space): same result from the two
+        // separate kernels, E read back once
+        int rc = gse_embed_common("geotx_gse_embed_scores", geometry, B, n, k, row_begin, row_count, div_term,
+                                  packed_weights, C, sigma_d, factor_a, reduce_mean, out_dtype, out, nullptr, 0, 0, 0, 0,
+                                  nullptr, stream);
+        if (rc) return rc;
+        return geotx_rpe_scores(qt, qt_stride_b, qt_stride_h, qt_stride_n, out, out_dtype, B, H, n, n, C, row_begin,
+                                row_count, scores_p, stream);
+    }
+    return gse_embed_common("geotx_gse_embed_scores", geometry, B, n, k, row_begin, row_count, div_term, packed_weights,
+                            C, sigma_d, factor_a, reduce_mean, out_dtype, out, qt, qt_stride_b, qt_stride_h, qt_stride_n,
+                            H, scores_p, stream);
 }

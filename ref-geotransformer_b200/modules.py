@@ -158,11 +158,15 @@ class GeometricStructureEmbedding(nn.Module):
         geom = self.geometry(points)
         return ops.gse_indices(geom, self.sigma_d, self.factor_a)
 
-    def embed(self, geom, out_dtype, row_begin=0, row_count=None, out=None):
+    def embed(self, geom, out_dtype, row_begin=0, row_count=None, out=None, qt=None):
+        """E of the rows [row_begin, row_begin + row_count).  With `qt` (tensor-core path, <= 4 heads) returns
+        (E, scores_p): the first 'self' block's additive scores come out of the same kernel."""
         mean = self.reduction_a == 'mean'
         if self._use_tensor_cores():
             return ops.gse_embed(geom, self.embedding.div_term, self._packed_weights(), self.hidden_dim, self.sigma_d,
-                                 self.factor_a, mean, out_dtype, row_begin, row_count, out)
+                                 self.factor_a, mean, out_dtype, row_begin, row_count, out, qt=qt)
+        if qt is not None:
+            raise RuntimeError('fused first-block scores need the tensor-core embedding kernel')
         return ops.gse_embed_fp32(geom, self.embedding.div_term, self.proj_d.weight.detach(),
                                   self.proj_d.bias.detach(), self.proj_a.weight.detach(), self.proj_a.bias.detach(),
                                   self.sigma_d, self.factor_a, mean, out_dtype, row_begin, row_count, out)
@@ -416,8 +420,9 @@ class StreamedEmbedding:
     three full HBM reads of E (one per 'self' block); the slab still drains to HBM for the later blocks.
     `slab_bytes` = 0 produces E in one launch (the scores kernel then reads it from HBM as in the later blocks)."""
 
-    def __init__(self, embedding, geom, dtype, slab_bytes):
+    def __init__(self, embedding, geom, dtype, slab_bytes, fuse_scores=False):
         self.embedding, self.geom, self.dtype, self.slab_bytes = embedding, geom, dtype, slab_bytes
+        self.fuse_scores = fuse_scores
         self.E = None
 
     def materialise(self):
@@ -429,6 +434,10 @@ class StreamedEmbedding:
         """qt (1,H,n,C) -> scores_p (1,H,n,n) of the first 'self' block; E is complete afterwards."""
         if self.E is not None:
             return ops.rpe_scores(qt, self.E)
+        if self.fuse_scores and self.slab_bytes <= 0 and qt.shape[1] <= 4 and self.embedding._use_tensor_cores():
+            # the embedding kernel emits these scores from its accumulators: one HBM read of E less
+            self.E, scores_p = self.embedding.embed(self.geom, self.dtype, qt=qt)
+            return scores_p
         n, C = self.geom.n, self.embedding.hidden_dim
         row_bytes = n * C * (4 if self.dtype == torch.float32 else 2)
         rows = n if self.slab_bytes <= 0 else max(1, min(n, self.slab_bytes // row_bytes))
@@ -595,6 +604,10 @@ class GeometricTransformer(nn.Module):
         self.out_proj = nn.Linear(hidden_dim, output_dim)
         # slab of E kept L2-resident between the embedding kernel and the first block's scores kernel (0 = off)
         self.l2_slab_bytes = int(os.environ.get('GEOTX_L2_SLAB_BYTES', DEFAULT_L2_SLAB_BYTES))
+        # first 'self' block's scores from the embedding kernel's accumulators: one HBM pass over E less, but the
+        # extra epilogue work costs the embedding kernel more than the pass saves (measured: 0.50 -> 0.64 ms per
+        # cloud at n = 1024 against 0.094 ms saved), so it is opt-in
+        self.fuse_scores = os.environ.get('GEOTX_FUSE_SCORES', '0') != '0'
 
     def _side_stream(self, device):
         streams = self.__dict__.setdefault('_side_streams', {})
@@ -635,8 +648,8 @@ class GeometricTransformer(nn.Module):
             cur.wait_stream(side)
             for t in (src_geom.buf, src_geom.knn) + (() if one_buffer else (src_feats,)):
                 t.record_stream(cur)  # allocated on the side stream, consumed (and later freed) on this one
-            ref_embeddings = StreamedEmbedding(self.embedding, ref_geom, e_dtype, self.l2_slab_bytes)
-            src_embeddings = StreamedEmbedding(self.embedding, src_geom, e_dtype, self.l2_slab_bytes)
+            ref_embeddings = StreamedEmbedding(self.embedding, ref_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores)
+            src_embeddings = StreamedEmbedding(self.embedding, src_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores)
             ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
                                                     masks0=ref_masks, masks1=src_masks)
             if ref_feats.shape[0] == 1 and ref_feats.data_ptr() + ref_feats.numel() * 4 == src_feats.data_ptr():

@@ -87,18 +87,40 @@ def _slab(geom, row_begin, row_count):
 
 
 def gse_embed(geom, div_term, packed, C, sigma_d, factor_a, reduce_mean=False, out_dtype=torch.float16,
-              row_begin=0, row_count=None, out=None):
-    """tcgen05 path.  -> E (B,row_count,n,C).  geotransformer.py:57-72."""
+              row_begin=0, row_count=None, out=None, qt=None, scores_out=None):
+    """tcgen05 path.  -> E (B,row_count,n,C).  geotransformer.py:57-72.
+    With `qt` (folded query of the first 'self' block, logical (B,H,n,C), see rpe_scores) the kernel also writes
+    scores_p (B,H,n,n) fp32 for the slab's rows into `scores_out` (allocated if None) and returns (E, scores_p)."""
     _check(div_term, 'div_term', torch.float32, 1)
     row_begin, row_count = _slab(geom, row_begin, row_count)
     if out is None:
         out = torch.empty(geom.B, row_count, geom.n, C, dtype=out_dtype, device=geom.buf.device)
     else:
         _check(out, 'out', out_dtype)
-    _abi.call('geotx_gse_embed', _p(geom.buf), geom.B, geom.n, geom.k, row_begin, row_count, _p(div_term),
-              _p(packed), C, float(sigma_d), float(factor_a), int(bool(reduce_mean)), _DT[out_dtype], _p(out),
+    head = (_p(geom.buf), geom.B, geom.n, geom.k, row_begin, row_count, _p(div_term), _p(packed), C, float(sigma_d),
+            float(factor_a), int(bool(reduce_mean)), _DT[out_dtype], _p(out))
+    if qt is None:
+        _abi.call('geotx_gse_embed', *head, _stream())
+        return out
+    qt, H = _folded_query(qt, geom.B, geom.n, C)
+    if scores_out is None:
+        scores_out = torch.empty(geom.B, H, geom.n, geom.n, dtype=torch.float32, device=out.device)
+    elif tuple(_check(scores_out, 'scores_out', torch.float32, 4).shape) != (geom.B, H, geom.n, geom.n):
+        raise RuntimeError(f'scores_out must be {(geom.B, H, geom.n, geom.n)}, got {tuple(scores_out.shape)}')
+    _abi.call('geotx_gse_embed_scores', *head, _p(qt), qt.stride(0), qt.stride(1), qt.stride(2), H, _p(scores_out),
               _stream())
-    return out
+    return out, scores_out
+
+
+def _folded_query(qt, B, n, C):
+    """(B,H,n,C) fp32 CUDA view with unit channel stride and 16-byte aligned rows (made contiguous otherwise)."""
+    if not (isinstance(qt, torch.Tensor) and qt.is_cuda and qt.dtype == torch.float32 and qt.dim() == 4):
+        raise RuntimeError('qt must be a 4-d fp32 CUDA tensor')
+    if qt.shape[0] != B or qt.shape[2] != n or qt.shape[3] != C:
+        raise RuntimeError(f'qt must be (B={B}, H, n={n}, C={C}), got {tuple(qt.shape)}')
+    if qt.stride(3) != 1 or any(st % 4 for st in qt.stride()[:3]) or qt.data_ptr() % 16:
+        qt = qt.contiguous()
+    return qt, qt.shape[1]
 
 
 def gse_embed_fp32(geom, div_term, w_d, b_d, w_a, b_a, sigma_d, factor_a, reduce_mean=False,

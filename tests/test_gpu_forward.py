@@ -89,6 +89,7 @@ def test_l2_slab_interleave_is_bit_identical(pkg, oracle, slab_rows):
     rp, sp, rf, sf = pkg.synth.make_pair('3dmatch', n, m, seed=5)
     model = build_model(pkg, cfg, sd)
     args = (rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV))
+    model.fuse_scores = False  # compare the two schedules that run the same two kernels
     with torch.no_grad():
         model.l2_slab_bytes = 0
         a0, a1 = [t.clone() for t in model(*args)]
@@ -117,3 +118,24 @@ def test_pipelined_host_to_host_serving_matches_direct_forward(pkg, oracle):
     again = [tuple(o.clone() for o in out) for out in pipe.map(host[::-1])]
     for w, g in zip(want[::-1], again):
         assert torch.equal(w[0], g[0]) and torch.equal(w[1], g[1])
+
+
+def test_first_block_scores_fused_into_the_embedding_kernel(pkg, oracle):
+    """geotx_gse_embed_scores: the first 'self' block's scores_p from the embedding kernel's accumulators must agree with
+    the separate scores kernel (which reads the stored, 16-bit-rounded E) and both with the oracle."""
+    for shape, n, m in (('3dmatch', 200, 131), ('kitti', 256, 256)):
+        cfg = dict(pkg.synth.CONFIGS[shape])
+        sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+        rp, sp, rf, sf = pkg.synth.make_pair(shape, n, m, seed=7)
+        model = build_model(pkg, cfg, sd)
+        args = (rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV))
+        exp0, exp1 = oracle.geometric_transformer(sd, cfg, rp, sp, rf, sf)[:2]
+        with torch.no_grad():
+            model.fuse_scores = True
+            f0, f1 = [t.clone() for t in model(*args)]
+            model.fuse_scores = False
+            u0, u1 = model(*args)
+        assert rel(f0, u0) <= 2e-3 and rel(f1, u1) <= 2e-3
+        assert rel(f0, exp0) <= TOL_BF16 and rel(f1, exp1) <= TOL_BF16
+        print(f'{shape}: fused vs separate {rel(f0, u0):.2e}, fused vs oracle {rel(f0, exp0):.2e}')
+    assert pkg._abi.watchdog() is None

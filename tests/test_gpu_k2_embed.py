@@ -128,3 +128,32 @@ def test_storage_format_falls_back_to_bf16_when_half_could_overflow(pkg, oracle)
         e = m.embed(m.geometry(pts.to(DEV)), m.storage_dtype())
     assert torch.isfinite(e).all()
     assert rel(e, exp) <= 1e-2
+
+
+@pytest.mark.parametrize('C,H,n,reduction', [(256, 4, 173, 'max'), (128, 4, 256, 'max'), (256, 2, 128, 'mean'), (256, 4, 384, 'max')])
+def test_fused_first_block_scores(pkg, oracle, C, H, n, reduction):
+    """geotx_gse_embed_scores: scores_p[b,h,i,j] = qt[b,h,i,:] . E[b,i,j,:] out of the embedding kernel (ragged n so
+    that tiles straddle query rows, B = 2, row slab), against the fp32 output of the same launch."""
+    cfg = dict(hidden_dim=C, sigma_d=0.3, sigma_a=10, angle_k=3, reduction_a=reduction)
+    sd = oracle.init_state_dict(8, 8, C, [], seed=5)
+    g = torch.Generator().manual_seed(n)
+    pts = torch.rand(2, n, 3, generator=g) * 2.5
+    qt = torch.randn(2, H, n, C, generator=g).to(DEV)
+    m = _gse(pkg, cfg, sd, 'bf16')
+    with torch.no_grad():
+        geom = m.geometry(pts.to(DEV))
+        e32, sc = m.embed(geom, torch.float32, qt=qt)
+        plain = m.embed(geom, torch.float32)
+        assert torch.equal(e32, plain), 'E must not depend on whether the scores are fused'
+        want = torch.einsum('bhic,bijc->bhij', qt.double(), e32.double()).float()
+        assert rel(sc, want) <= 1e-5
+        # slab of rows [30, 100): only those rows of scores are written
+        part = torch.full_like(sc, -7.0)
+        pkg.ops.gse_embed(geom, m.embedding.div_term, m._packed_weights(), C, m.sigma_d, m.factor_a,
+                          reduction == 'mean', torch.float16, 30, 70, qt=qt, scores_out=part)
+        if n % 128 == 0:  # fused in the kernel: independent of the storage format of E
+            assert torch.equal(part[:, :, 30:100], sc[:, :, 30:100])
+        else:             # two-kernel fallback: the scores kernel reads the f16-rounded E
+            assert rel(part[:, :, 30:100], want[:, :, 30:100]) <= 2e-3
+        assert float((part[:, :, :30] + 7.0).abs().max()) == 0.0 and float((part[:, :, 100:] + 7.0).abs().max()) == 0.0
+    assert pkg._abi.watchdog() is None
