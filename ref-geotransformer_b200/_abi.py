@@ -7,7 +7,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'lib', 'libgeotx_b200.so')
+LIB_PATH = os.environ.get('GEOTX_LIB') or os.path.join(_HERE, 'lib', 'libgeotx_b200.so')  # GEOTX_LIB: timing experiments
 
 _p = ctypes.c_void_p
 _i = ctypes.c_int

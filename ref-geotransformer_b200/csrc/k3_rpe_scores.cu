@@ -62,7 +62,7 @@ __device__ __forceinline__ uint4 ldg_stream16(const void* p) {
 // Streaming structure: the kernel is HBM-bound, so what matters is bytes in flight, not registers.  Every warp owns a
 // private ring of K3A_STAGES shared-memory stages and is its own producer: lane 0 asks the TMA unit (cp.async.bulk) for
 // the next 16 key rows of E (16 x 2C bytes, contiguous in HBM) while the warp contracts the previous ones, completion
-// signalled on a per-stage mbarrier.  8 warps x 3 stages x 8 KB keep ~190 KB per SM in flight (Little's law needs ~40).
+// signalled on a per-stage mbarrier.  8 warps x 16 KB keep 128 KB per SM in flight (Little's law needs ~40).
 // One bulk copy per chunk: per-row copies into a padded (conflict-free) layout were TMA-issue-bound (72 % of HBM peak);
 // the unpadded layout costs a 2-way bank conflict on the fragment reads, which need <1/4 of the smem bandwidth anyway.
 // Work is split into chunks of 16 keys of one query row; each warp takes a contiguous range of chunks (persistent grid,
@@ -71,7 +71,15 @@ __device__ __forceinline__ uint4 ldg_stream16(const void* p) {
 // Channel permutation: lane (g = lane/4, t = lane%4) owns channels 32 s + 8 t + [0,8) of E row j0+g for every s;
 // the two k16 steps of chunk s use the 8 channels as k-slots {2t,2t+1 | 2t+8,2t+9}.  Any fixed permutation of
 // the contraction index is legal as long as A (the folded query) uses the same one, which it does.
-constexpr int K3A_STAGES = 3;
+// ring depth per warp, measured at n = 2048 (tools/k3_bench.py): C = 256 (8 KB stages): 2 deep 6.3 TB/s, 3 deep
+// 5.8 TB/s; C = 128 (4 KB stages): 2 / 3 / 4 / 6 deep 5.75 / 5.88 / 6.11 / 5.85 TB/s -- 128 KB in flight per SM is
+// the sweet spot (more outstanding bulk copies lose DRAM locality)
+#ifndef K3A_ST256
+#define K3A_ST256 2
+#endif
+#ifndef K3A_ST128
+#define K3A_ST128 4
+#endif
 constexpr int K3A_KEYS = 16;  // keys per chunk / stage
 
 template <int C>
@@ -79,7 +87,8 @@ struct K3ACfg {
     static constexpr int ROW_BYTES = 2 * C;
     static constexpr int PITCH = ROW_BYTES;  // one bulk copy per chunk; the 2-way bank conflict of the reads is free here
     static constexpr int STAGE_BYTES = K3A_KEYS * PITCH;
-    static constexpr int SMEM_BYTES = K3A_WARPS * K3A_STAGES * STAGE_BYTES + K3A_WARPS * K3A_STAGES * 8 + 128;
+    static constexpr int STAGES = (C == 256) ? K3A_ST256 : K3A_ST128;
+    static constexpr int SMEM_BYTES = K3A_WARPS * STAGES * STAGE_BYTES + K3A_WARPS * STAGES * 8 + 128;
 };
 
 template <int C, bool F16>
@@ -89,6 +98,7 @@ rpe_scores_tc_kernel(const float* __restrict__ qt, long long qsb, long long qsh,
                        int H, int n, int m, int row_begin, int row_count, long long chunks_total, int chunks_per_row,
                        long long chunks_per_warp, float* __restrict__ scores) {
     using Cfg = K3ACfg<C>;
+    constexpr int K3A_STAGES = Cfg::STAGES;
     constexpr int S = C / 32;
     extern __shared__ __align__(128) uint8_t k3a_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

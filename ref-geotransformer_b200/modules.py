@@ -411,6 +411,17 @@ def _check_block_type(block):
         raise ValueError('Unsupported block type "{}".'.format(block))
 
 
+_SIDE_STREAMS = {}
+
+
+def _side_stream(device):
+    """One auxiliary stream per device for the small launches that are overlapped with a bandwidth-bound kernel."""
+    device = torch.device(device)
+    if device not in _SIDE_STREAMS:
+        _SIDE_STREAMS[device] = torch.cuda.Stream(device)
+    return _SIDE_STREAMS[device]
+
+
 class StreamedEmbedding:
     """E of one cloud, produced slab by slab together with the FIRST 'self' block's scores_p.
 
@@ -470,6 +481,7 @@ class RPEConditionalTransformer(nn.Module):
         self.layers = nn.ModuleList(layers)
         self.return_attention_scores = return_attention_scores
         self.parallel = parallel
+        self.overlap_attention = os.environ.get('GEOTX_OVERLAP_ATTENTION', '1') != '0'
 
     # ---- fused schedule (same math, fewer and larger launches) ------------------------------------------------
     # Both clouds share every layer's weights, so all token-wise work of a 'self' block (one fused q|k|v|folded-query
@@ -522,6 +534,7 @@ class RPEConditionalTransformer(nn.Module):
                 w, b = att.fused_qkvp()
                 y = F.linear(x, w, b)  # (1, T, 3C + H*C): q | k | v | folded query per head
                 hidden = x.new_empty(1, T, C)
+                cur = side = None
                 for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
                     emb = embs[which]
                     qt = y[:, lo:hi, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
@@ -530,8 +543,20 @@ class RPEConditionalTransformer(nn.Module):
                         embs[which] = emb.E
                     else:
                         scores_p = ops.rpe_scores(qt, emb.contiguous())
-                    ops.attention(y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask,
-                                  out=hidden[:, lo:hi])
+                    att_args = (y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask)
+                    if which == 0 and self.overlap_attention:
+                        # the first cloud's attention core (a short, latency-bound launch) runs on a side stream
+                        # underneath the second cloud's HBM-bound scores kernel
+                        cur = torch.cuda.current_stream(x.device)
+                        side = _side_stream(x.device)
+                        side.wait_stream(cur)
+                        with torch.cuda.stream(side):
+                            ops.attention(*att_args, out=hidden[:, lo:hi])
+                        scores_p.record_stream(side)
+                    else:
+                        ops.attention(*att_args, out=hidden[:, lo:hi])
+                if side is not None:
+                    cur.wait_stream(side)
                 x = self._post_attention(layer, hidden, x)
             else:
                 # One q|k|v projection of ALL tokens serves both steps' queries (each step queries with the OLD tokens
@@ -609,12 +634,6 @@ class GeometricTransformer(nn.Module):
         # cloud at n = 1024 against 0.094 ms saved), so it is opt-in
         self.fuse_scores = os.environ.get('GEOTX_FUSE_SCORES', '0') != '0'
 
-    def _side_stream(self, device):
-        streams = self.__dict__.setdefault('_side_streams', {})
-        if device not in streams:
-            streams[device] = torch.cuda.Stream(device)
-        return streams[device]
-
     def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
         _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
         if not all(isinstance(t, torch.Tensor) and t.is_cuda for t in (ref_points, src_points, ref_feats, src_feats)):
@@ -625,7 +644,7 @@ class GeometricTransformer(nn.Module):
         # The second cloud's k-NN + packing and its in_proj run on a side stream next to the first cloud's: all four
         # are small launches (~25 us of latency-bound work each) that leave most of the GPU idle on their own.
         cur = torch.cuda.current_stream(ref_points.device)
-        side = self._side_stream(ref_points.device)
+        side = _side_stream(ref_points.device)
         one_buffer = ref_feats.dim() == 3 and ref_feats.shape[0] == 1 and src_feats.shape[0] == 1
         with _dense_precision(allow_tf32=tc):
             if one_buffer:  # both clouds' tokens side by side: the transformer's fused schedule wants exactly this

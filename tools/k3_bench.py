@@ -1,4 +1,5 @@
-"""GPU timing of K3a (geotx_rpe_scores) and K3b (geotx_attention) alone, through the C ABI."""
+"""GPU timing of K3a (geotx_rpe_scores) and K3b (geotx_attention) alone, through the C ABI (eager calls: the attention
+numbers include host launch overhead, use tools/k3b_bench.py for those).  usage: k3_bench.py [lib.so]"""
 import os
 import sys
 
@@ -9,6 +10,8 @@ sys.path.insert(0, ROOT)
 import pkgpath  # noqa: E402
 
 pkg = pkgpath.load_package()
+if len(sys.argv) > 1:
+    pkg._abi.LIB_PATH = os.path.abspath(sys.argv[1])
 dev = 'cuda:0'
 
 
