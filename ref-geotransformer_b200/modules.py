@@ -535,6 +535,12 @@ class RPEConditionalTransformer(nn.Module):
                 y = F.linear(x, w, b)  # (1, T, 3C + H*C): q | k | v | folded query per head
                 hidden = x.new_empty(1, T, C)
                 cur = side = None
+                streamed = any(isinstance(e, StreamedEmbedding) for e in embs)
+                if streamed and not any(isinstance(e, StreamedEmbedding) and (e.fuse_scores or e.slab_bytes > 0)
+                                        for e in embs):
+                    # plain schedule: both embedding kernels back to back, each with the whole GPU to itself
+                    embs = [e.materialise() if isinstance(e, StreamedEmbedding) else e for e in embs]
+                    streamed = False
                 for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
                     emb = embs[which]
                     qt = y[:, lo:hi, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
@@ -544,7 +550,7 @@ class RPEConditionalTransformer(nn.Module):
                     else:
                         scores_p = ops.rpe_scores(qt, emb.contiguous())
                     att_args = (y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask)
-                    if which == 0 and self.overlap_attention:
+                    if which == 0 and self.overlap_attention and not streamed:
                         # the first cloud's attention core (a short, latency-bound launch) runs on a side stream
                         # underneath the second cloud's HBM-bound scores kernel
                         cur = torch.cuda.current_stream(x.device)

@@ -23,15 +23,17 @@ for C, n, sd in CASES:
     pts = (torch.rand(1, n, 3) * (3.0 if C == 256 else 100.0)).to(dev)
     with torch.no_grad():
         geom = m.geometry(pts)
-        out = torch.empty(1, n, n, C, dtype=DT, device=dev)
-        for _ in range(3):
-            m.embed(geom, DT, out=out)
+        nbuf = int(os.environ.get('K2_BUFFERS', '1'))  # >1: rotate output buffers (as the two clouds of a pair do)
+        outs = [torch.empty(1, n, n, C, dtype=DT, device=dev) for _ in range(nbuf)]
+        out = outs[0]
+        for i in range(3):
+            m.embed(geom, DT, out=outs[i % nbuf])
         torch.cuda.synchronize()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         reps = 10
         ev[0].record()
-        for _ in range(reps):
-            m.embed(geom, DT, out=out)
+        for i in range(reps):
+            m.embed(geom, DT, out=outs[i % nbuf])
         ev[1].record()
         torch.cuda.synchronize()
     ms = ev[0].elapsed_time(ev[1]) / reps
