@@ -15,3 +15,37 @@ __all__ = [
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
     'AttentionOutput', 'SinusoidalPositionalEmbedding', 'ops', 'synth',
 ]
+
+_REFERENCE_PATCHES = (
+    # (module of the reference, names it exports that this package re-implements)
+    ('geotransformer.modules.geotransformer.geotransformer', ('GeometricTransformer', 'GeometricStructureEmbedding')),
+    ('geotransformer.modules.geotransformer', ('GeometricTransformer', 'GeometricStructureEmbedding')),
+    ('geotransformer.modules.transformer', ('RPEConditionalTransformer', 'RPETransformerLayer', 'TransformerLayer',
+                                            'SinusoidalPositionalEmbedding')),
+)
+_saved = {}
+
+
+def install_into_reference():
+    """Zero-edit drop-in: rebinds the reference's hot-path classes (geotransformer/modules/geotransformer/__init__.py:1,
+    geotransformer/modules/transformer/__init__.py:1-19) to this package's, so that `experiments/*/model.py:9-15,35-45`
+    builds the B200 path without being touched.  Call it AFTER `geotransformer` is importable and BEFORE the
+    experiment's model.py is imported (its `from ... import GeometricTransformer` binds at import time).
+    Returns the list of rebound 'module.name' strings; `uninstall_from_reference()` undoes it."""
+    import importlib
+    done = []
+    here = globals()
+    for modname, names in _REFERENCE_PATCHES:
+        mod = importlib.import_module(modname)
+        for name in names:
+            _saved.setdefault((modname, name), getattr(mod, name))
+            setattr(mod, name, here[name])
+            done.append(f'{modname}.{name}')
+    return done
+
+
+def uninstall_from_reference():
+    import importlib
+    for (modname, name), orig in list(_saved.items()):
+        setattr(importlib.import_module(modname), name, orig)
+        del _saved[(modname, name)]

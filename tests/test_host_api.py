@@ -147,3 +147,27 @@ def test_synthetic_inputs_are_deterministic(pkg):
     assert a[0].shape == (1, 64, 3) and a[1].shape == (1, 50, 3) and a[2].shape == (1, 64, 1024)
     pts = torch.tensor([[0., 0, 0], [1, 0, 0], [-1, 0, 0], [0, 2, 0], [0, 0, 3], [5, 5, 5]])
     assert not pkg.synth.tie_free(pts)  # two neighbours at exactly distance 1
+
+
+@pytest.mark.skipif(not reference_available(), reason='/root/reference not present (GPU box)')
+def test_install_into_reference_rebinds_and_restores(pkg):
+    """Zero-edit drop-in: the reference's own import paths hand out this package's classes after install."""
+    import importlib
+    GT, GSE = load_reference()
+    done = pkg.install_into_reference()
+    try:
+        g = importlib.import_module('geotransformer.modules.geotransformer')
+        t = importlib.import_module('geotransformer.modules.transformer')
+        assert g.GeometricTransformer is pkg.GeometricTransformer
+        assert g.GeometricStructureEmbedding is pkg.GeometricStructureEmbedding
+        assert t.RPEConditionalTransformer is pkg.RPEConditionalTransformer
+        assert 'geotransformer.modules.geotransformer.GeometricTransformer' in done
+        # what experiments/*/model.py:35-45 does, with its own import statement
+        ns = {}
+        exec('from geotransformer.modules.geotransformer import GeometricTransformer', ns)
+        m = ns['GeometricTransformer'](1024, 256, 256, 4, ['self', 'cross'], 0.2, 15, 3, reduction_a='max')
+        assert isinstance(m, pkg.GeometricTransformer)
+    finally:
+        pkg.uninstall_from_reference()
+    g = importlib.import_module('geotransformer.modules.geotransformer.geotransformer')
+    assert g.GeometricTransformer is GT and g.GeometricStructureEmbedding is GSE
