@@ -17,7 +17,7 @@
 //
 // Warp roles (896 threads per CTA): warps 0-15 producers, 16-23 epilogue (TMEM lane quarter = warp % 4, column half =
 // (warp-16)/4), 24 MMA issuer (leader CTA only), 25 weight loader (one bulk copy at start), 26 TMEM allocator, 27 idle.
-// Register budget (setmaxnreg, 64512 in the CTA's pool): producers 56, epilogue 120, the rest 40.
+// Register budget (setmaxnreg, 64512 in the CTA's pool): producers 64, epilogue 104, the rest 40.
 // Cross-CTA signalling: producers / epilogue warps of the peer CTA arrive remotely on the leader's mbarriers
 // (mapa + mbarrier.arrive.release.cluster); tcgen05.commit multicasts "stage free" / "accumulator ready" to both.
 #include <cuda_fp16.h>
@@ -32,23 +32,16 @@ constexpr int KCHUNK = 64;                     // bf16 elements per 128-byte swi
 constexpr int A_STAGE_BYTES = TILE_M * 128;    // 16 KB
 constexpr int NUM_PRODUCER_WARPS = 16;  // 4 per SM sub-partition: the per-chunk fence / barrier latencies overlap
 constexpr int ARG_PARTS = NUM_PRODUCER_WARPS * 32 / 128;  // producer threads per row of a tile (argument split)
-// The producer warps form K2_PGROUPS groups that build alternate chunks (group g: chunks g, g + G, ...).  A warp's
-// fixed per-chunk latencies (empty-barrier wait, argument / frequency loads, proxy fence, arrive) are then paid once
-// per G chunk periods and overlap the MUFU work of the other groups; with one group every warp pays them every chunk
-// and the XU pipe idles half of the time (ncu: 46 % busy).
-#ifndef K2_PGROUPS
-#define K2_PGROUPS 2
-#endif
-constexpr int PGROUPS = K2_PGROUPS;
-constexpr int WARPS_PER_PGROUP = NUM_PRODUCER_WARPS / PGROUPS;
-constexpr int PARTS = WARPS_PER_PGROUP * 32 / 128;  // threads of one group per row (1, 2 or 4)
-constexpr int GROUPS_PER_THREAD = 8 / PARTS;        // 16-byte pieces of its 128-byte row a thread builds
-static_assert(PGROUPS == 1 || PGROUPS == 2 || PGROUPS == 4, "producer groups");
+// The producer warps form KCH groups (KCH = C / 64 K-chunks per slot); group g builds K-chunk g of EVERY slot.  A thread
+// therefore always works on the same frequencies and keeps its div_term values in registers for the whole kernel:
+// fetching them from shared memory per chunk (LDS.128 broadcasts, two wavefronts each, with the multiplies waiting on
+// them) cost 15 % of the kernel at C = 256 and 33 % at C = 128.  A warp's fixed per-chunk latencies (empty-barrier
+// wait, proxy fence, arrive) are paid once per KCH chunk periods and overlap the MUFU work of the other groups.
 constexpr int NUM_EPILOGUE_WARPS = 8;
 constexpr int WARP_MMA = NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS, WARP_LOADER = WARP_MMA + 1, WARP_ALLOC = WARP_MMA + 2;
 constexpr int K2_THREADS = (WARP_MMA + 4) * 32;
 #ifndef K2_MUFU_GROUPS
-#define K2_MUFU_GROUPS GROUPS_PER_THREAD  // of a thread's 16-byte pieces per chunk: this many on MUFU, the rest on the FMA pipe
+#define K2_MUFU_GROUPS 8  // of a thread's 16-byte pieces per chunk: this many on MUFU, the rest on the FMA pipe (experiment)
 #endif
 
 template <int C>
@@ -57,6 +50,12 @@ struct K2Cfg {
     static constexpr int W_CHUNK_BYTES = (C / 2) * 128;  // this CTA's C/2 weight rows x 64 bf16
     static constexpr int W_HALF_BYTES = KCH * W_CHUNK_BYTES;  // = C*C bytes: one matrix, this CTA's half of the rows
     static constexpr int NSTAGE = (C == 256) ? 5 : 8;
+    static constexpr int PGROUPS = KCH;                                // producer groups
+    static constexpr int WARPS_PER_PGROUP = NUM_PRODUCER_WARPS / PGROUPS;
+    static constexpr int PARTS = WARPS_PER_PGROUP * 32 / 128;          // threads of one group per row (1 or 2)
+    static constexpr int GROUPS_PER_THREAD = 8 / PARTS;                // 16-byte pieces of its 128-byte row a thread builds
+    static constexpr bool PREGEN = GROUPS_PER_THREAD <= 4;             // build the whole share before the stage wait
+    static_assert(PARTS >= 1 && NUM_PRODUCER_WARPS % PGROUPS == 0, "producer groups");
     static constexpr int TMEM_COLS = 2 * C;              // two fp32 accumulators of C columns (per CTA)
     static constexpr int COLS_PER_THREAD = C / 2;
     static constexpr int NBAR = 2 * NSTAGE + 5;
@@ -156,7 +155,7 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
     for (int t = threadIdx.x; t < C / 2; t += K2_THREADS) s_div[t] = prm.div_term[t];
     if (threadIdx.x == 0) {
         for (int s = 0; s < Cfg::NSTAGE; ++s) {
-            ptx::mbar_init(bar_full + 8 * s, 2 * WARPS_PER_PGROUP);
+            ptx::mbar_init(bar_full + 8 * s, 2 * Cfg::WARPS_PER_PGROUP);
             ptx::mbar_init(bar_empty + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
@@ -189,10 +188,11 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
 
     if (warp < NUM_PRODUCER_WARPS) {
         // =============================== PRODUCERS: sinusoid rows -> swizzled smem ===============================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
         const int row = threadIdx.x & (TILE_M - 1);
         const int argpart = threadIdx.x >> 7;     // which of its row's k+1 arguments this thread evaluates
-        const int pgroup = argpart / PARTS;       // producer group: builds chunks pgroup, pgroup + PGROUPS, ...
+        constexpr int PGROUPS = Cfg::PGROUPS, PARTS = Cfg::PARTS, GROUPS_PER_THREAD = Cfg::GROUPS_PER_THREAD;
+        const int pgroup = argpart / PARTS;       // producer group = the K-chunk (of every slot) it builds
         const int part = argpart - pgroup * PARTS;  // which GROUPS_PER_THREAD of the 8 sixteen-byte pieces of a row
         const long long per_b = (long long)prm.row_count * prm.n;
         const float4* s_div4 = (const float4*)s_div;
@@ -228,50 +228,77 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
             xbuf ^= 1;
         };
 
-        const int chunks_per_tile = slots * Cfg::KCH;
-        int ci = pgroup;  // this group's next chunk of the current tile (chunk = K-chunk ci % KCH of slot ci / KCH)
+        // this thread's frequencies, for the whole kernel (chunk pgroup of every slot, pieces part*GPT .. +GPT-1)
+        float4 w[GROUPS_PER_THREAD];
+#pragma unroll
+        for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
+            w[gg] = s_div4[pgroup * 8 + part * GROUPS_PER_THREAD + gg];
+        }
+        // one 16-byte piece: 4 frequencies -> (sin, cos) pairs as bf16
+        // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
+        auto piece = [&](float xv, int gg, uint32_t* o) {
+            const float o0 = __fmul_rn(xv, w[gg].x), o1 = __fmul_rn(xv, w[gg].y);
+            const float o2 = __fmul_rn(xv, w[gg].z), o3 = __fmul_rn(xv, w[gg].w);
+#ifdef K2_DBG_NO_SINCOS  // timing experiments only (tools/k2_variants.sh)
+            o[0] = pack_bf16x2(o0, o0 + 1.f); o[1] = pack_bf16x2(o1, o1 + 1.f);
+            o[2] = pack_bf16x2(o2, o2 + 1.f); o[3] = pack_bf16x2(o3, o3 + 1.f);
+#else
+            if (gg < K2_MUFU_GROUPS) {  // MUFU.SIN / MUFU.COS (XU pipe, 16 results / clk / SM)
+                o[0] = pack_bf16x2(__sinf(o0), __cosf(o0));
+                o[1] = pack_bf16x2(__sinf(o1), __cosf(o1));
+                o[2] = pack_bf16x2(__sinf(o2), __cosf(o2));
+                o[3] = pack_bf16x2(__sinf(o3), __cosf(o3));
+            } else {                    // polynomial on the FMA pipe (experiment: not faster)
+                float s0, c0, s1, c1, s2, c2, s3, c3;
+                sincos_fma(o0, s0, c0); sincos_fma(o1, s1, c1); sincos_fma(o2, s2, c2); sincos_fma(o3, s3, c3);
+                o[0] = pack_bf16x2(s0, c0); o[1] = pack_bf16x2(s1, c1);
+                o[2] = pack_bf16x2(s2, c2); o[3] = pack_bf16x2(s3, c3);
+            }
+#endif
+        };
+        auto store_piece = [&](uint32_t a_dst, int gg, const uint32_t* o) {
+#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_STS)
+            const uint32_t addr = a_dst + (((part * GROUPS_PER_THREAD + gg) ^ sw) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3])
+                         : "memory");
+#endif
+        };
+
         for (int tp = cluster_id; tp < prm.num_tile_pairs; tp += num_clusters) {
             load_x(tp);
 #pragma unroll 1
-            for (; ci < chunks_per_tile; ci += PGROUPS) {
-                const int s = ci / Cfg::KCH, kc = ci - s * Cfg::KCH;
-                uint32_t v[GROUPS_PER_THREAD][4];  // this thread's share of its row (4 frequencies per 16-byte piece)
-#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_GEN)
+            for (int s = 0; s < slots; ++s) {  // chunk (slot s, K-chunk pgroup)
                 const float xv = x_row[s * TILE_M];  // angle s for s < k, distance at s == k
-#pragma unroll
-                for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
-                    // positional_embedding.py:28-31: omega = x * div_term (fp32 product), then sin / cos
-                    const float4 w = s_div4[kc * 8 + part * GROUPS_PER_THREAD + gg];
-                    const float o0 = __fmul_rn(xv, w.x), o1 = __fmul_rn(xv, w.y);
-                    const float o2 = __fmul_rn(xv, w.z), o3 = __fmul_rn(xv, w.w);
-#ifdef K2_DBG_NO_SINCOS  // timing experiments only (tools/k2_variants.sh)
-                    v[gg][0] = pack_bf16x2(o0, o0 + 1.f); v[gg][1] = pack_bf16x2(o1, o1 + 1.f);
-                    v[gg][2] = pack_bf16x2(o2, o2 + 1.f); v[gg][3] = pack_bf16x2(o3, o3 + 1.f);
-#else
-                    if (gg < K2_MUFU_GROUPS) {  // MUFU.SIN / MUFU.COS (XU pipe, 16 results / clk / SM)
-                        v[gg][0] = pack_bf16x2(__sinf(o0), __cosf(o0));
-                        v[gg][1] = pack_bf16x2(__sinf(o1), __cosf(o1));
-                        v[gg][2] = pack_bf16x2(__sinf(o2), __cosf(o2));
-                        v[gg][3] = pack_bf16x2(__sinf(o3), __cosf(o3));
-                    } else {                    // polynomial on the FMA pipe (experiment: not faster)
-                        float s0, c0, s1, c1, s2, c2, s3, c3;
-                        sincos_fma(o0, s0, c0); sincos_fma(o1, s1, c1); sincos_fma(o2, s2, c2); sincos_fma(o3, s3, c3);
-                        v[gg][0] = pack_bf16x2(s0, c0); v[gg][1] = pack_bf16x2(s1, c1);
-                        v[gg][2] = pack_bf16x2(s2, c2); v[gg][3] = pack_bf16x2(s3, c3);
-                    }
-#endif
-                }
-#endif
-                // the row is built in registers BEFORE the wait: the stage is normally free by then
-                ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)ci);
-#if !defined(K2_DBG_NO_PRODUCE) && !defined(K2_DBG_NO_STS)
                 const uint32_t a_dst = a_row + stage * A_STAGE_BYTES;
+#if defined(K2_DBG_NO_PRODUCE) || defined(K2_DBG_NO_GEN)
+                ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)s);
+                uint32_t z[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
-                for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) {
-                    const uint32_t addr = a_dst + (((part * GROUPS_PER_THREAD + gg) ^ sw) << 4);
-                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v[gg][0]),
-                                 "r"(v[gg][1]), "r"(v[gg][2]), "r"(v[gg][3])
-                                 : "memory");
+                for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) store_piece(a_dst, gg, z);
+#else
+                if (Cfg::PREGEN) {
+                    // the thread's whole share is built in registers BEFORE the wait: the stage is normally free by then
+                    uint32_t v[GROUPS_PER_THREAD][4];
+#pragma unroll
+                    for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) piece(xv, gg, v[gg]);
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)s);
+#pragma unroll
+                    for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) store_piece(a_dst, gg, v[gg]);
+                } else {
+                    // 8 pieces do not fit next to the resident frequencies: the first half is built before the wait
+                    constexpr int HALF = GROUPS_PER_THREAD / 2;
+                    uint32_t v[HALF][4];
+#pragma unroll
+                    for (int gg = 0; gg < HALF; ++gg) piece(xv, gg, v[gg]);
+                    ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)s);
+#pragma unroll
+                    for (int gg = 0; gg < HALF; ++gg) store_piece(a_dst, gg, v[gg]);
+#pragma unroll
+                    for (int gg = HALF; gg < GROUPS_PER_THREAD; ++gg) {
+                        uint32_t o[4];
+                        piece(xv, gg, o);
+                        store_piece(a_dst, gg, o);
+                    }
                 }
 #endif
 #ifndef K2_DBG_NO_FENCE
@@ -282,13 +309,12 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 stage += PGROUPS;
                 if (stage >= Cfg::NSTAGE) { stage -= Cfg::NSTAGE; phase ^= 1; }
             }
-            ci -= chunks_per_tile;
         }
     } else if (warp < NUM_PRODUCER_WARPS + NUM_EPILOGUE_WARPS) {
         // =============================== EPILOGUE: TMEM -> registers -> running max -> HBM =======================
         // The running reduction over the k angle slots is kept as packed f16x2 (11-bit mantissa: 4x finer than the bf16
         // the result is stored in), which halves its register footprint -- the registers go to the producers.
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 120;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
         constexpr int NCOL = Cfg::COLS_PER_THREAD;
         const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 belong to this warp
         const int colhalf = (warp - NUM_PRODUCER_WARPS) >> 2;
