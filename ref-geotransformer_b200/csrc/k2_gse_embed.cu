@@ -54,6 +54,9 @@ struct K2Cfg {
     static constexpr int WARPS_PER_PGROUP = NUM_PRODUCER_WARPS / PGROUPS;
     static constexpr int PARTS = WARPS_PER_PGROUP * 32 / 128;          // threads of one group per row (1 or 2)
     static constexpr int GROUPS_PER_THREAD = 8 / PARTS;                // 16-byte pieces of its 128-byte row a thread builds
+#ifndef K2_PREGEN8
+#define K2_PREGEN8 4  // C = 256 (8 pieces per thread): how many are built before the stage wait
+#endif
     static constexpr bool PREGEN = GROUPS_PER_THREAD <= 4;             // build the whole share before the stage wait
     static_assert(PARTS >= 1 && NUM_PRODUCER_WARPS % PGROUPS == 0, "producer groups");
     static constexpr int TMEM_COLS = 2 * C;              // two fp32 accumulators of C columns (per CTA)
@@ -218,8 +221,12 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                 const float4 pi = __ldg(prm.pts4 + b * prm.n + i);
                 const float4 pj = __ldg(prm.pts4 + b * prm.n + j);
                 for (int s = argpart; s < slots; s += ARG_PARTS)
+#ifdef K2_DBG_NO_ARGS  // timing experiment: no atan2 / sqrt (wrong values)
+                    xs[s * TILE_M + row] = pi.x * pj.y + (float)s;
+#else
                     xs[s * TILE_M + row] = pair_argument_one(pi, pj, prm.refv + (b * prm.n + i) * k, k, s,
                                                              prm.sigma_d, prm.factor_a);
+#endif
             } else {
                 for (int s = argpart; s < slots; s += ARG_PARTS) xs[s * TILE_M + row] = 0.f;
             }
@@ -286,8 +293,8 @@ gse_embed_tc_kernel(const __grid_constant__ K2Params prm) {
                     for (int gg = 0; gg < GROUPS_PER_THREAD; ++gg) store_piece(a_dst, gg, v[gg]);
                 } else {
                     // 8 pieces do not fit next to the resident frequencies: the first half is built before the wait
-                    constexpr int HALF = GROUPS_PER_THREAD / 2;
-                    uint32_t v[HALF][4];
+                    constexpr int HALF = K2_PREGEN8;
+                    uint32_t v[HALF > 0 ? HALF : 1][4];
 #pragma unroll
                     for (int gg = 0; gg < HALF; ++gg) piece(xv, gg, v[gg]);
                     ptx::mbar_wait(bar_empty + 8 * stage, phase ^ 1, WD_PRODUCER | (uint32_t)s);
