@@ -132,6 +132,30 @@ int geotx_attention(const float* q, const float* k, const float* v, const float*
 int geotx_add_layernorm(const float* x, const float* residual, const float* gamma, const float* beta, int64_t rows,
                         int C, float eps, float* out, void* stream);
 
+/* Coarse matching behind the path: F.normalize of both clouds' output features
+ * (experiments/<cfg>/model.py:141-142) followed by SuperPointMatching.forward
+ * (geotransformer/modules/geotransformer/superpoint_matching.py:13-51, with pairwise_distance(normalized=True),
+ * modules/ops/pairwise_distance.py:24-25,30): scores = exp(-max(0, 2 - 2 x.y)); with dual_normalization
+ * scores = (s / rowsum) * (s / colsum); the num_corr largest entries of the (n,m) matrix in descending order.
+ *   ref_feats f32 [n,d], src_feats f32 [m,d]
+ *   ref_keep, src_keep   u8 [n], [m] or NULL: nonzero = keep (the reference's masks: "False if empty"); removed rows and
+ *                        columns take no part in the sums or the selection; indices returned are ORIGINAL row numbers
+ *   normalize != 0       rows are first divided by max(||row||_2, 1e-12); the unit rows are also written to
+ *                        ref_unit_out / src_unit_out (f32 [n,d] / [m,d]) when these are not NULL
+ *   ref_idx_out, src_idx_out i64 [num_corr], score_out f32 [num_corr], count_out i32 [1] (all device memory):
+ *                        count = min(num_corr, kept_rows * kept_cols) entries are valid, the rest are -1 / 0
+ *   score_matrix         optional f32 [n,m]: receives the final score matrix (removed entries hold the bit pattern
+ *                        0xFFFFFFFF); NULL keeps it inside the workspace
+ *   workspace            geotx_spm_workspace_bytes(n, m, d, num_corr) bytes, 256-byte aligned
+ * Equal scores are ordered by ascending flat index i*m + j (torch.topk leaves that order unspecified).
+ * num_corr <= 4096; n*m < 2^32.  fp32 arithmetic throughout. */
+int64_t geotx_spm_workspace_bytes(int n, int m, int d, int num_corr);
+int geotx_superpoint_matching(const float* ref_feats, const float* src_feats, int n, int m, int d,
+                              const uint8_t* ref_keep, const uint8_t* src_keep, int normalize, float* ref_unit_out,
+                              float* src_unit_out, int dual_normalization, int num_corr, int64_t* ref_idx_out,
+                              int64_t* src_idx_out, float* score_out, int32_t* count_out, float* score_matrix,
+                              void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,18 +8,20 @@ from .modules import (  # noqa: F401
     AttentionLayer, AttentionOutput, GeometricStructureEmbedding, GeometricTransformer, GraphedGeometricTransformer, PipelinedGeometricTransformer,
     MultiHeadAttention,
     RPEAttentionLayer, RPEConditionalTransformer, RPEMultiHeadAttention, RPETransformerLayer,
-    SinusoidalPositionalEmbedding, TransformerLayer, build_act_layer, build_dropout_layer)
+    SinusoidalPositionalEmbedding, SuperPointMatching, TransformerLayer, build_act_layer, build_dropout_layer)
 
 __all__ = [
     'GeometricTransformer', 'GraphedGeometricTransformer', 'PipelinedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
-    'AttentionOutput', 'SinusoidalPositionalEmbedding', 'ops', 'synth',
+    'AttentionOutput', 'SinusoidalPositionalEmbedding', 'SuperPointMatching', 'ops', 'synth',
 ]
 
 _REFERENCE_PATCHES = (
     # (module of the reference, names it exports that this package re-implements)
     ('geotransformer.modules.geotransformer.geotransformer', ('GeometricTransformer', 'GeometricStructureEmbedding')),
-    ('geotransformer.modules.geotransformer', ('GeometricTransformer', 'GeometricStructureEmbedding')),
+    ('geotransformer.modules.geotransformer', ('GeometricTransformer', 'GeometricStructureEmbedding',
+                                               'SuperPointMatching')),
+    ('geotransformer.modules.geotransformer.superpoint_matching', ('SuperPointMatching',)),
     ('geotransformer.modules.transformer', ('RPEConditionalTransformer', 'RPETransformerLayer', 'TransformerLayer',
                                             'SinusoidalPositionalEmbedding')),
 )

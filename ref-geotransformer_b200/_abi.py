@@ -30,6 +30,8 @@ SIGNATURES = {
     'geotx_rpe_scores': (_i, [_p, _i64, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
     'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _f, _p, _i, _p]),
     'geotx_add_layernorm': (_i, [_p, _p, _p, _p, _i64, _i, _f, _p, _p]),
+    'geotx_spm_workspace_bytes': (_i64, [_i, _i, _i, _i]),
+    'geotx_superpoint_matching': (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
 }
 
 GEOTX_F32 = 0
@@ -37,7 +39,8 @@ GEOTX_BF16 = 1
 GEOTX_F16 = 2
 
 # kernels each entry point enqueues (bench.py's gpu_launches is counted from this)
-KERNELS_PER_CALL = {'geotx_gse_knn': 2}  # pack_points + knn
+KERNELS_PER_CALL = {'geotx_gse_knn': 2,  # pack_points + knn
+                    'geotx_superpoint_matching': 10}  # prepare, scores, sums, 6 select passes, collect
 
 _lib = None
 launch_count = 0  # hand-written kernels launched through this binding so far

@@ -788,3 +788,41 @@ class PipelinedGeometricTransformer:
         for done in pending:
             done[2]['d2h'].synchronize()
             yield done[1]
+
+
+class SuperPointMatching(nn.Module):
+    """Drop-in for geotransformer/modules/geotransformer/superpoint_matching.py:7-51, on
+    `geotx_superpoint_matching` (exact fp32 scores, dual normalisation and global top-K select in hand-written CUDA;
+    one (n,m) buffer instead of the reference's five, no full sort).
+
+    forward(ref_feats, src_feats, ref_masks=None, src_masks=None) -> (ref_corr_indices, src_corr_indices, corr_scores)
+    with masks True = keep, as in the reference (:19-20).  Without masks nothing synchronises with the host (the
+    number of correspondences is min(num_correspondences, n*m), known on the host); with masks the count depends on
+    device data and is read back, like the reference's own `torch.nonzero` (:32-33).
+    `normalize=True` (extension) fuses model.py:141-142's F.normalize; `match_normalized()` also returns the unit rows."""
+
+    def __init__(self, num_correspondences, dual_normalization=True):
+        super().__init__()
+        self.num_correspondences = num_correspondences
+        self.dual_normalization = dual_normalization
+
+    def _run(self, ref_feats, src_feats, ref_masks, src_masks, normalize):
+        out = ops.superpoint_matching(ref_feats.contiguous(), src_feats.contiguous(), self.num_correspondences,
+                                      self.dual_normalization, ref_masks, src_masks, normalize=normalize)
+        if ref_masks is None and src_masks is None:
+            count = min(self.num_correspondences, ref_feats.shape[0] * src_feats.shape[0])
+        else:
+            count = int(out['count'].item())
+        return out, count
+
+    @torch.no_grad()
+    def forward(self, ref_feats, src_feats, ref_masks=None, src_masks=None, normalize=False):
+        out, count = self._run(ref_feats, src_feats, ref_masks, src_masks, normalize)
+        return out['ref_idx'][:count], out['src_idx'][:count], out['scores'][:count]
+
+    @torch.no_grad()
+    def match_normalized(self, ref_feats, src_feats, ref_masks=None, src_masks=None):
+        """F.normalize + matching in one call: returns (ref_unit, src_unit, ref_idx, src_idx, scores), i.e. what
+        model.py:141-157 puts into output_dict['ref_feats_c'], ['src_feats_c'] and the node correspondences."""
+        out, count = self._run(ref_feats, src_feats, ref_masks, src_masks, True)
+        return out['ref_unit'], out['src_unit'], out['ref_idx'][:count], out['src_idx'][:count], out['scores'][:count]

@@ -220,3 +220,47 @@ def add_layernorm(x, residual, weight, bias, eps=1e-5, out=None):
     _abi.call('geotx_add_layernorm', _p(x), _p(residual), _p(weight), _p(bias), x.numel() // C, C, float(eps), _p(out),
               _stream())
     return out
+
+
+def superpoint_matching(ref_feats, src_feats, num_correspondences, dual_normalization=True, ref_masks=None,
+                        src_masks=None, normalize=False, return_matrix=False):
+    """Coarse matching (model.py:141-157, superpoint_matching.py:13-51) on the hand-written fp32 path.
+
+    ref_feats (n,d), src_feats (m,d) fp32; masks bool (True = keep) or None.  Returns a dict with
+      ref_idx, src_idx int64 (num_correspondences,), scores fp32 (num_correspondences,), count int32 (1,)  [device;
+      the first `count` entries are valid], ref_unit / src_unit (the F.normalize'd rows, only with normalize=True),
+      matrix (n,m) (only with return_matrix=True).  No host synchronisation."""
+    _check(ref_feats, 'ref_feats', torch.float32, 2)
+    _check(src_feats, 'src_feats', torch.float32, 2)
+    n, d = ref_feats.shape
+    m, d2 = src_feats.shape
+    if d != d2:
+        raise RuntimeError(f'feature widths differ: {d} vs {d2}')
+    dev = ref_feats.device
+    keep = []
+    for t, name, rows in ((ref_masks, 'ref_masks', n), (src_masks, 'src_masks', m)):
+        if t is None:
+            keep.append(None)
+            continue
+        _check(t, name, torch.bool, 1)
+        if t.shape[0] != rows:
+            raise RuntimeError(f'{name} must have {rows} entries, got {t.shape[0]}')
+        keep.append(t.view(torch.uint8))
+    K = int(num_correspondences)
+    lib = _abi.load()
+    nbytes = lib.geotx_spm_workspace_bytes(n, m, d, K)
+    if nbytes <= 0:
+        raise RuntimeError(f'superpoint_matching: bad sizes n={n} m={m} d={d} num_correspondences={K}')
+    work = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    out = dict(ref_idx=torch.empty(K, dtype=torch.int64, device=dev), src_idx=torch.empty(K, dtype=torch.int64, device=dev),
+               scores=torch.empty(K, dtype=torch.float32, device=dev), count=torch.empty(1, dtype=torch.int32, device=dev))
+    if normalize:
+        out['ref_unit'] = torch.empty_like(ref_feats)
+        out['src_unit'] = torch.empty_like(src_feats)
+    if return_matrix:
+        out['matrix'] = torch.empty(n, m, dtype=torch.float32, device=dev)
+    _abi.call('geotx_superpoint_matching', _p(ref_feats), _p(src_feats), n, m, d, _p(keep[0]), _p(keep[1]),
+              1 if normalize else 0, _p(out.get('ref_unit')), _p(out.get('src_unit')), 1 if dual_normalization else 0, K,
+              _p(out['ref_idx']), _p(out['src_idx']), _p(out['scores']), _p(out['count']), _p(out.get('matrix')),
+              _p(work), _stream())
+    return out

@@ -148,3 +148,47 @@ def test_oracle_equals_live_reference(oracle, pkg):
         a0, a1 = ref(rp, sp, rf, sf, ref_masks=masks0)
     b0, b1 = oracle.geometric_transformer(sd, cfg, rp, sp, rf, sf, ref_masks=masks0)
     assert torch.equal(a0, b0) and torch.equal(a1, b1)
+
+
+SPM_CASES = ['small_dual', 'small_plain', 'small_masked', 'small_allpairs', 'mid_dual']
+
+
+@pytest.mark.parametrize('tag', SPM_CASES)
+def test_superpoint_matching_oracle_vs_golden(oracle, golden, tag):
+    """the oracle's F.normalize + SuperPointMatching restatement against vectors written by the
+    reference class itself (tests/golden/make_golden_spm.py)."""
+    z = golden('spm_cases.npz')
+    cfg = eval(str(z[f'{tag}.cfg']))
+    exact = _same_torch(z['meta'])
+    ri, si, sc = oracle.superpoint_matching(
+        torch.from_numpy(z[f'{tag}.ref_feats']), torch.from_numpy(z[f'{tag}.src_feats']), cfg['K'], cfg['dual'],
+        torch.from_numpy(z[f'{tag}.ref_masks']), torch.from_numpy(z[f'{tag}.src_masks']), normalize=True)
+    _close(sc, z[f'{tag}.scores'], exact)
+    if exact:
+        assert np.array_equal(ri.numpy(), z[f'{tag}.ref_idx']) and np.array_equal(si.numpy(), z[f'{tag}.src_idx'])
+
+
+def test_superpoint_matching_oracle_on_transformer_output(oracle, golden):
+    z, zin = golden('spm_cases.npz'), golden('3dmatch_n1024_out.npz')
+    exact = _same_torch(z['meta'])
+    ri, si, sc = oracle.superpoint_matching(torch.from_numpy(zin['out_ref'][0]), torch.from_numpy(zin['out_src'][0]), 256,
+                                            True, normalize=True)
+    _close(sc, z['3dmatch_1024.scores'], exact)
+    if exact:
+        assert np.array_equal(ri.numpy(), z['3dmatch_1024.ref_idx'])
+        assert np.array_equal(si.numpy(), z['3dmatch_1024.src_idx'])
+
+
+@pytest.mark.skipif(not reference_available(), reason='/root/reference not present (GPU box)')
+def test_superpoint_matching_oracle_vs_live_reference(oracle):
+    load_reference()
+    from geotransformer.modules.geotransformer.superpoint_matching import SuperPointMatching
+    g = torch.Generator().manual_seed(99)
+    ref, src = torch.randn(150, 64, generator=g), torch.randn(131, 64, generator=g)
+    rm, sm = torch.rand(150, generator=g) > 0.1, torch.rand(131, generator=g) > 0.1
+    rn, sn = torch.nn.functional.normalize(ref, p=2, dim=1), torch.nn.functional.normalize(src, p=2, dim=1)
+    for dual in (True, False):
+        want = SuperPointMatching(77, dual)(rn, sn, rm, sm)
+        got = oracle.superpoint_matching(ref, src, 77, dual, rm, sm, normalize=True)
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
