@@ -23,12 +23,20 @@
 // and the top-K ORDER is decided at the 1e-6 relative level, out of reach of tf32 / half tensor-core inputs.
 #include "geotx_common.cuh"
 #include "host_util.h"
+#include <stdlib.h>
 
 namespace geotx {
 
 constexpr int SPM_TILE = 64;        // scores tile edge
-constexpr int SPM_KC = 16;          // contraction chunk
-constexpr int SPM_PITCH = 68;       // floats per staged k-row (16-byte aligned, 2-way conflicts on the transposing stores only)
+#ifndef SPM_SMALL_KC
+#define SPM_SMALL_KC 32  // contraction chunk of the 64 x 64 tile (16 for the 128 x 128 one)
+#endif
+#ifndef SPM_SCAN_MAX_CTAS
+#define SPM_SCAN_MAX_CTAS (148 * 8)  // histogram flushes cost CTAs x bins global atomics
+#endif
+#ifndef SPM_BIG_TILE_MIN_CTAS
+#define SPM_BIG_TILE_MIN_CTAS 256
+#endif
 constexpr int SPM_BINS = 2048;      // histogram bins (widest digit: 11 bits)
 constexpr int SPM_PASSES = 6;       // digits of the 64-bit key, most significant first
 constexpr int SPM_MAX_K = 4096;     // keys the final shared-memory sort holds
@@ -117,26 +125,35 @@ spm_prepare_kernel(const float* __restrict__ ref, const float* __restrict__ src,
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// spm_scores: 64 x 64 tile per CTA, 256 threads, 4 x 4 outputs per thread, k chunks of 16 staged transposed in shared
-// memory with a register prefetch of the next chunk.  Dot products accumulate in ascending k with FMA.
+// spm_scores: (16 TM) x (16 TN) tile per CTA, 256 threads, TM x TN outputs per thread (rows ty*4 + 64 q, columns
+// tx*4 + 64 q: every shared-memory read is a conflict-free or broadcast LDS.128), k chunks of 16 staged transposed in
+// shared memory with a register prefetch of the next chunk.  Dot products accumulate in ascending k with FMA.
 // ---------------------------------------------------------------------------------------------------------------
+template <int TM, int TN, int KC>
 __global__ void __launch_bounds__(256)
 spm_scores_kernel(const float* __restrict__ a, const float* __restrict__ b, int n, int m, int d,
                   const uint8_t* __restrict__ ref_keep, const uint8_t* __restrict__ src_keep, int dual,
                   float* __restrict__ scores, float* __restrict__ row_part, float* __restrict__ col_part) {
-    __shared__ __align__(16) float As[2][SPM_KC][SPM_PITCH];
-    __shared__ __align__(16) float Bs[2][SPM_KC][SPM_PITCH];
-    __shared__ float s_col[16][SPM_TILE];
+    constexpr int RM = 16 * TM, RN = 16 * TN;            // tile rows / columns
+    constexpr int PA = RM + 4, PB = RN + 4;               // staged pitches (16-byte aligned)
+    constexpr int QM = TM / 4, QN = TN / 4;               // float4 groups per thread
+    constexpr int KQ = KC / 4;                            // float4 per staged row
+    constexpr int LA = RM * KQ / 256, LB = RN * KQ / 256; // float4 each thread stages per chunk
+    constexpr int SMEM_STAGE = 2 * KC * (PA + PB);        // floats
+    constexpr int SMEM_COL = 16 * RN;
+    static_assert(RM * KQ % 256 == 0 && RN * KQ % 256 == 0, "staging must divide over 256 threads");
+    __shared__ __align__(16) float s_mem[SMEM_STAGE > SMEM_COL ? SMEM_STAGE : SMEM_COL];
+    float (*As)[KC][PA] = reinterpret_cast<float (*)[KC][PA]>(s_mem);
+    float (*Bs)[KC][PB] = reinterpret_cast<float (*)[KC][PB]>(s_mem + 2 * KC * PA);
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-    const int i0 = blockIdx.y * SPM_TILE, j0 = blockIdx.x * SPM_TILE;
-    const int lrow = tid >> 2, lk = (tid & 3) * 4;  // this thread stages row lrow, k offsets lk..lk+3 of each operand
-    const bool a_ok = i0 + lrow < n, b_ok = j0 + lrow < m;
-    const float* ap = a + (size_t)(a_ok ? i0 + lrow : 0) * d;
-    const float* bp = b + (size_t)(b_ok ? j0 + lrow : 0) * d;
+    const int i0 = blockIdx.y * RM, j0 = blockIdx.x * RN;
+    const int lrow = tid / KQ, lk = (tid % KQ) * 4;  // staging: rows lrow + (256 / KQ) u, k offsets lk..lk+3
+    constexpr int LSTEP = 256 / KQ;
     const bool vec = (d & 3) == 0;
-    auto fetch = [&](const float* p, bool ok, int k) {
+    auto fetch = [&](const float* base, int row, int rows, int k) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (ok) {
+        if (row < rows) {
+            const float* p = base + (size_t)row * d;
             if (vec && k + 3 < d) {
                 v = __ldg((const float4*)(p + k));
             } else {
@@ -148,97 +165,120 @@ spm_scores_kernel(const float* __restrict__ a, const float* __restrict__ b, int 
         }
         return v;
     };
-    auto stage = [&](float (*S)[SPM_PITCH], const float4& v) {
-        S[lk][lrow] = v.x;
-        S[lk + 1][lrow] = v.y;
-        S[lk + 2][lrow] = v.z;
-        S[lk + 3][lrow] = v.w;
+    float4 ra[LA], rb[LB];
+    auto fetch_all = [&](int k) {
+#pragma unroll
+        for (int u = 0; u < LA; ++u) ra[u] = fetch(a, i0 + lrow + LSTEP * u, n, k + lk);
+#pragma unroll
+        for (int u = 0; u < LB; ++u) rb[u] = fetch(b, j0 + lrow + LSTEP * u, m, k + lk);
     };
-    float acc[4][4];
+    auto stage_all = [&](int buf) {
 #pragma unroll
-    for (int r = 0; r < 4; ++r)
+        for (int u = 0; u < LA; ++u) {
+            As[buf][lk][lrow + LSTEP * u] = ra[u].x;
+            As[buf][lk + 1][lrow + LSTEP * u] = ra[u].y;
+            As[buf][lk + 2][lrow + LSTEP * u] = ra[u].z;
+            As[buf][lk + 3][lrow + LSTEP * u] = ra[u].w;
+        }
 #pragma unroll
-        for (int c = 0; c < 4; ++c) acc[r][c] = 0.f;
-    const int chunks = (d + SPM_KC - 1) / SPM_KC;
-    float4 ra = fetch(ap, a_ok, lk), rb = fetch(bp, b_ok, lk);
-    stage(As[0], ra);
-    stage(Bs[0], rb);
+        for (int u = 0; u < LB; ++u) {
+            Bs[buf][lk][lrow + LSTEP * u] = rb[u].x;
+            Bs[buf][lk + 1][lrow + LSTEP * u] = rb[u].y;
+            Bs[buf][lk + 2][lrow + LSTEP * u] = rb[u].z;
+            Bs[buf][lk + 3][lrow + LSTEP * u] = rb[u].w;
+        }
+    };
+    float acc[TM][TN];
+#pragma unroll
+    for (int r = 0; r < TM; ++r)
+#pragma unroll
+        for (int c = 0; c < TN; ++c) acc[r][c] = 0.f;
+    const int chunks = (d + KC - 1) / KC;
+    fetch_all(0);
+    stage_all(0);
     __syncthreads();
     for (int ch = 0; ch < chunks; ++ch) {
         const int cur = ch & 1;
-        if (ch + 1 < chunks) {
-            ra = fetch(ap, a_ok, (ch + 1) * SPM_KC + lk);
-            rb = fetch(bp, b_ok, (ch + 1) * SPM_KC + lk);
-        }
+        if (ch + 1 < chunks) fetch_all((ch + 1) * KC);
 #pragma unroll
-        for (int kk = 0; kk < SPM_KC; ++kk) {
-            const float4 av = *(const float4*)&As[cur][kk][ty * 4];
-            const float4 bv = *(const float4*)&Bs[cur][kk][tx * 4];
-            const float ar[4] = {av.x, av.y, av.z, av.w}, br[4] = {bv.x, bv.y, bv.z, bv.w};
+        for (int kk = 0; kk < KC; ++kk) {
+            float ar[TM], br[TN];
 #pragma unroll
-            for (int r = 0; r < 4; ++r)
+            for (int q = 0; q < QM; ++q) {
+                const float4 v = *(const float4*)&As[cur][kk][q * 64 + ty * 4];
+                ar[4 * q] = v.x, ar[4 * q + 1] = v.y, ar[4 * q + 2] = v.z, ar[4 * q + 3] = v.w;
+            }
 #pragma unroll
-                for (int c = 0; c < 4; ++c) acc[r][c] = fmaf(ar[r], br[c], acc[r][c]);
+            for (int q = 0; q < QN; ++q) {
+                const float4 v = *(const float4*)&Bs[cur][kk][q * 64 + tx * 4];
+                br[4 * q] = v.x, br[4 * q + 1] = v.y, br[4 * q + 2] = v.z, br[4 * q + 3] = v.w;
+            }
+#pragma unroll
+            for (int r = 0; r < TM; ++r)
+#pragma unroll
+                for (int c = 0; c < TN; ++c) acc[r][c] = fmaf(ar[r], br[c], acc[r][c]);
         }
-        if (ch + 1 < chunks) {
-            stage(As[cur ^ 1], ra);
-            stage(Bs[cur ^ 1], rb);
-        }
+        if (ch + 1 < chunks) stage_all(cur ^ 1);
         __syncthreads();
     }
     // exp(-clamp(2 - 2 xy, 0)); removed rows / columns contribute 0 to the sums (superpoint_matching.py:32-37)
-    bool keep_r[4], keep_c[4];
+    auto row_of = [&](int r) { return i0 + (r >> 2) * 64 + ty * 4 + (r & 3); };
+    auto col_of = [&](int c) { return j0 + (c >> 2) * 64 + tx * 4 + (c & 3); };
+    bool keep_c[TN];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        const int i = i0 + ty * 4 + r;
-        keep_r[r] = i < n && (!ref_keep || ref_keep[i]);
-    }
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-        const int j = j0 + tx * 4 + c;
+    for (int c = 0; c < TN; ++c) {
+        const int j = col_of(c);
         keep_c[c] = j < m && (!src_keep || src_keep[j]);
     }
-    float rs[4] = {0.f, 0.f, 0.f, 0.f}, cs[4] = {0.f, 0.f, 0.f, 0.f};
+    float cs[TN];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
+    for (int c = 0; c < TN; ++c) cs[c] = 0.f;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+    for (int r = 0; r < TM; ++r) {
+        const int i = row_of(r);
+        const bool keep_r = i < n && (!ref_keep || ref_keep[i]);
+        float rs = 0.f;
+#pragma unroll
+        for (int c = 0; c < TN; ++c) {
             const float d2 = fmaxf(2.0f - 2.0f * acc[r][c], 0.0f);
-            const float s = (keep_r[r] && keep_c[c]) ? expf(-d2) : 0.f;
+            const float s = (keep_r && keep_c[c]) ? expf(-d2) : 0.f;
             acc[r][c] = s;
-            rs[r] += s;
+            rs += s;
             cs[c] += s;
         }
-        const int i = i0 + ty * 4 + r;
         if (i < n) {
-            float* out = scores + (size_t)i * m + j0 + tx * 4;
-            if ((m & 3) == 0 && j0 + tx * 4 + 3 < m) {
-                *(float4*)out = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
-            } else {
 #pragma unroll
-                for (int c = 0; c < 4; ++c)
-                    if (j0 + tx * 4 + c < m) out[c] = acc[r][c];
+            for (int q = 0; q < QN; ++q) {
+                const int j = col_of(4 * q);
+                float* out = scores + (size_t)i * m + j;
+                if ((m & 3) == 0 && j + 3 < m) {
+                    *(float4*)out = make_float4(acc[r][4 * q], acc[r][4 * q + 1], acc[r][4 * q + 2], acc[r][4 * q + 3]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+                        if (j + c < m) out[c] = acc[r][4 * q + c];
+                }
             }
+        }
+        if (dual) {  // row partial: the 16 threads of a row group are 16 consecutive lanes -> fixed xor tree
+#pragma unroll
+            for (int off = 8; off > 0; off >>= 1) rs += __shfl_xor_sync(0xffffffffu, rs, off);
+            if (tx == 0 && i < n) row_part[(size_t)blockIdx.x * n + i] = rs;
         }
     }
     if (!dual) return;
-    // row partials: the 16 threads of a row group are 16 consecutive lanes -> fixed xor tree
+    // column partials: through shared memory (the staging buffers are dead), added in ascending ty
+    float (*s_col)[RN] = reinterpret_cast<float (*)[RN]>(s_mem);
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-#pragma unroll
-        for (int off = 8; off > 0; off >>= 1) rs[r] += __shfl_xor_sync(0xffffffffu, rs[r], off);
-        const int i = i0 + ty * 4 + r;
-        if (tx == 0 && i < n) row_part[(size_t)blockIdx.x * n + i] = rs[r];
-    }
-    // column partials: through shared memory, added in ascending ty
-#pragma unroll
-    for (int c = 0; c < 4; ++c) s_col[ty][tx * 4 + c] = cs[c];
+    for (int c = 0; c < TN; ++c) s_col[ty][col_of(c) - j0] = cs[c];
     __syncthreads();
-    if (tid < SPM_TILE && j0 + tid < m) {
-        float t = 0.f;
+    for (int t = tid; t < RN; t += 256) {
+        if (j0 + t < m) {
+            float sum = 0.f;
 #pragma unroll
-        for (int y = 0; y < 16; ++y) t += s_col[y][tid];
-        col_part[(size_t)blockIdx.y * m + j0 + tid] = t;
+            for (int y = 0; y < 16; ++y) sum += s_col[y][t];
+            col_part[(size_t)blockIdx.y * m + j0 + t] = sum;
+        }
     }
 }
 
@@ -295,32 +335,59 @@ __device__ __forceinline__ unsigned long long spm_key(uint32_t bits, uint32_t id
     return ((unsigned long long)bits << 32) | (unsigned long long)(0xFFFFFFFFu - idx);
 }
 
-// Last CTA of a pass: walk the digit histogram from the top until `need` keys are covered.
-__device__ void spm_fix_digit(SpmState* state, const unsigned int* hist, int pass, unsigned int* s_part) {
-    const int tid = threadIdx.x;  // 256 threads, 8 bins each, bin 2047 first
+// Last CTA of a pass: find the digit at which the histogram, summed from the top, first covers `need` keys.
+// 256 threads sum 8 bins each (thread 0 = bins 2047..2040); warp 0 scans 8 of those per lane with shuffles, and the
+// one lane in whose range the count crosses `need` walks its <= 64 bins.
+__device__ void spm_fix_digit(SpmState* state, const unsigned int* hist, int pass, unsigned int* s_bins) {
+    __shared__ unsigned int s_part[256];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < SPM_BINS; i += blockDim.x) s_bins[i] = __ldcg(hist + i);  // the walk below must not chase L2
+    __syncthreads();
     unsigned int local = 0;
 #pragma unroll
-    for (int b = 0; b < 8; ++b) local += __ldcg(hist + (SPM_BINS - 1 - (tid * 8 + b)));
+    for (int b = 0; b < 8; ++b) local += s_bins[SPM_BINS - 1 - (tid * 8 + b)];
     s_part[tid] = local;
     __syncthreads();
-    if (tid == 0) {
-        const unsigned int need = state->need;
-        unsigned int cum = 0;
-        int g = 0;
-        while (g < 255 && cum + s_part[g] < need) cum += s_part[g++];
-        int bin = SPM_BINS - 1 - g * 8;
-        unsigned int h = __ldcg(hist + bin);
-        while (bin > 0 && cum + h < need) {
-            cum += h;
-            --bin;
-            h = __ldcg(hist + bin);
-        }
-        state->prefix |= (unsigned long long)bin << c_spm_shift[pass];
-        if (cum + h <= need) {  // the bucket is taken whole (== need; < need cannot happen while K_eff <= candidates)
-            state->resolved = 1u;
-        } else {
-            state->need = need - cum;
-        }
+    if (tid >= 32) return;
+    const unsigned int need = state->need;
+    unsigned int mine = 0;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) mine += s_part[tid * 8 + g];
+    unsigned int incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const unsigned int up = __shfl_up_sync(0xffffffffu, incl, off);
+        if (tid >= off) incl += up;
+    }
+    const unsigned int covers = __ballot_sync(0xffffffffu, incl >= need);
+    const int owner = covers ? __ffs(covers) - 1 : 31;  // no lane covers `need` only if K_eff exceeded the candidates
+    if (tid != owner) return;
+    unsigned int cum = incl - mine;
+    int bin = SPM_BINS - 1 - tid * 64;
+    const int last = bin - 63;
+    unsigned int h = s_bins[bin];
+    while (bin > last && cum + h < need) {
+        cum += h;
+        --bin;
+        h = s_bins[bin];
+    }
+    state->prefix |= (unsigned long long)bin << c_spm_shift[pass];
+    if (cum + h <= need) {  // the bucket is taken whole: keys >= prefix are exactly the selection
+        state->resolved = 1u;
+    } else {
+        state->need = need - cum;
+    }
+}
+
+// Histogram increment of a whole warp.  The scores are strongly clustered (nearly every entry shares its top digits),
+// and 32 shared-memory atomics on one bin serialise: when all lanes agree, one lane adds 32; otherwise the digits are
+// spread and per-lane atomics rarely collide.  digit == ~0u: nothing to add.
+__device__ __forceinline__ void spm_hist_add(unsigned int* s_hist, unsigned int digit, int lane) {
+    const unsigned int first = __shfl_sync(0xffffffffu, digit, 0);
+    if (__all_sync(0xffffffffu, digit == first)) {
+        if (lane == 0 && digit != ~0u) atomicAdd(&s_hist[digit], 32u);
+    } else if (digit != ~0u) {
+        atomicAdd(&s_hist[digit], 1u);
     }
 }
 
@@ -335,27 +402,67 @@ spm_pass_kernel(float* __restrict__ scores, int n, int m, int dual, const float*
     unsigned int* hist = hist_all + pass * SPM_BINS;
     for (int i = threadIdx.x; i < SPM_BINS; i += blockDim.x) s_hist[i] = 0u;
     __syncthreads();
+    const int lane = threadIdx.x & 31;
     const int shift = c_spm_shift[pass], width = c_spm_width[pass];
     const unsigned long long prefix = FIRST ? 0ull : state->prefix;
     const int above = shift + width;  // bits above this digit must equal the prefix
     const unsigned int dmask = (1u << width) - 1u;
     const size_t total = (size_t)n * m;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-        uint32_t bits;
+    // entry idx -> its digit (or ~0u); FIRST also turns the raw score into the final one, in place
+    auto visit = [&](uint32_t raw, size_t idx, int i, int j) -> uint32_t {
+        uint32_t bits = raw;
         if (FIRST) {
-            const int i = (int)(idx / (unsigned)m), j = (int)(idx - (size_t)i * m);
             const bool keep = (!ref_keep || ref_keep[i]) && (!src_keep || src_keep[j]);
-            float f = scores[idx];
+            float f = __uint_as_float(raw);
             if (dual) f = __fdiv_rn(f, __ldg(row_sum + i)) * __fdiv_rn(f, __ldg(col_sum + j));  // superpoint_matching.py:39-41
             bits = keep ? __float_as_uint(f) : SPM_MASKED;
-            ((uint32_t*)scores)[idx] = bits;
-        } else {
-            bits = ((const uint32_t*)scores)[idx];
         }
-        if (bits == SPM_MASKED) continue;
+        return bits;
+    };
+    auto digit_of = [&](uint32_t bits, size_t idx) -> unsigned int {
+        if (bits == SPM_MASKED) return ~0u;
         const unsigned long long key = spm_key(bits, (uint32_t)idx);
-        if (FIRST || (above < 64 && (key >> above) == (prefix >> above)))
-            atomicAdd(&s_hist[(unsigned int)(key >> shift) & dmask], 1u);
+        if (!FIRST && (key >> above) != (prefix >> above)) return ~0u;
+        return (unsigned int)(key >> shift) & dmask;
+    };
+    const size_t quads = total >> 2;
+    uint4* q4 = (uint4*)scores;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q - lane < quads; q += stride) {  // warp-uniform bound
+        const bool live = q < quads;
+        uint4 v = make_uint4(SPM_MASKED, SPM_MASKED, SPM_MASKED, SPM_MASKED);
+        const size_t idx = q << 2;
+        if (live) {
+            v = q4[q];
+            if (FIRST) {
+                int i = (int)(idx / (unsigned)m), j = (int)(idx - (size_t)i * m);
+                uint32_t* e = &v.x;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    e[t] = visit(e[t], idx + t, i, j);
+                    if (++j == m) j = 0, ++i;
+                }
+                q4[q] = v;
+            }
+        }
+        spm_hist_add(s_hist, live ? digit_of(v.x, idx) : ~0u, lane);
+        spm_hist_add(s_hist, live ? digit_of(v.y, idx + 1) : ~0u, lane);
+        spm_hist_add(s_hist, live ? digit_of(v.z, idx + 2) : ~0u, lane);
+        spm_hist_add(s_hist, live ? digit_of(v.w, idx + 3) : ~0u, lane);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 32) {  // the last total % 4 entries
+        const size_t idx = (quads << 2) + lane;
+        unsigned int digit = ~0u;
+        if (lane < (int)(total & 3)) {
+            uint32_t bits = ((uint32_t*)scores)[idx];
+            if (FIRST) {
+                const int i = (int)(idx / (unsigned)m), j = (int)(idx - (size_t)i * m);
+                bits = visit(bits, idx, i, j);
+                ((uint32_t*)scores)[idx] = bits;
+            }
+            digit = digit_of(bits, idx);
+        }
+        spm_hist_add(s_hist, digit, lane);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < SPM_BINS; i += blockDim.x) {
@@ -385,14 +492,24 @@ spm_collect_kernel(const float* __restrict__ scores, int n, int m, SpmState* sta
     const unsigned int k_eff = state->k_eff;
     const size_t total = (size_t)n * m;
     if (k_eff > 0) {
-        for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-            const uint32_t bits = ((const uint32_t*)scores)[idx];
-            if (bits == SPM_MASKED) continue;
+        auto take = [&](uint32_t bits, size_t idx) {
+            if (bits == SPM_MASKED) return;
             const unsigned long long key = spm_key(bits, (uint32_t)idx);
             if (key >= threshold) {
                 const unsigned int pos = atomicAdd(&state->list_count, 1u);
                 if (pos < (unsigned int)num_corr) list[pos] = key;
             }
+        };
+        const size_t quads = total >> 2;
+        const uint4* q4 = (const uint4*)scores;
+        for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < quads; q += (size_t)gridDim.x * blockDim.x) {
+            const uint4 v = q4[q];
+            const size_t idx = q << 2;
+            take(v.x, idx), take(v.y, idx + 1), take(v.z, idx + 2), take(v.w, idx + 3);
+        }
+        if (blockIdx.x == 0 && threadIdx.x < (total & 3)) {
+            const size_t idx = (quads << 2) + threadIdx.x;
+            take(((const uint32_t*)scores)[idx], idx);
         }
     }
     __threadfence();
@@ -465,30 +582,50 @@ extern "C" int geotx_superpoint_matching(const float* ref_feats, const float* sr
                     (uintptr_t)score_matrix) & 15) == 0,
                   "geotx_superpoint_matching: feature / matrix pointers must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
+#ifdef SPM_DBG_STOP
+    const char* stop_env = getenv("GEOTX_SPM_STOP_AFTER");
+    int stop_after = stop_env ? atoi(stop_env) : 100, launched = 0;
+#define SPM_STEP() do { if (++launched >= stop_after) return launch_status("geotx_superpoint_matching"); } while (0)
+#else
+#define SPM_STEP() do { } while (0)
+#endif
     SpmWorkspace w = spm_layout(workspace, n, m, d, num_corr);
     float* ref_unit = ref_unit_out ? ref_unit_out : w.ref_unit;
     float* src_unit = src_unit_out ? src_unit_out : w.src_unit;
     float* matrix = score_matrix ? score_matrix : w.scores;
-    const int tiles_n = (n + SPM_TILE - 1) / SPM_TILE, tiles_m = (m + SPM_TILE - 1) / SPM_TILE;
+    // 128 x 128 tiles (64 accumulators per thread) once they fill the 148 SMs about twice, else 64 x 64
+    const bool big_tile = (long long)((n + 127) / 128) * ((m + 127) / 128) >= SPM_BIG_TILE_MIN_CTAS;
+    const int tile = big_tile ? 128 : SPM_TILE;
+    const int tiles_n = (n + tile - 1) / tile, tiles_m = (m + tile - 1) / tile;
     const int prep_blocks = normalize ? (n + m + 7) / 8 : 1;
     spm_prepare_kernel<<<prep_blocks, 256, 0, st>>>(ref_feats, src_feats, n, m, d, normalize, ref_unit, src_unit, w.state,
                                                     w.hist);
+    SPM_STEP();
     const float* a = normalize ? ref_unit : ref_feats;
     const float* b = normalize ? src_unit : src_feats;
-    spm_scores_kernel<<<dim3(tiles_m, tiles_n), 256, 0, st>>>(a, b, n, m, d, ref_keep, src_keep, dual_normalization,
-                                                              matrix, w.row_part, w.col_part);
+    if (big_tile)
+        spm_scores_kernel<8, 8, 16><<<dim3(tiles_m, tiles_n), 256, 0, st>>>(a, b, n, m, d, ref_keep, src_keep, dual_normalization,
+                                                                        matrix, w.row_part, w.col_part);
+    else
+        spm_scores_kernel<4, 4, SPM_SMALL_KC><<<dim3(tiles_m, tiles_n), 256, 0, st>>>(a, b, n, m, d, ref_keep, src_keep, dual_normalization,
+                                                                        matrix, w.row_part, w.col_part);
+    SPM_STEP();
     spm_sums_kernel<<<(n + m + 255) / 256, 256, 0, st>>>(w.row_part, w.col_part, n, m, tiles_n, tiles_m,
                                                          dual_normalization, ref_keep, src_keep, num_corr, w.row_sum,
                                                          w.col_sum, w.state);
+    SPM_STEP();
     const size_t total = (size_t)n * m;
-    int scan_blocks = (int)((total + 256 * 8 - 1) / (256 * 8));  // ~8 entries per thread
-    if (scan_blocks > 148 * 8) scan_blocks = 148 * 8;
+    int scan_blocks = (int)((total + 256 * 8 - 1) / (256 * 8));  // two 16-byte accesses per thread
+    if (scan_blocks > SPM_SCAN_MAX_CTAS) scan_blocks = SPM_SCAN_MAX_CTAS;
     if (scan_blocks < 1) scan_blocks = 1;
     spm_pass_kernel<true><<<scan_blocks, 256, 0, st>>>(matrix, n, m, dual_normalization, w.row_sum, w.col_sum, ref_keep,
                                                        src_keep, 0, w.state, w.hist);
-    for (int pass = 1; pass < SPM_PASSES; ++pass)
+    SPM_STEP();
+    for (int pass = 1; pass < SPM_PASSES; ++pass) {
         spm_pass_kernel<false><<<scan_blocks, 256, 0, st>>>(matrix, n, m, dual_normalization, w.row_sum, w.col_sum,
                                                             ref_keep, src_keep, pass, w.state, w.hist);
+        SPM_STEP();
+    }
     int sort_size = 1;
     while (sort_size < num_corr) sort_size <<= 1;
     spm_collect_kernel<<<scan_blocks, 256, sizeof(unsigned long long) * sort_size, st>>>(
