@@ -229,6 +229,69 @@ def time_matching(pkg, outputs, num_corr=256, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
+def _graph_time_us(once, calls, replays):
+    """`calls` invocations captured in one CUDA graph, `replays` replays between two CUDA events; us per invocation."""
+    import torch
+    once()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(calls):
+            keep = once()
+    g.replay()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(replays):
+        g.replay()
+    b.record()
+    torch.cuda.synchronize()
+    del keep
+    return a.elapsed_time(b) * 1e3 / (calls * replays)
+
+
+def time_partition(pkg, shape, num_nodes, calls=10, replays=5):
+    """geotx_point_to_node_partition (4 kernels) for BOTH clouds of a pair (model.py:98-103) on
+    synthetic fine clouds; microseconds per pair."""
+    import torch
+    try:
+        K, ppn = (128, 24) if shape == 'kitti' else (64, 16)
+        clouds = [tuple(t.cuda() for t in pkg.synth.make_partition_inputs(shape, num_nodes, ppn, seed=pkg.synth.SEED + s))
+                  for s in (0, 1)]
+
+        def once():
+            return [pkg.ops.point_to_node_partition(p, q, K, return_points=True) for p, q in clouds]
+        us = _graph_time_us(once, calls, replays)
+        N = clouds[0][0].shape[0]
+        return {'us_per_pair': us, 'points_per_cloud': N, 'nodes_per_cloud': num_nodes, 'point_limit': K,
+                'kernels_per_call': 4, 'calls_per_pair': 2, 'dtype': 'f32 distances, u64 keys',
+                'distance_evals_per_s': 2.0 * N * num_nodes / (us * 1e-6),
+                'timing': f'{calls} pairs captured in one CUDA graph, {replays} replays, CUDA events'}
+    except Exception as exc:
+        return {'error': f'{type(exc).__name__}: {exc}'}
+
+
+def time_transport(pkg, shape, calls=10, replays=5):
+    """geotx_log_optimal_transport (one kernel, 100 iterations inside) on the 256 patch score
+    matrices of a pair (model.py:184-189); microseconds per pair."""
+    import torch
+    try:
+        K = 128 if shape == 'kitti' else 64
+        scores, rm, cm = (t.cuda() for t in pkg.synth.make_patch_scores(256, K, K, 256, seed=pkg.synth.SEED))
+        alpha = torch.ones((), device='cuda')
+
+        def once():
+            return pkg.ops.log_optimal_transport(scores, alpha, 100, rm, cm)
+        us = _graph_time_us(once, calls, replays)
+        exps = 256 * 100 * 2 * (K + 1) * (K + 1)
+        return {'us_per_pair': us, 'problems': 256, 'rows': K + 1, 'cols': K + 1, 'iterations': 100, 'kernels_per_call': 1,
+                'dtype': 'f32', 'exp_per_s': exps / (us * 1e-6),
+                'mufu_frac': exps / (us * 1e-6) / (16 * 148 * 1.965e9),
+                'timing': f'{calls} calls captured in one CUDA graph, {replays} replays, CUDA events'}
+    except Exception as exc:
+        return {'error': f'{type(exc).__name__}: {exc}'}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -365,6 +428,9 @@ def run_b200(args):
         # ---- next row: the path's consumer (F.normalize + SuperPointMatching), timed alone on the
         #      outputs of the last pair; not part of `value` ----
         matching = time_matching(pkg, last) if world == 1 else None
+        shape_name = WORKLOADS[args.workload][0]
+        partition = time_partition(pkg, shape_name, n) if world == 1 else None
+        transport = time_transport(pkg, shape_name) if world == 1 else None
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -404,7 +470,8 @@ def run_b200(args):
             'pair_tflops': flops_pair(n, m, cfg) / 1e12,
             'pair_tensor_frac': flops_pair(n, m, cfg) * value / world / 1e12 / peaks['tensor_sustained'],
             'clocks': clocks,
-            'next_rows': {'superpoint_matching': matching},
+            'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
+                          'log_optimal_transport': transport},
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)

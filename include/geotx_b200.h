@@ -29,6 +29,7 @@ extern "C" {
 #define GEOTX_E_CUDA (-2)  /* CUDA runtime error (text in geotx_last_error) */
 
 #define GEOTX_MAX_ANGLE_K 7
+#define GEOTX_MAX_POINT_LIMIT 8192 /* geotx_point_to_node_partition: points kept per node */
 
 /* dtype tags for buffers that may be stored in either precision */
 #define GEOTX_F32 0
@@ -155,6 +156,38 @@ int geotx_superpoint_matching(const float* ref_feats, const float* src_feats, in
                               float* src_unit_out, int dual_normalization, int num_corr, int64_t* ref_idx_out,
                               int64_t* src_idx_out, float* score_out, int32_t* count_out, float* score_matrix,
                               void* workspace, void* stream);
+
+/* Point-to-node partition in front of the path: modules/ops/pointcloud_partition.py:61-107
+ * (`point_to_node_partition`, called at experiments/<cfg>/model.py:98-103) plus the patch gather of model.py:105-108.
+ * Every point is assigned to its nearest node (pairwise_distance(nodes, points), ops/pairwise_distance.py:22-30, same
+ * fp32 operation order; argmin over nodes); every node keeps the point_limit nearest of ITS OWN points, ascending.
+ *   points f32 [num_points,3], nodes f32 [num_nodes,3]
+ *   point_to_node    i64 [num_points]           index of the nearest node
+ *   node_sizes       i64 [num_nodes] or NULL    points assigned to each node (return_count=True)
+ *   node_masks       u8  [num_nodes]            1 if the node owns at least one point
+ *   node_knn_indices i64 [num_nodes,point_limit] own points by ascending distance, then the sentinel num_points
+ *   node_knn_masks   u8  [num_nodes,point_limit] 1 for real entries
+ *   node_knn_points  f32 [num_nodes,point_limit,3] or NULL: points[node_knn_indices] with zeros at the sentinel
+ *   workspace        geotx_p2n_workspace_bytes(...) bytes, 256-byte aligned
+ * Equal distances are ordered by the smaller index (torch.min / torch.topk leave that order unspecified).
+ * Like torch.topk, point_limit > num_points is an error.  point_limit <= GEOTX_MAX_POINT_LIMIT. */
+int64_t geotx_p2n_workspace_bytes(int num_points, int num_nodes, int point_limit);
+int geotx_point_to_node_partition(const float* points, int num_points, const float* nodes, int num_nodes,
+                                  int point_limit, int64_t* point_to_node, int64_t* node_sizes, uint8_t* node_masks,
+                                  int64_t* node_knn_indices, uint8_t* node_knn_masks, float* node_knn_points,
+                                  void* workspace, void* stream);
+
+/* Optimal transport behind the coarse matching: modules/sinkhorn/learnable_sinkhorn.py:13-66
+ * (`LearnableLogOptimalTransport.forward`, called at experiments/<cfg>/model.py:187-189): scores padded with a dustbin
+ * row and column holding alpha, masked rows / columns filled with -inf_value, num_iterations log-domain Sinkhorn
+ * iterations (two logsumexp each), result (scores + u + v) - norm.  One CTA per problem; the padded matrix stays in
+ * shared memory for the whole loop.
+ *   scores f32 [B,M,N]; row_masks u8 [B,M] / col_masks u8 [B,N] or NULL, nonzero = VALID (the reference's masks);
+ *   alpha f32 [1] (device: the module's parameter); out f32 [B,M+1,N+1].
+ * (M+1) x (N+1) must fit shared memory (about 230 x 230).  fp32 arithmetic in the reference's operation order. */
+int geotx_log_optimal_transport(const float* scores, const uint8_t* row_masks, const uint8_t* col_masks,
+                                const float* alpha, int num_iterations, float inf_value, int B, int M, int N,
+                                float* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -62,3 +62,44 @@ void geotx_oracle_knn(const float* points, int n, int k, float sigma_d, int64_t*
         for (int q = 0; q < k; ++q) knn_out[(int64_t)i * k + q] = bi[q + 1];
     }
 }
+
+/* SURVEY.md 8(f)-2 -- /root/reference/geotransformer/modules/ops/pointcloud_partition.py:82-98, torch-independent:
+ * d2(node, point) with x = node, y = point (pairwise_distance(nodes, points)); every point goes to the node with the
+ * smallest d2 (first one on ties); every node lists its own points by ascending (d2, index), at most point_limit of
+ * them, then the sentinel num_points.
+ *   point_to_node: N int64; node_sizes: M int64; knn_indices: M*K int64; knn_masks: M*K bytes; best_d2: N floats scratch */
+void geotx_oracle_point_to_node(const float* points, int N, const float* nodes, int M, int K, int64_t* point_to_node,
+                                int64_t* node_sizes, int64_t* knn_indices, uint8_t* knn_masks, float* best_d2) {
+    for (int m = 0; m < M; ++m) node_sizes[m] = 0;
+    for (int p = 0; p < N; ++p) {
+        float best = INFINITY;
+        int bi = 0;
+        for (int m = 0; m < M; ++m) {
+            float d = geotx_oracle_sqdist(nodes + 3 * m, points + 3 * p);
+            if (d < best) { best = d; bi = m; }
+        }
+        point_to_node[p] = bi;
+        best_d2[p] = best;
+        node_sizes[bi]++;
+    }
+    for (int m = 0; m < M; ++m) {
+        int cnt = 0;
+        int64_t* idx = knn_indices + (int64_t)m * K;
+        for (int p = 0; p < N; ++p) {
+            if (point_to_node[p] != m) continue;
+            /* insertion into the sorted list of the K smallest; p ascends, strict < keeps the smaller index first */
+            int pos = cnt;
+            while (pos > 0 && best_d2[p] < best_d2[idx[pos - 1]]) --pos;
+            if (pos < K) {
+                int last = cnt < K ? cnt : K - 1;
+                for (int q = last; q > pos; --q) idx[q] = idx[q - 1];
+                idx[pos] = p;
+                if (cnt < K) ++cnt;
+            }
+        }
+        for (int q = 0; q < K; ++q) {
+            knn_masks[(int64_t)m * K + q] = q < cnt;
+            if (q >= cnt) idx[q] = N;
+        }
+    }
+}

@@ -8,12 +8,14 @@ from .modules import (  # noqa: F401
     AttentionLayer, AttentionOutput, GeometricStructureEmbedding, GeometricTransformer, GraphedGeometricTransformer, PipelinedGeometricTransformer,
     MultiHeadAttention,
     RPEAttentionLayer, RPEConditionalTransformer, RPEMultiHeadAttention, RPETransformerLayer,
-    SinusoidalPositionalEmbedding, SuperPointMatching, TransformerLayer, build_act_layer, build_dropout_layer)
+    SinusoidalPositionalEmbedding, SuperPointMatching, TransformerLayer, build_act_layer, build_dropout_layer,
+    LearnableLogOptimalTransport, point_to_node_partition)
 
 __all__ = [
     'GeometricTransformer', 'GraphedGeometricTransformer', 'PipelinedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
-    'AttentionOutput', 'SinusoidalPositionalEmbedding', 'SuperPointMatching', 'ops', 'synth',
+    'AttentionOutput', 'SinusoidalPositionalEmbedding', 'SuperPointMatching', 'LearnableLogOptimalTransport',
+    'point_to_node_partition', 'ops', 'synth',
 ]
 
 _REFERENCE_PATCHES = (
@@ -24,6 +26,10 @@ _REFERENCE_PATCHES = (
     ('geotransformer.modules.geotransformer.superpoint_matching', ('SuperPointMatching',)),
     ('geotransformer.modules.transformer', ('RPEConditionalTransformer', 'RPETransformerLayer', 'TransformerLayer',
                                             'SinusoidalPositionalEmbedding')),
+    ('geotransformer.modules.ops.pointcloud_partition', ('point_to_node_partition',)),
+    ('geotransformer.modules.ops', ('point_to_node_partition',)),
+    ('geotransformer.modules.sinkhorn.learnable_sinkhorn', ('LearnableLogOptimalTransport',)),
+    ('geotransformer.modules.sinkhorn', ('LearnableLogOptimalTransport',)),
 )
 _saved = {}
 

@@ -32,6 +32,9 @@ SIGNATURES = {
     'geotx_add_layernorm': (_i, [_p, _p, _p, _p, _i64, _i, _f, _p, _p]),
     'geotx_spm_workspace_bytes': (_i64, [_i, _i, _i, _i]),
     'geotx_superpoint_matching': (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
+    'geotx_p2n_workspace_bytes': (_i64, [_i, _i, _i]),
+    'geotx_point_to_node_partition': (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    'geotx_log_optimal_transport': (_i, [_p, _p, _p, _p, _i, _f, _i, _i, _i, _p, _p]),
 }
 
 GEOTX_F32 = 0
@@ -40,7 +43,8 @@ GEOTX_F16 = 2
 
 # kernels each entry point enqueues (bench.py's gpu_launches is counted from this)
 KERNELS_PER_CALL = {'geotx_gse_knn': 2,  # pack_points + knn
-                    'geotx_superpoint_matching': 10}  # prepare, scores, sums, 6 select passes, collect
+                    'geotx_superpoint_matching': 10,  # prepare, scores, sums, 6 select passes, collect
+                    'geotx_point_to_node_partition': 4}  # assign, offsets, scatter, select
 
 _lib = None
 launch_count = 0  # hand-written kernels launched through this binding so far

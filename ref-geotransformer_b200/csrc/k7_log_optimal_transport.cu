@@ -1,0 +1,186 @@
+// K7: LearnableLogOptimalTransport -- SuperGlue-style log-domain Sinkhorn with a dustbin row and
+// column, one CTA per problem, the whole iteration loop inside one launch.
+//
+// Replaces /root/reference/geotransformer/modules/sinkhorn/learnable_sinkhorn.py:13-66 (called from
+// experiments/*/model.py:187-189 on (256, 64, 64) / (256, 128, 128) patch score matrices with 100 iterations): the
+// reference issues two torch.logsumexp (plus broadcast adds) per iteration, about a thousand launches per pair, each a
+// pass over a (B, M+1, N+1) tensor in HBM.  Here the padded matrix lives in shared memory for the whole loop and HBM
+// sees the scores once and the result once.
+//
+// Arithmetic follows the reference operation by operation in fp32 (so the -1e12 "masked" entries absorb exactly as
+// they do there): x = S + v, m = max x, lse = log(sum exp(x - m)) + m, u = log_mu - lse; same for the columns;
+// out = ((S + u) + v) - norm.  exp is ex2.approx on the MUFU pipe (2 ulp), log is logf.
+//
+// Layout: padded matrix rows x cols (= M+1, N+1) with a row stride == 4 (mod 32) words, which makes BOTH passes
+// bank-conflict free with a 4-lane-per-row / 8-lane-per-column split of the warp:
+//   row pass     lane = l + 4*ii handles row r0+ii, columns l, l+4, ...   bank = 4*ii + l + const
+//   column pass  lane = jj + 4*rr handles column c0+jj, rows rr, rr+8, ... bank = 4*rr + jj + const
+#include "geotx_common.cuh"
+
+namespace geotx {
+
+constexpr int LOT_NREG = 34;  // x values a lane keeps in registers between the max and the sum (else re-read)
+
+__device__ __forceinline__ float lot_exp(float x) {  // exp(x), x <= 0
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+    return r;
+}
+
+// log-sum-exp over one line of the matrix, computed by G cooperating lanes (lane index g in the group):
+// element e = g + G*t lives at line[e * estride] and gets add[e] added first.
+template <int G>
+__device__ __forceinline__ float line_lse(const float* __restrict__ line, int estride, const float* __restrict__ add,
+                                          int len, int g) {
+    const int cnt = (len - g + G - 1) / G;  // elements of this lane (len >= G is not required)
+    float x[LOT_NREG];
+    float m = -__int_as_float(0x7f800000);
+    if (cnt <= LOT_NREG) {
+#pragma unroll
+        for (int t = 0; t < LOT_NREG; ++t) {
+            if (t < cnt) {
+                const int e = g + G * t;
+                x[t] = __fadd_rn(line[e * estride], add[e]);
+                m = fmaxf(m, x[t]);
+            }
+        }
+    } else {
+        for (int t = 0; t < cnt; ++t) {
+            const int e = g + G * t;
+            m = fmaxf(m, __fadd_rn(line[e * estride], add[e]));
+        }
+    }
+#pragma unroll
+    for (int off = 1; off < G; off <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off * (G == 4 ? 1 : 4)));
+    // torch.logsumexp replaces an infinite maximum by 0 before subtracting (ReduceOps: where(|max| == inf, 0, max))
+    const float ms = (fabsf(m) == __int_as_float(0x7f800000)) ? 0.f : m;
+    float s = 0.f;
+    if (cnt <= LOT_NREG) {
+#pragma unroll
+        for (int t = 0; t < LOT_NREG; ++t)
+            if (t < cnt) s += lot_exp(__fsub_rn(x[t], ms));
+    } else {
+        for (int t = 0; t < cnt; ++t) {
+            const int e = g + G * t;
+            s += lot_exp(__fsub_rn(__fadd_rn(line[e * estride], add[e]), ms));
+        }
+    }
+#pragma unroll
+    for (int off = 1; off < G; off <<= 1) s += __shfl_xor_sync(0xffffffffu, s, off * (G == 4 ? 1 : 4));
+    return __fadd_rn(logf(s), ms);
+}
+
+constexpr int LOT_MAX_WARPS = 20;  // 640 threads: <= 102 registers each, no spills with LOT_NREG cached values
+
+__global__ void __launch_bounds__(LOT_MAX_WARPS * 32)
+log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __restrict__ row_masks,
+                             const uint8_t* __restrict__ col_masks, const float* __restrict__ alpha_p, int iterations,
+                             float inf, int M, int N, int stride, float* __restrict__ out) {
+    extern __shared__ float smem[];
+    const int rows = M + 1, cols = N + 1;
+    float* S = smem;                    // rows x stride
+    float* u = S + (size_t)rows * stride;
+    float* v = u + rows;
+    float* log_mu = v + cols;
+    float* log_nu = log_mu + rows;
+    __shared__ int valid_s[2];
+    const int b = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarps = blockDim.x >> 5;
+    const float alpha = __ldg(alpha_p);
+    const uint8_t* rm = row_masks ? row_masks + (size_t)b * M : nullptr;  // nonzero = valid
+    const uint8_t* cm = col_masks ? col_masks + (size_t)b * N : nullptr;
+
+    if (tid < 2) valid_s[tid] = 0;
+    __syncthreads();
+    // learnable_sinkhorn.py:46,48: num_valid_row / num_valid_col
+    int cr = 0, cc = 0;
+    for (int i = tid; i < M; i += blockDim.x) cr += rm ? (rm[i] != 0) : 1;
+    for (int j = tid; j < N; j += blockDim.x) cc += cm ? (cm[j] != 0) : 1;
+    cr = __reduce_add_sync(0xffffffffu, cr);
+    cc = __reduce_add_sync(0xffffffffu, cc);
+    if (lane == 0) { atomicAdd(&valid_s[0], cr); atomicAdd(&valid_s[1], cc); }
+    // :41-44 padded scores: [scores | alpha] over [alpha ... alpha], masked rows / columns filled with -inf
+    const float* sb = scores + (size_t)b * M * N;
+    for (int i = wid; i < rows; i += nwarps) {
+        const bool rmask = i < M && rm && rm[i] == 0;
+        for (int j = lane; j < cols; j += 32) {
+            const bool cmask = j < N && cm && cm[j] == 0;
+            float val = (i < M && j < N) ? __ldg(sb + (size_t)i * N + j) : alpha;
+            if (rmask || cmask) val = -inf;
+            S[i * stride + j] = val;
+        }
+    }
+    __syncthreads();
+    const float nvr = (float)valid_s[0], nvc = (float)valid_s[1];
+    const float norm = -logf(__fadd_rn(nvr, nvc));  // :48
+    // :50-58 log_mu / log_nu; u = v = 0 (:15)
+    for (int i = tid; i < rows; i += blockDim.x) {
+        float val = i < M ? norm : __fadd_rn(logf(nvc), norm);
+        if (i < M && rm && rm[i] == 0) val = -inf;
+        log_mu[i] = val;
+        u[i] = 0.f;
+    }
+    for (int j = tid; j < cols; j += blockDim.x) {
+        float val = j < N ? norm : __fadd_rn(logf(nvr), norm);
+        if (j < N && cm && cm[j] == 0) val = -inf;
+        log_nu[j] = val;
+        v[j] = 0.f;
+    }
+    __syncthreads();
+
+    const int l4 = lane & 3, i8 = lane >> 2;  // row pass: 8 rows per warp, 4 lanes each
+    const int j4 = lane & 3, r8 = lane >> 2;  // column pass: 4 columns per warp, 8 lanes each
+    for (int it = 0; it < iterations; ++it) {
+        // :17  u = log_mu - logsumexp(scores + v, dim=2)
+        for (int r0 = wid * 8; r0 < rows; r0 += nwarps * 8) {
+            const int i = r0 + i8;
+            const bool act = i < rows;
+            const float lse = line_lse<4>(S + (size_t)(act ? i : 0) * stride, 1, v, act ? cols : 0, l4);
+            if (act && l4 == 0) u[i] = __fsub_rn(log_mu[i], lse);
+        }
+        __syncthreads();
+        // :18  v = log_nu - logsumexp(scores + u, dim=1)
+        for (int c0 = wid * 4; c0 < cols; c0 += nwarps * 4) {
+            const int j = c0 + j4;
+            const bool act = j < cols;
+            const float lse = line_lse<8>(S + (act ? j : 0), stride, u, act ? rows : 0, r8);
+            if (act && r8 == 0) v[j] = __fsub_rn(log_nu[j], lse);
+        }
+        __syncthreads();
+    }
+    // :19, :61  (scores + u + v) - norm
+    float* ob = out + (size_t)b * rows * cols;
+    for (int i = wid; i < rows; i += nwarps) {
+        const float ui = u[i];
+        for (int j = lane; j < cols; j += 32)
+            ob[(size_t)i * cols + j] = __fsub_rn(__fadd_rn(__fadd_rn(S[i * stride + j], ui), v[j]), norm);
+    }
+}
+
+}  // namespace geotx
+
+// ---- C ABI --------------------------------------------------------------------------------------------------
+#include "host_util.h"
+using namespace geotx;
+
+extern "C" int geotx_log_optimal_transport(const float* scores, const uint8_t* row_masks, const uint8_t* col_masks,
+                                           const float* alpha, int num_iterations, float inf, int B, int M, int N,
+                                           float* out, void* stream) {
+    GEOTX_REQUIRE(scores && alpha && out, "geotx_log_optimal_transport: null pointer");
+    GEOTX_REQUIRE(B > 0 && M > 0 && N > 0, "geotx_log_optimal_transport: bad sizes B=%d M=%d N=%d", B, M, N);
+    GEOTX_REQUIRE(num_iterations >= 0, "geotx_log_optimal_transport: num_iterations=%d", num_iterations);
+    const int rows = M + 1, cols = N + 1;
+    int stride = cols;
+    while ((stride & 31) != 4) ++stride;
+    const size_t smem = ((size_t)rows * stride + 2 * (size_t)rows + 2 * (size_t)cols) * sizeof(float);
+    GEOTX_REQUIRE(smem <= 227 * 1024, "geotx_log_optimal_transport: a (%d x %d) problem needs %zu bytes of shared "
+                  "memory (> 227 KB)", rows, cols, smem);
+    int rc = check_cuda(cudaFuncSetAttribute(log_optimal_transport_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem), "geotx_log_optimal_transport: shared memory");
+    if (rc) return rc;
+    int warps = max((rows + 7) / 8, (cols + 3) / 4);
+    warps = min(max(warps, 4), LOT_MAX_WARPS);  // more line groups than warps: the pass loops
+    log_optimal_transport_kernel<<<B, warps * 32, smem, (cudaStream_t)stream>>>(
+        scores, row_masks, col_masks, alpha, num_iterations, inf, M, N, stride, out);
+    return launch_status("geotx_log_optimal_transport");
+}

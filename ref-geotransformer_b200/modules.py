@@ -826,3 +826,31 @@ class SuperPointMatching(nn.Module):
         model.py:141-157 puts into output_dict['ref_feats_c'], ['src_feats_c'] and the node correspondences."""
         out, count = self._run(ref_feats, src_feats, ref_masks, src_masks, True)
         return out['ref_unit'], out['src_unit'], out['ref_idx'][:count], out['src_idx'][:count], out['scores'][:count]
+
+
+@torch.no_grad()
+def point_to_node_partition(points, nodes, point_limit, return_count=False):
+    """Drop-in for geotransformer/modules/ops/pointcloud_partition.py:61-107: same arguments, same
+    tuple, on `geotx_point_to_node_partition`."""
+    return ops.point_to_node_partition(points.contiguous(), nodes.contiguous(), point_limit, return_count)
+
+
+class LearnableLogOptimalTransport(nn.Module):
+    """Drop-in for geotransformer/modules/sinkhorn/learnable_sinkhorn.py:5-66: same constructor,
+    the same single `alpha` parameter (state_dict key `alpha`), same forward; all iterations in one launch of
+    `geotx_log_optimal_transport`.  Forward-only, like the rest of this package."""
+
+    def __init__(self, num_iterations, inf=1e12):
+        super().__init__()
+        self.num_iterations = num_iterations
+        self.register_parameter('alpha', torch.nn.Parameter(torch.tensor(1.0)))
+        self.inf = inf
+
+    def forward(self, scores, row_masks=None, col_masks=None):
+        _forward_only_guard(self, scores)
+        return ops.log_optimal_transport(scores.contiguous(), self.alpha.detach(), self.num_iterations,
+                                         None if row_masks is None else row_masks.contiguous(),
+                                         None if col_masks is None else col_masks.contiguous(), self.inf)
+
+    def __repr__(self):
+        return self.__class__.__name__ + '(num_iterations={})'.format(self.num_iterations)

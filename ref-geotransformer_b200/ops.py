@@ -264,3 +264,61 @@ def superpoint_matching(ref_feats, src_feats, num_correspondences, dual_normaliz
               _p(out['ref_idx']), _p(out['src_idx']), _p(out['scores']), _p(out['count']), _p(out.get('matrix')),
               _p(work), _stream())
     return out
+
+
+def point_to_node_partition(points, nodes, point_limit, return_count=False, return_points=False):
+    """modules/ops/pointcloud_partition.py:61-107 on the hand-written path (no (M,N) matrix in HBM).
+
+    points (N,3), nodes (M,3) fp32.  Returns the reference's tuple
+      (point_to_node int64 (N,), [node_sizes int64 (M,) if return_count,] node_masks bool (M,),
+       node_knn_indices int64 (M,K), node_knn_masks bool (M,K))
+    and, with return_points=True (extension), node_knn_points (M,K,3) = padded_points[node_knn_indices]
+    (model.py:105-108) as a last element.  No host synchronisation."""
+    _check(points, 'points', torch.float32, 2)
+    _check(nodes, 'nodes', torch.float32, 2)
+    if points.shape[1] != 3 or nodes.shape[1] != 3:
+        raise RuntimeError(f'points and nodes must be (*, 3), got {tuple(points.shape)} and {tuple(nodes.shape)}')
+    N, M, K = points.shape[0], nodes.shape[0], int(point_limit)
+    if K > N:  # torch.topk's own message (pointcloud_partition.py:93)
+        raise RuntimeError(f'selected index k out of range (point_limit={K} > {N} points)')
+    lib = _abi.load()
+    nbytes = lib.geotx_p2n_workspace_bytes(N, M, K)
+    if nbytes <= 0:
+        raise RuntimeError(f'point_to_node_partition: bad sizes points={N} nodes={M} point_limit={K}')
+    dev = points.device
+    work = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    point_to_node = torch.empty(N, dtype=torch.int64, device=dev)
+    node_sizes = torch.empty(M, dtype=torch.int64, device=dev) if return_count else None
+    node_masks = torch.empty(M, dtype=torch.bool, device=dev)
+    knn_indices = torch.empty(M, K, dtype=torch.int64, device=dev)
+    knn_masks = torch.empty(M, K, dtype=torch.bool, device=dev)
+    knn_points = torch.empty(M, K, 3, dtype=torch.float32, device=dev) if return_points else None
+    _abi.call('geotx_point_to_node_partition', _p(points), N, _p(nodes), M, K, _p(point_to_node), _p(node_sizes),
+              _p(node_masks), _p(knn_indices), _p(knn_masks), _p(knn_points), _p(work), _stream())
+    out = (point_to_node,) + ((node_sizes,) if return_count else ()) + (node_masks, knn_indices, knn_masks)
+    return out + ((knn_points,) if return_points else ())
+
+
+def log_optimal_transport(scores, alpha, num_iterations, row_masks=None, col_masks=None, inf=1e12):
+    """modules/sinkhorn/learnable_sinkhorn.py:21-63 in one launch: scores (B,M,N) fp32, alpha a 1-element fp32 CUDA
+    tensor (the module's parameter), masks bool (True = valid) or None -> (B,M+1,N+1) fp32."""
+    _check(scores, 'scores', torch.float32, 3)
+    _check(alpha, 'alpha', torch.float32)
+    if alpha.numel() != 1:
+        raise RuntimeError(f'alpha must hold one element, got shape {tuple(alpha.shape)}')
+    B, M, N = scores.shape
+    masks = []
+    for t, name, cols in ((row_masks, 'row_masks', M), (col_masks, 'col_masks', N)):
+        if t is None:
+            masks.append(None)
+            continue
+        _check(t, name, torch.bool, 2)
+        if tuple(t.shape) != (B, cols):
+            raise RuntimeError(f'{name} must be {(B, cols)}, got {tuple(t.shape)}')
+        masks.append(t.view(torch.uint8))
+    out = torch.empty(B, M + 1, N + 1, dtype=torch.float32, device=scores.device)
+    if B == 0:
+        return out
+    _abi.call('geotx_log_optimal_transport', _p(scores), _p(masks[0]), _p(masks[1]), _p(alpha), int(num_iterations),
+              float(inf), B, M, N, _p(out), _stream())
+    return out

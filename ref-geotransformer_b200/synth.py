@@ -75,3 +75,38 @@ def make_tie_free_pair(shape='3dmatch', n=1024, m=None, seed=SEED, input_dim=Non
         if tie_free(out[0][0], k) and tie_free(out[1][0], k):
             return out + (s,)
     raise RuntimeError('no tie-free seed found')
+
+
+def make_fine_cloud(shape, nodes, points_per_node, gen):
+    """Fine-level points for the point-to-node partition: `points_per_node` points scattered around
+    every node (sigma = half the node spacing, so patches overlap and sizes vary), shuffled.  nodes (M,3) -> (N,3).
+    3DMatch: stage-2 voxels 0.05 m under stage-4 nodes 0.2 m => about 16 points per node (config.py:79)."""
+    m = nodes.shape[0]
+    spacing = {'3dmatch': 0.3, 'kitti': 4.8, 'modelnet': 0.1}[shape]
+    n = m * points_per_node
+    owner = torch.arange(n) % m
+    pts = nodes[owner] + torch.randn(n, 3, generator=gen) * (0.5 * spacing)
+    return pts[torch.randperm(n, generator=gen)].contiguous()
+
+
+def make_partition_inputs(shape='3dmatch', num_nodes=1024, points_per_node=16, seed=SEED):
+    """Returns (points (N,3), nodes (M,3)) fp32 CPU for point_to_node_partition."""
+    gen = torch.Generator().manual_seed(seed)
+    nodes = make_cloud(shape, num_nodes, gen)
+    return make_fine_cloud(shape, nodes, points_per_node, gen), nodes.contiguous()
+
+
+def make_patch_scores(num_patches=256, rows=64, cols=64, dim=256, seed=SEED, valid_frac=0.8):
+    """Inputs of the optimal-transport step (experiments/*/model.py:184-189): patch feature products / sqrt(dim) and
+    the patches' validity masks (every patch keeps at least one valid point, as the partition guarantees).
+    Returns scores (P,rows,cols) fp32, row_masks (P,rows) bool, col_masks (P,cols) bool."""
+    gen = torch.Generator().manual_seed(seed)
+    a = torch.randn(num_patches, rows, dim, generator=gen)
+    b = a[:, torch.randperm(rows, generator=gen)][:, :cols] if cols <= rows else torch.randn(num_patches, cols, dim, generator=gen)
+    b = b + 0.5 * torch.randn(num_patches, cols, dim, generator=gen)
+    scores = torch.einsum('bnd,bmd->bnm', a, b) / dim ** 0.5
+    nr = (torch.rand(num_patches, generator=gen) * valid_frac * rows).long() + max(1, int((1 - valid_frac) * rows))
+    nc = (torch.rand(num_patches, generator=gen) * valid_frac * cols).long() + max(1, int((1 - valid_frac) * cols))
+    row_masks = torch.arange(rows)[None, :] < nr.clamp(1, rows)[:, None]  # valid points come first (sorted patches)
+    col_masks = torch.arange(cols)[None, :] < nc.clamp(1, cols)[:, None]
+    return scores.contiguous(), row_masks.contiguous(), col_masks.contiguous()
