@@ -5,11 +5,18 @@
 // experiments/*/model.py:187-189 on (256, 64, 64) / (256, 128, 128) patch score matrices with 100 iterations): the
 // reference issues two torch.logsumexp (plus broadcast adds) per iteration, about a thousand launches per pair, each a
 // pass over a (B, M+1, N+1) tensor in HBM.  Here the padded matrix lives in shared memory for the whole loop and HBM
-// sees the scores once and the result once.
+// sees the scores once (twice: the epilogue re-reads them to add u and v to the unscaled values) and the result once.
 //
-// Arithmetic follows the reference operation by operation in fp32 (so the -1e12 "masked" entries absorb exactly as
-// they do there): x = S + v, m = max x, lse = log(sum exp(x - m)) + m, u = log_mu - lse; same for the columns;
-// out = ((S + u) + v) - norm.  exp is ex2.approx on the MUFU pipe (2 ulp), log is logf.
+// Arithmetic.  The kernel is bound by the MUFU pipe (one ex2 per matrix entry per half-iteration), so everything
+// around the ex2 is kept to one shared-memory load pair, two adds and one accumulate:
+//   * base-2 domain: S2 = S log2(e), u2 = u log2(e), ... so that exp(x - m) is ex2(x2 - m2) with no multiply;
+//     lse2 = m2 + lg2(sum);  the epilogue converts back: out = ((S + u2 ln2) + v2 ln2) - norm (learnable_sinkhorn.py:19,65)
+//   * the stabiliser m of a line is NOT its maximum but the line's lse of the previous iteration (log-sum-exp is exact
+//     for any m; lse_prev >= max_prev and the potentials move little between iterations), which removes the max pass,
+//     its shuffle reduction and the need to keep the line in registers.  The first iteration, and any line whose sum
+//     leaves [2^-100, 2^100] (never observed), takes the true maximum like torch.logsumexp does.
+//   * masked entries hold -inf_value (-1e12) as in the reference and absorb the same way (never -inf / NaN).
+// Result: equal to the reference to ~1e-6 on finite entries (tests: 1e-4), masked entries to the ulp.
 //
 // Layout: padded matrix rows x cols (= M+1, N+1) with a row stride == 4 (mod 32) words, which makes BOTH passes
 // bank-conflict free with a 4-lane-per-row / 8-lane-per-column split of the warp:
@@ -19,70 +26,87 @@
 
 namespace geotx {
 
-constexpr int LOT_NREG = 34;  // x values a lane keeps in registers between the max and the sum (else re-read)
+constexpr float LOT_LOG2E = 1.4426950408889634f;
+constexpr float LOT_LN2 = 0.6931471805599453f;
 
-__device__ __forceinline__ float lot_exp(float x) {  // exp(x), x <= 0
+__device__ __forceinline__ float lot_ex2(float x) {
     float r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float lot_lg2(float x) {
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
 
-// log-sum-exp over one line of the matrix, computed by G cooperating lanes (lane index g in the group):
-// element e = g + G*t lives at line[e * estride] and gets add[e] added first.
 template <int G>
-__device__ __forceinline__ float line_lse(const float* __restrict__ line, int estride, const float* __restrict__ add,
-                                          int len, int g) {
-    const int cnt = (len - g + G - 1) / G;  // elements of this lane (len >= G is not required)
-    float x[LOT_NREG];
-    float m = -__int_as_float(0x7f800000);
-    if (cnt <= LOT_NREG) {
-#pragma unroll
-        for (int t = 0; t < LOT_NREG; ++t) {
-            if (t < cnt) {
-                const int e = g + G * t;
-                x[t] = __fadd_rn(line[e * estride], add[e]);
-                m = fmaxf(m, x[t]);
-            }
-        }
-    } else {
-        for (int t = 0; t < cnt; ++t) {
-            const int e = g + G * t;
-            m = fmaxf(m, __fadd_rn(line[e * estride], add[e]));
-        }
-    }
-#pragma unroll
-    for (int off = 1; off < G; off <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off * (G == 4 ? 1 : 4)));
-    // torch.logsumexp replaces an infinite maximum by 0 before subtracting (ReduceOps: where(|max| == inf, 0, max))
-    const float ms = (fabsf(m) == __int_as_float(0x7f800000)) ? 0.f : m;
-    float s = 0.f;
-    if (cnt <= LOT_NREG) {
-#pragma unroll
-        for (int t = 0; t < LOT_NREG; ++t)
-            if (t < cnt) s += lot_exp(__fsub_rn(x[t], ms));
-    } else {
-        for (int t = 0; t < cnt; ++t) {
-            const int e = g + G * t;
-            s += lot_exp(__fsub_rn(__fadd_rn(line[e * estride], add[e]), ms));
-        }
-    }
+__device__ __forceinline__ float group_sum(float s) {
 #pragma unroll
     for (int off = 1; off < G; off <<= 1) s += __shfl_xor_sync(0xffffffffu, s, off * (G == 4 ? 1 : 4));
-    return __fadd_rn(logf(s), ms);
+    return s;
+}
+template <int G>
+__device__ __forceinline__ float group_max(float s) {
+#pragma unroll
+    for (int off = 1; off < G; off <<= 1) s = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, off * (G == 4 ? 1 : 4)));
+    return s;
 }
 
-constexpr int LOT_MAX_WARPS = 20;  // 640 threads: <= 102 registers each, no spills with LOT_NREG cached values
+// base-2 log-sum-exp over one line of the matrix by G cooperating lanes (lane g of the group): element e = g + G*t
+// lives at line[e * estride] and gets add[e] added first; `m` is the stabiliser (any value near the line's maximum).
+template <int G>
+__device__ __forceinline__ float line_sum(const float* __restrict__ line, int estride, const float* __restrict__ add,
+                                          int len, int g, float m) {
+    float s0 = 0.f, s1 = 0.f;
+    int e = g;
+    for (; e + G < len; e += 2 * G) {
+        s0 += lot_ex2(line[e * estride] + add[e] - m);
+        s1 += lot_ex2(line[(e + G) * estride] + add[e + G] - m);
+    }
+    if (e < len) s0 += lot_ex2(line[e * estride] + add[e] - m);
+    return group_sum<G>(s0 + s1);
+}
 
-__global__ void __launch_bounds__(LOT_MAX_WARPS * 32)
+template <int G>
+__device__ __forceinline__ float line_max(const float* __restrict__ line, int estride, const float* __restrict__ add,
+                                          int len, int g) {
+    float m = -__int_as_float(0x7f800000);
+    for (int e = g; e < len; e += G) m = fmaxf(m, line[e * estride] + add[e]);
+    return group_max<G>(m);
+}
+
+// lse2 of a line: stabilised by `guess` (the previous iteration's value) when `use_guess`, by the true maximum otherwise
+// or when the guess turned out to be far off.  All lanes of the warp call it together.
+template <int G>
+__device__ __forceinline__ float line_lse2(const float* __restrict__ line, int estride, const float* __restrict__ add,
+                                           int len, int g, float guess, bool use_guess) {
+    float m = guess, s = 1.f;
+    if (use_guess) s = line_sum<G>(line, estride, add, len, g, m);
+    const bool redo = len > 0 && !(use_guess && s > 7.9e-31f && s < 1.2e30f);
+    if (__any_sync(0xffffffffu, redo)) {  // warp-uniform: the shuffles inside need every lane
+        const float mt = line_max<G>(line, estride, add, len, g);
+        const float st = line_sum<G>(line, estride, add, len, g, mt);
+        if (redo) { m = mt; s = st; }
+    }
+    return m + lot_lg2(s);
+}
+
+constexpr int LOT_MAX_WARPS = 20;
+
+__global__ void __launch_bounds__(LOT_MAX_WARPS * 32, 2)
 log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __restrict__ row_masks,
                              const uint8_t* __restrict__ col_masks, const float* __restrict__ alpha_p, int iterations,
                              float inf, int M, int N, int stride, float* __restrict__ out) {
     extern __shared__ float smem[];
     const int rows = M + 1, cols = N + 1;
-    float* S = smem;                    // rows x stride
+    float* S = smem;                    // rows x stride, base-2 domain
     float* u = S + (size_t)rows * stride;
     float* v = u + rows;
     float* log_mu = v + cols;
     float* log_nu = log_mu + rows;
+    float* lse_r = log_nu + cols;       // previous lse2 of every row / column: the next stabiliser
+    float* lse_c = lse_r + rows;
     __shared__ int valid_s[2];
     const int b = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarps = blockDim.x >> 5;
@@ -92,14 +116,14 @@ log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __
 
     if (tid < 2) valid_s[tid] = 0;
     __syncthreads();
-    // learnable_sinkhorn.py:46,48: num_valid_row / num_valid_col
+    // learnable_sinkhorn.py:50-51: num_valid_row / num_valid_col
     int cr = 0, cc = 0;
     for (int i = tid; i < M; i += blockDim.x) cr += rm ? (rm[i] != 0) : 1;
     for (int j = tid; j < N; j += blockDim.x) cc += cm ? (cm[j] != 0) : 1;
     cr = __reduce_add_sync(0xffffffffu, cr);
     cc = __reduce_add_sync(0xffffffffu, cc);
     if (lane == 0) { atomicAdd(&valid_s[0], cr); atomicAdd(&valid_s[1], cc); }
-    // :41-44 padded scores: [scores | alpha] over [alpha ... alpha], masked rows / columns filled with -inf
+    // :45-48 padded scores: [scores | alpha] over [alpha ... alpha], masked rows / columns filled with -inf
     const float* sb = scores + (size_t)b * M * N;
     for (int i = wid; i < rows; i += nwarps) {
         const bool rmask = i < M && rm && rm[i] == 0;
@@ -107,23 +131,23 @@ log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __
             const bool cmask = j < N && cm && cm[j] == 0;
             float val = (i < M && j < N) ? __ldg(sb + (size_t)i * N + j) : alpha;
             if (rmask || cmask) val = -inf;
-            S[i * stride + j] = val;
+            S[i * stride + j] = val * LOT_LOG2E;
         }
     }
     __syncthreads();
     const float nvr = (float)valid_s[0], nvc = (float)valid_s[1];
-    const float norm = -logf(__fadd_rn(nvr, nvc));  // :48
-    // :50-58 log_mu / log_nu; u = v = 0 (:15)
+    const float norm = -logf(__fadd_rn(nvr, nvc));  // :52
+    // :54-62 log_mu / log_nu; u = v = 0 (:15)
     for (int i = tid; i < rows; i += blockDim.x) {
         float val = i < M ? norm : __fadd_rn(logf(nvc), norm);
         if (i < M && rm && rm[i] == 0) val = -inf;
-        log_mu[i] = val;
+        log_mu[i] = val * LOT_LOG2E;
         u[i] = 0.f;
     }
     for (int j = tid; j < cols; j += blockDim.x) {
         float val = j < N ? norm : __fadd_rn(logf(nvr), norm);
         if (j < N && cm && cm[j] == 0) val = -inf;
-        log_nu[j] = val;
+        log_nu[j] = val * LOT_LOG2E;
         v[j] = 0.f;
     }
     __syncthreads();
@@ -135,25 +159,32 @@ log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __
         for (int r0 = wid * 8; r0 < rows; r0 += nwarps * 8) {
             const int i = r0 + i8;
             const bool act = i < rows;
-            const float lse = line_lse<4>(S + (size_t)(act ? i : 0) * stride, 1, v, act ? cols : 0, l4);
-            if (act && l4 == 0) u[i] = __fsub_rn(log_mu[i], lse);
+            const float lse = line_lse2<4>(S + (size_t)(act ? i : 0) * stride, 1, v, act ? cols : 0, l4,
+                                           act ? lse_r[i] : 0.f, it > 0);
+            if (act && l4 == 0) { u[i] = log_mu[i] - lse; lse_r[i] = lse; }
         }
         __syncthreads();
         // :18  v = log_nu - logsumexp(scores + u, dim=1)
         for (int c0 = wid * 4; c0 < cols; c0 += nwarps * 4) {
             const int j = c0 + j4;
             const bool act = j < cols;
-            const float lse = line_lse<8>(S + (act ? j : 0), stride, u, act ? rows : 0, r8);
-            if (act && r8 == 0) v[j] = __fsub_rn(log_nu[j], lse);
+            const float lse = line_lse2<8>(S + (act ? j : 0), stride, u, act ? rows : 0, r8, act ? lse_c[j] : 0.f,
+                                           it > 0);
+            if (act && r8 == 0) { v[j] = log_nu[j] - lse; lse_c[j] = lse; }
         }
         __syncthreads();
     }
-    // :19, :61  (scores + u + v) - norm
+    // :19, :65  (scores + u + v) - norm, on the unscaled scores
     float* ob = out + (size_t)b * rows * cols;
     for (int i = wid; i < rows; i += nwarps) {
-        const float ui = u[i];
-        for (int j = lane; j < cols; j += 32)
-            ob[(size_t)i * cols + j] = __fsub_rn(__fadd_rn(__fadd_rn(S[i * stride + j], ui), v[j]), norm);
+        const float ui = u[i] * LOT_LN2;
+        const bool rmask = i < M && rm && rm[i] == 0;
+        for (int j = lane; j < cols; j += 32) {
+            const bool cmask = j < N && cm && cm[j] == 0;
+            float val = (i < M && j < N) ? __ldg(sb + (size_t)i * N + j) : alpha;
+            if (rmask || cmask) val = -inf;
+            ob[(size_t)i * cols + j] = __fsub_rn(__fadd_rn(__fadd_rn(val, ui), v[j] * LOT_LN2), norm);
+        }
     }
 }
 
@@ -172,7 +203,7 @@ extern "C" int geotx_log_optimal_transport(const float* scores, const uint8_t* r
     const int rows = M + 1, cols = N + 1;
     int stride = cols;
     while ((stride & 31) != 4) ++stride;
-    const size_t smem = ((size_t)rows * stride + 2 * (size_t)rows + 2 * (size_t)cols) * sizeof(float);
+    const size_t smem = ((size_t)rows * stride + 3 * (size_t)rows + 3 * (size_t)cols) * sizeof(float);
     GEOTX_REQUIRE(smem <= 227 * 1024, "geotx_log_optimal_transport: a (%d x %d) problem needs %zu bytes of shared "
                   "memory (> 227 KB)", rows, cols, smem);
     int rc = check_cuda(cudaFuncSetAttribute(log_optimal_transport_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -1,0 +1,117 @@
+"""Times the 'next' rows of SURVEY.md 8(f) alone on the GPU: K6 point-to-node partition and K7 optimal transport, at the
+3DMatch and KITTI shapes (and beside them the same step written with stock torch ops on the same GPU, i.e. the
+reference's formulation).  python tools/next_bench.py [--no-torch] [--once]"""
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import pkgpath  # noqa: E402
+
+pkg = pkgpath.load_package()
+once_only = '--once' in sys.argv  # one call per kernel: for ncu
+
+
+def timed(fn, iters=50):
+    fn()
+    torch.cuda.synchronize()
+    if once_only:
+        return 0.0
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(10):
+            keep = fn()
+    g.replay()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters // 10):
+        g.replay()
+    b.record()
+    torch.cuda.synchronize()
+    del keep
+    return a.elapsed_time(b) * 1e3 / (iters // 10 * 10)
+
+
+def eager(fn, iters=10):
+    fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) * 1e3 / iters
+
+
+def torch_partition(points, nodes, K):
+    """pointcloud_partition.py:82-98 with stock torch CUDA ops."""
+    x2 = (nodes ** 2).sum(-1)[:, None]
+    y2 = (points ** 2).sum(-1)[None, :]
+    d = (x2 - 2 * nodes @ points.t() + y2).clamp(min=0.0)
+    p2n = d.min(dim=0)[1]
+    masks = torch.zeros(nodes.shape[0], dtype=torch.bool, device=points.device)
+    masks.index_fill_(0, p2n, True)
+    match = torch.zeros_like(d, dtype=torch.bool)
+    match[p2n, torch.arange(points.shape[0], device=points.device)] = True
+    d.masked_fill_(~match, 1e12)
+    idx = d.topk(k=K, dim=1, largest=False)[1]
+    kmask = p2n[idx] == torch.arange(nodes.shape[0], device=points.device)[:, None]
+    idx.masked_fill_(~kmask, points.shape[0])
+    return p2n, masks, idx, kmask
+
+
+def torch_transport(scores, alpha, iters, rm, cm, inf=1e12):
+    """learnable_sinkhorn.py:21-63 with stock torch CUDA ops."""
+    B, M, N = scores.shape
+    prm = torch.zeros(B, M + 1, dtype=torch.bool, device=scores.device)
+    prm[:, :M] = ~rm
+    pcm = torch.zeros(B, N + 1, dtype=torch.bool, device=scores.device)
+    pcm[:, :N] = ~cm
+    S = torch.cat([torch.cat([scores, alpha.expand(B, M, 1)], -1), alpha.expand(B, 1, N + 1)], 1)
+    S.masked_fill_(prm[:, :, None] | pcm[:, None, :], -inf)
+    nr, nc = rm.float().sum(1), cm.float().sum(1)
+    norm = -torch.log(nr + nc)
+    mu = norm[:, None].expand(B, M + 1).clone()
+    mu[:, M] = torch.log(nc) + norm
+    mu[prm] = -inf
+    nu = norm[:, None].expand(B, N + 1).clone()
+    nu[:, N] = torch.log(nr) + norm
+    nu[pcm] = -inf
+    u, v = torch.zeros_like(mu), torch.zeros_like(nu)
+    for _ in range(iters):
+        u = mu - torch.logsumexp(S + v[:, None, :], dim=2)
+        v = nu - torch.logsumexp(S + u[:, :, None], dim=1)
+    return S + u[:, :, None] + v[:, None, :] - norm[:, None, None]
+
+
+def main():
+    with_torch = '--no-torch' not in sys.argv and not once_only
+    res = {}
+    for shape, nodes_n, ppn, K in (('3dmatch', 1024, 16, 64), ('kitti', 2048, 24, 128), ('3dmatch', 4096, 16, 64)):
+        points, nodes = (t.cuda() for t in pkg.synth.make_partition_inputs(shape, nodes_n, ppn))
+        us = timed(lambda: pkg.ops.point_to_node_partition(points, nodes, K, return_points=True))
+        row = {'us': us, 'points': points.shape[0], 'nodes': nodes_n, 'point_limit': K,
+               'pair_evals_per_s': points.shape[0] * nodes_n / max(us, 1e-9) * 1e6}
+        if with_torch:
+            row['torch_eager_us'] = eager(lambda: torch_partition(points, nodes, K))
+        res[f'partition_{shape}_{nodes_n}'] = row
+    for shape, K in (('3dmatch', 64), ('kitti', 128)):
+        scores, rm, cm = (t.cuda() for t in pkg.synth.make_patch_scores(256, K, K, 256))
+        alpha = torch.ones((), device='cuda')
+        us = timed(lambda: pkg.ops.log_optimal_transport(scores, alpha, 100, rm, cm))
+        exps = 256 * 100 * 2 * (K + 1) ** 2
+        row = {'us': us, 'problems': 256, 'size': K + 1, 'iterations': 100,
+               'mufu_frac_at_1965MHz': exps / max(us, 1e-9) * 1e6 / (16 * 148 * 1.965e9)}
+        if with_torch:
+            row['torch_eager_us'] = eager(lambda: torch_transport(scores, alpha, 100, rm, cm), iters=3)
+        res[f'transport_{shape}'] = row
+    print(json.dumps(res))
+
+
+if __name__ == '__main__':
+    main()
