@@ -283,10 +283,9 @@ def time_transport(pkg, shape, calls=10, replays=5):
         def once():
             return pkg.ops.log_optimal_transport(scores, alpha, 100, rm, cm)
         us = _graph_time_us(once, calls, replays)
-        exps = 256 * 100 * 2 * (K + 1) * (K + 1)
         return {'us_per_pair': us, 'problems': 256, 'rows': K + 1, 'cols': K + 1, 'iterations': 100, 'kernels_per_call': 1,
-                'dtype': 'f32', 'exp_per_s': exps / (us * 1e-6),
-                'mufu_frac': exps / (us * 1e-6) / (16 * 148 * 1.965e9),
+                'dtype': 'f32', 'ns_per_half_iteration': us * 1e3 / 200,
+                'bound': 'latency: one barrier-to-barrier dependency chain per half-iteration (DESIGN.md K7)',
                 'timing': f'{calls} calls captured in one CUDA graph, {replays} replays, CUDA events'}
     except Exception as exc:
         return {'error': f'{type(exc).__name__}: {exc}'}

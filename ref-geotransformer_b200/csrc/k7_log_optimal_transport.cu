@@ -53,40 +53,51 @@ __device__ __forceinline__ float group_max(float s) {
     return s;
 }
 
-// base-2 log-sum-exp over one line of the matrix by G cooperating lanes (lane g of the group): element e = g + G*t
-// lives at line[e * estride] and gets add[e] added first; `m` is the stabiliser (any value near the line's maximum).
+// Sum over one line of the matrix of 2^(line[e] + add[e] - m), computed by G cooperating lanes; lane g of the group
+// takes the elements e = g + G*t.  `line` and `add` already point at the lane's first element, `lstep` / G are the
+// distances to its next one, `cnt` is its element count and `cnt_max` the group's largest (warp-uniform loop bound).
 template <int G>
-__device__ __forceinline__ float line_sum(const float* __restrict__ line, int estride, const float* __restrict__ add,
-                                          int len, int g, float m) {
-    float s0 = 0.f, s1 = 0.f;
-    int e = g;
-    for (; e + G < len; e += 2 * G) {
-        s0 += lot_ex2(line[e * estride] + add[e] - m);
-        s1 += lot_ex2(line[(e + G) * estride] + add[e + G] - m);
+__device__ __forceinline__ float line_sum(const float* __restrict__ line, int lstep, const float* __restrict__ add,
+                                          int cnt, int cnt_max, float m) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int t = 0;
+    for (; t + 4 <= cnt_max; t += 4) {
+        const float a0 = line[0], a1 = line[lstep], a2 = line[2 * lstep], a3 = line[3 * lstep];
+        const float b0 = add[0], b1 = add[G], b2 = add[2 * G], b3 = add[3 * G];
+        s0 += lot_ex2(a0 + b0 - m);
+        s1 += lot_ex2(a1 + b1 - m);
+        s2 += lot_ex2(a2 + b2 - m);
+        if (t + 3 < cnt) s3 += lot_ex2(a3 + b3 - m);  // only the last element of a lane can be missing
+        line += 4 * lstep;
+        add += 4 * G;
     }
-    if (e < len) s0 += lot_ex2(line[e * estride] + add[e] - m);
-    return group_sum<G>(s0 + s1);
+    for (; t < cnt_max; ++t) {
+        if (t < cnt) s0 += lot_ex2(line[0] + add[0] - m);
+        line += lstep;
+        add += G;
+    }
+    return group_sum<G>((s0 + s1) + (s2 + s3));
 }
 
 template <int G>
-__device__ __forceinline__ float line_max(const float* __restrict__ line, int estride, const float* __restrict__ add,
-                                          int len, int g) {
+__device__ __forceinline__ float line_max(const float* __restrict__ line, int lstep, const float* __restrict__ add,
+                                          int cnt) {
     float m = -__int_as_float(0x7f800000);
-    for (int e = g; e < len; e += G) m = fmaxf(m, line[e * estride] + add[e]);
+    for (int t = 0; t < cnt; ++t) m = fmaxf(m, line[t * lstep] + add[t * G]);
     return group_max<G>(m);
 }
 
 // lse2 of a line: stabilised by `guess` (the previous iteration's value) when `use_guess`, by the true maximum otherwise
-// or when the guess turned out to be far off.  All lanes of the warp call it together.
+// or when the guess turned out to be far off.  All lanes of the warp call it together (`act`: the lane's line exists).
 template <int G>
-__device__ __forceinline__ float line_lse2(const float* __restrict__ line, int estride, const float* __restrict__ add,
-                                           int len, int g, float guess, bool use_guess) {
+__device__ __forceinline__ float line_lse2(const float* __restrict__ line, int lstep, const float* __restrict__ add,
+                                           int cnt, int cnt_max, float guess, bool use_guess, bool act) {
     float m = guess, s = 1.f;
-    if (use_guess) s = line_sum<G>(line, estride, add, len, g, m);
-    const bool redo = len > 0 && !(use_guess && s > 7.9e-31f && s < 1.2e30f);
+    if (use_guess) s = line_sum<G>(line, lstep, add, cnt, cnt_max, m);
+    const bool redo = act && !(use_guess && s > 7.9e-31f && s < 1.2e30f);
     if (__any_sync(0xffffffffu, redo)) {  // warp-uniform: the shuffles inside need every lane
-        const float mt = line_max<G>(line, estride, add, len, g);
-        const float st = line_sum<G>(line, estride, add, len, g, mt);
+        const float mt = line_max<G>(line, lstep, add, cnt);
+        const float st = line_sum<G>(line, lstep, add, cnt, cnt_max, mt);
         if (redo) { m = mt; s = st; }
     }
     return m + lot_lg2(s);
@@ -152,15 +163,19 @@ log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __
     }
     __syncthreads();
 
-    const int l4 = lane & 3, i8 = lane >> 2;  // row pass: 8 rows per warp, 4 lanes each
-    const int j4 = lane & 3, r8 = lane >> 2;  // column pass: 4 columns per warp, 8 lanes each
+    // row pass: 8 rows per warp, 4 lanes each; column pass: 4 columns per warp, 8 lanes each.  A group whose line does
+    // not exist works on line 0 and discards the result, so that control flow stays warp-uniform.
+    const int l4 = lane & 3, i8 = lane >> 2;
+    const int j4 = lane & 3, r8 = lane >> 2;
+    const int rcnt = (cols - l4 + 3) >> 2, rcnt_max = (cols + 3) >> 2;  // elements of this lane in a row / a column
+    const int ccnt = (rows - r8 + 7) >> 3, ccnt_max = (rows + 7) >> 3;
     for (int it = 0; it < iterations; ++it) {
         // :17  u = log_mu - logsumexp(scores + v, dim=2)
         for (int r0 = wid * 8; r0 < rows; r0 += nwarps * 8) {
             const int i = r0 + i8;
             const bool act = i < rows;
-            const float lse = line_lse2<4>(S + (size_t)(act ? i : 0) * stride, 1, v, act ? cols : 0, l4,
-                                           act ? lse_r[i] : 0.f, it > 0);
+            const int ii = act ? i : 0;
+            const float lse = line_lse2<4>(S + (size_t)ii * stride + l4, 4, v + l4, rcnt, rcnt_max, lse_r[ii], it > 0, act);
             if (act && l4 == 0) { u[i] = log_mu[i] - lse; lse_r[i] = lse; }
         }
         __syncthreads();
@@ -168,8 +183,9 @@ log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __
         for (int c0 = wid * 4; c0 < cols; c0 += nwarps * 4) {
             const int j = c0 + j4;
             const bool act = j < cols;
-            const float lse = line_lse2<8>(S + (act ? j : 0), stride, u, act ? rows : 0, r8, act ? lse_c[j] : 0.f,
-                                           it > 0);
+            const int jj = act ? j : 0;
+            const float lse = line_lse2<8>(S + (size_t)r8 * stride + jj, 8 * stride, u + r8, ccnt, ccnt_max, lse_c[jj],
+                                           it > 0, act);
             if (act && r8 == 0) { v[j] = log_nu[j] - lse; lse_c[j] = lse; }
         }
         __syncthreads();
@@ -190,6 +206,8 @@ log_optimal_transport_kernel(const float* __restrict__ scores, const uint8_t* __
 
 }  // namespace geotx
 
+#include "k7_tile.cuh"
+
 // ---- C ABI --------------------------------------------------------------------------------------------------
 #include "host_util.h"
 using namespace geotx;
@@ -201,6 +219,17 @@ extern "C" int geotx_log_optimal_transport(const float* scores, const uint8_t* r
     GEOTX_REQUIRE(B > 0 && M > 0 && N > 0, "geotx_log_optimal_transport: bad sizes B=%d M=%d N=%d", B, M, N);
     GEOTX_REQUIRE(num_iterations >= 0, "geotx_log_optimal_transport: num_iterations=%d", num_iterations);
     const int rows = M + 1, cols = N + 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int rp = (rows + 7) & ~7, cp = (cols + 7) & ~7;
+    if (rp == cp && (rp == 72 || rp == 136)) {  // the shipped patch sizes (64 / 128 points): unrolled float2 kernel
+        if (rp == 72)
+            log_optimal_transport_tile_kernel<72><<<B, 72 * 4, 0, st>>>(scores, row_masks, col_masks, alpha,
+                                                                        num_iterations, inf, M, N, out);
+        else
+            log_optimal_transport_tile_kernel<136><<<B, 136 * 4, 0, st>>>(scores, row_masks, col_masks, alpha,
+                                                                          num_iterations, inf, M, N, out);
+        return launch_status("geotx_log_optimal_transport");
+    }
     int stride = cols;
     while ((stride & 31) != 4) ++stride;
     const size_t smem = ((size_t)rows * stride + 3 * (size_t)rows + 3 * (size_t)cols) * sizeof(float);
@@ -211,7 +240,7 @@ extern "C" int geotx_log_optimal_transport(const float* scores, const uint8_t* r
     if (rc) return rc;
     int warps = max((rows + 7) / 8, (cols + 3) / 4);
     warps = min(max(warps, 4), LOT_MAX_WARPS);  // more line groups than warps: the pass loops
-    log_optimal_transport_kernel<<<B, warps * 32, smem, (cudaStream_t)stream>>>(
+    log_optimal_transport_kernel<<<B, warps * 32, smem, st>>>(
         scores, row_masks, col_masks, alpha, num_iterations, inf, M, N, stride, out);
     return launch_status("geotx_log_optimal_transport");
 }

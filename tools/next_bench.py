@@ -104,9 +104,8 @@ def main():
         scores, rm, cm = (t.cuda() for t in pkg.synth.make_patch_scores(256, K, K, 256))
         alpha = torch.ones((), device='cuda')
         us = timed(lambda: pkg.ops.log_optimal_transport(scores, alpha, 100, rm, cm))
-        exps = 256 * 100 * 2 * (K + 1) ** 2
         row = {'us': us, 'problems': 256, 'size': K + 1, 'iterations': 100,
-               'mufu_frac_at_1965MHz': exps / max(us, 1e-9) * 1e6 / (16 * 148 * 1.965e9)}
+               'ns_per_half_iteration': us * 1e3 / 200}
         if with_torch:
             row['torch_eager_us'] = eager(lambda: torch_transport(scores, alpha, 100, rm, cm), iters=3)
         res[f'transport_{shape}'] = row
