@@ -291,6 +291,29 @@ def time_transport(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
+def time_procrustes(pkg, shape, calls=10, replays=5):
+    """geotx_weighted_procrustes (one kernel, 3x3 SVD on the device) as the fine matching calls it
+    (local_global_registration.py:169,181-191): one batch of 256 patch problems + 5 global problems; us per pair."""
+    import torch
+    try:
+        K = 128 if shape == 'kitti' else 64
+        local = [t.cuda() for t in pkg.synth.make_procrustes_inputs(256, K, seed=pkg.synth.SEED)[:3]]
+        glob = [t.cuda() for t in pkg.synth.make_procrustes_inputs(1, 5000, seed=pkg.synth.SEED + 1)[:3]]
+
+        def once():
+            keep = [pkg.ops.weighted_procrustes(*local)]
+            for _ in range(5):
+                keep.append(pkg.ops.weighted_procrustes(*glob))
+            return keep
+        us = _graph_time_us(once, calls, replays)
+        return {'us_per_pair': us, 'local_problems': 256, 'points_per_problem': K, 'global_problems': 5,
+                'points_per_global_problem': 5000, 'kernels_per_call': 1, 'calls_per_pair': 6, 'dtype': 'f32 (SVD in f64)',
+                'host_synchronisations': 0,
+                'timing': f'{calls} pairs captured in one CUDA graph, {replays} replays, CUDA events'}
+    except Exception as exc:
+        return {'error': f'{type(exc).__name__}: {exc}'}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -430,6 +453,7 @@ def run_b200(args):
         shape_name = WORKLOADS[args.workload][0]
         partition = time_partition(pkg, shape_name, n) if world == 1 else None
         transport = time_transport(pkg, shape_name) if world == 1 else None
+        procrustes = time_procrustes(pkg, shape_name) if world == 1 else None
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -470,7 +494,7 @@ def run_b200(args):
             'pair_tensor_frac': flops_pair(n, m, cfg) * value / world / 1e12 / peaks['tensor_sustained'],
             'clocks': clocks,
             'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
-                          'log_optimal_transport': transport},
+                          'log_optimal_transport': transport, 'weighted_procrustes': procrustes},
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)

@@ -189,6 +189,16 @@ int geotx_log_optimal_transport(const float* scores, const uint8_t* row_masks, c
                                 const float* alpha, int num_iterations, float inf_value, int B, int M, int N,
                                 float* out, void* stream);
 
+/* Weighted Procrustes / Kabsch with the 3x3 SVD on the device: modules/registration/procrustes.py:6-73
+ * (`weighted_procrustes`, called from modules/geotransformer/local_global_registration.py:169,181-191).  The reference
+ * moves the covariances to the host for torch.svd (procrustes.py:53-54); this entry point never leaves the device.
+ *   src_points, ref_points f32 [B,N,3]; weights f32 [B,N] or NULL (all ones)
+ *   weights below weight_thresh count as 0; the rest are divided by (their sum + eps)
+ *   transform_out f32 [B,4,4] row-major [R t; 0 0 0 1] with R, t mapping src onto ref
+ * (return_transform=False of the reference is R = T[:3,:3], t = T[:3,3]). */
+int geotx_weighted_procrustes(const float* src_points, const float* ref_points, const float* weights, int B, int N,
+                              float weight_thresh, float eps, float* transform_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

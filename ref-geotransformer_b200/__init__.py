@@ -9,13 +9,13 @@ from .modules import (  # noqa: F401
     MultiHeadAttention,
     RPEAttentionLayer, RPEConditionalTransformer, RPEMultiHeadAttention, RPETransformerLayer,
     SinusoidalPositionalEmbedding, SuperPointMatching, TransformerLayer, build_act_layer, build_dropout_layer,
-    LearnableLogOptimalTransport, point_to_node_partition)
+    LearnableLogOptimalTransport, WeightedProcrustes, point_to_node_partition, weighted_procrustes)
 
 __all__ = [
     'GeometricTransformer', 'GraphedGeometricTransformer', 'PipelinedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
     'AttentionOutput', 'SinusoidalPositionalEmbedding', 'SuperPointMatching', 'LearnableLogOptimalTransport',
-    'point_to_node_partition', 'ops', 'synth',
+    'point_to_node_partition', 'WeightedProcrustes', 'weighted_procrustes', 'ops', 'synth',
 ]
 
 _REFERENCE_PATCHES = (
@@ -30,6 +30,9 @@ _REFERENCE_PATCHES = (
     ('geotransformer.modules.ops', ('point_to_node_partition',)),
     ('geotransformer.modules.sinkhorn.learnable_sinkhorn', ('LearnableLogOptimalTransport',)),
     ('geotransformer.modules.sinkhorn', ('LearnableLogOptimalTransport',)),
+    ('geotransformer.modules.registration.procrustes', ('weighted_procrustes', 'WeightedProcrustes')),
+    ('geotransformer.modules.registration', ('weighted_procrustes', 'WeightedProcrustes')),
+    ('geotransformer.modules.geotransformer.local_global_registration', ('WeightedProcrustes',)),
 )
 _saved = {}
 

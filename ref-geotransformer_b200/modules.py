@@ -854,3 +854,35 @@ class LearnableLogOptimalTransport(nn.Module):
 
     def __repr__(self):
         return self.__class__.__name__ + '(num_iterations={})'.format(self.num_iterations)
+
+
+@torch.no_grad()
+def weighted_procrustes(src_points, ref_points, weights=None, weight_thresh=0.0, eps=1e-5, return_transform=False):
+    """Drop-in for geotransformer/modules/registration/procrustes.py:6-73: same arguments and
+    return values ((R, t) or the 4x4 transform; 2-D inputs are treated as a batch of one and squeezed again), with the
+    3x3 SVD on the device (`geotx_weighted_procrustes`) instead of the reference's host round trip."""
+    squeeze_first = src_points.ndim == 2  # :31-38
+    if squeeze_first:
+        src_points, ref_points = src_points.unsqueeze(0), ref_points.unsqueeze(0)
+        if weights is not None:
+            weights = weights.unsqueeze(0)
+    transform = ops.weighted_procrustes(src_points.contiguous(), ref_points.contiguous(),
+                                        None if weights is None else weights.contiguous(), weight_thresh, eps)
+    if return_transform:  # :62-67
+        return transform.squeeze(0) if squeeze_first else transform
+    R, t = transform[:, :3, :3], transform[:, :3, 3]  # :68-72
+    return (R.squeeze(0), t.squeeze(0)) if squeeze_first else (R, t)
+
+
+class WeightedProcrustes(nn.Module):
+    """Drop-in for procrustes.py:76-91."""
+
+    def __init__(self, weight_thresh=0.0, eps=1e-5, return_transform=False):
+        super().__init__()
+        self.weight_thresh = weight_thresh
+        self.eps = eps
+        self.return_transform = return_transform
+
+    def forward(self, src_points, tgt_points, weights=None):
+        return weighted_procrustes(src_points, tgt_points, weights=weights, weight_thresh=self.weight_thresh,
+                                   eps=self.eps, return_transform=self.return_transform)

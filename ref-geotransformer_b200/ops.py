@@ -322,3 +322,24 @@ def log_optimal_transport(scores, alpha, num_iterations, row_masks=None, col_mas
     _abi.call('geotx_log_optimal_transport', _p(scores), _p(masks[0]), _p(masks[1]), _p(alpha), int(num_iterations),
               float(inf), B, M, N, _p(out), _stream())
     return out
+
+
+def weighted_procrustes(src_points, ref_points, weights=None, weight_thresh=0.0, eps=1e-5):
+    """modules/registration/procrustes.py:31-59 on the device (no host SVD): src_points, ref_points (B,N,3) fp32,
+    weights (B,N) fp32 or None -> transform (B,4,4) fp32 mapping src onto ref.  No host synchronisation."""
+    _check(src_points, 'src_points', torch.float32, 3)
+    _check(ref_points, 'ref_points', torch.float32, 3)
+    if src_points.shape != ref_points.shape or src_points.shape[2] != 3:
+        raise RuntimeError(f'src_points and ref_points must both be (B, N, 3), got {tuple(src_points.shape)} and '
+                           f'{tuple(ref_points.shape)}')
+    B, N, _ = src_points.shape
+    if weights is not None:
+        _check(weights, 'weights', torch.float32, 2)
+        if tuple(weights.shape) != (B, N):
+            raise RuntimeError(f'weights must be {(B, N)}, got {tuple(weights.shape)}')
+    out = torch.empty(B, 4, 4, dtype=torch.float32, device=src_points.device)
+    if B == 0:
+        return out
+    _abi.call('geotx_weighted_procrustes', _p(src_points), _p(ref_points), _p(weights), B, N, float(weight_thresh),
+              float(eps), _p(out), _stream())
+    return out

@@ -110,3 +110,32 @@ def make_patch_scores(num_patches=256, rows=64, cols=64, dim=256, seed=SEED, val
     row_masks = torch.arange(rows)[None, :] < nr.clamp(1, rows)[:, None]  # valid points come first (sorted patches)
     col_masks = torch.arange(cols)[None, :] < nc.clamp(1, cols)[:, None]
     return scores.contiguous(), row_masks.contiguous(), col_masks.contiguous()
+
+
+def make_procrustes_inputs(batch=256, n=64, seed=SEED, noise=0.02, outliers=0.2, planar=False, reflect=False):
+    """Inputs of weighted_procrustes as the fine matching feeds it (local_global_registration.py:169): per problem a
+    random rigid motion of `n` points plus noise, a fraction of gross outliers with small weights, zero-padded tails
+    (weights 0).  planar=True puts the points on a plane (rank-2 covariance); reflect=True mirrors ref so that the
+    determinant correction of the Kabsch solution is exercised.
+    Returns src (B,n,3), ref (B,n,3), weights (B,n), true transforms (B,4,4), fp32 CPU."""
+    gen = torch.Generator().manual_seed(seed)
+    src = torch.rand(batch, n, 3, generator=gen) * 2 - 1
+    if planar:
+        src[:, :, 2] = 0.3 * src[:, :, 0] - 0.2 * src[:, :, 1]
+    T = torch.eye(4).repeat(batch, 1, 1)
+    for b in range(batch):
+        T[b, :3, :3] = _rotation(gen, 180.0).float()
+        T[b, :3, 3] = torch.rand(3, generator=gen) * 2 - 1
+    ref = src @ T[:, :3, :3].transpose(1, 2) + T[:, None, :3, 3] + noise * torch.randn(batch, n, 3, generator=gen)
+    if reflect:
+        ref[:, :, 0] = -ref[:, :, 0]
+    weights = torch.rand(batch, n, generator=gen) * 0.9 + 0.1
+    bad = torch.rand(batch, n, generator=gen) < outliers
+    ref = torch.where(bad[:, :, None], torch.rand(batch, n, 3, generator=gen) * 4 - 2, ref)
+    weights = torch.where(bad, weights * 0.05, weights)
+    valid = (torch.rand(batch, generator=gen) * 0.5 + 0.5) * n
+    pad = torch.arange(n)[None, :] >= valid[:, None].clamp(min=4)
+    weights = torch.where(pad, torch.zeros_like(weights), weights)
+    src = torch.where(pad[:, :, None], torch.zeros_like(src), src)
+    ref = torch.where(pad[:, :, None], torch.zeros_like(ref), ref)
+    return src.contiguous(), ref.contiguous(), weights.contiguous(), T

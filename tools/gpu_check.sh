@@ -3,9 +3,9 @@
 # the CUDA context of the others), then smoke() and a short bench.  Logs land in gpurun_out/.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/gpu.txt 2>&1
-for f in k1_knn k3_attention k2_embed forward k5_matching; do
-  timeout 600 python -m pytest tests/test_gpu_$f.py -m gpu -q -s --timeout 300 > gpurun_out/test_$f.log 2>&1
-  echo "test_gpu_$f exit $?" | tee -a gpurun_out/summary.txt
+for f in gpu_k1_knn gpu_k3_attention gpu_k2_embed gpu_forward gpu_k5_matching gpu_next procrustes; do
+  timeout 600 python -m pytest tests/test_$f.py -m gpu -q -s --timeout 300 > gpurun_out/test_$f.log 2>&1
+  echo "test_$f exit $?" | tee -a gpurun_out/summary.txt
   tail -n 15 gpurun_out/test_$f.log
 done
 timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1

@@ -89,6 +89,19 @@ def torch_transport(scores, alpha, iters, rm, cm, inf=1e12):
     return S + u[:, :, None] + v[:, None, :] - norm[:, None, None]
 
 
+def torch_procrustes(src, ref, w, eps=1e-5):
+    """procrustes.py:40-67 with stock torch ops, including the reference's host round trip for the SVD."""
+    w = (w / (w.sum(1, keepdim=True) + eps))[:, :, None]
+    cs, cr = (src * w).sum(1, keepdim=True), (ref * w).sum(1, keepdim=True)
+    H = (src - cs).permute(0, 2, 1) @ (w * (ref - cr))
+    U, _, V = torch.svd(H.cpu())
+    Ut, V = U.transpose(1, 2).cuda(), V.cuda()
+    eye = torch.eye(3).unsqueeze(0).repeat(src.shape[0], 1, 1).cuda()
+    eye[:, -1, -1] = torch.sign(torch.det(V @ Ut))
+    R = V @ eye @ Ut
+    return R, (cr.permute(0, 2, 1) - R @ cs.permute(0, 2, 1)).squeeze(2)
+
+
 def main():
     with_torch = '--no-torch' not in sys.argv and not once_only
     res = {}
@@ -109,6 +122,12 @@ def main():
         if with_torch:
             row['torch_eager_us'] = eager(lambda: torch_transport(scores, alpha, 100, rm, cm), iters=3)
         res[f'transport_{shape}'] = row
+    for batch, n in ((256, 64), (256, 128), (1, 5000)):
+        src, ref, w = (t.cuda() for t in pkg.synth.make_procrustes_inputs(batch, n)[:3])
+        row = {'us': timed(lambda: pkg.ops.weighted_procrustes(src, ref, w)), 'problems': batch, 'points': n}
+        if with_torch:
+            row['torch_eager_host_svd_us'] = eager(lambda: torch_procrustes(src, ref, w))
+        res[f'procrustes_{batch}x{n}'] = row
     print(json.dumps(res))
 
 
