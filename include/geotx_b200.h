@@ -29,6 +29,7 @@ extern "C" {
 #define GEOTX_E_CUDA (-2)  /* CUDA runtime error (text in geotx_last_error) */
 
 #define GEOTX_MAX_ANGLE_K 7
+#define GEOTX_MAX_NEIGHBOR_LIMIT 512 /* geotx_radius_neighbors: neighbours kept per query */
 #define GEOTX_MAX_POINT_LIMIT 8192 /* geotx_point_to_node_partition: points kept per node */
 
 /* dtype tags for buffers that may be stored in either precision */
@@ -198,6 +199,22 @@ int geotx_log_optimal_transport(const float* scores, const uint8_t* row_masks, c
  * (return_transform=False of the reference is R = T[:3,:3], t = T[:3,3]). */
 int geotx_weighted_procrustes(const float* src_points, const float* ref_points, const float* weights, int B, int N,
                               float weight_thresh, float eps, float* transform_out, void* stream);
+
+/* Radius neighbours in stack mode: extensions/cpu/radius_neighbors/radius_neighbors_cpu.cpp:3-104
+ * (exported as ext.radius_neighbors, extensions/pybind.cpp) followed by the truncation of modules/ops/radius_search.py:
+ * 24-27; called 3 times per pyramid stage from utils/data.py:33-72.  For every query point: the support points of the
+ * SAME batch element with ((qx-sx)^2 + (qy-sy)^2) + (qz-sz)^2 < radius^2 (fp32, the reference's own arithmetic),
+ * nearest first, at most `limit`, then the sentinel sum(s_lengths).
+ *   q_points f32 [sum(q_lengths),3], s_points f32 [sum(s_lengths),3] (device; batch elements stacked)
+ *   host_q_lengths, host_s_lengths i64 [batch] (HOST memory, as in the reference where they are CPU tensors)
+ *   neighbors i64 [sum(q_lengths), limit]   indices into the stacked s_points
+ *   counts    i32 [sum(q_lengths)]          in-radius support points of every query BEFORE truncation
+ *   max_count i32 [1]                       their maximum = the width of the reference's untruncated result; the
+ *                                           reference returns min(max_count, limit) columns
+ * Equal distances are ordered by the smaller index (std::sort leaves ties unspecified).  limit <= 512. */
+int geotx_radius_neighbors(const float* q_points, const float* s_points, const int64_t* host_q_lengths,
+                           const int64_t* host_s_lengths, int batch, float radius, int limit, int64_t* neighbors,
+                           int32_t* counts, int32_t* max_count, void* stream);
 
 #ifdef __cplusplus
 }

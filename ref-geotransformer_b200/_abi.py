@@ -36,6 +36,7 @@ SIGNATURES = {
     'geotx_point_to_node_partition': (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
     'geotx_log_optimal_transport': (_i, [_p, _p, _p, _p, _i, _f, _i, _i, _i, _p, _p]),
     'geotx_weighted_procrustes': (_i, [_p, _p, _p, _i, _i, _f, _f, _p, _p]),
+    'geotx_radius_neighbors': (_i, [_p, _p, _p, _p, _i, _f, _i, _p, _p, _p, _p]),
 }
 
 GEOTX_F32 = 0

@@ -886,3 +886,18 @@ class WeightedProcrustes(nn.Module):
     def forward(self, src_points, tgt_points, weights=None):
         return weighted_procrustes(src_points, tgt_points, weights=weights, weight_thresh=self.weight_thresh,
                                    eps=self.eps, return_transform=self.return_transform)
+
+
+@torch.no_grad()
+def radius_search(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit):
+    """Drop-in for geotransformer/modules/ops/radius_search.py:7-27 for points that already live on
+    the GPU: same arguments, same result -- (N, min(max_count, neighbor_limit)) int64, filled with M.  The reference
+    runs nanoflann on the host inside the data loader; here the width of the result depends on device data, so this
+    wrapper reads one integer back (the only synchronisation); `ops.radius_neighbors` returns the fixed-width form
+    without it.  neighbor_limit <= 0 (the reference's "no truncation") is not supported."""
+    if neighbor_limit <= 0:
+        raise RuntimeError('radius_search: neighbor_limit must be positive on the GPU path')
+    neighbors, _, max_count = ops.radius_neighbors(q_points.contiguous(), s_points.contiguous(), q_lengths, s_lengths,
+                                                   radius, neighbor_limit)
+    width = min(int(max_count.item()), int(neighbor_limit))
+    return neighbors[:, :width] if width < neighbor_limit else neighbors

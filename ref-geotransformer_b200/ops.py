@@ -343,3 +343,35 @@ def weighted_procrustes(src_points, ref_points, weights=None, weight_thresh=0.0,
     _abi.call('geotx_weighted_procrustes', _p(src_points), _p(ref_points), _p(weights), B, N, float(weight_thresh),
               float(eps), _p(out), _stream())
     return out
+
+
+def _host_lengths(lengths, name):
+    """Batch lengths as a ctypes int64 array (they live on the host in the reference: utils/data.py builds them in the
+    collate function).  A CUDA tensor is accepted but costs a synchronising copy."""
+    vals = [int(x) for x in (lengths.tolist() if isinstance(lengths, torch.Tensor) else lengths)]
+    if any(v < 0 for v in vals):
+        raise RuntimeError(f'{name} must be non-negative, got {vals}')
+    return (ctypes.c_int64 * len(vals))(*vals), vals
+
+
+def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit):
+    """extensions/cpu/radius_neighbors (ext.radius_neighbors) + modules/ops/radius_search.py:24-27 on the device.
+    q_points (Nq,3), s_points (Ns,3) fp32 CUDA; q_lengths, s_lengths: the batch lengths (host).  Returns
+    (neighbors int64 (Nq, neighbor_limit) padded with Ns, counts int32 (Nq,), max_count int32 (1,)); nothing
+    synchronises."""
+    _check(q_points, 'q_points', torch.float32, 2)
+    _check(s_points, 's_points', torch.float32, 2)
+    if q_points.shape[1] != 3 or s_points.shape[1] != 3:
+        raise RuntimeError(f'points must be (*, 3), got {tuple(q_points.shape)} and {tuple(s_points.shape)}')
+    ql, qv = _host_lengths(q_lengths, 'q_lengths')
+    sl, sv = _host_lengths(s_lengths, 's_lengths')
+    if len(qv) != len(sv) or sum(qv) != q_points.shape[0] or sum(sv) != s_points.shape[0]:
+        raise RuntimeError(f'lengths {qv} / {sv} do not match {q_points.shape[0]} query and {s_points.shape[0]} support points')
+    limit = int(neighbor_limit)
+    dev = q_points.device
+    neighbors = torch.empty(q_points.shape[0], limit, dtype=torch.int64, device=dev)
+    counts = torch.empty(q_points.shape[0], dtype=torch.int32, device=dev)
+    max_count = torch.empty(1, dtype=torch.int32, device=dev)
+    _abi.call('geotx_radius_neighbors', _p(q_points), _p(s_points), ql, sl, len(qv), float(radius), limit, _p(neighbors),
+              _p(counts), _p(max_count), _stream())
+    return neighbors, counts, max_count

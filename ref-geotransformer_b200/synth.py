@@ -139,3 +139,19 @@ def make_procrustes_inputs(batch=256, n=64, seed=SEED, noise=0.02, outliers=0.2,
     src = torch.where(pad[:, :, None], torch.zeros_like(src), src)
     ref = torch.where(pad[:, :, None], torch.zeros_like(ref), ref)
     return src.contiguous(), ref.contiguous(), weights.contiguous(), T
+
+
+def make_dense_cloud(n, extent=3.0, seed=SEED, jitter=0.005):
+    """A raw-scan-like cloud for the collate operators: n points on three orthogonal walls of a
+    room of size `extent` (surfaces, not a volume, so that neighbour counts per radius look like a depth scan's), with
+    a little off-surface jitter.  Returns (n,3) fp32 CPU."""
+    gen = torch.Generator().manual_seed(seed)
+    uv = torch.rand(n, 2, generator=gen) * extent
+    wall = torch.randint(0, 3, (n,), generator=gen)
+    off = torch.randn(n, generator=gen) * jitter
+    pts = torch.empty(n, 3)
+    for w in range(3):
+        m = wall == w
+        a, b = [(1, 2), (0, 2), (0, 1)][w]
+        pts[m, a], pts[m, b], pts[m, w] = uv[m, 0], uv[m, 1], off[m]
+    return pts.contiguous()

@@ -1,0 +1,59 @@
+"""ctypes access to oracle/_ref/libgeotx_ref_cpu.so: the REFERENCE's own CPU collate operators compiled from
+/root/reference by oracle/build_ref.sh (test infrastructure; see oracle/ref_cpu_shim.cpp)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SO = os.path.join(ROOT, 'oracle', '_ref', 'libgeotx_ref_cpu.so')
+_lib = None
+
+
+def available():
+    return os.path.exists(SO) or os.path.isdir('/root/reference/geotransformer/extensions')
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if os.path.isdir('/root/reference/geotransformer/extensions'):
+            srcs = [os.path.join(ROOT, 'oracle', f) for f in ('ref_cpu_shim.cpp', 'build_ref.sh')]
+            if not os.path.exists(SO) or any(os.path.getmtime(s) > os.path.getmtime(SO) for s in srcs):
+                subprocess.run(['bash', os.path.join(ROOT, 'oracle', 'build_ref.sh')], check=True, stdout=subprocess.DEVNULL)
+        lib = ctypes.CDLL(SO)
+        lib.geotx_ref_radius_neighbors.restype = ctypes.c_int64
+        lib.geotx_ref_grid_subsampling.restype = ctypes.c_int64
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius):
+    """numpy in, numpy out: the reference's ext.radius_neighbors (untruncated (Nq, max_count) int64)."""
+    lib = load()
+    q = np.ascontiguousarray(q_points, np.float32)
+    s = np.ascontiguousarray(s_points, np.float32)
+    ql, sl = np.asarray(q_lengths, np.int64), np.asarray(s_lengths, np.int64)
+    width = lib.geotx_ref_radius_neighbors(_ptr(q), ctypes.c_int64(q.shape[0]), _ptr(s), ctypes.c_int64(s.shape[0]),
+                                           _ptr(ql), _ptr(sl), ctypes.c_int(len(ql)), ctypes.c_float(radius))
+    out = np.empty((q.shape[0], width), np.int64)
+    lib.geotx_ref_radius_neighbors_copy(_ptr(out))
+    return out
+
+
+def grid_subsampling(points, lengths, voxel_size):
+    """The reference's ext.grid_subsampling: (s_points (M,3) float32, s_lengths (B,) int64)."""
+    lib = load()
+    p = np.ascontiguousarray(points, np.float32)
+    ln = np.asarray(lengths, np.int64)
+    m = lib.geotx_ref_grid_subsampling(_ptr(p), ctypes.c_int64(p.shape[0]), _ptr(ln), ctypes.c_int(len(ln)),
+                                       ctypes.c_float(voxel_size))
+    sp = np.empty((m, 3), np.float32)
+    sl = np.empty(len(ln), np.int64)
+    lib.geotx_ref_grid_subsampling_copy(_ptr(sp), _ptr(sl))
+    return sp, sl

@@ -1,0 +1,150 @@
+"""K9 radius neighbours.  The checker is the REFERENCE's own C++ operator
+(extensions/cpu/radius_neighbors, compiled from /root/reference into oracle/_ref by oracle/build_ref.sh) and golden
+vectors written by it (tests/golden/make_golden_collate.py).  Index work: bit-exact, except that the reference sorts
+with std::sort on the distance alone, so neighbours at EXACTLY equal fp32 distance may come in either order (and either
+of two such neighbours may be the one cut off at `limit`); the comparison allows exactly that and nothing else."""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import ref_cpu
+
+_spec = importlib.util.spec_from_file_location(
+    'make_golden_collate', os.path.join(os.path.dirname(__file__), 'golden', 'make_golden_collate.py'))
+_mod = None
+
+
+def _gold():
+    global _mod
+    if _mod is None:
+        _mod = importlib.util.module_from_spec(_spec)
+        _spec.loader.exec_module(_mod)
+    return _mod
+
+
+TAGS = ['rn_small', 'rn_cross', 'rn_sparse', 'rn_stage']
+
+
+def ref_dist(q, s):
+    """nanoflann L2_Simple_Adaptor::evalMetric in fp32: ((qx-sx)^2 + (qy-sy)^2) + (qz-sz)^2 (nanoflann.hpp:432-439)."""
+    d = (q - s).astype(np.float32)
+    return ((d[..., 0] * d[..., 0]).astype(np.float32) + (d[..., 1] * d[..., 1]).astype(np.float32)).astype(np.float32) \
+        + (d[..., 2] * d[..., 2]).astype(np.float32)
+
+
+def assert_same_neighbors(got, want, q, s, sentinel):
+    """got, want (Nq, W) int: equal, or differing only by permutations inside groups of equal reference distance
+    (including the group that straddles the cut at W)."""
+    assert got.shape == want.shape, (got.shape, want.shape)
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    sp = np.concatenate([s, np.full((1, 3), np.inf, np.float32)])  # the sentinel is infinitely far
+    for r in bad:
+        dg = ref_dist(q[r][None], sp[np.minimum(got[r], sentinel)])
+        dw = ref_dist(q[r][None], sp[np.minimum(want[r], sentinel)])
+        assert np.array_equal(dg, dw), f'query {r}: distance sequences differ'
+        diff = got[r] != want[r]
+        for d in np.unique(dw[diff]):
+            grp = dw == d
+            a, b = set(got[r][grp]), set(want[r][grp])
+            if a != b:  # only legal when the tie group reaches the last column (one of the tied points was cut)
+                assert grp[-1], f'query {r}: different neighbours at distance {d}'
+    return len(bad)
+
+
+def test_reference_operator_matches_its_golden(pkg, golden):
+    """oracle/_ref (built here from /root/reference, or the prebuilt one on the GPU box) reproduces the vectors."""
+    if not ref_cpu.available():
+        pytest.skip('oracle/_ref not built and /root/reference absent')
+    z = golden('collate_cases.npz')
+    for tag in TAGS:
+        q, s, ql, sl, radius, limit = _gold().case_inputs(pkg.synth, tag)
+        full = ref_cpu.radius_neighbors(q.numpy(), s.numpy(), ql, sl, radius)
+        assert full.shape[1] == int(z[f'{tag}.max_count'])
+        assert np.array_equal(full[:, :limit], z[f'{tag}.neighbors'])
+
+
+def test_golden_semantics(pkg, golden):
+    """What the vectors mean (and what the GPU kernel must reproduce): in-radius test d < r^2 in fp32, ascending
+    distance, per batch element, sentinel = total number of support points."""
+    z = golden('collate_cases.npz')
+    q, s, ql, sl, radius, limit = _gold().case_inputs(pkg.synth, 'rn_small')
+    want = z['rn_small.neighbors']
+    qn, sn = q.numpy(), s.numpy()
+    r2 = np.float32(radius) * np.float32(radius)
+    q0 = s0 = 0
+    for b in range(len(ql)):
+        for r in range(q0, q0 + ql[b], 37):
+            d = ref_dist(qn[r][None], sn[s0:s0 + sl[b]])
+            inside = np.nonzero(d < r2)[0]
+            order = inside[np.lexsort((inside, d[inside]))][:limit] + s0
+            row = want[r]
+            assert np.array_equal(np.sort(d[order - s0]), d[row[row < sn.shape[0]] - s0])
+            assert (row[len(order):] == sn.shape[0]).all()
+        q0 += ql[b]
+        s0 += sl[b]
+
+
+def test_host_api_without_gpu(pkg):
+    with pytest.raises(RuntimeError):
+        pkg.radius_search(torch.zeros(4, 3), torch.zeros(4, 3), [4], [4], 0.1, 8)  # CPU tensors: no fallback
+    import ctypes
+    lib = pkg._abi.load()
+    p = ctypes.c_void_p(256)
+    one = (ctypes.c_int64 * 1)(4)
+    assert lib.geotx_radius_neighbors(p, p, one, one, 1, 0.1, 0, p, p, p, None) == -1
+    assert lib.geotx_radius_neighbors(p, p, one, one, 1, 0.1, 513, p, p, p, None) == -1
+
+
+# ---- GPU ----------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize('tag', TAGS)
+def test_gpu_vs_reference_golden(pkg, golden, tag):
+    from gpu_common import DEV
+    z = golden('collate_cases.npz')
+    q, s, ql, sl, radius, limit = _gold().case_inputs(pkg.synth, tag)
+    got = pkg.radius_search(q.to(DEV), s.to(DEV), torch.tensor(ql), torch.tensor(sl), radius, limit)
+    assert got.dtype == torch.int64 and got.shape[1] == min(limit, int(z[f'{tag}.max_count']))
+    assert_same_neighbors(got.cpu().numpy(), z[f'{tag}.neighbors'].astype(np.int64), q.numpy(), s.numpy(), s.shape[0])
+    nb, counts, max_count = pkg.ops.radius_neighbors(q.to(DEV), s.to(DEV), ql, sl, radius, limit)
+    assert nb.shape == (q.shape[0], limit) and int(max_count) == int(z[f'{tag}.max_count'])
+    assert int(counts.max()) == int(max_count)
+    assert torch.equal((nb < s.shape[0]).sum(1).cpu(), counts.cpu().clamp(max=limit).long())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('sizes,radius,limit', [((20000, 18000), 0.0625, 38), ((5000, 5000), 0.25, 36),
+                                                ((3000, 1, 2000), 0.3, 64), ((40, 33), 10.0, 256)])
+def test_gpu_full_size_vs_reference_operator(pkg, sizes, radius, limit):
+    """A stage-0-sized pair (3DMatch: ~20k points per cloud, radius 2.5 x 0.025 m, limit 38: config.py:79-80,
+    utils/data.py), a dense stage, a one-point batch element and a search where everything is in range, against the
+    reference's operator itself.  (Empty batch elements are not compared: the reference's loop advances at most one
+    element per query, radius_neighbors_cpu.cpp:37-52, and never leaves an empty one.)"""
+    if not ref_cpu.available():
+        pytest.skip('oracle/_ref not built and /root/reference absent')
+    from gpu_common import DEV
+    clouds = [pkg.synth.make_dense_cloud(n, 3.0, 900 + b) if n else torch.zeros(0, 3) for b, n in enumerate(sizes)]
+    s = torch.cat(clouds)
+    full = ref_cpu.radius_neighbors(s.numpy(), s.numpy(), list(sizes), list(sizes), radius)
+    got = pkg.radius_search(s.to(DEV), s.to(DEV), list(sizes), list(sizes), radius, limit).cpu().numpy()
+    assert_same_neighbors(got, full[:, :limit], s.numpy(), s.numpy(), s.shape[0])
+    # size-independent properties: every point finds itself first (distance 0); lists stay inside the batch element
+    assert np.array_equal(got[:, 0], np.arange(s.shape[0]))
+    start = 0
+    for n in sizes:
+        blk = got[start:start + n]
+        assert ((blk >= start) & (blk < start + n) | (blk == s.shape[0])).all()
+        start += n
+
+
+@pytest.mark.gpu
+def test_gpu_empty_batch_element(pkg):
+    """Our own semantics for an empty element: it contributes no queries and no neighbours, the others are unaffected."""
+    from gpu_common import DEV
+    a, b = pkg.synth.make_dense_cloud(500, 3.0, 1), pkg.synth.make_dense_cloud(400, 3.0, 2)
+    s = torch.cat([a, b]).to(DEV)
+    with_empty = pkg.ops.radius_neighbors(s, s, [500, 0, 400], [500, 0, 400], 0.3, 16)[0]
+    without = pkg.ops.radius_neighbors(s, s, [500, 400], [500, 400], 0.3, 16)[0]
+    assert torch.equal(with_empty, without)

@@ -128,6 +128,21 @@ def main():
         if with_torch:
             row['torch_eager_host_svd_us'] = eager(lambda: torch_procrustes(src, ref, w))
         res[f'procrustes_{batch}x{n}'] = row
+    import time
+    sys.path.insert(0, os.path.join(ROOT, 'tests'))
+    import ref_cpu
+    for sizes, radius, limit in (((20000, 18000), 0.0625, 38), ((5000, 4500), 0.25, 36)):
+        clouds = [pkg.synth.make_dense_cloud(n, 3.0, 900 + b) for b, n in enumerate(sizes)]
+        s_cpu = torch.cat(clouds)
+        s_gpu = s_cpu.cuda()
+        row = {'us': timed(lambda: pkg.ops.radius_neighbors(s_gpu, s_gpu, list(sizes), list(sizes), radius, limit)),
+               'points': list(sizes), 'radius': radius, 'limit': limit,
+               'pair_evals': sum(n * n for n in sizes)}
+        if with_torch and ref_cpu.available():  # the reference's own operator (nanoflann KD-tree, one host thread)
+            t0 = time.perf_counter()
+            ref_cpu.radius_neighbors(s_cpu.numpy(), s_cpu.numpy(), list(sizes), list(sizes), radius)
+            row['reference_cpu_operator_us'] = (time.perf_counter() - t0) * 1e6
+        res[f'radius_neighbors_{sizes[0]}'] = row
     print(json.dumps(res))
 
 
