@@ -216,6 +216,21 @@ int geotx_radius_neighbors(const float* q_points, const float* s_points, const i
                            const int64_t* host_s_lengths, int batch, float radius, int limit, int64_t* neighbors,
                            int32_t* counts, int32_t* max_count, void* stream);
 
+/* Grid (voxel barycentre) subsampling in stack mode: extensions/cpu/grid_subsampling/
+ * grid_subsampling_cpu.cpp:3-79 (ext.grid_subsampling; modules/ops/grid_subsample.py:9-22; utils/data.py:22-30).
+ * Per batch element: voxels of size voxel_size anchored at floor(min_corner / voxel) * voxel (the reference's fp32
+ * sequence, bit for bit), every occupied voxel replaced by the barycentre of its points.
+ *   points f32 [sum(lengths),3] (device), host_lengths i64 [batch] (HOST; every element needs >= 1 point)
+ *   s_points  f32 [sum(lengths),3] capacity; the first sum(s_lengths) rows are written, batch elements stacked
+ *   s_lengths i64 [batch] (device): occupied voxels per element, or -1 if the element's bounding grid has more than
+ *             max_cells cells (nothing is written for it)
+ *   workspace geotx_grid_subsample_workspace_bytes(max_cells) bytes, 256-byte aligned; max_cells <= 2^31
+ * Output order: ascending voxel index (x fastest) inside every element; the reference's order is that of a
+ * std::unordered_map.  Barycentres are summed in fp64 and rounded once (the reference: fp32, input order). */
+int64_t geotx_grid_subsample_workspace_bytes(int64_t max_cells);
+int geotx_grid_subsample(const float* points, const int64_t* host_lengths, int batch, float voxel_size, float* s_points,
+                         int64_t* s_lengths, void* workspace, int64_t max_cells, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

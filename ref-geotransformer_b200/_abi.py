@@ -37,6 +37,8 @@ SIGNATURES = {
     'geotx_log_optimal_transport': (_i, [_p, _p, _p, _p, _i, _f, _i, _i, _i, _p, _p]),
     'geotx_weighted_procrustes': (_i, [_p, _p, _p, _i, _i, _f, _f, _p, _p]),
     'geotx_radius_neighbors': (_i, [_p, _p, _p, _p, _i, _f, _i, _p, _p, _p, _p]),
+    'geotx_grid_subsample_workspace_bytes': (_i64, [_i64]),
+    'geotx_grid_subsample': (_i, [_p, _p, _i, _f, _p, _p, _p, _i64, _p]),
 }
 
 GEOTX_F32 = 0
@@ -46,7 +48,8 @@ GEOTX_F16 = 2
 # kernels each entry point enqueues (bench.py's gpu_launches is counted from this)
 KERNELS_PER_CALL = {'geotx_gse_knn': 2,  # pack_points + knn
                     'geotx_superpoint_matching': 10,  # prepare, scores, sums, 6 select passes, collect
-                    'geotx_point_to_node_partition': 4}  # assign, offsets, scatter, select
+                    'geotx_point_to_node_partition': 4,  # assign, offsets, scatter, select
+                    'geotx_grid_subsample': 14}  # 7 per batch element (bounds, clear, accumulate, count, scan, emit, advance)
 
 _lib = None
 launch_count = 0  # hand-written kernels launched through this binding so far

@@ -901,3 +901,17 @@ def radius_search(q_points, s_points, q_lengths, s_lengths, radius, neighbor_lim
                                                    radius, neighbor_limit)
     width = min(int(max_count.item()), int(neighbor_limit))
     return neighbors[:, :width] if width < neighbor_limit else neighbors
+
+
+@torch.no_grad()
+def grid_subsample(points, lengths, voxel_size, max_cells=1 << 24):
+    """Drop-in for geotransformer/modules/ops/grid_subsample.py:9-22 (plain path, length_ref = length_src = None;
+    SURVEY.md 8(f)-4) for points that already live on the GPU.  Returns (s_points (M,3) CUDA, s_lengths (B,) int64 on
+    the HOST, where the reference keeps them); M depends on device data, so the lengths are read back once.  The
+    voxels come out in ascending voxel index instead of the reference's hash-table order."""
+    buf, s_lengths = ops.grid_subsample(points.contiguous(), lengths, voxel_size, max_cells)
+    s_lengths = s_lengths.cpu()
+    if bool((s_lengths < 0).any()):
+        raise RuntimeError(f'grid_subsample: the voxel grid of a batch element has more than max_cells={max_cells} '
+                           f'cells at voxel_size={voxel_size}; pass a larger max_cells')
+    return buf[:int(s_lengths.sum())], s_lengths

@@ -375,3 +375,31 @@ def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_
     _abi.call('geotx_radius_neighbors', _p(q_points), _p(s_points), ql, sl, len(qv), float(radius), limit, _p(neighbors),
               _p(counts), _p(max_count), _stream())
     return neighbors, counts, max_count
+
+
+_GS_WORK = {}
+
+
+def grid_subsample(points, lengths, voxel_size, max_cells=1 << 24):
+    """extensions/cpu/grid_subsampling (ext.grid_subsampling) on the device.  points (N,3) fp32 CUDA, lengths: the batch
+    lengths (host).  Returns (s_points (N,3) buffer whose first sum(s_lengths) rows are valid, s_lengths int64 (B,) on
+    the device; -1 marks an element whose bounding grid exceeds max_cells).  Nothing synchronises.  The workspace
+    (32 B per cell) is kept per device and size."""
+    _check(points, 'points', torch.float32, 2)
+    if points.shape[1] != 3:
+        raise RuntimeError(f'points must be (N, 3), got {tuple(points.shape)}')
+    ln, vals = _host_lengths(lengths, 'lengths')
+    if sum(vals) != points.shape[0] or any(v < 1 for v in vals):
+        raise RuntimeError(f'lengths {vals} must be positive and sum to {points.shape[0]}')
+    lib = _abi.load()
+    key = (points.device, int(max_cells))
+    if key not in _GS_WORK:
+        nbytes = lib.geotx_grid_subsample_workspace_bytes(int(max_cells))
+        if nbytes <= 0:
+            raise RuntimeError(f'grid_subsample: bad max_cells={max_cells}')
+        _GS_WORK[key] = torch.empty(nbytes, dtype=torch.uint8, device=points.device)
+    s_points = torch.empty_like(points)
+    s_lengths = torch.empty(len(vals), dtype=torch.int64, device=points.device)
+    _abi.call('geotx_grid_subsample', _p(points), ln, len(vals), float(voxel_size), _p(s_points), _p(s_lengths),
+              _p(_GS_WORK[key]), int(max_cells), _stream())
+    return s_points, s_lengths

@@ -148,3 +148,95 @@ def test_gpu_empty_batch_element(pkg):
     with_empty = pkg.ops.radius_neighbors(s, s, [500, 0, 400], [500, 0, 400], 0.3, 16)[0]
     without = pkg.ops.radius_neighbors(s, s, [500, 400], [500, 400], 0.3, 16)[0]
     assert torch.equal(with_empty, without)
+
+
+# ---- K10 grid subsampling -----------------------------------------------------------------------------------------
+GS_CASES = [((5000, 4000), 3.0, 0.05), ((30000, 25000), 3.0, 0.05), ((12000, 12000), 3.0, 0.1), ((300, 1, 7), 3.0, 0.4)]
+GS_TOL = 2e-6  # relative to the cloud's extent: fp64 sums rounded once vs the reference's sequential fp32 sums
+
+
+def _gs_inputs(pkg, sizes, extent, seed=700):
+    clouds = [pkg.synth.make_dense_cloud(n, extent, seed + b) - (1.3 if b else 0.0) for b, n in enumerate(sizes)]
+    return torch.cat(clouds).contiguous()
+
+
+def _lexsort_rows(a):
+    return a[np.lexsort((a[:, 2], a[:, 1], a[:, 0]))]
+
+
+def test_reference_grid_subsampling_semantics(pkg):
+    """What the reference operator computes (pins the shim): per element, one barycentre per occupied voxel of the
+    grid anchored at floor(min / voxel) * voxel; every point lies in the voxel of exactly one output."""
+    if not ref_cpu.available():
+        pytest.skip('oracle/_ref not built and /root/reference absent')
+    sizes, extent, voxel = GS_CASES[0]
+    pts = _gs_inputs(pkg, sizes, extent).numpy()
+    sp, sl = ref_cpu.grid_subsampling(pts, list(sizes), voxel)
+    assert sl.sum() == sp.shape[0] and len(sl) == 2
+    start = out = 0
+    for n, m in zip(sizes, sl):
+        p = pts[start:start + n]
+        origin = np.floor(p.min(0) * np.float32(1.0 / voxel)) * np.float32(voxel)
+        cells = np.floor((p - origin) / np.float32(voxel)).astype(np.int64)
+        uniq = np.unique(cells, axis=0)
+        assert len(uniq) == m
+        bary_cells = np.floor((sp[out:out + m] - origin) / np.float32(voxel)).astype(np.int64)
+        assert len(np.unique(bary_cells, axis=0)) >= 0.99 * m  # barycentres sit in their own voxels (up to rounding)
+        start += n
+        out += m
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('sizes,extent,voxel', GS_CASES)
+def test_gpu_grid_subsample_vs_reference_operator(pkg, sizes, extent, voxel):
+    if not ref_cpu.available():
+        pytest.skip('oracle/_ref not built and /root/reference absent')
+    from gpu_common import DEV
+    pts = _gs_inputs(pkg, sizes, extent)
+    want_p, want_l = ref_cpu.grid_subsampling(pts.numpy(), list(sizes), voxel)
+    got_p, got_l = pkg.grid_subsample(pts.to(DEV), torch.tensor(sizes), voxel)
+    assert got_l.dtype == torch.int64 and not got_l.is_cuda and got_p.is_cuda
+    assert np.array_equal(got_l.numpy(), want_l), (got_l, want_l)  # voxel counts: exact
+    got_p = got_p.cpu().numpy()
+    g0 = w0 = 0
+    for m in want_l:
+        a, b = _lexsort_rows(got_p[g0:g0 + m]), _lexsort_rows(want_p[w0:w0 + m])
+        err = np.abs(a - b).max()
+        if err > GS_TOL * extent:  # two barycentres whose x differ by less than the tolerance may sort differently
+            from scipy.spatial import cKDTree
+            d, idx = cKDTree(b).query(a)
+            assert d.max() <= GS_TOL * extent * 2 and len(np.unique(idx)) == len(a)
+        g0 += m
+        w0 += m
+    # our own order: ascending voxel index (x fastest) inside every element
+    start = out = 0
+    for n, m in zip(sizes, want_l):
+        p = pts[start:start + n].numpy()
+        origin = np.floor(p.min(0) * np.float32(1.0 / voxel)) * np.float32(voxel)
+        cells = np.floor((p - origin) / np.float32(voxel)).astype(np.int64)
+        dims = cells.max(0) + 1
+        keys = np.unique(cells[:, 0] + dims[0] * (cells[:, 1] + dims[1] * cells[:, 2]))
+        c = np.floor((got_p[out:out + m] - origin) / np.float32(voxel)).astype(np.int64)
+        got_keys = c[:, 0] + dims[0] * (c[:, 1] + dims[1] * c[:, 2])
+        assert (np.abs(got_keys - keys) > 0).mean() < 0.01  # barycentres on a voxel face may round into the neighbour
+        start += n
+        out += m
+
+
+@pytest.mark.gpu
+def test_gpu_grid_subsample_properties_and_errors(pkg):
+    from gpu_common import DEV
+    pts = _gs_inputs(pkg, (20000,), 3.0).to(DEV)
+    once, l1 = pkg.grid_subsample(pts, [20000], 0.05)
+    again, l2 = pkg.grid_subsample(pts, [20000], 0.05)
+    assert torch.equal(once, again) and torch.equal(l1, l2)  # deterministic despite the atomics
+    sub2, l3 = pkg.grid_subsample(once, l1, 0.05)            # a barycentre stays in its voxel: (almost) idempotent
+    assert abs(int(l3[0]) - int(l1[0])) <= 0.01 * int(l1[0])
+    big, lb = pkg.grid_subsample(pts, [20000], 1e6)          # one voxel: the centroid
+    assert int(lb[0]) == 1 and torch.allclose(big[0], pts.double().mean(0).float(), atol=1e-5)
+    with pytest.raises(RuntimeError, match='max_cells'):
+        pkg.grid_subsample(pts, [20000], 1e-4)               # 30000^3 cells
+    with pytest.raises(RuntimeError):
+        pkg.grid_subsample(pts, [19999], 0.05)
+    with pytest.raises(RuntimeError):
+        pkg.grid_subsample(pts.cpu(), [20000], 0.05)

@@ -143,6 +143,16 @@ def main():
             ref_cpu.radius_neighbors(s_cpu.numpy(), s_cpu.numpy(), list(sizes), list(sizes), radius)
             row['reference_cpu_operator_us'] = (time.perf_counter() - t0) * 1e6
         res[f'radius_neighbors_{sizes[0]}'] = row
+    for sizes, voxel in (((30000, 25000), 0.05), ((120000, 100000), 0.05)):
+        clouds = [pkg.synth.make_dense_cloud(n, 3.0, 700 + b) for b, n in enumerate(sizes)]
+        p_cpu = torch.cat(clouds)
+        p_gpu = p_cpu.cuda()
+        row = {'us': timed(lambda: pkg.ops.grid_subsample(p_gpu, list(sizes), voxel)), 'points': list(sizes), 'voxel': voxel}
+        if with_torch and ref_cpu.available():  # the reference's own operator (std::unordered_map, one host thread)
+            t0 = time.perf_counter()
+            ref_cpu.grid_subsampling(p_cpu.numpy(), list(sizes), voxel)
+            row['reference_cpu_operator_us'] = (time.perf_counter() - t0) * 1e6
+        res[f'grid_subsample_{sizes[0]}'] = row
     print(json.dumps(res))
 
 
