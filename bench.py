@@ -314,6 +314,41 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
+def time_pyramid(pkg, calls=3):
+    """precompute_data_stack_mode (K10 grid subsampling + K9 radius neighbours, the KPConv pyramid of
+    utils/data.py:13-81) for one 3DMatch-sized pair on the GPU, and the same pipeline on the reference's own C++
+    operators (oracle/_ref, compiled from the reference's sources) on one host thread; microseconds per pair."""
+    import time
+    import torch
+    try:
+        sizes, limits = (20000, 18000), [38, 36, 36, 38]
+        p_cpu = torch.cat([pkg.synth.make_dense_cloud(n, 3.0, 800 + b) for b, n in enumerate(sizes)])
+        p_gpu = p_cpu.cuda()
+
+        def once():
+            return pkg.precompute_data_stack_mode(p_gpu, list(sizes), 4, 0.025, 0.0625, limits)
+        once()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(calls):
+            once()
+        b.record()
+        torch.cuda.synchronize()
+        out = {'us_per_pair': a.elapsed_time(b) * 1e3 / calls, 'points': list(sizes), 'stages': 4,
+               'kernels_per_call': 3 * 14 + 10, 'timing': f'eager, {calls} calls, CUDA events (data-dependent shapes are read back)'}
+        sys.path.insert(0, os.path.join(ROOT, 'tests'))
+        import ref_cpu
+        if ref_cpu.available():
+            t0 = time.perf_counter()
+            ref_cpu.precompute_data_stack_mode(p_cpu.numpy(), list(sizes), 4, 0.025, 0.0625, limits)
+            out['reference_cpu'] = {'us_per_pair': (time.perf_counter() - t0) * 1e6, 'kind': 'reference', 'cores': 1,
+                                    'what': 'oracle/_ref: the reference\'s own grid_subsampling / radius_neighbors C++'}
+        return out
+    except Exception as exc:
+        return {'error': f'{type(exc).__name__}: {exc}'}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -454,6 +489,7 @@ def run_b200(args):
         partition = time_partition(pkg, shape_name, n) if world == 1 else None
         transport = time_transport(pkg, shape_name) if world == 1 else None
         procrustes = time_procrustes(pkg, shape_name) if world == 1 else None
+        pyramid = time_pyramid(pkg) if world == 1 else None
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -494,7 +530,8 @@ def run_b200(args):
             'pair_tensor_frac': flops_pair(n, m, cfg) * value / world / 1e12 / peaks['tensor_sustained'],
             'clocks': clocks,
             'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
-                          'log_optimal_transport': transport, 'weighted_procrustes': procrustes},
+                          'log_optimal_transport': transport, 'weighted_procrustes': procrustes,
+                          'collate_pyramid': pyramid},
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)

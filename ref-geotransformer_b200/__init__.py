@@ -9,14 +9,15 @@ from .modules import (  # noqa: F401
     MultiHeadAttention,
     RPEAttentionLayer, RPEConditionalTransformer, RPEMultiHeadAttention, RPETransformerLayer,
     SinusoidalPositionalEmbedding, SuperPointMatching, TransformerLayer, build_act_layer, build_dropout_layer,
-    LearnableLogOptimalTransport, WeightedProcrustes, grid_subsample, point_to_node_partition, radius_search,
+    LearnableLogOptimalTransport, WeightedProcrustes, grid_subsample, point_to_node_partition, precompute_data_stack_mode,
+    radius_search,
     weighted_procrustes)
 
 __all__ = [
     'GeometricTransformer', 'GraphedGeometricTransformer', 'PipelinedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
     'AttentionOutput', 'SinusoidalPositionalEmbedding', 'SuperPointMatching', 'LearnableLogOptimalTransport',
-    'point_to_node_partition', 'WeightedProcrustes', 'weighted_procrustes', 'radius_search', 'grid_subsample', 'ops', 'synth',
+    'point_to_node_partition', 'WeightedProcrustes', 'weighted_procrustes', 'radius_search', 'grid_subsample', 'precompute_data_stack_mode', 'ops', 'synth',
 ]
 
 _REFERENCE_PATCHES = (

@@ -135,13 +135,15 @@ gs_accumulate_kernel(const float* __restrict__ points, int n, float voxel, GsWor
     atomicAdd(&c->count, 1);
 }
 
-// occupied cells per block of GS_SCAN_BLOCK cells
+// occupied cells per tile of GS_SCAN_BLOCK cells (persistent CTAs walk the tiles the grid really has)
 __global__ void __launch_bounds__(GS_SCAN_BLOCK) gs_count_kernel(GsWorkspace w) {
     if (w.grid->overflow) return;
-    const unsigned long long c = (unsigned long long)blockIdx.x * GS_SCAN_BLOCK + threadIdx.x;
-    const bool occ = c < w.grid->cells && w.cells[c].count > 0;
-    const int n = __syncthreads_count(occ);
-    if (threadIdx.x == 0) w.block_counts[blockIdx.x] = (c - threadIdx.x < w.grid->cells) ? (unsigned int)n : 0u;
+    const unsigned long long cells = w.grid->cells;
+    for (unsigned long long tile = blockIdx.x; tile * GS_SCAN_BLOCK < cells; tile += gridDim.x) {
+        const unsigned long long c = tile * GS_SCAN_BLOCK + threadIdx.x;
+        const int n = __syncthreads_count(c < cells && w.cells[c].count > 0);
+        if (threadIdx.x == 0) w.block_counts[tile] = (unsigned int)n;
+    }
 }
 
 // exclusive scan of the block counts (one CTA); s_lengths[b] = total
@@ -190,31 +192,34 @@ __global__ void __launch_bounds__(1024) gs_scan_kernel(int nblocks, GsWorkspace 
 __global__ void __launch_bounds__(GS_SCAN_BLOCK) gs_emit_kernel(GsWorkspace w, float* __restrict__ s_points) {
     __shared__ unsigned int warp_sum[32];
     if (w.grid->overflow) return;
-    const unsigned long long c = (unsigned long long)blockIdx.x * GS_SCAN_BLOCK + threadIdx.x;
-    if (c - threadIdx.x >= w.grid->cells) return;  // whole block outside the grid
-    const bool occ = c < w.grid->cells && w.cells[c].count > 0;
+    const unsigned long long cells = w.grid->cells;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const unsigned int ballot = __ballot_sync(0xffffffffu, occ);
-    if (lane == 0) warp_sum[wid] = __popc(ballot);
-    __syncthreads();
-    if (wid == 0) {
-        unsigned int s = warp_sum[lane];
+    for (unsigned long long tile = blockIdx.x; tile * GS_SCAN_BLOCK < cells; tile += gridDim.x) {
+        const unsigned long long c = tile * GS_SCAN_BLOCK + threadIdx.x;
+        const bool occ = c < cells && w.cells[c].count > 0;
+        const unsigned int ballot = __ballot_sync(0xffffffffu, occ);
+        __syncthreads();  // warp_sum of the previous tile has been read
+        if (lane == 0) warp_sum[wid] = __popc(ballot);
+        __syncthreads();
+        if (wid == 0) {
+            unsigned int s = warp_sum[lane];
 #pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const unsigned int o = __shfl_up_sync(0xffffffffu, s, off);
-            if (lane >= off) s += o;
+            for (int off = 1; off < 32; off <<= 1) {
+                const unsigned int o = __shfl_up_sync(0xffffffffu, s, off);
+                if (lane >= off) s += o;
+            }
+            warp_sum[lane] = s;  // inclusive
         }
-        warp_sum[lane] = s;  // inclusive
+        __syncthreads();
+        if (!occ) continue;
+        const unsigned long long rank = *w.out_base + w.block_counts[tile] + (wid ? warp_sum[wid - 1] : 0u) +
+                                        __popc(ballot & ((1u << lane) - 1u));
+        const GsCell cell = w.cells[c];
+        const float inv = (float)(1.0 / (double)cell.count);
+        s_points[3 * rank] = __fmul_rn((float)cell.sx, inv);
+        s_points[3 * rank + 1] = __fmul_rn((float)cell.sy, inv);
+        s_points[3 * rank + 2] = __fmul_rn((float)cell.sz, inv);
     }
-    __syncthreads();
-    if (!occ) return;
-    const unsigned long long rank = *w.out_base + w.block_counts[blockIdx.x] + (wid ? warp_sum[wid - 1] : 0u) +
-                                    __popc(ballot & ((1u << lane) - 1u));
-    const GsCell cell = w.cells[c];
-    const float inv = (float)(1.0 / (double)cell.count);
-    s_points[3 * rank] = __fmul_rn((float)cell.sx, inv);
-    s_points[3 * rank + 1] = __fmul_rn((float)cell.sy, inv);
-    s_points[3 * rank + 2] = __fmul_rn((float)cell.sz, inv);
 }
 
 __global__ void gs_advance_kernel(GsWorkspace w, const long long* __restrict__ s_length) {
@@ -254,9 +259,9 @@ extern "C" int geotx_grid_subsample(const float* points, const int64_t* host_len
         gs_bounds_kernel<<<1, 1024, 0, st>>>(p, (int)n, voxel_size, (long long)max_cells, w);
         gs_clear_kernel<<<148 * 8, 256, 0, st>>>(w);
         gs_accumulate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(p, (int)n, voxel_size, w);
-        gs_count_kernel<<<nblocks, GS_SCAN_BLOCK, 0, st>>>(w);
+        gs_count_kernel<<<148 * 2, GS_SCAN_BLOCK, 0, st>>>(w);
         gs_scan_kernel<<<1, 1024, 0, st>>>(nblocks, w, (long long*)s_lengths + b);
-        gs_emit_kernel<<<nblocks, GS_SCAN_BLOCK, 0, st>>>(w, s_points);
+        gs_emit_kernel<<<148 * 2, GS_SCAN_BLOCK, 0, st>>>(w, s_points);
         gs_advance_kernel<<<1, 1, 0, st>>>(w, (const long long*)s_lengths + b);
         start += n;
     }

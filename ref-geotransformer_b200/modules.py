@@ -915,3 +915,34 @@ def grid_subsample(points, lengths, voxel_size, max_cells=1 << 24):
         raise RuntimeError(f'grid_subsample: the voxel grid of a batch element has more than max_cells={max_cells} '
                            f'cells at voxel_size={voxel_size}; pass a larger max_cells')
     return buf[:int(s_lengths.sum())], s_lengths
+
+
+@torch.no_grad()
+def precompute_data_stack_mode(points, lengths, num_stages, voxel_size, radius, neighbor_limits, max_cells=1 << 24):
+    """Drop-in for geotransformer/utils/data.py:13-81 (the KPConv pyramid the collate function builds on the host, one
+    nanoflann tree per search) for points that already live on the GPU: same arguments, same dictionary
+    ('points', 'lengths', 'neighbors', 'subsampling', 'upsampling': lists over the stages), built from
+    `grid_subsample` (K10) and `radius_search` (K9).  Point and index tensors are CUDA tensors, lengths stay on the host
+    as in the reference.  Subsampled stages list their voxels in ascending voxel index (the reference: hash-table
+    order), so indices into stages >= 1 are a permutation of the reference's."""
+    assert num_stages == len(neighbor_limits)
+    points_list, lengths_list, neighbors_list, subsampling_list, upsampling_list = [], [], [], [], []
+    lengths = torch.as_tensor(lengths, dtype=torch.int64).cpu()
+    for i in range(num_stages):  # data.py:22-30
+        if i > 0:
+            points, lengths = grid_subsample(points, lengths, voxel_size=voxel_size, max_cells=max_cells)
+        points_list.append(points)
+        lengths_list.append(lengths)
+        voxel_size *= 2
+    for i in range(num_stages):  # data.py:33-72
+        cur_points, cur_lengths = points_list[i], lengths_list[i]
+        neighbors_list.append(radius_search(cur_points, cur_points, cur_lengths, cur_lengths, radius, neighbor_limits[i]))
+        if i < num_stages - 1:
+            sub_points, sub_lengths = points_list[i + 1], lengths_list[i + 1]
+            subsampling_list.append(radius_search(sub_points, cur_points, sub_lengths, cur_lengths, radius,
+                                                  neighbor_limits[i]))
+            upsampling_list.append(radius_search(cur_points, sub_points, cur_lengths, sub_lengths, radius * 2,
+                                                 neighbor_limits[i + 1]))
+        radius *= 2
+    return {'points': points_list, 'lengths': lengths_list, 'neighbors': neighbors_list,
+            'subsampling': subsampling_list, 'upsampling': upsampling_list}

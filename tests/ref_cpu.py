@@ -57,3 +57,27 @@ def grid_subsampling(points, lengths, voxel_size):
     sl = np.empty(len(ln), np.int64)
     lib.geotx_ref_grid_subsampling_copy(_ptr(sp), _ptr(sl))
     return sp, sl
+
+
+def precompute_data_stack_mode(points, lengths, num_stages, voxel_size, radius, neighbor_limits):
+    """geotransformer/utils/data.py:13-81 on the reference's own operators (numpy arrays; the truncation of
+    modules/ops/radius_search.py:24-27 included)."""
+    def search(q, s, ql, sl, r, limit):
+        return radius_neighbors(q, s, ql, sl, r)[:, :limit]
+    points_list, lengths_list, neighbors, subsampling, upsampling = [], [], [], [], []
+    for i in range(num_stages):
+        if i > 0:
+            points, lengths = grid_subsampling(points, lengths, voxel_size)
+        points_list.append(points)
+        lengths_list.append(np.asarray(lengths, np.int64))
+        voxel_size *= 2
+    for i in range(num_stages):
+        cp, cl = points_list[i], lengths_list[i]
+        neighbors.append(search(cp, cp, cl, cl, radius, neighbor_limits[i]))
+        if i < num_stages - 1:
+            sp, sl = points_list[i + 1], lengths_list[i + 1]
+            subsampling.append(search(sp, cp, sl, cl, radius, neighbor_limits[i]))
+            upsampling.append(search(cp, sp, cl, sl, radius * 2, neighbor_limits[i + 1]))
+        radius *= 2
+    return {'points': points_list, 'lengths': lengths_list, 'neighbors': neighbors, 'subsampling': subsampling,
+            'upsampling': upsampling}

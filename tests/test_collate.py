@@ -240,3 +240,48 @@ def test_gpu_grid_subsample_properties_and_errors(pkg):
         pkg.grid_subsample(pts, [19999], 0.05)
     with pytest.raises(RuntimeError):
         pkg.grid_subsample(pts.cpu(), [20000], 0.05)
+
+
+# ---- the whole pyramid (utils/data.py:13-81) ------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_gpu_pyramid_vs_reference_pipeline(pkg):
+    """precompute_data_stack_mode on the GPU against the same pipeline on the reference's own operators, at the 3DMatch
+    settings (4 stages, voxel 0.025, radius 2.5 voxels, neighbour limits of config.py:79-81 scale).  Stage 0 is the
+    input itself: exact.  Later stages hold the same voxels in another order and barycentres that differ in the last
+    bits, so their index lists are compared after mapping through the point correspondence; a row may differ only where
+    a barycentre distance sits within rounding of the radius or of another neighbour's distance (< 0.2 % of rows)."""
+    if not ref_cpu.available():
+        pytest.skip('oracle/_ref not built and /root/reference absent')
+    from scipy.spatial import cKDTree
+    from gpu_common import DEV
+    sizes = (20000, 18000)
+    pts = torch.cat([pkg.synth.make_dense_cloud(n, 3.0, 800 + b) for b, n in enumerate(sizes)])
+    limits = [38, 36, 36, 38]
+    want = ref_cpu.precompute_data_stack_mode(pts.numpy(), list(sizes), 4, 0.025, 0.0625, limits)
+    got = pkg.precompute_data_stack_mode(pts.to(DEV), torch.tensor(sizes), 4, 0.025, 0.0625, limits)
+    assert set(got) == set(want)
+    perm = []  # perm[i][our index] = the reference's index of the same point (with the sentinel mapped to the sentinel)
+    for i in range(4):
+        assert np.array_equal(got['lengths'][i].numpy(), want['lengths'][i])
+        a, b = got['points'][i].cpu().numpy(), want['points'][i]
+        if i == 0:
+            assert np.array_equal(a, b)
+            m = np.arange(len(a))
+        else:
+            d, m = cKDTree(b).query(a)
+            assert d.max() <= 1e-5 and len(np.unique(m)) == len(a)
+        perm.append(np.concatenate([m, [len(a)]]))
+
+    def mismatch(ours, theirs, q_perm, s_perm):
+        ours = s_perm[ours.cpu().numpy()]
+        rows = np.empty_like(theirs)
+        rows[q_perm[:-1]] = ours[:, :theirs.shape[1]] if ours.shape[1] >= theirs.shape[1] else np.pad(
+            ours, ((0, 0), (0, theirs.shape[1] - ours.shape[1])), constant_values=s_perm[-1])
+        return float((np.sort(rows, 1) != np.sort(theirs, 1)).any(1).mean())
+
+    assert_same_neighbors(got['neighbors'][0].cpu().numpy(), want['neighbors'][0], pts.numpy(), pts.numpy(), len(pts))
+    for i in range(4):
+        assert mismatch(got['neighbors'][i], want['neighbors'][i], perm[i], perm[i]) < 2e-3
+        if i < 3:
+            assert mismatch(got['subsampling'][i], want['subsampling'][i], perm[i + 1], perm[i]) < 2e-3
+            assert mismatch(got['upsampling'][i], want['upsampling'][i], perm[i], perm[i + 1]) < 2e-3

@@ -153,6 +153,16 @@ def main():
             ref_cpu.grid_subsampling(p_cpu.numpy(), list(sizes), voxel)
             row['reference_cpu_operator_us'] = (time.perf_counter() - t0) * 1e6
         res[f'grid_subsample_{sizes[0]}'] = row
+    sizes, limits = (20000, 18000), [38, 36, 36, 38]
+    p_cpu = torch.cat([pkg.synth.make_dense_cloud(n, 3.0, 800 + b) for b, n in enumerate(sizes)])
+    p_gpu = p_cpu.cuda()
+    row = {'us': eager(lambda: pkg.precompute_data_stack_mode(p_gpu, list(sizes), 4, 0.025, 0.0625, limits), iters=5),
+           'points': list(sizes), 'stages': 4, 'note': 'eager (14 data-dependent shapes are read back), CUDA events'}
+    if with_torch and ref_cpu.available():
+        t0 = time.perf_counter()
+        ref_cpu.precompute_data_stack_mode(p_cpu.numpy(), list(sizes), 4, 0.025, 0.0625, limits)
+        row['reference_cpu_operators_us'] = (time.perf_counter() - t0) * 1e6
+    res['pyramid_3dmatch'] = row
     print(json.dumps(res))
 
 
