@@ -34,6 +34,8 @@ WORKLOADS = {
     '3dmatch_512': ('3dmatch', 512, 512),
     '3dmatch_2048': ('3dmatch', 2048, 2048),
     '3dmatch_4096': ('3dmatch', 4096, 4096),   # configs[3] sweep point named by north_star
+    '3dmatch_8192': ('3dmatch', 8192, 8192),   # configs[3]: E = 34 GB per cloud, stored
+    '3dmatch_16384': ('3dmatch', 16384, 16384),  # configs[3]: E = 137 GB per cloud: never stored, regenerated per 'self' block
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of one gse_embed_tc_kernel launch (ncu --set full, profiles/r01_ncu_k2_*)
 K2_NCU_TRAFFIC_BYTES = {"3dmatch_1024": 483.98e6}  # profiles/r01_ncu_k2_v4.txt
@@ -56,14 +58,15 @@ def flops_gse(n, C, k):
     return 2.0 * n * n * C * C * (1 + k)
 
 
-def flops_pair(n, m, cfg):
-    """SURVEY.md 8d F_min (proj_p folded, E stored)."""
+def flops_pair(n, m, cfg, regenerate=False):
+    """SURVEY.md 8d F_min (proj_p folded, E stored); regenerate=True: E is rebuilt for every 'self' block, so the
+    embedding flops are executed Ls times ("add (Ls-1) gse and say so")."""
     C, H, k = cfg['hidden_dim'], cfg['num_heads'], cfg['angle_k']
     Ls = sum(b == 'self' for b in cfg['blocks'])
     Lc = len(cfg['blocks']) - Ls
     f = 0.0
     for x in (n, m):
-        f += flops_gse(x, C, k) + Ls * (16 * x * C * C + 2 * x * C * C + 2 * x * x * C * H + 4 * x * x * C)
+        f += (Ls if regenerate else 1) * flops_gse(x, C, k) + Ls * (16 * x * C * C + 2 * x * C * C + 2 * x * x * C * H + 4 * x * x * C)
         f += 2 * x * cfg['input_dim'] * C + 2 * x * C * cfg['output_dim']
     f += Lc * ((12 * n * C * C + 4 * m * C * C + 4 * n * m * C) + (12 * m * C * C + 4 * n * C * C + 4 * n * m * C))
     return f
@@ -371,6 +374,9 @@ def run_b200(args):
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     torch.manual_seed(pkg.synth.SEED)
     model = pkg.GeometricTransformer(**cfg).to(dev).eval()  # default nn.Linear init under seed 7351 = oracle init
+    big = max(n, m) >= 8192  # E of both clouds: 69 GB at 8192 (stored, one graph alive at a time), 275 GB at 16384
+    if os.environ.get('GEOTX_E_MODE') is None:
+        model.e_mode = 'regenerate' if 2 * max(n, m) ** 2 * C * 2 > 140e9 else 'store'
 
     # a small rotation of distinct pairs per rank; E (n*n*C*2 bytes per cloud) alone exceeds the 126 MB L2
     n_pairs = 4
@@ -442,6 +448,8 @@ def run_b200(args):
                 k2_ms, k2_launch_flops = in_graph, in_graph_flops
                 k2_timing = 'CUDA events recorded inside the CUDA graph of the forward, around every launch'
             del probe
+            if big:
+                torch.cuda.empty_cache()
         except Exception as exc:  # older torch: no external events in graphs
             k2_timing += f' (in-graph events unavailable: {type(exc).__name__})'
         external[0] = False
@@ -468,7 +476,11 @@ def run_b200(args):
 
         # ---- end to end: host (pinned) inputs -> device -> forward -> host outputs, every step, through the serving
         #      API (PipelinedGeometricTransformer: the upload of pair p+1 / download of pair p-1 overlap pair p) ----
-        pipe = pkg.PipelinedGeometricTransformer(model, *resident[0], depth=2)
+        depth = 1 if big else 2
+        if big:  # one set of graph-private buffers at a time
+            del fast
+            torch.cuda.empty_cache()
+        pipe = pkg.PipelinedGeometricTransformer(model, *resident[0], depth=depth)
         for o in pipe.map(host[s % n_pairs] for s in range(3)):
             pass
         barrier()
@@ -484,6 +496,9 @@ def run_b200(args):
 
         # ---- next row: the path's consumer (F.normalize + SuperPointMatching), timed alone on the
         #      outputs of the last pair; not part of `value` ----
+        if big:
+            del pipe
+            torch.cuda.empty_cache()
         matching = time_matching(pkg, last) if world == 1 else None
         shape_name = WORKLOADS[args.workload][0]
         partition = time_partition(pkg, shape_name, n) if world == 1 else None
@@ -507,13 +522,14 @@ def run_b200(args):
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
             'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': C, 'num_heads': cfg['num_heads'],
                        'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1, 'launch': 'one CUDA graph replay per step',
+                       'e_storage': model.last_e_mode + (f' (E never stored: rebuilt for each of the {sum(b == "self" for b in cfg["blocks"])} self blocks in {model.regenerate_slab_bytes >> 20} MiB row slabs; pair_tflops counts those passes)' if model.last_e_mode == 'regenerate' else ' (one embedding pass per cloud)'),
                        'l2_slab_bytes': model.l2_slab_bytes, 'first_block_scores_fused_into_embedding': bool(model.fuse_scores),
                        'l2': f'inputs larger than L2: E is {n * n * C * 2 / 1e6:.0f} MB per cloud, '
                              f'{n_pairs} distinct pairs rotated',
                        'sharding': f'by pair over {world} GPU(s); one all_gather of outputs'},
             'e2e': {'value': world * args.steps / (e2e_ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h,
-                    'api': 'PipelinedGeometricTransformer.map over pinned host pairs, depth 2, wall clock'},
+                    'api': f'PipelinedGeometricTransformer.map over pinned host pairs, depth {depth}, wall clock'},
             'gpu_launches': launches,
             'roofline': {'kernel': 'gse_embed_tc_kernel (geotx_gse_embed)', 'bound': 'tensor', 'achieved': achieved,
                          'peak': peaks['tensor_sustained'], 'unit': 'TFLOP/s',
@@ -526,8 +542,9 @@ def run_b200(args):
                          'timing': k2_timing + '; the value pass replays the identical kernels from a CUDA graph; '
                                    'share_of_step = timed launches per step / ms_per_step'},
             'eager_ms_per_step': eager_ms / args.steps,
-            'pair_tflops': flops_pair(n, m, cfg) / 1e12,
-            'pair_tensor_frac': flops_pair(n, m, cfg) * value / world / 1e12 / peaks['tensor_sustained'],
+            'pair_tflops': flops_pair(n, m, cfg, model.last_e_mode == 'regenerate') / 1e12,
+            'pair_tflops_min': flops_pair(n, m, cfg) / 1e12,
+            'pair_tensor_frac': flops_pair(n, m, cfg, model.last_e_mode == 'regenerate') * value / world / 1e12 / peaks['tensor_sustained'],
             'clocks': clocks,
             'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
                           'log_optimal_transport': transport, 'weighted_procrustes': procrustes,

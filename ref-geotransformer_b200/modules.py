@@ -431,12 +431,34 @@ class StreamedEmbedding:
     three full HBM reads of E (one per 'self' block); the slab still drains to HBM for the later blocks.
     `slab_bytes` = 0 produces E in one launch (the scores kernel then reads it from HBM as in the later blocks)."""
 
-    def __init__(self, embedding, geom, dtype, slab_bytes, fuse_scores=False):
+    def __init__(self, embedding, geom, dtype, slab_bytes, fuse_scores=False, regenerate_bytes=0):
         self.embedding, self.geom, self.dtype, self.slab_bytes = embedding, geom, dtype, slab_bytes
         self.fuse_scores = fuse_scores
         self.E = None
+        # > 0: E is NEVER stored.  Every 'self' block regenerates it in query-row slabs of this many bytes, each slab
+        # consumed at once by the scores kernel (for clouds whose n^2 C bytes do not fit the GPU next to the other
+        # cloud's: 137 GB per cloud at n = 16384).  Costs (number of 'self' blocks - 1) extra embedding passes.
+        self.regenerate_bytes = regenerate_bytes
+        self._slab = None
+
+    def regenerated_scores(self, qt):
+        """qt (1,H,n,C) -> scores_p (1,H,n,n); E exists one slab at a time."""
+        n, C = self.geom.n, self.embedding.hidden_dim
+        row_bytes = n * C * (4 if self.dtype == torch.float32 else 2)
+        rows = max(1, min(n, self.regenerate_bytes // row_bytes))
+        if self._slab is None:
+            self._slab = torch.empty(1, rows, n, C, dtype=self.dtype, device=qt.device)
+        scores_p = torch.empty(1, qt.shape[1], n, n, dtype=torch.float32, device=qt.device)
+        for r0 in range(0, n, rows):
+            rc = min(rows, n - r0)
+            self.embedding.embed(self.geom, self.dtype, r0, rc, out=self._slab[:, :rc])
+            ops.rpe_scores(qt, self._slab[:, :rc], n=n, row_begin=r0, out=scores_p)
+        return scores_p
 
     def materialise(self):
+        if self.regenerate_bytes > 0:
+            raise RuntimeError('this embedding is in regenerate mode (it does not fit in memory); only the fused '
+                               'single-pair schedule can consume it')
         if self.E is None:
             self.E = self.embedding.embed(self.geom, self.dtype)
         return self.E
@@ -536,15 +558,17 @@ class RPEConditionalTransformer(nn.Module):
                 hidden = x.new_empty(1, T, C)
                 cur = side = None
                 streamed = any(isinstance(e, StreamedEmbedding) for e in embs)
-                if streamed and not any(isinstance(e, StreamedEmbedding) and (e.fuse_scores or e.slab_bytes > 0)
-                                        for e in embs):
+                if streamed and not any(isinstance(e, StreamedEmbedding) and
+                                        (e.fuse_scores or e.slab_bytes > 0 or e.regenerate_bytes > 0) for e in embs):
                     # plain schedule: both embedding kernels back to back, each with the whole GPU to itself
                     embs = [e.materialise() if isinstance(e, StreamedEmbedding) else e for e in embs]
                     streamed = False
                 for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
                     emb = embs[which]
                     qt = y[:, lo:hi, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
-                    if isinstance(emb, StreamedEmbedding):
+                    if isinstance(emb, StreamedEmbedding) and emb.regenerate_bytes > 0:
+                        scores_p = emb.regenerated_scores(qt)  # E of this cloud is never stored
+                    elif isinstance(emb, StreamedEmbedding):
                         scores_p = emb.first_scores(qt)  # the first block interleaves with the embedding kernel
                         embs[which] = emb.E
                     else:
@@ -639,6 +663,30 @@ class GeometricTransformer(nn.Module):
         # extra epilogue work costs the embedding kernel more than the pass saves (measured: 0.50 -> 0.64 ms per
         # cloud at n = 1024 against 0.094 ms saved), so it is opt-in
         self.fuse_scores = os.environ.get('GEOTX_FUSE_SCORES', '0') != '0'
+        # E storage: 'store' keeps both clouds' E for all 'self' blocks (one embedding pass per cloud); 'regenerate'
+        # never stores E (one pass per cloud per 'self' block, in slabs of `regenerate_slab_bytes`); 'auto' stores
+        # when both E fit into 80 % of the free device memory.
+        self.e_mode = os.environ.get('GEOTX_E_MODE', 'auto')
+        self.regenerate_slab_bytes = int(os.environ.get('GEOTX_REGENERATE_SLAB_BYTES', 1 << 30))
+        self.last_e_mode = None
+        self._auto_mode = {}  # (n, m, dtype) -> decision of 'auto', taken on the first (eager) call of that shape
+
+    def _regenerate_bytes(self, n, m, e_dtype, device, batch):
+        if self.e_mode not in ('auto', 'store', 'regenerate'):
+            raise ValueError(f"GEOTX_E_MODE must be 'auto', 'store' or 'regenerate', got {self.e_mode!r}")
+        if self.e_mode == 'store' or batch != 1 or 'self' not in self.transformer.blocks:
+            return 0
+        if self.e_mode == 'auto':
+            key = (n, m, e_dtype)
+            if key not in self._auto_mode:  # never queried while a CUDA graph is being captured (shape seen before)
+                item = 4 if e_dtype == torch.float32 else 2
+                need = (n * n + m * m) * self.embedding.hidden_dim * item
+                free, _ = torch.cuda.mem_get_info(device)
+                reusable = torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
+                self._auto_mode[key] = need <= 0.8 * (free + reusable)
+            if self._auto_mode[key]:
+                return 0
+        return self.regenerate_slab_bytes
 
     def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
         _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
@@ -673,8 +721,13 @@ class GeometricTransformer(nn.Module):
             cur.wait_stream(side)
             for t in (src_geom.buf, src_geom.knn) + (() if one_buffer else (src_feats,)):
                 t.record_stream(cur)  # allocated on the side stream, consumed (and later freed) on this one
-            ref_embeddings = StreamedEmbedding(self.embedding, ref_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores)
-            src_embeddings = StreamedEmbedding(self.embedding, src_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores)
+            regen = self._regenerate_bytes(ref_points.shape[1], src_points.shape[1], e_dtype, ref_points.device,
+                                           ref_points.shape[0])
+            self.last_e_mode = 'regenerate' if regen else 'store'
+            ref_embeddings = StreamedEmbedding(self.embedding, ref_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores,
+                                               regen)
+            src_embeddings = StreamedEmbedding(self.embedding, src_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores,
+                                               regen)
             ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
                                                     masks0=ref_masks, masks1=src_masks)
             if ref_feats.shape[0] == 1 and ref_feats.data_ptr() + ref_feats.numel() * 4 == src_feats.data_ptr():

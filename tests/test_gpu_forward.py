@@ -139,3 +139,29 @@ def test_first_block_scores_fused_into_the_embedding_kernel(pkg, oracle):
         assert rel(f0, exp0) <= TOL_BF16 and rel(f1, exp1) <= TOL_BF16
         print(f'{shape}: fused vs separate {rel(f0, u0):.2e}, fused vs oracle {rel(f0, exp0):.2e}')
     assert pkg._abi.watchdog() is None
+
+
+def test_regenerated_embedding_equals_stored(pkg, oracle):
+    """E-storage modes (clouds whose n^2 C bytes do not fit, the N = 16384 sweep point): 'regenerate'
+    rebuilds E in row slabs for every 'self' block and never stores it.  Same kernels on the same values, so the
+    outputs must be bit-identical to the stored mode -- eagerly and through the CUDA-graph wrapper."""
+    cfg = dict(pkg.synth.CONFIGS['3dmatch'])
+    rp, sp, rf, sf, _ = pkg.synth.make_tie_free_pair('3dmatch', 640, 512, seed=pkg.synth.SEED)
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    model = build_model(pkg, cfg, sd)
+    args = [t.to(DEV) for t in (rp, sp, rf, sf)]
+    with torch.no_grad():
+        model.e_mode = 'store'
+        want = [t.clone() for t in model(*args)]
+        assert model.last_e_mode == 'store'
+        model.e_mode = 'regenerate'
+        model.regenerate_slab_bytes = 100 * 640 * 256 * 2  # 100 query rows per slab: 7 / 6 slabs, ragged tails
+        got = [t.clone() for t in model(*args)]
+        assert model.last_e_mode == 'regenerate'
+        graphed = pkg.GraphedGeometricTransformer(model, *args)
+        replay = [t.clone() for t in graphed(*args)]
+        model.e_mode = 'auto'
+        model(*args)
+        assert model.last_e_mode == 'store'  # 0.3 GB fits
+    for a, b, c in zip(want, got, replay):
+        assert torch.equal(a, b) and torch.equal(a, c)
