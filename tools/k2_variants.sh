@@ -11,7 +11,7 @@ for v in "$@"; do
     case $f in *=*) flags="$flags -DK2_$f";; *) flags="$flags -DK2_DBG_$f";; esac
   done
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Xcompiler -fPIC -shared $flags \
-    $SRC/abi.cu $SRC/k1_knn.cu $SRC/k2_gse_embed_fp32.cu $SRC/k2_gse_embed.cu $SRC/k3_rpe_scores.cu $SRC/k3_attention.cu $SRC/k4_add_layernorm.cu \
+    $SRC/*.cu \
     -o tools/bin/variants/lib_$v.so -lcudart &
 done
 wait
