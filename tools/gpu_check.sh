@@ -14,3 +14,7 @@ tail -n 5 gpurun_out/smoke.log
 timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.log 2>&1
 echo "bench exit $?" | tee -a gpurun_out/summary.txt
 tail -n 3 gpurun_out/bench.log
+# launch list of the same bench command (ncu serialises and runs cold: shares, not absolute times)
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/launches.csv \
+  python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1
+echo "ncu launches exit $?" | tee -a gpurun_out/summary.txt
