@@ -155,3 +155,35 @@ def make_dense_cloud(n, extent=3.0, seed=SEED, jitter=0.005):
         a, b = [(1, 2), (0, 2), (0, 1)][w]
         pts[m, a], pts[m, b], pts[m, w] = uv[m, 0], uv[m, 1], off[m]
     return pts.contiguous()
+
+
+def make_lgr_inputs(num_patches=256, K=64, seed=SEED, outlier_patches=0.3, noise=0.01, valid_frac=0.7):
+    """Inputs of LocalGlobalRegistration.forward as model.py:198-205 feeds it: per patch correspondence K reference and
+    K source points (src = the reference points under ONE global rigid motion, permuted, plus noise; in a fraction of
+    the patches the source points are unrelated: wrong superpoint matches), validity masks, and a (P,K,K) matrix of
+    log matching scores that is confident (0.3 ... 0.9) on the true point matches and near zero elsewhere.
+    Returns ref_knn_points, src_knn_points, ref_knn_masks, src_knn_masks, score_mat, global_scores, transform."""
+    gen = torch.Generator().manual_seed(seed)
+    centers = torch.rand(num_patches, 1, 3, generator=gen) * 3.0
+    ref = centers + (torch.rand(num_patches, K, 3, generator=gen) - 0.5) * 0.3
+    T = torch.eye(4)
+    T[:3, :3] = _rotation(gen, 60.0).float()
+    T[:3, 3] = torch.rand(3, generator=gen) - 0.5
+    # ref = R src + t  =>  src = R^T (ref - t)
+    src_true = (ref - T[:3, 3]) @ T[:3, :3]
+    perm = torch.stack([torch.randperm(K, generator=gen) for _ in range(num_patches)])  # src slot j holds ref perm[j]
+    src = torch.gather(src_true, 1, perm[:, :, None].expand(-1, -1, 3)) + noise * torch.randn(num_patches, K, 3, generator=gen)
+    bad = torch.rand(num_patches, generator=gen) < outlier_patches
+    src[bad] = torch.rand(int(bad.sum()), K, 3, generator=gen) * 3.0
+    nr = ((torch.rand(num_patches, generator=gen) * (1 - valid_frac) + valid_frac) * K).long().clamp(3, K)
+    ns = ((torch.rand(num_patches, generator=gen) * (1 - valid_frac) + valid_frac) * K).long().clamp(3, K)
+    ref_masks = torch.arange(K)[None, :] < nr[:, None]
+    src_masks = torch.arange(K)[None, :] < ns[:, None]
+    prob = torch.rand(num_patches, K, K, generator=gen) * 0.02  # background
+    conf = torch.rand(num_patches, K, generator=gen) * 0.6 + 0.3
+    weak = torch.rand(num_patches, K, generator=gen) < 0.25      # a quarter of the true matches stay below the threshold
+    conf = torch.where(weak, conf * 0.1, conf)
+    prob[torch.arange(num_patches)[:, None], perm, torch.arange(K)[None, :].expand(num_patches, -1)] = conf
+    global_scores = torch.rand(num_patches, generator=gen) * 0.5 + 0.5
+    return (ref.contiguous(), src.contiguous(), ref_masks.contiguous(), src_masks.contiguous(),
+            torch.log(prob).contiguous(), global_scores, T)
