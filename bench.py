@@ -317,6 +317,38 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
+def time_registration(pkg, shape, calls=10, replays=5):
+    """geotx_local_global_registration (5 kernels, K11) on one pair's 256 patch score matrices
+    (local_global_registration.py:145-235 as model.py:198-205 calls it); us per pair on the GPU, and the oracle's torch
+    restatement of the reference module on the host cores for the same input."""
+    import time
+    import torch
+    try:
+        K, k = (128, 2) if shape == 'kitti' else (64, 3)
+        inp = pkg.synth.make_lgr_inputs(num_patches=256, K=K, seed=pkg.synth.SEED)
+        dev = [t.cuda() for t in inp[:6]]
+
+        def once():
+            return pkg.ops.local_global_registration(*dev[:5], None, k, 0.1)
+        us = _graph_time_us(once, calls, replays)
+        count = int(once()[3].item())
+        out = {'us_per_pair': us, 'patch_pairs': 256, 'points_per_patch': K, 'topk': k, 'correspondences': count,
+               'kernels_per_call': 5, 'host_synchronisations': 0, 'dtype': 'f32 (SVD in f64)',
+               'timing': f'{calls} pairs captured in one CUDA graph, {replays} replays, CUDA events'}
+        if os.path.join(ROOT, 'oracle') not in sys.path:
+            sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+        import geotx_oracle
+        with torch.no_grad():
+            geotx_oracle.local_global_registration(*inp[:6], k=k, acceptance_radius=0.1)
+            t0 = time.perf_counter()
+            geotx_oracle.local_global_registration(*inp[:6], k=k, acceptance_radius=0.1)
+            out['oracle_cpu_us'] = (time.perf_counter() - t0) * 1e6
+            out['oracle_cpu_threads'] = torch.get_num_threads()
+        return out
+    except Exception as exc:
+        return {'error': f'{type(exc).__name__}: {exc}'}
+
+
 def time_pyramid(pkg, calls=3):
     """precompute_data_stack_mode (K10 grid subsampling + K9 radius neighbours, the KPConv pyramid of
     utils/data.py:13-81) for one 3DMatch-sized pair on the GPU, and the same pipeline on the reference's own C++
@@ -505,6 +537,7 @@ def run_b200(args):
         transport = time_transport(pkg, shape_name) if world == 1 else None
         procrustes = time_procrustes(pkg, shape_name) if world == 1 else None
         pyramid = time_pyramid(pkg) if world == 1 else None
+        registration = time_registration(pkg, shape_name) if world == 1 else None
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -548,7 +581,7 @@ def run_b200(args):
             'clocks': clocks,
             'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
                           'log_optimal_transport': transport, 'weighted_procrustes': procrustes,
-                          'collate_pyramid': pyramid},
+                          'local_global_registration': registration, 'collate_pyramid': pyramid},
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)

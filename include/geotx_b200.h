@@ -231,6 +231,28 @@ int64_t geotx_grid_subsample_workspace_bytes(int64_t max_cells);
 int geotx_grid_subsample(const float* points, const int64_t* host_lengths, int batch, float voxel_size, float* s_points,
                          int64_t* s_lengths, void* workspace, int64_t max_cells, void* stream);
 
+/* K11 LocalGlobalRegistration on the device.  Replaces
+ * geotransformer/modules/geotransformer/local_global_registration.py:49-235 (use_dustbin = False,
+ * correspondence_limit = None, as in every shipped config).
+ *   ref_knn_points, src_knn_points  (P, K, 3) f32 patch points        ref_knn_masks, src_knn_masks  (P, K) u8
+ *   score_mat        f32 log-likelihoods, element (b, i, j) at b*score_batch_stride + i*score_row_stride + j (so the
+ *                    reference's matching_scores[:, :-1, :-1] view is passed without a copy)
+ *   global_scores    (P,) f32 or NULL (use_global_score = False)
+ *   topk             the module's k (<= 8), K <= 128
+ *   outputs          ref_corr_points / src_corr_points (cap, 3) f32 and corr_scores (cap,) f32 with
+ *                    cap = 2 * P * K * topk, filled in torch.nonzero order (patch, i, j) for count_out[0] entries;
+ *                    transform_out 16 f32 (row-major 4x4)
+ *   workspace        geotx_lgr_workspace_bytes(P, K) bytes, 256-byte aligned
+ * No host synchronisation; equal scores inside a top-k are ordered by index. */
+int64_t geotx_lgr_workspace_bytes(int num_patches, int K);
+int geotx_local_global_registration(const float* ref_knn_points, const float* src_knn_points,
+                                    const uint8_t* ref_knn_masks, const uint8_t* src_knn_masks, const float* score_mat,
+                                    int64_t score_batch_stride, int64_t score_row_stride, const float* global_scores,
+                                    int num_patches, int K, int topk, float acceptance_radius, int mutual,
+                                    float confidence_threshold, int correspondence_threshold, int num_refinement_steps,
+                                    float* ref_corr_points, float* src_corr_points, float* corr_scores,
+                                    int32_t* count_out, float* transform_out, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,7 @@ from .modules import (  # noqa: F401
     MultiHeadAttention,
     RPEAttentionLayer, RPEConditionalTransformer, RPEMultiHeadAttention, RPETransformerLayer,
     SinusoidalPositionalEmbedding, SuperPointMatching, TransformerLayer, build_act_layer, build_dropout_layer,
-    LearnableLogOptimalTransport, WeightedProcrustes, grid_subsample, point_to_node_partition, precompute_data_stack_mode,
+    LearnableLogOptimalTransport, LocalGlobalRegistration, WeightedProcrustes, grid_subsample, point_to_node_partition, precompute_data_stack_mode,
     radius_search,
     weighted_procrustes)
 
@@ -17,6 +17,7 @@ __all__ = [
     'GeometricTransformer', 'GraphedGeometricTransformer', 'PipelinedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
     'AttentionOutput', 'SinusoidalPositionalEmbedding', 'SuperPointMatching', 'LearnableLogOptimalTransport',
+    'LocalGlobalRegistration',
     'point_to_node_partition', 'WeightedProcrustes', 'weighted_procrustes', 'radius_search', 'grid_subsample', 'precompute_data_stack_mode', 'ops', 'synth',
 ]
 
@@ -24,7 +25,7 @@ _REFERENCE_PATCHES = (
     # (module of the reference, names it exports that this package re-implements)
     ('geotransformer.modules.geotransformer.geotransformer', ('GeometricTransformer', 'GeometricStructureEmbedding')),
     ('geotransformer.modules.geotransformer', ('GeometricTransformer', 'GeometricStructureEmbedding',
-                                               'SuperPointMatching')),
+                                               'SuperPointMatching', 'LocalGlobalRegistration')),
     ('geotransformer.modules.geotransformer.superpoint_matching', ('SuperPointMatching',)),
     ('geotransformer.modules.transformer', ('RPEConditionalTransformer', 'RPETransformerLayer', 'TransformerLayer',
                                             'SinusoidalPositionalEmbedding')),
@@ -34,7 +35,8 @@ _REFERENCE_PATCHES = (
     ('geotransformer.modules.sinkhorn', ('LearnableLogOptimalTransport',)),
     ('geotransformer.modules.registration.procrustes', ('weighted_procrustes', 'WeightedProcrustes')),
     ('geotransformer.modules.registration', ('weighted_procrustes', 'WeightedProcrustes')),
-    ('geotransformer.modules.geotransformer.local_global_registration', ('WeightedProcrustes',)),
+    ('geotransformer.modules.geotransformer.local_global_registration', ('WeightedProcrustes',
+                                                                        'LocalGlobalRegistration')),
 )
 _saved = {}
 

@@ -39,6 +39,9 @@ SIGNATURES = {
     'geotx_radius_neighbors': (_i, [_p, _p, _p, _p, _i, _f, _i, _p, _p, _p, _p]),
     'geotx_grid_subsample_workspace_bytes': (_i64, [_i64]),
     'geotx_grid_subsample': (_i, [_p, _p, _i, _f, _p, _p, _p, _i64, _p]),
+    'geotx_lgr_workspace_bytes': (_i64, [_i, _i]),
+    'geotx_local_global_registration': (_i, [_p, _p, _p, _p, _p, _i64, _i64, _p, _i, _i, _i, _f, _i, _f, _i, _i,
+                                             _p, _p, _p, _p, _p, _p, _p]),
 }
 
 GEOTX_F32 = 0
@@ -49,7 +52,8 @@ GEOTX_F16 = 2
 KERNELS_PER_CALL = {'geotx_gse_knn': 2,  # pack_points + knn
                     'geotx_superpoint_matching': 10,  # prepare, scores, sums, 6 select passes, collect
                     'geotx_point_to_node_partition': 4,  # assign, offsets, scatter, select
-                    'geotx_grid_subsample': 14}  # 7 per batch element (bounds, clear, accumulate, count, scan, emit, advance)
+                    'geotx_grid_subsample': 14,
+                    'geotx_local_global_registration': 5}  # 7 per batch element (bounds, clear, accumulate, count, scan, emit, advance)
 
 _lib = None
 launch_count = 0  # hand-written kernels launched through this binding so far

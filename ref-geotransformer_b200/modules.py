@@ -941,6 +941,45 @@ class WeightedProcrustes(nn.Module):
                                    eps=self.eps, return_transform=self.return_transform)
 
 
+class LocalGlobalRegistration(nn.Module):
+    """Drop-in for geotransformer/modules/geotransformer/local_global_registration.py:11-235: same
+    constructor, same forward arguments and results -- (ref_corr_points (C,3), src_corr_points (C,3), corr_scores (C,),
+    estimated_transform (4,4)).  One launch sequence of five kernels (K11) replaces the reference's scatter / nonzero /
+    host-side chunk loop / six Procrustes calls with a host SVD each; the only synchronisation is the read of C that
+    sizes the returned views (`ops.local_global_registration` is the fixed-capacity form without it).
+    use_dustbin = True and correspondence_limit are not shipped by any configuration (experiments/*/config.py:116-125)
+    and raise."""
+
+    def __init__(self, k, acceptance_radius, mutual=True, confidence_threshold=0.05, use_dustbin=False,
+                 use_global_score=False, correspondence_threshold=3, correspondence_limit=None,
+                 num_refinement_steps=5):
+        super().__init__()
+        if use_dustbin:
+            raise NotImplementedError('LocalGlobalRegistration: use_dustbin=True is not built on the B200 path')
+        if correspondence_limit is not None:
+            raise NotImplementedError('LocalGlobalRegistration: correspondence_limit is not built on the B200 path')
+        self.k = k
+        self.acceptance_radius = acceptance_radius
+        self.mutual = mutual
+        self.confidence_threshold = confidence_threshold
+        self.use_dustbin = use_dustbin
+        self.use_global_score = use_global_score
+        self.correspondence_threshold = correspondence_threshold
+        self.correspondence_limit = correspondence_limit
+        self.num_refinement_steps = num_refinement_steps
+
+    @torch.no_grad()
+    def forward(self, ref_knn_points, src_knn_points, ref_knn_masks, src_knn_masks, score_mat, global_scores):
+        ref_corr, src_corr, scores, count, transform = ops.local_global_registration(
+            ref_knn_points.contiguous(), src_knn_points.contiguous(), ref_knn_masks.contiguous(),
+            src_knn_masks.contiguous(), score_mat if score_mat.stride(-1) == 1 else score_mat.contiguous(),
+            global_scores.contiguous() if self.use_global_score else None, self.k, self.acceptance_radius,
+            mutual=self.mutual, confidence_threshold=self.confidence_threshold,
+            correspondence_threshold=self.correspondence_threshold, num_refinement_steps=self.num_refinement_steps)
+        c = int(count.item())
+        return ref_corr[:c], src_corr[:c], scores[:c], transform
+
+
 @torch.no_grad()
 def radius_search(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit):
     """Drop-in for geotransformer/modules/ops/radius_search.py:7-27 for points that already live on

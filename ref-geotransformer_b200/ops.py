@@ -403,3 +403,52 @@ def grid_subsample(points, lengths, voxel_size, max_cells=1 << 24):
     _abi.call('geotx_grid_subsample', _p(points), ln, len(vals), float(voxel_size), _p(s_points), _p(s_lengths),
               _p(_GS_WORK[key]), int(max_cells), _stream())
     return s_points, s_lengths
+
+
+def local_global_registration(ref_knn_points, src_knn_points, ref_knn_masks, src_knn_masks, score_mat, global_scores,
+                              k, acceptance_radius, mutual=True, confidence_threshold=0.05,
+                              correspondence_threshold=3, num_refinement_steps=5):
+    """modules/geotransformer/local_global_registration.py:145-235 on the device.  ref_knn_points, src_knn_points
+    (P,K,3) fp32; ref_knn_masks, src_knn_masks (P,K) bool; score_mat (P,K,K) fp32 log-likelihoods whose last dimension
+    is dense (the reference's matching_scores[:, :-1, :-1] view is taken as it is); global_scores (P,) fp32 or None.
+    Returns (ref_corr_points (cap,3), src_corr_points (cap,3), corr_scores (cap,), count int32 (1,), transform (4,4))
+    with cap = 2*P*K*k; the first count[0] rows are the correspondences in torch.nonzero order.  Nothing
+    synchronises."""
+    _check(ref_knn_points, 'ref_knn_points', torch.float32, 3)
+    _check(src_knn_points, 'src_knn_points', torch.float32, 3)
+    P, K, _ = ref_knn_points.shape
+    if tuple(ref_knn_points.shape) != (P, K, 3) or tuple(src_knn_points.shape) != (P, K, 3):
+        raise RuntimeError(f'knn points must both be (P, K, 3), got {tuple(ref_knn_points.shape)} and '
+                           f'{tuple(src_knn_points.shape)}')
+    masks = []
+    for name, m in (('ref_knn_masks', ref_knn_masks), ('src_knn_masks', src_knn_masks)):
+        _check(m, name, None, 2)
+        if m.dtype not in (torch.bool, torch.uint8) or tuple(m.shape) != (P, K):
+            raise RuntimeError(f'{name} must be bool {(P, K)}, got {m.dtype} {tuple(m.shape)}')
+        masks.append(m.view(torch.uint8) if m.dtype == torch.bool else m)
+    if not isinstance(score_mat, torch.Tensor) or not score_mat.is_cuda or score_mat.dtype != torch.float32:
+        raise RuntimeError('score_mat must be a float32 CUDA tensor')
+    if tuple(score_mat.shape) != (P, K, K) or (K > 1 and score_mat.stride(2) != 1):
+        raise RuntimeError(f'score_mat must be {(P, K, K)} with a dense last dimension, got {tuple(score_mat.shape)} '
+                           f'strides {score_mat.stride()}')
+    if global_scores is not None:
+        _check(global_scores, 'global_scores', torch.float32, 1)
+        if global_scores.shape[0] != P:
+            raise RuntimeError(f'global_scores must be ({P},), got {tuple(global_scores.shape)}')
+    dev = ref_knn_points.device
+    cap = 2 * P * K * int(k)
+    ref_corr = torch.empty(cap, 3, dtype=torch.float32, device=dev)
+    src_corr = torch.empty(cap, 3, dtype=torch.float32, device=dev)
+    scores = torch.empty(cap, dtype=torch.float32, device=dev)
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    transform = torch.empty(4, 4, dtype=torch.float32, device=dev)
+    if P == 0:
+        raise RuntimeError('local_global_registration: no patch pairs')
+    nbytes = _abi.load().geotx_lgr_workspace_bytes(P, K)
+    work = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=dev)
+    _abi.call('geotx_local_global_registration', _p(ref_knn_points), _p(src_knn_points), _p(masks[0]), _p(masks[1]),
+              _p(score_mat), int(score_mat.stride(0)), int(score_mat.stride(1)), _p(global_scores), P, K, int(k),
+              float(acceptance_radius), int(bool(mutual)), float(confidence_threshold), int(correspondence_threshold),
+              int(num_refinement_steps), _p(ref_corr), _p(src_corr), _p(scores), _p(count), _p(transform), _p(work),
+              _stream())
+    return ref_corr, src_corr, scores, count, transform
