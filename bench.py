@@ -318,7 +318,7 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
 
 
 def time_registration(pkg, shape, calls=10, replays=5):
-    """geotx_local_global_registration (5 kernels, K11) on one pair's 256 patch score matrices
+    """geotx_local_global_registration (4 kernels, K11) on one pair's 256 patch score matrices
     (local_global_registration.py:145-235 as model.py:198-205 calls it); us per pair on the GPU, and the oracle's torch
     restatement of the reference module on the host cores for the same input."""
     import time
@@ -333,7 +333,7 @@ def time_registration(pkg, shape, calls=10, replays=5):
         us = _graph_time_us(once, calls, replays)
         count = int(once()[3].item())
         out = {'us_per_pair': us, 'patch_pairs': 256, 'points_per_patch': K, 'topk': k, 'correspondences': count,
-               'kernels_per_call': 5, 'host_synchronisations': 0, 'dtype': 'f32 (SVD in f64)',
+               'kernels_per_call': 4, 'host_synchronisations': 0, 'dtype': 'f32 (SVD in f64)',
                'timing': f'{calls} pairs captured in one CUDA graph, {replays} replays, CUDA events'}
         if os.path.join(ROOT, 'oracle') not in sys.path:
             sys.path.insert(0, os.path.join(ROOT, 'oracle'))

@@ -53,7 +53,7 @@ KERNELS_PER_CALL = {'geotx_gse_knn': 2,  # pack_points + knn
                     'geotx_superpoint_matching': 10,  # prepare, scores, sums, 6 select passes, collect
                     'geotx_point_to_node_partition': 4,  # assign, offsets, scatter, select
                     'geotx_grid_subsample': 14,
-                    'geotx_local_global_registration': 5}  # 7 per batch element (bounds, clear, accumulate, count, scan, emit, advance)
+                    'geotx_local_global_registration': 4}  # 7 per batch element (bounds, clear, accumulate, count, scan, emit, advance)
 
 _lib = None
 launch_count = 0  # hand-written kernels launched through this binding so far

@@ -10,14 +10,20 @@
 //   patch   one CTA per patch pair: exp(scores) in shared memory, row / column top-k as bit masks, the mutual (or
 //           either-side) correspondence mask, and that patch pair's own Procrustes hypothesis straight from the masked
 //           K x K weights (no padding, no gather)
-//   scan    exclusive scan of the per-patch counts
-//   emit    correspondences written in (patch, i, j) order -- torch.nonzero's order (:147)
-//   inlier  every hypothesis scored on ALL correspondences (:178-183)
-//   refine  one CTA: best hypothesis, then num_refinement_steps re-weighted Procrustes solutions (:184-198)
+//   emit    every CTA sums the counts of the patch pairs before its own and writes its correspondences in
+//           (patch, i, j) order -- torch.nonzero's order (:147)
+//   inlier  every hypothesis scored on ALL correspondences (:178-183): a thread keeps one correspondence in registers
+//           and walks the hypotheses in shared memory
+//   refine  one cluster of 8 CTAs: best hypothesis, then num_refinement_steps re-weighted Procrustes solutions
+//           (:184-198), the partial moments exchanged through distributed shared memory, one cluster barrier a step
+// Every Procrustes solve is ONE pass over its correspondences: the 16 shifted moments (sum w, sum w s', sum w r',
+// sum w s' r'^T with s' = s - a, r' = r - b for a fixed pair of points a, b near the data) give the reference's
+// normalised weights, centroids and covariance in closed form (lgr_solve); the reference makes three passes.
 // No host synchronisation; the number of correspondences is left in device memory.
 // Equal scores in a top-k are ordered by the smaller index (torch.topk leaves ties unspecified).
 #include "geotx_common.cuh"
 #include "procrustes.cuh"
+#include "sm100_ptx.cuh"
 
 namespace geotx {
 
@@ -29,7 +35,7 @@ constexpr float LGR_EPS = 1e-5f;  // WeightedProcrustes default eps (procrustes.
 struct LgrWorkspace {
     unsigned int* corr_bits;  // [P][K][LGR_WORDS]
     int* counts;              // [P]
-    int* offsets;             // [P + 1]
+    int* total;               // [1] number of correspondences
     float* transforms;        // [P][16] local hypotheses
     int* inliers;             // [P]  (-1: the patch pair has fewer than correspondence_threshold correspondences)
 };
@@ -40,71 +46,60 @@ __host__ inline size_t lgr_layout(int P, int K, char* base, LgrWorkspace* w) {
     auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += lgr_align(bytes); return p; };
     char* a = take((size_t)P * K * LGR_WORDS * 4);
     char* b = take((size_t)P * 4);
-    char* c = take((size_t)(P + 1) * 4);
+    char* c = take(4);
     char* d = take((size_t)P * 16 * 4);
     char* e = take((size_t)P * 4);
     if (w) {
         w->corr_bits = (unsigned int*)a;
         w->counts = (int*)b;
-        w->offsets = (int*)c;
+        w->total = (int*)c;
         w->transforms = (float*)d;
         w->inliers = (int*)e;
     }
     return off;
 }
 
-// Sums N values per thread over the CTA; every thread gets the totals.  red: [N][32] floats of shared memory.
-template <int N>
-__device__ __forceinline__ void lgr_block_sum(float (&v)[N], float (*red)[32]) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+
+// ---- one-pass weighted Procrustes ----------------------------------------------------------------------------------
+// m[0] = sum w, m[1..3] = sum w s', m[4..6] = sum w r', m[7 + 3i + j] = sum w s'_i r'_j   (s' = s - a, r' = r - b)
+__device__ __forceinline__ void lgr_accumulate(float (&m)[16], const float* s, const float* r, float w, const float* a,
+                                               const float* b) {
+    const float sp[3] = {s[0] - a[0], s[1] - a[1], s[2] - a[2]};
+    const float rp[3] = {r[0] - b[0], r[1] - b[1], r[2] - b[2]};
+    m[0] += w;
 #pragma unroll
-    for (int k = 0; k < N; ++k) {
+    for (int i = 0; i < 3; ++i) {
+        const float ws = w * sp[i];
+        m[1 + i] += ws;
+        m[4 + i] = __fmaf_rn(w, rp[i], m[4 + i]);
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
-    }
-    __syncthreads();
-    if (lane == 0) {
-#pragma unroll
-        for (int k = 0; k < N; ++k) red[k][wid] = v[k];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < N; ++k) {
-        float s = 0.f;
-        for (int w = 0; w < nw; ++w) s += red[k][w];
-        v[k] = s;
+        for (int j = 0; j < 3; ++j) m[7 + 3 * i + j] = __fmaf_rn(ws, rp[j], m[7 + 3 * i + j]);
     }
 }
 
-// Weighted Procrustes over the items a CTA can enumerate: `visit(f)` calls f(src, ref, weight) for each item of this
-// thread.  procrustes.py:43-59 with weight_thresh = 0.  The transform lands in T (16 floats, shared or global); all
-// threads must call it; T is valid after the trailing __syncthreads().
-template <class Visit>
-__device__ __forceinline__ void lgr_procrustes(Visit visit, float (*red)[32], float* T) {
-    float acc[1] = {0.f};
-    visit([&](const float* s, const float* r, float w) { acc[0] += w; });
-    lgr_block_sum(acc, red);
-    const float inv = 1.0f / (acc[0] + LGR_EPS);
-    float c[6] = {0, 0, 0, 0, 0, 0};
-    visit([&](const float* s, const float* r, float w) {
-        const float wn = w * inv;
-#pragma unroll
-        for (int d = 0; d < 3; ++d) { c[d] += s[d] * wn; c[3 + d] += r[d] * wn; }
-    });
-    lgr_block_sum(c, red);
-    float h[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-    visit([&](const float* s, const float* r, float w) {
-        const float wn = w * inv;
-        const float sc[3] = {s[0] - c[0], s[1] - c[1], s[2] - c[2]};
-        const float rc[3] = {wn * (r[0] - c[3]), wn * (r[1] - c[4]), wn * (r[2] - c[5])};
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-#pragma unroll
-            for (int j = 0; j < 3; ++j) h[3 * i + j] += sc[i] * rc[j];
-    });
-    lgr_block_sum(h, red);
-    if (threadIdx.x == 0) kabsch_transform(h, c, T);
-    __syncthreads();
+// procrustes.py:43-59 (weight_thresh = 0) from the 16 moments.  With d = W + eps, rho = W / d, S = sum w s' / d,
+// R = sum w r' / d, M = sum w s' r'^T / d:  c_src = S + rho a, c_ref = R + rho b, and with u = S - (1 - rho) a,
+// v = R - (1 - rho) b:  H = sum w_n (s - c_src)(r - c_ref)^T = M - S v^T - u R^T + rho u v^T.  One thread; T gets the
+// 4x4 transform, c (6 floats) the two centroids.
+__device__ inline void lgr_solve(const float* m, const float* a, const float* b, float* T, float* c) {
+    const double d = (double)m[0] + (double)LGR_EPS, rho = (double)m[0] / d;
+    double S[3], R[3], u[3], v[3];
+    for (int i = 0; i < 3; ++i) {
+        S[i] = (double)m[1 + i] / d;
+        R[i] = (double)m[4 + i] / d;
+        u[i] = S[i] - (1.0 - rho) * (double)a[i];
+        v[i] = R[i] - (1.0 - rho) * (double)b[i];
+    }
+    float h[9], cc[6];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            h[3 * i + j] = (float)((double)m[7 + 3 * i + j] / d - S[i] * v[j] - u[i] * R[j] + rho * u[i] * v[j]);
+    for (int i = 0; i < 3; ++i) {
+        cc[i] = (float)(S[i] + rho * (double)a[i]);
+        cc[3 + i] = (float)(R[i] + rho * (double)b[i]);
+    }
+    kabsch_transform(h, cc, T);
+    for (int i = 0; i < 6; ++i) c[i] = cc[i];
 }
 
 // modules/ops/transformation.py:39 + local_global_registration.py:139-141: |ref - (R src + t)| < radius
@@ -119,135 +114,166 @@ __device__ __forceinline__ bool lgr_inlier(const float* T, const float* s, const
     return sqrtf(d2) < radius;
 }
 
+// xor-shuffle sum of 16 values over a warp (every lane gets the totals)
+__device__ __forceinline__ void lgr_warp_sum(float (&m)[16]) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) m[k] += __shfl_xor_sync(0xffffffffu, m[k], off);
+    }
+}
+
 // ---- patch: correspondence mask + local hypothesis of one patch pair -------------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int LGR_PATCH_THREADS = 256;
+__host__ __device__ inline int lgr_pitch(int K) { return K | 1; }  // odd row pitch: rows AND columns conflict-free
+__host__ inline size_t lgr_patch_smem(int K) { return ((size_t)K * lgr_pitch(K) + 6 * (size_t)K) * sizeof(float); }
+
+__global__ void __launch_bounds__(LGR_PATCH_THREADS)
 lgr_patch_kernel(const float* __restrict__ ref_knn_points, const float* __restrict__ src_knn_points,
                  const uint8_t* __restrict__ ref_masks, const uint8_t* __restrict__ src_masks,
                  const float* __restrict__ score_mat, long long score_bs, long long score_rs,
                  const float* __restrict__ global_scores, int K, int topk, int mutual, float conf_thr, int corr_thr,
                  LgrWorkspace w) {
-    extern __shared__ __align__(16) float lgr_S[];  // K x K: exp(score_mat[b])   (:216)
+    extern __shared__ __align__(16) float lgr_smem[];
+    const int pitch = lgr_pitch(K);
+    float* S = lgr_smem;           // K x pitch: exp(score_mat[b])   (:216)
+    float* pr = S + K * pitch;     // K x 3 ref patch points
+    float* ps = pr + 3 * K;        // K x 3 src patch points
     __shared__ unsigned int rb[LGR_MAX_K][LGR_WORDS], cb[LGR_MAX_K][LGR_WORDS], corr[LGR_MAX_K][LGR_WORDS];
-    __shared__ float red[9][32];
-    __shared__ int count_s;
-    const int b = blockIdx.x, tid = threadIdx.x;
+    __shared__ float red[16][LGR_PATCH_THREADS / 32];
+    __shared__ int count_s, first_s;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float* sm = score_mat + (size_t)b * score_bs;
-    for (int e = tid; e < K * K; e += blockDim.x) lgr_S[e] = expf(sm[(size_t)(e / K) * score_rs + (e % K)]);
-    for (int e = tid; e < LGR_MAX_K * LGR_WORDS; e += blockDim.x) {
+    // all loads of a batch in flight before the first exp: the matrix comes from HBM once, latency paid K*K/2048 times
+    const int total = K * K;
+    for (int base = tid; base < total; base += LGR_PATCH_THREADS * 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int e = base + u * LGR_PATCH_THREADS;
+            v[u] = e < total ? sm[(size_t)(e / K) * score_rs + (e % K)] : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int e = base + u * LGR_PATCH_THREADS;
+            if (e < total) S[(e / K) * pitch + (e % K)] = expf(v[u]);
+        }
+    }
+    for (int e = tid; e < 3 * K; e += LGR_PATCH_THREADS) {
+        pr[e] = ref_knn_points[(size_t)b * K * 3 + e];
+        ps[e] = src_knn_points[(size_t)b * K * 3 + e];
+    }
+    for (int e = tid; e < LGR_MAX_K * LGR_WORDS; e += LGR_PATCH_THREADS) {
         (&rb[0][0])[e] = 0u;
         (&cb[0][0])[e] = 0u;
     }
-    if (tid == 0) count_s = 0;
+    if (tid == 0) { count_s = 0; first_s = 0x7fffffff; }
     __syncthreads();
     // :57-62 / :65-70: the k largest of every row (threads 0..K-1) and of every column (threads K..2K-1), kept if
-    // above the confidence threshold.  2K <= 256 threads.
+    // above the confidence threshold.  2K <= 256 threads.  Pass t takes the successor of pass t-1 in (value descending,
+    // index ascending) order, so nothing has to be remembered but the last pick.
     if (tid < 2 * K) {
         const bool is_row = tid < K;
         const int line = is_row ? tid : tid - K;
-        const int stride = is_row ? 1 : K;
-        const float* base = lgr_S + (is_row ? line * K : line);
-        int taken[LGR_MAX_TOPK];
+        const int stride = is_row ? 1 : pitch;
+        const float* base = S + (is_row ? line * pitch : line);
+        float pv = __int_as_float(0x7f800000);
+        int pe = -1;
         for (int t = 0; t < topk; ++t) {
             float best = -__int_as_float(0x7f800000);
             int bi = -1;
+#pragma unroll 4
             for (int e = 0; e < K; ++e) {
                 const float v = base[e * stride];
-                bool used = false;
-                for (int q = 0; q < t; ++q) used |= taken[q] == e;
-                if (!used && v > best) { best = v; bi = e; }
+                const bool cand = v < pv || (v == pv && e > pe);
+                if (cand && v > best) { best = v; bi = e; }
             }
-            taken[t] = bi;
-            if (bi >= 0 && best > conf_thr) {
-                if (is_row) rb[line][bi >> 5] |= 1u << (bi & 31);       // only this thread writes row `line`
-                else atomicOr(&cb[bi][line >> 5], 1u << (line & 31));
-            }
+            if (bi < 0 || !(best > conf_thr)) break;  // the rest of the order is not larger
+            pv = best;
+            pe = bi;
+            if (is_row) rb[line][bi >> 5] |= 1u << (bi & 31);  // only this thread writes row `line`
+            else atomicOr(&cb[bi][line >> 5], 1u << (line & 31));
         }
     }
     __syncthreads();
     // :73-82 merge the two sides, then the validity masks of the patch points
     const uint8_t* rm = ref_masks + (size_t)b * K;
     const uint8_t* sk = src_masks + (size_t)b * K;
-    for (int e = tid; e < K * LGR_WORDS; e += blockDim.x) {
+    for (int e = tid; e < K * LGR_WORDS; e += LGR_PATCH_THREADS) {
         const int i = e / LGR_WORDS, wd = e % LGR_WORDS;
         unsigned int m = mutual ? (rb[i][wd] & cb[i][wd]) : (rb[i][wd] | cb[i][wd]);
-        unsigned int cols = 0u;
-        for (int j = wd * 32; j < min(K, wd * 32 + 32); ++j) cols |= (sk[j] ? 1u : 0u) << (j & 31);
-        m = rm[i] ? (m & cols) : 0u;
+        if (m && rm[i]) {
+            unsigned int cols = 0u;
+            for (unsigned int rest = m; rest;) {
+                const int j = wd * 32 + __ffs(rest) - 1;
+                rest &= rest - 1;
+                cols |= (sk[j] ? 1u : 0u) << (j & 31);
+            }
+            m &= cols;
+        } else {
+            m = 0u;
+        }
         corr[i][wd] = m;
         w.corr_bits[((size_t)b * K + i) * LGR_WORDS + wd] = m;
-        if (m) atomicAdd(&count_s, __popc(m));
+        if (m) {
+            atomicAdd(&count_s, __popc(m));
+            atomicMin(&first_s, i * LGR_MAX_K + wd * 32 + __ffs(m) - 1);
+        }
     }
     __syncthreads();
     const int count = count_s;
     if (tid == 0) {
         w.counts[b] = count;
-        w.inliers[b] = count >= corr_thr ? 0 : -1;  // :168-171 chunks below the threshold give no hypothesis
+        w.inliers[b] = (count >= corr_thr && count > 0) ? 0 : -1;  // :168-171 small chunks give no hypothesis
     }
-    if (count < corr_thr) return;
-    // :173-177 the patch pair's own weighted Procrustes, straight from the masked weights
+    if (count < corr_thr || count == 0) return;
+    // :173-177 the patch pair's own weighted Procrustes, straight from the masked weights, shifted to the first
+    // correspondence's points
     const float gs = global_scores ? global_scores[b] : 1.0f;  // :222-223
-    const float* rp = ref_knn_points + (size_t)b * K * 3;
-    const float* sp = src_knn_points + (size_t)b * K * 3;
-    auto visit = [&](auto f) {
-        for (int i = tid; i < K; i += blockDim.x)
-            for (int wd = 0; wd < LGR_WORDS; ++wd) {
-                unsigned int m = corr[i][wd];
-                while (m) {
-                    const int j = wd * 32 + __ffs(m) - 1;
-                    m &= m - 1;
-                    f(sp + 3 * j, rp + 3 * i, lgr_S[i * K + j] * gs);
-                }
-            }
-    };
-    lgr_procrustes(visit, red, w.transforms + (size_t)b * 16);
-}
-
-// ---- scan: where every patch pair's correspondences start ------------------------------------------------------------
-__global__ void __launch_bounds__(1024) lgr_scan_kernel(int P, LgrWorkspace w, int* __restrict__ count_out) {
-    __shared__ int warp_sum[32];
-    __shared__ int carry_s;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) carry_s = 0;
-    __syncthreads();
-    for (int base = 0; base < P; base += 1024) {
-        const int i = base + threadIdx.x;
-        const int c = i < P ? w.counts[i] : 0;
-        int incl = c;
+    const float* a = ps + 3 * (first_s % LGR_MAX_K);
+    const float* bb = pr + 3 * (first_s / LGR_MAX_K);
+    float m16[16];
 #pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, incl, off);
-            if (lane >= off) incl += o;
+    for (int q = 0; q < 16; ++q) m16[q] = 0.f;
+    for (int e = tid; e < K * LGR_WORDS; e += LGR_PATCH_THREADS) {
+        const int i = e / LGR_WORDS, wd = e % LGR_WORDS;
+        for (unsigned int rest = corr[i][wd]; rest;) {
+            const int j = wd * 32 + __ffs(rest) - 1;
+            rest &= rest - 1;
+            lgr_accumulate(m16, ps + 3 * j, pr + 3 * i, S[i * pitch + j] * gs, a, bb);
         }
-        if (lane == 31) warp_sum[wid] = incl;
-        __syncthreads();
-        if (wid == 0) {
-            int s = warp_sum[lane];
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const int o = __shfl_up_sync(0xffffffffu, s, off);
-                if (lane >= off) s += o;
-            }
-            warp_sum[lane] = s;
-        }
-        __syncthreads();
-        const int before = carry_s + (wid ? warp_sum[wid - 1] : 0) + incl - c;
-        if (i < P) w.offsets[i] = before;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry_s = before + c;
-        __syncthreads();
     }
-    if (threadIdx.x == 0) { w.offsets[P] = carry_s; *count_out = carry_s; }
+    lgr_warp_sum(m16);
+    if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < 16; ++q) red[q][wid] = m16[q];
+    }
+    __syncthreads();
+    if (tid == 0) {
+        float tot[16], c[6];
+        for (int q = 0; q < 16; ++q) {
+            float t = 0.f;
+            for (int ww = 0; ww < LGR_PATCH_THREADS / 32; ++ww) t += red[q][ww];
+            tot[q] = t;
+        }
+        lgr_solve(tot, a, bb, w.transforms + (size_t)b * 16, c);
+    }
 }
 
 // ---- emit: correspondences in (patch, i, j) order (:147-150) -----------------------------------------------------------
 __global__ void __launch_bounds__(LGR_MAX_K)
 lgr_emit_kernel(const float* __restrict__ ref_knn_points, const float* __restrict__ src_knn_points,
                 const float* __restrict__ score_mat, long long score_bs, long long score_rs,
-                const float* __restrict__ global_scores, int K, LgrWorkspace w, float* __restrict__ ref_corr,
-                float* __restrict__ src_corr, float* __restrict__ corr_scores) {
+                const float* __restrict__ global_scores, int P, int K, LgrWorkspace w, float* __restrict__ ref_corr,
+                float* __restrict__ src_corr, float* __restrict__ corr_scores, int* __restrict__ count_out) {
     __shared__ int row_start[LGR_MAX_K + 1];
-    const int b = blockIdx.x, i = threadIdx.x;
-    if (w.counts[b] == 0) return;
+    __shared__ int warp_part[LGR_MAX_K / 32];
+    const int b = blockIdx.x, i = threadIdx.x, lane = i & 31, wid = i >> 5;
+    // where this patch pair's correspondences start: the counts of the pairs before it
+    int before = 0;
+    for (int p = i; p < b; p += LGR_MAX_K) before += w.counts[p];
+    before = __reduce_add_sync(0xffffffffu, before);
+    if (lane == 0) warp_part[wid] = before;
     unsigned int m[LGR_WORDS];
     int n = 0;
 #pragma unroll
@@ -255,27 +281,40 @@ lgr_emit_kernel(const float* __restrict__ ref_knn_points, const float* __restric
         m[wd] = i < K ? w.corr_bits[((size_t)b * K + i) * LGR_WORDS + wd] : 0u;
         n += __popc(m[wd]);
     }
-    row_start[i + 1] = n;
-    if (i == 0) row_start[0] = 0;
+    // exclusive scan of the row counts over the CTA
+    int incl = n;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += o;
+    }
+    if (lane == 31) row_start[wid] = incl;
     __syncthreads();
-    if (i == 0)
-        for (int r = 1; r <= LGR_MAX_K; ++r) row_start[r] += row_start[r - 1];
-    __syncthreads();
+    int offset = 0, row0 = incl - n;
+#pragma unroll
+    for (int ww = 0; ww < LGR_MAX_K / 32; ++ww) {
+        offset += warp_part[ww];
+        if (ww < wid) row0 += row_start[ww];
+    }
+    if (b == P - 1 && i == LGR_MAX_K - 1) {  // the last thread of the last pair knows the total
+        *w.total = offset + row0 + n;
+        *count_out = offset + row0 + n;
+    }
     if (n == 0) return;
     const float gs = global_scores ? global_scores[b] : 1.0f;
     const float* sm = score_mat + (size_t)b * score_bs + (size_t)i * score_rs;
-    size_t o = (size_t)w.offsets[b] + row_start[i];
+    size_t o = (size_t)offset + row0;
+    const float r0 = ref_knn_points[((size_t)b * K + i) * 3], r1 = ref_knn_points[((size_t)b * K + i) * 3 + 1],
+                r2 = ref_knn_points[((size_t)b * K + i) * 3 + 2];
 #pragma unroll
     for (int wd = 0; wd < LGR_WORDS; ++wd) {
         unsigned int bits = m[wd];
         while (bits) {
             const int j = wd * 32 + __ffs(bits) - 1;
             bits &= bits - 1;
-#pragma unroll
-            for (int d = 0; d < 3; ++d) {
-                ref_corr[3 * o + d] = ref_knn_points[((size_t)b * K + i) * 3 + d];
-                src_corr[3 * o + d] = src_knn_points[((size_t)b * K + j) * 3 + d];
-            }
+            const float* sp = src_knn_points + ((size_t)b * K + j) * 3;
+            ref_corr[3 * o] = r0; ref_corr[3 * o + 1] = r1; ref_corr[3 * o + 2] = r2;
+            src_corr[3 * o] = sp[0]; src_corr[3 * o + 1] = sp[1]; src_corr[3 * o + 2] = sp[2];
             corr_scores[o] = expf(sm[j]) * gs;  // :216, :222-224
             ++o;
         }
@@ -283,63 +322,124 @@ lgr_emit_kernel(const float* __restrict__ ref_knn_points, const float* __restric
 }
 
 // ---- inlier: every local hypothesis against all correspondences (:178-183) ----------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int LGR_INL_THREADS = 256;  // correspondences per tile, one per thread
+constexpr int LGR_INL_HYPS = 64;      // hypotheses per CTA (grid.y walks them)
+
+__global__ void __launch_bounds__(LGR_INL_THREADS)
 lgr_inlier_kernel(const float* __restrict__ ref_corr, const float* __restrict__ src_corr, int P, float radius,
                   LgrWorkspace w) {
-    __shared__ float T[16];
-    __shared__ int total_s;
-    const int b = blockIdx.x;
-    if (w.inliers[b] < 0) return;
-    if (threadIdx.x < 16) T[threadIdx.x] = w.transforms[(size_t)b * 16 + threadIdx.x];
-    if (threadIdx.x == 0) total_s = 0;
+    __shared__ __align__(16) float Ts[LGR_INL_HYPS][12];
+    __shared__ int valid[LGR_INL_HYPS], hits[LGR_INL_HYPS];
+    const int C = *w.total;
+    const int h0 = blockIdx.y * LGR_INL_HYPS, nh = min(LGR_INL_HYPS, P - h0);
+    if ((long long)blockIdx.x * LGR_INL_THREADS >= C) return;
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int e = tid; e < nh; e += LGR_INL_THREADS) {
+        valid[e] = w.inliers[h0 + e] >= 0;  // stable: only hypotheses that start at 0 are ever added to
+        hits[e] = 0;
+    }
+    for (int e = tid; e < nh * 12; e += LGR_INL_THREADS)
+        Ts[e / 12][e % 12] = w.transforms[(size_t)(h0 + e / 12) * 16 + e % 12];
     __syncthreads();
-    const int C = w.offsets[P];
-    int n = 0;
-    for (int e = threadIdx.x; e < C; e += blockDim.x) n += lgr_inlier(T, src_corr + 3 * (size_t)e, ref_corr + 3 * (size_t)e, radius);
-    n = __reduce_add_sync(0xffffffffu, n);
-    if ((threadIdx.x & 31) == 0) atomicAdd(&total_s, n);
+    for (long long tile = blockIdx.x; tile * LGR_INL_THREADS < C; tile += gridDim.x) {
+        const long long e = tile * LGR_INL_THREADS + tid;
+        const bool live = e < C;
+        float s[3] = {0.f, 0.f, 0.f}, r[3] = {0.f, 0.f, 0.f};
+        if (live) {
+#pragma unroll
+            for (int d = 0; d < 3; ++d) { s[d] = src_corr[3 * e + d]; r[d] = ref_corr[3 * e + d]; }
+        }
+#pragma unroll 4
+        for (int h = 0; h < nh; ++h) {
+            if (!valid[h]) continue;
+            const unsigned int ballot = __ballot_sync(0xffffffffu, live && lgr_inlier(Ts[h], s, r, radius));
+            if (lane == 0 && ballot) atomicAdd(&hits[h], __popc(ballot));
+        }
+    }
     __syncthreads();
-    if (threadIdx.x == 0) w.inliers[b] = total_s;
+    for (int e = tid; e < nh; e += LGR_INL_THREADS)
+        if (hits[e]) atomicAdd(&w.inliers[h0 + e], hits[e]);
 }
 
 // ---- refine: best hypothesis, then re-weighted global Procrustes (:184-198) ---------------------------------------------
-__global__ void __launch_bounds__(1024)
+constexpr int LGR_REF_CTAS = 8;  // one portable cluster
+constexpr int LGR_REF_THREADS = 512;
+
+__global__ void __cluster_dims__(LGR_REF_CTAS, 1, 1) __launch_bounds__(LGR_REF_THREADS)
 lgr_refine_kernel(const float* __restrict__ ref_corr, const float* __restrict__ src_corr,
                   const float* __restrict__ corr_scores, int P, float radius, int steps, LgrWorkspace w,
                   float* __restrict__ transform_out) {
-    __shared__ float red[9][32];
-    __shared__ float T[16];
-    __shared__ int best_s;
-    const int C = w.offsets[P];
-    if (threadIdx.x == 0) {  // :183 argmax over the hypotheses, first maximum
-        int best = -1, best_n = -1;
-        for (int b = 0; b < P; ++b)
-            if (w.inliers[b] > best_n) { best_n = w.inliers[b]; best = b; }
-        best_s = best;
+    __shared__ float red[16][LGR_REF_THREADS / 32];
+    __shared__ __align__(16) float part[2][16];  // this CTA's partial moments, by step parity (peers read them)
+    __shared__ float tot[16], T[16], shift[6];
+    __shared__ unsigned long long best_part[LGR_REF_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const unsigned int rank = ptx::cluster_ctarank();
+    const int C = *w.total;
+    // :183 argmax of the inlier counts over the hypotheses, first maximum (every CTA finds it for itself)
+    unsigned long long key = 0ull;
+    for (int p = tid; p < P; p += LGR_REF_THREADS) {
+        const int n = w.inliers[p];
+        if (n >= 0) key = max(key, ((unsigned long long)(unsigned int)(n + 1) << 32) | (0xffffffffu - (unsigned int)p));
     }
-    __syncthreads();
-    auto all_weighted = [&](auto weight) {
-        return [&, weight](auto f) {
-            for (int e = threadIdx.x; e < C; e += blockDim.x)
-                f(src_corr + 3 * (size_t)e, ref_corr + 3 * (size_t)e, weight(e));
-        };
-    };
-    if (best_s >= 0) {
-        if (threadIdx.x < 16) T[threadIdx.x] = w.transforms[(size_t)best_s * 16 + threadIdx.x];
-        __syncthreads();
-    } else {  // :185-190 no patch pair reached the threshold: start from all correspondences
-        lgr_procrustes(all_weighted([&](int e) { return corr_scores[e]; }), red, T);
-    }
-    for (int s = 0; s < steps; ++s) {  // :184 / :193-198: weights = scores x inliers of the current transform
-        float Tc[16];
 #pragma unroll
-        for (int q = 0; q < 16; ++q) Tc[q] = T[q];
-        __syncthreads();  // everybody holds the current transform before thread 0 overwrites T
-        lgr_procrustes(all_weighted([&](int e) {
-            return lgr_inlier(Tc, src_corr + 3 * (size_t)e, ref_corr + 3 * (size_t)e, radius) ? corr_scores[e] : 0.0f;
-        }), red, T);
+    for (int off = 16; off > 0; off >>= 1) key = max(key, __shfl_xor_sync(0xffffffffu, key, off));
+    if (lane == 0) best_part[wid] = key;
+    __syncthreads();
+#pragma unroll
+    for (int ww = 0; ww < LGR_REF_THREADS / 32; ++ww) key = max(key, best_part[ww]);
+    const int best = key ? (int)(0xffffffffu - (unsigned int)(key & 0xffffffffull)) : -1;
+    if (tid < 16) T[tid] = best >= 0 ? w.transforms[(size_t)best * 16 + tid] : (tid % 5 == 0 ? 1.f : 0.f);
+    if (tid < 3) {  // the moments are taken about the first correspondence, later about the last centroids
+        shift[tid] = C > 0 ? src_corr[tid] : 0.f;
+        shift[3 + tid] = C > 0 ? ref_corr[tid] : 0.f;
     }
-    if (threadIdx.x < 16) transform_out[threadIdx.x] = T[threadIdx.x];
+    // :185-190 without a hypothesis the first solve takes all correspondences with their scores; every solve after
+    // it (and every solve of the normal path, :184 / :193-198) weights them by scores x inliers of the last transform
+    const int iters = steps + (best < 0 ? 1 : 0);
+    for (int it = 0; it < iters; ++it) {
+        __syncthreads();  // T and shift of the last solve are in place
+        const bool plain = best < 0 && it == 0;
+        float Tl[16], a[3], b[3], m[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) { Tl[q] = T[q]; m[q] = 0.f; }
+#pragma unroll
+        for (int d = 0; d < 3; ++d) { a[d] = shift[d]; b[d] = shift[3 + d]; }
+        for (int e = rank * LGR_REF_THREADS + tid; e < C; e += LGR_REF_CTAS * LGR_REF_THREADS) {
+            const float s[3] = {src_corr[3 * (size_t)e], src_corr[3 * (size_t)e + 1], src_corr[3 * (size_t)e + 2]};
+            const float r[3] = {ref_corr[3 * (size_t)e], ref_corr[3 * (size_t)e + 1], ref_corr[3 * (size_t)e + 2]};
+            const float sc = corr_scores[e];
+            lgr_accumulate(m, s, r, (plain || lgr_inlier(Tl, s, r, radius)) ? sc : 0.f, a, b);
+        }
+        lgr_warp_sum(m);
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) red[q][wid] = m[q];
+        }
+        __syncthreads();
+        if (tid < 16) {
+            float t = 0.f;
+#pragma unroll
+            for (int ww = 0; ww < LGR_REF_THREADS / 32; ++ww) t += red[tid][ww];
+            part[it & 1][tid] = t;
+        }
+        ptx::cluster_sync();  // every CTA's partial of this step is visible cluster-wide
+        if (tid < 16) {
+            const uint32_t mine = (uint32_t)__cvta_generic_to_shared(&part[it & 1][tid]);
+            float t = 0.f;
+#pragma unroll
+            for (unsigned int z = 0; z < LGR_REF_CTAS; ++z) {  // fixed order: all CTAs get the same bits
+                float x;
+                asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(x) : "r"(ptx::map_to_cta(mine, z)));
+                t += x;
+            }
+            tot[tid] = t;
+        }
+        __syncthreads();
+        if (tid == 0) lgr_solve(tot, shift, shift + 3, T, shift);  // reads a, b before it writes the new centroids
+    }
+    ptx::cluster_sync();  // nobody leaves while a peer may still read its partials
+    if (rank == 0 && tid < 16) transform_out[tid] = T[tid];
 }
 
 }  // namespace geotx
@@ -371,28 +471,30 @@ extern "C" int geotx_local_global_registration(
     GEOTX_REQUIRE(score_row_stride >= K && score_batch_stride >= (int64_t)K * score_row_stride,
                   "geotx_local_global_registration: score strides %lld/%lld too small for K=%d",
                   (long long)score_batch_stride, (long long)score_row_stride, K);
-    GEOTX_REQUIRE((int64_t)num_patches * K * 2 * topk < 2147483647LL,
-                  "geotx_local_global_registration: too many correspondences");
+    const int64_t cap = (int64_t)num_patches * K * 2 * topk;
+    GEOTX_REQUIRE(cap < 2147483647LL, "geotx_local_global_registration: too many correspondences");
     cudaStream_t st = (cudaStream_t)stream;
     LgrWorkspace w;
     lgr_layout(num_patches, K, (char*)workspace, &w);
-    const size_t smem = (size_t)K * K * sizeof(float);
+    const size_t smem = lgr_patch_smem(K);
     if (smem > 32 * 1024) {
         int rc = check_cuda(cudaFuncSetAttribute(lgr_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                             "geotx_local_global_registration: shared memory");
         if (rc) return rc;
     }
-    lgr_patch_kernel<<<num_patches, 256, smem, st>>>(ref_knn_points, src_knn_points, ref_knn_masks, src_knn_masks,
-                                                     score_mat, (long long)score_batch_stride,
-                                                     (long long)score_row_stride, global_scores, K, topk, mutual,
-                                                     confidence_threshold, correspondence_threshold, w);
-    lgr_scan_kernel<<<1, 1024, 0, st>>>(num_patches, w, count_out);
+    lgr_patch_kernel<<<num_patches, LGR_PATCH_THREADS, smem, st>>>(
+        ref_knn_points, src_knn_points, ref_knn_masks, src_knn_masks, score_mat, (long long)score_batch_stride,
+        (long long)score_row_stride, global_scores, K, topk, mutual, confidence_threshold, correspondence_threshold, w);
     lgr_emit_kernel<<<num_patches, LGR_MAX_K, 0, st>>>(ref_knn_points, src_knn_points, score_mat,
                                                        (long long)score_batch_stride, (long long)score_row_stride,
-                                                       global_scores, K, w, ref_corr_points, src_corr_points,
-                                                       corr_scores);
-    lgr_inlier_kernel<<<num_patches, 256, 0, st>>>(ref_corr_points, src_corr_points, num_patches, acceptance_radius, w);
-    lgr_refine_kernel<<<1, 1024, 0, st>>>(ref_corr_points, src_corr_points, corr_scores, num_patches,
-                                          acceptance_radius, num_refinement_steps, w, transform_out);
+                                                       global_scores, num_patches, K, w, ref_corr_points,
+                                                       src_corr_points, corr_scores, count_out);
+    const int tiles = (int)((cap + LGR_INL_THREADS - 1) / LGR_INL_THREADS);
+    const dim3 inl_grid(tiles < 148 ? tiles : 148, (num_patches + LGR_INL_HYPS - 1) / LGR_INL_HYPS);
+    lgr_inlier_kernel<<<inl_grid, LGR_INL_THREADS, 0, st>>>(ref_corr_points, src_corr_points, num_patches,
+                                                            acceptance_radius, w);
+    lgr_refine_kernel<<<LGR_REF_CTAS, LGR_REF_THREADS, 0, st>>>(ref_corr_points, src_corr_points, corr_scores,
+                                                                num_patches, acceptance_radius, num_refinement_steps,
+                                                                w, transform_out);
     return launch_status("geotx_local_global_registration");
 }

@@ -12,3 +12,5 @@ print(json.dumps({s: bench.time_registration(pkg, s) for s in ('3dmatch', 'kitti
 PY
 echo "lgr_timing exit $?" | tee -a gpurun_out/summary.txt
 cat gpurun_out/lgr_timing.json; tail -n 5 gpurun_out/lgr_timing.err
+ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/lgr_launches.csv python tools/lgr_once.py > gpurun_out/lgr_ncu.log 2>&1
+python tools/ncu_launches.py gpurun_out/lgr_launches.csv 6
