@@ -82,28 +82,35 @@ __device__ __forceinline__ void lgr_accumulate(float (&m)[16], const float* s, c
 // v = R - (1 - rho) b:  H = sum w_n (s - c_src)(r - c_ref)^T = M - S v^T - u R^T + rho u v^T.  One thread; T gets the
 // 4x4 transform, c (6 floats) the two centroids.
 __device__ inline void lgr_solve(const float* m, const float* a, const float* b, float* T, float* c) {
-    const double d = (double)m[0] + (double)LGR_EPS, rho = (double)m[0] / d;
+    const double inv = 1.0 / ((double)m[0] + (double)LGR_EPS), rho = (double)m[0] * inv;
     double S[3], R[3], u[3], v[3];
+#pragma unroll
     for (int i = 0; i < 3; ++i) {
-        S[i] = (double)m[1 + i] / d;
-        R[i] = (double)m[4 + i] / d;
+        S[i] = (double)m[1 + i] * inv;
+        R[i] = (double)m[4 + i] * inv;
         u[i] = S[i] - (1.0 - rho) * (double)a[i];
         v[i] = R[i] - (1.0 - rho) * (double)b[i];
     }
     float h[9], cc[6];
+#pragma unroll
     for (int i = 0; i < 3; ++i)
+#pragma unroll
         for (int j = 0; j < 3; ++j)
-            h[3 * i + j] = (float)((double)m[7 + 3 * i + j] / d - S[i] * v[j] - u[i] * R[j] + rho * u[i] * v[j]);
+            h[3 * i + j] = (float)((double)m[7 + 3 * i + j] * inv - S[i] * v[j] - u[i] * R[j] + rho * u[i] * v[j]);
+#pragma unroll
     for (int i = 0; i < 3; ++i) {
         cc[i] = (float)(S[i] + rho * (double)a[i]);
         cc[3 + i] = (float)(R[i] + rho * (double)b[i]);
     }
-    kabsch_transform(h, cc, T);
+    kabsch_transform<float>(h, cc, T);  // SVD in the reference's precision (torch.svd on an fp32 matrix)
+#pragma unroll
     for (int i = 0; i < 6; ++i) c[i] = cc[i];
 }
 
 // modules/ops/transformation.py:39 + local_global_registration.py:139-141: |ref - (R src + t)| < radius
-__device__ __forceinline__ bool lgr_inlier(const float* T, const float* s, const float* r, float radius) {
+// `d2_max` is the largest float whose (correctly rounded) square root is below the radius, found by the launcher, so
+// the test is the reference's without the square root.
+__device__ __forceinline__ bool lgr_inlier(const float* T, const float* s, const float* r, float d2_max) {
     float d2 = 0.f;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -111,7 +118,7 @@ __device__ __forceinline__ bool lgr_inlier(const float* T, const float* s, const
         const float d = r[i] - a;
         d2 += d * d;
     }
-    return sqrtf(d2) < radius;
+    return d2 <= d2_max;
 }
 
 // xor-shuffle sum of 16 values over a warp (every lane gets the totals)
@@ -140,7 +147,7 @@ lgr_patch_kernel(const float* __restrict__ ref_knn_points, const float* __restri
     float* pr = S + K * pitch;     // K x 3 ref patch points
     float* ps = pr + 3 * K;        // K x 3 src patch points
     __shared__ unsigned int rb[LGR_MAX_K][LGR_WORDS], cb[LGR_MAX_K][LGR_WORDS], corr[LGR_MAX_K][LGR_WORDS];
-    __shared__ float red[16][LGR_PATCH_THREADS / 32];
+    __shared__ float red[16][LGR_PATCH_THREADS / 32], tot_s[16];
     __shared__ int count_s, first_s;
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float* sm = score_mat + (size_t)b * score_bs;
@@ -249,14 +256,16 @@ lgr_patch_kernel(const float* __restrict__ ref_knn_points, const float* __restri
         for (int q = 0; q < 16; ++q) red[q][wid] = m16[q];
     }
     __syncthreads();
+    if (tid < 16) {
+        float t = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < LGR_PATCH_THREADS / 32; ++ww) t += red[tid][ww];
+        tot_s[tid] = t;
+    }
+    __syncthreads();
     if (tid == 0) {
-        float tot[16], c[6];
-        for (int q = 0; q < 16; ++q) {
-            float t = 0.f;
-            for (int ww = 0; ww < LGR_PATCH_THREADS / 32; ++ww) t += red[q][ww];
-            tot[q] = t;
-        }
-        lgr_solve(tot, a, bb, w.transforms + (size_t)b * 16, c);
+        float c[6];
+        lgr_solve(tot_s, a, bb, w.transforms + (size_t)b * 16, c);
     }
 }
 
@@ -323,10 +332,10 @@ lgr_emit_kernel(const float* __restrict__ ref_knn_points, const float* __restric
 
 // ---- inlier: every local hypothesis against all correspondences (:178-183) ----------------------------------------------
 constexpr int LGR_INL_THREADS = 256;  // correspondences per tile, one per thread
-constexpr int LGR_INL_HYPS = 64;      // hypotheses per CTA (grid.y walks them)
+constexpr int LGR_INL_HYPS = 16;      // hypotheses per CTA (grid.y walks them): enough CTAs to fill the SMs
 
 __global__ void __launch_bounds__(LGR_INL_THREADS)
-lgr_inlier_kernel(const float* __restrict__ ref_corr, const float* __restrict__ src_corr, int P, float radius,
+lgr_inlier_kernel(const float* __restrict__ ref_corr, const float* __restrict__ src_corr, int P, float d2_max,
                   LgrWorkspace w) {
     __shared__ __align__(16) float Ts[LGR_INL_HYPS][12];
     __shared__ int valid[LGR_INL_HYPS], hits[LGR_INL_HYPS];
@@ -352,7 +361,7 @@ lgr_inlier_kernel(const float* __restrict__ ref_corr, const float* __restrict__ 
 #pragma unroll 4
         for (int h = 0; h < nh; ++h) {
             if (!valid[h]) continue;
-            const unsigned int ballot = __ballot_sync(0xffffffffu, live && lgr_inlier(Ts[h], s, r, radius));
+            const unsigned int ballot = __ballot_sync(0xffffffffu, live && lgr_inlier(Ts[h], s, r, d2_max));
             if (lane == 0 && ballot) atomicAdd(&hits[h], __popc(ballot));
         }
     }
@@ -367,7 +376,7 @@ constexpr int LGR_REF_THREADS = 512;
 
 __global__ void __cluster_dims__(LGR_REF_CTAS, 1, 1) __launch_bounds__(LGR_REF_THREADS)
 lgr_refine_kernel(const float* __restrict__ ref_corr, const float* __restrict__ src_corr,
-                  const float* __restrict__ corr_scores, int P, float radius, int steps, LgrWorkspace w,
+                  const float* __restrict__ corr_scores, int P, float d2_max, int steps, LgrWorkspace w,
                   float* __restrict__ transform_out) {
     __shared__ float red[16][LGR_REF_THREADS / 32];
     __shared__ __align__(16) float part[2][16];  // this CTA's partial moments, by step parity (peers read them)
@@ -409,7 +418,7 @@ lgr_refine_kernel(const float* __restrict__ ref_corr, const float* __restrict__ 
             const float s[3] = {src_corr[3 * (size_t)e], src_corr[3 * (size_t)e + 1], src_corr[3 * (size_t)e + 2]};
             const float r[3] = {ref_corr[3 * (size_t)e], ref_corr[3 * (size_t)e + 1], ref_corr[3 * (size_t)e + 2]};
             const float sc = corr_scores[e];
-            lgr_accumulate(m, s, r, (plain || lgr_inlier(Tl, s, r, radius)) ? sc : 0.f, a, b);
+            lgr_accumulate(m, s, r, (plain || lgr_inlier(Tl, s, r, d2_max)) ? sc : 0.f, a, b);
         }
         lgr_warp_sum(m);
         if (lane == 0) {
@@ -445,8 +454,18 @@ lgr_refine_kernel(const float* __restrict__ ref_corr, const float* __restrict__ 
 }  // namespace geotx
 
 // ---- C ABI --------------------------------------------------------------------------------------------------
+#include <math.h>
 #include "host_util.h"
 using namespace geotx;
+
+// sqrt(d2) < radius  <=>  d2 <= lgr_d2_max(radius): sqrtf is correctly rounded and monotone on both sides.
+static float lgr_d2_max(float radius) {
+    if (!(radius > 0.f)) return -1.f;
+    float x = radius * radius;
+    while (sqrtf(x) >= radius) x = nextafterf(x, 0.f);
+    while (sqrtf(nextafterf(x, INFINITY)) < radius) x = nextafterf(x, INFINITY);
+    return x;
+}
 
 extern "C" int64_t geotx_lgr_workspace_bytes(int num_patches, int K) {
     if (num_patches <= 0 || K <= 0) return 0;
@@ -491,10 +510,10 @@ extern "C" int geotx_local_global_registration(
                                                        src_corr_points, corr_scores, count_out);
     const int tiles = (int)((cap + LGR_INL_THREADS - 1) / LGR_INL_THREADS);
     const dim3 inl_grid(tiles < 148 ? tiles : 148, (num_patches + LGR_INL_HYPS - 1) / LGR_INL_HYPS);
-    lgr_inlier_kernel<<<inl_grid, LGR_INL_THREADS, 0, st>>>(ref_corr_points, src_corr_points, num_patches,
-                                                            acceptance_radius, w);
+    const float d2_max = lgr_d2_max(acceptance_radius);
+    lgr_inlier_kernel<<<inl_grid, LGR_INL_THREADS, 0, st>>>(ref_corr_points, src_corr_points, num_patches, d2_max, w);
     lgr_refine_kernel<<<LGR_REF_CTAS, LGR_REF_THREADS, 0, st>>>(ref_corr_points, src_corr_points, corr_scores,
-                                                                num_patches, acceptance_radius, num_refinement_steps,
+                                                                num_patches, d2_max, num_refinement_steps,
                                                                 w, transform_out);
     return launch_status("geotx_local_global_registration");
 }

@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_lgr.py -m gpu -q --timeout 300 > gpurun_out/test_lgr.log 2>&1
+timeout 600 python -m pytest tests/test_lgr.py tests/test_procrustes.py -m gpu -q --timeout 300 > gpurun_out/test_lgr.log 2>&1
 echo "test_lgr exit $?" | tee -a gpurun_out/summary.txt
 tail -n 40 gpurun_out/test_lgr.log
 timeout 300 python - > gpurun_out/lgr_timing.json 2> gpurun_out/lgr_timing.err <<'PY'
