@@ -121,13 +121,23 @@ __device__ __forceinline__ bool lgr_inlier(const float* T, const float* s, const
     return d2 <= d2_max;
 }
 
-// xor-shuffle sum of 16 values over a warp (every lane gets the totals)
-__device__ __forceinline__ void lgr_warp_sum(float (&m)[16]) {
+// Sum of 16 values over a warp in 16 shuffles: every exchange halves the values a lane keeps (offsets 16, 8, 4, 2),
+// the last one (offset 1) adds the two lanes that hold the same value.  Returns the total of value
+// lgr_warp_value(lane) (both lanes of a pair return it).
+__device__ __forceinline__ int lgr_warp_value(int lane) {
+    return ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+}
+__device__ __forceinline__ float lgr_warp_sum(float (&m)[16], int lane) {
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
+    for (int half = 8; half >= 1; half >>= 1) {
+        const bool upper = (lane & (half << 1)) != 0;  // this lane keeps m[half .. 2 half), its partner m[0 .. half)
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) m[k] += __shfl_xor_sync(0xffffffffu, m[k], off);
+        for (int k = 0; k < half; ++k) {
+            const float send = upper ? m[k] : m[k + half], keep = upper ? m[k + half] : m[k];
+            m[k] = keep + __shfl_xor_sync(0xffffffffu, send, half << 1);
+        }
     }
+    return m[0] + __shfl_xor_sync(0xffffffffu, m[0], 1);
 }
 
 // ---- patch: correspondence mask + local hypothesis of one patch pair -------------------------------------------------
@@ -250,10 +260,9 @@ lgr_patch_kernel(const float* __restrict__ ref_knn_points, const float* __restri
             lgr_accumulate(m16, ps + 3 * j, pr + 3 * i, S[i * pitch + j] * gs, a, bb);
         }
     }
-    lgr_warp_sum(m16);
-    if (lane == 0) {
-#pragma unroll
-        for (int q = 0; q < 16; ++q) red[q][wid] = m16[q];
+    {
+        const float t = lgr_warp_sum(m16, lane);
+        if ((lane & 1) == 0) red[lgr_warp_value(lane)][wid] = t;
     }
     __syncthreads();
     if (tid < 16) {
@@ -373,6 +382,7 @@ lgr_inlier_kernel(const float* __restrict__ ref_corr, const float* __restrict__ 
 // ---- refine: best hypothesis, then re-weighted global Procrustes (:184-198) ---------------------------------------------
 constexpr int LGR_REF_CTAS = 8;  // one portable cluster
 constexpr int LGR_REF_THREADS = 512;
+constexpr int LGR_REF_SLOTS = 4;  // correspondences a thread keeps in registers: 16384 over the cluster
 
 __global__ void __cluster_dims__(LGR_REF_CTAS, 1, 1) __launch_bounds__(LGR_REF_THREADS)
 lgr_refine_kernel(const float* __restrict__ ref_corr, const float* __restrict__ src_corr,
@@ -406,6 +416,21 @@ lgr_refine_kernel(const float* __restrict__ ref_corr, const float* __restrict__ 
     // :185-190 without a hypothesis the first solve takes all correspondences with their scores; every solve after
     // it (and every solve of the normal path, :184 / :193-198) weights them by scores x inliers of the last transform
     const int iters = steps + (best < 0 ? 1 : 0);
+    // the correspondences of this thread stay in registers over the steps (absent ones have weight 0)
+    constexpr int stride = LGR_REF_CTAS * LGR_REF_THREADS;
+    const int e0 = rank * LGR_REF_THREADS + tid;
+    float cs[LGR_REF_SLOTS][3], cr[LGR_REF_SLOTS][3], cw[LGR_REF_SLOTS];
+#pragma unroll
+    for (int q = 0; q < LGR_REF_SLOTS; ++q) {
+        const int e = e0 + q * stride;
+        const bool live = e < C;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            cs[q][d] = live ? src_corr[3 * (size_t)e + d] : 0.f;
+            cr[q][d] = live ? ref_corr[3 * (size_t)e + d] : 0.f;
+        }
+        cw[q] = live ? corr_scores[e] : 0.f;
+    }
     for (int it = 0; it < iters; ++it) {
         __syncthreads();  // T and shift of the last solve are in place
         const bool plain = best < 0 && it == 0;
@@ -414,16 +439,18 @@ lgr_refine_kernel(const float* __restrict__ ref_corr, const float* __restrict__ 
         for (int q = 0; q < 16; ++q) { Tl[q] = T[q]; m[q] = 0.f; }
 #pragma unroll
         for (int d = 0; d < 3; ++d) { a[d] = shift[d]; b[d] = shift[3 + d]; }
-        for (int e = rank * LGR_REF_THREADS + tid; e < C; e += LGR_REF_CTAS * LGR_REF_THREADS) {
+#pragma unroll
+        for (int q = 0; q < LGR_REF_SLOTS; ++q)
+            lgr_accumulate(m, cs[q], cr[q], (plain || lgr_inlier(Tl, cs[q], cr[q], d2_max)) ? cw[q] : 0.f, a, b);
+        for (int e = e0 + LGR_REF_SLOTS * stride; e < C; e += stride) {  // what the register slots do not hold
             const float s[3] = {src_corr[3 * (size_t)e], src_corr[3 * (size_t)e + 1], src_corr[3 * (size_t)e + 2]};
             const float r[3] = {ref_corr[3 * (size_t)e], ref_corr[3 * (size_t)e + 1], ref_corr[3 * (size_t)e + 2]};
             const float sc = corr_scores[e];
             lgr_accumulate(m, s, r, (plain || lgr_inlier(Tl, s, r, d2_max)) ? sc : 0.f, a, b);
         }
-        lgr_warp_sum(m);
-        if (lane == 0) {
-#pragma unroll
-            for (int q = 0; q < 16; ++q) red[q][wid] = m[q];
+        {
+            const float t = lgr_warp_sum(m, lane);
+            if ((lane & 1) == 0) red[lgr_warp_value(lane)][wid] = t;
         }
         __syncthreads();
         if (tid < 16) {
