@@ -187,3 +187,49 @@ def make_lgr_inputs(num_patches=256, K=64, seed=SEED, outlier_patches=0.3, noise
     global_scores = torch.rand(num_patches, generator=gen) * 0.5 + 0.5
     return (ref.contiguous(), src.contiguous(), ref_masks.contiguous(), src_masks.contiguous(),
             torch.log(prob).contiguous(), global_scores, T)
+
+
+def make_tail_inputs(num_nodes=512, points_per_node=16, dim=256, seed=SEED, keep=0.85, noise=0.003, feat_noise=0.05):
+    """A registration pair for the stages AFTER the transformer (experiments/*/model.py:98-108,141-205: partition,
+    coarse matching, patch gather, optimal transport, local-to-global registration): two overlapping fine clouds with
+    their coarse nodes and stand-ins for the backbone's features -- random Fourier features of a point's position in
+    the REFERENCE frame (coarse: wavelength ~ node spacing, fine: ~ point spacing), so that corresponding points have
+    near-equal features whatever the motion.
+    Returns dict(ref_points_f, src_points_f, ref_points_c, src_points_c, ref_feats_c, src_feats_c, ref_feats_f,
+    src_feats_f, transform) -- all fp32 CPU; transform (4,4) maps src onto ref."""
+    gen = torch.Generator().manual_seed(seed)
+    ref_c = make_cloud('3dmatch', num_nodes, gen)
+    ref_f = make_fine_cloud('3dmatch', ref_c, points_per_node, gen)
+    R = _rotation(gen, 45.0).float()
+    t = (torch.rand(3, generator=gen) - 0.5)
+    T = torch.eye(4)
+    T[:3, :3], T[:3, 3] = R, t
+
+    def to_src(p):  # ref frame -> src frame: p_ref = R p_src + t
+        return (p - t) @ R  # rows: R^T (p - t)
+
+    def take(p, frac, jitter):
+        idx = torch.randperm(p.shape[0], generator=gen)[:max(4, int(frac * p.shape[0]))]
+        q = p[idx] + torch.randn(idx.shape[0], 3, generator=gen) * jitter
+        return q.contiguous()
+
+    src_f_ref = take(ref_f, keep, noise)        # src points, still in the ref frame
+    src_c_ref = take(ref_c, keep, 0.02)
+
+    def fourier(p, wavelength, g):
+        omega = torch.randn(3, dim, generator=g) * (2.0 * math.pi / wavelength) / math.sqrt(3.0)
+        phase = torch.rand(dim, generator=g) * 2.0 * math.pi
+        return omega, phase
+
+    gc = torch.Generator().manual_seed(seed + 1)
+    oc, pc = fourier(None, 1.2, gc)
+    of, pf = fourier(None, 0.25, gc)
+
+    def feats(p, omega, phase):
+        f = torch.cos(p @ omega + phase)
+        return (f + torch.randn(f.shape, generator=gen) * feat_noise).contiguous()
+
+    return dict(ref_points_f=ref_f, src_points_f=to_src(src_f_ref).contiguous(), ref_points_c=ref_c.contiguous(),
+                src_points_c=to_src(src_c_ref).contiguous(), ref_feats_c=feats(ref_c, oc, pc),
+                src_feats_c=feats(src_c_ref, oc, pc), ref_feats_f=feats(ref_f, of, pf),
+                src_feats_f=feats(src_f_ref, of, pf), transform=T)
