@@ -317,6 +317,34 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
+def time_patch_scores(pkg, shape, calls=10, replays=5):
+    """geotx_patch_scores (K12: the glue of model.py:169-170,176-179,187-188 between coarse matching and optimal
+    transport) for one pair's 256 node correspondences; us per pair, next to the same lines written with stock torch
+    ops on the same GPU (both replayed from a CUDA graph)."""
+    import torch
+    try:
+        K, n, M = (128, 49152, 2048) if shape == 'kitti' else (64, 16384, 1024)
+        g = torch.Generator().manual_seed(pkg.synth.SEED)
+        feats = [torch.randn(n, 256, generator=g).cuda() for _ in range(2)]
+        knn = [torch.randint(0, n + 1, (M, K), generator=g).cuda() for _ in range(2)]
+        corr = [torch.randint(0, M, (256,), generator=g).cuda() for _ in range(2)]
+
+        def torch_glue():
+            a = torch.cat([feats[0], torch.zeros_like(feats[0][:1])], dim=0)[knn[0][corr[0]]]
+            b = torch.cat([feats[1], torch.zeros_like(feats[1][:1])], dim=0)[knn[1][corr[1]]]
+            return torch.einsum('bnd,bmd->bnm', a, b) / 256 ** 0.5
+        us = _graph_time_us(lambda: pkg.ops.patch_scores(feats[0], feats[1], knn[0], knn[1], corr[0], corr[1]),
+                            calls, replays)
+        ref = _graph_time_us(torch_glue, calls, replays)
+        flops = 2.0 * 256 * K * K * 256
+        return {'us_per_pair': us, 'stock_torch_us': ref, 'node_correspondences': 256, 'points_per_patch': K,
+                'channels': 256, 'fine_points': n, 'kernels_per_call': 1, 'dtype': 'f32 FMA',
+                'tflops': flops / us * 1e-6,
+                'timing': f'{calls} pairs captured in one CUDA graph, {replays} replays, CUDA events'}
+    except Exception as exc:
+        return {'error': f'{type(exc).__name__}: {exc}'}
+
+
 def time_registration(pkg, shape, calls=10, replays=5):
     """geotx_local_global_registration (4 kernels, K11) on one pair's 256 patch score matrices
     (local_global_registration.py:145-235 as model.py:198-205 calls it); us per pair on the GPU, and the oracle's torch
@@ -538,6 +566,7 @@ def run_b200(args):
         procrustes = time_procrustes(pkg, shape_name) if world == 1 else None
         pyramid = time_pyramid(pkg) if world == 1 else None
         registration = time_registration(pkg, shape_name) if world == 1 else None
+        patch_scores = time_patch_scores(pkg, shape_name) if world == 1 else None
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -581,7 +610,7 @@ def run_b200(args):
             'clocks': clocks,
             'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
                           'log_optimal_transport': transport, 'weighted_procrustes': procrustes,
-                          'local_global_registration': registration, 'collate_pyramid': pyramid},
+                          'patch_scores': patch_scores, 'local_global_registration': registration, 'collate_pyramid': pyramid},
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)

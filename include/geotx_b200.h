@@ -253,6 +253,19 @@ int geotx_local_global_registration(const float* ref_knn_points, const float* sr
                                     float* ref_corr_points, float* src_corr_points, float* corr_scores,
                                     int32_t* count_out, float* transform_out, void* workspace, void* stream);
 
+/* K12 patch matching scores: the glue between coarse matching and optimal transport.  Replaces
+ * experiments/<any>/model.py:169-170,176-179,187-188 (zero-row padding of the fine features, two (P,K,C) gathers,
+ * einsum('bnd,bmd->bnm') and the division by sqrt(C)).
+ *   ref_feats (n_ref, C), src_feats (n_src, C) f32, C % 4 == 0
+ *   ref_node_knn_indices (M_ref, K), src_node_knn_indices (M_src, K) int64 as point_to_node_partition returns them
+ *                    (n_ref / n_src marks a padded slot: its feature row is zero); K <= 128
+ *   ref_node_corr_indices, src_node_corr_indices (P,) int64 node correspondences (superpoint matching)
+ *   scores           (P, K, K) f32 out */
+int geotx_patch_scores(const float* ref_feats, int64_t n_ref, const float* src_feats, int64_t n_src, int C,
+                       const int64_t* ref_node_knn_indices, const int64_t* src_node_knn_indices, int K,
+                       const int64_t* ref_node_corr_indices, const int64_t* src_node_corr_indices, int P,
+                       float* scores, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,7 @@ from .modules import (  # noqa: F401
     MultiHeadAttention,
     RPEAttentionLayer, RPEConditionalTransformer, RPEMultiHeadAttention, RPETransformerLayer,
     SinusoidalPositionalEmbedding, SuperPointMatching, TransformerLayer, build_act_layer, build_dropout_layer,
-    LearnableLogOptimalTransport, LocalGlobalRegistration, WeightedProcrustes, grid_subsample, point_to_node_partition, precompute_data_stack_mode,
+    LearnableLogOptimalTransport, LocalGlobalRegistration, WeightedProcrustes, patch_matching_scores, grid_subsample, point_to_node_partition, precompute_data_stack_mode,
     radius_search,
     weighted_procrustes)
 
@@ -17,7 +17,7 @@ __all__ = [
     'GeometricTransformer', 'GraphedGeometricTransformer', 'PipelinedGeometricTransformer', 'GeometricStructureEmbedding', 'RPEConditionalTransformer', 'RPETransformerLayer',
     'RPEAttentionLayer', 'RPEMultiHeadAttention', 'TransformerLayer', 'AttentionLayer', 'MultiHeadAttention',
     'AttentionOutput', 'SinusoidalPositionalEmbedding', 'SuperPointMatching', 'LearnableLogOptimalTransport',
-    'LocalGlobalRegistration',
+    'LocalGlobalRegistration', 'patch_matching_scores',
     'point_to_node_partition', 'WeightedProcrustes', 'weighted_procrustes', 'radius_search', 'grid_subsample', 'precompute_data_stack_mode', 'ops', 'synth',
 ]
 

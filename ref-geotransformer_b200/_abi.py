@@ -42,6 +42,7 @@ SIGNATURES = {
     'geotx_lgr_workspace_bytes': (_i64, [_i, _i]),
     'geotx_local_global_registration': (_i, [_p, _p, _p, _p, _p, _i64, _i64, _p, _i, _i, _i, _f, _i, _f, _i, _i,
                                              _p, _p, _p, _p, _p, _p, _p]),
+    'geotx_patch_scores': (_i, [_p, _i64, _p, _i64, _i, _p, _p, _i, _p, _p, _i, _p, _p]),
 }
 
 GEOTX_F32 = 0

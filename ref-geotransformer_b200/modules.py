@@ -981,6 +981,17 @@ class LocalGlobalRegistration(nn.Module):
 
 
 @torch.no_grad()
+def patch_matching_scores(ref_feats_f, src_feats_f, ref_node_knn_indices, src_node_knn_indices, ref_node_corr_indices,
+                          src_node_corr_indices):
+    """The inline glue of experiments/*/model.py:169-170,176-179,187-188 as one call (K12): the (P, K, K) matching
+    scores of the node correspondences' patches, ready for LearnableLogOptimalTransport.  The reference has no function
+    of this name; a maintainer replaces those eight lines of `forward` by this call."""
+    return ops.patch_scores(ref_feats_f.contiguous(), src_feats_f.contiguous(), ref_node_knn_indices.contiguous(),
+                            src_node_knn_indices.contiguous(), ref_node_corr_indices.contiguous(),
+                            src_node_corr_indices.contiguous())
+
+
+@torch.no_grad()
 def radius_search(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit):
     """Drop-in for geotransformer/modules/ops/radius_search.py:7-27 for points that already live on
     the GPU: same arguments, same result -- (N, min(max_count, neighbor_limit)) int64, filled with M.  The reference

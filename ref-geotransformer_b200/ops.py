@@ -452,3 +452,29 @@ def local_global_registration(ref_knn_points, src_knn_points, ref_knn_masks, src
               int(num_refinement_steps), _p(ref_corr), _p(src_corr), _p(scores), _p(count), _p(transform), _p(work),
               _stream())
     return ref_corr, src_corr, scores, count, transform
+
+
+def patch_scores(ref_feats, src_feats, ref_node_knn_indices, src_node_knn_indices, ref_node_corr_indices,
+                 src_node_corr_indices):
+    """experiments/*/model.py:169-170,176-179,187-188 in one kernel: ref_feats (Nr,C), src_feats (Ns,C) fp32;
+    *_node_knn_indices (M,K) int64 (Nr / Ns = padded slot); *_node_corr_indices (P,) int64 -> scores (P,K,K) fp32 =
+    gathered patch feature products / sqrt(C).  Nothing synchronises."""
+    _check(ref_feats, 'ref_feats', torch.float32, 2)
+    _check(src_feats, 'src_feats', torch.float32, 2)
+    C = ref_feats.shape[1]
+    if src_feats.shape[1] != C or C % 4:
+        raise RuntimeError(f'feature widths must be equal and a multiple of 4, got {C} and {src_feats.shape[1]}')
+    for name, t, dims in (('ref_node_knn_indices', ref_node_knn_indices, 2), ('src_node_knn_indices', src_node_knn_indices, 2),
+                          ('ref_node_corr_indices', ref_node_corr_indices, 1), ('src_node_corr_indices', src_node_corr_indices, 1)):
+        _check(t, name, torch.int64, dims)
+    K = ref_node_knn_indices.shape[1]
+    P = ref_node_corr_indices.shape[0]
+    if src_node_knn_indices.shape[1] != K or src_node_corr_indices.shape[0] != P:
+        raise RuntimeError('ref and src sides must have the same patch size and the same number of correspondences')
+    out = torch.empty(P, K, K, dtype=torch.float32, device=ref_feats.device)
+    if P == 0:
+        return out
+    _abi.call('geotx_patch_scores', _p(ref_feats), int(ref_feats.shape[0]), _p(src_feats), int(src_feats.shape[0]), C,
+              _p(ref_node_knn_indices), _p(src_node_knn_indices), K, _p(ref_node_corr_indices),
+              _p(src_node_corr_indices), P, _p(out), _stream())
+    return out

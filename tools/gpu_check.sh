@@ -3,7 +3,7 @@
 # the CUDA context of the others), then smoke() and a short bench.  Logs land in gpurun_out/.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/gpu.txt 2>&1
-for f in gpu_k1_knn gpu_k3_attention gpu_k2_embed gpu_forward gpu_k5_matching gpu_next procrustes collate lgr tail_chain; do
+for f in gpu_k1_knn gpu_k3_attention gpu_k2_embed gpu_forward gpu_k5_matching gpu_next procrustes collate lgr tail_chain patch_scores; do
   timeout 600 python -m pytest tests/test_$f.py -m gpu -q -s --timeout 300 > gpurun_out/test_$f.log 2>&1
   echo "test_$f exit $?" | tee -a gpurun_out/summary.txt
   tail -n 15 gpurun_out/test_$f.log

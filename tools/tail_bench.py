@@ -13,7 +13,7 @@ pkg = pkgpath.load_package()
 tc.NUM_CORR, tc.POINT_LIMIT = 256, 64
 d = {k: v.cuda() for k, v in pkg.synth.make_tail_inputs(num_nodes=1024, points_per_node=16, seed=21).items()}
 stages = (pkg.point_to_node_partition, pkg.SuperPointMatching(256, True), pkg.LearnableLogOptimalTransport(100).cuda(),
-          pkg.LocalGlobalRegistration(3, 0.1))
+          pkg.LocalGlobalRegistration(3, 0.1), pkg.patch_matching_scores)
 out = tc.run_tail(d, *stages)
 torch.cuda.synchronize()
 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
