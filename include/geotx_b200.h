@@ -216,6 +216,17 @@ int geotx_radius_neighbors(const float* q_points, const float* s_points, const i
                            const int64_t* host_s_lengths, int batch, float radius, int limit, int64_t* neighbors,
                            int32_t* counts, int32_t* max_count, void* stream);
 
+/* The same search through per-element cell lists (uniform grid of cells of 1.001 x radius, 27 cells per query) instead
+ * of the exhaustive scan: identical results (same distance arithmetic, keys and selection), ~10-50x less work at the
+ * pyramid's sizes.  workspace: geotx_radius_neighbors_workspace_bytes(max_support_points, max_cells) bytes, 256-byte
+ * aligned; max_support_points >= every host_s_lengths[b]; when a batch element's grid would exceed max_cells its
+ * cells are made larger (still exact, only slower).  radius > 0. */
+int64_t geotx_radius_neighbors_workspace_bytes(int64_t max_support_points, int64_t max_cells);
+int geotx_radius_neighbors_grid(const float* q_points, const float* s_points, const int64_t* host_q_lengths,
+                                const int64_t* host_s_lengths, int batch, float radius, int limit, int64_t* neighbors,
+                                int32_t* counts, int32_t* max_count, void* workspace, int64_t max_support_points,
+                                int64_t max_cells, void* stream);
+
 /* Grid (voxel barycentre) subsampling in stack mode: extensions/cpu/grid_subsampling/
  * grid_subsampling_cpu.cpp:3-79 (ext.grid_subsampling; modules/ops/grid_subsample.py:9-22; utils/data.py:22-30).
  * Per batch element: voxels of size voxel_size anchored at floor(min_corner / voxel) * voxel (the reference's fp32

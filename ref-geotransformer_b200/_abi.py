@@ -37,6 +37,8 @@ SIGNATURES = {
     'geotx_log_optimal_transport': (_i, [_p, _p, _p, _p, _i, _f, _i, _i, _i, _p, _p]),
     'geotx_weighted_procrustes': (_i, [_p, _p, _p, _i, _i, _f, _f, _p, _p]),
     'geotx_radius_neighbors': (_i, [_p, _p, _p, _p, _i, _f, _i, _p, _p, _p, _p]),
+    'geotx_radius_neighbors_workspace_bytes': (_i64, [_i64, _i64]),
+    'geotx_radius_neighbors_grid': (_i, [_p, _p, _p, _p, _i, _f, _i, _p, _p, _p, _p, _i64, _i64, _p]),
     'geotx_grid_subsample_workspace_bytes': (_i64, [_i64]),
     'geotx_grid_subsample': (_i, [_p, _p, _i, _f, _p, _p, _p, _i64, _p]),
     'geotx_lgr_workspace_bytes': (_i64, [_i, _i]),

@@ -354,11 +354,15 @@ def _host_lengths(lengths, name):
     return (ctypes.c_int64 * len(vals))(*vals), vals
 
 
-def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit):
+_RN_WORK = {}
+
+
+def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit, method='grid', max_cells=1 << 21):
     """extensions/cpu/radius_neighbors (ext.radius_neighbors) + modules/ops/radius_search.py:24-27 on the device.
     q_points (Nq,3), s_points (Ns,3) fp32 CUDA; q_lengths, s_lengths: the batch lengths (host).  Returns
     (neighbors int64 (Nq, neighbor_limit) padded with Ns, counts int32 (Nq,), max_count int32 (1,)); nothing
-    synchronises."""
+    synchronises.  method 'grid' (default) searches per-element cell lists (geotx_radius_neighbors_grid), 'brute' scans
+    every support point (geotx_radius_neighbors); the results are identical."""
     _check(q_points, 'q_points', torch.float32, 2)
     _check(s_points, 's_points', torch.float32, 2)
     if q_points.shape[1] != 3 or s_points.shape[1] != 3:
@@ -372,8 +376,23 @@ def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_
     neighbors = torch.empty(q_points.shape[0], limit, dtype=torch.int64, device=dev)
     counts = torch.empty(q_points.shape[0], dtype=torch.int32, device=dev)
     max_count = torch.empty(1, dtype=torch.int32, device=dev)
-    _abi.call('geotx_radius_neighbors', _p(q_points), _p(s_points), ql, sl, len(qv), float(radius), limit, _p(neighbors),
-              _p(counts), _p(max_count), _stream())
+    if method == 'brute' or not float(radius) > 0.0:
+        _abi.call('geotx_radius_neighbors', _p(q_points), _p(s_points), ql, sl, len(qv), float(radius), limit,
+                  _p(neighbors), _p(counts), _p(max_count), _stream())
+        return neighbors, counts, max_count
+    if method != 'grid':
+        raise RuntimeError(f"radius_neighbors: method must be 'grid' or 'brute', got {method!r}")
+    cap = 1024
+    while cap < max(sv + [1]):
+        cap <<= 1
+    key = (dev, cap, int(max_cells))
+    if key not in _RN_WORK:
+        nbytes = _abi.load().geotx_radius_neighbors_workspace_bytes(cap, int(max_cells))
+        if nbytes <= 0:
+            raise RuntimeError(f'radius_neighbors: bad max_cells={max_cells}')
+        _RN_WORK[key] = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    _abi.call('geotx_radius_neighbors_grid', _p(q_points), _p(s_points), ql, sl, len(qv), float(radius), limit,
+              _p(neighbors), _p(counts), _p(max_count), _p(_RN_WORK[key]), cap, int(max_cells), _stream())
     return neighbors, counts, max_count
 
 

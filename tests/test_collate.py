@@ -150,6 +150,34 @@ def test_gpu_empty_batch_element(pkg):
     assert torch.equal(with_empty, without)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize('nq,ns,radius,limit,max_cells', [
+    ((20000, 18000), (20000, 18000), 0.0625, 38, 1 << 21),   # the pyramid's stage 0
+    ((6000, 5000), (1500, 1400), 0.25, 36, 1 << 21),         # a down-sampling search: queries and supports differ
+    ((1500, 1400), (6000, 5000), 0.125, 64, 1 << 21),        # up-sampling
+    ((4000, 3000), (4000, 3000), 0.0625, 38, 64),            # grid capped at 64 cells: larger cells, same result
+    ((300, 200), (300, 200), 100.0, 512, 1 << 21),           # everything in range: one cell
+    ((2000, 1), (1, 2000), 0.3, 16, 1 << 10),
+])
+def test_gpu_cell_lists_equal_exhaustive_scan(pkg, nq, ns, radius, limit, max_cells):
+    """The cell-list search and the exhaustive scan share the distance arithmetic, the keys and the selection: their
+    outputs are equal bit for bit, also for queries outside the supports' bounding box."""
+    from gpu_common import DEV
+    g = torch.Generator().manual_seed(sum(nq) + limit)
+    clouds = [pkg.synth.make_dense_cloud(n, 3.0, 50 + b) for b, n in enumerate(ns)]
+    queries = []
+    for c, n in zip(clouds, nq):  # jittered copies of support points; one in twenty pushed outside the supports' box
+        pick = c[torch.randint(0, c.shape[0], (n,), generator=g)] + torch.randn(n, 3, generator=g) * 0.02
+        pick[torch.rand(n, generator=g) < 0.05] += 3.2
+        queries.append(pick)
+    q, s = torch.cat(queries).to(DEV), torch.cat(clouds).to(DEV)
+    a = pkg.ops.radius_neighbors(q, s, list(nq), list(ns), radius, limit, method='grid', max_cells=max_cells)
+    b = pkg.ops.radius_neighbors(q, s, list(nq), list(ns), radius, limit, method='brute')
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    assert int(a[2]) > 0
+
+
 # ---- K10 grid subsampling -----------------------------------------------------------------------------------------
 GS_CASES = [((5000, 4000), 3.0, 0.05), ((30000, 25000), 3.0, 0.05), ((12000, 12000), 3.0, 0.1), ((300, 1, 7), 3.0, 0.4)]
 GS_TOL = 2e-6  # relative to the cloud's extent: fp64 sums rounded once vs the reference's sequential fp32 sums

@@ -8,4 +8,4 @@ echo "next_bench exit $?" | tee -a gpurun_out/summary.txt
 python -c "
 import json; d=json.load(open('gpurun_out/next_bench.json'))
 for k,v in d.items():
-    if 'radius' in k: print(k, v)"; tail -n 5 gpurun_out/next_bench.err
+    if 'radius' in k or 'pyramid' in k: print(k, v)"; tail -n 5 gpurun_out/next_bench.err

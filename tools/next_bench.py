@@ -136,6 +136,7 @@ def main():
         s_cpu = torch.cat(clouds)
         s_gpu = s_cpu.cuda()
         row = {'us': timed(lambda: pkg.ops.radius_neighbors(s_gpu, s_gpu, list(sizes), list(sizes), radius, limit)),
+               'brute_us': timed(lambda: pkg.ops.radius_neighbors(s_gpu, s_gpu, list(sizes), list(sizes), radius, limit, method='brute')),
                'points': list(sizes), 'radius': radius, 'limit': limit,
                'pair_evals': sum(n * n for n in sizes)}
         if with_torch and ref_cpu.available():  # the reference's own operator (nanoflann KD-tree, one host thread)
