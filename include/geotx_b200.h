@@ -219,8 +219,9 @@ int geotx_radius_neighbors(const float* q_points, const float* s_points, const i
 /* The same search through per-element cell lists (uniform grid of cells of 1.001 x radius, 27 cells per query) instead
  * of the exhaustive scan: identical results (same distance arithmetic, keys and selection), ~10-50x less work at the
  * pyramid's sizes.  workspace: geotx_radius_neighbors_workspace_bytes(max_support_points, max_cells) bytes, 256-byte
- * aligned; max_support_points >= every host_s_lengths[b]; when a batch element's grid would exceed max_cells its
- * cells are made larger (still exact, only slower).  radius > 0. */
+ * aligned; max_support_points >= sum(host_s_lengths); max_cells is per batch element (8 grids are kept, for the 8
+ * elements one set of launches searches): when an element's grid would exceed it the cells are made larger (still
+ * exact, only slower).  radius > 0. */
 int64_t geotx_radius_neighbors_workspace_bytes(int64_t max_support_points, int64_t max_cells);
 int geotx_radius_neighbors_grid(const float* q_points, const float* s_points, const int64_t* host_q_lengths,
                                 const int64_t* host_s_lengths, int batch, float radius, int limit, int64_t* neighbors,

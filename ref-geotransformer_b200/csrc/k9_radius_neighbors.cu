@@ -135,11 +135,19 @@ radius_neighbors_kernel(const float* __restrict__ q_points, int q_begin, int q_c
 // (distance, index) keys and bitonic select as the brute-force path, so the results are identical (the order in which
 // candidates are met does not matter: keys are unique and sorted).  A cell edge of 1.001 x radius (or larger, when the
 // grid would not fit `max_cells`) covers the rounding of the cell index computation.
-struct RnGrid {
-    unsigned int* bounds;  // [6] order-preserving encodings: min x,y,z, max x,y,z
-    float* params;         // [8] origin x,y,z, 1/cell, then nx, ny, nz as int bits
-    int* head;             // [max_cells] first point of the cell's list, -1: empty
-    float4* cell_points;   // [max support points of an element] x, y, z and (as int bits) the next point of the cell's list
+constexpr int RNG_SLOTS = 8;  // batch elements searched by one set of launches (blockIdx.y)
+
+struct RnBatch {  // by value in the kernel parameters: the lengths live on the host, as in the reference
+    int n;
+    int q_begin[RNG_SLOTS], q_count[RNG_SLOTS], s_begin[RNG_SLOTS], s_count[RNG_SLOTS];
+};
+
+struct RnGrid {  // one grid per slot
+    unsigned int* bounds;  // [2][RNG_SLOTS][3] order-preserving encodings: min x,y,z of every slot, then max x,y,z
+    float* params;         // [RNG_SLOTS][8] origin x,y,z, 1/cell, then nx, ny, nz as int bits
+    int* head;             // [RNG_SLOTS][max_cells] first point of the cell's list (index inside the element), -1: empty
+    long long max_cells;
+    float4* cell_points;   // [stacked support points] x, y, z and (as int bits) the next point of the cell's list
 };
 
 __device__ __forceinline__ unsigned int rn_encode(float f) {
@@ -150,7 +158,8 @@ __device__ __forceinline__ float rn_decode(unsigned int e) {
     return __uint_as_float((e & 0x80000000u) ? (e & 0x7fffffffu) : ~e);
 }
 
-__global__ void rn_bounds_kernel(const float* __restrict__ s_points, int s_begin, int s_count, RnGrid g) {
+__global__ void rn_bounds_kernel(const float* __restrict__ s_points, RnBatch b, RnGrid g) {
+    const int e = blockIdx.y, s_begin = b.s_begin[e], s_count = b.s_count[e];
     float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < s_count; i += gridDim.x * blockDim.x) {
 #pragma unroll
@@ -168,18 +177,23 @@ __global__ void rn_bounds_kernel(const float* __restrict__ s_points, int s_begin
             hi[d] = fmaxf(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], off));
         }
         if ((threadIdx.x & 31) == 0) {
-            atomicMin(&g.bounds[d], rn_encode(lo[d]));
-            atomicMax(&g.bounds[3 + d], rn_encode(hi[d]));
+            atomicMin(&g.bounds[3 * e + d], rn_encode(lo[d]));
+            atomicMax(&g.bounds[3 * (RNG_SLOTS + e) + d], rn_encode(hi[d]));
         }
     }
 }
 
-// One thread: the grid of this batch element.
-__global__ void rn_params_kernel(float radius, long long max_cells, RnGrid g) {
-    float lo[3], ext[3];
-    for (int d = 0; d < 3; ++d) {
-        lo[d] = rn_decode(g.bounds[d]);
-        ext[d] = fmaxf(rn_decode(g.bounds[3 + d]) - lo[d], 0.f);
+// One thread per slot: the grid of its batch element.
+__global__ void rn_params_kernel(float radius, RnBatch b, RnGrid g) {
+    const int e = threadIdx.x;
+    if (e >= b.n) return;
+    float* params = g.params + 8 * e;
+    float lo[3] = {0.f, 0.f, 0.f}, ext[3] = {0.f, 0.f, 0.f};
+    if (b.s_count[e] > 0) {
+        for (int d = 0; d < 3; ++d) {
+            lo[d] = rn_decode(g.bounds[3 * e + d]);
+            ext[d] = fmaxf(rn_decode(g.bounds[3 * (RNG_SLOTS + e) + d]) - lo[d], 0.f);
+        }
     }
     float cell = fmaxf(radius * 1.001f, 1e-30f);
     int n[3];
@@ -192,14 +206,14 @@ __global__ void rn_params_kernel(float radius, long long max_cells, RnGrid g) {
             n[d] = (int)cnt;
             total *= n[d];
         }
-        if (fits && total <= max_cells) break;
+        if (fits && total <= g.max_cells) break;
         cell *= 1.25f;
     }
     for (int d = 0; d < 3; ++d) {
-        g.params[d] = lo[d];
-        g.params[4 + d] = __int_as_float(n[d]);
+        params[d] = lo[d];
+        params[4 + d] = __int_as_float(n[d]);
     }
-    g.params[3] = 1.0f / cell;
+    params[3] = 1.0f / cell;
 }
 
 __device__ __forceinline__ void rn_cell_of(const float* __restrict__ params, float x, float y, float z, int (&c)[3]) {
@@ -208,26 +222,32 @@ __device__ __forceinline__ void rn_cell_of(const float* __restrict__ params, flo
     c[2] = (int)floorf((z - params[2]) * params[3]);
 }
 
-__global__ void rn_build_kernel(const float* __restrict__ s_points, int s_begin, int s_count, RnGrid g) {
+__global__ void rn_build_kernel(const float* __restrict__ s_points, RnBatch b, RnGrid g) {
+    const int e = blockIdx.y, s_begin = b.s_begin[e], s_count = b.s_count[e];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= s_count) return;
+    const float* params = g.params + 8 * e;
     const float* p = s_points + 3 * (size_t)(s_begin + i);
     int c[3];
-    rn_cell_of(g.params, p[0], p[1], p[2], c);
-    const int nx = __float_as_int(g.params[4]), ny = __float_as_int(g.params[5]), nz = __float_as_int(g.params[6]);
+    rn_cell_of(params, p[0], p[1], p[2], c);
+    const int nx = __float_as_int(params[4]), ny = __float_as_int(params[5]), nz = __float_as_int(params[6]);
     c[0] = min(max(c[0], 0), nx - 1);  // support points are inside the box; the clamp only absorbs rounding at the faces
     c[1] = min(max(c[1], 0), ny - 1);
     c[2] = min(max(c[2], 0), nz - 1);
-    const int next = atomicExch(&g.head[((size_t)c[2] * ny + c[1]) * nx + c[0]], i);
-    g.cell_points[i] = make_float4(p[0], p[1], p[2], __int_as_float(next));  // one 16-byte load per hop of a walk
+    const int next = atomicExch(&g.head[(size_t)e * g.max_cells + ((size_t)c[2] * ny + c[1]) * nx + c[0]], i);
+    g.cell_points[s_begin + i] = make_float4(p[0], p[1], p[2], __int_as_float(next));  // one 16-byte load per hop
 }
 
 constexpr int RNG_WARPS = 8;  // queries per CTA, one warp each
 
 __global__ void __launch_bounds__(RNG_WARPS * 32)
-rn_grid_query_kernel(const float* __restrict__ q_points, int q_begin, int q_count, const float* __restrict__ s_points,
-                     int s_begin, long long sentinel, float r2, int limit, int buf_len, RnGrid g,
-                     long long* __restrict__ neighbors, int* __restrict__ counts, int* __restrict__ max_count) {
+rn_grid_query_kernel(const float* __restrict__ q_points, RnBatch b, long long sentinel, float r2, int limit, int buf_len,
+                     RnGrid g, long long* __restrict__ neighbors, int* __restrict__ counts,
+                     int* __restrict__ max_count) {
+    const int e = blockIdx.y, q_begin = b.q_begin[e], q_count = b.q_count[e], s_begin = b.s_begin[e];
+    const float* params = g.params + 8 * e;
+    const int* head = g.head + (size_t)e * g.max_cells;
+    const float4* cell_points = g.cell_points + s_begin;
     extern __shared__ __align__(16) unsigned char rng_smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     unsigned long long* buf = reinterpret_cast<unsigned long long*>(rng_smem) + (size_t)wid * buf_len;
@@ -235,9 +255,9 @@ rn_grid_query_kernel(const float* __restrict__ q_points, int q_begin, int q_coun
     if (q >= q_count) return;
     const float* qp = q_points + 3 * (size_t)(q_begin + q);
     const float qx = qp[0], qy = qp[1], qz = qp[2];
-    const int nx = __float_as_int(g.params[4]), ny = __float_as_int(g.params[5]), nz = __float_as_int(g.params[6]);
+    const int nx = __float_as_int(params[4]), ny = __float_as_int(params[5]), nz = __float_as_int(params[6]);
     int c[3];
-    rn_cell_of(g.params, qx, qy, qz, c);
+    rn_cell_of(params, qx, qy, qz, c);
     // A query may lie outside the support box (the two clouds of a search differ): its own cell is not clamped, cells
     // outside the grid are empty.  A support point clamped onto a face cell is still within one cell of where the
     // unclamped index would put it.
@@ -245,7 +265,7 @@ rn_grid_query_kernel(const float* __restrict__ q_points, int q_begin, int q_coun
     if (lane < 27) {
         const int cx = c[0] + lane % 3 - 1, cy = c[1] + (lane / 3) % 3 - 1, cz = c[2] + lane / 9 - 1;
         if (cx >= 0 && cx < nx && cy >= 0 && cy < ny && cz >= 0 && cz < nz)
-            cur = g.head[((size_t)cz * ny + cy) * nx + cx];
+            cur = head[((size_t)cz * ny + cy) * nx + cx];
     }
     int filled = 0, total = 0;
     while (__any_sync(0xffffffffu, cur >= 0)) {
@@ -253,7 +273,7 @@ rn_grid_query_kernel(const float* __restrict__ q_points, int q_begin, int q_coun
         bool hit = false;
         const int cand = cur;
         if (cand >= 0) {
-            const float4 sp = g.cell_points[cand];
+            const float4 sp = cell_points[cand];
             const float dx = __fsub_rn(qx, sp.x), dy = __fsub_rn(qy, sp.y), dz = __fsub_rn(qz, sp.z);
             d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
             hit = d < r2;
@@ -326,16 +346,22 @@ static size_t rn_align(size_t x) { return (x + 255) & ~(size_t)255; }
 static size_t rn_grid_layout(int64_t max_support, int64_t max_cells, char* base, RnGrid* g) {
     size_t off = 0;
     auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += rn_align(bytes); return p; };
-    char* a = take(6 * sizeof(unsigned int));
-    char* b = take(8 * sizeof(float));
-    char* c = take((size_t)max_cells * sizeof(int));
+    char* a = take(2 * RNG_SLOTS * 3 * sizeof(unsigned int));
+    char* b = take(RNG_SLOTS * 8 * sizeof(float));
+    char* c = take((size_t)RNG_SLOTS * max_cells * sizeof(int));
     char* d = take((size_t)max_support * sizeof(float4));
-    if (g) { g->bounds = (unsigned int*)a; g->params = (float*)b; g->head = (int*)c; g->cell_points = (float4*)d; }
+    if (g) {
+        g->bounds = (unsigned int*)a;
+        g->params = (float*)b;
+        g->head = (int*)c;
+        g->max_cells = max_cells;
+        g->cell_points = (float4*)d;
+    }
     return off;
 }
 
 extern "C" int64_t geotx_radius_neighbors_workspace_bytes(int64_t max_support_points, int64_t max_cells) {
-    if (max_support_points < 0 || max_cells < 1 || max_cells > 2147483647LL || max_support_points > 2147483647LL) return 0;
+    if (max_support_points < 0 || max_cells < 1 || max_cells > 268435456LL || max_support_points > 2147483647LL) return 0;
     return (int64_t)rn_grid_layout(max_support_points, max_cells, nullptr, nullptr);
 }
 
@@ -347,16 +373,17 @@ extern "C" int geotx_radius_neighbors_grid(const float* q_points, const float* s
                   "geotx_radius_neighbors_grid: null pointer");
     GEOTX_REQUIRE(batch > 0 && limit > 0 && limit <= GEOTX_MAX_NEIGHBOR_LIMIT,
                   "geotx_radius_neighbors_grid: bad batch=%d or limit=%d (max %d)", batch, limit, GEOTX_MAX_NEIGHBOR_LIMIT);
-    GEOTX_REQUIRE(max_cells >= 1 && max_cells <= 2147483647LL && radius > 0.f,
+    GEOTX_REQUIRE(max_cells >= 1 && max_cells <= 268435456LL && radius > 0.f,
                   "geotx_radius_neighbors_grid: bad max_cells=%lld or radius", (long long)max_cells);
     int64_t nq = 0, ns = 0;
     for (int b = 0; b < batch; ++b) {
-        GEOTX_REQUIRE(host_q_lengths[b] >= 0 && host_s_lengths[b] >= 0 && host_s_lengths[b] <= max_support_points,
-                      "geotx_radius_neighbors_grid: length of element %d negative or above max_support_points", b);
+        GEOTX_REQUIRE(host_q_lengths[b] >= 0 && host_s_lengths[b] >= 0, "geotx_radius_neighbors_grid: negative length");
         nq += host_q_lengths[b];
         ns += host_s_lengths[b];
     }
-    GEOTX_REQUIRE(nq < 2147483647LL && ns < 2147483647LL, "geotx_radius_neighbors_grid: too many points");
+    GEOTX_REQUIRE(nq < 2147483647LL && ns < 2147483647LL && ns <= max_support_points,
+                  "geotx_radius_neighbors_grid: %lld support points, workspace sized for %lld", (long long)ns,
+                  (long long)max_support_points);
     cudaStream_t st = (cudaStream_t)stream;
     RnGrid g;
     rn_grid_layout(max_support_points, max_cells, (char*)workspace, &g);
@@ -364,41 +391,43 @@ extern "C" int geotx_radius_neighbors_grid(const float* q_points, const float* s
     if (rc) return rc;
     int buf_len = 64;
     while (buf_len < 2 * limit) buf_len <<= 1;
-    const size_t smem_grid = (size_t)RNG_WARPS * buf_len * sizeof(unsigned long long);
-    const size_t smem_brute = RN_TILE * sizeof(float4) + (size_t)RN_WARPS * RN_Q * buf_len * sizeof(unsigned long long);
-    if (smem_grid > 48 * 1024) {
-        rc = check_cuda(cudaFuncSetAttribute(rn_grid_query_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem_grid), "geotx_radius_neighbors_grid: shared memory");
-        if (rc) return rc;
-    }
-    if (smem_brute > 48 * 1024) {
-        rc = check_cuda(cudaFuncSetAttribute(radius_neighbors_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem_brute), "geotx_radius_neighbors_grid: shared memory");
+    const size_t smem = (size_t)RNG_WARPS * buf_len * sizeof(unsigned long long);
+    if (smem > 48 * 1024) {
+        rc = check_cuda(cudaFuncSetAttribute(rn_grid_query_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                        "geotx_radius_neighbors_grid: shared memory");
         if (rc) return rc;
     }
     const float r2 = radius * radius;  // radius_neighbors_cpu.cpp:12
     int64_t q0 = 0, s0 = 0;
-    for (int b = 0; b < batch; ++b) {
-        const int qc = (int)host_q_lengths[b], sc = (int)host_s_lengths[b];
-        if (qc > 0 && sc == 0) {  // nothing to bin: the scan kernel writes the sentinels
-            radius_neighbors_kernel<<<(qc + RN_WARPS * RN_Q - 1) / (RN_WARPS * RN_Q), RN_WARPS * 32, smem_brute, st>>>(
-                q_points, (int)q0, qc, s_points, (int)s0, sc, (long long)ns, r2, limit, buf_len, (long long*)neighbors,
-                counts, max_count);
-        } else if (qc > 0) {
-            rc = check_cuda(cudaMemsetAsync(g.bounds, 0xff, 3 * sizeof(unsigned int), st), "memset bounds");
-            if (!rc) rc = check_cuda(cudaMemsetAsync(g.bounds + 3, 0, 3 * sizeof(unsigned int), st), "memset bounds");
-            if (!rc) rc = check_cuda(cudaMemsetAsync(g.head, 0xff, (size_t)max_cells * sizeof(int), st), "memset head");
-            if (rc) return rc;
-            const int blocks = (sc + 255) / 256;
-            rn_bounds_kernel<<<blocks < 148 ? blocks : 148, 256, 0, st>>>(s_points, (int)s0, sc, g);
-            rn_params_kernel<<<1, 1, 0, st>>>(radius, (long long)max_cells, g);
-            rn_build_kernel<<<blocks, 256, 0, st>>>(s_points, (int)s0, sc, g);
-            rn_grid_query_kernel<<<(qc + RNG_WARPS - 1) / RNG_WARPS, RNG_WARPS * 32, smem_grid, st>>>(
-                q_points, (int)q0, qc, s_points, (int)s0, (long long)ns, r2, limit, buf_len, g, (long long*)neighbors,
-                counts, max_count);
+    for (int first = 0; first < batch; first += RNG_SLOTS) {  // RNG_SLOTS batch elements per set of launches
+        RnBatch b;
+        b.n = batch - first < RNG_SLOTS ? batch - first : RNG_SLOTS;
+        int q_max = 0, s_max = 0;
+        for (int e = 0; e < RNG_SLOTS; ++e) {
+            const bool live = e < b.n;
+            b.q_begin[e] = (int)q0;
+            b.s_begin[e] = (int)s0;
+            b.q_count[e] = live ? (int)host_q_lengths[first + e] : 0;
+            b.s_count[e] = live ? (int)host_s_lengths[first + e] : 0;
+            q0 += b.q_count[e];
+            s0 += b.s_count[e];
+            q_max = b.q_count[e] > q_max ? b.q_count[e] : q_max;
+            s_max = b.s_count[e] > s_max ? b.s_count[e] : s_max;
         }
-        q0 += qc;
-        s0 += sc;
+        if (q_max == 0) continue;
+        rc = check_cuda(cudaMemsetAsync(g.bounds, 0xff, RNG_SLOTS * 3 * sizeof(unsigned int), st), "memset bounds");
+        if (!rc) rc = check_cuda(cudaMemsetAsync(g.bounds + RNG_SLOTS * 3, 0, RNG_SLOTS * 3 * sizeof(unsigned int), st),
+                                 "memset bounds");
+        if (!rc) rc = check_cuda(cudaMemsetAsync(g.head, 0xff, (size_t)b.n * max_cells * sizeof(int), st), "memset head");
+        if (rc) return rc;
+        if (s_max > 0) {
+            const int blocks = (s_max + 255) / 256;
+            rn_bounds_kernel<<<dim3(blocks < 148 ? blocks : 148, b.n), 256, 0, st>>>(s_points, b, g);
+        }
+        rn_params_kernel<<<1, 32, 0, st>>>(radius, b, g);
+        if (s_max > 0) rn_build_kernel<<<dim3((s_max + 255) / 256, b.n), 256, 0, st>>>(s_points, b, g);
+        rn_grid_query_kernel<<<dim3((q_max + RNG_WARPS - 1) / RNG_WARPS, b.n), RNG_WARPS * 32, smem, st>>>(
+            q_points, b, (long long)ns, r2, limit, buf_len, g, (long long*)neighbors, counts, max_count);
     }
     return launch_status("geotx_radius_neighbors_grid");
 }

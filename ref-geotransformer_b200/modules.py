@@ -1037,15 +1037,28 @@ def precompute_data_stack_mode(points, lengths, num_stages, voxel_size, radius, 
         points_list.append(points)
         lengths_list.append(lengths)
         voxel_size *= 2
-    for i in range(num_stages):  # data.py:33-72
+    # data.py:33-72.  All searches are enqueued with fixed-width results; the widths of the reference's results
+    # (min(max_count, limit), radius_search.py:24-27) are read back together afterwards: one synchronisation for the
+    # ten searches instead of one each.
+    pending = []  # (list to fill, fixed-width neighbors, max_count, limit)
+
+    def search(dst, q_points, s_points, q_lengths, s_lengths, r, limit):
+        if limit <= 0:
+            raise RuntimeError('precompute_data_stack_mode: neighbor limits must be positive on the GPU path')
+        nb, _, max_count = ops.radius_neighbors(q_points.contiguous(), s_points.contiguous(), q_lengths, s_lengths, r,
+                                                limit)
+        pending.append((dst, nb, max_count, int(limit)))
+
+    for i in range(num_stages):
         cur_points, cur_lengths = points_list[i], lengths_list[i]
-        neighbors_list.append(radius_search(cur_points, cur_points, cur_lengths, cur_lengths, radius, neighbor_limits[i]))
+        search(neighbors_list, cur_points, cur_points, cur_lengths, cur_lengths, radius, neighbor_limits[i])
         if i < num_stages - 1:
             sub_points, sub_lengths = points_list[i + 1], lengths_list[i + 1]
-            subsampling_list.append(radius_search(sub_points, cur_points, sub_lengths, cur_lengths, radius,
-                                                  neighbor_limits[i]))
-            upsampling_list.append(radius_search(cur_points, sub_points, cur_lengths, sub_lengths, radius * 2,
-                                                 neighbor_limits[i + 1]))
+            search(subsampling_list, sub_points, cur_points, sub_lengths, cur_lengths, radius, neighbor_limits[i])
+            search(upsampling_list, cur_points, sub_points, cur_lengths, sub_lengths, radius * 2, neighbor_limits[i + 1])
         radius *= 2
+    widths = torch.cat([m for _, _, m, _ in pending]).tolist()
+    for (dst, nb, _, limit), width in zip(pending, widths):
+        dst.append(nb[:, :width] if width < limit else nb)
     return {'points': points_list, 'lengths': lengths_list, 'neighbors': neighbors_list,
             'subsampling': subsampling_list, 'upsampling': upsampling_list}

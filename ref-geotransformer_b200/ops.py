@@ -357,7 +357,7 @@ def _host_lengths(lengths, name):
 _RN_WORK = {}
 
 
-def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit, method='grid', max_cells=1 << 21):
+def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit, method='grid', max_cells=1 << 20):
     """extensions/cpu/radius_neighbors (ext.radius_neighbors) + modules/ops/radius_search.py:24-27 on the device.
     q_points (Nq,3), s_points (Ns,3) fp32 CUDA; q_lengths, s_lengths: the batch lengths (host).  Returns
     (neighbors int64 (Nq, neighbor_limit) padded with Ns, counts int32 (Nq,), max_count int32 (1,)); nothing
@@ -383,7 +383,7 @@ def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_
     if method != 'grid':
         raise RuntimeError(f"radius_neighbors: method must be 'grid' or 'brute', got {method!r}")
     cap = 1024
-    while cap < max(sv + [1]):
+    while cap < sum(sv):
         cap <<= 1
     key = (dev, cap, int(max_cells))
     if key not in _RN_WORK:

@@ -158,15 +158,20 @@ def test_gpu_empty_batch_element(pkg):
     ((4000, 3000), (4000, 3000), 0.0625, 38, 64),            # grid capped at 64 cells: larger cells, same result
     ((300, 200), (300, 200), 100.0, 512, 1 << 21),           # everything in range: one cell
     ((2000, 1), (1, 2000), 0.3, 16, 1 << 10),
+    ((200,) * 11, (300,) * 11, 0.3, 24, 1 << 12),            # more batch elements than one set of launches takes
+    ((500, 0, 400), (600, 0, 300), 0.3, 16, 1 << 12),        # an empty element in the middle
 ])
 def test_gpu_cell_lists_equal_exhaustive_scan(pkg, nq, ns, radius, limit, max_cells):
     """The cell-list search and the exhaustive scan share the distance arithmetic, the keys and the selection: their
     outputs are equal bit for bit, also for queries outside the supports' bounding box."""
     from gpu_common import DEV
     g = torch.Generator().manual_seed(sum(nq) + limit)
-    clouds = [pkg.synth.make_dense_cloud(n, 3.0, 50 + b) for b, n in enumerate(ns)]
+    clouds = [pkg.synth.make_dense_cloud(n, 3.0, 50 + b) if n else torch.zeros(0, 3) for b, n in enumerate(ns)]
     queries = []
     for c, n in zip(clouds, nq):  # jittered copies of support points; one in twenty pushed outside the supports' box
+        if n == 0 or c.shape[0] == 0:
+            queries.append(torch.rand(n, 3, generator=g) * 3.0)
+            continue
         pick = c[torch.randint(0, c.shape[0], (n,), generator=g)] + torch.randn(n, 3, generator=g) * 0.02
         pick[torch.rand(n, generator=g) < 0.05] += 3.2
         queries.append(pick)
