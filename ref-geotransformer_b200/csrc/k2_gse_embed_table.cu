@@ -1,0 +1,173 @@
+// K2t (experimental, opt-in): GeometricStructureEmbedding by TABULATION instead of by contraction.
+//
+// geotransformer.py:57-72 computes E[i,j,:] = proj_d(sinus(d_ij)) + max_k proj_a(sinus(a_ijk)).  Per output channel,
+// proj_x(sinus(x)) + bias is a function of ONE scalar x (positional_embedding.py:28-31 followed by a Linear):
+//     f_c(x) = b[c] + sum_t W[c,2t] sin(x div_t) + W[c,2t+1] cos(x div_t),      div_t <= 1,
+// smooth at the scale of one index unit (the highest frequency is 1 rad per unit).  K2 (k2_gse_embed.cu) spends
+// 2 C^2 (1+k) flop per pair on it on the tensor cores; here f_c is tabulated once per weight set on a grid of step h
+// (tables `fa`, `fd`: rows x C halves, bias folded in) and every (pair, slot) is a cubic Lagrange interpolation of four
+// table rows out of shared memory: 16 row reads and 64 packed half FMAs per pair for C = 256, bound by shared-memory
+// bandwidth (8 KB per pair) instead of the tensor pipe.  Interpolation error at h = 0.25: <= h^4 * 0.0234 * max|f''''|
+// ~ 2e-5, below the fp16 rounding of the stored E (and of K2's bf16 operands).
+//
+// One warp per pair: lane l owns channels 8l .. 8l+7 (one LDS.128 per table row, one 16-byte store of E).  The lanes of
+// a warp first compute the arguments of 32 consecutive pairs (one each), then walk them together.
+#include <cuda_fp16.h>
+#include "geotx_common.cuh"
+#include "host_util.h"
+
+namespace geotx {
+
+constexpr int TBL_C = 256;
+constexpr int TBL_THREADS = 512;
+
+// Row r of a table holds f(x) at x = (r - 1) * h, so that the four rows around any x >= 0 exist.
+__global__ void gse_table_build_kernel(const float* __restrict__ div_term, const float* __restrict__ w,
+                                       const float* __restrict__ bias, int C, float h, __half* __restrict__ table) {
+    const int r = blockIdx.x, c = threadIdx.x;
+    const double x = (double)(r - 1) * (double)h;
+    double acc = (double)bias[c];
+    for (int t = 0; t < C / 2; ++t) {
+        const double om = x * (double)div_term[t];
+        acc += (double)w[(size_t)c * C + 2 * t] * sin(om) + (double)w[(size_t)c * C + 2 * t + 1] * cos(om);
+    }
+    table[(size_t)r * C + c] = __float2half_rn((float)acc);
+}
+
+struct TblLookup {
+    int row;         // first of the four rows
+    __half2 w01, w23;  // cubic Lagrange weights
+};
+
+__device__ __forceinline__ TblLookup tbl_lookup(float x, float inv_h, int rows) {
+    const float u = x * inv_h;
+    float fl = floorf(u);
+    fl = fminf(fmaxf(fl, 0.f), (float)(rows - 4));  // row = floor + 1 - 1; clamped arguments are flagged by the caller
+    const float t = u - fl;
+    TblLookup L;
+    L.row = (int)fl;
+    const float tm1 = t - 1.f, tm2 = t - 2.f, tp1 = t + 1.f;
+    L.w01 = __floats2half2_rn(-t * tm1 * tm2 * (1.f / 6.f), tp1 * tm1 * tm2 * 0.5f);
+    L.w23 = __floats2half2_rn(-tp1 * t * tm2 * 0.5f, tp1 * t * tm1 * (1.f / 6.f));
+    return L;
+}
+
+// acc[0..3] (8 channels as 4 half2) = sum of the four weighted rows
+__device__ __forceinline__ void tbl_interp(const __half* __restrict__ table, int row, unsigned int w01, unsigned int w23,
+                                           int lane, __half2 (&acc)[4]) {
+    const __half2 a = *reinterpret_cast<const __half2*>(&w01), b = *reinterpret_cast<const __half2*>(&w23);
+    const __half2 w0 = __low2half2(a), w1 = __high2half2(a), w2 = __low2half2(b), w3 = __high2half2(b);
+    const uint4* base = reinterpret_cast<const uint4*>(table + (size_t)row * TBL_C) + lane;
+    const uint4 r0 = base[0], r1 = base[TBL_C / 8], r2 = base[2 * (TBL_C / 8)], r3 = base[3 * (TBL_C / 8)];
+    const __half2* p0 = reinterpret_cast<const __half2*>(&r0);
+    const __half2* p1 = reinterpret_cast<const __half2*>(&r1);
+    const __half2* p2 = reinterpret_cast<const __half2*>(&r2);
+    const __half2* p3 = reinterpret_cast<const __half2*>(&r3);
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        acc[q] = __hfma2(w3, p3[q], __hfma2(w2, p2[q], __hfma2(w1, p1[q], __hmul2(w0, p0[q]))));
+}
+
+template <int K>
+__global__ void __launch_bounds__(TBL_THREADS, 1)
+gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict__ refv, int n, int row_begin,
+                       int row_count, long long pairs_total, const __half* __restrict__ tables, int rows_a, int rows_d,
+                       float inv_h, float sigma_d, float factor_a, __half* __restrict__ out, int* __restrict__ overflow) {
+    extern __shared__ __align__(16) unsigned char tbl_smem[];
+    __half* fa = reinterpret_cast<__half*>(tbl_smem);
+    __half* fd = fa + (size_t)rows_a * TBL_C;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(tables);
+        uint4* dst = reinterpret_cast<uint4*>(tbl_smem);
+        const int total = (rows_a + rows_d) * TBL_C / 8;
+        for (int e = threadIdx.x; e < total; e += TBL_THREADS) dst[e] = src[e];
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const long long warp = (long long)blockIdx.x * (TBL_THREADS / 32) + (threadIdx.x >> 5);
+    const long long warps = (long long)gridDim.x * (TBL_THREADS / 32);
+    const long long per_b = (long long)row_count * n;
+    const float x_max_a = (float)(rows_a - 3) / inv_h, x_max_d = (float)(rows_d - 3) / inv_h;
+    bool clamped = false;
+    for (long long g0 = warp * 32; g0 < pairs_total; g0 += warps * 32) {
+        // this lane's pair of the group: arguments -> rows and weights
+        int row[K + 1];
+        unsigned int w01[K + 1], w23[K + 1];
+        {
+            const long long p = min(g0 + lane, pairs_total - 1);
+            const long long b = p / per_b, rem = p - b * per_b;
+            const int i = row_begin + (int)(rem / n), j = (int)(rem % n);
+            float x[K + 1];
+            pair_arguments<K>(__ldg(pts4 + b * n + i), __ldg(pts4 + b * n + j), refv + (b * n + i) * K, K, sigma_d,
+                              factor_a, x);
+#pragma unroll
+            for (int s = 0; s <= K; ++s) {
+                clamped |= !(x[s] <= (s < K ? x_max_a : x_max_d));
+                const TblLookup L = tbl_lookup(x[s], inv_h, s < K ? rows_a : rows_d);
+                row[s] = L.row;
+                w01[s] = *reinterpret_cast<const unsigned int*>(&L.w01);
+                w23[s] = *reinterpret_cast<const unsigned int*>(&L.w23);
+            }
+        }
+        const int count = (int)min((long long)32, pairs_total - g0);
+        for (int e = 0; e < count; ++e) {
+            __half2 best[4], cur[4];
+#pragma unroll
+            for (int s = 0; s < K; ++s) {  // geotransformer.py:66 max over the k angle slots
+                tbl_interp(fa, __shfl_sync(0xffffffffu, row[s], e), __shfl_sync(0xffffffffu, w01[s], e),
+                           __shfl_sync(0xffffffffu, w23[s], e), lane, cur);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
+            }
+            tbl_interp(fd, __shfl_sync(0xffffffffu, row[K], e), __shfl_sync(0xffffffffu, w01[K], e),
+                       __shfl_sync(0xffffffffu, w23[K], e), lane, cur);
+            uint4 o;
+            __half2* op = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) op[q] = __hadd2(cur[q], best[q]);  // :70
+            reinterpret_cast<uint4*>(out + (size_t)(g0 + e) * TBL_C)[lane] = o;
+        }
+    }
+    if (clamped) *overflow = 1;
+}
+
+}  // namespace geotx
+
+using namespace geotx;
+
+extern "C" int64_t geotx_gse_table_bytes(int C, int rows_a, int rows_d) {
+    if (C != TBL_C || rows_a < 4 || rows_d < 4) return 0;
+    return (int64_t)(rows_a + rows_d) * C * 2;
+}
+
+extern "C" int geotx_gse_build_tables(const float* div_term, const float* w_d, const float* b_d, const float* w_a,
+                                      const float* b_a, int C, float h, int rows_a, int rows_d, void* tables,
+                                      void* stream) {
+    GEOTX_REQUIRE(div_term && w_d && b_d && w_a && b_a && tables, "geotx_gse_build_tables: null pointer");
+    GEOTX_REQUIRE(C == TBL_C && rows_a >= 4 && rows_d >= 4 && h > 0.f, "geotx_gse_build_tables: C must be %d", TBL_C);
+    __half* t = (__half*)tables;
+    gse_table_build_kernel<<<rows_a, C, 0, (cudaStream_t)stream>>>(div_term, w_a, b_a, C, h, t);
+    gse_table_build_kernel<<<rows_d, C, 0, (cudaStream_t)stream>>>(div_term, w_d, b_d, C, h, t + (size_t)rows_a * C);
+    return launch_status("geotx_gse_build_tables");
+}
+
+extern "C" int geotx_gse_embed_table(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                                     const void* tables, int C, int rows_a, int rows_d, float h, float sigma_d,
+                                     float factor_a, void* out_f16, int32_t* overflow, void* stream) {
+    GEOTX_REQUIRE(geometry && tables && out_f16 && overflow, "geotx_gse_embed_table: null pointer");
+    GEOTX_REQUIRE(B > 0 && n > 0 && k == 3 && C == TBL_C, "geotx_gse_embed_table: prototype takes k = 3, C = %d", TBL_C);
+    GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed_table: bad row slab");
+    const size_t smem = (size_t)(rows_a + rows_d) * C * 2;
+    GEOTX_REQUIRE(rows_a >= 4 && rows_d >= 4 && smem <= 220 * 1024, "geotx_gse_embed_table: tables of %zu B do not fit",
+                  smem);
+    int rc = check_cuda(cudaFuncSetAttribute(gse_embed_table_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem), "geotx_gse_embed_table: shared memory");
+    if (rc) return rc;
+    const float4* pts4 = (const float4*)geometry;
+    const float4* refv = pts4 + (size_t)B * n;
+    const long long pairs = (long long)B * row_count * n;
+    gse_embed_table_kernel<3><<<148, TBL_THREADS, smem, (cudaStream_t)stream>>>(
+        pts4, refv, n, row_begin, row_count, pairs, (const __half*)tables, rows_a, rows_d, 1.0f / h, sigma_d, factor_a,
+        (__half*)out_f16, overflow);
+    return launch_status("geotx_gse_embed_table");
+}
