@@ -4,14 +4,16 @@
 // proj_x(sinus(x)) + bias is a function of ONE scalar x (positional_embedding.py:28-31 followed by a Linear):
 //     f_c(x) = b[c] + sum_t W[c,2t] sin(x div_t) + W[c,2t+1] cos(x div_t),      div_t <= 1,
 // smooth at the scale of one index unit (the highest frequency is 1 rad per unit).  K2 (k2_gse_embed.cu) spends
-// 2 C^2 (1+k) flop per pair on it on the tensor cores; here f_c is tabulated once per weight set on a grid of step h
-// (tables `fa`, `fd`: rows x C halves, bias folded in) and every (pair, slot) is a cubic Lagrange interpolation of four
-// table rows out of shared memory: 16 row reads and 64 packed half FMAs per pair for C = 256, bound by shared-memory
-// bandwidth (8 KB per pair) instead of the tensor pipe.  Interpolation error at h = 0.25: <= h^4 * 0.0234 * max|f''''|
-// ~ 2e-5, below the fp16 rounding of the stored E (and of K2's bf16 operands).
+// 2 C^2 (1+k) flop per pair on it on the tensor cores; here f_c is tabulated once per weight set (tables fa, fd:
+// rows x C halves, bias folded in) and interpolated out of shared memory: the angle term linearly on a fine grid
+// (step h_a = 1/16: two rows per slot, error <= h^2/8 max|f"| ~ 2e-4), the distance term, whose range is larger, by
+// cubic Lagrange interpolation on a coarse grid (step h_d = 1/4: four rows, error ~ 2e-5).  10 row reads (5 KB) and ~30
+// packed half FMAs per pair for C = 256, k = 3: bound by the shared-memory pipe instead of the tensor pipe, and below
+// the fp16 rounding of the stored E (and of K2's bf16 operands).
 //
 // One warp per pair: lane l owns channels 8l .. 8l+7 (one LDS.128 per table row, one 16-byte store of E).  The lanes of
-// a warp first compute the arguments of 32 consecutive pairs (one each), then walk them together.
+// a warp first compute the arguments of 32 consecutive pairs (one each), then walk them together; a lookup travels
+// between lanes as one word.
 #include <cuda_fp16.h>
 #include "geotx_common.cuh"
 #include "host_util.h"
@@ -20,12 +22,15 @@ namespace geotx {
 
 constexpr int TBL_C = 256;
 constexpr int TBL_THREADS = 512;
+constexpr int TBL_CTAS_PER_SM = 2;  // tables up to ~110 KB
 
-// Row r of a table holds f(x) at x = (r - 1) * h, so that the four rows around any x >= 0 exist.
+// Row r of a table holds f(x) at x = (r - first) * h (first = 1 for the cubic table, so that the four rows around any
+// x >= 0 exist).
 __global__ void gse_table_build_kernel(const float* __restrict__ div_term, const float* __restrict__ w,
-                                       const float* __restrict__ bias, int C, float h, __half* __restrict__ table) {
+                                       const float* __restrict__ bias, int C, float h, int first,
+                                       __half* __restrict__ table) {
     const int r = blockIdx.x, c = threadIdx.x;
-    const double x = (double)(r - 1) * (double)h;
+    const double x = (double)(r - first) * (double)h;
     double acc = (double)bias[c];
     for (int t = 0; t < C / 2; ++t) {
         const double om = x * (double)div_term[t];
@@ -34,30 +39,34 @@ __global__ void gse_table_build_kernel(const float* __restrict__ div_term, const
     table[(size_t)r * C + c] = __float2half_rn((float)acc);
 }
 
-struct TblLookup {
-    int row;         // first of the four rows
-    __half2 w01, w23;  // cubic Lagrange weights
-};
-
-__device__ __forceinline__ TblLookup tbl_lookup(float x, float inv_h, int rows) {
-    const float u = x * inv_h;
-    float fl = floorf(u);
-    fl = fminf(fmaxf(fl, 0.f), (float)(rows - 4));  // row = floor + 1 - 1; clamped arguments are flagged by the caller
-    const float t = u - fl;
-    TblLookup L;
-    L.row = (int)fl;
-    const float tm1 = t - 1.f, tm2 = t - 2.f, tp1 = t + 1.f;
-    L.w01 = __floats2half2_rn(-t * tm1 * tm2 * (1.f / 6.f), tp1 * tm1 * tm2 * 0.5f);
-    L.w23 = __floats2half2_rn(-tp1 * t * tm2 * 0.5f, tp1 * t * tm1 * (1.f / 6.f));
-    return L;
+// A lookup: table row (high 16 bits) and the position inside the interval as a 16-bit fraction.  `span` rows are read
+// (2 linear, 4 cubic).
+__device__ __forceinline__ unsigned int tbl_encode(float x, float inv_h, int rows, int span) {
+    const float u = fmaxf(x * inv_h, 0.f);
+    const float fl = fminf(floorf(u), (float)(rows - span));  // arguments beyond the table are flagged by the caller
+    const float t = fminf(u - fl, 0.99998f);
+    return ((unsigned int)fl << 16) | (unsigned int)(t * 65536.f);
 }
 
-// acc[0..3] (8 channels as 4 half2) = sum of the four weighted rows
-__device__ __forceinline__ void tbl_interp(const __half* __restrict__ table, int row, unsigned int w01, unsigned int w23,
-                                           int lane, __half2 (&acc)[4]) {
-    const __half2 a = *reinterpret_cast<const __half2*>(&w01), b = *reinterpret_cast<const __half2*>(&w23);
-    const __half2 w0 = __low2half2(a), w1 = __high2half2(a), w2 = __low2half2(b), w3 = __high2half2(b);
-    const uint4* base = reinterpret_cast<const uint4*>(table + (size_t)row * TBL_C) + lane;
+// 8 channels (4 half2) of lane `lane`: linear interpolation between rows r and r + 1
+__device__ __forceinline__ void tbl_linear(const __half* __restrict__ table, unsigned int code, int lane,
+                                           __half2 (&acc)[4]) {
+    const __half2 t = __float2half2_rn((float)(code & 0xffffu) * (1.f / 65536.f));
+    const uint4* base = reinterpret_cast<const uint4*>(table + (size_t)(code >> 16) * TBL_C) + lane;
+    const uint4 r0 = base[0], r1 = base[TBL_C / 8];
+    const __half2* p0 = reinterpret_cast<const __half2*>(&r0);
+    const __half2* p1 = reinterpret_cast<const __half2*>(&r1);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[q] = __hfma2(t, __hsub2(p1[q], p0[q]), p0[q]);
+}
+
+// cubic Lagrange interpolation over rows r .. r + 3 (nodes at -1, 0, 1, 2 around the interval)
+__device__ __forceinline__ void tbl_cubic(const __half* __restrict__ table, unsigned int code, int lane,
+                                          __half2 (&acc)[4]) {
+    const float t = (float)(code & 0xffffu) * (1.f / 65536.f), tm1 = t - 1.f, tm2 = t - 2.f, tp1 = t + 1.f;
+    const __half2 w0 = __float2half2_rn(-t * tm1 * tm2 * (1.f / 6.f)), w1 = __float2half2_rn(tp1 * tm1 * tm2 * 0.5f),
+                  w2 = __float2half2_rn(-tp1 * t * tm2 * 0.5f), w3 = __float2half2_rn(tp1 * t * tm1 * (1.f / 6.f));
+    const uint4* base = reinterpret_cast<const uint4*>(table + (size_t)(code >> 16) * TBL_C) + lane;
     const uint4 r0 = base[0], r1 = base[TBL_C / 8], r2 = base[2 * (TBL_C / 8)], r3 = base[3 * (TBL_C / 8)];
     const __half2* p0 = reinterpret_cast<const __half2*>(&r0);
     const __half2* p1 = reinterpret_cast<const __half2*>(&r1);
@@ -69,10 +78,11 @@ __device__ __forceinline__ void tbl_interp(const __half* __restrict__ table, int
 }
 
 template <int K>
-__global__ void __launch_bounds__(TBL_THREADS, 1)
+__global__ void __launch_bounds__(TBL_THREADS, TBL_CTAS_PER_SM)
 gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict__ refv, int n, int row_begin,
                        int row_count, long long pairs_total, const __half* __restrict__ tables, int rows_a, int rows_d,
-                       float inv_h, float sigma_d, float factor_a, __half* __restrict__ out, int* __restrict__ overflow) {
+                       float inv_ha, float inv_hd, float sigma_d, float factor_a, __half* __restrict__ out,
+                       int* __restrict__ overflow) {
     extern __shared__ __align__(16) unsigned char tbl_smem[];
     __half* fa = reinterpret_cast<__half*>(tbl_smem);
     __half* fd = fa + (size_t)rows_a * TBL_C;
@@ -87,12 +97,10 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
     const long long warp = (long long)blockIdx.x * (TBL_THREADS / 32) + (threadIdx.x >> 5);
     const long long warps = (long long)gridDim.x * (TBL_THREADS / 32);
     const long long per_b = (long long)row_count * n;
-    const float x_max_a = (float)(rows_a - 3) / inv_h, x_max_d = (float)(rows_d - 3) / inv_h;
+    const float x_max_a = (float)(rows_a - 1) / inv_ha, x_max_d = (float)(rows_d - 3) / inv_hd;
     bool clamped = false;
     for (long long g0 = warp * 32; g0 < pairs_total; g0 += warps * 32) {
-        // this lane's pair of the group: arguments -> rows and weights
-        int row[K + 1];
-        unsigned int w01[K + 1], w23[K + 1];
+        unsigned int code[K + 1];  // this lane's pair of the group: arguments -> lookups
         {
             const long long p = min(g0 + lane, pairs_total - 1);
             const long long b = p / per_b, rem = p - b * per_b;
@@ -101,26 +109,23 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
             pair_arguments<K>(__ldg(pts4 + b * n + i), __ldg(pts4 + b * n + j), refv + (b * n + i) * K, K, sigma_d,
                               factor_a, x);
 #pragma unroll
-            for (int s = 0; s <= K; ++s) {
-                clamped |= !(x[s] <= (s < K ? x_max_a : x_max_d));
-                const TblLookup L = tbl_lookup(x[s], inv_h, s < K ? rows_a : rows_d);
-                row[s] = L.row;
-                w01[s] = *reinterpret_cast<const unsigned int*>(&L.w01);
-                w23[s] = *reinterpret_cast<const unsigned int*>(&L.w23);
+            for (int s = 0; s < K; ++s) {
+                clamped |= !(x[s] <= x_max_a);
+                code[s] = tbl_encode(x[s], inv_ha, rows_a, 2);
             }
+            clamped |= !(x[K] <= x_max_d);
+            code[K] = tbl_encode(x[K], inv_hd, rows_d, 4);
         }
         const int count = (int)min((long long)32, pairs_total - g0);
         for (int e = 0; e < count; ++e) {
             __half2 best[4], cur[4];
 #pragma unroll
             for (int s = 0; s < K; ++s) {  // geotransformer.py:66 max over the k angle slots
-                tbl_interp(fa, __shfl_sync(0xffffffffu, row[s], e), __shfl_sync(0xffffffffu, w01[s], e),
-                           __shfl_sync(0xffffffffu, w23[s], e), lane, cur);
+                tbl_linear(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
             }
-            tbl_interp(fd, __shfl_sync(0xffffffffu, row[K], e), __shfl_sync(0xffffffffu, w01[K], e),
-                       __shfl_sync(0xffffffffu, w23[K], e), lane, cur);
+            tbl_cubic(fd, __shfl_sync(0xffffffffu, code[K], e), lane, cur);
             uint4 o;
             __half2* op = reinterpret_cast<__half2*>(&o);
 #pragma unroll
@@ -136,24 +141,25 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
 using namespace geotx;
 
 extern "C" int64_t geotx_gse_table_bytes(int C, int rows_a, int rows_d) {
-    if (C != TBL_C || rows_a < 4 || rows_d < 4) return 0;
+    if (C != TBL_C || rows_a < 4 || rows_d < 4 || rows_a > 65535 || rows_d > 65535) return 0;
     return (int64_t)(rows_a + rows_d) * C * 2;
 }
 
 extern "C" int geotx_gse_build_tables(const float* div_term, const float* w_d, const float* b_d, const float* w_a,
-                                      const float* b_a, int C, float h, int rows_a, int rows_d, void* tables,
-                                      void* stream) {
+                                      const float* b_a, int C, float h_a, float h_d, int rows_a, int rows_d,
+                                      void* tables, void* stream) {
     GEOTX_REQUIRE(div_term && w_d && b_d && w_a && b_a && tables, "geotx_gse_build_tables: null pointer");
-    GEOTX_REQUIRE(C == TBL_C && rows_a >= 4 && rows_d >= 4 && h > 0.f, "geotx_gse_build_tables: C must be %d", TBL_C);
+    GEOTX_REQUIRE(C == TBL_C && rows_a >= 4 && rows_d >= 4 && rows_a <= 65535 && rows_d <= 65535 && h_a > 0.f && h_d > 0.f,
+                  "geotx_gse_build_tables: C must be %d, 4..65535 rows per table", TBL_C);
     __half* t = (__half*)tables;
-    gse_table_build_kernel<<<rows_a, C, 0, (cudaStream_t)stream>>>(div_term, w_a, b_a, C, h, t);
-    gse_table_build_kernel<<<rows_d, C, 0, (cudaStream_t)stream>>>(div_term, w_d, b_d, C, h, t + (size_t)rows_a * C);
+    gse_table_build_kernel<<<rows_a, C, 0, (cudaStream_t)stream>>>(div_term, w_a, b_a, C, h_a, 0, t);
+    gse_table_build_kernel<<<rows_d, C, 0, (cudaStream_t)stream>>>(div_term, w_d, b_d, C, h_d, 1, t + (size_t)rows_a * C);
     return launch_status("geotx_gse_build_tables");
 }
 
 extern "C" int geotx_gse_embed_table(const void* geometry, int B, int n, int k, int row_begin, int row_count,
-                                     const void* tables, int C, int rows_a, int rows_d, float h, float sigma_d,
-                                     float factor_a, void* out_f16, int32_t* overflow, void* stream) {
+                                     const void* tables, int C, int rows_a, int rows_d, float h_a, float h_d,
+                                     float sigma_d, float factor_a, void* out_f16, int32_t* overflow, void* stream) {
     GEOTX_REQUIRE(geometry && tables && out_f16 && overflow, "geotx_gse_embed_table: null pointer");
     GEOTX_REQUIRE(B > 0 && n > 0 && k == 3 && C == TBL_C, "geotx_gse_embed_table: prototype takes k = 3, C = %d", TBL_C);
     GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed_table: bad row slab");
@@ -166,8 +172,9 @@ extern "C" int geotx_gse_embed_table(const void* geometry, int B, int n, int k, 
     const float4* pts4 = (const float4*)geometry;
     const float4* refv = pts4 + (size_t)B * n;
     const long long pairs = (long long)B * row_count * n;
-    gse_embed_table_kernel<3><<<148, TBL_THREADS, smem, (cudaStream_t)stream>>>(
-        pts4, refv, n, row_begin, row_count, pairs, (const __half*)tables, rows_a, rows_d, 1.0f / h, sigma_d, factor_a,
-        (__half*)out_f16, overflow);
+    gse_embed_table_kernel<3><<<148 * (smem <= 110 * 1024 ? TBL_CTAS_PER_SM : 1), TBL_THREADS, smem,
+                                (cudaStream_t)stream>>>(pts4, refv, n, row_begin, row_count, pairs,
+                                                        (const __half*)tables, rows_a, rows_d, 1.0f / h_a, 1.0f / h_d,
+                                                        sigma_d, factor_a, (__half*)out_f16, overflow);
     return launch_status("geotx_gse_embed_table");
 }

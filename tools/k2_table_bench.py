@@ -21,9 +21,9 @@ for n in (1024, 2048):
     with torch.no_grad():
         geom = m.geometry(pts)
         d_max = float(torch.cdist(pts[0], pts[0]).max()) / m.sigma_d
-        for h in (0.25, 0.5):
+        for h in (1.0 / 16, 1.0 / 8):
             tb = pkg.ops.gse_build_tables(m.embedding.div_term, m.proj_d.weight.detach(), m.proj_d.bias.detach(),
-                                          m.proj_a.weight.detach(), m.proj_a.bias.detach(), m.factor_a, d_max * 1.01, h)
+                                          m.proj_a.weight.detach(), m.proj_a.bias.detach(), m.factor_a, d_max * 1.01, h_a=h)
             rows = 64
             exact = pkg.ops.gse_embed_fp32(geom, m.embedding.div_term, m.proj_d.weight.detach(), m.proj_d.bias.detach(),
                                            m.proj_a.weight.detach(), m.proj_a.bias.detach(), m.sigma_d, m.factor_a, False,
