@@ -317,6 +317,35 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
+def time_table_variant(pkg, model, resident, n_pairs, steps, default_out):
+    """The same forward with the embedding by tabulation (K2t, experimental, GEOTX_EMBED=table)
+    instead of the tcgen05 contraction: graph replay, CUDA events, same pairs; reported beside `value`, not as it."""
+    import torch
+    try:
+        model.embedding.embed_kernel = 'table'
+        fast = pkg.GraphedGeometricTransformer(model, *resident[0])
+        for s in range(3):
+            out = fast(*resident[s % n_pairs])
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for s in range(steps):
+            out = fast(*resident[s % n_pairs])
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        diff = max(float((x - y).norm() / y.norm()) for x, y in zip(out, default_out))
+        del fast
+        return {'embedding': 'geotx_gse_embed_table (tabulated, shared-memory bound)', 'value': steps / (ms * 1e-3),
+                'unit': 'pairs/s', 'ms_per_step': ms / steps,
+                'rel_diff_of_outputs_vs_default_embedding': diff,
+                'overflow_flag': int(model.embedding._tables().overflow.item())}
+    except Exception as exc:
+        return {'error': f'{type(exc).__name__}: {exc}'}
+    finally:
+        model.embedding.embed_kernel = 'tensor'
+
+
 def time_patch_scores(pkg, shape, calls=10, replays=5):
     """geotx_patch_scores (K12: the glue of model.py:169-170,176-179,187-188 between coarse matching and optimal
     transport) for one pair's 256 node correspondences; us per pair, next to the same lines written with stock torch
@@ -567,6 +596,9 @@ def run_b200(args):
         pyramid = time_pyramid(pkg) if world == 1 else None
         registration = time_registration(pkg, shape_name) if world == 1 else None
         patch_scores = time_patch_scores(pkg, shape_name) if world == 1 else None
+        variant = None
+        if world == 1 and not big and model.embedding.embed_kernel == 'tensor' and C == 256 and k == 3:
+            variant = time_table_variant(pkg, model, resident, n_pairs, args.steps, last)
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -611,6 +643,7 @@ def run_b200(args):
             'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
                           'log_optimal_transport': transport, 'weighted_procrustes': procrustes,
                           'patch_scores': patch_scores, 'local_global_registration': registration, 'collate_pyramid': pyramid},
+            'variants': {'embed_table': variant},
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)

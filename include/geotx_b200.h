@@ -283,15 +283,16 @@ int geotx_patch_scores(const float* ref_feats, int64_t n_ref, const float* src_f
  * x = r h_a, rows_a >= pi*factor_a/h_a + 2; read by linear interpolation) and the distance term every h_d (row r at
  * x = (r-1) h_d, rows_d >= max d_index/h_d + 4; cubic), as halves (geotx_gse_table_bytes bytes), and
  * geotx_gse_embed_table interpolates them out of shared memory instead of contracting on the tensor cores.  Same geometry scratch and E layout (f16) as geotx_gse_embed; k = 3, C = 256, reduction 'max'.
- * *overflow is set to 1 when an argument fell outside its table (the caller must then rebuild with more rows or use
- * geotx_gse_embed); it is never cleared by the kernel. */
+ * A distance beyond the table is evaluated exactly from div_term, w_d, b_d (slow, meant to be rare); *overflow is set to
+ * 1 only if an ANGLE argument fell outside its table (cannot happen for rows_a as above); never cleared. */
 int64_t geotx_gse_table_bytes(int C, int rows_a, int rows_d);
 int geotx_gse_build_tables(const float* div_term, const float* w_d, const float* b_d, const float* w_a,
                            const float* b_a, int C, float h_a, float h_d, int rows_a, int rows_d, void* tables,
                            void* stream);
 int geotx_gse_embed_table(const void* geometry, int B, int n, int k, int row_begin, int row_count, const void* tables,
                           int C, int rows_a, int rows_d, float h_a, float h_d, float sigma_d, float factor_a,
-                          void* out_f16, int32_t* overflow, void* stream);
+                          const float* div_term, const float* w_d, const float* b_d, void* out_f16, int32_t* overflow,
+                          void* stream);
 
 #ifdef __cplusplus
 }

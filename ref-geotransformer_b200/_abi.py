@@ -46,7 +46,7 @@ SIGNATURES = {
                                              _p, _p, _p, _p, _p, _p, _p]),
     'geotx_gse_table_bytes': (_i64, [_i, _i, _i]),
     'geotx_gse_build_tables': (_i, [_p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
-    'geotx_gse_embed_table': (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _i, _i, _f, _f, _f, _f, _p, _p, _p]),
+    'geotx_gse_embed_table': (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _i, _i, _f, _f, _f, _f, _p, _p, _p, _p, _p, _p]),
     'geotx_patch_scores': (_i, [_p, _i64, _p, _i64, _i, _p, _p, _i, _p, _p, _i, _p, _p]),
 }
 

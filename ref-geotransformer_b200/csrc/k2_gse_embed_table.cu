@@ -77,11 +77,32 @@ __device__ __forceinline__ void tbl_cubic(const __half* __restrict__ table, unsi
         acc[q] = __hfma2(w3, p3[q], __hfma2(w2, p2[q], __hfma2(w1, p1[q], __hmul2(w0, p0[q]))));
 }
 
+// A distance beyond the table (a cloud larger than the range the tables were built for): the function itself,
+// positional_embedding.py:28-31 + the Linear, for this lane's 8 channels.  Rare and slow (128 sincos + 2048 FMA).
+__device__ __noinline__ void tbl_exact(const float* __restrict__ div_term, const float* __restrict__ w,
+                                       const float* __restrict__ bias, float x, int lane, __half2 (&acc)[4]) {
+    float a[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) a[q] = bias[8 * lane + q];
+    for (int t = 0; t < TBL_C / 2; ++t) {
+        float sn, cs;
+        sincosf(__fmul_rn(x, div_term[t]), &sn, &cs);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const float2 wt = *reinterpret_cast<const float2*>(w + (size_t)(8 * lane + q) * TBL_C + 2 * t);
+            a[q] = fmaf(wt.y, cs, fmaf(wt.x, sn, a[q]));
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[q] = __floats2half2_rn(a[2 * q], a[2 * q + 1]);
+}
+
 template <int K>
 __global__ void __launch_bounds__(TBL_THREADS, TBL_CTAS_PER_SM)
 gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict__ refv, int n, int row_begin,
                        int row_count, long long pairs_total, const __half* __restrict__ tables, int rows_a, int rows_d,
-                       float inv_ha, float inv_hd, float sigma_d, float factor_a, __half* __restrict__ out,
+                       float inv_ha, float inv_hd, float sigma_d, float factor_a, const float* __restrict__ div_term,
+                       const float* __restrict__ w_d, const float* __restrict__ b_d, __half* __restrict__ out,
                        int* __restrict__ overflow) {
     extern __shared__ __align__(16) unsigned char tbl_smem[];
     __half* fa = reinterpret_cast<__half*>(tbl_smem);
@@ -101,6 +122,7 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
     bool clamped = false;
     for (long long g0 = warp * 32; g0 < pairs_total; g0 += warps * 32) {
         unsigned int code[K + 1];  // this lane's pair of the group: arguments -> lookups
+        float x_d;
         {
             const long long p = min(g0 + lane, pairs_total - 1);
             const long long b = p / per_b, rem = p - b * per_b;
@@ -113,8 +135,8 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
                 clamped |= !(x[s] <= x_max_a);
                 code[s] = tbl_encode(x[s], inv_ha, rows_a, 2);
             }
-            clamped |= !(x[K] <= x_max_d);
-            code[K] = tbl_encode(x[K], inv_hd, rows_d, 4);
+            x_d = x[K];
+            code[K] = x_d <= x_max_d ? tbl_encode(x_d, inv_hd, rows_d, 4) : 0xffffffffu;  // beyond the table: exact
         }
         const int count = (int)min((long long)32, pairs_total - g0);
         for (int e = 0; e < count; ++e) {
@@ -125,7 +147,9 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
 #pragma unroll
                 for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
             }
-            tbl_cubic(fd, __shfl_sync(0xffffffffu, code[K], e), lane, cur);
+            const unsigned int code_d = __shfl_sync(0xffffffffu, code[K], e);
+            if (code_d != 0xffffffffu) tbl_cubic(fd, code_d, lane, cur);
+            else tbl_exact(div_term, w_d, b_d, __shfl_sync(0xffffffffu, x_d, e), lane, cur);
             uint4 o;
             __half2* op = reinterpret_cast<__half2*>(&o);
 #pragma unroll
@@ -159,8 +183,9 @@ extern "C" int geotx_gse_build_tables(const float* div_term, const float* w_d, c
 
 extern "C" int geotx_gse_embed_table(const void* geometry, int B, int n, int k, int row_begin, int row_count,
                                      const void* tables, int C, int rows_a, int rows_d, float h_a, float h_d,
-                                     float sigma_d, float factor_a, void* out_f16, int32_t* overflow, void* stream) {
-    GEOTX_REQUIRE(geometry && tables && out_f16 && overflow, "geotx_gse_embed_table: null pointer");
+                                     float sigma_d, float factor_a, const float* div_term, const float* w_d,
+                                     const float* b_d, void* out_f16, int32_t* overflow, void* stream) {
+    GEOTX_REQUIRE(geometry && tables && out_f16 && overflow && div_term && w_d && b_d, "geotx_gse_embed_table: null pointer");
     GEOTX_REQUIRE(B > 0 && n > 0 && k == 3 && C == TBL_C, "geotx_gse_embed_table: prototype takes k = 3, C = %d", TBL_C);
     GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed_table: bad row slab");
     const size_t smem = (size_t)(rows_a + rows_d) * C * 2;
@@ -175,6 +200,7 @@ extern "C" int geotx_gse_embed_table(const void* geometry, int B, int n, int k, 
     gse_embed_table_kernel<3><<<148 * (smem <= 110 * 1024 ? TBL_CTAS_PER_SM : 1), TBL_THREADS, smem,
                                 (cudaStream_t)stream>>>(pts4, refv, n, row_begin, row_count, pairs,
                                                         (const __half*)tables, rows_a, rows_d, 1.0f / h_a, 1.0f / h_d,
-                                                        sigma_d, factor_a, (__half*)out_f16, overflow);
+                                                        sigma_d, factor_a, div_term, w_d, b_d, (__half*)out_f16,
+                                                        overflow);
     return launch_status("geotx_gse_embed_table");
 }

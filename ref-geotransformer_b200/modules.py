@@ -101,7 +101,11 @@ class SinusoidalPositionalEmbedding(nn.Module):
 
 class GeometricStructureEmbedding(nn.Module):
     """geotransformer.py:9-72.  `precision`: 'bf16' = tcgen05 kernel (hidden_dim 128/256), 'fp32' = CUDA-core
-    kernel (any even hidden_dim); 'auto' picks bf16 when the hidden size allows it."""
+    kernel (any even hidden_dim); 'auto' picks bf16 when the hidden size allows it.
+    `embed_kernel` (attribute; default from GEOTX_EMBED, 'tensor'): 'table' makes the 16-bit embedding of the shipped
+    shape (hidden_dim 256, angle_k 3, 'max') go through the tabulated kernel K2t (experimental:
+    twice as fast and closer to fp32 than the bf16 contraction); `table_d_index_max` is the distance index up to
+    which its table reaches (beyond it the kernel evaluates exactly, slowly)."""
 
     def __init__(self, hidden_dim, sigma_d, sigma_a, angle_k, reduction_a='max', precision='auto'):
         super().__init__()
@@ -122,6 +126,12 @@ class GeometricStructureEmbedding(nn.Module):
         self._packed = None
         self._packed_key = None
         self._e_bound = math.inf
+        self.embed_kernel = os.environ.get('GEOTX_EMBED', 'tensor')
+        if self.embed_kernel not in ('tensor', 'table'):
+            raise ValueError(f"GEOTX_EMBED must be 'tensor' or 'table', got {self.embed_kernel!r}")
+        self.table_d_index_max = 48.0
+        self._tables_cache = None
+        self._tables_key = None
 
     def _use_tensor_cores(self):
         ok = self.hidden_dim in (128, 256)
@@ -139,6 +149,20 @@ class GeometricStructureEmbedding(nn.Module):
             self._e_bound = float((w_d.abs().sum(1) + w_a.abs().sum(1) + (b_d + b_a).abs()).max())
             self._packed_key = key
         return self._packed
+
+    def _tables(self):
+        ts = (self.proj_d.weight, self.proj_d.bias, self.proj_a.weight, self.proj_a.bias)
+        key = tuple((t.data_ptr(), t._version) for t in ts) + (self.table_d_index_max,)
+        if self._tables_cache is None or key != self._tables_key:
+            w_d, b_d, w_a, b_a = [t.detach().contiguous() for t in ts]
+            self._tables_cache = ops.gse_build_tables(self.embedding.div_term, w_d, b_d, w_a, b_a, self.factor_a,
+                                                      self.table_d_index_max, h_a=0.125, h_d=0.25)
+            self._tables_key = key
+        return self._tables_cache
+
+    def _use_table(self, out_dtype, qt):
+        return (self.embed_kernel == 'table' and self.hidden_dim == 256 and self.angle_k == 3 and
+                self.reduction_a == 'max' and out_dtype == torch.float16 and qt is None and self.precision != 'fp32')
 
     def storage_dtype(self):
         """Format E is stored in between the embedding kernel and the 'self' blocks: IEEE half (11-bit significand)
@@ -162,6 +186,8 @@ class GeometricStructureEmbedding(nn.Module):
         """E of the rows [row_begin, row_begin + row_count).  With `qt` (tensor-core path, <= 4 heads) returns
         (E, scores_p): the first 'self' block's additive scores come out of the same kernel."""
         mean = self.reduction_a == 'mean'
+        if self._use_table(out_dtype, qt):
+            return ops.gse_embed_table(geom, self._tables(), self.sigma_d, self.factor_a, row_begin, row_count, out)
         if self._use_tensor_cores():
             return ops.gse_embed(geom, self.embedding.div_term, self._packed_weights(), self.hidden_dim, self.sigma_d,
                                  self.factor_a, mean, out_dtype, row_begin, row_count, out, qt=qt)

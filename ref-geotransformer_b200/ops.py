@@ -501,16 +501,16 @@ def patch_scores(ref_feats, src_feats, ref_node_knn_indices, src_node_knn_indice
 
 class EmbeddingTables:
     """Sampled proj_d(sinus(x)) + b_d and proj_a(sinus(x)) + b_a for the tabulated embedding (geotx_gse_embed_table)."""
-    __slots__ = ('buf', 'C', 'h_a', 'h_d', 'rows_a', 'rows_d', 'overflow')
+    __slots__ = ('buf', 'C', 'h_a', 'h_d', 'rows_a', 'rows_d', 'overflow', 'weights')
 
-    def __init__(self, buf, C, h_a, h_d, rows_a, rows_d, overflow):
-        self.buf, self.C, self.h_a, self.h_d = buf, C, h_a, h_d
+    def __init__(self, buf, C, h_a, h_d, rows_a, rows_d, overflow, weights):
+        self.buf, self.C, self.h_a, self.h_d, self.weights = buf, C, h_a, h_d, weights
         self.rows_a, self.rows_d, self.overflow = rows_a, rows_d, overflow
 
 
 def gse_build_tables(div_term, w_d, b_d, w_a, b_a, factor_a, d_index_max, h_a=1.0 / 16, h_d=0.25):
     """Tables for `gse_embed_table` (experimental): angle arguments lie in [0, pi * factor_a],
-    distance arguments in [0, d_index_max] (the caller's bound: largest pair distance / sigma_d)."""
+    distance arguments in [0, d_index_max] are read from the table, larger ones are evaluated exactly (slowly)."""
     import math
     for name, t in (('div_term', div_term), ('w_d', w_d), ('b_d', b_d), ('w_a', w_a), ('b_a', b_a)):
         _check(t, name, torch.float32)
@@ -524,7 +524,8 @@ def gse_build_tables(div_term, w_d, b_d, w_a, b_a, factor_a, d_index_max, h_a=1.
     overflow = torch.zeros(1, dtype=torch.int32, device=w_d.device)
     _abi.call('geotx_gse_build_tables', _p(div_term), _p(w_d), _p(b_d), _p(w_a), _p(b_a), C, float(h_a), float(h_d),
               rows_a, rows_d, _p(buf), _stream())
-    return EmbeddingTables(buf, C, float(h_a), float(h_d), rows_a, rows_d, overflow)
+    return EmbeddingTables(buf, C, float(h_a), float(h_d), rows_a, rows_d, overflow,
+                           (div_term, w_d.contiguous(), b_d.contiguous()))
 
 
 def gse_embed_table(geom, tables, sigma_d, factor_a, row_begin=0, row_count=None, out=None):
@@ -536,6 +537,6 @@ def gse_embed_table(geom, tables, sigma_d, factor_a, row_begin=0, row_count=None
     else:
         _check(out, 'out', torch.float16)
     _abi.call('geotx_gse_embed_table', _p(geom.buf), geom.B, geom.n, geom.k, row_begin, row_count, _p(tables.buf),
-              tables.C, tables.rows_a, tables.rows_d, tables.h_a, tables.h_d, float(sigma_d), float(factor_a), _p(out),
-              _p(tables.overflow), _stream())
+              tables.C, tables.rows_a, tables.rows_d, tables.h_a, tables.h_d, float(sigma_d), float(factor_a),
+              _p(tables.weights[0]), _p(tables.weights[1]), _p(tables.weights[2]), _p(out), _p(tables.overflow), _stream())
     return out

@@ -157,3 +157,70 @@ def test_fused_first_block_scores(pkg, oracle, C, H, n, reduction):
             assert rel(part[:, :, 30:100], want[:, :, 30:100]) <= 2e-3
         assert float((part[:, :, :30] + 7.0).abs().max()) == 0.0 and float((part[:, :, 100:] + 7.0).abs().max()) == 0.0
     assert pkg._abi.watchdog() is None
+
+
+# ---- K2t: the tabulated embedding (experimental, GEOTX_EMBED=table) ---------------------------------------------------
+TOL_TABLE = 2e-3  # Frobenius-relative: half tables + half arithmetic; measured ~5e-4 (the bf16 contraction: ~4e-3)
+
+
+@pytest.mark.parametrize('name', ['3dmatch_n192', 'modelnet_n128'])
+def test_table_kernel_vs_reference_golden(pkg, oracle, golden, name):
+    """The C = 256 shipped configs: golden rows of E written by the reference, through the tabulated kernel."""
+    z = golden(f'{name}.npz')
+    cfg = eval(str(z['cfg']))
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    pts = pkg.synth.make_tie_free_pair(str(z['shape']), int(z['n']), int(z['m']), seed=int(z['seed']))[0]
+    m = _gse(pkg, cfg, sd, 'auto')
+    m.embed_kernel = 'table'
+    rows = torch.from_numpy(z['rows'])
+    with torch.no_grad():
+        e = m(pts.to(DEV), out_dtype=torch.float16)
+    assert e.dtype == torch.float16 and int(m._tables().overflow.item()) == 0
+    err = rel(e[0].float().cpu()[rows], z['E_rows'])
+    print(f'{name} table: E rel err {err:.3e}')
+    assert err <= TOL_TABLE
+
+
+def test_table_kernel_vs_oracle_and_beyond_the_table(pkg, oracle):
+    """Ragged n, B = 2, row slabs; then the same clouds with a table that ends at a tenth of their extent, so that most
+    distances take the exact path: both must agree with the oracle."""
+    cfg = dict(hidden_dim=256, sigma_d=0.2, sigma_a=15, angle_k=3, reduction_a='max')
+    sd = oracle.init_state_dict(8, 8, 256, [], seed=6)
+    pts = torch.rand(2, 173, 3, generator=torch.Generator().manual_seed(3)) * 2.5
+    exp = oracle.gse(pts, sd, 'embedding.', cfg['sigma_d'], cfg['sigma_a'], cfg['angle_k'], 'max')
+    m = _gse(pkg, cfg, sd, 'auto')
+    m.embed_kernel = 'table'
+    with torch.no_grad():
+        geom = m.geometry(pts.to(DEV))
+        e = m.embed(geom, torch.float16)
+        slab = m.embed(geom, torch.float16, row_begin=40, row_count=77)
+        assert m._tables().rows_d > 150
+        m.table_d_index_max = 2.0  # 0.4 m of a 2.5 m cloud
+        short = m.embed(geom, torch.float16)
+        assert m._tables().rows_d < 20
+        m.embed_kernel = 'tensor'
+        tensor = m.embed(geom, torch.float16)
+    assert rel(e.float(), exp) <= TOL_TABLE and rel(short.float(), exp) <= TOL_TABLE
+    assert torch.equal(slab, e[:, 40:117])
+    assert rel(e.float(), exp) < rel(tensor.float(), exp), 'the tabulated kernel should sit closer to fp32 than bf16 MMA'
+    assert int(m._tables().overflow.item()) == 0
+
+
+def test_forward_with_table_embedding(pkg, oracle, golden):
+    """GeometricTransformer.forward with the tabulated embedding against the reference's golden outputs (3DMatch 1024,
+    BASELINE.json configs[1]); it must not be further from the reference than the tensor-core embedding."""
+    z = golden('3dmatch_n1024_out.npz')
+    cfg = eval(str(z['cfg']))
+    n = int(z['n'])
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    rp, sp, rf, sf, _ = pkg.synth.make_tie_free_pair(str(z['shape']), n, n, seed=int(z['seed']))
+    model = pkg.GeometricTransformer(**cfg).to(DEV).eval()
+    model.load_state_dict(sd, strict=True)
+    errs = {}
+    for kernel in ('tensor', 'table'):
+        model.embedding.embed_kernel = kernel
+        with torch.no_grad():
+            o0, o1 = model(rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV))
+        errs[kernel] = max(rel(o0, z['out_ref']), rel(o1, z['out_src']))
+    print(f'forward rel err: {errs}')
+    assert errs['table'] <= TOL_BF16 and errs['table'] <= errs['tensor'] * 1.5
