@@ -37,6 +37,8 @@ WORKLOADS = {
     '3dmatch_8192': ('3dmatch', 8192, 8192),   # configs[3]: E = 34 GB per cloud, stored
     '3dmatch_16384': ('3dmatch', 16384, 16384),  # configs[3]: E = 137 GB per cloud: never stored, regenerated per 'self' block
 }
+# dram__bytes_read.sum + dram__bytes_write.sum of one rpe_scores_tc_kernel launch (ncu --set full, profiles/r01_ncu_k3a_r01.txt)
+K3A_NCU_TRAFFIC_BYTES = {'3dmatch_1024': 560.4e6}
 # dram__bytes_read.sum + dram__bytes_write.sum of one gse_embed_tc_kernel launch (ncu --set full, profiles/r01_ncu_k2_*)
 K2_NCU_TRAFFIC_BYTES = {"3dmatch_1024": 483.98e6}  # profiles/r01_ncu_k2_v4.txt
 METRIC = 'registration pairs/sec (embed+RPE-attn) at N superpoints'
@@ -317,12 +319,14 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
-def time_table_variant(pkg, model, resident, n_pairs, steps, default_out):
-    """The same forward with the embedding by tabulation (K2t, experimental, GEOTX_EMBED=table)
-    instead of the tcgen05 contraction: graph replay, CUDA events, same pairs; reported beside `value`, not as it."""
+def time_embed_variant(pkg, model, resident, n_pairs, steps, default_out):
+    """The same forward with the OTHER embedding kernel (tabulated K2t <-> tcgen05 contraction K2): graph replay, CUDA
+    events, same pairs; reported beside `value`, not as it."""
     import torch
+    default = model.embedding.embed_kernel
+    other = 'tensor' if default == 'table' else 'table'
     try:
-        model.embedding.embed_kernel = 'table'
+        model.embedding.embed_kernel = other
         fast = pkg.GraphedGeometricTransformer(model, *resident[0])
         for s in range(3):
             out = fast(*resident[s % n_pairs])
@@ -336,14 +340,12 @@ def time_table_variant(pkg, model, resident, n_pairs, steps, default_out):
         ms = a.elapsed_time(b)
         diff = max(float((x - y).norm() / y.norm()) for x, y in zip(out, default_out))
         del fast
-        return {'embedding': 'geotx_gse_embed_table (tabulated, shared-memory bound)', 'value': steps / (ms * 1e-3),
-                'unit': 'pairs/s', 'ms_per_step': ms / steps,
-                'rel_diff_of_outputs_vs_default_embedding': diff,
-                'overflow_flag': int(model.embedding._tables().overflow.item())}
+        return {'embed_kernel': other, 'value': steps / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms / steps,
+                'rel_diff_of_outputs_vs_default': diff}
     except Exception as exc:
         return {'error': f'{type(exc).__name__}: {exc}'}
     finally:
-        model.embedding.embed_kernel = 'tensor'
+        model.embedding.embed_kernel = default
 
 
 def time_patch_scores(pkg, shape, calls=10, replays=5):
@@ -493,6 +495,22 @@ def run_b200(args):
         return res
     model.embedding.embed = timed_embed
 
+    # the same bracket around every launch of the RPE score kernel (K3a, HBM-bound on E): the dominant kernel when the
+    # embedding runs by tabulation
+    k3_events = []
+    orig_scores = pkg.ops.rpe_scores
+
+    def timed_scores(qt, E, n=None, row_begin=0, out=None):
+        kw = dict(enable_timing=True, external=True) if external[0] else dict(enable_timing=True)
+        e0, e1 = torch.cuda.Event(**kw), torch.cuda.Event(**kw)
+        e0.record()
+        res = orig_scores(qt, E, n=n, row_begin=row_begin, out=out)
+        e1.record()
+        heads = qt.shape[1] if qt.dim() == 4 else cfg['num_heads']
+        k3_events.append((e0, e1, E.numel() * E.element_size() + E.numel() // E.shape[-1] * heads * 4))
+        return res
+    pkg.ops.rpe_scores = timed_scores
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -505,6 +523,7 @@ def run_b200(args):
             last = model(*resident[s % n_pairs])
         barrier()
         k2_events.clear()
+        k3_events.clear()
         launches0 = pkg._abi.launch_count
         e_start, e_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e_start.record()
@@ -516,25 +535,35 @@ def run_b200(args):
         launches = pkg._abi.launch_count - launches0
         k2_ms = [a.elapsed_time(b) for a, b, _ in k2_events]
         k2_launch_flops = [f for _, _, f in k2_events]
+        k3_ms = [a.elapsed_time(b) for a, b, _ in k3_events]
+        k3_launch_bytes = [f for _, _, f in k3_events]
         k2_timing = 'CUDA events around every launch in an eager pass over the same steps'
         # Preferred: the same event pairs captured INSIDE a CUDA graph of the forward (external event-record nodes), so
         # that the kernel is timed in exactly the context the value pass runs it in (eager launches at n ~ 1k are
         # host-bound: the GPU idles between launches and the kernel then starts from a lower power state).
         try:
             k2_events.clear()
+            k3_events.clear()
             external[0] = True
             probe = pkg.GraphedGeometricTransformer(model, *resident[0])
             per_forward = max(len(k2_ms) // max(args.steps, 1), 1)
             pairs_per_replay = list(k2_events)[-per_forward:]  # those recorded during the capture itself
+            per_forward3 = max(len(k3_ms) // max(args.steps, 1), 1)
+            pairs3_per_replay = list(k3_events)[-per_forward3:]
             in_graph, in_graph_flops = [], []
+            in_graph3, in_graph3_bytes = [], []
             for s in range(3 + args.steps):
                 probe(*resident[s % n_pairs])
                 torch.cuda.synchronize()
                 if s >= 3:
                     in_graph += [a.elapsed_time(b) for a, b, _ in pairs_per_replay]
                     in_graph_flops += [f for _, _, f in pairs_per_replay]
+                    in_graph3 += [a.elapsed_time(b) for a, b, _ in pairs3_per_replay]
+                    in_graph3_bytes += [f for _, _, f in pairs3_per_replay]
             if in_graph and all(t > 0 for t in in_graph):
                 k2_ms, k2_launch_flops = in_graph, in_graph_flops
+                if in_graph3 and all(t > 0 for t in in_graph3):
+                    k3_ms, k3_launch_bytes = in_graph3, in_graph3_bytes
                 k2_timing = 'CUDA events recorded inside the CUDA graph of the forward, around every launch'
             del probe
             if big:
@@ -543,6 +572,7 @@ def run_b200(args):
             k2_timing += f' (in-graph events unavailable: {type(exc).__name__})'
         external[0] = False
         model.embedding.embed = orig_embed
+        pkg.ops.rpe_scores = orig_scores
 
         # ---- pass 2 (the timed region of `value`): the same forward replayed as one CUDA graph per step ----
         fast = pkg.GraphedGeometricTransformer(model, *resident[0])
@@ -597,8 +627,8 @@ def run_b200(args):
         registration = time_registration(pkg, shape_name) if world == 1 else None
         patch_scores = time_patch_scores(pkg, shape_name) if world == 1 else None
         variant = None
-        if world == 1 and not big and model.embedding.embed_kernel == 'tensor' and C == 256 and k == 3:
-            variant = time_table_variant(pkg, model, resident, n_pairs, args.steps, last)
+        if world == 1 and not big and C == 256 and k == 3:
+            variant = time_embed_variant(pkg, model, resident, n_pairs, args.steps, last)
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -610,6 +640,39 @@ def run_b200(args):
         k2_avg_ms = sum(k2_ms) / max(len(k2_ms), 1)
         k2_flops = sum(k2_launch_flops) / max(len(k2_ms), 1)  # average over launches (row slabs of E)
         achieved = k2_flops / (k2_avg_ms * 1e-3) / 1e12 if k2_ms else 0.0
+        step_ms = ms / args.steps
+        k3_avg_ms = sum(k3_ms) / max(len(k3_ms), 1)
+        k3_bytes = sum(k3_launch_bytes) / max(len(k3_ms), 1)
+        k3_gbs = k3_bytes / (k3_avg_ms * 1e-3) / 1e9 if k3_ms else 0.0
+        table = model.embedding.embed_kernel == 'table' and model.embedding._use_table(model.embedding.storage_dtype(), None)
+        timing_note = k2_timing + ('; the value pass replays the identical kernels from a CUDA graph; '
+                                   'share_of_step = timed launches per step / ms_per_step')
+        tensor_roof = {'kernel': 'gse_embed_tc_kernel (geotx_gse_embed)', 'bound': 'tensor', 'achieved': achieved,
+                       'peak': peaks['tensor_sustained'], 'unit': 'TFLOP/s',
+                       'frac': achieved / peaks['tensor_sustained'],
+                       'traffic': K2_NCU_TRAFFIC_BYTES.get(args.workload),
+                       'peak_source': peaks['source'] + ' bf16 sustained (kernel timed inside the step)',
+                       'frac_of_burst_peak': achieved / peaks['tensor_burst'],
+                       'flops_per_launch': k2_flops, 'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
+                       'share_of_step': sum(k2_ms) / args.steps / step_ms if ms else None, 'timing': timing_note}
+        hbm_roof = {'kernel': 'rpe_scores_tc_kernel (geotx_rpe_scores)', 'bound': 'hbm', 'achieved': k3_gbs,
+                    'peak': peaks['hbm'], 'unit': 'GB/s', 'frac': k3_gbs / peaks['hbm'],
+                    'traffic': K3A_NCU_TRAFFIC_BYTES.get(args.workload),
+                    'peak_source': peaks['source'] + ' copy bandwidth',
+                    'bytes_per_launch': k3_bytes, 'avg_launch_ms': k3_avg_ms, 'launches_timed': len(k3_ms),
+                    'share_of_step': sum(k3_ms) / args.steps / step_ms if ms else None,
+                    'algorithmic_bytes': 'E read once (n*n*C*2) + scores written (n*n*H*4) per launch',
+                    'timing': timing_note}
+        if table:  # the embedding runs by tabulation (shared-memory bound): the HBM-bound score kernel dominates
+            roofline = hbm_roof
+            kernel_stats = {'embedding': {'kernel': 'gse_embed_table_kernel (geotx_gse_embed_table)',
+                                          'bound': 'shared-memory pipe (10 table rows = 5 KB of LDS.128 per pair)',
+                                          'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
+                                          'share_of_step': sum(k2_ms) / args.steps / step_ms if ms else None,
+                                          'lds_bytes_per_launch': 5120.0 * k2_flops / flops_gse(n, C, k) * n * n if n else None}}
+        else:
+            roofline = tensor_roof
+            kernel_stats = {'rpe_scores': hbm_roof}
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
@@ -617,6 +680,7 @@ def run_b200(args):
             'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': C, 'num_heads': cfg['num_heads'],
                        'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1, 'launch': 'one CUDA graph replay per step',
                        'e_storage': model.last_e_mode + (f' (E never stored: rebuilt for each of the {sum(b == "self" for b in cfg["blocks"])} self blocks in {model.regenerate_slab_bytes >> 20} MiB row slabs; pair_tflops counts those passes)' if model.last_e_mode == 'regenerate' else ' (one embedding pass per cloud)'),
+                       'embed_kernel': 'table (geotx_gse_embed_table)' if table else 'tensor (geotx_gse_embed, tcgen05)',
                        'l2_slab_bytes': model.l2_slab_bytes, 'first_block_scores_fused_into_embedding': bool(model.fuse_scores),
                        'l2': f'inputs larger than L2: E is {n * n * C * 2 / 1e6:.0f} MB per cloud, '
                              f'{n_pairs} distinct pairs rotated',
@@ -625,16 +689,8 @@ def run_b200(args):
                     'd2h_bytes_per_step': d2h,
                     'api': f'PipelinedGeometricTransformer.map over pinned host pairs, depth {depth}, wall clock'},
             'gpu_launches': launches,
-            'roofline': {'kernel': 'gse_embed_tc_kernel (geotx_gse_embed)', 'bound': 'tensor', 'achieved': achieved,
-                         'peak': peaks['tensor_sustained'], 'unit': 'TFLOP/s',
-                         'frac': achieved / peaks['tensor_sustained'],
-                         'traffic': K2_NCU_TRAFFIC_BYTES.get(args.workload),
-                         'peak_source': peaks['source'] + ' bf16 sustained (kernel timed inside the step)',
-                         'frac_of_burst_peak': achieved / peaks['tensor_burst'],
-                         'flops_per_launch': k2_flops, 'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
-                         'share_of_step': sum(k2_ms) / args.steps / (ms / args.steps) if ms else None,
-                         'timing': k2_timing + '; the value pass replays the identical kernels from a CUDA graph; '
-                                   'share_of_step = timed launches per step / ms_per_step'},
+            'roofline': roofline,
+            'kernels': kernel_stats,
             'eager_ms_per_step': eager_ms / args.steps,
             'pair_tflops': flops_pair(n, m, cfg, model.last_e_mode == 'regenerate') / 1e12,
             'pair_tflops_min': flops_pair(n, m, cfg) / 1e12,
@@ -643,7 +699,7 @@ def run_b200(args):
             'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
                           'log_optimal_transport': transport, 'weighted_procrustes': procrustes,
                           'patch_scores': patch_scores, 'local_global_registration': registration, 'collate_pyramid': pyramid},
-            'variants': {'embed_table': variant},
+            'variants': {'other_embed_kernel': variant},
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)

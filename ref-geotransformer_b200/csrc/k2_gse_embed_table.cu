@@ -139,22 +139,42 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
             code[K] = x_d <= x_max_d ? tbl_encode(x_d, inv_hd, rows_d, 4) : 0xffffffffu;  // beyond the table: exact
         }
         const int count = (int)min((long long)32, pairs_total - g0);
-        for (int e = 0; e < count; ++e) {
-            __half2 best[4], cur[4];
+        // groups without a distance beyond the table (all of them, normally) run the branch-free loop
+        if (!__any_sync(0xffffffffu, code[K] == 0xffffffffu)) {
+            for (int e = 0; e < count; ++e) {
+                __half2 best[4], cur[4];
 #pragma unroll
-            for (int s = 0; s < K; ++s) {  // geotransformer.py:66 max over the k angle slots
-                tbl_linear(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
+                for (int s = 0; s < K; ++s) {  // geotransformer.py:66 max over the k angle slots
+                    tbl_linear(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
+                    for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
+                }
+                tbl_cubic(fd, __shfl_sync(0xffffffffu, code[K], e), lane, cur);
+                uint4 o;
+                __half2* op = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) op[q] = __hadd2(cur[q], best[q]);  // :70
+                reinterpret_cast<uint4*>(out + (size_t)(g0 + e) * TBL_C)[lane] = o;
             }
-            const unsigned int code_d = __shfl_sync(0xffffffffu, code[K], e);
-            if (code_d != 0xffffffffu) tbl_cubic(fd, code_d, lane, cur);
-            else tbl_exact(div_term, w_d, b_d, __shfl_sync(0xffffffffu, x_d, e), lane, cur);
-            uint4 o;
-            __half2* op = reinterpret_cast<__half2*>(&o);
+        } else {
+            for (int e = 0; e < count; ++e) {
+                __half2 best[4], cur[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) op[q] = __hadd2(cur[q], best[q]);  // :70
-            reinterpret_cast<uint4*>(out + (size_t)(g0 + e) * TBL_C)[lane] = o;
+                for (int s = 0; s < K; ++s) {
+                    tbl_linear(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
+                }
+                const unsigned int code_d = __shfl_sync(0xffffffffu, code[K], e);
+                const float xe = __shfl_sync(0xffffffffu, x_d, e);
+                if (code_d != 0xffffffffu) tbl_cubic(fd, code_d, lane, cur);
+                else tbl_exact(div_term, w_d, b_d, xe, lane, cur);
+                uint4 o;
+                __half2* op = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) op[q] = __hadd2(cur[q], best[q]);
+                reinterpret_cast<uint4*>(out + (size_t)(g0 + e) * TBL_C)[lane] = o;
+            }
         }
     }
     if (clamped) *overflow = 1;

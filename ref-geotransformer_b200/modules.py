@@ -102,10 +102,11 @@ class SinusoidalPositionalEmbedding(nn.Module):
 class GeometricStructureEmbedding(nn.Module):
     """geotransformer.py:9-72.  `precision`: 'bf16' = tcgen05 kernel (hidden_dim 128/256), 'fp32' = CUDA-core
     kernel (any even hidden_dim); 'auto' picks bf16 when the hidden size allows it.
-    `embed_kernel` (attribute; default from GEOTX_EMBED, 'tensor'): 'table' makes the 16-bit embedding of the shipped
-    shape (hidden_dim 256, angle_k 3, 'max') go through the tabulated kernel K2t (experimental:
-    twice as fast and closer to fp32 than the bf16 contraction); `table_d_index_max` is the distance index up to
-    which its table reaches (beyond it the kernel evaluates exactly, slowly)."""
+    `embed_kernel` (attribute; default from GEOTX_EMBED, 'table'): 'table' makes the half-precision embedding of the
+    3DMatch / ModelNet shape (hidden_dim 256, angle_k 3, 'max') go through the tabulated kernel K2t (twice as fast and
+    closer to fp32 than the bf16 contraction); every other shape, output type and the fused first-block scores take the
+    tcgen05 kernel as with 'tensor'.  `table_d_index_max` is the distance index up to which the table reaches (96 =
+    19 m at sigma_d = 0.2; beyond it the kernel evaluates the function itself, slowly)."""
 
     def __init__(self, hidden_dim, sigma_d, sigma_a, angle_k, reduction_a='max', precision='auto'):
         super().__init__()
@@ -126,10 +127,10 @@ class GeometricStructureEmbedding(nn.Module):
         self._packed = None
         self._packed_key = None
         self._e_bound = math.inf
-        self.embed_kernel = os.environ.get('GEOTX_EMBED', 'tensor')
+        self.embed_kernel = os.environ.get('GEOTX_EMBED', 'table')
         if self.embed_kernel not in ('tensor', 'table'):
             raise ValueError(f"GEOTX_EMBED must be 'tensor' or 'table', got {self.embed_kernel!r}")
-        self.table_d_index_max = 48.0
+        self.table_d_index_max = 96.0
         self._tables_cache = None
         self._tables_key = None
 
@@ -156,7 +157,7 @@ class GeometricStructureEmbedding(nn.Module):
         if self._tables_cache is None or key != self._tables_key:
             w_d, b_d, w_a, b_a = [t.detach().contiguous() for t in ts]
             self._tables_cache = ops.gse_build_tables(self.embedding.div_term, w_d, b_d, w_a, b_a, self.factor_a,
-                                                      self.table_d_index_max, h_a=0.125, h_d=0.25)
+                                                      self.table_d_index_max, h_a=0.125, h_d=0.5)
             self._tables_key = key
         return self._tables_cache
 

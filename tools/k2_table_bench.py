@@ -21,9 +21,10 @@ for n in (1024, 2048):
     with torch.no_grad():
         geom = m.geometry(pts)
         d_max = float(torch.cdist(pts[0], pts[0]).max()) / m.sigma_d
-        for h in (1.0 / 16, 1.0 / 8):
+        for h, hd, dmax in ((1.0 / 8, 0.25, None), (1.0 / 8, 0.25, 48.0), (1.0 / 8, 0.5, 48.0), (1.0 / 8, 0.5, 96.0)):
             tb = pkg.ops.gse_build_tables(m.embedding.div_term, m.proj_d.weight.detach(), m.proj_d.bias.detach(),
-                                          m.proj_a.weight.detach(), m.proj_a.bias.detach(), m.factor_a, d_max * 1.01, h_a=h)
+                                          m.proj_a.weight.detach(), m.proj_a.bias.detach(), m.factor_a,
+                                          d_max * 1.01 if dmax is None else dmax, h_a=h, h_d=hd)
             rows = 64
             exact = pkg.ops.gse_embed_fp32(geom, m.embedding.div_term, m.proj_d.weight.detach(), m.proj_d.bias.detach(),
                                            m.proj_a.weight.detach(), m.proj_a.bias.detach(), m.sigma_d, m.factor_a, False,
@@ -45,7 +46,7 @@ for n in (1024, 2048):
                 b.record()
                 torch.cuda.synchronize()
                 return a.elapsed_time(b) / reps
-            res[f'n{n}_h{h}'] = {
+            res[f'n{n}_ha{h}_hd{hd}_dmax{dmax}'] = {
                 'table_rows': [tb.rows_a, tb.rows_d], 'table_bytes': int(tb.buf.numel()),
                 'max_abs_E': scale,
                 'table_vs_fp32_max_abs': float((tab - exact).abs().max()),
@@ -57,5 +58,5 @@ for n in (1024, 2048):
                 'overflow': int(tb.overflow.item()),
                 'full_max_abs_table_vs_tcgen05': float((out_tb.float() - out_tc.float()).abs().max()),
             }
-            print(json.dumps({f'n{n}_h{h}': res[f'n{n}_h{h}']}), flush=True)
+            print(json.dumps({f'n{n}_ha{h}_hd{hd}_dmax{dmax}': res[f'n{n}_ha{h}_hd{hd}_dmax{dmax}']}), flush=True)
 json.dump(res, open(os.path.join(ROOT, 'gpurun_out', 'k2_table.json'), 'w'), indent=1)
