@@ -8,9 +8,10 @@ import json
 try:
     d = json.loads(open('gpurun_out/sweep_$wl.json').read().strip().splitlines()[-1])
     r = d['roofline']
-    print('$wl: %.1f pairs/s  %.3f ms  e2e %.1f  K2 %.0f TF/s (%.2f of sustained)  pair_tensor_frac %.3f  clocks %s %s' % (
-        d['value'], d['ms_per_step'], d['e2e']['value'], r['achieved'], r['frac'], d['pair_tensor_frac'],
-        d['clocks']['sm_mhz'], d['clocks']['reasons']))
+    v = (d.get('variants') or {}).get('other_embed_kernel') or {}
+    print('$wl: %.1f pairs/s  %.3f ms  e2e %.1f  [%s] %s %.0f %s (%.2f of peak, share %.2f)  other kernel: %s  clocks %s %s' % (
+        d['value'], d['ms_per_step'], d['e2e']['value'], d['config']['embed_kernel'].split()[0], r['kernel'].split()[0],
+        r['achieved'], r['unit'], r['frac'], r['share_of_step'] or 0, v.get('value'), d['clocks']['sm_mhz'], d['clocks']['reasons']))
 except Exception as e:
     print('$wl: failed', e)
 PY
