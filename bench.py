@@ -627,7 +627,7 @@ def run_b200(args):
         registration = time_registration(pkg, shape_name) if world == 1 else None
         patch_scores = time_patch_scores(pkg, shape_name) if world == 1 else None
         variant = None
-        if world == 1 and not big and C == 256 and k == 3:
+        if world == 1 and not big and C in (128, 256) and k == 3:
             variant = time_embed_variant(pkg, model, resident, n_pairs, args.steps, last)
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
@@ -666,10 +666,10 @@ def run_b200(args):
         if table:  # the embedding runs by tabulation (shared-memory bound): the HBM-bound score kernel dominates
             roofline = hbm_roof
             kernel_stats = {'embedding': {'kernel': 'gse_embed_table_kernel (geotx_gse_embed_table)',
-                                          'bound': 'shared-memory pipe (10 table rows = 5 KB of LDS.128 per pair)',
+                                          'bound': 'shared-memory pipe (10 table rows = 20 C bytes of shared-memory reads per pair)',
                                           'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
                                           'share_of_step': sum(k2_ms) / args.steps / step_ms if ms else None,
-                                          'lds_bytes_per_launch': 5120.0 * k2_flops / flops_gse(n, C, k) * n * n if n else None}}
+                                          'lds_bytes_per_launch': 20.0 * C * k2_flops / flops_gse(n, C, k) * n * n if n else None}}
         else:
             roofline = tensor_roof
             kernel_stats = {'rpe_scores': hbm_roof}

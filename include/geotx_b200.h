@@ -282,7 +282,7 @@ int geotx_patch_scores(const float* ref_feats, int64_t n_ref, const float* src_f
  * channel, a function of one scalar; geotx_gse_build_tables samples the angle term every h_a index units (row r at
  * x = r h_a, rows_a >= pi*factor_a/h_a + 2; read by linear interpolation) and the distance term every h_d (row r at
  * x = (r-1) h_d, rows_d >= max d_index/h_d + 4; cubic), as halves (geotx_gse_table_bytes bytes), and
- * geotx_gse_embed_table interpolates them out of shared memory instead of contracting on the tensor cores.  Same geometry scratch and E layout (f16) as geotx_gse_embed; k = 3, C = 256, reduction 'max'.
+ * geotx_gse_embed_table interpolates them out of shared memory instead of contracting on the tensor cores.  Same geometry scratch and E layout (f16) as geotx_gse_embed; k = 3, C = 128 or 256, reduction 'max'.
  * A distance beyond the table is evaluated exactly from div_term, w_d, b_d (slow, meant to be rare); *overflow is set to
  * 1 only if an ANGLE argument fell outside its table (cannot happen for rows_a as above); never cleared. */
 int64_t geotx_gse_table_bytes(int C, int rows_a, int rows_d);

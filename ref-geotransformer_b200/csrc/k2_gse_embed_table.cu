@@ -11,7 +11,8 @@
 // packed half FMAs per pair for C = 256, k = 3: bound by the shared-memory pipe instead of the tensor pipe, and below
 // the fp16 rounding of the stored E (and of K2's bf16 operands).
 //
-// One warp per pair: lane l owns channels 8l .. 8l+7 (one LDS.128 per table row, one 16-byte store of E).  The lanes of
+// One warp per pair: lane l owns C/32 consecutive channels (one LDS.128 per table row and one 16-byte store of E at
+// C = 256, LDS.64 / 8 bytes at C = 128).  The lanes of
 // a warp first compute the arguments of 32 consecutive pairs (one each), then walk them together; a lookup travels
 // between lanes as one word.
 #include <cuda_fp16.h>
@@ -20,7 +21,9 @@
 
 namespace geotx {
 
-constexpr int TBL_C = 256;
+template <int C> struct TblVec;  // what one lane reads of a table row: C / 32 halves
+template <> struct TblVec<256> { typedef uint4 type; };
+template <> struct TblVec<128> { typedef uint2 type; };
 constexpr int TBL_THREADS = 512;
 constexpr int TBL_CTAS_PER_SM = 2;  // tables up to ~110 KB
 
@@ -48,56 +51,62 @@ __device__ __forceinline__ unsigned int tbl_encode(float x, float inv_h, int row
     return ((unsigned int)fl << 16) | (unsigned int)(t * 65536.f);
 }
 
-// 8 channels (4 half2) of lane `lane`: linear interpolation between rows r and r + 1
+// C / 32 channels (C / 64 half2) of lane `lane`: linear interpolation between rows r and r + 1
+template <int C>
 __device__ __forceinline__ void tbl_linear(const __half* __restrict__ table, unsigned int code, int lane,
-                                           __half2 (&acc)[4]) {
+                                           __half2 (&acc)[C / 64]) {
+    typedef typename TblVec<C>::type V;
     const __half2 t = __float2half2_rn((float)(code & 0xffffu) * (1.f / 65536.f));
-    const uint4* base = reinterpret_cast<const uint4*>(table + (size_t)(code >> 16) * TBL_C) + lane;
-    const uint4 r0 = base[0], r1 = base[TBL_C / 8];
+    const V* base = reinterpret_cast<const V*>(table + (size_t)(code >> 16) * C) + lane;
+    const V r0 = base[0], r1 = base[32];
     const __half2* p0 = reinterpret_cast<const __half2*>(&r0);
     const __half2* p1 = reinterpret_cast<const __half2*>(&r1);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) acc[q] = __hfma2(t, __hsub2(p1[q], p0[q]), p0[q]);
+    for (int q = 0; q < C / 64; ++q) acc[q] = __hfma2(t, __hsub2(p1[q], p0[q]), p0[q]);
 }
 
 // cubic Lagrange interpolation over rows r .. r + 3 (nodes at -1, 0, 1, 2 around the interval)
+template <int C>
 __device__ __forceinline__ void tbl_cubic(const __half* __restrict__ table, unsigned int code, int lane,
-                                          __half2 (&acc)[4]) {
+                                          __half2 (&acc)[C / 64]) {
+    typedef typename TblVec<C>::type V;
     const float t = (float)(code & 0xffffu) * (1.f / 65536.f), tm1 = t - 1.f, tm2 = t - 2.f, tp1 = t + 1.f;
     const __half2 w0 = __float2half2_rn(-t * tm1 * tm2 * (1.f / 6.f)), w1 = __float2half2_rn(tp1 * tm1 * tm2 * 0.5f),
                   w2 = __float2half2_rn(-tp1 * t * tm2 * 0.5f), w3 = __float2half2_rn(tp1 * t * tm1 * (1.f / 6.f));
-    const uint4* base = reinterpret_cast<const uint4*>(table + (size_t)(code >> 16) * TBL_C) + lane;
-    const uint4 r0 = base[0], r1 = base[TBL_C / 8], r2 = base[2 * (TBL_C / 8)], r3 = base[3 * (TBL_C / 8)];
+    const V* base = reinterpret_cast<const V*>(table + (size_t)(code >> 16) * C) + lane;
+    const V r0 = base[0], r1 = base[32], r2 = base[64], r3 = base[96];
     const __half2* p0 = reinterpret_cast<const __half2*>(&r0);
     const __half2* p1 = reinterpret_cast<const __half2*>(&r1);
     const __half2* p2 = reinterpret_cast<const __half2*>(&r2);
     const __half2* p3 = reinterpret_cast<const __half2*>(&r3);
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
+    for (int q = 0; q < C / 64; ++q)
         acc[q] = __hfma2(w3, p3[q], __hfma2(w2, p2[q], __hfma2(w1, p1[q], __hmul2(w0, p0[q]))));
 }
 
 // A distance beyond the table (a cloud larger than the range the tables were built for): the function itself,
 // positional_embedding.py:28-31 + the Linear, for this lane's 8 channels.  Rare and slow (128 sincos + 2048 FMA).
+template <int C>
 __device__ __noinline__ void tbl_exact(const float* __restrict__ div_term, const float* __restrict__ w,
-                                       const float* __restrict__ bias, float x, int lane, __half2 (&acc)[4]) {
-    float a[8];
+                                       const float* __restrict__ bias, float x, int lane, __half2 (&acc)[C / 64]) {
+    constexpr int PER = C / 32;
+    float a[PER];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) a[q] = bias[8 * lane + q];
-    for (int t = 0; t < TBL_C / 2; ++t) {
+    for (int q = 0; q < PER; ++q) a[q] = bias[PER * lane + q];
+    for (int t = 0; t < C / 2; ++t) {
         float sn, cs;
         sincosf(__fmul_rn(x, div_term[t]), &sn, &cs);
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const float2 wt = *reinterpret_cast<const float2*>(w + (size_t)(8 * lane + q) * TBL_C + 2 * t);
+        for (int q = 0; q < PER; ++q) {
+            const float2 wt = *reinterpret_cast<const float2*>(w + (size_t)(PER * lane + q) * C + 2 * t);
             a[q] = fmaf(wt.y, cs, fmaf(wt.x, sn, a[q]));
         }
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) acc[q] = __floats2half2_rn(a[2 * q], a[2 * q + 1]);
+    for (int q = 0; q < C / 64; ++q) acc[q] = __floats2half2_rn(a[2 * q], a[2 * q + 1]);
 }
 
-template <int K>
+template <int K, int C>
 __global__ void __launch_bounds__(TBL_THREADS, TBL_CTAS_PER_SM)
 gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict__ refv, int n, int row_begin,
                        int row_count, long long pairs_total, const __half* __restrict__ tables, int rows_a, int rows_d,
@@ -106,11 +115,12 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
                        int* __restrict__ overflow) {
     extern __shared__ __align__(16) unsigned char tbl_smem[];
     __half* fa = reinterpret_cast<__half*>(tbl_smem);
-    __half* fd = fa + (size_t)rows_a * TBL_C;
+    typedef typename TblVec<C>::type V;
+    __half* fd = fa + (size_t)rows_a * C;
     {
         const uint4* src = reinterpret_cast<const uint4*>(tables);
         uint4* dst = reinterpret_cast<uint4*>(tbl_smem);
-        const int total = (rows_a + rows_d) * TBL_C / 8;
+        const int total = (rows_a + rows_d) * C / 8;
         for (int e = threadIdx.x; e < total; e += TBL_THREADS) dst[e] = src[e];
     }
     __syncthreads();
@@ -142,38 +152,38 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
         // groups without a distance beyond the table (all of them, normally) run the branch-free loop
         if (!__any_sync(0xffffffffu, code[K] == 0xffffffffu)) {
             for (int e = 0; e < count; ++e) {
-                __half2 best[4], cur[4];
+                __half2 best[C / 64], cur[C / 64];
 #pragma unroll
                 for (int s = 0; s < K; ++s) {  // geotransformer.py:66 max over the k angle slots
-                    tbl_linear(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
+                    tbl_linear<C>(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
+                    for (int q = 0; q < C / 64; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
                 }
-                tbl_cubic(fd, __shfl_sync(0xffffffffu, code[K], e), lane, cur);
-                uint4 o;
+                tbl_cubic<C>(fd, __shfl_sync(0xffffffffu, code[K], e), lane, cur);
+                V o;
                 __half2* op = reinterpret_cast<__half2*>(&o);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) op[q] = __hadd2(cur[q], best[q]);  // :70
-                reinterpret_cast<uint4*>(out + (size_t)(g0 + e) * TBL_C)[lane] = o;
+                for (int q = 0; q < C / 64; ++q) op[q] = __hadd2(cur[q], best[q]);  // :70
+                reinterpret_cast<V*>(out + (size_t)(g0 + e) * C)[lane] = o;
             }
         } else {
             for (int e = 0; e < count; ++e) {
-                __half2 best[4], cur[4];
+                __half2 best[C / 64], cur[C / 64];
 #pragma unroll
                 for (int s = 0; s < K; ++s) {
-                    tbl_linear(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
+                    tbl_linear<C>(fa, __shfl_sync(0xffffffffu, code[s], e), lane, cur);
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
+                    for (int q = 0; q < C / 64; ++q) best[q] = s == 0 ? cur[q] : __hmax2(best[q], cur[q]);
                 }
                 const unsigned int code_d = __shfl_sync(0xffffffffu, code[K], e);
                 const float xe = __shfl_sync(0xffffffffu, x_d, e);
-                if (code_d != 0xffffffffu) tbl_cubic(fd, code_d, lane, cur);
-                else tbl_exact(div_term, w_d, b_d, xe, lane, cur);
-                uint4 o;
+                if (code_d != 0xffffffffu) tbl_cubic<C>(fd, code_d, lane, cur);
+                else tbl_exact<C>(div_term, w_d, b_d, xe, lane, cur);
+                V o;
                 __half2* op = reinterpret_cast<__half2*>(&o);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) op[q] = __hadd2(cur[q], best[q]);
-                reinterpret_cast<uint4*>(out + (size_t)(g0 + e) * TBL_C)[lane] = o;
+                for (int q = 0; q < C / 64; ++q) op[q] = __hadd2(cur[q], best[q]);
+                reinterpret_cast<V*>(out + (size_t)(g0 + e) * C)[lane] = o;
             }
         }
     }
@@ -185,7 +195,7 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
 using namespace geotx;
 
 extern "C" int64_t geotx_gse_table_bytes(int C, int rows_a, int rows_d) {
-    if (C != TBL_C || rows_a < 4 || rows_d < 4 || rows_a > 65535 || rows_d > 65535) return 0;
+    if ((C != 256 && C != 128) || rows_a < 4 || rows_d < 4 || rows_a > 65535 || rows_d > 65535) return 0;
     return (int64_t)(rows_a + rows_d) * C * 2;
 }
 
@@ -193,8 +203,8 @@ extern "C" int geotx_gse_build_tables(const float* div_term, const float* w_d, c
                                       const float* b_a, int C, float h_a, float h_d, int rows_a, int rows_d,
                                       void* tables, void* stream) {
     GEOTX_REQUIRE(div_term && w_d && b_d && w_a && b_a && tables, "geotx_gse_build_tables: null pointer");
-    GEOTX_REQUIRE(C == TBL_C && rows_a >= 4 && rows_d >= 4 && rows_a <= 65535 && rows_d <= 65535 && h_a > 0.f && h_d > 0.f,
-                  "geotx_gse_build_tables: C must be %d, 4..65535 rows per table", TBL_C);
+    GEOTX_REQUIRE((C == 256 || C == 128) && rows_a >= 4 && rows_d >= 4 && rows_a <= 65535 && rows_d <= 65535 &&
+                      h_a > 0.f && h_d > 0.f, "geotx_gse_build_tables: C must be 128 or 256, 4..65535 rows per table");
     __half* t = (__half*)tables;
     gse_table_build_kernel<<<rows_a, C, 0, (cudaStream_t)stream>>>(div_term, w_a, b_a, C, h_a, 0, t);
     gse_table_build_kernel<<<rows_d, C, 0, (cudaStream_t)stream>>>(div_term, w_d, b_d, C, h_d, 1, t + (size_t)rows_a * C);
@@ -206,21 +216,26 @@ extern "C" int geotx_gse_embed_table(const void* geometry, int B, int n, int k, 
                                      float sigma_d, float factor_a, const float* div_term, const float* w_d,
                                      const float* b_d, void* out_f16, int32_t* overflow, void* stream) {
     GEOTX_REQUIRE(geometry && tables && out_f16 && overflow && div_term && w_d && b_d, "geotx_gse_embed_table: null pointer");
-    GEOTX_REQUIRE(B > 0 && n > 0 && k == 3 && C == TBL_C, "geotx_gse_embed_table: prototype takes k = 3, C = %d", TBL_C);
+    GEOTX_REQUIRE(B > 0 && n > 0 && k == 3 && (C == 256 || C == 128), "geotx_gse_embed_table: takes k = 3, C = 128 or 256");
     GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed_table: bad row slab");
     const size_t smem = (size_t)(rows_a + rows_d) * C * 2;
     GEOTX_REQUIRE(rows_a >= 4 && rows_d >= 4 && smem <= 220 * 1024, "geotx_gse_embed_table: tables of %zu B do not fit",
                   smem);
-    int rc = check_cuda(cudaFuncSetAttribute(gse_embed_table_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem), "geotx_gse_embed_table: shared memory");
-    if (rc) return rc;
     const float4* pts4 = (const float4*)geometry;
     const float4* refv = pts4 + (size_t)B * n;
     const long long pairs = (long long)B * row_count * n;
-    gse_embed_table_kernel<3><<<148 * (smem <= 110 * 1024 ? TBL_CTAS_PER_SM : 1), TBL_THREADS, smem,
-                                (cudaStream_t)stream>>>(pts4, refv, n, row_begin, row_count, pairs,
-                                                        (const __half*)tables, rows_a, rows_d, 1.0f / h_a, 1.0f / h_d,
-                                                        sigma_d, factor_a, div_term, w_d, b_d, (__half*)out_f16,
-                                                        overflow);
+    const int grid = 148 * (smem <= 110 * 1024 ? TBL_CTAS_PER_SM : 1);
+    auto launch = [&](auto kernel) -> int {
+        int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                            "geotx_gse_embed_table: shared memory");
+        if (rc) return rc;
+        kernel<<<grid, TBL_THREADS, smem, (cudaStream_t)stream>>>(pts4, refv, n, row_begin, row_count, pairs,
+                                                                  (const __half*)tables, rows_a, rows_d, 1.0f / h_a,
+                                                                  1.0f / h_d, sigma_d, factor_a, div_term, w_d, b_d,
+                                                                  (__half*)out_f16, overflow);
+        return 0;
+    };
+    int rc = C == 256 ? launch(gse_embed_table_kernel<3, 256>) : launch(gse_embed_table_kernel<3, 128>);
+    if (rc) return rc;
     return launch_status("geotx_gse_embed_table");
 }

@@ -103,7 +103,7 @@ class GeometricStructureEmbedding(nn.Module):
     """geotransformer.py:9-72.  `precision`: 'bf16' = tcgen05 kernel (hidden_dim 128/256), 'fp32' = CUDA-core
     kernel (any even hidden_dim); 'auto' picks bf16 when the hidden size allows it.
     `embed_kernel` (attribute; default from GEOTX_EMBED, 'table'): 'table' makes the half-precision embedding of the
-    3DMatch / ModelNet shape (hidden_dim 256, angle_k 3, 'max') go through the tabulated kernel K2t (twice as fast and
+    shipped shapes (hidden_dim 128 or 256, angle_k 3, 'max') go through the tabulated kernel K2t (twice as fast and
     closer to fp32 than the bf16 contraction); every other shape, output type and the fused first-block scores take the
     tcgen05 kernel as with 'tensor'.  `table_d_index_max` is the distance index up to which the table reaches (96 =
     19 m at sigma_d = 0.2; beyond it the kernel evaluates the function itself, slowly)."""
@@ -162,7 +162,7 @@ class GeometricStructureEmbedding(nn.Module):
         return self._tables_cache
 
     def _use_table(self, out_dtype, qt):
-        return (self.embed_kernel == 'table' and self.hidden_dim == 256 and self.angle_k == 3 and
+        return (self.embed_kernel == 'table' and self.hidden_dim in (128, 256) and self.angle_k == 3 and
                 self.reduction_a == 'max' and out_dtype == torch.float16 and qt is None and self.precision != 'fp32')
 
     def storage_dtype(self):

@@ -163,9 +163,10 @@ def test_fused_first_block_scores(pkg, oracle, C, H, n, reduction):
 TOL_TABLE = 2e-3  # Frobenius-relative: half tables + half arithmetic; measured ~5e-4 (the bf16 contraction: ~4e-3)
 
 
-@pytest.mark.parametrize('name', ['3dmatch_n192', 'modelnet_n128'])
+@pytest.mark.parametrize('name', ['3dmatch_n192', 'kitti_n256', 'modelnet_n128'])
 def test_table_kernel_vs_reference_golden(pkg, oracle, golden, name):
-    """The C = 256 shipped configs: golden rows of E written by the reference, through the tabulated kernel."""
+    """The three shipped configs (C = 256 / 128 / 256): golden rows of E written by the reference, through the
+    tabulated kernel."""
     z = golden(f'{name}.npz')
     cfg = eval(str(z['cfg']))
     sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
