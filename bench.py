@@ -676,7 +676,7 @@ def run_b200(args):
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16' if table else 'bf16', 'data': 'synthetic',
             'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': C, 'num_heads': cfg['num_heads'],
                        'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1, 'launch': 'one CUDA graph replay per step',
                        'e_storage': model.last_e_mode + (f' (E never stored: rebuilt for each of the {sum(b == "self" for b in cfg["blocks"])} self blocks in {model.regenerate_slab_bytes >> 20} MiB row slabs; pair_tflops counts those passes)' if model.last_e_mode == 'regenerate' else ' (one embedding pass per cloud)'),
