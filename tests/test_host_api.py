@@ -171,3 +171,22 @@ def test_install_into_reference_rebinds_and_restores(pkg):
         pkg.uninstall_from_reference()
     g = importlib.import_module('geotransformer.modules.geotransformer.geotransformer')
     assert g.GeometricTransformer is GT and g.GeometricStructureEmbedding is GSE
+
+
+def test_embedding_kernel_switch(pkg, monkeypatch):
+    """GEOTX_EMBED selects the embedding kernel at construction; the tabulated kernel only takes the shapes it was
+    built for (every other request goes to the tcgen05 / fp32 kernels, never to a CPU path)."""
+    import torch
+    m = pkg.GeometricStructureEmbedding(256, 0.2, 15, 3)
+    assert m.embed_kernel == 'table' and m._use_table(torch.float16, None)
+    assert not m._use_table(torch.float32, None) and not m._use_table(torch.float16, object())
+    assert not pkg.GeometricStructureEmbedding(256, 0.2, 15, 2)._use_table(torch.float16, None)
+    assert not pkg.GeometricStructureEmbedding(256, 0.2, 15, 3, reduction_a='mean')._use_table(torch.float16, None)
+    assert not pkg.GeometricStructureEmbedding(64, 0.2, 15, 3)._use_table(torch.float16, None)
+    assert pkg.GeometricStructureEmbedding(128, 4.8, 15, 3)._use_table(torch.float16, None)
+    monkeypatch.setenv('GEOTX_EMBED', 'tensor')
+    assert pkg.GeometricStructureEmbedding(256, 0.2, 15, 3).embed_kernel == 'tensor'
+    monkeypatch.setenv('GEOTX_EMBED', 'cpu')
+    import pytest
+    with pytest.raises(ValueError):
+        pkg.GeometricStructureEmbedding(256, 0.2, 15, 3)
