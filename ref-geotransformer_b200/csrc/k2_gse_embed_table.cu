@@ -21,6 +21,16 @@
 
 namespace geotx {
 
+// E is written once and never read by this SM: no L1 line is allocated for it (the stores share the L1 / shared-memory
+// path with the table reads).
+__device__ __forceinline__ void tbl_store(void* p, const uint4& v) {
+    asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void tbl_store(void* p, const uint2& v) {
+    asm volatile("st.global.L1::no_allocate.v2.b32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
 template <int C> struct TblVec;  // what one lane reads of a table row: C / 32 halves
 template <> struct TblVec<256> { typedef uint4 type; };
 template <> struct TblVec<128> { typedef uint2 type; };
@@ -164,7 +174,7 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
                 __half2* op = reinterpret_cast<__half2*>(&o);
 #pragma unroll
                 for (int q = 0; q < C / 64; ++q) op[q] = __hadd2(cur[q], best[q]);  // :70
-                reinterpret_cast<V*>(out + (size_t)(g0 + e) * C)[lane] = o;
+                tbl_store(reinterpret_cast<V*>(out + (size_t)(g0 + e) * C) + lane, o);
             }
         } else {
             for (int e = 0; e < count; ++e) {
@@ -183,7 +193,7 @@ gse_embed_table_kernel(const float4* __restrict__ pts4, const float4* __restrict
                 __half2* op = reinterpret_cast<__half2*>(&o);
 #pragma unroll
                 for (int q = 0; q < C / 64; ++q) op[q] = __hadd2(cur[q], best[q]);
-                reinterpret_cast<V*>(out + (size_t)(g0 + e) * C)[lane] = o;
+                tbl_store(reinterpret_cast<V*>(out + (size_t)(g0 + e) * C) + lane, o);
             }
         }
     }
