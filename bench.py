@@ -319,7 +319,36 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
-def time_embed_variant(pkg, model, resident, n_pairs, steps, default_out):
+class InFlight:
+    """`count` CUDA-graph instances of the forward, each on its own stream: step s replays instance s % count, so that
+    the small kernels of one pair (the cross blocks keep few SMs busy) run under the GPU-filling kernels of the next.
+    Independent pairs, identical kernels per pair; count = 1 is the plain replay loop."""
+
+    def __init__(self, pkg, model, example, count):
+        import torch
+        self.torch = torch
+        self.graphs = [pkg.GraphedGeometricTransformer(model, *example) for _ in range(count)]
+        self.streams = [torch.cuda.Stream() for _ in range(count)] if count > 1 else [None]
+
+    def run(self, resident, n_pairs, steps):
+        torch = self.torch
+        main = torch.cuda.current_stream()
+        out = None
+        if self.streams[0] is None:
+            for s in range(steps):
+                out = self.graphs[0](*resident[s % n_pairs])
+            return out
+        for st in self.streams:
+            st.wait_stream(main)
+        for s in range(steps):
+            with torch.cuda.stream(self.streams[s % len(self.graphs)]):
+                out = self.graphs[s % len(self.graphs)](*resident[s % n_pairs])
+        for st in self.streams:
+            main.wait_stream(st)
+        return out
+
+
+def time_embed_variant(pkg, model, resident, n_pairs, steps, default_out, inflight):
     """The same forward with the OTHER embedding kernel (tabulated K2t <-> tcgen05 contraction K2): graph replay, CUDA
     events, same pairs; reported beside `value`, not as it."""
     import torch
@@ -327,14 +356,12 @@ def time_embed_variant(pkg, model, resident, n_pairs, steps, default_out):
     other = 'tensor' if default == 'table' else 'table'
     try:
         model.embedding.embed_kernel = other
-        fast = pkg.GraphedGeometricTransformer(model, *resident[0])
-        for s in range(3):
-            out = fast(*resident[s % n_pairs])
+        fast = InFlight(pkg, model, resident[0], inflight)
+        out = fast.run(resident, n_pairs, 2 * inflight + 1)
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        for s in range(steps):
-            out = fast(*resident[s % n_pairs])
+        out = fast.run(resident, n_pairs, steps)
         b.record()
         torch.cuda.synchronize()
         ms = a.elapsed_time(b)
@@ -575,17 +602,19 @@ def run_b200(args):
         pkg.ops.rpe_scores = orig_scores
 
         # ---- pass 2 (the timed region of `value`): the same forward replayed as one CUDA graph per step ----
-        fast = pkg.GraphedGeometricTransformer(model, *resident[0])
-        for s in range(max(args.warmup, 3)):
-            last = fast(*resident[s % n_pairs])
+        # graph-private buffers per instance: E of both clouds (n = 4096: 17 GB); keep the instances alive at once
+        # (value, end-to-end pipeline, variant) below ~100 GB
+        many = max(n, m) <= 2048
+        inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '3'))) if many else 1
+        fast = InFlight(pkg, model, resident[0], inflight)
+        last = fast.run(resident, n_pairs, max(args.warmup, 3, 2 * inflight))
         barrier()
         sampler = ClockSampler(local) if rank == 0 else None
         if sampler:
             sampler.start()
         t_start, t_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_start.record()
-        for s in range(args.steps):
-            last = fast(*resident[s % n_pairs])
+        last = fast.run(resident, n_pairs, args.steps)
         if world > 1:  # the one collective of the job: gather the outputs of the last pair of every rank
             gathered = pkg.dist.gather_pair_outputs([torch.cat(last, dim=1)[0]], world)
         t_stop.record()
@@ -595,8 +624,8 @@ def run_b200(args):
 
         # ---- end to end: host (pinned) inputs -> device -> forward -> host outputs, every step, through the serving
         #      API (PipelinedGeometricTransformer: the upload of pair p+1 / download of pair p-1 overlap pair p) ----
-        depth = 1 if big else 2
-        if big:  # one set of graph-private buffers at a time
+        depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', '3'))) if many else 2)
+        if big or not many:  # one set of graph-private buffers at a time
             del fast
             torch.cuda.empty_cache()
         pipe = pkg.PipelinedGeometricTransformer(model, *resident[0], depth=depth)
@@ -628,7 +657,7 @@ def run_b200(args):
         patch_scores = time_patch_scores(pkg, shape_name) if world == 1 else None
         variant = None
         if world == 1 and not big and C in (128, 256) and k == 3:
-            variant = time_embed_variant(pkg, model, resident, n_pairs, args.steps, last)
+            variant = time_embed_variant(pkg, model, resident, n_pairs, args.steps, last, inflight)
 
     tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -678,7 +707,7 @@ def run_b200(args):
             'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16' if table else 'bf16', 'data': 'synthetic',
             'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': C, 'num_heads': cfg['num_heads'],
-                       'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1, 'launch': 'one CUDA graph replay per step',
+                       'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1, 'launch': 'one CUDA graph replay per step' + (f'; {inflight} graph instances in flight on {inflight} streams (independent pairs overlap)' if inflight > 1 else ''),
                        'e_storage': model.last_e_mode + (f' (E never stored: rebuilt for each of the {sum(b == "self" for b in cfg["blocks"])} self blocks in {model.regenerate_slab_bytes >> 20} MiB row slabs; pair_tflops counts those passes)' if model.last_e_mode == 'regenerate' else ' (one embedding pass per cloud)'),
                        'embed_kernel': 'table (geotx_gse_embed_table)' if table else 'tensor (geotx_gse_embed, tcgen05)',
                        'l2_slab_bytes': model.l2_slab_bytes, 'first_block_scores_fused_into_embedding': bool(model.fuse_scores),

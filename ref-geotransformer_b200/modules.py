@@ -828,10 +828,10 @@ class PipelinedGeometricTransformer:
         if depth < 1:
             raise ValueError('depth must be >= 1')
         if overlap_compute is None:
-            overlap_compute = os.environ.get('GEOTX_PIPE_OVERLAP', '0') != '0'
-        # overlap_compute (opt-in, GEOTX_PIPE_OVERLAP=1): every slot replays on its own stream, so that the small kernels
-        # of one pair (the cross blocks keep few SMs busy) could run under the GPU-filling kernels of the next; results
-        # are still handed out in order.  Measured neutral at n = 1024 (675 vs 674 pairs/s): off by default.
+            overlap_compute = os.environ.get('GEOTX_PIPE_OVERLAP', '1') != '0'
+        # overlap_compute (GEOTX_PIPE_OVERLAP, default on): every slot replays on its own stream, so that the small kernels
+        # of one pair (the cross blocks keep few SMs busy) run under the GPU-filling kernels of the next; results are
+        # still handed out in order.  n = 1024, host to host: 692 pairs/s without, 703 / 747 / 761 at depth 2 / 3 / 4.
         self.compute_streams = [torch.cuda.Stream() for _ in range(depth)] if overlap_compute and depth > 1 else None
         self.slots = []
         for _ in range(depth):
