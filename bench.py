@@ -9,9 +9,13 @@ configs[1]: 3DMatch stage-4 config, N = M = 1024 superpoints, random-init weight
 own pairs (pair sharding, no collective on the path; one NCCL all_gather of the outputs at the end).
 Prints ONE JSON line on rank 0.
 
-  value     pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks
-  e2e       pairs/s through the public module call with HOST (pinned) inputs and a host read of the outputs
-  roofline  the fused embedding kernel (geotx_gse_embed, tcgen05): algorithmic flops / CUDA-event time, per launch
+  value     pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks; up to N = 2048 three CUDA-graph instances
+            of the forward are in flight on three streams (independent pairs overlap; GEOTX_INFLIGHT)
+  e2e       pairs/s through PipelinedGeometricTransformer.map with HOST (pinned) inputs and a host read of the outputs
+  roofline  the dominant kernel, timed by CUDA events captured inside the forward's graph: with the tabulated embedding
+            (default) the HBM-bound RPE score kernel (algorithmic bytes / time against the measured copy bandwidth), with
+            GEOTX_EMBED=tensor the tcgen05 embedding kernel (algorithmic flops against the measured bf16 rate)
+  kernels   the other of the two; variants.other_embed_kernel: the same run with the other embedding kernel
   cpu_baseline  the oracle (CPU restatement of the reference's formulation) on this box's host cores
 
 --impl reference times that CPU oracle alone (rank 0 only)."""
