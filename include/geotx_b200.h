@@ -43,7 +43,7 @@ int geotx_abi_version(void);
 /* Bytes of caller-provided scratch needed by geotx_gse_knn for B clouds of n points and k neighbours
  * (packed float4 points + k reference vectors per point).  The scratch is an OUTPUT of geotx_gse_knn and an
  * INPUT of geotx_gse_indices / geotx_gse_embed (it holds p and p_knn - p in the kernels' layout). */
-int64_t geotx_gse_geometry_bytes(int B, int n, int k);
+int64_t geotx_gse_geometry_bytes(int B, int n, int k);  /* includes a 16-byte trailer: the clouds' largest squared distance */
 
 /* modules/geotransformer/geotransformer.py:38,42 (+ modules/ops/pairwise_distance.py:4-31):
  * knn[b,i,:] = indices of the k+1 smallest sqrt(d2(i,:)), first dropped.  Bit-exact with the reference's
@@ -278,7 +278,48 @@ int geotx_patch_scores(const float* ref_feats, int64_t n_ref, const float* src_f
                        const int64_t* ref_node_corr_indices, const int64_t* src_node_corr_indices, int P,
                        float* scores, void* stream);
 
-/* K2t (experimental, opt-in): the embedding by tabulation.  proj_x(sinus(x)) + bias is, per
+/* K2c, the default embedding kernel: geotransformer.py:57-72 + positional_embedding.py:18-34 as a LOW-RANK contraction.
+ * Per output channel, proj_x(sinus(x)) is a band-limited function of one scalar on a bounded interval, so it has a
+ * short Chebyshev expansion f_c(x) = sum_{m<K} G[m,c] T_m(2x/L - 1): K = 16 * ka_tiles for the angle term (L = pi *
+ * factor_a: 16 coefficients up to 13 index units, 32 up to 37) and K_d = 16 .. 128 for the distance term, in six
+ * prebuilt sets for ranges up to geotx_gse_cheb_d_range(0..5) = 13, 37, 64, 93, 150, 210 index units.
+ *   geotx_gse_cheb_ka_tiles(pi * factor_a)   1 or 2; 0 = the angle range is not covered (use geotx_gse_embed)
+ *   geotx_gse_build_cheb   once per weight set: G in fp64 (Gauss-Chebyshev quadrature of the module's own weights and
+ *                          div_term), rounded to half, in the kernel's register-image layout (geotx_gse_cheb_bytes bytes);
+ *                          stats f32 [7][4] (device; set 0 = angle, 1..6 = distance sets): {largest |expansion - f| found
+ *                          at 256 check points per channel, largest |f|, largest |G|, 0} -- the caller's accuracy guard
+ *   geotx_gse_embed_cheb   E[b,i,j,:] (f16 or bf16) for a slab of query rows, any k <= GEOTX_MAX_ANGLE_K, 'max' or 'mean'.
+ *                          The basis values are generated per pair in registers (three-term recurrence, fp32), stored as
+ *                          halves in shared memory and contracted with mma.sync.m16n8k16 (fp32 accumulation); the max
+ *                          over k and the sum with the distance term happen in the accumulator registers.
+ *                          The kernel selects the distance set from the clouds' largest distance, which geotx_gse_knn
+ *                          leaves in the geometry scratch; max_d_set caps the choice (it sizes the shared memory).
+ *                          *overflow is set to 1 (never cleared) if an argument fell outside its range (distance beyond
+ *                          set max_d_set; the value is then clamped to the end of the range). */
+int geotx_gse_cheb_ka_tiles(float angle_index_max);
+float geotx_gse_cheb_d_range(int d_set);
+int64_t geotx_gse_cheb_bytes(int C, int ka_tiles);
+int geotx_gse_build_cheb(const float* div_term, const float* w_d, const float* b_d, const float* w_a, const float* b_a,
+                         int C, float angle_index_max, int ka_tiles, void* coef, float* stats, void* stream);
+int geotx_gse_embed_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count, const void* coef,
+                         int C, float angle_index_max, int ka_tiles, int max_d_set, float sigma_d, float factor_a,
+                         int reduce_mean, int out_dtype, void* out, int32_t* overflow, void* stream);
+
+/* K3r: geotransformer.py:57-72 fused with rpe_transformer.py:54-56 (proj_p folded into the query, see geotx_rpe_scores):
+ *   scores_p[b,h,i,j] = sum_c qt[b,h,i,c] * E[b,i,j,c]      for the slab's rows i, all j
+ * WITHOUT E ever being written to or read from memory: the kernel of geotx_gse_embed_cheb rebuilds E for 128 keys of one
+ * query row at a time in its accumulator registers (rounded to half, exactly what a stored half E holds), feeds them
+ * back as the A operand of a second mma.sync contraction with that row's folded query (hi + lo halves, as in
+ * geotx_rpe_scores), adds the 8 channel blocks' partial scores in shared memory and writes 512-byte rows of scores_p.
+ * One launch per 'self' block and cloud replaces one embedding pass (n^2 C 2 B written) plus one HBM read of E per block.
+ *   qt f32 addressed as in geotx_rpe_scores (16-byte aligned, strides multiples of 4); H <= 8; scores_p f32 [B,H,n,n]
+ *   (only the slab's rows are written); coef / angle_index_max / ka_tiles / max_d_set / overflow as in geotx_gse_embed_cheb. */
+int geotx_rpe_scores_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count, const void* coef,
+                          int C, float angle_index_max, int ka_tiles, int max_d_set, float sigma_d, float factor_a,
+                          int reduce_mean, const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n,
+                          int H, float* scores_p, int32_t* overflow, void* stream);
+
+/* K2t (superseded by K2c, kept as embed_kernel='table'): the embedding by tabulation.  proj_x(sinus(x)) + bias is, per
  * channel, a function of one scalar; geotx_gse_build_tables samples the angle term every h_a index units (row r at
  * x = r h_a, rows_a >= pi*factor_a/h_a + 2; read by linear interpolation) and the distance term every h_d (row r at
  * x = (r-1) h_d, rows_d >= max d_index/h_d + 4; cubic), as halves (geotx_gse_table_bytes bytes), and

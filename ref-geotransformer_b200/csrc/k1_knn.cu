@@ -10,8 +10,11 @@
 namespace geotx {
 
 // points (B*n, 3) fp32  ->  pts4 (B*n) float4 = (x, y, z, |p|^2 in the reference's rounding order)
-__global__ void pack_points_kernel(const float* __restrict__ points, float4* __restrict__ pts4, int total) {
+// Also clears the word behind the geometry scratch in which knn_kernel leaves the largest squared distance.
+__global__ void pack_points_kernel(const float* __restrict__ points, float4* __restrict__ pts4, int total,
+                                   unsigned int* __restrict__ dmax2_bits) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) *dmax2_bits = 0u;
     if (t >= total) return;
     float x = points[3 * t], y = points[3 * t + 1], z = points[3 * t + 2];
     pts4[t] = make_float4(x, y, z, sq_norm_ref(x, y, z));
@@ -28,7 +31,7 @@ __device__ __forceinline__ bool cand_less(float va, int ia, float vb, int ib) {
 // reference's topk over sqrt(d2) produces wherever that order is defined (tie-free rows, see synth.tie_free).
 __global__ void __launch_bounds__(KNN_WARPS * 32)
 knn_kernel(const float4* __restrict__ pts4, int n, int k, int rows_total,
-           long long* __restrict__ knn_out, float4* __restrict__ refv_out) {
+           long long* __restrict__ knn_out, float4* __restrict__ refv_out, unsigned int* __restrict__ dmax2_bits) {
     const int lane = threadIdx.x & 31;
     const int row = blockIdx.x * KNN_WARPS + (threadIdx.x >> 5);
     if (row >= rows_total) return;
@@ -42,9 +45,11 @@ knn_kernel(const float4* __restrict__ pts4, int n, int k, int rows_total,
 #pragma unroll
     for (int q = 0; q < KK_MAX; ++q) { bv[q] = __int_as_float(0x7f800000); bi[q] = 0x7fffffff; }
 
+    float dmax = 0.f;  // largest squared distance of the row: the range of the distance embedding (K2c)
     for (int j = lane; j < n; j += 32) {
         const float4 pj = __ldg(base + j);
         const float d = sqdist_ref(pi, pj);
+        dmax = fmaxf(dmax, d);
         // strict '<' against the current worst kept candidate: j only grows within a lane, so equal values
         // keep the smaller index first
         bool worse_or_equal = true;
@@ -64,6 +69,10 @@ knn_kernel(const float4* __restrict__ pts4, int n, int k, int rows_total,
             }
         }
     }
+
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, off));
+    if (lane == 0) atomicMax(dmax2_bits, __float_as_uint(dmax));  // d >= 0: the bit patterns order like the values
 
     // warp merge: pop the global minimum k+1 times; rank 0 is dropped (geotransformer.py:42 "[:, :, 1:]")
     for (int r = 0; r < kk; ++r) {
@@ -118,7 +127,7 @@ using namespace geotx;
 
 extern "C" int64_t geotx_gse_geometry_bytes(int B, int n, int k) {
     if (B <= 0 || n <= 0 || k <= 0) return 0;
-    return (int64_t)16 * B * n * (1 + (int64_t)k);
+    return (int64_t)16 * B * n * (1 + (int64_t)k) + 16;  // + the largest squared distance (one word, 16-byte slot)
 }
 
 extern "C" int geotx_gse_knn(const float* points, int B, int n, int k, int64_t* knn_out, void* geometry,
@@ -133,9 +142,10 @@ extern "C" int geotx_gse_knn(const float* points, int B, int n, int k, int64_t* 
     float4* pts4 = (float4*)geometry;
     float4* refv = pts4 + (size_t)B * n;
     int total = B * n;
-    pack_points_kernel<<<(total + 255) / 256, 256, 0, st>>>(points, pts4, total);
+    unsigned int* dmax2_bits = (unsigned int*)(refv + (size_t)total * k);
+    pack_points_kernel<<<(total + 255) / 256, 256, 0, st>>>(points, pts4, total, dmax2_bits);
     knn_kernel<<<(total + KNN_WARPS - 1) / KNN_WARPS, KNN_WARPS * 32, 0, st>>>(
-        pts4, n, k, total, (long long*)knn_out, refv);
+        pts4, n, k, total, (long long*)knn_out, refv, dmax2_bits);
     return launch_status("geotx_gse_knn");
 }
 

@@ -1,0 +1,596 @@
+// K2c: GeometricStructureEmbedding as a LOW-RANK contraction (the default embedding kernel).
+//
+// geotransformer.py:57-72 computes E[i,j,:] = proj_d(sinus(d_ij)) + reduce_k proj_a(sinus(a_ijk)).  Per output channel
+// c, proj_x(sinus(x))[c] is a function of ONE scalar (positional_embedding.py:28-31 followed by a Linear):
+//     f_c(x) = sum_t W[c,2t] sin(x div_t) + W[c,2t+1] cos(x div_t),      0 < div_t <= 1,
+// i.e. band-limited (highest frequency 1 rad per index unit) on a bounded interval [0, L] (angles: L = pi * factor_a
+// = 12 index units for sigma_a = 15; distances: L = the cloud's largest distance / sigma_d).  Such a function has a
+// Chebyshev expansion of length K ~ L/2 + 12 that is exact to ~1e-6 of sum_t |W[c,t]| (the coefficients decay like the
+// Bessel functions J_m(L/2)): K = 16 covers L <= 13, 32 -> 37, 48 -> 64, 64 -> 93, 96 -> 150, 128 -> 210.  So
+//     f_c(x) = sum_{m<K} G[m,c] T_m(2x/L - 1)          (G: K x C, built once per weight set in fp64)
+// and the (n^2 (1+k)) x C x C contraction of the reference (K2, k2_gse_embed.cu: 524 kflop per pair) becomes a
+// (n^2 (1+k)) x C x K one with K = 16 per angle slot and 32-48 for the distance: 41-49 kflop per pair.  Unlike a
+// sampled table (K2t, k2_gse_embed_table.cu) the truncation error does not depend on the size of the weights (it is
+// relative to them, and is measured in fp64 when the coefficients are built), and any angle_k and both reductions are
+// covered ('mean' is linear: the slots' basis vectors are averaged before the contraction).
+//
+// The kernel: a CTA of 8 warps walks tiles of 128 consecutive (i,j) pairs.  Per tile
+//   produce  two threads per pair (in different warps) compute the pair's k+1 arguments (same arithmetic as get_embedding_indices,
+//            geotx_common.cuh), run the three-term recurrence T_{m+1} = 2t T_m - T_{m-1} in fp32 and store the basis
+//            values as IEEE half into a shared-memory A tile [128 pairs][16 (slots + distance tiles)] (double-buffered,
+//            row pitch = 16 (mod 32) bytes: conflict-free for ldmatrix);
+//   consume  warp w owns 32 output channels.  Its B operand (G for those channels, <= 40 registers) never leaves the
+//            register file.  Per 16 pairs: one ldmatrix.x4 + 4 mma.sync.m16n8k16 (f16 x f16 -> f32) per angle slot, a
+//            running max over the slots in registers (geotransformer.py:66), then the distance tiles accumulate ON TOP
+//            of that max (:70; the biases b_d + b_a ride in G_d[0], T_0 = 1), one convert, and each thread stores 16
+//            contiguous bytes of E per row (the channel <-> fragment-column assignment is chosen so that a thread's 8
+//            accumulator columns are 8 consecutive channels).
+// Nothing of size n x n x k x C exists; shared memory carries 160 B per pair instead of K2t's 5 KB of table reads and
+// the accumulators are never read back from TMEM (K2's epilogue moves 4 KB per pair at TMEM's 64 B/clk).
+// The distance range is not known on the host without a synchronisation: geotx_gse_knn leaves the largest squared
+// distance of the cloud behind the geometry scratch, and the kernel picks the coefficient set (K_d) from it.
+#include <cuda_fp16.h>
+#include "geotx_common.cuh"
+#include "host_util.h"
+
+namespace geotx {
+
+constexpr int CHEB_THREADS = 256;
+constexpr int CHEB_TILE = 128;                 // pairs per tile
+constexpr int CHEB_NUM_D_SETS = 6;
+__host__ __device__ constexpr int cheb_kd_tiles(int s) { return s == 0 ? 1 : s == 1 ? 2 : s == 2 ? 3 : s == 3 ? 4 : s == 4 ? 6 : 8; }
+// largest argument the set is built for (tail of the expansion of a unit sinusoid <= 1e-5, see the header)
+__host__ __device__ constexpr float cheb_range(int s) {
+    return s == 0 ? 13.f : s == 1 ? 37.f : s == 2 ? 64.f : s == 3 ? 93.f : s == 4 ? 150.f : 210.f;
+}
+constexpr int CHEB_BUILD_NODES = 256;          // Gauss-Chebyshev nodes of the coefficient quadrature (> 2 K_max)
+constexpr int CHEB_STATS_PER_SET = 4;          // max |error|, max |f|, max |G|, unused
+
+// halves of one coefficient set in the register-image layout [ktile][C/32][4 n-tiles][32 lanes][2 regs][2 halves]
+__host__ __device__ constexpr size_t cheb_set_halves(int C, int ktiles) { return (size_t)ktiles * C * 16; }
+
+__host__ inline size_t cheb_set_offset(int C, int ka_tiles, int set /* 0 = angle, 1.. = distance sets */) {
+    size_t off = 0;
+    if (set >= 1) off += cheb_set_halves(C, ka_tiles);
+    for (int s = 1; s < set; ++s) off += cheb_set_halves(C, cheb_kd_tiles(s - 1));
+    return off;  // in halves
+}
+
+// ---- coefficient build (once per weight set) ------------------------------------------------------------------------
+// One block per output channel.  F_q = f_c(x_q) at the Gauss-Chebyshev nodes in fp64, G_m = (2/M) sum_q F_q cos(m theta_q)
+// (discrete orthogonality: exact for the interpolant of degree M-1, of which the first K terms are kept), rounded to
+// half and scattered into the mma B-fragment register image.  Then the half-rounded expansion is compared with f_c at
+// M points between the nodes (both ends included): the largest deviation, the largest |f| and the largest |G| go to
+// stats (atomicMax on the bit patterns of non-negative floats), which the host reads once per weight set.
+__global__ void __launch_bounds__(CHEB_BUILD_NODES)
+cheb_build_kernel(const float* __restrict__ div_term, const float* __restrict__ w, const float* __restrict__ bias0,
+                  const float* __restrict__ bias1, int C, float L, int K, __half* __restrict__ frag,
+                  unsigned int* __restrict__ stats) {
+    __shared__ double F[CHEB_BUILD_NODES];
+    __shared__ double Gh[128];
+    __shared__ float red[3][CHEB_BUILD_NODES / 32];
+    const int c = blockIdx.x, q = threadIdx.x;
+    constexpr int M = CHEB_BUILD_NODES;
+    const double bias = (bias0 ? (double)bias0[c] : 0.0) + (bias1 ? (double)bias1[c] : 0.0);
+    auto f = [&](double x) {
+        double acc = bias;
+        for (int t = 0; t < C / 2; ++t) {
+            double sn, cs;
+            sincos(x * (double)div_term[t], &sn, &cs);
+            acc += (double)w[(size_t)c * C + 2 * t] * sn + (double)w[(size_t)c * C + 2 * t + 1] * cs;
+        }
+        return acc;
+    };
+    F[q] = f((cospi((q + 0.5) / M) + 1.0) * 0.5 * (double)L);
+    __syncthreads();
+    float gmax = 0.f;
+    if (q < K) {
+        double acc = 0.0;
+        for (int j = 0; j < M; ++j) acc += F[j] * cospi((double)q * (j + 0.5) / M);
+        acc *= (q == 0 ? 1.0 : 2.0) / M;
+        const __half h = __double2half(acc);
+        Gh[q] = (double)__half2float(h);
+        gmax = fabsf((float)acc);
+        // fragment image: channel c = 32 cb + 8 qq + 2 t + e  <->  n-tile t, B column n = 2 qq + e;  row kk = q % 16 of
+        // k-tile q / 16 lives in lane n * 4 + (kk % 8) / 2, register kk / 8, half kk & 1
+        const int cb = c >> 5, cc = c & 31, qq = cc >> 3, t = (cc & 7) >> 1, e = cc & 1, n = 2 * qq + e;
+        const int kt = q >> 4, kk = q & 15, lane = n * 4 + ((kk & 7) >> 1), reg = kk >> 3, hi = kk & 1;
+        frag[((((size_t)kt * (C / 32) + cb) * 4 + t) * 32 + lane) * 4 + reg * 2 + hi] = h;
+    }
+    __syncthreads();
+    // check at theta = q pi / (M - 1): q = 0 is x = L, q = M - 1 is x = 0
+    const double th = (double)q / (M - 1);
+    const double exact = f((cospi(th) + 1.0) * 0.5 * (double)L);
+    double approx = 0.0;
+    for (int m = 0; m < K; ++m) approx += Gh[m] * cospi(m * th);
+    float err = (float)fabs(approx - exact), fmx = (float)fabs(exact);
+    for (int off = 16; off > 0; off >>= 1) {
+        err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, off));
+        fmx = fmaxf(fmx, __shfl_xor_sync(0xffffffffu, fmx, off));
+        gmax = fmaxf(gmax, __shfl_xor_sync(0xffffffffu, gmax, off));
+    }
+    if ((q & 31) == 0) { red[0][q >> 5] = err; red[1][q >> 5] = fmx; red[2][q >> 5] = gmax; }
+    __syncthreads();
+    if (q < 3) {
+        float v = 0.f;
+        for (int i = 0; i < M / 32; ++i) v = fmaxf(v, red[q][i]);
+        atomicMax(stats + q, __float_as_uint(v));
+    }
+}
+
+// ---- the embedding kernel -------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ldsm4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+// d = a b (fresh accumulator)
+__device__ __forceinline__ void mma_new(float (&d)[4], const uint32_t (&a)[4], const uint2& b) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "f"(0.f));
+}
+// d += a b
+__device__ __forceinline__ void mma_acc(float (&d)[4], const uint32_t (&a)[4], const uint2& b) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+}
+__device__ __forceinline__ uint32_t pack_half2(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ void st_na_v4(void* p, const uint4& v) {
+    asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// 16 * TILES Chebyshev values of t (T_0 = 1, T_1 = t, T_{m+1} = 2 t T_m - T_{m-1}) as halves, to smem at `addr`
+template <int TILES>
+__device__ __forceinline__ void cheb_store(uint32_t addr, float t) {
+    const float t2 = t + t;
+    float a = 1.f, b = t;  // T_m, T_{m+1}
+#pragma unroll
+    for (int blk = 0; blk < 2 * TILES; ++blk) {
+        uint32_t w[4];
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+            w[h] = pack_half2(a, b);
+            a = fmaf(t2, b, -a);
+            b = fmaf(t2, a, -b);
+        }
+        sts_v4(addr + blk * 16, make_uint4(w[0], w[1], w[2], w[3]));
+    }
+}
+// the same, accumulated in registers (for the 'mean' reduction): acc[m] += scale * T_m(t)
+template <int TILES>
+__device__ __forceinline__ void cheb_accumulate(float (&acc)[16 * TILES], float t, float scale) {
+    const float t2 = t + t;
+    float a = scale, b = t * scale;
+#pragma unroll
+    for (int m = 0; m < 16 * TILES; m += 2) {
+        acc[m] += a;
+        acc[m + 1] += b;
+        a = fmaf(t2, b, -a);
+        b = fmaf(t2, a, -b);
+    }
+}
+
+struct ChebArgs {
+    const float4* pts4;
+    const float4* refv;
+    const unsigned int* dmax2_bits;  // largest squared distance of the clouds (geotx_gse_knn)
+    const __half* coef;              // angle set, then the distance sets
+    void* out;                       // E (f16 / bf16), or scores_p (f32) in the scores mode
+    int* overflow;
+    long long pairs_total;           // E mode: pairs of the slab, flattened
+    long long tiles;
+    int n, k, slots, reduce_mean, row_begin, row_count, out_bf16, max_d_set;
+    float sigma_d, factor_a, inv_half_la;  // 2 / L_a
+    unsigned int d_set_offset[CHEB_NUM_D_SETS];  // halves from coef to distance set s
+    // scores mode (K3r): folded query qt[b,h,i,c] with element strides, H heads, key blocks per row
+    const float* qt;
+    long long qsb, qsh, qsn;
+    int H, key_blocks;
+};
+
+// saturating hi / lo split of two floats into halves (the folded query enters the score contraction as hi + lo, like
+// geotx_rpe_scores, so that only E carries a 16-bit rounding)
+__device__ __forceinline__ void cheb_split(float x, float y, uint32_t& hi, uint32_t& lo) {
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(y), "f"(x));
+    const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(y - hf.y), "f"(x - hf.x));
+}
+
+// SCORES = false: E of the slab is written (geotx_gse_embed_cheb); tiles are 128 consecutive flattened pairs.
+// SCORES = true (K3r, geotx_rpe_scores_cheb): E never leaves the registers.  A tile is 128 consecutive keys j of ONE
+// query row (b, i); the finished accumulators (rounded to half, exactly what the stored E would hold) become the A
+// operand of a second contraction with that row's folded query (B operand: channels x heads, hi + lo halves), each
+// warp producing the partial scores of its 32 channels; the 8 partials meet in shared memory and the tile's
+// H x 128 scores are written as 512-byte rows of scores_p.
+template <int C, int KA, int KD, bool SCORES>
+__device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned char* smem) {
+    constexpr int NCB = C / 32;                 // 32-channel blocks = warps sharing a pair group
+    constexpr int MT_PER_WARP = NCB;            // 8 m-tiles of 16 pairs / (8 / NCB) pair groups
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cb = warp % NCB, mt0 = (warp / NCB) * MT_PER_WARP;
+    const int slots = p.slots;
+    const int ktot = slots * 16 * KA + 16 * KD;  // halves per A row
+    const uint32_t pitch = ktot * 2 + 16;         // bytes: = 16 (mod 32), ldmatrix rows fall into distinct banks
+    const uint32_t a_base = smem_u32(smem);
+    const uint32_t buf_bytes = CHEB_TILE * pitch;
+    // scores mode: partial[2][NCB][hp][128] floats behind the two A tiles
+    const int hp = p.H <= 4 ? 4 : 8;
+    float* const partial = reinterpret_cast<float*>(smem + 2 * buf_bytes);
+    const int partial_floats = NCB * hp * CHEB_TILE;
+
+    // B operand: this warp's 32 channels of G, register-resident for the whole kernel
+    uint2 b_a[KA][4], b_d[KD][4];
+    {
+        const uint2* src = reinterpret_cast<const uint2*>(p.coef);
+#pragma unroll
+        for (int kt = 0; kt < KA; ++kt)
+#pragma unroll
+            for (int t = 0; t < 4; ++t) b_a[kt][t] = __ldg(src + ((kt * NCB + cb) * 4 + t) * 32 + lane);
+        src = reinterpret_cast<const uint2*>(p.coef + p.d_set_offset[d_set]);
+#pragma unroll
+        for (int kt = 0; kt < KD; ++kt)
+#pragma unroll
+            for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(src + ((kt * NCB + cb) * 4 + t) * 32 + lane);
+    }
+    const float inv_half_ld = 2.f / cheb_range(d_set);
+    const float x_lim_d = cheb_range(d_set) * 1.0001f, x_lim_a = 2.0002f / p.inv_half_la;
+    const long long per_b = (long long)p.row_count * p.n;
+    const long long tiles = p.tiles;
+    bool clamped = false;
+
+    // producer role (warp-uniform): warps 0-3 take the first half of the angle slots of pair tid, warps 4-7 the rest and
+    // the distance of pair tid - 128
+    const int ppair = tid & (CHEB_TILE - 1), prole = tid >> 7;
+    const int s_split = (slots + 1) >> 1;
+    const int s_begin = prole ? s_split : 0, s_end = prole ? slots : s_split;
+
+    // tile -> (cloud b, query row i, first key j0); E mode: of the tile's pair `local`
+    auto locate = [&](long long tile, int local, long long& b, int& i, int& j) {
+        if (SCORES) {
+            const long long row = tile / p.key_blocks;
+            b = row / p.row_count;
+            i = p.row_begin + (int)(row - b * p.row_count);
+            j = min((int)(tile - row * p.key_blocks) * CHEB_TILE + local, p.n - 1);
+        } else {
+            const long long g = min(tile * CHEB_TILE + local, p.pairs_total - 1);
+            b = g / per_b;
+            const long long rem = g - b * per_b;
+            i = p.row_begin + (int)(rem / p.n);
+            j = (int)(rem % p.n);
+        }
+    };
+
+    auto produce = [&](long long tile, int buf) {
+        long long b;
+        int i, j;
+        locate(tile, ppair, b, i, j);
+        const float4 pi = __ldg(p.pts4 + b * p.n + i), pj = __ldg(p.pts4 + b * p.n + j);
+        const float4* refv_i = p.refv + (b * p.n + i) * p.k;
+        const uint32_t row = a_base + buf * buf_bytes + ppair * pitch;
+        if (!p.reduce_mean) {
+            for (int s = s_begin; s < s_end; ++s) {
+                const float x = pair_argument_one(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
+                clamped |= !(x <= x_lim_a);
+                cheb_store<KA>(row + s * (32 * KA), fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f));
+            }
+        } else if (!prole) {  // geotransformer.py:68: the mean over the k neighbours is linear in the basis
+            float acc[16 * KA];
+#pragma unroll
+            for (int m = 0; m < 16 * KA; ++m) acc[m] = 0.f;
+            const float scale = 1.f / (float)p.k;
+            for (int s = 0; s < p.k; ++s) {
+                const float x = pair_argument_one(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
+                clamped |= !(x <= x_lim_a);
+                cheb_accumulate<KA>(acc, fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f), scale);
+            }
+#pragma unroll
+            for (int blk = 0; blk < 2 * KA; ++blk)
+                sts_v4(row + blk * 16, make_uint4(pack_half2(acc[8 * blk], acc[8 * blk + 1]), pack_half2(acc[8 * blk + 2], acc[8 * blk + 3]),
+                                                  pack_half2(acc[8 * blk + 4], acc[8 * blk + 5]), pack_half2(acc[8 * blk + 6], acc[8 * blk + 7])));
+        }
+        if (prole) {
+            const float x = pair_argument_one(pi, pj, refv_i, p.k, p.k, p.sigma_d, p.factor_a);
+            clamped |= !(x <= x_lim_d);
+            cheb_store<KD>(row + slots * (32 * KA), fminf(fmaxf(fmaf(x, inv_half_ld, -1.f), -1.f), 1.f));
+        }
+    };
+
+    // ldmatrix: lane l addresses row (l & 15) of the m-tile, columns 8 (l >> 4) ..; mma: g = lane / 4 is the fragment
+    // row, q = lane % 4 the column pair
+    const uint32_t ld_off = (lane & 15) * pitch + (lane >> 4) * 16;
+    const int g = lane >> 2, q = lane & 3;
+    unsigned char* const out_bytes = reinterpret_cast<unsigned char*>(p.out);
+
+    // scores mode: B fragments of the folded query of a tile's row.  Fragment column n = g is the head; thread (g, q)
+    // holds the 8 consecutive channels 32 cb + 8 q .. + 7 (the same channel <-> k-slot assignment as the accumulators
+    // that become the A operand: n-tiles 2 kt2, 2 kt2 + 1 form k-tile kt2)
+    uint32_t q_hi[2][2], q_lo[2][2];
+    auto load_query = [&](long long tile) {
+        long long b;
+        int i, j;
+        locate(tile, 0, b, i, j);
+        float f[8];
+        if (g < p.H) {
+            const float* src = p.qt + b * p.qsb + (long long)g * p.qsh + (long long)i * p.qsn + cb * 32 + q * 8;
+            const float4 u = __ldg(reinterpret_cast<const float4*>(src)), v = __ldg(reinterpret_cast<const float4*>(src + 4));
+            f[0] = u.x; f[1] = u.y; f[2] = u.z; f[3] = u.w; f[4] = v.x; f[5] = v.y; f[6] = v.z; f[7] = v.w;
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = 0.f;
+        }
+#pragma unroll
+        for (int kt2 = 0; kt2 < 2; ++kt2)
+#pragma unroll
+            for (int r = 0; r < 2; ++r) cheb_split(f[4 * kt2 + 2 * r], f[4 * kt2 + 2 * r + 1], q_hi[kt2][r], q_lo[kt2][r]);
+    };
+
+    auto consume = [&](long long tile, int buf) {
+        const uint32_t tile_addr = a_base + buf * buf_bytes + ld_off;
+        const long long pair0 = tile * CHEB_TILE;
+        if (SCORES) load_query(tile);
+#pragma unroll 1
+        for (int mi = 0; mi < MT_PER_WARP; ++mi) {
+            const int mt = mt0 + mi;
+            uint32_t addr = tile_addr + mt * 16 * pitch;
+            float best[4][4];
+            uint32_t a[4];
+            for (int s = 0; s < slots; ++s) {
+                float cur[4][4];
+#pragma unroll
+                for (int kt = 0; kt < KA; ++kt) {
+                    ldsm4(a, addr);
+                    addr += 32;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        if (kt == 0) mma_new(cur[t], a, b_a[kt][t]);
+                        else mma_acc(cur[t], a, b_a[kt][t]);
+                    }
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) best[t][r] = s == 0 ? cur[t][r] : fmaxf(best[t][r], cur[t][r]);
+            }
+#pragma unroll
+            for (int kt = 0; kt < KD; ++kt) {
+                ldsm4(a, addr);
+                addr += 32;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) mma_acc(best[t], a, b_d[kt][t]);
+            }
+            if (SCORES) {
+                // E (rounded to half like the stored E) x folded query: rows = the m-tile's 16 keys, columns = heads
+                float sc[4];
+#pragma unroll
+                for (int kt2 = 0; kt2 < 2; ++kt2) {
+                    const uint32_t ea[4] = {pack_half2(best[2 * kt2][0], best[2 * kt2][1]), pack_half2(best[2 * kt2][2], best[2 * kt2][3]),
+                                            pack_half2(best[2 * kt2 + 1][0], best[2 * kt2 + 1][1]),
+                                            pack_half2(best[2 * kt2 + 1][2], best[2 * kt2 + 1][3])};
+                    if (kt2 == 0) mma_new(sc, ea, make_uint2(q_hi[0][0], q_hi[0][1]));
+                    else mma_acc(sc, ea, make_uint2(q_hi[1][0], q_hi[1][1]));
+                    mma_acc(sc, ea, make_uint2(q_lo[kt2][0], q_lo[kt2][1]));
+                }
+                // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
+                if (2 * q < hp) {
+                    float* dst = partial + (buf * NCB + cb) * hp * CHEB_TILE + (2 * q) * CHEB_TILE + mt * 16 + g;
+                    dst[0] = sc[0];
+                    dst[CHEB_TILE] = sc[1];
+                    dst[8] = sc[2];
+                    dst[CHEB_TILE + 8] = sc[3];
+                }
+            } else {
+                // thread (g, q): rows g and g + 8 of the m-tile, channels 32 cb + 8 q .. + 7 (n-tile t holds 2 t, 2 t + 1)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const long long pair = pair0 + mt * 16 + g + 8 * h;
+                    if (pair < p.pairs_total) {
+                        uint4 o;
+                        if (!p.out_bf16) {
+                            o = make_uint4(pack_half2(best[0][2 * h], best[0][2 * h + 1]), pack_half2(best[1][2 * h], best[1][2 * h + 1]),
+                                           pack_half2(best[2][2 * h], best[2][2 * h + 1]), pack_half2(best[3][2 * h], best[3][2 * h + 1]));
+                        } else {
+                            o = make_uint4(pack_bf16x2(best[0][2 * h], best[0][2 * h + 1]), pack_bf16x2(best[1][2 * h], best[1][2 * h + 1]),
+                                           pack_bf16x2(best[2][2 * h], best[2][2 * h + 1]), pack_bf16x2(best[3][2 * h], best[3][2 * h + 1]));
+                        }
+                        st_na_v4(out_bytes + ((size_t)pair * C + cb * 32 + q * 8) * 2, o);
+                    }
+                }
+            }
+        }
+    };
+
+    // scores mode: the 8 channel blocks' partial scores of a finished tile -> scores_p[b, h, i, j0 .. j0 + 127]
+    auto reduce = [&](long long tile, int buf) {
+        long long b;
+        int i, j0;
+        locate(tile, 0, b, i, j0);
+        const float* src = partial + buf * partial_floats;
+        float* const out = reinterpret_cast<float*>(p.out);
+        for (int e = tid; e < p.H * CHEB_TILE; e += CHEB_THREADS) {
+            const int h = e >> 7, jl = e & (CHEB_TILE - 1);
+            float v = 0.f;
+#pragma unroll
+            for (int w = 0; w < NCB; ++w) v += src[(w * hp + h) * CHEB_TILE + jl];
+            if (j0 + jl < p.n) out[(((size_t)b * p.H + h) * p.n + i) * p.n + j0 + jl] = v;
+        }
+    };
+
+    long long tile = blockIdx.x;
+    int buf = 0;
+    if (tile < tiles) produce(tile, 0);
+    __syncthreads();
+    for (; tile < tiles; tile += gridDim.x) {
+        const long long next = tile + gridDim.x;
+        if (next < tiles) produce(next, buf ^ 1);
+        consume(tile, buf);
+        __syncthreads();
+        if (SCORES) reduce(tile, buf);  // reads partial[buf]; the next writer of partial[buf] is two barriers away
+        buf ^= 1;
+    }
+    if (clamped) *p.overflow = 1;
+}
+
+template <int C, int KA, bool SCORES>
+__global__ void __launch_bounds__(CHEB_THREADS, 2) gse_embed_cheb_kernel(const ChebArgs p) {
+    extern __shared__ __align__(16) unsigned char cheb_smem[];
+    // the coefficient set of the distance term: the shortest expansion that covers the clouds' largest distance
+    const float x_max = __fdiv_rn(__fsqrt_rn(__uint_as_float(__ldg(p.dmax2_bits))), p.sigma_d);
+    int d_set = 0;
+    while (d_set < p.max_d_set && x_max > cheb_range(d_set)) ++d_set;
+    switch (d_set) {
+        case 0: cheb_run<C, KA, 1, SCORES>(p, 0, cheb_smem); break;
+        case 1: cheb_run<C, KA, 2, SCORES>(p, 1, cheb_smem); break;
+        case 2: cheb_run<C, KA, 3, SCORES>(p, 2, cheb_smem); break;
+        case 3: cheb_run<C, KA, 4, SCORES>(p, 3, cheb_smem); break;
+        case 4: cheb_run<C, KA, 6, SCORES>(p, 4, cheb_smem); break;
+        default: cheb_run<C, KA, 8, SCORES>(p, 5, cheb_smem); break;
+    }
+}
+
+}  // namespace geotx
+
+using namespace geotx;
+
+static bool cheb_shape_ok(int C, int ka_tiles) { return (C == 256 || C == 128) && (ka_tiles == 1 || ka_tiles == 2); }
+
+extern "C" int geotx_gse_cheb_ka_tiles(float angle_index_max) {
+    if (!(angle_index_max > 0.f)) return 0;
+    if (angle_index_max <= cheb_range(0)) return 1;
+    if (angle_index_max <= cheb_range(1)) return 2;
+    return 0;
+}
+
+extern "C" float geotx_gse_cheb_d_range(int d_set) {
+    return d_set >= 0 && d_set < CHEB_NUM_D_SETS ? cheb_range(d_set) : 0.f;
+}
+
+extern "C" int64_t geotx_gse_cheb_bytes(int C, int ka_tiles) {
+    if (!cheb_shape_ok(C, ka_tiles)) return 0;
+    return (int64_t)cheb_set_offset(C, ka_tiles, 1 + CHEB_NUM_D_SETS) * 2;
+}
+
+extern "C" int geotx_gse_build_cheb(const float* div_term, const float* w_d, const float* b_d, const float* w_a,
+                                    const float* b_a, int C, float angle_index_max, int ka_tiles, void* coef,
+                                    float* stats, void* stream) {
+    GEOTX_REQUIRE(div_term && w_d && b_d && w_a && b_a && coef && stats, "geotx_gse_build_cheb: null pointer");
+    GEOTX_REQUIRE(cheb_shape_ok(C, ka_tiles), "geotx_gse_build_cheb: C must be 128 or 256, ka_tiles 1 or 2");
+    GEOTX_REQUIRE(angle_index_max > 0.f && angle_index_max <= cheb_range(ka_tiles - 1),
+                  "geotx_gse_build_cheb: angle range %g is not covered by %d coefficients", angle_index_max, 16 * ka_tiles);
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = check_cuda(cudaMemsetAsync(stats, 0, sizeof(float) * CHEB_STATS_PER_SET * (1 + CHEB_NUM_D_SETS), st),
+                        "geotx_gse_build_cheb: memset");
+    if (rc) return rc;
+    __half* base = (__half*)coef;
+    // the angle term carries no bias: max over the slots commutes with adding b_a, which rides with b_d in G_d[0]
+    cheb_build_kernel<<<C, CHEB_BUILD_NODES, 0, st>>>(div_term, w_a, nullptr, nullptr, C, angle_index_max, 16 * ka_tiles,
+                                                     base, (unsigned int*)stats);
+    for (int s = 0; s < CHEB_NUM_D_SETS; ++s)
+        cheb_build_kernel<<<C, CHEB_BUILD_NODES, 0, st>>>(div_term, w_d, b_d, b_a, C, cheb_range(s), 16 * cheb_kd_tiles(s),
+                                                         base + cheb_set_offset(C, ka_tiles, 1 + s),
+                                                         (unsigned int*)stats + CHEB_STATS_PER_SET * (1 + s));
+    return launch_status("geotx_gse_build_cheb");
+}
+
+// shared launcher: E mode (scores == nullptr) or scores mode
+static int cheb_launch(const char* what, const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                       const void* coef, int C, float angle_index_max, int ka_tiles, int max_d_set, float sigma_d,
+                       float factor_a, int reduce_mean, int out_dtype, void* out, const float* qt, int64_t qsb,
+                       int64_t qsh, int64_t qsn, int H, int32_t* overflow, void* stream) {
+    const bool scores = qt != nullptr;
+    ChebArgs p;
+    p.pts4 = (const float4*)geometry;
+    p.refv = p.pts4 + (size_t)B * n;
+    p.dmax2_bits = (const unsigned int*)(p.refv + (size_t)B * n * k);
+    p.coef = (const __half*)coef;
+    p.out = out;
+    p.overflow = overflow;
+    p.pairs_total = (long long)B * row_count * n;
+    p.n = n;
+    p.k = k;
+    p.slots = reduce_mean ? 1 : k;
+    p.reduce_mean = reduce_mean;
+    p.row_begin = row_begin;
+    p.row_count = row_count;
+    p.out_bf16 = out_dtype == GEOTX_BF16;
+    p.max_d_set = max_d_set;
+    p.sigma_d = sigma_d;
+    p.factor_a = factor_a;
+    p.inv_half_la = 2.f / angle_index_max;
+    for (int s = 0; s < CHEB_NUM_D_SETS; ++s) p.d_set_offset[s] = (unsigned int)cheb_set_offset(C, ka_tiles, 1 + s);
+    p.qt = qt;
+    p.qsb = qsb;
+    p.qsh = qsh;
+    p.qsn = qsn;
+    p.H = H;
+    p.key_blocks = (n + CHEB_TILE - 1) / CHEB_TILE;
+    p.tiles = scores ? (long long)B * row_count * p.key_blocks : (p.pairs_total + CHEB_TILE - 1) / CHEB_TILE;
+    const int ktot_max = p.slots * 16 * ka_tiles + 16 * cheb_kd_tiles(max_d_set);
+    size_t smem = (size_t)2 * CHEB_TILE * (ktot_max * 2 + 16);
+    if (scores) smem += (size_t)2 * (C / 32) * (H <= 4 ? 4 : 8) * CHEB_TILE * sizeof(float);
+    GEOTX_REQUIRE(smem <= 220 * 1024, "%s: %zu B of shared memory (k=%d, max_d_set=%d) do not fit", what, smem, k, max_d_set);
+    int dev = 0, sms = 0;
+    int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+    if (rc) return rc;
+    rc = check_cuda(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
+    if (rc) return rc;
+    const int per_sm = smem <= 110 * 1024 ? 2 : 1;
+    const int grid = (int)std::min<long long>(p.tiles, (long long)sms * per_sm);
+    auto launch = [&](auto kernel) -> int {
+        int r = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), what);
+        if (r) return r;
+        kernel<<<grid, CHEB_THREADS, smem, (cudaStream_t)stream>>>(p);
+        return 0;
+    };
+    if (scores) {
+        if (C == 256) rc = ka_tiles == 1 ? launch(gse_embed_cheb_kernel<256, 1, true>) : launch(gse_embed_cheb_kernel<256, 2, true>);
+        else rc = ka_tiles == 1 ? launch(gse_embed_cheb_kernel<128, 1, true>) : launch(gse_embed_cheb_kernel<128, 2, true>);
+    } else {
+        if (C == 256) rc = ka_tiles == 1 ? launch(gse_embed_cheb_kernel<256, 1, false>) : launch(gse_embed_cheb_kernel<256, 2, false>);
+        else rc = ka_tiles == 1 ? launch(gse_embed_cheb_kernel<128, 1, false>) : launch(gse_embed_cheb_kernel<128, 2, false>);
+    }
+    if (rc) return rc;
+    return launch_status(what);
+}
+
+extern "C" int geotx_gse_embed_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                                    const void* coef, int C, float angle_index_max, int ka_tiles, int max_d_set,
+                                    float sigma_d, float factor_a, int reduce_mean, int out_dtype, void* out,
+                                    int32_t* overflow, void* stream) {
+    GEOTX_REQUIRE(geometry && coef && out && overflow, "geotx_gse_embed_cheb: null pointer");
+    GEOTX_REQUIRE(B > 0 && n > 0 && k >= 1 && k <= GEOTX_MAX_ANGLE_K, "geotx_gse_embed_cheb: bad sizes (B=%d n=%d k=%d)", B, n, k);
+    GEOTX_REQUIRE(cheb_shape_ok(C, ka_tiles), "geotx_gse_embed_cheb: C must be 128 or 256, ka_tiles 1 or 2");
+    GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_gse_embed_cheb: bad row slab");
+    GEOTX_REQUIRE(out_dtype == GEOTX_F16 || out_dtype == GEOTX_BF16, "geotx_gse_embed_cheb: out_dtype must be f16 or bf16");
+    GEOTX_REQUIRE(max_d_set >= 0 && max_d_set < CHEB_NUM_D_SETS, "geotx_gse_embed_cheb: max_d_set outside [0,%d)", CHEB_NUM_D_SETS);
+    GEOTX_REQUIRE(angle_index_max > 0.f && sigma_d > 0.f, "geotx_gse_embed_cheb: bad scales");
+    return cheb_launch("geotx_gse_embed_cheb", geometry, B, n, k, row_begin, row_count, coef, C, angle_index_max, ka_tiles,
+                       max_d_set, sigma_d, factor_a, reduce_mean, out_dtype, out, nullptr, 0, 0, 0, 0, overflow, stream);
+}
+
+extern "C" int geotx_rpe_scores_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count,
+                                     const void* coef, int C, float angle_index_max, int ka_tiles, int max_d_set,
+                                     float sigma_d, float factor_a, int reduce_mean, const float* qt,
+                                     int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n, int H,
+                                     float* scores_p, int32_t* overflow, void* stream) {
+    GEOTX_REQUIRE(geometry && coef && qt && scores_p && overflow, "geotx_rpe_scores_cheb: null pointer");
+    GEOTX_REQUIRE(B > 0 && n > 0 && k >= 1 && k <= GEOTX_MAX_ANGLE_K, "geotx_rpe_scores_cheb: bad sizes (B=%d n=%d k=%d)", B, n, k);
+    GEOTX_REQUIRE(cheb_shape_ok(C, ka_tiles), "geotx_rpe_scores_cheb: C must be 128 or 256, ka_tiles 1 or 2");
+    GEOTX_REQUIRE(row_begin >= 0 && row_count > 0 && row_begin + row_count <= n, "geotx_rpe_scores_cheb: bad row slab");
+    GEOTX_REQUIRE(max_d_set >= 0 && max_d_set < CHEB_NUM_D_SETS, "geotx_rpe_scores_cheb: max_d_set outside [0,%d)", CHEB_NUM_D_SETS);
+    GEOTX_REQUIRE(angle_index_max > 0.f && sigma_d > 0.f, "geotx_rpe_scores_cheb: bad scales");
+    GEOTX_REQUIRE(H >= 1 && H <= 8, "geotx_rpe_scores_cheb: H=%d outside [1,8]", H);
+    GEOTX_REQUIRE(((uintptr_t)qt & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0 && qt_stride_n % 4 == 0,
+                  "geotx_rpe_scores_cheb: qt must be 16-byte aligned with strides that are multiples of 4 elements");
+    return cheb_launch("geotx_rpe_scores_cheb", geometry, B, n, k, row_begin, row_count, coef, C, angle_index_max, ka_tiles,
+                       max_d_set, sigma_d, factor_a, reduce_mean, GEOTX_F16, scores_p, qt, qt_stride_b, qt_stride_h,
+                       qt_stride_n, H, overflow, stream);
+}

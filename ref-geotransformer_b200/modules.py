@@ -10,6 +10,7 @@ The heavy math runs in the sm_100a kernels behind include/geotx_b200.h (see ops.
 (C x C Linears, LayerNorm, ReLU: <0.5 % of the path's flops) are issued through torch on
 the same stream.  Forward-only: calling with autograd enabled on anything that requires grad raises."""
 import math
+import warnings
 import os
 
 import torch
@@ -21,6 +22,23 @@ from . import ops
 # slab of E (bytes) written by the embedding kernel and consumed from L2 by the first block's scores kernel; the
 # B200 L2 is 126 MB.  Measured sweep in DESIGN.md section 5.
 DEFAULT_L2_SLAB_BYTES = 0
+
+
+def _joint_view(a, b):
+    """(1, n+m, C) view over two (1, n, C) / (1, m, C) tensors when b starts where a ends INSIDE ONE storage (two slices
+    of one token buffer); None otherwise.  Comparing data pointers alone is not enough: two separate allocations that
+    the caching allocator happened to place back to back would pass, and as_strided over the first would then run past
+    its storage."""
+    if a.dim() != 3 or b.dim() != 3 or a.shape[0] != 1 or b.shape[0] != 1 or a.shape[2] != b.shape[2]:
+        return None
+    if a.dtype != b.dtype or not a.is_contiguous() or not b.is_contiguous():
+        return None
+    sa, sb = a.untyped_storage(), b.untyped_storage()
+    if sa.data_ptr() != sb.data_ptr() or a.storage_offset() + a.numel() != b.storage_offset():
+        return None
+    if (b.storage_offset() + b.numel()) * a.element_size() > sa.nbytes():
+        return None
+    return torch.as_strided(a, (1, a.shape[1] + b.shape[1], a.shape[2]), a.stride())
 
 _ACTIVATIONS = {  # geotransformer/modules/layers/factory.py:18-27,71-80
     'ReLU': nn.ReLU, 'LeakyReLU': nn.LeakyReLU, 'ELU': nn.ELU, 'GELU': nn.GELU, 'Sigmoid': nn.Sigmoid,
@@ -100,13 +118,17 @@ class SinusoidalPositionalEmbedding(nn.Module):
 
 
 class GeometricStructureEmbedding(nn.Module):
-    """geotransformer.py:9-72.  `precision`: 'bf16' = tcgen05 kernel (hidden_dim 128/256), 'fp32' = CUDA-core
-    kernel (any even hidden_dim); 'auto' picks bf16 when the hidden size allows it.
-    `embed_kernel` (attribute; default from GEOTX_EMBED, 'table'): 'table' makes the half-precision embedding of the
-    shipped shapes (hidden_dim 128 or 256, angle_k 3, 'max') go through the tabulated kernel K2t (twice as fast and
-    closer to fp32 than the bf16 contraction); every other shape, output type and the fused first-block scores take the
-    tcgen05 kernel as with 'tensor'.  `table_d_index_max` is the distance index up to which the table reaches (96 =
-    19 m at sigma_d = 0.2; beyond it the kernel evaluates the function itself, slowly)."""
+    """geotransformer.py:9-72.  `precision`: 'bf16' = 16-bit storage of E through the tensor-core kernels (hidden_dim
+    128/256), 'fp32' = CUDA-core kernel (any even hidden_dim); 'auto' picks the former when the hidden size allows it.
+    `embed_kernel` (attribute; default from GEOTX_EMBED, 'cheb') selects the kernel behind a 16-bit E:
+      'cheb'    K2c, the low-rank (Chebyshev) contraction on mma.sync: any angle_k, 'max' and 'mean', f16 / bf16;
+                its truncation + rounding error is MEASURED against this module's weights when the coefficients are
+                built (`cheb_report()`), and a weight set that misses `cheb_error_budget` falls back to 'tensor' with a
+                warning (never to a CPU path);
+      'table'   K2t, the sampled tables of round 1 (hidden_dim 128/256, angle_k 3, 'max', f16 only);
+      'tensor'  K2, the full-rank tcgen05 contraction (also used for fp32 output and the fused first-block scores).
+    `cheb_d_index_max` caps the distance range K2c is prepared for (210 index units = 42 m at sigma_d = 0.2); the kernel
+    itself picks the shortest expansion that covers the cloud at hand.  `table_d_index_max`: reach of K2t's table."""
 
     def __init__(self, hidden_dim, sigma_d, sigma_a, angle_k, reduction_a='max', precision='auto'):
         super().__init__()
@@ -127,12 +149,18 @@ class GeometricStructureEmbedding(nn.Module):
         self._packed = None
         self._packed_key = None
         self._e_bound = math.inf
-        self.embed_kernel = os.environ.get('GEOTX_EMBED', 'table')
-        if self.embed_kernel not in ('tensor', 'table'):
-            raise ValueError(f"GEOTX_EMBED must be 'tensor' or 'table', got {self.embed_kernel!r}")
+        self.embed_kernel = os.environ.get('GEOTX_EMBED', 'cheb')
+        if self.embed_kernel not in ('tensor', 'table', 'cheb'):
+            raise ValueError(f"GEOTX_EMBED must be 'cheb', 'table' or 'tensor', got {self.embed_kernel!r}")
         self.table_d_index_max = 96.0
         self._tables_cache = None
         self._tables_key = None
+        self.cheb_d_index_max = 210.0
+        self.cheb_error_budget = 2e-3  # largest |expansion - f| over largest |f|, per coefficient set
+        self._cheb_cache = None
+        self._cheb_key = None
+        self._cheb_ok = False
+        self._overflow_checked = set()
 
     def _use_tensor_cores(self):
         ok = self.hidden_dim in (128, 256)
@@ -161,6 +189,49 @@ class GeometricStructureEmbedding(nn.Module):
             self._tables_key = key
         return self._tables_cache
 
+    def _weight_key(self):
+        ts = (self.proj_d.weight, self.proj_d.bias, self.proj_a.weight, self.proj_a.bias, self.embedding.div_term)
+        return tuple((t.data_ptr(), t._version) for t in ts)
+
+    def _cheb(self):
+        """Chebyshev coefficients of the current weights (rebuilt when a weight changes), or None when K2c's measured
+        error on this weight set exceeds `cheb_error_budget` (the caller then takes the tcgen05 kernel)."""
+        key = self._weight_key()
+        if self._cheb_cache is None or key != self._cheb_key:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError('the embedding weights changed since the coefficients of the low-rank embedding '
+                                   'kernel were built; run one forward outside CUDA graph capture first')
+            ts = (self.proj_d.weight, self.proj_d.bias, self.proj_a.weight, self.proj_a.bias)
+            w_d, b_d, w_a, b_a = [t.detach().contiguous() for t in ts]
+            coef = ops.gse_build_cheb(self.embedding.div_term, w_d, b_d, w_a, b_a, self.factor_a)
+            used = [0] + list(range(1, 2 + ops.gse_cheb_max_d_set(self.cheb_d_index_max)))
+            rep = coef.report()
+            bad = [rep[i] for i in used
+                   if not rep[i]['max_error'] <= self.cheb_error_budget * max(rep[i]['max_abs_f'], 1e-30)]
+            self._cheb_ok = not bad
+            if bad:
+                warnings.warn('ref-geotransformer_b200: the low-rank embedding kernel misses its error budget on these '
+                              f'weights ({bad[0]}); using the tcgen05 embedding kernel instead')
+            self._cheb_cache, self._cheb_key = coef, key
+        return self._cheb_cache if self._cheb_ok else None
+
+    def cheb_report(self):
+        """Measured accuracy of K2c's expansions on the current weights (see ops.ChebCoefficients.report)."""
+        self._cheb()
+        return self._cheb_cache.report()
+
+    def _use_cheb(self, out_dtype, qt):
+        return (self.embed_kernel == 'cheb' and self.hidden_dim in (128, 256) and qt is None and
+                out_dtype in (torch.float16, torch.bfloat16) and self.precision != 'fp32' and
+                ops.gse_cheb_ka_tiles(math.pi * self.factor_a * (1.0 + 1e-6)) > 0 and self._cheb() is not None)
+
+    def check_overflow(self):
+        """Raises if an embedding argument ever fell outside the range its kernel was prepared for (synchronises)."""
+        for cache, what in ((self._cheb_cache, 'cheb_d_index_max'), (self._tables_cache, 'the angle table')):
+            if cache is not None and int(cache.overflow.item()) != 0:
+                raise RuntimeError(f'GeometricStructureEmbedding: an argument fell outside {what}; raise '
+                                   f"cheb_d_index_max (<= 210) or set embed_kernel = 'tensor'")
+
     def _use_table(self, out_dtype, qt):
         return (self.embed_kernel == 'table' and self.hidden_dim in (128, 256) and self.angle_k == 3 and
                 self.reduction_a == 'max' and out_dtype == torch.float16 and qt is None and self.precision != 'fp32')
@@ -187,6 +258,14 @@ class GeometricStructureEmbedding(nn.Module):
         """E of the rows [row_begin, row_begin + row_count).  With `qt` (tensor-core path, <= 4 heads) returns
         (E, scores_p): the first 'self' block's additive scores come out of the same kernel."""
         mean = self.reduction_a == 'mean'
+        if self._use_cheb(out_dtype, qt):
+            e = ops.gse_embed_cheb(geom, self._cheb_cache, self.sigma_d, self.factor_a, mean, out_dtype,
+                                   ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out)
+            shape = (geom.B, geom.n)
+            if shape not in self._overflow_checked and not torch.cuda.is_current_stream_capturing():
+                self._overflow_checked.add(shape)  # first eager call of a shape: one synchronising read of the flag
+                self.check_overflow()
+            return e
         if self._use_table(out_dtype, qt):
             return ops.gse_embed_table(geom, self._tables(), self.sigma_d, self.factor_a, row_begin, row_count, out)
         if self._use_tensor_cores():
@@ -197,6 +276,20 @@ class GeometricStructureEmbedding(nn.Module):
         return ops.gse_embed_fp32(geom, self.embedding.div_term, self.proj_d.weight.detach(),
                                   self.proj_d.bias.detach(), self.proj_a.weight.detach(), self.proj_a.bias.detach(),
                                   self.sigma_d, self.factor_a, mean, out_dtype, row_begin, row_count, out)
+
+    def scores(self, geom, qt, row_begin=0, row_count=None, out=None):
+        """K3r: scores_p[b,h,i,j] = qt[b,h,i,:] . E[b,i,j,:] (rpe_transformer.py:54-56 with proj_p folded into qt) without E
+        ever being formed in memory; E enters the contraction rounded to half, exactly like a stored half E."""
+        if not self._use_cheb(torch.float16, None):
+            raise RuntimeError('GeometricStructureEmbedding.scores needs the low-rank embedding kernel (embed_kernel = '
+                               "'cheb', hidden_dim 128 / 256)")
+        sc = ops.rpe_scores_cheb(geom, self._cheb_cache, qt, self.sigma_d, self.factor_a, self.reduction_a == 'mean',
+                                 ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out)
+        shape = (geom.B, geom.n)
+        if shape not in self._overflow_checked and not torch.cuda.is_current_stream_capturing():
+            self._overflow_checked.add(shape)
+            self.check_overflow()
+        return sc
 
     def forward(self, points, out_dtype=torch.float32):
         """(B,n,3) -> (B,n,n,C).  Standalone calls return fp32 like the reference; GeometricTransformer asks for
@@ -263,8 +356,8 @@ class _FusedAttentionBase(nn.Module):
 class RPEMultiHeadAttention(_FusedAttentionBase):
     """rpe_transformer.py:18-72.  proj_p is folded into the query (exact):
     sum_c q_c (W_p e + b_p)_c = (W_p^T q) . e + q . b_p, and the second term is constant over keys so it cancels
-    in the softmax.  proj_p.bias therefore only exists for state_dict parity (and for need_scores=False paths it
-    has no effect on any output, as in exact arithmetic for the reference)."""
+    in the softmax.  proj_p.bias therefore has no effect on any output (as in exact arithmetic for the reference) unless
+    `key_weights` / `attention_factors` rescale the scores before the softmax; forward() restores the term then."""
 
     def __init__(self, d_model, num_heads, dropout=None):
         super().__init__()
@@ -316,6 +409,13 @@ class RPEMultiHeadAttention(_FusedAttentionBase):
         k = self.proj_k(input_k)
         v = self.proj_v(input_v)
         scores_p = ops.rpe_scores(self.folded_query(q), embed_qk.contiguous())
+        if key_weights is not None or attention_factors is not None:
+            # rpe_transformer.py:58-62 multiplies the summed scores by attention_factors[b,i,j] / key_weights[b,j] BEFORE
+            # the softmax: the folded-away term q . b_p is then no longer constant over the keys and must be restored
+            B, n, _ = q.shape
+            H, c = self.num_heads, self.d_model_per_head
+            qb = torch.einsum('bnhc,hc->bhn', q.view(B, n, H, c), self.proj_p.bias.view(H, c))
+            scores_p = scores_p + qb.unsqueeze(-1)
         return self._attend(q, k, v, scores_p, key_weights, key_masks, attention_factors)
 
 
@@ -458,15 +558,22 @@ class StreamedEmbedding:
     three full HBM reads of E (one per 'self' block); the slab still drains to HBM for the later blocks.
     `slab_bytes` = 0 produces E in one launch (the scores kernel then reads it from HBM as in the later blocks)."""
 
-    def __init__(self, embedding, geom, dtype, slab_bytes, fuse_scores=False, regenerate_bytes=0):
+    def __init__(self, embedding, geom, dtype, slab_bytes, fuse_scores=False, regenerate_bytes=0, direct=False):
         self.embedding, self.geom, self.dtype, self.slab_bytes = embedding, geom, dtype, slab_bytes
         self.fuse_scores = fuse_scores
         self.E = None
+        # direct: E is never stored AND never formed in memory: every 'self' block gets its scores_p from K3r
+        # (geotx_rpe_scores_cheb), which rebuilds E tile by tile in registers from the geometry
+        self.direct = direct
         # > 0: E is NEVER stored.  Every 'self' block regenerates it in query-row slabs of this many bytes, each slab
         # consumed at once by the scores kernel (for clouds whose n^2 C bytes do not fit the GPU next to the other
         # cloud's: 137 GB per cloud at n = 16384).  Costs (number of 'self' blocks - 1) extra embedding passes.
         self.regenerate_bytes = regenerate_bytes
         self._slab = None
+
+    def direct_scores(self, qt):
+        """qt (1,H,n,C) -> scores_p (1,H,n,n) straight from the geometry (K3r); E never exists."""
+        return self.embedding.scores(self.geom, qt)
 
     def regenerated_scores(self, qt):
         """qt (1,H,n,C) -> scores_p (1,H,n,n); E exists one slab at a time."""
@@ -483,6 +590,8 @@ class StreamedEmbedding:
         return scores_p
 
     def materialise(self):
+        if self.direct:
+            self.direct = False  # a consumer wants E itself (layer-by-layer path): store it after all
         if self.regenerate_bytes > 0:
             raise RuntimeError('this embedding is in regenerate mode (it does not fit in memory); only the fused '
                                'single-pair schedule can consume it')
@@ -569,10 +678,8 @@ class RPEConditionalTransformer(nn.Module):
     def _forward_fused(self, feats0, feats1, embeddings0, embeddings1, masks0, masks1):
         N, C = feats0.shape[1], feats0.shape[2]
         embs = [embeddings0, embeddings1]
-        if feats0.data_ptr() + feats0.numel() * feats0.element_size() == feats1.data_ptr():
-            # GeometricTransformer.forward projects both clouds into one buffer: view it, do not copy
-            x = torch.as_strided(feats0, (1, N + feats1.shape[1], C), feats0.stride())
-        else:
+        x = _joint_view(feats0, feats1)  # GeometricTransformer.forward projects both clouds into one buffer: no copy
+        if x is None:
             x = torch.cat([feats0, feats1], dim=1)  # (1, N+M, C); cloud slices of it are contiguous views
         T = x.shape[1]
         for i, block in enumerate(self.blocks):
@@ -586,14 +693,17 @@ class RPEConditionalTransformer(nn.Module):
                 cur = side = None
                 streamed = any(isinstance(e, StreamedEmbedding) for e in embs)
                 if streamed and not any(isinstance(e, StreamedEmbedding) and
-                                        (e.fuse_scores or e.slab_bytes > 0 or e.regenerate_bytes > 0) for e in embs):
+                                        (e.direct or e.fuse_scores or e.slab_bytes > 0 or e.regenerate_bytes > 0)
+                                        for e in embs):
                     # plain schedule: both embedding kernels back to back, each with the whole GPU to itself
                     embs = [e.materialise() if isinstance(e, StreamedEmbedding) else e for e in embs]
                     streamed = False
                 for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
                     emb = embs[which]
                     qt = y[:, lo:hi, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
-                    if isinstance(emb, StreamedEmbedding) and emb.regenerate_bytes > 0:
+                    if isinstance(emb, StreamedEmbedding) and emb.direct:
+                        scores_p = emb.direct_scores(qt)  # K3r: E of this cloud is never formed in memory
+                    elif isinstance(emb, StreamedEmbedding) and emb.regenerate_bytes > 0:
                         scores_p = emb.regenerated_scores(qt)  # E of this cloud is never stored
                     elif isinstance(emb, StreamedEmbedding):
                         scores_p = emb.first_scores(qt)  # the first block interleaves with the embedding kernel
@@ -690,18 +800,21 @@ class GeometricTransformer(nn.Module):
         # extra epilogue work costs the embedding kernel more than the pass saves (measured: 0.50 -> 0.64 ms per
         # cloud at n = 1024 against 0.094 ms saved), so it is opt-in
         self.fuse_scores = os.environ.get('GEOTX_FUSE_SCORES', '0') != '0'
-        # E storage: 'store' keeps both clouds' E for all 'self' blocks (one embedding pass per cloud); 'regenerate'
-        # never stores E (one pass per cloud per 'self' block, in slabs of `regenerate_slab_bytes`); 'auto' stores
-        # when both E fit into 80 % of the free device memory.
+        # E storage: 'scores' never forms E in memory at all: each 'self' block's additive scores come from K3r
+        # (geotx_rpe_scores_cheb), which rebuilds E tile by tile in registers (needs the low-rank embedding kernel,
+        # half-precision E, <= 8 heads, B = 1); 'store' keeps both clouds' E for all 'self' blocks (one embedding
+        # pass per cloud, one HBM read per block); 'regenerate' never stores E (one pass per cloud per 'self' block,
+        # in slabs of `regenerate_slab_bytes`); 'auto' = 'scores' when possible, else 'store' when both E fit into
+        # 80 % of the free device memory, else 'regenerate'.
         self.e_mode = os.environ.get('GEOTX_E_MODE', 'auto')
         self.regenerate_slab_bytes = int(os.environ.get('GEOTX_REGENERATE_SLAB_BYTES', 1 << 30))
         self.last_e_mode = None
         self._auto_mode = {}  # (n, m, dtype) -> decision of 'auto', taken on the first (eager) call of that shape
 
     def _regenerate_bytes(self, n, m, e_dtype, device, batch):
-        if self.e_mode not in ('auto', 'store', 'regenerate'):
-            raise ValueError(f"GEOTX_E_MODE must be 'auto', 'store' or 'regenerate', got {self.e_mode!r}")
-        if self.e_mode == 'store' or batch != 1 or 'self' not in self.transformer.blocks:
+        if self.e_mode not in ('auto', 'store', 'regenerate', 'scores'):
+            raise ValueError(f"GEOTX_E_MODE must be 'auto', 'scores', 'store' or 'regenerate', got {self.e_mode!r}")
+        if self.e_mode in ('store', 'scores') or batch != 1 or 'self' not in self.transformer.blocks:
             return 0
         if self.e_mode == 'auto':
             key = (n, m, e_dtype)
@@ -714,6 +827,19 @@ class GeometricTransformer(nn.Module):
             if self._auto_mode[key]:
                 return 0
         return self.regenerate_slab_bytes
+
+    def _direct_scores(self, e_dtype, batch, feats):
+        """Whether the 'self' blocks take their scores straight from the geometry (K3r) instead of from a stored E."""
+        if self.e_mode not in ('auto', 'scores') or 'self' not in self.transformer.blocks:
+            return False
+        t = self.transformer
+        ok = (batch == 1 and e_dtype == torch.float16 and self.embedding._use_cheb(e_dtype, None) and
+              t._fused_ok(feats, feats) and all(l.attention.attention.num_heads <= 8 for l in t.layers) and
+              not self.fuse_scores and self.l2_slab_bytes <= 0)
+        if self.e_mode == 'scores' and not ok:
+            raise RuntimeError("GEOTX_E_MODE='scores' needs the low-rank embedding kernel (embed_kernel 'cheb', hidden_dim "
+                               '128 / 256), half-precision E, B = 1 and <= 8 heads')
+        return ok
 
     def forward(self, ref_points, src_points, ref_feats, src_feats, ref_masks=None, src_masks=None):
         _forward_only_guard(self, ref_points, src_points, ref_feats, src_feats)
@@ -748,19 +874,20 @@ class GeometricTransformer(nn.Module):
             cur.wait_stream(side)
             for t in (src_geom.buf, src_geom.knn) + (() if one_buffer else (src_feats,)):
                 t.record_stream(cur)  # allocated on the side stream, consumed (and later freed) on this one
-            regen = self._regenerate_bytes(ref_points.shape[1], src_points.shape[1], e_dtype, ref_points.device,
-                                           ref_points.shape[0])
-            self.last_e_mode = 'regenerate' if regen else 'store'
+            direct = self._direct_scores(e_dtype, ref_points.shape[0], ref_feats)
+            regen = 0 if direct else self._regenerate_bytes(ref_points.shape[1], src_points.shape[1], e_dtype,
+                                                            ref_points.device, ref_points.shape[0])
+            self.last_e_mode = 'scores' if direct else 'regenerate' if regen else 'store'
             ref_embeddings = StreamedEmbedding(self.embedding, ref_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores,
-                                               regen)
+                                               regen, direct)
             src_embeddings = StreamedEmbedding(self.embedding, src_geom, e_dtype, self.l2_slab_bytes, self.fuse_scores,
-                                               regen)
+                                               regen, direct)
             ref_feats, src_feats = self.transformer(ref_feats, src_feats, ref_embeddings, src_embeddings,
                                                     masks0=ref_masks, masks1=src_masks)
-            if ref_feats.shape[0] == 1 and ref_feats.data_ptr() + ref_feats.numel() * 4 == src_feats.data_ptr():
+            both = _joint_view(ref_feats, src_feats)
+            if both is not None:
                 # the fused schedule returns two slices of one (1, N+M, C) buffer: project them in one GEMM
                 n = ref_feats.shape[1]
-                both = torch.as_strided(ref_feats, (1, n + src_feats.shape[1], ref_feats.shape[2]), ref_feats.stride())
                 out = self.out_proj(both)
                 return out[:, :n], out[:, n:]
             return self.out_proj(ref_feats), self.out_proj(src_feats)
@@ -771,9 +898,13 @@ class GraphedGeometricTransformer:
 
     One forward is ~190 kernel launches of a few microseconds each at n ~ 1k; issued eagerly the host cannot keep the
     GPU fed.  The whole forward (our kernels and the cuBLASLt GEMMs between them) is captured once into a CUDA graph on
-    static input/output buffers and replayed with one launch.  Weights are read at replay time from the module's own
-    parameter storage, so in-place updates (load_state_dict) are seen, except proj_d/proj_a whose packed bf16 image is
-    rebuilt only at capture: call `recapture()` after changing them.
+    static input/output buffers and replayed with one launch.  The graph reads the plain weights from the module's own
+    parameter storage, but also DERIVED buffers that exist only as of the capture (the fused q|k|v|folded-query
+    projections of every block, the embedding kernel's coefficients / tables / packed weights).  Every call therefore
+    compares the version counters of all parameters and buffers with those seen at capture and recaptures when any of
+    them moved (load_state_dict, in-place updates): a replay never mixes new and old weights and never reads a derived
+    buffer that has been freed.  Replacing a parameter OBJECT (module.weight = nn.Parameter(...)) is not an in-place
+    update: call `recapture()` yourself after that.
 
         fast = GraphedGeometricTransformer(model, ref_points, src_points, ref_feats, src_feats)   # example inputs
         ref_out, src_out = fast(ref_points, src_points, ref_feats, src_feats)    # any inputs of the same shapes
@@ -787,8 +918,18 @@ class GraphedGeometricTransformer:
         self.warmup = warmup
         self.recapture()
 
+    def _weight_versions(self):
+        return [t._version for t in self._weights]
+
+    def stale(self):
+        """True when a parameter or buffer of the model changed in place since the graph was captured."""
+        return self._weight_versions() != self._captured_versions
+
     @torch.no_grad()
     def recapture(self):
+        self._weights = list(self.model.parameters()) + list(self.model.buffers())
+        self._captured_versions = self._weight_versions()
+        self.captures = getattr(self, 'captures', 0) + 1
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):  # warm-up off the capture: lazy cuBLAS / function-attribute initialisation
@@ -806,8 +947,16 @@ class GraphedGeometricTransformer:
                 raise RuntimeError(f'graphed forward was captured for shape {tuple(s.shape)}, got {tuple(t.shape)}')
             if s.data_ptr() != t.data_ptr():
                 s.copy_(t, non_blocking=True)
-        self.graph.replay()
+        self.replay()
         return self.static_out
+
+    def replay(self):
+        """graph.replay() on the current stream, after recapturing if the weights changed since the capture (the
+        recapture synchronises the device: the graph being replaced may still be running)."""
+        if self.stale():
+            torch.cuda.synchronize()
+            self.recapture()
+        self.graph.replay()
 
 
 class PipelinedGeometricTransformer:
@@ -820,7 +969,8 @@ class PipelinedGeometricTransformer:
 
         pipe = PipelinedGeometricTransformer(model, ref_points, src_points, ref_feats, src_feats)  # example DEVICE inputs
         for ref_out, src_out in pipe.map(host_pairs):    # iterable of 4-tuples of (pinned) host tensors
-            ...                                          # pinned host tensors, valid until `depth` more results
+            ...                                          # pinned host tensors, valid until the NEXT result is requested
+                                                         # (their slot is re-enqueued then): clone what must outlive it
 
     Results come back in order and are bit-identical to `model(...)` on the same inputs."""
 
@@ -868,7 +1018,7 @@ class PipelinedGeometricTransformer:
             compute.wait_event(ev['h2d'])
             compute.wait_event(ev['d2h'])  # the slot's last download no longer reads its static outputs
             with torch.cuda.stream(compute):
-                g.graph.replay()
+                g.replay()
             ev['compute'].record(compute)
             self.copy_out.wait_event(ev['compute'])
             with torch.cuda.stream(self.copy_out):

@@ -540,3 +540,105 @@ def gse_embed_table(geom, tables, sigma_d, factor_a, row_begin=0, row_count=None
               tables.C, tables.rows_a, tables.rows_d, tables.h_a, tables.h_d, float(sigma_d), float(factor_a),
               _p(tables.weights[0]), _p(tables.weights[1]), _p(tables.weights[2]), _p(out), _p(tables.overflow), _stream())
     return out
+
+
+class ChebCoefficients:
+    """Chebyshev coefficients of proj_a(sinus(x)) and proj_d(sinus(x)) + b_d + b_a for geotx_gse_embed_cheb (K2c)."""
+    __slots__ = ('buf', 'C', 'angle_index_max', 'ka_tiles', 'stats', 'overflow', '_report')
+
+    def __init__(self, buf, C, angle_index_max, ka_tiles, stats, overflow):
+        self.buf, self.C, self.angle_index_max, self.ka_tiles = buf, C, angle_index_max, ka_tiles
+        self.stats, self.overflow, self._report = stats, overflow, None
+
+    def report(self):
+        """One host read per weight set: [{'range', 'coefficients', 'max_error', 'max_abs_f', 'max_abs_g'}, ...] for the
+        angle set and the six distance sets (errors measured by the build kernel in fp64 against the module's own
+        weights, at 256 points per channel between the quadrature nodes)."""
+        if self._report is None:
+            lib = _abi.load()
+            st = self.stats.cpu().view(7, 4).tolist()
+            rows = [dict(range=self.angle_index_max, coefficients=16 * self.ka_tiles)]
+            rows += [dict(range=float(lib.geotx_gse_cheb_d_range(s)), coefficients=16 * (1, 2, 3, 4, 6, 8)[s])
+                     for s in range(6)]
+            for r, (err, fmax, gmax, _) in zip(rows, st):
+                r.update(max_error=err, max_abs_f=fmax, max_abs_g=gmax)
+            self._report = rows
+        return self._report
+
+
+def gse_cheb_ka_tiles(angle_index_max):
+    """16-coefficient tiles the angle term needs for arguments in [0, angle_index_max]; 0 = not covered by K2c."""
+    return int(_abi.load().geotx_gse_cheb_ka_tiles(float(angle_index_max)))
+
+
+def gse_cheb_max_d_set(d_index_max):
+    """Smallest prebuilt distance set whose range reaches d_index_max (5 = the largest, 210 index units)."""
+    lib = _abi.load()
+    for s in range(6):
+        if float(d_index_max) <= float(lib.geotx_gse_cheb_d_range(s)):
+            return s
+    return 5
+
+
+def gse_build_cheb(div_term, w_d, b_d, w_a, b_a, factor_a):
+    """Coefficients for `gse_embed_cheb`, built on the device in fp64 from the module's weights (once per weight set).
+    geotransformer.py:60-64 + positional_embedding.py:28-32."""
+    import math
+    for name, t in (('div_term', div_term), ('w_d', w_d), ('b_d', b_d), ('w_a', w_a), ('b_a', b_a)):
+        _check(t, name, torch.float32)
+    C = w_d.shape[0]
+    angle_index_max = math.pi * float(factor_a) * (1.0 + 1e-6)
+    lib = _abi.load()
+    ka = int(lib.geotx_gse_cheb_ka_tiles(angle_index_max))
+    nbytes = lib.geotx_gse_cheb_bytes(C, ka) if ka > 0 else 0
+    if nbytes <= 0:
+        raise RuntimeError(f'gse_build_cheb: hidden_dim {C} / angle range {angle_index_max:.1f} is not supported by the '
+                           f'low-rank embedding kernel')
+    dev = w_d.device
+    buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    stats = torch.empty(28, dtype=torch.float32, device=dev)
+    overflow = torch.zeros(1, dtype=torch.int32, device=dev)
+    _abi.call('geotx_gse_build_cheb', _p(div_term), _p(w_d.contiguous()), _p(b_d.contiguous()), _p(w_a.contiguous()),
+              _p(b_a.contiguous()), C, angle_index_max, ka, _p(buf), _p(stats), _stream())
+    return ChebCoefficients(buf, C, angle_index_max, ka, stats, overflow)
+
+
+def gse_embed_cheb(geom, coef, sigma_d, factor_a, reduce_mean, out_dtype, max_d_set=5, row_begin=0, row_count=None,
+                   out=None):
+    """Low-rank embedding K2c: -> E (B,row_count,n,C) f16 / bf16; coef.overflow becomes 1 if a distance fell beyond the
+    range of set `max_d_set`.  geotransformer.py:57-72."""
+    row_begin, row_count = _slab(geom, row_begin, row_count)
+    if out_dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError(f'gse_embed_cheb: out_dtype must be float16 or bfloat16, got {out_dtype}')
+    if out is None:
+        out = torch.empty(geom.B, row_count, geom.n, coef.C, dtype=out_dtype, device=geom.buf.device)
+    else:
+        _check(out, 'out', out_dtype)
+    _abi.call('geotx_gse_embed_cheb', _p(geom.buf), geom.B, geom.n, geom.k, row_begin, row_count, _p(coef.buf), coef.C,
+              coef.angle_index_max, coef.ka_tiles, int(max_d_set), float(sigma_d), float(factor_a), int(bool(reduce_mean)),
+              _abi.GEOTX_F16 if out_dtype == torch.float16 else _abi.GEOTX_BF16, _p(out), _p(coef.overflow), _stream())
+    return out
+
+
+def rpe_scores_cheb(geom, coef, qt, sigma_d, factor_a, reduce_mean=False, max_d_set=5, row_begin=0, row_count=None,
+                    out=None):
+    """K3r: rpe_transformer.py:54-56 (proj_p folded into qt, see rpe_scores) fused with the embedding
+    (geotransformer.py:57-72): scores_p (B,H,n,n) fp32 straight from the geometry; E is rebuilt tile by tile in
+    registers and never stored.  qt: logical (B,H,n,C) fp32 with a dense last dimension (any strides over b, h, i)."""
+    row_begin, row_count = _slab(geom, row_begin, row_count)
+    if not isinstance(qt, torch.Tensor) or not qt.is_cuda or qt.dtype != torch.float32 or qt.dim() != 4:
+        raise RuntimeError('qt must be a 4-d float32 CUDA tensor (B,H,n,C)')
+    B, H, n, C = qt.shape
+    if (B, n, C) != (geom.B, geom.n, coef.C) or qt.stride(3) != 1:
+        raise RuntimeError(f'qt {tuple(qt.shape)} (strides {qt.stride()}) does not match the geometry '
+                           f'(B={geom.B}, n={geom.n}) / hidden_dim {coef.C}, or its last dimension is not dense')
+    if out is None:
+        out = torch.empty(B, H, n, n, dtype=torch.float32, device=qt.device)
+    else:
+        _check(out, 'out', torch.float32, 4)
+        if tuple(out.shape) != (B, H, n, n):
+            raise RuntimeError(f'out must be {(B, H, n, n)}, got {tuple(out.shape)}')
+    _abi.call('geotx_rpe_scores_cheb', _p(geom.buf), B, n, geom.k, row_begin, row_count, _p(coef.buf), C,
+              coef.angle_index_max, coef.ka_tiles, int(max_d_set), float(sigma_d), float(factor_a), int(bool(reduce_mean)),
+              _p(qt), int(qt.stride(0)), int(qt.stride(1)), int(qt.stride(2)), H, _p(out), _p(coef.overflow), _stream())
+    return out

@@ -8,10 +8,13 @@ from gpu_common import DEV, TOL_BF16, TOL_FP32, rel, sd_from_npz
 pytestmark = pytest.mark.gpu
 
 
-def _gse(pkg, cfg, sd, precision):
+def _gse(pkg, cfg, sd, precision, kernel='tensor'):
+    """`kernel`: which kernel serves a 16-bit E ('tensor' = K2 tcgen05, 'table' = K2t, 'cheb' = K2c, the default of the
+    module); fp32 output always comes from K2 / the CUDA-core kernel."""
     m = pkg.GeometricStructureEmbedding(cfg['hidden_dim'], cfg['sigma_d'], cfg['sigma_a'], cfg['angle_k'],
                                         reduction_a=cfg.get('reduction_a', 'max'), precision=precision)
     m.load_state_dict({k[len('embedding.'):]: v for k, v in sd.items() if k.startswith('embedding.')}, strict=True)
+    m.embed_kernel = kernel
     return m.to(DEV).eval()
 
 
@@ -159,7 +162,7 @@ def test_fused_first_block_scores(pkg, oracle, C, H, n, reduction):
     assert pkg._abi.watchdog() is None
 
 
-# ---- K2t: the tabulated embedding (experimental, GEOTX_EMBED=table) ---------------------------------------------------
+# ---- K2t: the tabulated embedding (GEOTX_EMBED=table; superseded by K2c) -----------------------------------------------
 TOL_TABLE = 2e-3  # Frobenius-relative: half tables + half arithmetic; measured ~5e-4 (the bf16 contraction: ~4e-3)
 
 
@@ -225,3 +228,165 @@ def test_forward_with_table_embedding(pkg, oracle, golden):
         errs[kernel] = max(rel(o0, z['out_ref']), rel(o1, z['out_src']))
     print(f'forward rel err: {errs}')
     assert errs['table'] <= TOL_BF16 and errs['table'] <= errs['tensor'] * 1.5
+
+
+# ---- K2c: the low-rank (Chebyshev) contraction, the default embedding kernel ------------------------------------------
+TOL_CHEB = 1e-3  # Frobenius-relative: half operands, fp32 accumulation, half storage of E; measured ~3e-4
+
+
+@pytest.mark.parametrize('name', ['3dmatch_n192', 'kitti_n256', 'modelnet_n128'])
+def test_cheb_kernel_vs_reference_golden(pkg, oracle, golden, name):
+    """The three shipped configs (C = 256 / 128 / 256): golden rows of E written by the reference, through K2c, which
+    is what GeometricTransformer runs by default."""
+    z = golden(f'{name}.npz')
+    cfg = eval(str(z['cfg']))
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    pts = pkg.synth.make_tie_free_pair(str(z['shape']), int(z['n']), int(z['m']), seed=int(z['seed']))[0]
+    m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
+    assert pkg.GeometricStructureEmbedding(256, 0.2, 15, 3).embed_kernel == 'cheb'
+    rows = torch.from_numpy(z['rows'])
+    with torch.no_grad():
+        assert m._use_cheb(torch.float16, None)
+        e = m(pts.to(DEV), out_dtype=torch.float16)
+    m.check_overflow()
+    rep = m.cheb_report()
+    print(f'{name} cheb report: {[(r["range"], r["coefficients"], "%.1e" % r["max_error"]) for r in rep]}')
+    assert all(r['max_error'] <= 2e-3 * r['max_abs_f'] for r in rep)
+    err = rel(e[0].float().cpu()[rows], z['E_rows'])
+    print(f'{name} cheb: E rel err {err:.3e}')
+    assert e.dtype == torch.float16 and err <= TOL_CHEB
+
+
+@pytest.mark.parametrize('C,reduction,k', [(256, 'max', 3), (128, 'max', 3), (256, 'mean', 3), (256, 'max', 1),
+                                           (128, 'mean', 2), (256, 'max', 5), (128, 'max', 7)])
+def test_cheb_kernel_vs_oracle(pkg, oracle, C, reduction, k):
+    """Ragged n (tile tail), B = 2, every reduction and several k, f16 / bf16 outputs, row slabs, the oracle as checker;
+    K2c must sit closer to fp32 than the bf16 tcgen05 contraction."""
+    cfg = dict(hidden_dim=C, sigma_d=0.3, sigma_a=10, angle_k=k, reduction_a=reduction)
+    sd = oracle.init_state_dict(8, 8, C, [], seed=5)
+    pts = torch.rand(2, 173, 3, generator=torch.Generator().manual_seed(C + k)) * 2.5
+    exp = oracle.gse(pts, sd, 'embedding.', cfg['sigma_d'], cfg['sigma_a'], k, reduction)
+    m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
+    with torch.no_grad():
+        geom = m.geometry(pts.to(DEV))
+        assert m._use_cheb(torch.float16, None)
+        eh = m.embed(geom, torch.float16)
+        eb = m.embed(geom, torch.bfloat16)
+        slab = m.embed(geom, torch.float16, row_begin=40, row_count=77)
+        m.embed_kernel = 'tensor'
+        tensor = m.embed(geom, torch.float16)
+    m.check_overflow()
+    err = rel(eh.float(), exp)
+    print(f'C={C} {reduction} k={k}: cheb {err:.3e}, tcgen05 bf16 {rel(tensor.float(), exp):.3e}')
+    assert err <= TOL_CHEB and rel(eb.float(), exp) <= 4e-3
+    assert torch.equal(slab, eh[:, 40:117]), 'row slabs must reproduce the whole-cloud result bit for bit'
+    assert err < rel(tensor.float(), exp)
+
+
+@pytest.mark.parametrize('extent,want_set', [(1.5, 0), (6.0, 1), (11.0, 2), (17.0, 3), (28.0, 4), (40.0, 5)])
+def test_cheb_distance_sets(pkg, oracle, extent, want_set):
+    """The kernel picks the distance expansion from the cloud's largest distance (left behind by geotx_gse_knn): clouds
+    of growing extent walk through all six prebuilt sets (ranges 13 .. 210 index units at sigma_d = 0.2)."""
+    cfg = dict(hidden_dim=128, sigma_d=0.2, sigma_a=15, angle_k=3, reduction_a='max')
+    sd = oracle.init_state_dict(8, 8, 128, [], seed=9)
+    pts = torch.rand(1, 200, 3, generator=torch.Generator().manual_seed(int(extent * 10)))
+    pts[0, 0] = 0.0
+    pts[0, 1] = torch.tensor([1.0, 0.0, 0.0])  # the largest distance is >= 1 * extent and <= sqrt(3) * extent
+    pts = pts * extent / 3 ** 0.5
+    d_max = float(torch.cdist(pts[0].double(), pts[0].double()).max()) / cfg['sigma_d']
+    lib = pkg._abi.load()
+    ranges = [float(lib.geotx_gse_cheb_d_range(s)) for s in range(6)]
+    assert min(s for s in range(6) if d_max <= ranges[s]) == want_set, (d_max, ranges)
+    exp = oracle.gse(pts, sd, 'embedding.', cfg['sigma_d'], cfg['sigma_a'], 3, 'max')
+    m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
+    with torch.no_grad():
+        e = m(pts.to(DEV), out_dtype=torch.float16)
+    m.check_overflow()
+    err = rel(e.float(), exp)
+    print(f'extent {extent}: d_max {d_max:.1f} index units -> set {want_set}, err {err:.3e}')
+    assert err <= TOL_CHEB
+
+
+def test_cheb_overflow_and_guard(pkg, oracle):
+    """(1) A cloud larger than cheb_d_index_max allows: the flag is raised and the first eager call of the shape raises
+    instead of returning clamped values.  (2) Weights scaled x50 and x2000: the measured error of the expansions stays
+    RELATIVE to the weights (a sampled table's would not), the module keeps K2c and still matches the oracle."""
+    cfg = dict(hidden_dim=128, sigma_d=0.2, sigma_a=15, angle_k=3, reduction_a='max')
+    sd = oracle.init_state_dict(8, 8, 128, [], seed=9)
+    pts = torch.rand(1, 100, 3, generator=torch.Generator().manual_seed(2)) * 6.0
+    m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
+    m.cheb_d_index_max = 13.0  # set 0 only: 2.6 m
+    with pytest.raises(RuntimeError, match='cheb_d_index_max'), torch.no_grad():
+        m(pts.to(DEV), out_dtype=torch.float16)
+    for scale in (50.0, 2000.0):
+        big = {k: (v * scale if k.endswith(('proj_a.weight', 'proj_d.weight')) else v) for k, v in sd.items()}
+        exp = oracle.gse(pts, big, 'embedding.', cfg['sigma_d'], cfg['sigma_a'], 3, 'max')
+        m = _gse(pkg, cfg, big, 'auto', kernel='cheb')
+        with torch.no_grad():
+            assert m._use_cheb(m.storage_dtype(), None)
+            e = m(pts.to(DEV), out_dtype=m.storage_dtype())
+        err = rel(e.float(), exp)
+        print(f'weights x{scale:g}: storage {m.storage_dtype()}, cheb err {err:.3e}')
+        assert err <= (TOL_CHEB if m.storage_dtype() == torch.float16 else 4e-3)
+
+
+def test_cheb_full_size_properties_n4096(pkg, oracle):
+    """BASELINE full size (n = 4096, C = 256) through K2c, the kernel behind every headline number: (1) relabelling the
+    points permutes E exactly; (2) a row slab equals the same rows of a larger slab; (3) sampled rows match the oracle
+    evaluated on those rows (the reference itself cannot materialise n = 4096)."""
+    cfg = dict(pkg.synth.CONFIGS['3dmatch'])
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    n = 4096
+    pts = pkg.synth.make_tie_free_pair('3dmatch', n, n, seed=pkg.synth.SEED, input_dim=4)[0]
+    m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
+    perm = torch.randperm(n, generator=torch.Generator().manual_seed(3))
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(n)
+    rows = torch.tensor([0, 1, 777, 2048, 4095])
+    with torch.no_grad():
+        geom = m.geometry(pts.to(DEV))
+        geom_p = m.geometry(pts[:, perm].contiguous().to(DEV))
+        got = []
+        for r in rows.tolist():
+            e = m.embed(geom, torch.float16, row_begin=r, row_count=1)[0, 0]             # (n, C): E[r, :, :]
+            ep = m.embed(geom_p, torch.float16, row_begin=int(inv[r]), row_count=1)[0, 0]  # same point, relabelled
+            assert torch.equal(ep.cpu(), e.cpu()[perm]), 'E is not equivariant under point relabelling'
+            got.append(e.float().cpu())
+        big = m.embed(geom, torch.float16, row_begin=700, row_count=100)
+        assert torch.equal(big[0, 77].cpu().float(), got[2])
+        d_idx, a_idx, _ = oracle.embedding_indices(pts, cfg['sigma_d'], cfg['sigma_a'], cfg['angle_k'])
+        exp = oracle.gse_from_indices(d_idx[:, rows], a_idx[:, rows], sd, 'embedding.')
+    m.check_overflow()
+    err = rel(torch.stack(got), exp[0])
+    print(f'n = 4096 cheb rows: {err:.3e}')
+    assert err <= TOL_CHEB
+
+
+@pytest.mark.parametrize('C,H,n,reduction,k', [(256, 4, 173, 'max', 3), (128, 4, 256, 'max', 3), (256, 8, 130, 'mean', 2),
+                                               (256, 2, 384, 'max', 1), (128, 1, 64, 'max', 5)])
+def test_cheb_scores_without_e(pkg, oracle, C, H, n, reduction, k):
+    """K3r (geotx_rpe_scores_cheb): scores_p = qt . E straight from the geometry must equal the two-kernel path
+    (K2c writes the half E, K3a reads it back) up to the summation order, and the oracle's E within K2c's tolerance;
+    ragged n (key tiles with a tail), B = 2, 1..8 heads, row slabs, strided qt."""
+    cfg = dict(hidden_dim=C, sigma_d=0.3, sigma_a=10, angle_k=k, reduction_a=reduction)
+    sd = oracle.init_state_dict(8, 8, C, [], seed=5)
+    g = torch.Generator().manual_seed(n + H)
+    pts = torch.rand(2, n, 3, generator=g) * 2.5
+    wide = torch.randn(2, n, H * C + 32, generator=g).to(DEV)
+    qt = wide[:, :, 32:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (B,H,n,C) view of a wider projection output
+    m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
+    with torch.no_grad():
+        geom = m.geometry(pts.to(DEV))
+        E = m.embed(geom, torch.float16)
+        want = pkg.ops.rpe_scores(qt, E)
+        got = m.scores(geom, qt)
+        part = torch.full_like(got, -7.0)
+        m.scores(geom, qt, row_begin=30, row_count=20, out=part)
+    m.check_overflow()
+    exp = torch.einsum('bhic,bijc->bhij', qt.double().cpu(),
+                       oracle.gse(pts, sd, 'embedding.', 0.3, 10, k, reduction).double()).float()
+    print(f'C={C} H={H} n={n}: K3r vs K2c+K3a {rel(got, want):.3e}, vs oracle {rel(got, exp):.3e}')
+    assert rel(got, want) <= 1e-5
+    assert rel(got, exp) <= TOL_CHEB
+    assert torch.equal(part[:, :, 30:50], got[:, :, 30:50])
+    assert float((part[:, :, :30] + 7.0).abs().max()) == 0.0 and float((part[:, :, 50:] + 7.0).abs().max()) == 0.0

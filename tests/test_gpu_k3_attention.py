@@ -109,3 +109,34 @@ def test_strided_operands_of_a_fused_projection(pkg):
     assert torch.equal(sp, pkg.ops.rpe_scores(qt.contiguous(), E))
     got = pkg.ops.attention(q, k, v, H, sp)
     assert torch.equal(got, pkg.ops.attention(q.contiguous(), k.contiguous(), v.contiguous(), H, sp))
+
+
+@pytest.mark.parametrize('with_masks', [False, True])
+def test_rpe_attention_with_key_weights_and_attention_factors(pkg, oracle, with_masks):
+    """rpe_transformer.py:58-64: attention_factors and key_weights rescale the summed scores BEFORE the softmax, so the
+    q . b_p term that the folded query drops is no longer constant over the keys: the module must restore it.
+    proj_p.bias is made large so that a missing term cannot hide inside the tolerance."""
+    C, H, n, m, B = 128, 4, 70, 70, 2
+    g = torch.Generator().manual_seed(11)
+    sd = {f'a.proj_{x}.weight': _rand(g, C, C) / C ** 0.5 for x in 'qkvp'}
+    sd.update({f'a.proj_{x}.bias': _rand(g, C) * (3.0 if x == 'p' else 0.1) for x in 'qkvp'})
+    x = _rand(g, B, n, C)
+    E = _rand(g, B, n, m, C)
+    kw = torch.rand(B, m, generator=g) + 0.5
+    af = torch.rand(B, n, m, generator=g) + 0.5
+    masks = (torch.rand(B, m, generator=g) < 0.2) if with_masks else None
+    exp, exp_scores = oracle.multi_head_attention(x, x, x, sd, 'a.', H, embed_qk=E, key_weights=kw, key_masks=masks,
+                                                  attention_factors=af)
+    att = pkg.RPEMultiHeadAttention(C, H).to(DEV).eval()
+    att.load_state_dict({k[2:]: v for k, v in sd.items()}, strict=True)
+    att.need_scores = True
+    with torch.no_grad():
+        got, scores = att(x.to(DEV), x.to(DEV), x.to(DEV), E.to(DEV), key_weights=kw.to(DEV),
+                          key_masks=None if masks is None else masks.to(DEV), attention_factors=af.to(DEV))
+    assert rel(got, exp) <= 1e-4 and rel(scores, exp_scores) <= 1e-4
+    # and without the modifiers the bias still has no effect (fast path, folded query)
+    with torch.no_grad():
+        att.need_scores = False
+        fast, _ = att(x.to(DEV), x.to(DEV), x.to(DEV), E.to(DEV))
+    plain, _ = oracle.multi_head_attention(x, x, x, sd, 'a.', H, embed_qk=E)
+    assert rel(fast, plain) <= 2e-3  # half operands in the flash kernel

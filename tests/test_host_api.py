@@ -122,7 +122,12 @@ def test_abi_library_exports_every_declared_symbol(pkg):
         assert hasattr(lib, name), f'{name} declared in include/geotx_b200.h but not exported'
     loaded = pkg._abi.load()
     assert loaded.geotx_abi_version() == 1
-    assert loaded.geotx_gse_geometry_bytes(2, 100, 3) == 16 * 2 * 100 * 4
+    assert loaded.geotx_gse_geometry_bytes(2, 100, 3) == 16 * 2 * 100 * 4 + 16  # + the largest squared distance
+    # K2c: 16 coefficients reach 13 index units, 32 reach 37; six distance sets of 16..128 coefficients
+    assert [loaded.geotx_gse_cheb_ka_tiles(x) for x in (12.0, 13.5, 37.0, 38.0, 0.0)] == [1, 2, 2, 0, 0]
+    assert [loaded.geotx_gse_cheb_d_range(s) for s in range(7)] == [13.0, 37.0, 64.0, 93.0, 150.0, 210.0, 0.0]
+    assert loaded.geotx_gse_cheb_bytes(256, 1) == 2 * 16 * 256 * (1 + 1 + 2 + 3 + 4 + 6 + 8)
+    assert loaded.geotx_gse_cheb_bytes(96, 1) == 0 and loaded.geotx_gse_cheb_bytes(128, 3) == 0
     assert loaded.geotx_gse_packed_weight_bytes(256) == 4 * 256 * 256 + 4 * 256
     assert loaded.geotx_gse_packed_weight_bytes(100) == 0
 
@@ -178,8 +183,11 @@ def test_embedding_kernel_switch(pkg, monkeypatch):
     built for (every other request goes to the tcgen05 / fp32 kernels, never to a CPU path)."""
     import torch
     m = pkg.GeometricStructureEmbedding(256, 0.2, 15, 3)
-    assert m.embed_kernel == 'table' and m._use_table(torch.float16, None)
+    assert m.embed_kernel == 'cheb'  # K2c, the low-rank contraction, is the default
+    m.embed_kernel = 'table'
+    assert m._use_table(torch.float16, None)
     assert not m._use_table(torch.float32, None) and not m._use_table(torch.float16, object())
+    monkeypatch.setenv('GEOTX_EMBED', 'table')
     assert not pkg.GeometricStructureEmbedding(256, 0.2, 15, 2)._use_table(torch.float16, None)
     assert not pkg.GeometricStructureEmbedding(256, 0.2, 15, 3, reduction_a='mean')._use_table(torch.float16, None)
     assert not pkg.GeometricStructureEmbedding(64, 0.2, 15, 3)._use_table(torch.float16, None)
@@ -190,3 +198,25 @@ def test_embedding_kernel_switch(pkg, monkeypatch):
     import pytest
     with pytest.raises(ValueError):
         pkg.GeometricStructureEmbedding(256, 0.2, 15, 3)
+
+
+def test_joint_view_only_inside_one_storage(pkg):
+    """The fused schedule views two cloud slices as one token buffer only when they are adjacent slices of ONE storage;
+    two separate allocations that merely sit back to back in memory must be concatenated instead."""
+    import torch
+    jv = pkg.modules._joint_view
+    buf = torch.arange(40.).view(1, 10, 4)
+    v = jv(buf[:, :6], buf[:, 6:])
+    assert v is not None and tuple(v.shape) == (1, 10, 4) and v.data_ptr() == buf.data_ptr() and torch.equal(v, buf)
+    assert jv(buf[:, :5], buf[:, 6:]) is None            # a gap
+    assert jv(buf[:, :6].clone(), buf[:, 6:].clone()) is None  # separate storages, wherever the allocator put them
+    assert jv(torch.zeros(2, 3, 4)[:, :2], torch.zeros(2, 3, 4)[:, 2:]) is None  # B > 1 is not one token buffer
+    big = torch.zeros(1 << 18)
+    a, b = big[:1024].view(1, 4, 256), big[1024:2048].view(1, 4, 256)
+    assert jv(a, b) is not None
+    # adjacent in address space but different storages (emulated with two views created through from-buffer copies)
+    import numpy as np
+    raw = np.zeros(2048, dtype=np.float32)
+    a = torch.from_numpy(raw[:1024]).view(1, 4, 256)
+    b = torch.from_numpy(raw[1024:]).view(1, 4, 256)
+    assert a.data_ptr() + a.numel() * 4 == b.data_ptr() and jv(a, b) is None

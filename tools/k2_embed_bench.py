@@ -1,0 +1,78 @@
+"""The three embedding kernels side by side (K2c 'cheb' = default, K2t 'table', K2 'tensor'): time for the whole cloud
+(CUDA events, back-to-back launches over an output larger than L2), GB/s of E written against MEASURED_PEAKS.json, and
+the error of a row slab against the fp32 CUDA-core kernel.  usage: k2_embed_bench.py [once <kernel> <n> <C>]"""
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import pkgpath  # noqa: E402
+
+pkg = pkgpath.load_package()
+dev = 'cuda:0'
+PEAK = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['hbm_gbs']
+
+
+def setup(n, C, kernel):
+    torch.manual_seed(1)
+    sigma_d = 0.2 if C == 256 else 4.8
+    m = pkg.GeometricStructureEmbedding(C, sigma_d, 15, 3).to(dev).eval()
+    m.embed_kernel = kernel
+    pts = pkg.synth.make_pair('3dmatch' if C == 256 else 'kitti', n)[0].to(dev)
+    with torch.no_grad():
+        geom = m.geometry(pts)
+    return m, geom
+
+
+def timed(fn, reps=10):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+if len(sys.argv) > 1 and sys.argv[1] == 'once':  # for ncu: three launches of one kernel
+    kernel, n, C = sys.argv[2], int(sys.argv[3]), int(sys.argv[4])
+    m, geom = setup(n, C, kernel)
+    out = torch.empty(1, n, n, C, dtype=torch.float16, device=dev)
+    with torch.no_grad():
+        for _ in range(3):
+            m.embed(geom, torch.float16, out=out)
+    torch.cuda.synchronize()
+    print('ok', float(out[0, :8].float().abs().max()))
+    sys.exit(0)
+
+res = {}
+for n, C in ((512, 256), (1024, 256), (2048, 256), (4096, 256), (717, 256), (2048, 128)):
+    row = {}
+    out = torch.empty(1, n, n, C, dtype=torch.float16, device=dev)
+    exact = None
+    for kernel in ('cheb', 'table', 'tensor'):
+        m, geom = setup(n, C, kernel)
+        with torch.no_grad():
+            if exact is None:
+                w = [t.detach() for t in (m.proj_d.weight, m.proj_d.bias, m.proj_a.weight, m.proj_a.bias)]
+                exact = pkg.ops.gse_embed_fp32(geom, m.embedding.div_term, *w, m.sigma_d, m.factor_a, False,
+                                               torch.float32, 0, 64)
+            got = m.embed(geom, torch.float16, 0, 64).float()
+            ms = timed(lambda: m.embed(geom, torch.float16, out=out))
+        gbs = n * n * C * 2 / ms / 1e6
+        row[kernel] = {'ms': ms, 'e_write_gbs': gbs, 'frac_of_measured_hbm_peak': gbs / PEAK,
+                       'rel_err_vs_fp32_kernel': float((got - exact).norm() / exact.norm()),
+                       'max_abs_err': float((got - exact).abs().max())}
+        if kernel == 'cheb':
+            m.check_overflow()
+            row['cheb_sets'] = [(r['range'], r['coefficients'], r['max_error'], r['max_abs_f']) for r in m.cheb_report()]
+    res[f'n{n}_C{C}'] = row
+    print(json.dumps({f'n{n}_C{C}': row}), flush=True)
+os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
+json.dump(res, open(os.path.join(ROOT, 'gpurun_out', 'k2_embed_bench.json'), 'w'), indent=1)
