@@ -134,6 +134,30 @@ int geotx_attention(const float* q, const float* k, const float* v, const float*
 int geotx_add_layernorm(const float* x, const float* residual, const float* gamma, const float* beta, int64_t rows,
                         int C, float eps, float* out, void* stream);
 
+/* K13: y = x W^T + b (torch.nn.Linear) for the token-wise projections of the path that are not part of
+ * geotx_post_attention's chain: in_proj / out_proj (geotransformer.py:140-141,152-153) and the q | k | v | folded-query
+ * projections (rpe_transformer.py:51-53, vanilla_transformer.py:50-52; several Linears of a block are concatenated along
+ * N by the caller).  x f32 [T,K] with row stride ld_x (floats), rounded to half on its way into shared memory; w_f16
+ * [N][K] IEEE half (geotx_f32_to_f16 of the nn.Linear weight); mma.sync.m16n8k16, fp32 accumulation; y f32 [T,N] with
+ * row stride ld_y; bias f32 [N] or NULL; relu != 0 applies max(., 0).  K % 32 == 0, N % 64 == 0. */
+int geotx_f32_to_f16(const float* src, void* dst, int64_t count, void* stream);
+int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias, int N,
+                     int relu, float* y, int64_t ld_y, void* stream);
+
+/* K4f: everything a transformer layer does after its attention core, in one kernel (rpe_transformer.py:101-103 /
+ * vanilla_transformer.py:99-101 followed by output_layer.py:15-21):
+ *   x1  = LayerNorm(hidden W_lin^T + b_lin + x_in; gamma1, beta1, eps1)
+ *   out = LayerNorm(x1 + (ReLU(x1 W_expand^T + b_expand)) W_squeeze^T + b_squeeze; gamma2, beta2, eps2)
+ * hidden, x_in, out f32 [T,C] with row strides in floats (multiples of 4); C = 128 or 256; weights as IEEE half in
+ * nn.Linear layout (w_lin [C][C], w_expand [2C][C], w_squeeze [C][2C]); biases and LayerNorm parameters f32.
+ * A CTA keeps a tile of 32 tokens in shared memory through the whole chain; activations enter the contractions as
+ * halves (saturated), accumulation / residuals / LayerNorm are fp32 (torch.nn.LayerNorm semantics). */
+int geotx_post_attention(const float* hidden, int64_t ld_hidden, const float* x_in, int64_t ld_x, int64_t T, int C,
+                         const void* w_lin_f16, const float* b_lin, const float* gamma1, const float* beta1, float eps1,
+                         const void* w_expand_f16, const float* b_expand, const void* w_squeeze_f16,
+                         const float* b_squeeze, const float* gamma2, const float* beta2, float eps2, float* out,
+                         int64_t ld_out, void* stream);
+
 /* Coarse matching behind the path: F.normalize of both clouds' output features
  * (experiments/<cfg>/model.py:141-142) followed by SuperPointMatching.forward
  * (geotransformer/modules/geotransformer/superpoint_matching.py:13-51, with pairwise_distance(normalized=True),

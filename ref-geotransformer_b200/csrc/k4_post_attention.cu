@@ -1,0 +1,304 @@
+// K4f: everything a transformer layer does after its attention core, in ONE kernel:
+//     x1  = LayerNorm(linear(hidden) + x_in)                       rpe_transformer.py:101-103 / vanilla_transformer.py:99-101
+//     out = LayerNorm(x1 + squeeze(ReLU(expand(x1))))              output_layer.py:15-21 (AttentionOutput)
+// The reference (and round 1 of this repo) runs these as 3 library GEMMs + 2 residual/LayerNorm kernels per layer and
+// cloud step: 45 launches of a few microseconds per forward, each one latency-bound at ~2k tokens.  All five steps are
+// token-local (LayerNorm normalises over the channels of ONE token), so a CTA that owns a tile of 32 tokens can run
+// the whole chain without leaving the SM: the three weight matrices stream through a 3-stage cp.async ring in 32-wide
+// K chunks (655 KB of half weights per CTA at C = 256, from L2), the activations live in shared memory between the
+// GEMMs (half as mma A operands, fp32 for the residuals), the contractions run on mma.sync.m16n8k16 (f16 operands --
+// the same 11-bit significand as the TF32 library path it replaces -- fp32 accumulation), LayerNorm is fp32 with warp
+// shuffles (torch.nn.LayerNorm: biased variance, eps inside the root).
+// Why mma.sync and not tcgen05: at T ~ 2k tokens a 128-token tcgen05 tile gives 16 CTAs on 148 SMs, and every CTA has
+// to pull all three weight matrices through its own L2 port; 32-token tiles put the same chain on 64+ SMs.  The kernel
+// is bound by that weight stream and by the dependent GEMM chain, not by tensor throughput (0.67 GFLOP per call).
+#include <cuda_fp16.h>
+#include <type_traits>
+#include "geotx_common.cuh"
+#include "host_util.h"
+
+namespace geotx {
+
+constexpr int PA_BM = 32;        // tokens per CTA
+constexpr int PA_THREADS = 256;  // 8 warps: each owns N / 8 output columns of every GEMM
+constexpr int PA_KC = 32;        // K chunk of the weight ring (halves)
+constexpr int PA_STAGES = 3;
+constexpr int PA_WPITCH = PA_KC * 2 + 16;  // bytes per weight row in a stage: 80 = 16 * 5 (odd: conflict-free ldmatrix)
+
+struct PostAttnArgs {
+    const float* hidden; long long ld_hidden;   // attention output [T, C]
+    const float* x_in; long long ld_x;          // the layer's input tokens (residual) [T, C]
+    float* out; long long ld_out;               // [T, C]
+    const __half* w_lin; const float* b_lin;    // [C][C]
+    const float* g1; const float* be1;          // attention.norm
+    const __half* w_exp; const float* b_exp;    // [2C][C]
+    const __half* w_sq; const float* b_sq;      // [C][2C]
+    const float* g2; const float* be2;          // output.norm
+    float eps1, eps2;
+    int T;
+};
+
+__device__ __forceinline__ void pa_ldsm4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void pa_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pa_pack(float lo, float hi) {  // saturating: a stray large activation stays finite
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ void pa_cp16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+
+template <int C>
+struct PACfg {
+    static constexpr int A_PITCH = C * 2 + 16;        // half A operand [32][C]      (bytes, odd multiple of 16)
+    static constexpr int E_PITCH = 2 * C * 2 + 16;    // half A operand [32][2C]
+    static constexpr int X_PITCH = C + 4;             // fp32 staging / residual [32][C] (floats)
+    static constexpr int STAGE_BYTES = 2 * C * PA_WPITCH;  // the widest GEMM (N = 2C) sizes a stage
+    static constexpr int OFF_A = 0;
+    static constexpr int OFF_E = OFF_A + PA_BM * A_PITCH;
+    static constexpr int OFF_X = OFF_E + PA_BM * E_PITCH;
+    static constexpr int OFF_W = OFF_X + PA_BM * X_PITCH * 4;
+    static constexpr int SMEM = OFF_W + PA_STAGES * STAGE_BYTES;
+    // chunk schedule: GEMM 0 (linear: N = C, K = C), 1 (expand: N = 2C, K = C), 2 (squeeze: N = C, K = 2C)
+    static constexpr int CH0 = C / PA_KC, CH1 = C / PA_KC, CH2 = 2 * C / PA_KC, CHUNKS = CH0 + CH1 + CH2;
+};
+
+template <int C>
+__global__ void __launch_bounds__(PA_THREADS, 1) post_attention_kernel(const PostAttnArgs p) {
+    using Cfg = PACfg<C>;
+    extern __shared__ __align__(16) unsigned char pa_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const int row0 = blockIdx.x * PA_BM;
+    const uint32_t s_base = smem_u32(pa_smem);
+    const uint32_t sA = s_base + Cfg::OFF_A, sE = s_base + Cfg::OFF_E, sW = s_base + Cfg::OFF_W;
+    float* const sX = reinterpret_cast<float*>(pa_smem + Cfg::OFF_X);
+
+    // weight chunk c of the flat schedule -> ring stage c % 3 (cp.async, 16 B per request)
+    auto issue = [&](int c) {
+        if (c < Cfg::CHUNKS) {
+            const __half* w;
+            int N, K, k0;
+            if (c < Cfg::CH0) { w = p.w_lin; N = C; K = C; k0 = c * PA_KC; }
+            else if (c < Cfg::CH0 + Cfg::CH1) { w = p.w_exp; N = 2 * C; K = C; k0 = (c - Cfg::CH0) * PA_KC; }
+            else { w = p.w_sq; N = C; K = 2 * C; k0 = (c - Cfg::CH0 - Cfg::CH1) * PA_KC; }
+            const uint32_t dst = sW + (c % PA_STAGES) * Cfg::STAGE_BYTES;
+            for (int e = tid; e < N * 4; e += PA_THREADS) {  // 4 x 16 B per weight row
+                const int n = e >> 2, part = e & 3;
+                pa_cp16(dst + n * PA_WPITCH + part * 16, w + (size_t)n * K + k0 + part * 8);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");  // one group per chunk slot, empty past the end
+    };
+
+    issue(0);
+    issue(1);
+    // the tile's attention output -> half A operand
+    for (int e = tid; e < PA_BM * (C / 4); e += PA_THREADS) {
+        const int r = e / (C / 4), c4 = e % (C / 4);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row0 + r < p.T) v = __ldg(reinterpret_cast<const float4*>(p.hidden + (size_t)(row0 + r) * p.ld_hidden) + c4);
+        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(pa_pack(v.x, v.y)),
+                     "r"(pa_pack(v.z, v.w)) : "memory");
+    }
+
+    // one GEMM of the chain: acc[mt][nt] (2 m-tiles x NT n-tiles of this warp's N / 8 columns) += A (smem, half) x W^T
+    auto gemm = [&](auto& acc, auto nt_tag, uint32_t a_addr, int a_pitch, int chunk0, int chunks) {
+        constexpr int NT = decltype(nt_tag)::value;
+        const int n_warp = warp * NT * 8;
+        for (int c = 0; c < chunks; ++c) {
+            asm volatile("cp.async.wait_group 1;" ::: "memory");  // chunk (chunk0 + c) has landed
+            __syncthreads();                                      // ... for every thread; stage (c+2) % 3 is free again
+            issue(chunk0 + c + 2);
+            const uint32_t w_addr = sW + ((chunk0 + c) % PA_STAGES) * Cfg::STAGE_BYTES;
+#pragma unroll
+            for (int ks = 0; ks < PA_KC / 16; ++ks) {
+                uint32_t a[2][4];
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+                    pa_ldsm4(a[mt], a_addr + (mt * 16 + (lane & 15)) * a_pitch + (c * PA_KC + ks * 16 + (lane >> 4) * 8) * 2);
+#pragma unroll
+                for (int np = 0; np < NT / 2; ++np) {  // two n-tiles per ldmatrix.x4
+                    uint32_t b[4];
+                    pa_ldsm4(b, w_addr + (n_warp + np * 16 + (lane & 7) + ((lane >> 4) & 1) * 8) * PA_WPITCH +
+                                    (ks * 16 + ((lane >> 3) & 1) * 8) * 2);
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt) {
+                        pa_mma(acc[mt][2 * np], a[mt], b[0], b[1]);
+                        pa_mma(acc[mt][2 * np + 1], a[mt], b[2], b[3]);
+                    }
+                }
+            }
+        }
+    };
+
+    // LayerNorm of the 32 rows staged in sX (fp32): warp w normalises rows 4w .. 4w+3, lane owns C / 32 channels
+    auto layer_norm = [&](const float* gamma, const float* beta, float eps, bool to_global) {
+        constexpr int PER = C / 32;
+#pragma unroll 1
+        for (int rr = 0; rr < PA_BM / 8; ++rr) {
+            const int r = warp * (PA_BM / 8) + rr;
+            float* row = sX + r * Cfg::X_PITCH;
+            float v[PER];
+            float sum = 0.f;
+#pragma unroll
+            for (int i = 0; i < PER / 4; ++i) {
+                const float4 t = *reinterpret_cast<const float4*>(row + (lane + 32 * i) * 4);
+                v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+                sum += (t.x + t.y) + (t.z + t.w);
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+            const float mean = sum / (float)C;
+            float sq = 0.f;
+#pragma unroll
+            for (int i = 0; i < PER; ++i) sq += (v[i] - mean) * (v[i] - mean);
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, off);
+            const float rstd = rsqrtf(sq / (float)C + eps);
+#pragma unroll
+            for (int i = 0; i < PER / 4; ++i) {
+                const int c4 = lane + 32 * i;
+                const float4 gm = __ldg(reinterpret_cast<const float4*>(gamma) + c4), bt = __ldg(reinterpret_cast<const float4*>(beta) + c4);
+                float4 o;
+                o.x = (v[4 * i] - mean) * rstd * gm.x + bt.x;
+                o.y = (v[4 * i + 1] - mean) * rstd * gm.y + bt.y;
+                o.z = (v[4 * i + 2] - mean) * rstd * gm.z + bt.z;
+                o.w = (v[4 * i + 3] - mean) * rstd * gm.w + bt.w;
+                if (to_global) {
+                    if (row0 + r < p.T) *reinterpret_cast<float4*>(p.out + (size_t)(row0 + r) * p.ld_out + c4 * 4) = o;
+                } else {
+                    *reinterpret_cast<float4*>(row + c4 * 4) = o;  // x1 stays in fp32 for the second residual
+                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(pa_pack(o.x, o.y)),
+                                 "r"(pa_pack(o.z, o.w)) : "memory");  // ... and as the expand GEMM's A operand
+                }
+            }
+        }
+    };
+
+    // ---- GEMM 0: linear(hidden); + bias + residual -> sX; LayerNorm -> x1 (sX fp32, sA half) ----
+    {
+        float acc[2][C / 64][4] = {};
+        gemm(acc, std::integral_constant<int, C / 64>{}, sA, Cfg::A_PITCH, 0, Cfg::CH0);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < C / 64; ++nt) {
+                const int col = warp * (C / 8) + nt * 8 + 2 * q;
+                const float2 bias = __ldg(reinterpret_cast<const float2*>(p.b_lin + col));
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int r = mt * 16 + g + 8 * h;
+                    float2 res = make_float2(0.f, 0.f);
+                    if (row0 + r < p.T) res = __ldg(reinterpret_cast<const float2*>(p.x_in + (size_t)(row0 + r) * p.ld_x + col));
+                    *reinterpret_cast<float2*>(sX + r * Cfg::X_PITCH + col) =
+                        make_float2(acc[mt][nt][2 * h] + bias.x + res.x, acc[mt][nt][2 * h + 1] + bias.y + res.y);
+                }
+            }
+    }
+    __syncthreads();  // all of sX written; every warp is done reading sA (hidden)
+    layer_norm(p.g1, p.be1, p.eps1, false);
+    // ---- GEMM 1: ReLU(expand(x1) + bias) -> sE (half).  Its first barrier orders the LayerNorm's writes ----
+    {
+        float acc[2][C / 32][4] = {};
+        gemm(acc, std::integral_constant<int, C / 32>{}, sA, Cfg::A_PITCH, Cfg::CH0, Cfg::CH1);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < C / 32; ++nt) {
+                const int col = warp * (C / 4) + nt * 8 + 2 * q;
+                const float2 bias = __ldg(reinterpret_cast<const float2*>(p.b_exp + col));
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int r = mt * 16 + g + 8 * h;
+                    asm volatile("st.shared.b32 [%0], %1;" ::"r"(sE + r * Cfg::E_PITCH + col * 2),
+                                 "r"(pa_pack(fmaxf(acc[mt][nt][2 * h] + bias.x, 0.f), fmaxf(acc[mt][nt][2 * h + 1] + bias.y, 0.f)))
+                                 : "memory");
+                }
+            }
+    }
+    // ---- GEMM 2: squeeze(e) + bias + x1 -> sX (in place: each element is read and written by one thread); LayerNorm ----
+    {
+        float acc[2][C / 64][4] = {};
+        gemm(acc, std::integral_constant<int, C / 64>{}, sE, Cfg::E_PITCH, Cfg::CH0 + Cfg::CH1, Cfg::CH2);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < C / 64; ++nt) {
+                const int col = warp * (C / 8) + nt * 8 + 2 * q;
+                const float2 bias = __ldg(reinterpret_cast<const float2*>(p.b_sq + col));
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float2* x = reinterpret_cast<float2*>(sX + (mt * 16 + g + 8 * h) * Cfg::X_PITCH + col);
+                    const float2 x1 = *x;
+                    *x = make_float2(acc[mt][nt][2 * h] + bias.x + x1.x, acc[mt][nt][2 * h + 1] + bias.y + x1.y);
+                }
+            }
+    }
+    __syncthreads();
+    layer_norm(p.g2, p.be2, p.eps2, true);
+}
+
+__global__ void f32_to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, long long count) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) dst[i] = __float2half_rn(src[i]);
+}
+
+}  // namespace geotx
+
+using namespace geotx;
+
+extern "C" int geotx_f32_to_f16(const float* src, void* dst, int64_t count, void* stream) {
+    GEOTX_REQUIRE(src && dst && count > 0, "geotx_f32_to_f16: bad arguments");
+    const long long blocks = (count + 255) / 256;
+    GEOTX_REQUIRE(blocks < 2147483647LL, "geotx_f32_to_f16: too many elements");
+    f32_to_f16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__half*)dst, count);
+    return launch_status("geotx_f32_to_f16");
+}
+
+extern "C" int geotx_post_attention(const float* hidden, int64_t ld_hidden, const float* x_in, int64_t ld_x, int64_t T,
+                                    int C, const void* w_lin_f16, const float* b_lin, const float* gamma1,
+                                    const float* beta1, float eps1, const void* w_expand_f16, const float* b_expand,
+                                    const void* w_squeeze_f16, const float* b_squeeze, const float* gamma2,
+                                    const float* beta2, float eps2, float* out, int64_t ld_out, void* stream) {
+    GEOTX_REQUIRE(hidden && x_in && w_lin_f16 && b_lin && gamma1 && beta1 && w_expand_f16 && b_expand && w_squeeze_f16 &&
+                      b_squeeze && gamma2 && beta2 && out, "geotx_post_attention: null pointer");
+    GEOTX_REQUIRE(C == 128 || C == 256, "geotx_post_attention: C must be 128 or 256 (got %d)", C);
+    GEOTX_REQUIRE(T > 0 && T < 2147483647LL / 2, "geotx_post_attention: bad token count");
+    GEOTX_REQUIRE(ld_hidden >= C && ld_x >= C && ld_out >= C && ld_hidden % 4 == 0 && ld_x % 4 == 0 && ld_out % 4 == 0,
+                  "geotx_post_attention: row strides must be >= C and multiples of 4 floats");
+    GEOTX_REQUIRE((((uintptr_t)hidden | (uintptr_t)x_in | (uintptr_t)out | (uintptr_t)w_lin_f16 | (uintptr_t)w_expand_f16 |
+                    (uintptr_t)w_squeeze_f16 | (uintptr_t)gamma1 | (uintptr_t)beta1 | (uintptr_t)gamma2 | (uintptr_t)beta2 |
+                    (uintptr_t)b_lin | (uintptr_t)b_expand | (uintptr_t)b_squeeze) & 15) == 0,
+                  "geotx_post_attention: pointers must be 16-byte aligned");
+    PostAttnArgs p;
+    p.hidden = hidden; p.ld_hidden = ld_hidden;
+    p.x_in = x_in; p.ld_x = ld_x;
+    p.out = out; p.ld_out = ld_out;
+    p.w_lin = (const __half*)w_lin_f16; p.b_lin = b_lin;
+    p.g1 = gamma1; p.be1 = beta1;
+    p.w_exp = (const __half*)w_expand_f16; p.b_exp = b_expand;
+    p.w_sq = (const __half*)w_squeeze_f16; p.b_sq = b_squeeze;
+    p.g2 = gamma2; p.be2 = beta2;
+    p.eps1 = eps1; p.eps2 = eps2;
+    p.T = (int)T;
+    const int grid = (int)((T + PA_BM - 1) / PA_BM);
+    auto launch = [&](auto kernel, int smem) -> int {
+        int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                            "geotx_post_attention: shared memory");
+        if (rc) return rc;
+        kernel<<<grid, PA_THREADS, smem, (cudaStream_t)stream>>>(p);
+        return 0;
+    };
+    int rc = C == 256 ? launch(post_attention_kernel<256>, PACfg<256>::SMEM) : launch(post_attention_kernel<128>, PACfg<128>::SMEM);
+    if (rc) return rc;
+    return launch_status("geotx_post_attention");
+}

@@ -98,6 +98,42 @@ def _forward_only_guard(module, *tensors):
             'freeze the parameters and inputs.')
 
 
+def _dense_own():
+    """GEOTX_DENSE: 'own' (default) routes the token-wise Linears / LayerNorms of the fused schedule through the
+    hand-written kernels K13 (geotx_linear_f16) and K4f (geotx_post_attention); 'cublas' keeps round 1's cuBLASLt TF32
+    GEMMs + K4 (also what shapes outside the kernels' tile constraints take)."""
+    mode = os.environ.get('GEOTX_DENSE', 'own')
+    if mode not in ('own', 'cublas'):
+        raise ValueError(f"GEOTX_DENSE must be 'own' or 'cublas', got {mode!r}")
+    return mode == 'own'
+
+
+def _half_of(owner, name, t):
+    """IEEE-half copy of weight `t`, cached on `owner` and rebuilt when `t` changes (new storage or in-place update)."""
+    cache = owner.__dict__.setdefault('_half_cache', {})
+    key = (t.data_ptr(), t._version)
+    ent = cache.get(name)
+    if ent is None or ent[0] != key:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError('a weight changed since its half copy was made; run one forward outside CUDA graph '
+                               'capture first')
+        ent = (key, ops.to_half(t.detach()))
+        cache[name] = ent
+    return ent[1]
+
+
+def _linear(x, owner, name, weight, bias, out=None):
+    """nn.Linear on K13 when the shape fits its tiles and GEOTX_DENSE allows it, else F.linear."""
+    N, K = weight.shape
+    if _dense_own() and x.is_cuda and x.dtype == torch.float32 and ops.linear_supported(K, N) and x.stride(-1) == 1:
+        return ops.linear_f16(x, _half_of(owner, name, weight), bias, out=out)
+    y = F.linear(x, weight, bias)
+    if out is not None:
+        out.copy_(y)
+        return out
+    return y
+
+
 class SinusoidalPositionalEmbedding(nn.Module):
     """positional_embedding.py:8-34.  Only the `div_term` buffer matters on the fused path (the kernels read it
     instead of recomputing it); forward() is kept for API parity and runs as plain device ops."""
@@ -665,6 +701,13 @@ class RPEConditionalTransformer(nn.Module):
     def _post_attention(layer, hidden, x_in, out=None):
         """rpe_transformer.py:101-103 / vanilla_transformer.py:99-101 + output_layer.py:15-21 on (1, T, C) tokens."""
         al, ao = layer.attention, layer.output
+        C = hidden.shape[-1]
+        if _dense_own() and C in (128, 256) and isinstance(ao.activation, nn.ReLU) and hidden.dtype == torch.float32:
+            return ops.post_attention(hidden, x_in, _half_of(al.linear, 'w', al.linear.weight), al.linear.bias,
+                                      al.norm.weight, al.norm.bias, al.norm.eps,
+                                      _half_of(ao.expand, 'w', ao.expand.weight), ao.expand.bias,
+                                      _half_of(ao.squeeze, 'w', ao.squeeze.weight), ao.squeeze.bias,
+                                      ao.norm.weight, ao.norm.bias, ao.norm.eps, out=out)
         h = F.linear(hidden, al.linear.weight, al.linear.bias)
         x1 = ops.add_layernorm(h, x_in, al.norm.weight, al.norm.bias, al.norm.eps)
         T, C = x1.shape[1], x1.shape[2]
@@ -688,7 +731,7 @@ class RPEConditionalTransformer(nn.Module):
             H = att.num_heads
             if block == 'self':
                 w, b = att.fused_qkvp()
-                y = F.linear(x, w, b)  # (1, T, 3C + H*C): q | k | v | folded query per head
+                y = _linear(x, att, 'qkvp', w, b)  # (1, T, 3C + H*C): q | k | v | folded query per head
                 hidden = x.new_empty(1, T, C)
                 cur = side = None
                 streamed = any(isinstance(e, StreamedEmbedding) for e in embs)
@@ -732,12 +775,12 @@ class RPEConditionalTransformer(nn.Module):
                 # (parallel=True reads the old one: no second projection at all).
                 x_new = torch.empty_like(x)
                 w3, b3 = att.fused_qkv()
-                y = F.linear(x, w3, b3)  # (1, T, 3C): q | k | v
+                y = _linear(x, att, 'qkv', w3, b3)  # (1, T, 3C): q | k | v
                 order = ((0, N, N, T, masks1), (N, T, 0, N, masks0))  # (query cloud, memory cloud, memory mask)
                 for step, (qlo, qhi, mlo, mhi, mask) in enumerate(order):
                     if step == 1 and not self.parallel:
                         wkv, bkv = att.fused_kv()
-                        kv = F.linear(x_new[:, mlo:mhi], wkv, bkv)
+                        kv = _linear(x_new[:, mlo:mhi], att, 'kv', wkv, bkv)
                         k_mem, v_mem = kv[:, :, :C], kv[:, :, C:]
                     else:
                         k_mem, v_mem = y[:, mlo:mhi, C:2 * C], y[:, mlo:mhi, 2 * C:]
@@ -828,6 +871,15 @@ class GeometricTransformer(nn.Module):
                 return 0
         return self.regenerate_slab_bytes
 
+    def _in_proj_into(self, feats, out, w_t):
+        """geotransformer.py:140-141 for one cloud, written into its slice of the joint token buffer."""
+        w = self.in_proj.weight
+        if _dense_own() and feats.dtype == torch.float32 and ops.linear_supported(w.shape[1], w.shape[0]) and \
+                feats.stride(-1) == 1:
+            ops.linear_f16(feats, _half_of(self.in_proj, 'w', w), self.in_proj.bias, out=out)
+        else:
+            torch.addmm(self.in_proj.bias, feats, w_t, out=out)
+
     def _direct_scores(self, e_dtype, batch, feats):
         """Whether the 'self' blocks take their scores straight from the geometry (K3r) instead of from a stored E."""
         if self.e_mode not in ('auto', 'scores') or 'self' not in self.transformer.blocks:
@@ -862,12 +914,12 @@ class GeometricTransformer(nn.Module):
             with torch.cuda.stream(side):
                 src_geom = self.embedding.geometry(src_points)
                 if one_buffer:
-                    torch.addmm(self.in_proj.bias, src_feats[0], w_t, out=x[0, N:])
+                    self._in_proj_into(src_feats[0], x[0, N:], w_t)
                 else:
                     src_proj = self.in_proj(src_feats)
             ref_geom = self.embedding.geometry(ref_points)
             if one_buffer:
-                torch.addmm(self.in_proj.bias, ref_feats[0], w_t, out=x[0, :N])
+                self._in_proj_into(ref_feats[0], x[0, :N], w_t)
                 ref_feats, src_feats = x[:, :N], x[:, N:]
             else:
                 ref_feats, src_feats = self.in_proj(ref_feats), src_proj
@@ -888,7 +940,7 @@ class GeometricTransformer(nn.Module):
             if both is not None:
                 # the fused schedule returns two slices of one (1, N+M, C) buffer: project them in one GEMM
                 n = ref_feats.shape[1]
-                out = self.out_proj(both)
+                out = _linear(both, self.out_proj, 'w', self.out_proj.weight, self.out_proj.bias)
                 return out[:, :n], out[:, n:]
             return self.out_proj(ref_feats), self.out_proj(src_feats)
 

@@ -642,3 +642,80 @@ def rpe_scores_cheb(geom, coef, qt, sigma_d, factor_a, reduce_mean=False, max_d_
               coef.angle_index_max, coef.ka_tiles, int(max_d_set), float(sigma_d), float(factor_a), int(bool(reduce_mean)),
               _p(qt), int(qt.stride(0)), int(qt.stride(1)), int(qt.stride(2)), H, _p(out), _p(coef.overflow), _stream())
     return out
+
+
+def to_half(t):
+    """fp32 CUDA tensor -> contiguous IEEE-half copy (the weight format of linear_f16 / post_attention)."""
+    _check(t, 't', torch.float32)
+    t = t.contiguous()
+    out = torch.empty(t.shape, dtype=torch.float16, device=t.device)
+    _abi.call('geotx_f32_to_f16', _p(t), _p(out), t.numel(), _stream())
+    return out
+
+
+def _rows2d(t, name, cols):
+    """(…, cols) fp32 CUDA tensor whose leading dimensions flatten into equally strided rows -> (rows, row stride)."""
+    _check(t, name, torch.float32)
+    if t.shape[-1] != cols or (cols > 1 and t.stride(-1) != 1):
+        raise RuntimeError(f'{name}: last dimension must be dense and of size {cols}, got {tuple(t.shape)} strides {t.stride()}')
+    rows = t.numel() // cols
+    lead = [(s, st) for s, st in zip(t.shape[:-1], t.stride()[:-1]) if s != 1]
+    ld = lead[-1][1] if lead else cols
+    for (s0, st0), (s1, st1) in zip(lead[:-1], lead[1:]):
+        if st0 != s1 * st1:
+            raise RuntimeError(f'{name}: rows are not equally strided ({tuple(t.shape)}, strides {t.stride()})')
+    return rows, ld
+
+
+def linear_supported(K, N):
+    return K >= 32 and K % 32 == 0 and N >= 64 and N % 64 == 0
+
+
+def linear_f16(x, w_half, bias, out=None, relu=False):
+    """y = x W^T + b (nn.Linear semantics) on the hand-written mma.sync kernel K13: x (..., K) fp32 with equally strided
+    rows, w_half (N, K) IEEE half (`to_half(weight)`), bias (N,) fp32 or None -> (..., N) fp32 (into `out` if given;
+    rows of `out` may be strided).  K % 32 == 0, N % 64 == 0."""
+    if not isinstance(w_half, torch.Tensor) or not w_half.is_cuda or w_half.dtype != torch.float16 or w_half.dim() != 2 \
+            or not w_half.is_contiguous():
+        raise RuntimeError('w_half must be a contiguous 2-d float16 CUDA tensor (N, K)')
+    N, K = w_half.shape
+    if not linear_supported(K, N):
+        raise RuntimeError(f'linear_f16: K={K} must be a multiple of 32 and N={N} a multiple of 64')
+    T, ld_x = _rows2d(x, 'x', K)
+    if bias is not None:
+        _check(bias, 'bias', torch.float32, 1)
+    if out is None:
+        out = torch.empty(*x.shape[:-1], N, dtype=torch.float32, device=x.device)
+    T_out, ld_y = _rows2d(out, 'out', N)
+    if T_out != T:
+        raise RuntimeError(f'out has {T_out} rows, x has {T}')
+    _abi.call('geotx_linear_f16', _p(x), ld_x, T, K, _p(w_half), _p(bias), N, int(bool(relu)), _p(out), ld_y, _stream())
+    return out
+
+
+def post_attention(hidden, x_in, w_lin, b_lin, g1, be1, eps1, w_exp, b_exp, w_sq, b_sq, g2, be2, eps2, out=None):
+    """K4f: LayerNorm(x1 + squeeze(ReLU(expand(x1)))) with x1 = LayerNorm(linear(hidden) + x_in) in one kernel
+    (rpe_transformer.py:101-103 / vanilla_transformer.py:99-101 + output_layer.py:15-21).  hidden, x_in (..., C) fp32
+    with equally strided rows, C in {128, 256}; w_* IEEE-half copies of the nn.Linear weights; the rest fp32."""
+    C = hidden.shape[-1]
+    T, ld_h = _rows2d(hidden, 'hidden', C)
+    T2, ld_x = _rows2d(x_in, 'x_in', C)
+    if T2 != T:
+        raise RuntimeError(f'x_in has {T2} rows, hidden has {T}')
+    for name, t, shape in (('w_lin', w_lin, (C, C)), ('w_exp', w_exp, (2 * C, C)), ('w_sq', w_sq, (C, 2 * C))):
+        if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.float16 or tuple(t.shape) != shape \
+                or not t.is_contiguous():
+            raise RuntimeError(f'{name} must be a contiguous float16 CUDA tensor of shape {shape}')
+    for name, t, size in (('b_lin', b_lin, C), ('g1', g1, C), ('be1', be1, C), ('b_exp', b_exp, 2 * C), ('b_sq', b_sq, C),
+                          ('g2', g2, C), ('be2', be2, C)):
+        _check(t, name, torch.float32, 1)
+        if t.numel() != size:
+            raise RuntimeError(f'{name} must hold {size} elements, got {t.numel()}')
+    if out is None:
+        out = torch.empty(hidden.shape, dtype=torch.float32, device=hidden.device)
+    T3, ld_o = _rows2d(out, 'out', C)
+    if T3 != T:
+        raise RuntimeError(f'out has {T3} rows, hidden has {T}')
+    _abi.call('geotx_post_attention', _p(hidden), ld_h, _p(x_in), ld_x, T, C, _p(w_lin), _p(b_lin), _p(g1), _p(be1),
+              float(eps1), _p(w_exp), _p(b_exp), _p(w_sq), _p(b_sq), _p(g2), _p(be2), float(eps2), _p(out), ld_o, _stream())
+    return out
