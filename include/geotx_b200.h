@@ -202,6 +202,24 @@ int geotx_point_to_node_partition(const float* points, int num_points, const flo
                                   int64_t* node_knn_indices, uint8_t* node_knn_masks, float* node_knn_points,
                                   void* workspace, void* stream);
 
+/* Allocation-free variant of geotx_point_to_node_partition.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same inputs, outputs, arithmetic and results as geotx_point_to_node_partition, but
+ * the workspace is a file-scope `static __device__` array of GEOTX_P2N_STATIC_SCRATCH_BYTES inside the library (every
+ * GPU that loads the library holds it until the process exits); the call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine) and takes no workspace argument.  Sizes whose workspace
+ * (geotx_p2n_workspace_bytes(num_points, num_nodes, point_limit)) exceeds GEOTX_P2N_STATIC_SCRATCH_BYTES are rejected
+ * with GEOTX_E_ARG -- e.g. 65 536 points x 4096 nodes (1.36 MB) fits, 131 072 points do not.
+ * All calls on a device share the array, which keeps the last call's contents (each call clears the counters it needs):
+ * calls on ONE stream are ordered and safe; calls that overlap on the GPU (different streams, or this entry point
+ * replayed from two graphs at once) RACE and must be serialised by the caller.  The device must be current. */
+#define GEOTX_P2N_STATIC_SCRATCH_BYTES (2 * 1024 * 1024)
+int64_t geotx_p2n_static_scratch_bytes(void);
+int geotx_point_to_node_partition_static(const float* points, int num_points, const float* nodes, int num_nodes,
+                                         int point_limit, int64_t* point_to_node, int64_t* node_sizes,
+                                         uint8_t* node_masks, int64_t* node_knn_indices, uint8_t* node_knn_masks,
+                                         float* node_knn_points, void* stream);
+
 /* Optimal transport behind the coarse matching: modules/sinkhorn/learnable_sinkhorn.py:13-66
  * (`LearnableLogOptimalTransport.forward`, called at experiments/<cfg>/model.py:187-189): scores padded with a dustbin
  * row and column holding alpha, masked rows / columns filled with -inf_value, num_iterations log-domain Sinkhorn

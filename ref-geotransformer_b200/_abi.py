@@ -34,6 +34,8 @@ SIGNATURES = {
     'geotx_superpoint_matching': (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
     'geotx_p2n_workspace_bytes': (_i64, [_i, _i, _i]),
     'geotx_point_to_node_partition': (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    'geotx_p2n_static_scratch_bytes': (_i64, []),
+    'geotx_point_to_node_partition_static': (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
     'geotx_log_optimal_transport': (_i, [_p, _p, _p, _p, _i, _f, _i, _i, _i, _p, _p]),
     'geotx_weighted_procrustes': (_i, [_p, _p, _p, _i, _i, _f, _f, _p, _p]),
     'geotx_radius_neighbors': (_i, [_p, _p, _p, _p, _i, _f, _i, _p, _p, _p, _p]),
@@ -69,6 +71,7 @@ GEOTX_F16 = 2
 KERNELS_PER_CALL = {'geotx_gse_knn': 2,  # pack_points + knn
                     'geotx_superpoint_matching': 10,  # prepare, scores, sums, 6 select passes, collect
                     'geotx_point_to_node_partition': 4,  # assign, offsets, scatter, select
+                    'geotx_point_to_node_partition_static': 4,
                     'geotx_grid_subsample': 14,
                     'geotx_local_global_registration': 4}  # 7 per batch element (bounds, clear, accumulate, count, scan, emit, advance)
 

@@ -17,6 +17,7 @@
 // y = point, exactly pairwise_distance(nodes, points)); equal distances are ordered by the smaller index
 // (torch.min / torch.topk leave that order unspecified).
 #include "geotx_common.cuh"
+#include <mutex>
 
 namespace geotx {
 
@@ -268,4 +269,81 @@ extern "C" int geotx_point_to_node_partition(const float* points, int num_points
     p2n_select_kernel<<<num_nodes, 128, smem, st>>>(points, num_points, point_limit, sort_n, w,
                                                     (long long*)node_knn_indices, node_knn_masks, node_knn_points);
     return launch_status("geotx_point_to_node_partition");
+}
+
+// ---- allocation-free variant (no counterpart in the reference; see include/geotx_b200.h) --------------------------
+// The workspace of the entry point above lives in a file-scope device array instead of caller memory.  Every GPU that
+// loads the library holds these GEOTX_P2N_STATIC_SCRATCH_BYTES until the process exits.  In host code the array's name
+// is only a handle: its device address is looked up once per device with cudaGetSymbolAddress (that device current) and
+// cached; the kernels receive that address.  All calls on one device share the array, so calls that overlap on the GPU
+// (different streams) race; calls on one stream are ordered and each call clears the counters it needs.
+static __device__ __align__(256) unsigned char g_p2n_static_scratch[GEOTX_P2N_STATIC_SCRATCH_BYTES];
+
+constexpr int P2N_MAX_DEVICES = 64;
+static void* g_p2n_static_addr[P2N_MAX_DEVICES];  // device address of g_p2n_static_scratch, per device (0 = not yet)
+static std::mutex g_p2n_static_mutex;
+
+static int p2n_static_scratch_address(void** out) {
+    int dev = -1;
+    int rc = check_cuda(cudaGetDevice(&dev), "geotx_point_to_node_partition_static: cudaGetDevice");
+    if (rc) return rc;
+    GEOTX_REQUIRE(dev >= 0 && dev < P2N_MAX_DEVICES, "geotx_point_to_node_partition_static: device %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_p2n_static_mutex);
+    if (!g_p2n_static_addr[dev]) {
+        void* ptr = nullptr;
+        rc = check_cuda(cudaGetSymbolAddress(&ptr, g_p2n_static_scratch),
+                        "geotx_point_to_node_partition_static: cudaGetSymbolAddress");
+        if (rc) return rc;
+        GEOTX_REQUIRE(ptr && ((uintptr_t)ptr & 255) == 0,
+                      "geotx_point_to_node_partition_static: scratch symbol resolved to a bad address");
+        g_p2n_static_addr[dev] = ptr;
+    }
+    *out = g_p2n_static_addr[dev];
+    return GEOTX_OK;
+}
+
+extern "C" int64_t geotx_p2n_static_scratch_bytes(void) { return (int64_t)GEOTX_P2N_STATIC_SCRATCH_BYTES; }
+
+extern "C" int geotx_point_to_node_partition_static(const float* points, int num_points, const float* nodes,
+                                                    int num_nodes, int point_limit, int64_t* point_to_node,
+                                                    int64_t* node_sizes, uint8_t* node_masks, int64_t* node_knn_indices,
+                                                    uint8_t* node_knn_masks, float* node_knn_points, void* stream) {
+    GEOTX_REQUIRE(points && nodes && point_to_node && node_masks && node_knn_indices && node_knn_masks,
+                  "geotx_point_to_node_partition_static: null pointer");
+    GEOTX_REQUIRE(num_points > 0 && num_nodes > 0,
+                  "geotx_point_to_node_partition_static: empty input (points=%d nodes=%d)", num_points, num_nodes);
+    GEOTX_REQUIRE(point_limit >= 1 && point_limit <= num_points,
+                  "geotx_point_to_node_partition_static: selected index k out of range (point_limit=%d, points=%d)",
+                  point_limit, num_points);
+    GEOTX_REQUIRE(point_limit <= GEOTX_MAX_POINT_LIMIT, "geotx_point_to_node_partition_static: point_limit=%d > %d",
+                  point_limit, GEOTX_MAX_POINT_LIMIT);
+    const size_t need = p2n_layout(num_points, num_nodes, nullptr, nullptr);
+    GEOTX_REQUIRE(need <= (size_t)GEOTX_P2N_STATIC_SCRATCH_BYTES,
+                  "geotx_point_to_node_partition_static: points=%d nodes=%d need %zu bytes of scratch, the built-in "
+                  "array holds %d; use geotx_point_to_node_partition with a caller workspace",
+                  num_points, num_nodes, need, (int)GEOTX_P2N_STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    int rc = p2n_static_scratch_address(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    P2NWorkspace w;
+    p2n_layout(num_points, num_nodes, (char*)scratch, &w);
+    // the array keeps the previous call's contents: the histogram and the scatter cursors must start at zero
+    rc = check_cuda(cudaMemsetAsync(w.counts, 0, (size_t)num_nodes * 8, st), "geotx_point_to_node_partition_static: memset");
+    if (rc) return rc;
+    p2n_assign_kernel<<<(num_points + P2N_POINTS_PER_BLOCK - 1) / P2N_POINTS_PER_BLOCK,
+                        P2N_POINTS_PER_BLOCK * P2N_SLICES, 0, st>>>(points, num_points, nodes, num_nodes,
+                                                                    (long long*)point_to_node, w);
+    p2n_offsets_kernel<<<1, 1024, 0, st>>>(num_nodes, w, (long long*)node_sizes, node_masks);
+    p2n_scatter_kernel<<<(num_points + 255) / 256, 256, 0, st>>>(num_points, w);
+    const int sort_n = p2n_sort_n(point_limit);
+    const size_t smem = (size_t)sort_n * 8;
+    if (smem > 48 * 1024) {
+        rc = check_cuda(cudaFuncSetAttribute(p2n_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                        "geotx_point_to_node_partition_static: shared memory");
+        if (rc) return rc;
+    }
+    p2n_select_kernel<<<num_nodes, 128, smem, st>>>(points, num_points, point_limit, sort_n, w,
+                                                    (long long*)node_knn_indices, node_knn_masks, node_knn_points);
+    return launch_status("geotx_point_to_node_partition_static");
 }
