@@ -5,20 +5,28 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One "step" = one forward of the hot path over one synthetic registration pair of the workload (BASELINE.json
-configs[1]: 3DMatch stage-4 config, N = M = 1024 superpoints, random-init weights, seed 7351).  Rank r works on its
-own pairs (pair sharding, no collective on the path; one NCCL all_gather of the outputs at the end).
+configs[1]: 3DMatch stage-4 config, N = M = 1024 superpoints, random-init weights, seed 7351) on every rank.  Rank r
+works on its own pairs (pair sharding, no collective on the path); with N > 1 the outputs of ALL timed
+steps of all ranks are gathered with one NCCL all_gather inside the timed region (after a warm-up gather).
 Prints ONE JSON line on rank 0.
 
-  value     pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks; up to N = 2048 three CUDA-graph instances
-            of the forward are in flight on three streams (independent pairs overlap; GEOTX_INFLIGHT)
-  e2e       pairs/s through PipelinedGeometricTransformer.map with HOST (pinned) inputs and a host read of the outputs
-  roofline  the dominant kernel, timed by CUDA events captured inside the forward's graph: with the tabulated embedding
-            (default) the HBM-bound RPE score kernel (algorithmic bytes / time against the measured copy bandwidth), with
-            GEOTX_EMBED=tensor the tcgen05 embedding kernel (algorithmic flops against the measured bf16 rate)
-  kernels   the other of the two; variants.other_embed_kernel: the same run with the other embedding kernel
-  cpu_baseline  the oracle (CPU restatement of the reference's formulation) on this box's host cores
+  value      pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks; up to n = 2048 three CUDA-graph instances
+             of the forward are in flight on three streams (independent pairs overlap; GEOTX_INFLIGHT)
+  e2e        pairs/s through PipelinedGeometricTransformer.map with HOST (pinned) inputs and a host read of the outputs
+  roofline   the dominant kernel of the default path, K3r (geotx_rpe_scores_cheb: low-rank embedding + folded-query
+             scores, E never stored), timed by CUDA events captured inside the forward's graph: flops the kernel
+             EXECUTES / time against the measured bf16 tensor rate, with its share of the legacy mma.sync pipe beside it
+  kernels    every other kernel class of the step, timed the same way (launches, time, share of the step)
+  variants   the same forward (a) with E stored: K2c writes it, K3a reads it (the HBM-bound formulation, both with their
+             fraction of the measured copy bandwidth); (b) with the full-rank tcgen05 embedding K2 (north_star's "% of
+             tensor-pipe peak": SURVEY.md 8d's F_min flops / time against the measured bf16 rate); (c) with the library
+             GEMM glue of round 1
+  sweep      bounded runs of 3dmatch_4096 (north_star's size) and kitti_2048 in the same process
+  configs4   BASELINE.json configs[4]: 256 pairs in total sharded over the ranks, all outputs gathered (strong scaling)
+  cpu_baseline  the reference's formulation on this box's host cores (the reference itself when its tree is on the box)
 
---impl reference times that CPU oracle alone (rank 0 only)."""
+--impl reference times the reference's CPU implementation alone (rank 0 only): the UNMODIFIED reference classes when a
+reference tree is present (GEOTX_REFERENCE_ROOT, baseline/_ref, /root/reference), else the oracle port; whole pairs."""
 import argparse
 import json
 import os
@@ -30,6 +38,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+
 WORKLOADS = {
     # name: (synth shape / config, n, m)
     '3dmatch_1024': ('3dmatch', 1024, 1024),   # BASELINE.json configs[1]  (the metric's configuration)
@@ -38,15 +47,15 @@ WORKLOADS = {
     '3dmatch_512': ('3dmatch', 512, 512),
     '3dmatch_2048': ('3dmatch', 2048, 2048),
     '3dmatch_4096': ('3dmatch', 4096, 4096),   # configs[3] sweep point named by north_star
-    '3dmatch_8192': ('3dmatch', 8192, 8192),   # configs[3]: E = 34 GB per cloud, stored
-    '3dmatch_16384': ('3dmatch', 16384, 16384),  # configs[3]: E = 137 GB per cloud: never stored, regenerated per 'self' block
+    '3dmatch_8192': ('3dmatch', 8192, 8192),
+    '3dmatch_16384': ('3dmatch', 16384, 16384),
 }
-# dram__bytes_read.sum + dram__bytes_write.sum of one rpe_scores_tc_kernel launch (ncu --set full, profiles/r01_ncu_k3a_r01.txt)
-K3A_NCU_TRAFFIC_BYTES = {'3dmatch_1024': 560.4e6}
-# dram__bytes_read.sum + dram__bytes_write.sum of one gse_embed_tc_kernel launch (ncu --set full, profiles/r01_ncu_k2_*)
-K2_NCU_TRAFFIC_BYTES = {"3dmatch_1024": 483.98e6}  # profiles/r01_ncu_k2_v4.txt
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` captures of the SHIPPED kernels
+# (profiles/r02_ncu_*.txt; None until captured)
+NCU_TRAFFIC_BYTES = {}
 METRIC = 'registration pairs/sec (embed+RPE-attn) at N superpoints'
 UNIT = 'pairs/s'
+CONFIGS4_PAIRS = 256
 
 
 def measured_peaks():
@@ -130,8 +139,16 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------------------
-# CPU legs (oracle): test infrastructure used only as the timed baseline
+# CPU legs: test infrastructure used only as the timed baseline
 # ------------------------------------------------------------------------------------------------------------
+def find_reference_root():
+    """A tree of the UNMODIFIED reference on this machine, if any (never present on a plain GPU box)."""
+    for cand in (os.environ.get('GEOTX_REFERENCE_ROOT'), os.path.join(ROOT, 'baseline', '_ref'), '/root/reference'):
+        if cand and os.path.isdir(os.path.join(cand, 'geotransformer', 'modules')):
+            return cand
+    return None
+
+
 def cpu_setup(workload):
     import torch
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
@@ -150,56 +167,97 @@ def cpu_setup(workload):
     return oracle, cfg, sd, inputs, n, m, cores
 
 
-def cpu_sample_seconds(oracle, cfg, sd, inputs, rows):
-    t0 = time.perf_counter()
-    oracle.sampled_forward(sd, cfg, *inputs, rows=rows)
-    return time.perf_counter() - t0
-
-
-def cpu_baseline(workload, budget_s=25.0):
-    """Bounded CPU baseline beside the GPU number (rank 0, N=1 only)."""
+def cpu_forward_fn(workload):
+    """-> (callable running ONE whole pair of the workload on the host cores, kind, cores, description).
+    kind 'reference': the unmodified reference classes (geotransformer.py:114-155) imported from a reference tree, run
+    whole when its (n, n, k, C) intermediates fit the host memory, else driven in query-row chunks through its own
+    submodules; kind 'port': the oracle's row-chunked restatement (no reference tree on this machine)."""
+    import torch
     oracle, cfg, sd, inputs, n, m, cores = cpu_setup(workload)
-    rows = min(64, n)
-    cpu_sample_seconds(oracle, cfg, sd, inputs, min(16, n))  # warm the thread pool / allocator
-    t = cpu_sample_seconds(oracle, cfg, sd, inputs, rows)
-    est_full = t * n / rows
-    if est_full <= budget_s:
+    root = find_reference_root()
+    if root is not None:
+        os.environ['GEOTX_REFERENCE_ROOT'] = root
+        import importlib
+        import load_reference
+        importlib.reload(load_reference)
+        GT, _ = load_reference.load_reference()
+        torch.manual_seed(7351)
+        model = GT(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['num_heads'], cfg['blocks'], cfg['sigma_d'],
+                   cfg['sigma_a'], cfg['angle_k'], reduction_a=cfg.get('reduction_a', 'max')).eval()
+        model.load_state_dict(sd, strict=True)
+        whole = max(n, m) ** 2 * cfg['angle_k'] * cfg['hidden_dim'] * 4 * 5 < 0.5 * _host_memory_bytes()
+        if whole:
+            def run():
+                with torch.no_grad():
+                    return model(*inputs)
+            how = 'unmodified reference GeometricTransformer.forward'
+        else:
+            sys.path.insert(0, os.path.join(ROOT, 'tests', 'golden'))
+            from make_golden_large import chunked_forward
+
+            def run():
+                with torch.no_grad():
+                    return chunked_forward(model, *inputs, 64)[:2]
+            how = 'unmodified reference submodules driven in 64-row chunks (its (n,n,k,C) tensors do not fit this host)'
+        return run, 'reference', cores, f'{how} from {root}'
+
+    def run():
+        return oracle.geometric_transformer_chunked(sd, cfg, *inputs, rows=128)
+    return run, 'port', cores, 'oracle port (row-chunked restatement of the reference; no reference tree on this machine)'
+
+
+def _host_memory_bytes():
+    try:
+        return os.sysconf('SC_PAGE_SIZE') * os.sysconf('SC_PHYS_PAGES')
+    except (ValueError, OSError):
+        return 32 << 30
+
+
+def cpu_baseline(workload, max_pairs=3, budget_s=25.0):
+    """Bounded CPU baseline beside the GPU number (rank 0, N=1 only): whole pairs, as many as fit ~25 s (at least one)."""
+    run, kind, cores, how = cpu_forward_fn(workload)
+    times = []
+    t_all = time.perf_counter()
+    while len(times) < max_pairs and (not times or time.perf_counter() - t_all + times[-1] < budget_s):
         t0 = time.perf_counter()
-        oracle.geometric_transformer_chunked(sd, cfg, *inputs, rows=128)
-        t_full = time.perf_counter() - t0
-        return {'value': 1.0 / t_full, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                'sample': f'1 full pair ({workload}), row-chunked oracle (128 rows), {t_full:.2f} s'}
-    rows2 = max(rows, min(n, int(rows * budget_s / max(t, 1e-3) / 2)))
-    t2 = cpu_sample_seconds(oracle, cfg, sd, inputs, rows2)
-    return {'value': (rows2 / n) / t2, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-            'sample': f'{rows2} of {n} query rows of every block of 1 pair ({workload}), {t2:.2f} s, scaled by n/rows'}
+        run()
+        times.append(time.perf_counter() - t0)
+    best = min(times)
+    return {'value': 1.0 / best, 'unit': UNIT, 'cores': cores, 'kind': kind,
+            'sample': f'{len(times)} whole pair(s) of {workload}, best {best:.2f} s; {how}'}
 
 
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    oracle, cfg, sd, inputs, n, m, cores = cpu_setup(args.workload)
-    rows = min(128, n)
-    for _ in range(args.warmup):
-        cpu_sample_seconds(oracle, cfg, sd, inputs, rows)
+    shape, n, m = WORKLOADS[args.workload]
+    run, kind, cores, how = cpu_forward_fn(args.workload)
+    for _ in range(min(args.warmup, 1)):  # one untimed pair warms the thread pool / allocator (a pair takes seconds)
+        run()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        cpu_sample_seconds(oracle, cfg, sd, inputs, rows)
+        run()
     dt = (time.perf_counter() - t0) / args.steps
-    value = (rows / n) / dt
-    sample = f'each step = {rows} of {n} query rows of every block of 1 pair, scaled by n/rows'
+    value = 1.0 / dt
+    sample = f'each step = 1 whole pair of {args.workload}; {how}'
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
-        'warmup': args.warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'warmup': min(args.warmup, 1), 'ms_per_step': dt * 1e3, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': cfg['hidden_dim'],
-                   'note': 'CPU oracle port of the reference formulation (reference is pure PyTorch; /root/reference '
-                           'does not travel to the GPU box), all host threads'},
-        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'config': bench_config(args.workload, args.gpus),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': kind, 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }))
+
+
+def bench_config(workload, world):
+    """The `config` object both arms print (identical on both, so that the driver's same_config check reads true); what
+    is specific to the GPU arm goes under `setup`."""
+    shape, n, m = WORKLOADS[workload]
+    return {'workload': workload, 'n': n, 'm': m, 'pairs_per_step_per_gpu': 1, 'sharding': f'by pair over {world} GPU(s)',
+            'l2': 'inputs larger than L2: distinct pairs rotated whose inputs together exceed the 126 MB L2 (count in setup.l2)'}
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -323,62 +381,6 @@ def time_procrustes(pkg, shape, calls=10, replays=5):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
-class InFlight:
-    """`count` CUDA-graph instances of the forward, each on its own stream: step s replays instance s % count, so that
-    the small kernels of one pair (the cross blocks keep few SMs busy) run under the GPU-filling kernels of the next.
-    Independent pairs, identical kernels per pair; count = 1 is the plain replay loop."""
-
-    def __init__(self, pkg, model, example, count):
-        import torch
-        self.torch = torch
-        self.graphs = [pkg.GraphedGeometricTransformer(model, *example) for _ in range(count)]
-        self.streams = [torch.cuda.Stream() for _ in range(count)] if count > 1 else [None]
-
-    def run(self, resident, n_pairs, steps):
-        torch = self.torch
-        main = torch.cuda.current_stream()
-        out = None
-        if self.streams[0] is None:
-            for s in range(steps):
-                out = self.graphs[0](*resident[s % n_pairs])
-            return out
-        for st in self.streams:
-            st.wait_stream(main)
-        for s in range(steps):
-            with torch.cuda.stream(self.streams[s % len(self.graphs)]):
-                out = self.graphs[s % len(self.graphs)](*resident[s % n_pairs])
-        for st in self.streams:
-            main.wait_stream(st)
-        return out
-
-
-def time_embed_variant(pkg, model, resident, n_pairs, steps, default_out, inflight):
-    """The same forward with the OTHER embedding kernel (tabulated K2t <-> tcgen05 contraction K2): graph replay, CUDA
-    events, same pairs; reported beside `value`, not as it."""
-    import torch
-    default = model.embedding.embed_kernel
-    other = 'tensor' if default == 'table' else 'table'
-    try:
-        model.embedding.embed_kernel = other
-        fast = InFlight(pkg, model, resident[0], inflight)
-        out = fast.run(resident, n_pairs, 2 * inflight + 1)
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        out = fast.run(resident, n_pairs, steps)
-        b.record()
-        torch.cuda.synchronize()
-        ms = a.elapsed_time(b)
-        diff = max(float((x - y).norm() / y.norm()) for x, y in zip(out, default_out))
-        del fast
-        return {'embed_kernel': other, 'value': steps / (ms * 1e-3), 'unit': 'pairs/s', 'ms_per_step': ms / steps,
-                'rel_diff_of_outputs_vs_default': diff}
-    except Exception as exc:
-        return {'error': f'{type(exc).__name__}: {exc}'}
-    finally:
-        model.embedding.embed_kernel = default
-
-
 def time_patch_scores(pkg, shape, calls=10, replays=5):
     """geotx_patch_scores (K12: the glue of model.py:169-170,176-179,187-188 between coarse matching and optimal
     transport) for one pair's 256 node correspondences; us per pair, next to the same lines written with stock torch
@@ -474,6 +476,160 @@ def time_pyramid(pkg, calls=3):
         return {'error': f'{type(exc).__name__}: {exc}'}
 
 
+class InFlight:
+    """`count` CUDA-graph instances of the forward, each on its own stream: step s replays instance s % count, so that
+    the small kernels of one pair (the cross blocks keep few SMs busy) run under the GPU-filling kernels of the next.
+    Independent pairs, identical kernels per pair; count = 1 is the plain replay loop.  `keep` (a (steps, n+m, Dout)
+    tensor) receives every step's output features (what a multi-GPU job gathers at its end)."""
+
+    def __init__(self, pkg, model, example, count):
+        import torch
+        self.torch = torch
+        self.graphs = [pkg.GraphedGeometricTransformer(model, *example) for _ in range(count)]
+        self.streams = [torch.cuda.Stream() for _ in range(count)] if count > 1 else [None]
+
+    def run(self, resident, n_pairs, steps, keep=None):
+        torch = self.torch
+        main = torch.cuda.current_stream()
+        out = None
+
+        def one(s):
+            o = self.graphs[s % len(self.graphs)](*resident[s % n_pairs])
+            if keep is not None:
+                n = o[0].shape[1]
+                keep[s, :n].copy_(o[0][0], non_blocking=True)
+                keep[s, n:].copy_(o[1][0], non_blocking=True)
+            return o
+        if self.streams[0] is None:
+            for s in range(steps):
+                out = one(s)
+            return out
+        for st in self.streams:
+            st.wait_stream(main)
+        for s in range(steps):
+            with torch.cuda.stream(self.streams[s % len(self.graphs)]):
+                out = one(s)
+        for st in self.streams:
+            main.wait_stream(st)
+        return out
+
+
+class KernelTimers:
+    """CUDA-event brackets around the calls of the C-ABI wrappers (`pkg.ops.<fn>`), usable inside a CUDA-graph capture
+    (external events): the kernels are timed where they really run, inside the replayed step."""
+
+    def __init__(self, torch):
+        self.torch, self.external, self.records, self._restore = torch, False, {}, []
+
+    def wrap(self, owner, attr, name, work=None):
+        orig = getattr(owner, attr)
+        timers = self
+
+        def timed(*a, **k):
+            kw = dict(enable_timing=True, external=True) if timers.external else dict(enable_timing=True)
+            e0, e1 = timers.torch.cuda.Event(**kw), timers.torch.cuda.Event(**kw)
+            e0.record()
+            res = orig(*a, **k)
+            e1.record()
+            timers.records.setdefault(name, []).append((e0, e1, work(*a, **k) if work else 0.0))
+            return res
+        setattr(owner, attr, timed)
+        self._restore.append((owner, attr, orig))
+
+    def clear(self):
+        self.records = {}
+
+    def restore(self):
+        for owner, attr, orig in self._restore:
+            setattr(owner, attr, orig)
+        self._restore = []
+
+    def summary(self, records=None):
+        """name -> (list of ms, list of work) over the given (or all) event pairs; synchronise first."""
+        out = {}
+        for name, evs in (records or self.records).items():
+            out[name] = ([a.elapsed_time(b) for a, b, _ in evs], [w for _, _, w in evs])
+        return out
+
+
+def host_d_set(pkg, points, sigma_d):
+    """The distance-expansion set K2c / K3r pick on the device for this cloud (largest distance / sigma_d against the
+    sets' ranges), recomputed on the host for reporting the executed flops."""
+    import torch
+    p = points[0].double()
+    d_max = float(torch.cdist(p, p).max()) / sigma_d if p.shape[0] <= 8192 else float((p.max(0)[0] - p.min(0)[0]).norm()) / sigma_d
+    lib = pkg._abi.load()
+    for s in range(6):
+        if d_max <= float(lib.geotx_gse_cheb_d_range(s)):
+            return s, d_max
+    return 5, d_max
+
+
+KD_TILES = (1, 2, 3, 4, 6, 8)
+
+
+def measure_mma_sync_peak(pkg, torch, dev):
+    """TFLOP/s of mma.sync.m16n8k16 (f16, fp32 accumulate) on register operands, all SMs busy (geotx_mma_sync_probe)."""
+    import ctypes
+    try:
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        ctas, iters = sms * 4, 4000
+        out = torch.empty(ctas * 256, device=dev)
+        st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        best = 0.0
+        for rep in range(4):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            pkg._abi.call('geotx_mma_sync_probe', ctas, iters, ctypes.c_void_p(out.data_ptr()), st)
+            b.record()
+            torch.cuda.synchronize()
+            if rep:
+                best = max(best, ctas * 8.0 * iters * 16 * 4096 / (a.elapsed_time(b) * 1e-3) / 1e12)
+        return best
+    except Exception:
+        return None
+
+
+def timed_value(torch, fast, resident, n_pairs, steps, warm):
+    fast.run(resident, n_pairs, warm)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    out = fast.run(resident, n_pairs, steps)
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b), out
+
+
+def probe_kernels(pkg, torch, model, timers, resident, n_pairs, steps):
+    """Per-kernel-class times INSIDE a replayed CUDA graph of the forward: the wrappers record external event pairs
+    during the capture; every replay refreshes them.  -> name -> dict(ms per launch, launches per step, work per launch)."""
+    timers.clear()
+    timers.external = True
+    try:
+        probe = pkg.GraphedGeometricTransformer(model, *resident[0], warmup=1)
+        # the wrappers saw two forwards: the eager warm-up and the captured one; the capture's event pairs are the second
+        # half of every list
+        rec = {name: evs[len(evs) // 2:] for name, evs in timers.records.items()}
+        acc = {name: ([], [w for _, _, w in evs]) for name, evs in rec.items()}
+        for s in range(3 + steps):
+            probe(*resident[s % n_pairs])
+            torch.cuda.synchronize()
+            if s >= 3:
+                for name, evs in rec.items():
+                    acc[name][0].append([a.elapsed_time(b) for a, b, _ in evs])
+        del probe
+        out = {}
+        for name, (per_replay, work) in acc.items():
+            launches = len(work)
+            ms = [sum(r[i] for r in per_replay) / len(per_replay) for i in range(launches)]
+            out[name] = {'launches_per_step': launches, 'ms_per_launch': ms, 'work_per_launch': work}
+        return out, 'CUDA events recorded inside the CUDA graph of the forward, around every launch, averaged over the replays'
+    finally:
+        timers.external = False
+        timers.clear()
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -489,72 +645,128 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
     pkg._abi.load()
-
-    shape, n, m = WORKLOADS[args.workload]
-    cfg = dict(pkg.synth.CONFIGS[shape])
-    C, k = cfg['hidden_dim'], cfg['angle_k']
-    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
-    torch.manual_seed(pkg.synth.SEED)
-    model = pkg.GeometricTransformer(**cfg).to(dev).eval()  # default nn.Linear init under seed 7351 = oracle init
-    big = max(n, m) >= 8192  # E of both clouds: 69 GB at 8192 (stored, one graph alive at a time), 275 GB at 16384
-    if os.environ.get('GEOTX_E_MODE') is None:
-        model.e_mode = 'regenerate' if 2 * max(n, m) ** 2 * C * 2 > 140e9 else 'store'
-
-    # a small rotation of distinct pairs per rank; E (n*n*C*2 bytes per cloud) alone exceeds the 126 MB L2
-    n_pairs = 4
-    host = [pkg.synth.make_pair(shape, n, m, seed=pkg.synth.SEED + rank * 101 + p) for p in range(n_pairs)]
-    host = [tuple(t.pin_memory() for t in pr) for pr in host]
-    resident = [tuple(t.to(dev) for t in pr) for pr in host]
-    h2d = sum(t.numel() * t.element_size() for t in host[0])
-    out_host = [torch.empty(1, x, cfg['output_dim']).pin_memory() for x in (n, m)]
-    d2h = sum(t.numel() * t.element_size() for t in out_host)
-
-    # CUDA-event bracket around every launch of the dominant kernel (fused embedding, K2)
-    k2_events = []
-    orig_embed = model.embedding.embed
-
-    external = [False]
-
-    def timed_embed(geom, out_dtype, row_begin=0, row_count=None, out=None, qt=None):
-        kw = dict(enable_timing=True, external=True) if external[0] else dict(enable_timing=True)
-        e0, e1 = torch.cuda.Event(**kw), torch.cuda.Event(**kw)
-        e0.record()
-        res = orig_embed(geom, out_dtype, row_begin, row_count, out, qt=qt)
-        e1.record()
-        rows = geom.n - row_begin if row_count is None else row_count
-        k2_events.append((e0, e1, flops_gse(geom.n, C, k) * rows / geom.n))  # a launch covers `rows` query rows
-        return res
-    model.embedding.embed = timed_embed
-
-    # the same bracket around every launch of the RPE score kernel (K3a, HBM-bound on E): the dominant kernel when the
-    # embedding runs by tabulation
-    k3_events = []
-    orig_scores = pkg.ops.rpe_scores
-
-    def timed_scores(qt, E, n=None, row_begin=0, out=None):
-        kw = dict(enable_timing=True, external=True) if external[0] else dict(enable_timing=True)
-        e0, e1 = torch.cuda.Event(**kw), torch.cuda.Event(**kw)
-        e0.record()
-        res = orig_scores(qt, E, n=n, row_begin=row_begin, out=out)
-        e1.record()
-        heads = qt.shape[1] if qt.dim() == 4 else cfg['num_heads']
-        k3_events.append((e0, e1, E.numel() * E.element_size() + E.numel() // E.shape[-1] * heads * 4))
-        return res
-    pkg.ops.rpe_scores = timed_scores
+    peaks = measured_peaks()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    last = None
+    def build(workload):
+        shape, n, m = WORKLOADS[workload]
+        cfg = dict(pkg.synth.CONFIGS[shape])
+        torch.manual_seed(pkg.synth.SEED)
+        model = pkg.GeometricTransformer(**cfg).to(dev).eval()  # default nn.Linear init under seed 7351 = oracle init
+        return shape, n, m, cfg, model
+
+    def make_pairs(shape, n, m, count, first_seed):
+        host = [pkg.synth.make_pair(shape, n, m, seed=first_seed + p) for p in range(count)]
+        host = [tuple(t.pin_memory() for t in pr) for pr in host]
+        return host, [tuple(t.to(dev) for t in pr) for pr in host]
+
+    shape, n, m, cfg, model = build(args.workload)
+    C, k, H = cfg['hidden_dim'], cfg['angle_k'], cfg['num_heads']
+    Ls = sum(b == 'self' for b in cfg['blocks'])
+    big = max(n, m) >= 8192
+    # inputs larger than L2: a rotation of distinct pairs per rank whose inputs together exceed the 126 MB L2 (on top of
+    # that every step streams its n^2 H fp32 score matrices, 16.8 MB per 'self' block and cloud at n = 1024)
+    pair_bytes = (n + m) * (cfg['input_dim'] + 3) * 4
+    n_pairs = max(4, -(-140_000_000 // pair_bytes))  # distinct input pairs rotated: together larger than the 126 MB L2
+    host, resident = make_pairs(shape, n, m, n_pairs, pkg.synth.SEED + rank * 101)
+    h2d = sum(t.numel() * t.element_size() for t in host[0])
+    d2h = (n + m) * cfg['output_dim'] * 4
+    d_set = max(host_d_set(pkg, host[0][0], cfg['sigma_d'])[0], host_d_set(pkg, host[0][1], cfg['sigma_d'])[0])
+    kd = 16 * KD_TILES[d_set]
+
+    def k3r_flops(geom, coef, qt, *a, **kw):  # flops the kernel EXECUTES: expansions of k angle slots + distance, scores hi + lo
+        rows = geom.n
+        return geom.B * rows * geom.n * (2.0 * C * (k * 16 * coef.ka_tiles + kd) + 2.0 * C * 8 * 2)
+
+    def embed_bytes(geom, out_dtype, row_begin=0, row_count=None, out=None, qt=None):
+        rows = geom.n - row_begin if row_count is None else row_count
+        return float(geom.B * rows * geom.n * C * (4 if out_dtype == torch.float32 else 2))
+
+    def k3a_bytes(qt, E, n=None, row_begin=0, out=None):
+        return float(E.numel() * E.element_size() + E.numel() // E.shape[-1] * qt.shape[1] * 4)
+
+    timers = KernelTimers(torch)
+    timers.wrap(pkg.ops, 'rpe_scores_cheb', 'rpe_scores_cheb (K3r)', k3r_flops)
+    timers.wrap(pkg.ops, 'rpe_scores', 'rpe_scores (K3a)', k3a_bytes)
+    timers.wrap(model.embedding, 'embed', 'gse_embed (K2c / K2 / K2t)', embed_bytes)
+    timers.wrap(pkg.ops, 'attention', 'attention (K3b)',
+                lambda q, kk, v, heads, *a, **kw: 4.0 * q.shape[0] * q.shape[1] * kk.shape[1] * q.shape[2])
+    timers.wrap(pkg.ops, 'post_attention', 'post_attention (K4f)',
+                lambda hidden, *a, **kw: 2.0 * (hidden.numel() // hidden.shape[-1]) * 5 * hidden.shape[-1] ** 2)
+    timers.wrap(pkg.ops, 'linear_f16', 'linear_f16 (K13)',
+                lambda x, w, *a, **kw: 2.0 * (x.numel() // x.shape[-1]) * w.shape[0] * w.shape[1])
+    timers.wrap(pkg.ops, 'gse_knn', 'gse_knn (K1)', lambda points, kk: float(points.shape[0] * points.shape[1] ** 2 * 16))
+    timers.wrap(pkg.ops, 'add_layernorm', 'add_layernorm (K4)', None)
+
+    def kernel_report(per_kernel, step_ms):
+        rep = {}
+        for name, d in sorted(per_kernel.items()):
+            total = sum(d['ms_per_launch'])
+            rep[name] = {'launches_per_step': d['launches_per_step'], 'ms_per_step': total,
+                         'avg_launch_ms': total / max(d['launches_per_step'], 1),
+                         'share_of_step': total / step_ms if step_ms else None}
+        return rep
+
+    def roof_tensor(name, d, step_ms, mma_peak, what):
+        ms = sum(d['ms_per_launch']) / max(d['launches_per_step'], 1)
+        fl = sum(d['work_per_launch']) / max(d['launches_per_step'], 1)
+        ach = fl / (ms * 1e-3) / 1e12 if ms else 0.0
+        r = {'kernel': name, 'bound': 'tensor', 'achieved': ach, 'peak': peaks['tensor_sustained'], 'unit': 'TFLOP/s',
+             'frac': ach / peaks['tensor_sustained'], 'traffic': NCU_TRAFFIC_BYTES.get((name, args.workload)),
+             'peak_source': peaks['source'] + ' bf16 sustained (cuBLAS on tcgen05; the kernel is timed inside the step)',
+             'flops_per_launch': fl, 'flops': what, 'avg_launch_ms': ms, 'launches_per_step': d['launches_per_step'],
+             'share_of_step': sum(d['ms_per_launch']) / step_ms if step_ms else None}
+        if mma_peak:
+            r['mma_sync_peak_tflops'] = mma_peak
+            r['frac_of_mma_sync_peak'] = ach / mma_peak
+            r['pipe'] = ('mma.sync.m16n8k16 (legacy tensor path): the accumulators must be max-reduced over the k angle slots '
+                         'in registers; through tcgen05 they would have to be read back from TMEM at 64 B/clk/SM, 3x slower '
+                         'than the contraction itself (DESIGN.md section 4)')
+        return r
+
+    def roof_hbm(name, d, step_ms, what):
+        ms = sum(d['ms_per_launch']) / max(d['launches_per_step'], 1)
+        by = sum(d['work_per_launch']) / max(d['launches_per_step'], 1)
+        gbs = by / (ms * 1e-3) / 1e9 if ms else 0.0
+        return {'kernel': name, 'bound': 'hbm', 'achieved': gbs, 'peak': peaks['hbm'], 'unit': 'GB/s',
+                'frac': gbs / peaks['hbm'], 'traffic': NCU_TRAFFIC_BYTES.get((name, args.workload)),
+                'peak_source': peaks['source'] + ' copy bandwidth', 'bytes_per_launch': by, 'algorithmic_bytes': what,
+                'avg_launch_ms': ms, 'launches_per_step': d['launches_per_step'],
+                'share_of_step': sum(d['ms_per_launch']) / step_ms if step_ms else None}
+
+    many = max(n, m) <= 2048
+    inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '3'))) if many else 1
+
+    def run_variant(tag, setup, undo, steps, want_kernels=True):
+        """The same forward under another configuration: value (graph replay, CUDA events) + its kernel table."""
+        try:
+            setup()
+            with torch.no_grad():
+                model(*resident[0])
+                fast = InFlight(pkg, model, resident[0], inflight)
+                ms, out = timed_value(torch, fast, resident, n_pairs, steps, max(3, 2 * inflight))
+                del fast
+                res = {'value': steps / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms / steps, 'e_storage': model.last_e_mode}
+                if want_kernels:
+                    per_kernel, _ = probe_kernels(pkg, torch, model, timers, resident, n_pairs, min(steps, 10))
+                    res['kernels'] = kernel_report(per_kernel, ms / steps)
+                    res['_raw'] = per_kernel
+            return res, out
+        except Exception as exc:  # keeps the headline line alive
+            return {'error': f'{type(exc).__name__}: {exc}'}, None
+        finally:
+            undo()
+            torch.cuda.empty_cache()
+
     with torch.no_grad():
-        # ---- pass 1 (eager launches): per-launch CUDA-event timing of the dominant kernel + launch count ----
+        # ---- pass 1 (eager): launch count through the C ABI ----
         for s in range(3):
             last = model(*resident[s % n_pairs])
         barrier()
-        k2_events.clear()
-        k3_events.clear()
         launches0 = pkg._abi.launch_count
         e_start, e_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e_start.record()
@@ -564,53 +776,18 @@ def run_b200(args):
         barrier()
         eager_ms = e_start.elapsed_time(e_stop)
         launches = pkg._abi.launch_count - launches0
-        k2_ms = [a.elapsed_time(b) for a, b, _ in k2_events]
-        k2_launch_flops = [f for _, _, f in k2_events]
-        k3_ms = [a.elapsed_time(b) for a, b, _ in k3_events]
-        k3_launch_bytes = [f for _, _, f in k3_events]
-        k2_timing = 'CUDA events around every launch in an eager pass over the same steps'
-        # Preferred: the same event pairs captured INSIDE a CUDA graph of the forward (external event-record nodes), so
-        # that the kernel is timed in exactly the context the value pass runs it in (eager launches at n ~ 1k are
-        # host-bound: the GPU idles between launches and the kernel then starts from a lower power state).
-        try:
-            k2_events.clear()
-            k3_events.clear()
-            external[0] = True
-            probe = pkg.GraphedGeometricTransformer(model, *resident[0])
-            per_forward = max(len(k2_ms) // max(args.steps, 1), 1)
-            pairs_per_replay = list(k2_events)[-per_forward:]  # those recorded during the capture itself
-            per_forward3 = max(len(k3_ms) // max(args.steps, 1), 1)
-            pairs3_per_replay = list(k3_events)[-per_forward3:]
-            in_graph, in_graph_flops = [], []
-            in_graph3, in_graph3_bytes = [], []
-            for s in range(3 + args.steps):
-                probe(*resident[s % n_pairs])
-                torch.cuda.synchronize()
-                if s >= 3:
-                    in_graph += [a.elapsed_time(b) for a, b, _ in pairs_per_replay]
-                    in_graph_flops += [f for _, _, f in pairs_per_replay]
-                    in_graph3 += [a.elapsed_time(b) for a, b, _ in pairs3_per_replay]
-                    in_graph3_bytes += [f for _, _, f in pairs3_per_replay]
-            if in_graph and all(t > 0 for t in in_graph):
-                k2_ms, k2_launch_flops = in_graph, in_graph_flops
-                if in_graph3 and all(t > 0 for t in in_graph3):
-                    k3_ms, k3_launch_bytes = in_graph3, in_graph3_bytes
-                k2_timing = 'CUDA events recorded inside the CUDA graph of the forward, around every launch'
-            del probe
-            if big:
-                torch.cuda.empty_cache()
-        except Exception as exc:  # older torch: no external events in graphs
-            k2_timing += f' (in-graph events unavailable: {type(exc).__name__})'
-        external[0] = False
-        model.embedding.embed = orig_embed
-        pkg.ops.rpe_scores = orig_scores
+        default_mode = model.last_e_mode
 
-        # ---- pass 2 (the timed region of `value`): the same forward replayed as one CUDA graph per step ----
-        # graph-private buffers per instance: E of both clouds (n = 4096: 17 GB); keep the instances alive at once
-        # (value, end-to-end pipeline, variant) below ~100 GB
-        many = max(n, m) <= 2048
-        inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '3'))) if many else 1
+        # ---- per-kernel times inside the replayed graph of the forward ----
+        per_kernel, kernel_timing = probe_kernels(pkg, torch, model, timers, resident, n_pairs, args.steps)
+        mma_peak = measure_mma_sync_peak(pkg, torch, dev) if rank == 0 else None
+
+        # ---- pass 2 (the timed region of `value`): the forward replayed as one CUDA graph per step ----
         fast = InFlight(pkg, model, resident[0], inflight)
+        keep = torch.empty(args.steps, n + m, cfg['output_dim'], device=dev) if world > 1 else None
+        if world > 1:  # warm-up gather: NCCL channel setup and buffer registration stay outside the timed region
+            pkg.dist.gather_pair_outputs(list(torch.zeros(args.steps, n + m, cfg['output_dim'], device=dev)),
+                                         args.steps * world)
         last = fast.run(resident, n_pairs, max(args.warmup, 3, 2 * inflight))
         barrier()
         sampler = ClockSampler(local) if rank == 0 else None
@@ -618,20 +795,39 @@ def run_b200(args):
             sampler.start()
         t_start, t_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_start.record()
-        last = fast.run(resident, n_pairs, args.steps)
-        if world > 1:  # the one collective of the job: gather the outputs of the last pair of every rank
-            gathered = pkg.dist.gather_pair_outputs([torch.cat(last, dim=1)[0]], world)
+        last = fast.run(resident, n_pairs, args.steps, keep=keep)
+        if world > 1:  # the one collective of the job: every rank ends up with the features of all steps x ranks pairs
+            gathered = pkg.dist.gather_pair_outputs(list(keep), args.steps * world)
         t_stop.record()
         barrier()
         clocks = sampler.stop() if sampler else None
         ms = t_start.elapsed_time(t_stop)
+        gather_bytes = args.steps * world * (n + m) * cfg['output_dim'] * 4 if world > 1 else 0
+
+        # ---- BASELINE.json configs[4]: 256 pairs in total, sharded by pair, every output gathered (strong scaling) ----
+        configs4 = None
+        if not big:
+            try:
+                mine = pkg.dist.shard_pairs(CONFIGS4_PAIRS, rank, world)
+                keep4 = torch.empty(len(mine), n + m, cfg['output_dim'], device=dev)
+                barrier()
+                c_start, c_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                c_start.record()
+                fast.run(resident, n_pairs, len(mine), keep=keep4)
+                all4 = pkg.dist.gather_pair_outputs(list(keep4), CONFIGS4_PAIRS)
+                c_stop.record()
+                barrier()
+                configs4 = {'ms': c_start.elapsed_time(c_stop), 'pairs': CONFIGS4_PAIRS, 'pairs_per_rank': len(mine),
+                            'gathered_shape': list(all4.shape), 'gather_bytes': all4.numel() * 4}
+                del all4, keep4
+            except Exception as exc:
+                configs4 = {'error': f'{type(exc).__name__}: {exc}'}
 
         # ---- end to end: host (pinned) inputs -> device -> forward -> host outputs, every step, through the serving
         #      API (PipelinedGeometricTransformer: the upload of pair p+1 / download of pair p-1 overlap pair p) ----
         depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', '3'))) if many else 2)
-        if big or not many:  # one set of graph-private buffers at a time
-            del fast
-            torch.cuda.empty_cache()
+        del fast
+        torch.cuda.empty_cache()
         pipe = pkg.PipelinedGeometricTransformer(model, *resident[0], depth=depth)
         for o in pipe.map(host[s % n_pairs] for s in range(3)):
             pass
@@ -645,94 +841,160 @@ def run_b200(args):
         e2e_s = time.perf_counter() - w0
         if checksum != checksum:
             raise RuntimeError('end-to-end outputs are NaN')
+        del pipe
+        torch.cuda.empty_cache()
 
-        # ---- next row: the path's consumer (F.normalize + SuperPointMatching), timed alone on the
-        #      outputs of the last pair; not part of `value` ----
-        if big:
-            del pipe
-            torch.cuda.empty_cache()
-        matching = time_matching(pkg, last) if world == 1 else None
-        shape_name = WORKLOADS[args.workload][0]
-        partition = time_partition(pkg, shape_name, n) if world == 1 else None
-        transport = time_transport(pkg, shape_name) if world == 1 else None
-        procrustes = time_procrustes(pkg, shape_name) if world == 1 else None
-        pyramid = time_pyramid(pkg) if world == 1 else None
-        registration = time_registration(pkg, shape_name) if world == 1 else None
-        patch_scores = time_patch_scores(pkg, shape_name) if world == 1 else None
-        variant = None
-        if world == 1 and not big and C in (128, 256) and k == 3:
-            variant = time_embed_variant(pkg, model, resident, n_pairs, args.steps, last, inflight)
-
-    tt = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    tt = torch.tensor([ms, e2e_s * 1e3, configs4['ms'] if configs4 and 'ms' in configs4 else 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = tt.tolist()
+    ms, e2e_ms, c4_ms = tt.tolist()
+
+    variants, sweep, next_rows = {}, {}, None
+    if rank == 0 and world == 1:
+        emb = model.embedding
+
+        def set_mode(e_mode=None, kernel=None, dense=None):
+            def f():
+                if e_mode:
+                    model.e_mode = e_mode
+                if kernel:
+                    emb.embed_kernel = kernel
+                if dense:
+                    os.environ['GEOTX_DENSE'] = dense
+            return f
+
+        def reset():
+            model.e_mode, emb.embed_kernel = 'auto', 'cheb'
+            os.environ.pop('GEOTX_DENSE', None)
+        vsteps = min(args.steps, 20)
+        if not big and default_mode == 'scores':
+            # (a) E stored: K2c writes it once per cloud, K3a reads it once per 'self' block -- the HBM-bound formulation
+            v, out = run_variant('stored_e', set_mode(e_mode='store'), reset, vsteps)
+            if 'error' not in v:
+                raw = v.pop('_raw')
+                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, last))
+                if 'gse_embed (K2c / K2 / K2t)' in raw:
+                    v['embedding_write'] = roof_hbm('gse_embed_cheb_kernel (geotx_gse_embed_cheb, K2c)', raw['gse_embed (K2c / K2 / K2t)'],
+                                                    v['ms_per_step'], 'E written once: n*n*C*2 bytes per launch')
+                if 'rpe_scores (K3a)' in raw:
+                    v['scores_read'] = roof_hbm('rpe_scores_tc_kernel (geotx_rpe_scores, K3a)', raw['rpe_scores (K3a)'], v['ms_per_step'],
+                                                'E read once (n*n*C*2) + scores written (n*n*H*4) per launch')
+            variants['stored_e'] = v
+            # (b) the full-rank tcgen05 embedding: north_star's "% of tensor-pipe peak" on the formulation it names
+            v, out = run_variant('tensor_embedding', set_mode(e_mode='store', kernel='tensor'), reset, vsteps)
+            if 'error' not in v:
+                raw = v.pop('_raw')
+                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, last))
+                if 'gse_embed (K2c / K2 / K2t)' in raw:
+                    d = dict(raw['gse_embed (K2c / K2 / K2t)'])
+                    d['work_per_launch'] = [flops_gse(n if i % 2 == 0 else m, C, k) for i in range(d['launches_per_step'])]
+                    v['embedding_tensor_roof'] = roof_tensor('gse_embed_tc_kernel (geotx_gse_embed, K2, tcgen05)', d, v['ms_per_step'],
+                                                             None, 'SURVEY.md 8d: 2 n^2 C^2 (1+k) per cloud')
+                v['pair_tflops_min'] = flops_pair(n, m, cfg) / 1e12
+                v['pair_tensor_frac'] = flops_pair(n, m, cfg) * v['value'] / 1e12 / peaks['tensor_sustained']
+                v['pair_tensor_frac_note'] = 'F_min of SURVEY.md 8d (the flops this variant really executes) x pairs/s / measured bf16 sustained'
+            variants['tensor_embedding'] = v
+            # (c) round 1's dense glue (cuBLASLt TF32 GEMMs + K4) under the default embedding / scores
+            v, out = run_variant('library_gemm_glue', set_mode(dense='cublas'), reset, vsteps, want_kernels=False)
+            if 'error' not in v:
+                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, last))
+            variants['library_gemm_glue'] = v
+
+        # ---- bounded sweep points in the same process (driver-visible): north_star's size and KITTI ----
+        if args.workload == '3dmatch_1024' and not args.no_sweep:
+            for wl, ssteps in (('3dmatch_4096', 5), ('kitti_2048', 10)):
+                try:
+                    s_shape, s_n, s_m, s_cfg, s_model = build(wl)
+                    _, s_res = make_pairs(s_shape, s_n, s_m, 2, pkg.synth.SEED)
+                    entry = {}
+                    with torch.no_grad():
+                        for tag, e_mode, kernel in (('default', 'auto', 'cheb'), ('tensor_embedding', 'store', 'tensor')):
+                            s_model.e_mode, s_model.embedding.embed_kernel = e_mode, kernel
+                            s_model(*s_res[0])
+                            sf = InFlight(pkg, s_model, s_res[0], 1)
+                            s_ms, _ = timed_value(torch, sf, s_res, 2, ssteps, 3)
+                            del sf
+                            torch.cuda.empty_cache()
+                            val = ssteps / (s_ms * 1e-3)
+                            entry[tag] = {'value': val, 'unit': UNIT, 'ms_per_step': s_ms / ssteps, 'e_storage': s_model.last_e_mode}
+                            if tag == 'tensor_embedding':
+                                entry[tag]['pair_tflops_min'] = flops_pair(s_n, s_m, s_cfg) / 1e12
+                                entry[tag]['pair_tensor_frac'] = flops_pair(s_n, s_m, s_cfg) * val / 1e12 / peaks['tensor_sustained']
+                        entry['default']['fmin_equivalent_tensor_frac'] = (flops_pair(s_n, s_m, s_cfg) * entry['default']['value'] / 1e12 /
+                                                                           peaks['tensor_sustained'])
+                        entry['note'] = ('fmin_equivalent_tensor_frac = what running SURVEY.md 8d\'s F_min at this rate would need; the '
+                                         'default path executes ~12x fewer flops (low-rank embedding), so it is a throughput '
+                                         'equivalent, not a utilisation')
+                    sweep[wl] = entry
+                    del s_model, s_res
+                    torch.cuda.empty_cache()
+                except Exception as exc:
+                    sweep[wl] = {'error': f'{type(exc).__name__}: {exc}'}
+
+        with torch.no_grad():
+            shape_name = WORKLOADS[args.workload][0]
+            next_rows = {'superpoint_matching': time_matching(pkg, last),
+                         'point_to_node_partition': time_partition(pkg, shape_name, n),
+                         'log_optimal_transport': time_transport(pkg, shape_name),
+                         'weighted_procrustes': time_procrustes(pkg, shape_name),
+                         'patch_scores': time_patch_scores(pkg, shape_name),
+                         'local_global_registration': time_registration(pkg, shape_name),
+                         'collate_pyramid': time_pyramid(pkg)}
+    timers.restore()
+
     if rank == 0:
-        peaks = measured_peaks()
         value = world * args.steps / (ms * 1e-3)
-        k2_avg_ms = sum(k2_ms) / max(len(k2_ms), 1)
-        k2_flops = sum(k2_launch_flops) / max(len(k2_ms), 1)  # average over launches (row slabs of E)
-        achieved = k2_flops / (k2_avg_ms * 1e-3) / 1e12 if k2_ms else 0.0
         step_ms = ms / args.steps
-        k3_avg_ms = sum(k3_ms) / max(len(k3_ms), 1)
-        k3_bytes = sum(k3_launch_bytes) / max(len(k3_ms), 1)
-        k3_gbs = k3_bytes / (k3_avg_ms * 1e-3) / 1e9 if k3_ms else 0.0
-        table = model.embedding.embed_kernel == 'table' and model.embedding._use_table(model.embedding.storage_dtype(), None)
-        timing_note = k2_timing + ('; the value pass replays the identical kernels from a CUDA graph; '
-                                   'share_of_step = timed launches per step / ms_per_step')
-        tensor_roof = {'kernel': 'gse_embed_tc_kernel (geotx_gse_embed)', 'bound': 'tensor', 'achieved': achieved,
-                       'peak': peaks['tensor_sustained'], 'unit': 'TFLOP/s',
-                       'frac': achieved / peaks['tensor_sustained'],
-                       'traffic': K2_NCU_TRAFFIC_BYTES.get(args.workload),
-                       'peak_source': peaks['source'] + ' bf16 sustained (kernel timed inside the step)',
-                       'frac_of_burst_peak': achieved / peaks['tensor_burst'],
-                       'flops_per_launch': k2_flops, 'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
-                       'share_of_step': sum(k2_ms) / args.steps / step_ms if ms else None, 'timing': timing_note}
-        hbm_roof = {'kernel': 'rpe_scores_tc_kernel (geotx_rpe_scores)', 'bound': 'hbm', 'achieved': k3_gbs,
-                    'peak': peaks['hbm'], 'unit': 'GB/s', 'frac': k3_gbs / peaks['hbm'],
-                    'traffic': K3A_NCU_TRAFFIC_BYTES.get(args.workload),
-                    'peak_source': peaks['source'] + ' copy bandwidth',
-                    'bytes_per_launch': k3_bytes, 'avg_launch_ms': k3_avg_ms, 'launches_timed': len(k3_ms),
-                    'share_of_step': sum(k3_ms) / args.steps / step_ms if ms else None,
-                    'algorithmic_bytes': 'E read once (n*n*C*2) + scores written (n*n*H*4) per launch',
-                    'timing': timing_note}
-        if table:  # the embedding runs by tabulation (shared-memory bound): the HBM-bound score kernel dominates
-            roofline = hbm_roof
-            kernel_stats = {'embedding': {'kernel': 'gse_embed_table_kernel (geotx_gse_embed_table)',
-                                          'bound': 'shared-memory pipe (10 table rows = 20 C bytes of shared-memory reads per pair)',
-                                          'avg_launch_ms': k2_avg_ms, 'launches_timed': len(k2_ms),
-                                          'share_of_step': sum(k2_ms) / args.steps / step_ms if ms else None,
-                                          'lds_bytes_per_launch': 20.0 * C * k2_flops / flops_gse(n, C, k) * n * n if n else None}}
+        kernels = kernel_report(per_kernel, step_ms)
+        dom = 'rpe_scores_cheb (K3r)'
+        if dom in per_kernel:
+            roofline = roof_tensor('gse_embed_cheb_kernel<SCORES> (geotx_rpe_scores_cheb, K3r)', per_kernel[dom], step_ms, mma_peak,
+                                   f'executed: per (i,j) pair 2 C (16 k ka + {kd}) for the expansions of the {k} angle slots and the '
+                                   f'distance (distance set {d_set}: {kd} coefficients) + 2 C 8 2 for the folded-query scores (hi + lo)')
+            dtype = 'f16'
+        elif 'rpe_scores (K3a)' in per_kernel:
+            roofline = roof_hbm('rpe_scores_tc_kernel (geotx_rpe_scores, K3a)', per_kernel['rpe_scores (K3a)'], step_ms,
+                                'E read once (n*n*C*2) + scores written (n*n*H*4) per launch')
+            dtype = 'f16'
         else:
-            roofline = tensor_roof
-            kernel_stats = {'rpe_scores': hbm_roof}
+            roofline, dtype = None, 'f32'
+        if roofline is not None:
+            roofline['timing'] = kernel_timing + '; share_of_step = timed launches per step / ms_per_step'
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
-            'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f16' if table else 'bf16', 'data': 'synthetic',
-            'config': {'workload': args.workload, 'n': n, 'm': m, 'hidden_dim': C, 'num_heads': cfg['num_heads'],
-                       'blocks': len(cfg['blocks']), 'angle_k': k, 'pairs_per_step_per_gpu': 1, 'launch': 'one CUDA graph replay per step' + (f'; {inflight} graph instances in flight on {inflight} streams (independent pairs overlap)' if inflight > 1 else ''),
-                       'e_storage': model.last_e_mode + (f' (E never stored: rebuilt for each of the {sum(b == "self" for b in cfg["blocks"])} self blocks in {model.regenerate_slab_bytes >> 20} MiB row slabs; pair_tflops counts those passes)' if model.last_e_mode == 'regenerate' else ' (one embedding pass per cloud)'),
-                       'embed_kernel': 'table (geotx_gse_embed_table)' if table else 'tensor (geotx_gse_embed, tcgen05)',
-                       'l2_slab_bytes': model.l2_slab_bytes, 'first_block_scores_fused_into_embedding': bool(model.fuse_scores),
-                       'l2': f'inputs larger than L2: E is {n * n * C * 2 / 1e6:.0f} MB per cloud, '
-                             f'{n_pairs} distinct pairs rotated',
-                       'sharding': f'by pair over {world} GPU(s); one all_gather of outputs'},
+            'warmup': max(args.warmup, 3), 'ms_per_step': step_ms, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': dtype, 'data': 'synthetic',
+            'config': bench_config(args.workload, world),
+            'setup': {
+                'hidden_dim': C, 'num_heads': H, 'blocks': len(cfg['blocks']), 'angle_k': k,
+                'launch': 'one CUDA graph replay per step' + (f'; {inflight} graph instances in flight on {inflight} streams (independent pairs overlap)' if inflight > 1 else ''),
+                'e_storage': default_mode + (' (E never formed in memory: K3r rebuilds it tile by tile in registers for each of the '
+                                             f'{Ls} self blocks)' if default_mode == 'scores' else ''),
+                'embed_kernel': model.embedding.embed_kernel, 'dense_glue': os.environ.get('GEOTX_DENSE', 'own'),
+                'l2': f'inputs larger than L2: {n_pairs} distinct pairs ({n_pairs * pair_bytes / 1e6:.0f} MB of inputs) rotated over '
+                      f'{inflight} graph instance(s); every step also streams {2 * Ls * n * n * H * 4 / 1e6:.0f} MB of score matrices',
+                'gather': f'all_gather of the outputs of every step of every rank inside the timed region ({gather_bytes / 1e6:.0f} MB), after one warm-up gather' if world > 1 else 'single GPU: nothing to gather'},
             'e2e': {'value': world * args.steps / (e2e_ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h,
                     'api': f'PipelinedGeometricTransformer.map over pinned host pairs, depth {depth}, wall clock'},
             'gpu_launches': launches,
+            'gpu_launches_per_step': launches / args.steps,
             'roofline': roofline,
-            'kernels': kernel_stats,
+            'kernels': kernels,
             'eager_ms_per_step': eager_ms / args.steps,
-            'pair_tflops': flops_pair(n, m, cfg, model.last_e_mode == 'regenerate') / 1e12,
-            'pair_tflops_min': flops_pair(n, m, cfg) / 1e12,
-            'pair_tensor_frac': flops_pair(n, m, cfg, model.last_e_mode == 'regenerate') * value / world / 1e12 / peaks['tensor_sustained'],
+            'pair_tflops_executed': sum(sum(d['work_per_launch']) for nme, d in per_kernel.items()
+                                        if nme.split(' ')[0] in ('rpe_scores_cheb', 'attention', 'post_attention', 'linear_f16')) / 1e12,
+            'pair_tflops_min_reference_formulation': flops_pair(n, m, cfg) / 1e12,
+            'fmin_equivalent_tensor_frac': flops_pair(n, m, cfg) * value / world / 1e12 / peaks['tensor_sustained'],
+            'fmin_equivalent_note': 'throughput equivalent only: SURVEY.md 8d F_min x pairs/s / measured bf16 sustained; the default '
+                                    'path does not execute F_min (see pair_tflops_executed); variants.tensor_embedding.pair_tensor_frac '
+                                    'is the utilisation figure of the formulation north_star names',
             'clocks': clocks,
-            'next_rows': {'superpoint_matching': matching, 'point_to_node_partition': partition,
-                          'log_optimal_transport': transport, 'weighted_procrustes': procrustes,
-                          'patch_scores': patch_scores, 'local_global_registration': registration, 'collate_pyramid': pyramid},
-            'variants': {'other_embed_kernel': variant},
+            'configs4': ({'value': CONFIGS4_PAIRS / (c4_ms * 1e-3), 'unit': UNIT, 'scaling': 'strong', 'ms': c4_ms,
+                          **{kk: vv for kk, vv in configs4.items() if kk != 'ms'}} if configs4 and 'ms' in configs4 else configs4),
+            'next_rows': next_rows,
+            'variants': variants,
+            'sweep': sweep,
         }
         if world == 1 and not args.no_cpu_baseline:
             line['cpu_baseline'] = cpu_baseline(args.workload)
@@ -751,6 +1013,7 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--workload', default='3dmatch_1024', choices=sorted(WORKLOADS))
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-sweep', action='store_true')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

@@ -87,6 +87,11 @@ int geotx_gse_embed_scores(const void* geometry, int B, int n, int k, int row_be
                            int reduce_mean, int out_dtype, void* out, const float* qt, int64_t qt_stride_b,
                            int64_t qt_stride_h, int64_t qt_stride_n, int H, float* scores_p, void* stream);
 
+/* Diagnostic, no reference counterpart: ctas x 8 warps x iters x 16 mma.sync.m16n8k16 (f16 x f16 -> f32, 4096 flop each)
+ * on register operands; the caller times the launch.  bench.py uses it to state the peak of the legacy tensor path that
+ * K2c / K3r / K4f / K13 run on, next to the measured tcgen05 rate.  out f32 [ctas * 256]. */
+int geotx_mma_sync_probe(int ctas, int iters, float* out, void* stream);
+
 /* Debug aid (synchronises the device): the tcgen05 kernel's mbarrier waits are bounded; a wait that times out
  * records {0x80000000 | role<<24 | ring position, barrier smem address, parity, block} and the launch finishes with
  * undefined output instead of hanging the GPU.  Copies the record to host_out4 (all zero = healthy) and clears it. */

@@ -60,6 +60,7 @@ SIGNATURES = {
     'geotx_linear_f16': (_i, [_p, _i64, _i64, _i, _p, _p, _i, _i, _p, _i64, _p]),
     'geotx_post_attention': (_i, [_p, _i64, _p, _i64, _i64, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _f, _p, _i64,
                                   _p]),
+    'geotx_mma_sync_probe': (_i, [_i, _i, _p, _p]),
     'geotx_patch_scores': (_i, [_p, _i64, _p, _i64, _i, _p, _p, _i, _p, _p, _i, _p, _p]),
 }
 

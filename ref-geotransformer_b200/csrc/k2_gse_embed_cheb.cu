@@ -35,6 +35,12 @@
 
 namespace geotx {
 
+#ifndef CHEB_UNROLL
+#define CHEB_UNROLL 2  // m-tiles of a warp unrolled together (timing experiments: -DCHEB_UNROLL=1|2|4)
+#endif
+#ifndef CHEB_MIN_CTAS
+#define CHEB_MIN_CTAS 2
+#endif
 constexpr int CHEB_THREADS = 256;
 constexpr int CHEB_TILE = 128;                 // pairs per tile
 constexpr int CHEB_NUM_D_SETS = 6;
@@ -165,6 +171,21 @@ __device__ __forceinline__ void cheb_store(uint32_t addr, float t) {
         sts_v4(addr + blk * 16, make_uint4(w[0], w[1], w[2], w[3]));
     }
 }
+// runtime tile count (generic instance)
+__device__ __forceinline__ void cheb_store_rt(uint32_t addr, float t, int tiles) {
+    const float t2 = t + t;
+    float a = 1.f, b = t;
+    for (int blk = 0; blk < 2 * tiles; ++blk) {
+        uint32_t w[4];
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+            w[h] = pack_half2(a, b);
+            a = fmaf(t2, b, -a);
+            b = fmaf(t2, a, -b);
+        }
+        sts_v4(addr + blk * 16, make_uint4(w[0], w[1], w[2], w[3]));
+    }
+}
 // the same, accumulated in registers (for the 'mean' reduction): acc[m] += scale * T_m(t)
 template <int TILES>
 __device__ __forceinline__ void cheb_accumulate(float (&acc)[16 * TILES], float t, float scale) {
@@ -177,6 +198,38 @@ __device__ __forceinline__ void cheb_accumulate(float (&acc)[16 * TILES], float 
         a = fmaf(t2, b, -a);
         b = fmaf(t2, a, -b);
     }
+}
+
+// One embedding argument of a pair (same arithmetic as geotx_common.cuh: pair_argument_one).  -DCHEB_FAST_ATAN=1 (timing
+// experiment) replaces atan2f's branchy slow path by a branch-free minimax polynomial (|error| < 3e-6 rad = 1e-5 index
+// units, 30x below the half rounding of the basis values).
+#ifndef CHEB_FAST_ATAN
+#define CHEB_FAST_ATAN 0
+#endif
+__device__ __forceinline__ float cheb_argument(const float4& pi, const float4& pj, const float4* __restrict__ refv_i, int k,
+                                               int s, float sigma_d, float factor_a) {
+#if CHEB_FAST_ATAN
+    if (s < k) {
+        const float ax = __fsub_rn(pj.x, pi.x), ay = __fsub_rn(pj.y, pi.y), az = __fsub_rn(pj.z, pi.z);
+        const float4 r = __ldg(refv_i + s);
+        const float cx = r.y * az - r.z * ay, cy = r.z * ax - r.x * az, cz = r.x * ay - r.y * ax;
+        const float sn = sqrtf(cx * cx + cy * cy + cz * cz), cs = r.x * ax + r.y * ay + r.z * az;
+        const float ac = fabsf(cs), mx = fmaxf(sn, ac), mn = fminf(sn, ac);
+        const float a = mx > 0.f ? __fdividef(mn, mx) : 0.f, a2 = a * a;
+        float t = fmaf(a2, -0.01172120f, 0.05265332f);
+        t = fmaf(a2, t, -0.11643287f);
+        t = fmaf(a2, t, 0.19354346f);
+        t = fmaf(a2, t, -0.33262347f);
+        t = fmaf(a2, t, 0.99997726f);
+        t *= a;
+        t = sn > ac ? 1.57079633f - t : t;
+        t = cs < 0.f ? 3.14159265f - t : t;
+        return t * factor_a;
+    }
+    return __fdiv_rn(__fsqrt_rn(sqdist_ref(pi, pj)), sigma_d);
+#else
+    return pair_argument_one(pi, pj, refv_i, k, s, sigma_d, factor_a);
+#endif
 }
 
 struct ChebArgs {
@@ -211,15 +264,20 @@ __device__ __forceinline__ void cheb_split(float x, float y, uint32_t& hi, uint3
 // operand of a second contraction with that row's folded query (B operand: channels x heads, hi + lo halves), each
 // warp producing the partial scores of its 32 channels; the 8 partials meet in shared memory and the tile's
 // H x 128 scores are written as 512-byte rows of scores_p.
-template <int C, int KA, int KD, bool SCORES>
+// KD, SL > 0: compile-time numbers of distance K tiles and angle slots (the fast instances: k = 3 with 'max', distance sets 1
+// and 2, i.e. clouds up to 64 index units across -- every shipped configuration); G stays in registers.  KD = SL = 0: the
+// generic instance (any k, 'mean', distance sets 3..5): runtime loops, G read through L1 for every m-tile.
+template <int C, int KA, int KD, bool SCORES, int SL>
 __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned char* smem) {
+    constexpr bool FAST = KD > 0 && SL > 0;
     constexpr int NCB = C / 32;                 // 32-channel blocks = warps sharing a pair group
     constexpr int MT_PER_WARP = NCB;            // 8 m-tiles of 16 pairs / (8 / NCB) pair groups
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int cb = warp % NCB, mt0 = (warp / NCB) * MT_PER_WARP;
-    const int slots = p.slots;
-    const int ktot = slots * 16 * KA + 16 * KD;  // halves per A row
-    const uint32_t pitch = ktot * 2 + 16;         // bytes: = 16 (mod 32), ldmatrix rows fall into distinct banks
+    const int slots = FAST ? SL : p.slots;
+    const int kd_tiles = FAST ? KD : cheb_kd_tiles(d_set);
+    const int ktot = slots * 16 * KA + 16 * kd_tiles;  // halves per A row
+    const uint32_t pitch = ktot * 2 + 16;               // bytes: = 16 (mod 32), ldmatrix rows fall into distinct banks
     const uint32_t a_base = smem_u32(smem);
     const uint32_t buf_bytes = CHEB_TILE * pitch;
     // scores mode: partial[2][NCB][hp][128] floats behind the two A tiles
@@ -227,19 +285,19 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     float* const partial = reinterpret_cast<float*>(smem + 2 * buf_bytes);
     const int partial_floats = NCB * hp * CHEB_TILE;
 
-    // B operand: this warp's 32 channels of G, register-resident for the whole kernel
-    uint2 b_a[KA][4], b_d[KD][4];
-    {
-        const uint2* src = reinterpret_cast<const uint2*>(p.coef);
+    // B operand: this warp's 32 channels of G
+    const uint2* const g_a = reinterpret_cast<const uint2*>(p.coef) + cb * 128 + lane;                       // + (kt * NCB * 4 + t) * 32
+    const uint2* const g_d = reinterpret_cast<const uint2*>(p.coef + p.d_set_offset[d_set]) + cb * 128 + lane;
+    uint2 b_a[KA][4], b_d[FAST ? KD : 1][4];
+    if (FAST) {
 #pragma unroll
         for (int kt = 0; kt < KA; ++kt)
 #pragma unroll
-            for (int t = 0; t < 4; ++t) b_a[kt][t] = __ldg(src + ((kt * NCB + cb) * 4 + t) * 32 + lane);
-        src = reinterpret_cast<const uint2*>(p.coef + p.d_set_offset[d_set]);
+            for (int t = 0; t < 4; ++t) b_a[kt][t] = __ldg(g_a + (kt * NCB * 4 + t) * 32);
 #pragma unroll
         for (int kt = 0; kt < KD; ++kt)
 #pragma unroll
-            for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(src + ((kt * NCB + cb) * 4 + t) * 32 + lane);
+            for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(g_d + (kt * NCB * 4 + t) * 32);
     }
     const float inv_half_ld = 2.f / cheb_range(d_set);
     const float x_lim_d = cheb_range(d_set) * 1.0001f, x_lim_a = 2.0002f / p.inv_half_la;
@@ -278,7 +336,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         const uint32_t row = a_base + buf * buf_bytes + ppair * pitch;
         if (!p.reduce_mean) {
             for (int s = s_begin; s < s_end; ++s) {
-                const float x = pair_argument_one(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
+                const float x = cheb_argument(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
                 clamped |= !(x <= x_lim_a);
                 cheb_store<KA>(row + s * (32 * KA), fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f));
             }
@@ -288,7 +346,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
             for (int m = 0; m < 16 * KA; ++m) acc[m] = 0.f;
             const float scale = 1.f / (float)p.k;
             for (int s = 0; s < p.k; ++s) {
-                const float x = pair_argument_one(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
+                const float x = cheb_argument(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
                 clamped |= !(x <= x_lim_a);
                 cheb_accumulate<KA>(acc, fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f), scale);
             }
@@ -298,9 +356,11 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                                                   pack_half2(acc[8 * blk + 4], acc[8 * blk + 5]), pack_half2(acc[8 * blk + 6], acc[8 * blk + 7])));
         }
         if (prole) {
-            const float x = pair_argument_one(pi, pj, refv_i, p.k, p.k, p.sigma_d, p.factor_a);
+            const float x = cheb_argument(pi, pj, refv_i, p.k, p.k, p.sigma_d, p.factor_a);
             clamped |= !(x <= x_lim_d);
-            cheb_store<KD>(row + slots * (32 * KA), fminf(fmaxf(fmaf(x, inv_half_ld, -1.f), -1.f), 1.f));
+            const float t = fminf(fmaxf(fmaf(x, inv_half_ld, -1.f), -1.f), 1.f);
+            if (FAST) cheb_store<FAST ? KD : 1>(row + slots * (32 * KA), t);
+            else cheb_store_rt(row + slots * (32 * KA), t, kd_tiles);
         }
     };
 
@@ -333,15 +393,45 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
             for (int r = 0; r < 2; ++r) cheb_split(f[4 * kt2 + 2 * r], f[4 * kt2 + 2 * r + 1], q_hi[kt2][r], q_lo[kt2][r]);
     };
 
-    auto consume = [&](long long tile, int buf) {
-        const uint32_t tile_addr = a_base + buf * buf_bytes + ld_off;
-        const long long pair0 = tile * CHEB_TILE;
-        if (SCORES) load_query(tile);
-#pragma unroll 1
-        for (int mi = 0; mi < MT_PER_WARP; ++mi) {
-            const int mt = mt0 + mi;
-            uint32_t addr = tile_addr + mt * 16 * pitch;
-            float best[4][4];
+    // E of one m-tile (16 pairs x this warp's 32 channels) in the accumulator layout
+    auto mtile = [&](uint32_t addr, float (&best)[4][4]) {
+        if (FAST) {
+            // every ldmatrix first, then SL * KA * 4 + KD * 4 MMAs of which only the K tiles of one expansion depend on
+            // each other, then the max over the slots (geotransformer.py:66) and the sum (:70) in registers
+            uint32_t a_s[FAST ? SL : 1][KA][4], a_d[FAST ? KD : 1][4];
+#pragma unroll
+            for (int sl = 0; sl < SL; ++sl)
+#pragma unroll
+                for (int kt = 0; kt < KA; ++kt) ldsm4(a_s[sl][kt], addr + (sl * KA + kt) * 32);
+#pragma unroll
+            for (int kt = 0; kt < KD; ++kt) ldsm4(a_d[kt], addr + (SL * KA + kt) * 32);
+            float acc[FAST ? SL : 1][4][4], accd[4][4];
+#pragma unroll
+            for (int sl = 0; sl < SL; ++sl)
+#pragma unroll
+                for (int kt = 0; kt < KA; ++kt)
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        if (kt == 0) mma_new(acc[sl][t], a_s[sl][kt], b_a[kt][t]);
+                        else mma_acc(acc[sl][t], a_s[sl][kt], b_a[kt][t]);
+                    }
+#pragma unroll
+            for (int kt = 0; kt < KD; ++kt)
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    if (kt == 0) mma_new(accd[t], a_d[kt], b_d[kt][t]);
+                    else mma_acc(accd[t], a_d[kt], b_d[kt][t]);
+                }
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    float v = acc[0][t][r];
+#pragma unroll
+                    for (int sl = 1; sl < SL; ++sl) v = fmaxf(v, acc[sl][t][r]);
+                    best[t][r] = v + accd[t][r];
+                }
+        } else {
             uint32_t a[4];
             for (int s = 0; s < slots; ++s) {
                 float cur[4][4];
@@ -351,8 +441,9 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                     addr += 32;
 #pragma unroll
                     for (int t = 0; t < 4; ++t) {
-                        if (kt == 0) mma_new(cur[t], a, b_a[kt][t]);
-                        else mma_acc(cur[t], a, b_a[kt][t]);
+                        const uint2 bb = __ldg(g_a + (kt * NCB * 4 + t) * 32);
+                        if (kt == 0) mma_new(cur[t], a, bb);
+                        else mma_acc(cur[t], a, bb);
                     }
                 }
 #pragma unroll
@@ -360,13 +451,34 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
 #pragma unroll
                     for (int r = 0; r < 4; ++r) best[t][r] = s == 0 ? cur[t][r] : fmaxf(best[t][r], cur[t][r]);
             }
-#pragma unroll
-            for (int kt = 0; kt < KD; ++kt) {
+            float accd[4][4];
+            for (int kt = 0; kt < kd_tiles; ++kt) {
                 ldsm4(a, addr);
                 addr += 32;
 #pragma unroll
-                for (int t = 0; t < 4; ++t) mma_acc(best[t], a, b_d[kt][t]);
+                for (int t = 0; t < 4; ++t) {
+                    const uint2 bb = __ldg(g_d + (kt * NCB * 4 + t) * 32);
+                    if (kt == 0) mma_new(accd[t], a, bb);
+                    else mma_acc(accd[t], a, bb);
+                }
             }
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) best[t][r] += accd[t][r];
+        }
+    };
+
+    auto consume = [&](long long tile, int buf) {
+        const uint32_t tile_addr = a_base + buf * buf_bytes + ld_off;
+        const long long pair0 = tile * CHEB_TILE;
+        if (SCORES) load_query(tile);
+        constexpr int kUnroll = FAST ? CHEB_UNROLL : 1;
+#pragma unroll kUnroll
+        for (int mi = 0; mi < MT_PER_WARP; ++mi) {
+            const int mt = mt0 + mi;
+            float best[4][4];
+            mtile(tile_addr + mt * 16 * pitch, best);
             if (SCORES) {
                 // E (rounded to half like the stored E) x folded query: rows = the m-tile's 16 keys, columns = heads
                 float sc[4];
@@ -440,20 +552,17 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
 }
 
 template <int C, int KA, bool SCORES>
-__global__ void __launch_bounds__(CHEB_THREADS, 2) gse_embed_cheb_kernel(const ChebArgs p) {
+__global__ void __launch_bounds__(CHEB_THREADS, CHEB_MIN_CTAS) gse_embed_cheb_kernel(const ChebArgs p) {
     extern __shared__ __align__(16) unsigned char cheb_smem[];
     // the coefficient set of the distance term: the shortest expansion that covers the clouds' largest distance
     const float x_max = __fdiv_rn(__fsqrt_rn(__uint_as_float(__ldg(p.dmax2_bits))), p.sigma_d);
     int d_set = 0;
     while (d_set < p.max_d_set && x_max > cheb_range(d_set)) ++d_set;
-    switch (d_set) {
-        case 0: cheb_run<C, KA, 1, SCORES>(p, 0, cheb_smem); break;
-        case 1: cheb_run<C, KA, 2, SCORES>(p, 1, cheb_smem); break;
-        case 2: cheb_run<C, KA, 3, SCORES>(p, 2, cheb_smem); break;
-        case 3: cheb_run<C, KA, 4, SCORES>(p, 3, cheb_smem); break;
-        case 4: cheb_run<C, KA, 6, SCORES>(p, 4, cheb_smem); break;
-        default: cheb_run<C, KA, 8, SCORES>(p, 5, cheb_smem); break;
-    }
+    // fast instances: 3 angle slots (k = 3, 'max'), distance sets 1 (also serving set 0: its 32 coefficients cover the
+    // shorter range too) and 2; everything else runs the generic instance
+    if (p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3>(p, 1, cheb_smem);
+    else if (p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3>(p, 2, cheb_smem);
+    else cheb_run<C, KA, 0, SCORES, 0>(p, d_set, cheb_smem);
 }
 
 }  // namespace geotx

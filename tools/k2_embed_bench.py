@@ -27,6 +27,11 @@ def setup(n, C, kernel):
     return m, geom
 
 
+def geom_pts(geom):
+    """(n, 3) points back out of the packed geometry (float4 x, y, z, |p|^2)."""
+    return geom.buf[:geom.n * 16].view(torch.float32).view(geom.n, 4)[:, :3].double()
+
+
 def timed(fn, reps=10):
     for _ in range(3):
         fn()
@@ -52,11 +57,13 @@ if len(sys.argv) > 1 and sys.argv[1] == 'once':  # for ncu: three launches of on
     sys.exit(0)
 
 res = {}
-for n, C in ((512, 256), (1024, 256), (2048, 256), (4096, 256), (717, 256), (2048, 128)):
+QUICK = os.environ.get('K2_QUICK') == '1'  # variant libraries (GEOTX_LIB): the low-rank kernel only, three sizes
+SIZES = ((1024, 256), (4096, 256), (2048, 128)) if QUICK else ((512, 256), (1024, 256), (2048, 256), (4096, 256), (717, 256), (2048, 128))
+for n, C in SIZES:
     row = {}
     out = torch.empty(1, n, n, C, dtype=torch.float16, device=dev)
     exact = None
-    for kernel in ('cheb', 'table', 'tensor'):
+    for kernel in (('cheb',) if QUICK else ('cheb', 'table', 'tensor')):
         m, geom = setup(n, C, kernel)
         with torch.no_grad():
             if exact is None:
@@ -70,9 +77,21 @@ for n, C in ((512, 256), (1024, 256), (2048, 256), (4096, 256), (717, 256), (204
                        'rel_err_vs_fp32_kernel': float((got - exact).norm() / exact.norm()),
                        'max_abs_err': float((got - exact).abs().max())}
         if kernel == 'cheb':
+            # K3r: the same expansion + the folded-query scores, E never stored (what the forward runs by default)
+            H = 4
+            qt = torch.randn(1, H, n, C, device=dev)
+            sc = torch.empty(1, H, n, n, device=dev)
+            with torch.no_grad():
+                ms_s = timed(lambda: m.scores(geom, qt, out=sc))
+            kd = 16 * (1, 2, 3, 4, 6, 8)[pkg.ops.gse_cheb_max_d_set(float(torch.cdist(geom_pts(geom), geom_pts(geom)).max()) / m.sigma_d)] \
+                if n <= 4096 else 48
+            flops = n * n * (2.0 * C * (3 * 16 + kd) + 2.0 * C * 8 * 2)
+            row['cheb_scores_K3r'] = {'ms': ms_s, 'executed_tflops': flops / ms_s / 1e9, 'kd': kd,
+                                      'hmma_per_pair': ((3 + kd // 16) * 4 + 4) * (C // 32) / 16.0,
+                                      'clk_per_pair_per_sm_at_1965MHz': ms_s * 1e-3 * 1.965e9 * 148 / (n * n)}
             m.check_overflow()
             row['cheb_sets'] = [(r['range'], r['coefficients'], r['max_error'], r['max_abs_f']) for r in m.cheb_report()]
     res[f'n{n}_C{C}'] = row
     print(json.dumps({f'n{n}_C{C}': row}), flush=True)
 os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
-json.dump(res, open(os.path.join(ROOT, 'gpurun_out', 'k2_embed_bench.json'), 'w'), indent=1)
+json.dump(res, open(os.path.join(ROOT, 'gpurun_out', os.environ.get('K2_OUT', 'k2_embed_bench.json')), 'w'), indent=1)
