@@ -41,8 +41,10 @@ namespace geotx {
 #ifndef CHEB_MIN_CTAS
 #define CHEB_MIN_CTAS 2
 #endif
-constexpr int CHEB_THREADS = 256;
-constexpr int CHEB_TILE = 128;                 // pairs per tile
+constexpr int CHEB_CONSUMER_WARPS = 8, CHEB_PRODUCER_WARPS = 4;
+constexpr int CHEB_THREADS = 32 * (CHEB_CONSUMER_WARPS + CHEB_PRODUCER_WARPS);
+constexpr int CHEB_TILE = 32 * CHEB_PRODUCER_WARPS;  // pairs per tile: one producer thread per pair
+constexpr int CHEB_MT = CHEB_TILE / 16;              // m-tiles (16 pairs) per tile
 constexpr int CHEB_NUM_D_SETS = 6;
 __host__ __device__ constexpr int cheb_kd_tiles(int s) { return s == 0 ? 1 : s == 1 ? 2 : s == 2 ? 3 : s == 3 ? 4 : s == 4 ? 6 : 8; }
 // largest argument the set is built for (tail of the expansion of a unit sinusoid <= 1e-5, see the header)
@@ -141,6 +143,27 @@ __device__ __forceinline__ void mma_acc(float (&d)[4], const uint32_t (&a)[4], c
                  : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
+// half accumulators (fast instances): d = a b and d += a b with D/C as two half2 registers (rows g and g + 8)
+__device__ __forceinline__ void mma_h_new(uint32_t (&d)[2], const uint32_t (&a)[4], const uint2& b) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f16.f16.f16.f16 {%0,%1}, {%2,%3,%4,%5}, {%6,%7}, {%8,%8};"
+                 : "=r"(d[0]), "=r"(d[1])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y), "r"(0u));
+}
+__device__ __forceinline__ void mma_h_acc(uint32_t (&d)[2], const uint32_t (&a)[4], const uint2& b) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f16.f16.f16.f16 {%0,%1}, {%2,%3,%4,%5}, {%6,%7}, {%0,%1};"
+                 : "+r"(d[0]), "+r"(d[1])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+}
+__device__ __forceinline__ uint32_t hmax2_u(uint32_t x, uint32_t y) {
+    uint32_t r;
+    asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(y));
+    return r;
+}
+__device__ __forceinline__ uint32_t hadd2_u(uint32_t x, uint32_t y) {
+    uint32_t r;
+    asm("add.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(x), "r"(y));
+    return r;
+}
 __device__ __forceinline__ uint32_t pack_half2(float lo, float hi) {
     uint32_t r;
     asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
@@ -153,6 +176,11 @@ __device__ __forceinline__ void st_na_v4(void* p, const uint4& v) {
 __device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+
+// named barriers between the producer and the consumer warps (all CHEB_THREADS threads take part: the signalling side
+// arrives, the waiting side syncs)
+__device__ __forceinline__ void cheb_bar_sync(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(CHEB_THREADS) : "memory"); }
+__device__ __forceinline__ void cheb_bar_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "n"(CHEB_THREADS) : "memory"); }
 
 // 16 * TILES Chebyshev values of t (T_0 = 1, T_1 = t, T_{m+1} = 2 t T_m - T_{m-1}) as halves, to smem at `addr`
 template <int TILES>
@@ -200,36 +228,34 @@ __device__ __forceinline__ void cheb_accumulate(float (&acc)[16 * TILES], float 
     }
 }
 
-// One embedding argument of a pair (same arithmetic as geotx_common.cuh: pair_argument_one).  -DCHEB_FAST_ATAN=1 (timing
-// experiment) replaces atan2f's branchy slow path by a branch-free minimax polynomial (|error| < 3e-6 rad = 1e-5 index
-// units, 30x below the half rounding of the basis values).
-#ifndef CHEB_FAST_ATAN
-#define CHEB_FAST_ATAN 0
-#endif
+// One embedding argument of a pair: the quantities of geotx_common.cuh (pair_argument_one / get_embedding_indices,
+// geotransformer.py:38-53) without their IEEE slow paths -- the producers are issue-bound, and the basis values built
+// from the argument are rounded to half (2.4e-4) anyway: sqrt as x rsqrt(x) (2 ulp), the division by sigma_d as a
+// multiplication, atan2 as a branch-free minimax polynomial (7 odd terms on [0,1], |error| < 3.4e-7 rad = 1.3e-6 index
+// units at sigma_a = 15).  atan2(0, 0) = 0 like the reference's (j = i).
+__device__ __forceinline__ float cheb_sqrt(float x) { return x * rsqrtf(fmaxf(x, 1e-30f)); }
+
 __device__ __forceinline__ float cheb_argument(const float4& pi, const float4& pj, const float4* __restrict__ refv_i, int k,
-                                               int s, float sigma_d, float factor_a) {
-#if CHEB_FAST_ATAN
+                                               int s, float inv_sigma_d, float factor_a) {
     if (s < k) {
-        const float ax = __fsub_rn(pj.x, pi.x), ay = __fsub_rn(pj.y, pi.y), az = __fsub_rn(pj.z, pi.z);
+        const float ax = pj.x - pi.x, ay = pj.y - pi.y, az = pj.z - pi.z;
         const float4 r = __ldg(refv_i + s);
         const float cx = r.y * az - r.z * ay, cy = r.z * ax - r.x * az, cz = r.x * ay - r.y * ax;
-        const float sn = sqrtf(cx * cx + cy * cy + cz * cz), cs = r.x * ax + r.y * ay + r.z * az;
+        const float sn = cheb_sqrt(cx * cx + cy * cy + cz * cz), cs = r.x * ax + r.y * ay + r.z * az;
         const float ac = fabsf(cs), mx = fmaxf(sn, ac), mn = fminf(sn, ac);
         const float a = mx > 0.f ? __fdividef(mn, mx) : 0.f, a2 = a * a;
-        float t = fmaf(a2, -0.01172120f, 0.05265332f);
-        t = fmaf(a2, t, -0.11643287f);
-        t = fmaf(a2, t, 0.19354346f);
-        t = fmaf(a2, t, -0.33262347f);
-        t = fmaf(a2, t, 0.99997726f);
+        float t = fmaf(a2, 0.006811776198446751f, -0.033604178577661514f);
+        t = fmaf(a2, t, 0.07962363958358765f);
+        t = fmaf(a2, t, -0.1323334127664566f);
+        t = fmaf(a2, t, 0.19807815551757812f);
+        t = fmaf(a2, t, -0.3331736922264099f);
+        t = fmaf(a2, t, 0.9999961256980896f);
         t *= a;
-        t = sn > ac ? 1.57079633f - t : t;
-        t = cs < 0.f ? 3.14159265f - t : t;
+        t = sn > ac ? 1.5707963267948966f - t : t;
+        t = cs < 0.f ? 3.141592653589793f - t : t;
         return t * factor_a;
     }
-    return __fdiv_rn(__fsqrt_rn(sqdist_ref(pi, pj)), sigma_d);
-#else
-    return pair_argument_one(pi, pj, refv_i, k, s, sigma_d, factor_a);
-#endif
+    return cheb_sqrt(sqdist_ref(pi, pj)) * inv_sigma_d;
 }
 
 struct ChebArgs {
@@ -242,7 +268,7 @@ struct ChebArgs {
     long long pairs_total;           // E mode: pairs of the slab, flattened
     long long tiles;
     int n, k, slots, reduce_mean, row_begin, row_count, out_bf16, max_d_set;
-    float sigma_d, factor_a, inv_half_la;  // 2 / L_a
+    float sigma_d, inv_sigma_d, factor_a, inv_half_la;  // 2 / L_a
     unsigned int d_set_offset[CHEB_NUM_D_SETS];  // halves from coef to distance set s
     // scores mode (K3r): folded query qt[b,h,i,c] with element strides, H heads, key blocks per row
     const float* qt;
@@ -265,59 +291,58 @@ __device__ __forceinline__ void cheb_split(float x, float y, uint32_t& hi, uint3
 // warp producing the partial scores of its 32 channels; the 8 partials meet in shared memory and the tile's
 // H x 128 scores are written as 512-byte rows of scores_p.
 // KD, SL > 0: compile-time numbers of distance K tiles and angle slots (the fast instances: k = 3 with 'max', distance sets 1
-// and 2, i.e. clouds up to 64 index units across -- every shipped configuration); G stays in registers.  KD = SL = 0: the
-// generic instance (any k, 'mean', distance sets 3..5): runtime loops, G read through L1 for every m-tile.
+// and 2, i.e. clouds up to 64 index units across -- every shipped configuration); G stays in registers, accumulators are
+// halves.  KD = SL = 0: the generic instance (any k, 'mean', bf16 output, distance sets 3..5): runtime loops, fp32
+// accumulators, G read through L1 for every m-tile.
+//
+// Warp-specialised CTA of 12 warps over tiles of 128 pairs (8 m-tiles), two tiles in flight:
+//   warps 8-11  producers (48 registers): one thread per pair computes the pair's arguments, runs the recurrences and
+//               writes the pair's row of the A tile; in the scores mode they also stage the tile row's folded query as
+//               mma B fragments and, one tile later, add up the consumers' partial scores and write scores_p
+//   warps 0-7   consumers (96 registers, setmaxnreg): warp w owns 32 channels (C = 256: channel block w of all 8 m-tiles;
+//               C = 128: block w % 4 of four m-tiles); they do nothing but ldmatrix / mma / max / add / store, so that
+//               the tensor pipe never waits for a produce phase
+// Hand-over through named barriers (1, 2: tile buffer b is full; 3, 4: buffer b has been consumed), bar.arrive on the
+// signalling side, bar.sync on the waiting side.
 template <int C, int KA, int KD, bool SCORES, int SL>
 __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned char* smem) {
     constexpr bool FAST = KD > 0 && SL > 0;
-    constexpr int NCB = C / 32;                 // 32-channel blocks = warps sharing a pair group
-    constexpr int MT_PER_WARP = NCB;            // 8 m-tiles of 16 pairs / (8 / NCB) pair groups
+    constexpr int NCB = C / 32;                          // 32-channel blocks
+    constexpr int MT_PER_WARP = CHEB_MT * NCB / CHEB_CONSUMER_WARPS;  // 8 (C = 256) or 4 (C = 128)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int cb = warp % NCB, mt0 = (warp / NCB) * MT_PER_WARP;
     const int slots = FAST ? SL : p.slots;
     const int kd_tiles = FAST ? KD : cheb_kd_tiles(d_set);
     const int ktot = slots * 16 * KA + 16 * kd_tiles;  // halves per A row
     const uint32_t pitch = ktot * 2 + 16;               // bytes: = 16 (mod 32), ldmatrix rows fall into distinct banks
     const uint32_t a_base = smem_u32(smem);
     const uint32_t buf_bytes = CHEB_TILE * pitch;
-    // scores mode: partial[2][NCB][hp][128] floats behind the two A tiles
+    // scores mode, behind the two A tiles: partial[2][NCB][hp][CHEB_TILE] floats (every channel block's share of the
+    // scores) and qimg[2][NCB][32 lanes][8 words]: the tile row's folded query as mma B fragments, hi | lo halves
     const int hp = p.H <= 4 ? 4 : 8;
     float* const partial = reinterpret_cast<float*>(smem + 2 * buf_bytes);
     const int partial_floats = NCB * hp * CHEB_TILE;
-
-    // B operand: this warp's 32 channels of G
-    const uint2* const g_a = reinterpret_cast<const uint2*>(p.coef) + cb * 128 + lane;                       // + (kt * NCB * 4 + t) * 32
-    const uint2* const g_d = reinterpret_cast<const uint2*>(p.coef + p.d_set_offset[d_set]) + cb * 128 + lane;
-    uint2 b_a[KA][4], b_d[FAST ? KD : 1][4];
-    if (FAST) {
-#pragma unroll
-        for (int kt = 0; kt < KA; ++kt)
-#pragma unroll
-            for (int t = 0; t < 4; ++t) b_a[kt][t] = __ldg(g_a + (kt * NCB * 4 + t) * 32);
-#pragma unroll
-        for (int kt = 0; kt < KD; ++kt)
-#pragma unroll
-            for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(g_d + (kt * NCB * 4 + t) * 32);
-    }
-    const float inv_half_ld = 2.f / cheb_range(d_set);
-    const float x_lim_d = cheb_range(d_set) * 1.0001f, x_lim_a = 2.0002f / p.inv_half_la;
-    const long long per_b = (long long)p.row_count * p.n;
+    const uint32_t qimg = a_base + 2 * buf_bytes + 2 * partial_floats * 4;
+    constexpr int QIMG_BYTES = NCB * 32 * 32;
     const long long tiles = p.tiles;
-    bool clamped = false;
+    const long long per_b = (long long)p.row_count * p.n;
 
-    // producer role (warp-uniform): warps 0-3 take the first half of the angle slots of pair tid, warps 4-7 the rest and
-    // the distance of pair tid - 128
-    const int ppair = tid & (CHEB_TILE - 1), prole = tid >> 7;
-    const int s_split = (slots + 1) >> 1;
-    const int s_begin = prole ? s_split : 0, s_end = prole ? slots : s_split;
-
-    // tile -> (cloud b, query row i, first key j0); E mode: of the tile's pair `local`
+    // tile -> (cloud b, query row i, key j) of the tile's pair `local`.  32-bit arithmetic whenever the slab has fewer
+    // than 2^32 pairs (64-bit divisions cost ~100 instructions each)
+    const bool small = (unsigned long long)p.pairs_total < 0xffffffffull;
     auto locate = [&](long long tile, int local, long long& b, int& i, int& j) {
         if (SCORES) {
-            const long long row = tile / p.key_blocks;
-            b = row / p.row_count;
-            i = p.row_begin + (int)(row - b * p.row_count);
-            j = min((int)(tile - row * p.key_blocks) * CHEB_TILE + local, p.n - 1);
+            const unsigned row = (unsigned)tile / (unsigned)p.key_blocks;
+            const unsigned bb = row / (unsigned)p.row_count;
+            b = bb;
+            i = p.row_begin + (int)(row - bb * (unsigned)p.row_count);
+            j = min((int)((unsigned)tile - row * (unsigned)p.key_blocks) * CHEB_TILE + local, p.n - 1);
+        } else if (small) {
+            const unsigned g = min((unsigned)tile * CHEB_TILE + (unsigned)local, (unsigned)p.pairs_total - 1u);
+            const unsigned rowg = g / (unsigned)p.n;  // = b * row_count + local row
+            const unsigned bb = rowg / (unsigned)p.row_count;
+            b = bb;
+            i = p.row_begin + (int)(rowg - bb * (unsigned)p.row_count);
+            j = (int)(g - rowg * (unsigned)p.n);
         } else {
             const long long g = min(tile * CHEB_TILE + local, p.pairs_total - 1);
             b = g / per_b;
@@ -327,228 +352,273 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         }
     };
 
-    auto produce = [&](long long tile, int buf) {
-        long long b;
-        int i, j;
-        locate(tile, ppair, b, i, j);
-        const float4 pi = __ldg(p.pts4 + b * p.n + i), pj = __ldg(p.pts4 + b * p.n + j);
-        const float4* refv_i = p.refv + (b * p.n + i) * p.k;
-        const uint32_t row = a_base + buf * buf_bytes + ppair * pitch;
-        if (!p.reduce_mean) {
-            for (int s = s_begin; s < s_end; ++s) {
-                const float x = cheb_argument(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
-                clamped |= !(x <= x_lim_a);
-                cheb_store<KA>(row + s * (32 * KA), fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f));
+    if (SCORES) {  // fragment lanes of heads >= H read zeros
+        for (int e = tid; e < 2 * QIMG_BYTES / 16; e += CHEB_THREADS) sts_v4(qimg + e * 16, make_uint4(0u, 0u, 0u, 0u));
+    }
+    __syncthreads();
+
+    if (warp >= CHEB_CONSUMER_WARPS) {
+        // ======================================== producers ========================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
+        const int ptid = tid - CHEB_CONSUMER_WARPS * 32;  // = the pair of the tile this thread builds
+        const float inv_half_ld = 2.f / cheb_range(d_set);
+        const float x_lim_d = cheb_range(d_set) * 1.0001f;
+        bool clamped = false;
+
+        auto produce = [&](long long tile, int buf) {
+            long long b;
+            int i, j;
+            locate(tile, ptid, b, i, j);
+            const float4 pi = __ldg(p.pts4 + b * p.n + i), pj = __ldg(p.pts4 + b * p.n + j);
+            const float4* refv_i = p.refv + (b * p.n + i) * p.k;
+            const uint32_t row = a_base + buf * buf_bytes + ptid * pitch;
+            if (FAST) {  // k = SL slots, 'max': straight-line code, the recurrences of the slots interleave
+#pragma unroll
+                for (int s = 0; s < SL; ++s) {
+                    const float x = cheb_argument(pi, pj, refv_i, SL, s, p.inv_sigma_d, p.factor_a);
+                    cheb_store<KA>(row + s * (32 * KA), fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f));
+                }
+            } else if (!p.reduce_mean) {
+                for (int s = 0; s < slots; ++s) {
+                    const float x = cheb_argument(pi, pj, refv_i, p.k, s, p.inv_sigma_d, p.factor_a);
+                    cheb_store<KA>(row + s * (32 * KA), fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f));
+                }
+            } else {  // geotransformer.py:68: the mean over the k neighbours is linear in the basis
+                float acc[16 * KA];
+#pragma unroll
+                for (int m = 0; m < 16 * KA; ++m) acc[m] = 0.f;
+                const float scale = 1.f / (float)p.k;
+                for (int s = 0; s < p.k; ++s) {
+                    const float x = cheb_argument(pi, pj, refv_i, p.k, s, p.inv_sigma_d, p.factor_a);
+                    cheb_accumulate<KA>(acc, fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f), scale);
+                }
+#pragma unroll
+                for (int blk = 0; blk < 2 * KA; ++blk)
+                    sts_v4(row + blk * 16, make_uint4(pack_half2(acc[8 * blk], acc[8 * blk + 1]), pack_half2(acc[8 * blk + 2], acc[8 * blk + 3]),
+                                                      pack_half2(acc[8 * blk + 4], acc[8 * blk + 5]), pack_half2(acc[8 * blk + 6], acc[8 * blk + 7])));
             }
-        } else if (!prole) {  // geotransformer.py:68: the mean over the k neighbours is linear in the basis
-            float acc[16 * KA];
-#pragma unroll
-            for (int m = 0; m < 16 * KA; ++m) acc[m] = 0.f;
-            const float scale = 1.f / (float)p.k;
-            for (int s = 0; s < p.k; ++s) {
-                const float x = cheb_argument(pi, pj, refv_i, p.k, s, p.sigma_d, p.factor_a);
-                clamped |= !(x <= x_lim_a);
-                cheb_accumulate<KA>(acc, fminf(fmaxf(fmaf(x, p.inv_half_la, -1.f), -1.f), 1.f), scale);
+            {
+                const float x = cheb_argument(pi, pj, refv_i, p.k, p.k, p.inv_sigma_d, p.factor_a);
+                clamped |= !(x <= x_lim_d);
+                const float t = fminf(fmaxf(fmaf(x, inv_half_ld, -1.f), -1.f), 1.f);
+                if (FAST) cheb_store<FAST ? KD : 1>(row + slots * (32 * KA), t);
+                else cheb_store_rt(row + slots * (32 * KA), t, kd_tiles);
             }
+            if (SCORES) {
+                // the folded query of the tile's row as B fragments of the score contraction: fragment column n = head;
+                // lane (g = head, q) of channel block cb holds the 8 consecutive channels 32 cb + 8 q .. + 7 (the channel
+                // <-> k-slot assignment of the accumulators that become the A operand), as two half2 pairs per 16-channel
+                // k-tile, hi then lo.  Item = (head, 8-channel group); lanes of heads >= H stay zero.
+                for (int it = ptid; it < p.H * (C / 8); it += CHEB_PRODUCER_WARPS * 32) {
+                    const int h = it / (C / 8), grp = it - h * (C / 8);  // grp = 4 cb + q
+                    const float* src = p.qt + b * p.qsb + (long long)h * p.qsh + (long long)i * p.qsn + grp * 8;
+                    const float4 u = __ldg(reinterpret_cast<const float4*>(src)), v = __ldg(reinterpret_cast<const float4*>(src + 4));
+                    uint4 hi, lo;
+                    cheb_split(u.x, u.y, hi.x, lo.x);
+                    cheb_split(u.z, u.w, hi.y, lo.y);
+                    cheb_split(v.x, v.y, hi.z, lo.z);
+                    cheb_split(v.z, v.w, hi.w, lo.w);
+                    const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * 32;
+                    sts_v4(dst, hi);
+                    sts_v4(dst + 16, lo);
+                }
+            }
+        };
+        // the channel blocks' partial scores of a consumed tile -> scores_p[b, h, i, j0 .. j0 + CHEB_TILE - 1]
+        auto reduce = [&](long long tile, int buf) {
+            long long b;
+            int i, j0;
+            locate(tile, 0, b, i, j0);
+            const float* src = partial + buf * partial_floats;
+            float* const out = reinterpret_cast<float*>(p.out) + (((size_t)b * p.H) * p.n + i) * p.n + j0;
+            for (int e = ptid; e < p.H * CHEB_TILE; e += CHEB_PRODUCER_WARPS * 32) {
+                const int h = e / CHEB_TILE, jl = e & (CHEB_TILE - 1);
+                float v = 0.f;
 #pragma unroll
-            for (int blk = 0; blk < 2 * KA; ++blk)
-                sts_v4(row + blk * 16, make_uint4(pack_half2(acc[8 * blk], acc[8 * blk + 1]), pack_half2(acc[8 * blk + 2], acc[8 * blk + 3]),
-                                                  pack_half2(acc[8 * blk + 4], acc[8 * blk + 5]), pack_half2(acc[8 * blk + 6], acc[8 * blk + 7])));
-        }
-        if (prole) {
-            const float x = cheb_argument(pi, pj, refv_i, p.k, p.k, p.sigma_d, p.factor_a);
-            clamped |= !(x <= x_lim_d);
-            const float t = fminf(fmaxf(fmaf(x, inv_half_ld, -1.f), -1.f), 1.f);
-            if (FAST) cheb_store<FAST ? KD : 1>(row + slots * (32 * KA), t);
-            else cheb_store_rt(row + slots * (32 * KA), t, kd_tiles);
-        }
-    };
+                for (int w = 0; w < NCB; ++w) v += src[(w * hp + h) * CHEB_TILE + jl];
+                if (j0 + jl < p.n) out[(size_t)h * p.n * p.n + jl] = v;
+            }
+        };
 
-    // ldmatrix: lane l addresses row (l & 15) of the m-tile, columns 8 (l >> 4) ..; mma: g = lane / 4 is the fragment
-    // row, q = lane % 4 the column pair
-    const uint32_t ld_off = (lane & 15) * pitch + (lane >> 4) * 16;
-    const int g = lane >> 2, q = lane & 3;
-    unsigned char* const out_bytes = reinterpret_cast<unsigned char*>(p.out);
-
-    // scores mode: B fragments of the folded query of a tile's row.  Fragment column n = g is the head; thread (g, q)
-    // holds the 8 consecutive channels 32 cb + 8 q .. + 7 (the same channel <-> k-slot assignment as the accumulators
-    // that become the A operand: n-tiles 2 kt2, 2 kt2 + 1 form k-tile kt2)
-    uint32_t q_hi[2][2], q_lo[2][2];
-    auto load_query = [&](long long tile) {
-        long long b;
-        int i, j;
-        locate(tile, 0, b, i, j);
-        float f[8];
-        if (g < p.H) {
-            const float* src = p.qt + b * p.qsb + (long long)g * p.qsh + (long long)i * p.qsn + cb * 32 + q * 8;
-            const float4 u = __ldg(reinterpret_cast<const float4*>(src)), v = __ldg(reinterpret_cast<const float4*>(src + 4));
-            f[0] = u.x; f[1] = u.y; f[2] = u.z; f[3] = u.w; f[4] = v.x; f[5] = v.y; f[6] = v.z; f[7] = v.w;
-        } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = 0.f;
+        int it = 0;
+        long long tile = blockIdx.x, older = 0, old = 0;  // the tiles of the two previous iterations
+        for (; tile < tiles; tile += gridDim.x, ++it) {
+            const int buf = it & 1;
+            if (it >= 2) {
+                cheb_bar_sync(3 + buf);  // the consumers are done with tile it - 2: A[buf] is free, partial[buf] complete
+                if (SCORES) reduce(older, buf);
+            }
+            produce(tile, buf);
+            __threadfence_block();
+            cheb_bar_arrive(1 + buf);
+            older = old;
+            old = tile;
         }
-#pragma unroll
-        for (int kt2 = 0; kt2 < 2; ++kt2)
-#pragma unroll
-            for (int r = 0; r < 2; ++r) cheb_split(f[4 * kt2 + 2 * r], f[4 * kt2 + 2 * r + 1], q_hi[kt2][r], q_lo[kt2][r]);
-    };
-
-    // E of one m-tile (16 pairs x this warp's 32 channels) in the accumulator layout
-    auto mtile = [&](uint32_t addr, float (&best)[4][4]) {
+        // drain: the last two tiles' scores
+        if (it >= 2) {
+            cheb_bar_sync(3 + (it & 1));
+            if (SCORES) reduce(older, it & 1);
+        }
+        if (it >= 1) {
+            cheb_bar_sync(3 + ((it + 1) & 1));
+            if (SCORES) reduce(old, (it + 1) & 1);
+        }
+        if (clamped) *p.overflow = 1;
+    } else {
+        // ======================================== consumers ========================================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 96;");
+        const int cb = warp % NCB, mt0 = (warp / NCB) * MT_PER_WARP;
+        // B operand: this warp's 32 channels of G
+        const uint2* const g_a = reinterpret_cast<const uint2*>(p.coef) + cb * 128 + lane;  // + (kt * NCB * 4 + t) * 32
+        const uint2* const g_d = reinterpret_cast<const uint2*>(p.coef + p.d_set_offset[d_set]) + cb * 128 + lane;
+        uint2 b_a[KA][4], b_d[FAST ? KD : 1][4];
         if (FAST) {
-            // every ldmatrix first, then SL * KA * 4 + KD * 4 MMAs of which only the K tiles of one expansion depend on
-            // each other, then the max over the slots (geotransformer.py:66) and the sum (:70) in registers
-            uint32_t a_s[FAST ? SL : 1][KA][4], a_d[FAST ? KD : 1][4];
 #pragma unroll
-            for (int sl = 0; sl < SL; ++sl)
+            for (int kt = 0; kt < KA; ++kt)
 #pragma unroll
-                for (int kt = 0; kt < KA; ++kt) ldsm4(a_s[sl][kt], addr + (sl * KA + kt) * 32);
-#pragma unroll
-            for (int kt = 0; kt < KD; ++kt) ldsm4(a_d[kt], addr + (SL * KA + kt) * 32);
-            float acc[FAST ? SL : 1][4][4], accd[4][4];
-#pragma unroll
-            for (int sl = 0; sl < SL; ++sl)
-#pragma unroll
-                for (int kt = 0; kt < KA; ++kt)
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        if (kt == 0) mma_new(acc[sl][t], a_s[sl][kt], b_a[kt][t]);
-                        else mma_acc(acc[sl][t], a_s[sl][kt], b_a[kt][t]);
-                    }
+                for (int t = 0; t < 4; ++t) b_a[kt][t] = __ldg(g_a + (kt * NCB * 4 + t) * 32);
 #pragma unroll
             for (int kt = 0; kt < KD; ++kt)
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    if (kt == 0) mma_new(accd[t], a_d[kt], b_d[kt][t]);
-                    else mma_acc(accd[t], a_d[kt], b_d[kt][t]);
-                }
+                for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(g_d + (kt * NCB * 4 + t) * 32);
+        }
+        // ldmatrix: lane l addresses row (l & 15) of the m-tile, columns 8 (l >> 4) ..; mma: g = lane / 4 is the fragment
+        // row, q = lane % 4 the column pair
+        const uint32_t ld_off = (lane & 15) * pitch + (lane >> 4) * 16;
+        const int g = lane >> 2, q = lane & 3;
+        unsigned char* const out_bytes = reinterpret_cast<unsigned char*>(p.out);
+
+        auto consume = [&](long long tile, int buf) {
+            const uint32_t tile_addr = a_base + buf * buf_bytes + ld_off;
+            const long long pair0 = tile * CHEB_TILE;
+            uint4 qh, ql;  // the tile row's folded query, this warp's channel block (hi | lo)
+            if (SCORES) {
+                const uint32_t src = qimg + buf * QIMG_BYTES + (cb * 32 + lane) * 32;
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(qh.x), "=r"(qh.y), "=r"(qh.z), "=r"(qh.w) : "r"(src));
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ql.x), "=r"(ql.y), "=r"(ql.z), "=r"(ql.w) : "r"(src + 16));
+            }
+            constexpr int kUnroll = FAST ? CHEB_UNROLL : 1;
+#pragma unroll kUnroll
+            for (int mi = 0; mi < MT_PER_WARP; ++mi) {
+                const int mt = mt0 + mi;
+                uint32_t addr = tile_addr + mt * 16 * pitch;
+                uint32_t bh[4][2];  // E of the m-tile as half2: [n-tile][row g | row g + 8]
+                if (FAST) {
+                    // HALF accumulators: max over the slots (geotransformer.py:66) and the sum with the distance term
+                    // (:70) as packed half2 operations; the registers are already in the layout of the store and of the
+                    // score contraction's A operand
+                    uint32_t a[4], cur[4][2], accd[4][2];
 #pragma unroll
-            for (int t = 0; t < 4; ++t)
+                    for (int sl = 0; sl < SL; ++sl) {
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    float v = acc[0][t][r];
+                        for (int kt = 0; kt < KA; ++kt) {
+                            ldsm4(a, addr + (sl * KA + kt) * 32);
 #pragma unroll
-                    for (int sl = 1; sl < SL; ++sl) v = fmaxf(v, acc[sl][t][r]);
-                    best[t][r] = v + accd[t][r];
-                }
-        } else {
-            uint32_t a[4];
-            for (int s = 0; s < slots; ++s) {
-                float cur[4][4];
+                            for (int t = 0; t < 4; ++t) {
+                                if (kt == 0) mma_h_new(cur[t], a, b_a[kt][t]);
+                                else mma_h_acc(cur[t], a, b_a[kt][t]);
+                            }
+                        }
 #pragma unroll
-                for (int kt = 0; kt < KA; ++kt) {
-                    ldsm4(a, addr);
-                    addr += 32;
+                        for (int t = 0; t < 4; ++t) {
+                            bh[t][0] = sl == 0 ? cur[t][0] : hmax2_u(bh[t][0], cur[t][0]);
+                            bh[t][1] = sl == 0 ? cur[t][1] : hmax2_u(bh[t][1], cur[t][1]);
+                        }
+                    }
+#pragma unroll
+                    for (int kt = 0; kt < KD; ++kt) {
+                        ldsm4(a, addr + (SL * KA + kt) * 32);
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            if (kt == 0) mma_h_new(accd[t], a, b_d[kt][t]);
+                            else mma_h_acc(accd[t], a, b_d[kt][t]);
+                        }
+                    }
 #pragma unroll
                     for (int t = 0; t < 4; ++t) {
-                        const uint2 bb = __ldg(g_a + (kt * NCB * 4 + t) * 32);
-                        if (kt == 0) mma_new(cur[t], a, bb);
-                        else mma_acc(cur[t], a, bb);
+                        bh[t][0] = hadd2_u(bh[t][0], accd[t][0]);
+                        bh[t][1] = hadd2_u(bh[t][1], accd[t][1]);
                     }
-                }
+                } else {
+                    // generic instance: fp32 accumulators, runtime loops, G read through L1
+                    uint32_t a[4];
+                    float best[4][4];
+                    for (int s = 0; s < slots; ++s) {
+                        float cur[4][4];
 #pragma unroll
-                for (int t = 0; t < 4; ++t)
+                        for (int kt = 0; kt < KA; ++kt) {
+                            ldsm4(a, addr);
+                            addr += 32;
 #pragma unroll
-                    for (int r = 0; r < 4; ++r) best[t][r] = s == 0 ? cur[t][r] : fmaxf(best[t][r], cur[t][r]);
-            }
-            float accd[4][4];
-            for (int kt = 0; kt < kd_tiles; ++kt) {
-                ldsm4(a, addr);
-                addr += 32;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const uint2 bb = __ldg(g_d + (kt * NCB * 4 + t) * 32);
-                    if (kt == 0) mma_new(accd[t], a, bb);
-                    else mma_acc(accd[t], a, bb);
-                }
-            }
-#pragma unroll
-            for (int t = 0; t < 4; ++t)
-#pragma unroll
-                for (int r = 0; r < 4; ++r) best[t][r] += accd[t][r];
-        }
-    };
-
-    auto consume = [&](long long tile, int buf) {
-        const uint32_t tile_addr = a_base + buf * buf_bytes + ld_off;
-        const long long pair0 = tile * CHEB_TILE;
-        if (SCORES) load_query(tile);
-        constexpr int kUnroll = FAST ? CHEB_UNROLL : 1;
-#pragma unroll kUnroll
-        for (int mi = 0; mi < MT_PER_WARP; ++mi) {
-            const int mt = mt0 + mi;
-            float best[4][4];
-            mtile(tile_addr + mt * 16 * pitch, best);
-            if (SCORES) {
-                // E (rounded to half like the stored E) x folded query: rows = the m-tile's 16 keys, columns = heads
-                float sc[4];
-#pragma unroll
-                for (int kt2 = 0; kt2 < 2; ++kt2) {
-                    const uint32_t ea[4] = {pack_half2(best[2 * kt2][0], best[2 * kt2][1]), pack_half2(best[2 * kt2][2], best[2 * kt2][3]),
-                                            pack_half2(best[2 * kt2 + 1][0], best[2 * kt2 + 1][1]),
-                                            pack_half2(best[2 * kt2 + 1][2], best[2 * kt2 + 1][3])};
-                    if (kt2 == 0) mma_new(sc, ea, make_uint2(q_hi[0][0], q_hi[0][1]));
-                    else mma_acc(sc, ea, make_uint2(q_hi[1][0], q_hi[1][1]));
-                    mma_acc(sc, ea, make_uint2(q_lo[kt2][0], q_lo[kt2][1]));
-                }
-                // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
-                if (2 * q < hp) {
-                    float* dst = partial + (buf * NCB + cb) * hp * CHEB_TILE + (2 * q) * CHEB_TILE + mt * 16 + g;
-                    dst[0] = sc[0];
-                    dst[CHEB_TILE] = sc[1];
-                    dst[8] = sc[2];
-                    dst[CHEB_TILE + 8] = sc[3];
-                }
-            } else {
-                // thread (g, q): rows g and g + 8 of the m-tile, channels 32 cb + 8 q .. + 7 (n-tile t holds 2 t, 2 t + 1)
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const long long pair = pair0 + mt * 16 + g + 8 * h;
-                    if (pair < p.pairs_total) {
-                        uint4 o;
-                        if (!p.out_bf16) {
-                            o = make_uint4(pack_half2(best[0][2 * h], best[0][2 * h + 1]), pack_half2(best[1][2 * h], best[1][2 * h + 1]),
-                                           pack_half2(best[2][2 * h], best[2][2 * h + 1]), pack_half2(best[3][2 * h], best[3][2 * h + 1]));
-                        } else {
-                            o = make_uint4(pack_bf16x2(best[0][2 * h], best[0][2 * h + 1]), pack_bf16x2(best[1][2 * h], best[1][2 * h + 1]),
-                                           pack_bf16x2(best[2][2 * h], best[2][2 * h + 1]), pack_bf16x2(best[3][2 * h], best[3][2 * h + 1]));
+                            for (int t = 0; t < 4; ++t) {
+                                const uint2 bb = __ldg(g_a + (kt * NCB * 4 + t) * 32);
+                                if (kt == 0) mma_new(cur[t], a, bb);
+                                else mma_acc(cur[t], a, bb);
+                            }
                         }
-                        st_na_v4(out_bytes + ((size_t)pair * C + cb * 32 + q * 8) * 2, o);
+#pragma unroll
+                        for (int t = 0; t < 4; ++t)
+#pragma unroll
+                            for (int r = 0; r < 4; ++r) best[t][r] = s == 0 ? cur[t][r] : fmaxf(best[t][r], cur[t][r]);
+                    }
+                    float accd[4][4];
+                    for (int kt = 0; kt < kd_tiles; ++kt) {
+                        ldsm4(a, addr);
+                        addr += 32;
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            const uint2 bb = __ldg(g_d + (kt * NCB * 4 + t) * 32);
+                            if (kt == 0) mma_new(accd[t], a, bb);
+                            else mma_acc(accd[t], a, bb);
+                        }
+                    }
+                    const bool bf16 = !SCORES && p.out_bf16;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const float v0 = best[t][0] + accd[t][0], v1 = best[t][1] + accd[t][1];
+                        const float v2 = best[t][2] + accd[t][2], v3 = best[t][3] + accd[t][3];
+                        bh[t][0] = bf16 ? pack_bf16x2(v0, v1) : pack_half2(v0, v1);
+                        bh[t][1] = bf16 ? pack_bf16x2(v2, v3) : pack_half2(v2, v3);
+                    }
+                }
+                if (SCORES) {
+                    // E (half, exactly what a stored E would hold) x folded query (hi + lo): rows = the m-tile's 16 keys,
+                    // columns = heads; two independent chains (channels 0-15 | 16-31 of the block)
+                    float sc[4], sc1[4];
+                    const uint32_t e0[4] = {bh[0][0], bh[0][1], bh[1][0], bh[1][1]};
+                    const uint32_t e1[4] = {bh[2][0], bh[2][1], bh[3][0], bh[3][1]};
+                    mma_new(sc, e0, make_uint2(qh.x, qh.y));
+                    mma_new(sc1, e1, make_uint2(qh.z, qh.w));
+                    mma_acc(sc, e0, make_uint2(ql.x, ql.y));
+                    mma_acc(sc1, e1, make_uint2(ql.z, ql.w));
+                    if (2 * q < hp) {  // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
+                        float* dst = partial + (buf * NCB + cb) * hp * CHEB_TILE + (2 * q) * CHEB_TILE + mt * 16 + g;
+                        dst[0] = sc[0] + sc1[0];
+                        dst[CHEB_TILE] = sc[1] + sc1[1];
+                        dst[8] = sc[2] + sc1[2];
+                        dst[CHEB_TILE + 8] = sc[3] + sc1[3];
+                    }
+                } else {
+                    // thread (g, q): rows g and g + 8 of the m-tile, channels 32 cb + 8 q .. + 7 (n-tile t holds 2 t, 2 t + 1)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const long long pair = pair0 + mt * 16 + g + 8 * h;
+                        if (pair < p.pairs_total)
+                            st_na_v4(out_bytes + ((size_t)pair * C + cb * 32 + q * 8) * 2, make_uint4(bh[0][h], bh[1][h], bh[2][h], bh[3][h]));
                     }
                 }
             }
-        }
-    };
+        };
 
-    // scores mode: the 8 channel blocks' partial scores of a finished tile -> scores_p[b, h, i, j0 .. j0 + 127]
-    auto reduce = [&](long long tile, int buf) {
-        long long b;
-        int i, j0;
-        locate(tile, 0, b, i, j0);
-        const float* src = partial + buf * partial_floats;
-        float* const out = reinterpret_cast<float*>(p.out);
-        for (int e = tid; e < p.H * CHEB_TILE; e += CHEB_THREADS) {
-            const int h = e >> 7, jl = e & (CHEB_TILE - 1);
-            float v = 0.f;
-#pragma unroll
-            for (int w = 0; w < NCB; ++w) v += src[(w * hp + h) * CHEB_TILE + jl];
-            if (j0 + jl < p.n) out[(((size_t)b * p.H + h) * p.n + i) * p.n + j0 + jl] = v;
+        int it = 0;
+        for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+            const int buf = it & 1;
+            cheb_bar_sync(1 + buf);  // the producers have filled A[buf] (and the query image)
+            consume(tile, buf);
+            __threadfence_block();
+            cheb_bar_arrive(3 + buf);
         }
-    };
-
-    long long tile = blockIdx.x;
-    int buf = 0;
-    if (tile < tiles) produce(tile, 0);
-    __syncthreads();
-    for (; tile < tiles; tile += gridDim.x) {
-        const long long next = tile + gridDim.x;
-        if (next < tiles) produce(next, buf ^ 1);
-        consume(tile, buf);
-        __syncthreads();
-        if (SCORES) reduce(tile, buf);  // reads partial[buf]; the next writer of partial[buf] is two barriers away
-        buf ^= 1;
     }
-    if (clamped) *p.overflow = 1;
 }
 
 template <int C, int KA, bool SCORES>
@@ -560,8 +630,9 @@ __global__ void __launch_bounds__(CHEB_THREADS, CHEB_MIN_CTAS) gse_embed_cheb_ke
     while (d_set < p.max_d_set && x_max > cheb_range(d_set)) ++d_set;
     // fast instances: 3 angle slots (k = 3, 'max'), distance sets 1 (also serving set 0: its 32 coefficients cover the
     // shorter range too) and 2; everything else runs the generic instance
-    if (p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3>(p, 1, cheb_smem);
-    else if (p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3>(p, 2, cheb_smem);
+    const bool half_out = SCORES || !p.out_bf16;  // the fast instances accumulate in half
+    if (half_out && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3>(p, 1, cheb_smem);
+    else if (half_out && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3>(p, 2, cheb_smem);
     else cheb_run<C, KA, 0, SCORES, 0>(p, d_set, cheb_smem);
 }
 
@@ -632,6 +703,7 @@ static int cheb_launch(const char* what, const void* geometry, int B, int n, int
     p.out_bf16 = out_dtype == GEOTX_BF16;
     p.max_d_set = max_d_set;
     p.sigma_d = sigma_d;
+    p.inv_sigma_d = 1.f / sigma_d;
     p.factor_a = factor_a;
     p.inv_half_la = 2.f / angle_index_max;
     for (int s = 0; s < CHEB_NUM_D_SETS; ++s) p.d_set_offset[s] = (unsigned int)cheb_set_offset(C, ka_tiles, 1 + s);
@@ -642,20 +714,23 @@ static int cheb_launch(const char* what, const void* geometry, int B, int n, int
     p.H = H;
     p.key_blocks = (n + CHEB_TILE - 1) / CHEB_TILE;
     p.tiles = scores ? (long long)B * row_count * p.key_blocks : (p.pairs_total + CHEB_TILE - 1) / CHEB_TILE;
+    GEOTX_REQUIRE(p.tiles < 2147483647LL, "%s: too many tiles", what);
     const int ktot_max = p.slots * 16 * ka_tiles + 16 * cheb_kd_tiles(max_d_set);
     size_t smem = (size_t)2 * CHEB_TILE * (ktot_max * 2 + 16);
-    if (scores) smem += (size_t)2 * (C / 32) * (H <= 4 ? 4 : 8) * CHEB_TILE * sizeof(float);
+    if (scores) smem += (size_t)2 * (C / 32) * (H <= 4 ? 4 : 8) * CHEB_TILE * sizeof(float) + (size_t)2 * (C / 32) * 32 * 32;
     GEOTX_REQUIRE(smem <= 220 * 1024, "%s: %zu B of shared memory (k=%d, max_d_set=%d) do not fit", what, smem, k, max_d_set);
     int dev = 0, sms = 0;
     int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
     if (rc) return rc;
     rc = check_cuda(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
     if (rc) return rc;
-    const int per_sm = smem <= 110 * 1024 ? 2 : 1;
-    const int grid = (int)std::min<long long>(p.tiles, (long long)sms * per_sm);
     auto launch = [&](auto kernel) -> int {
         int r = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), what);
         if (r) return r;
+        int per_sm = 0;  // persistent grid: exactly the CTAs that are resident at once
+        r = check_cuda(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, CHEB_THREADS, smem), what);
+        if (r) return r;
+        const int grid = (int)std::min<long long>(p.tiles, (long long)sms * std::max(per_sm, 1));
         kernel<<<grid, CHEB_THREADS, smem, (cudaStream_t)stream>>>(p);
         return 0;
     };

@@ -163,8 +163,12 @@ class GeometricStructureEmbedding(nn.Module):
                 warning (never to a CPU path);
       'table'   K2t, the sampled tables of round 1 (hidden_dim 128/256, angle_k 3, 'max', f16 only);
       'tensor'  K2, the full-rank tcgen05 contraction (also used for fp32 output and the fused first-block scores).
-    `cheb_d_index_max` caps the distance range K2c is prepared for (210 index units = 42 m at sigma_d = 0.2); the kernel
-    itself picks the shortest expansion that covers the cloud at hand.  `table_d_index_max`: reach of K2t's table."""
+    `cheb_d_index_max` is the largest distance / sigma_d K2c / K3r are prepared for: it sizes their shared memory (64
+    index units -- 12.8 m at sigma_d = 0.2, 307 m at KITTI's 4.8 -- keeps two CTAs per SM; at most 210); below it the
+    kernel itself picks the shortest expansion that covers the cloud at hand.  A cloud that exceeds it raises the
+    kernel's overflow flag: the first eager call of every shape reads the flag, widens `cheb_d_index_max` to 210 and
+    repeats the call; CUDA-graph replays check the flag of the PREVIOUS replay (GraphedGeometricTransformer).
+    `table_d_index_max`: reach of K2t's table."""
 
     def __init__(self, hidden_dim, sigma_d, sigma_a, angle_k, reduction_a='max', precision='auto'):
         super().__init__()
@@ -191,7 +195,7 @@ class GeometricStructureEmbedding(nn.Module):
         self.table_d_index_max = 96.0
         self._tables_cache = None
         self._tables_key = None
-        self.cheb_d_index_max = 210.0
+        self.cheb_d_index_max = 64.0
         self.cheb_error_budget = 2e-3  # largest |expansion - f| over largest |f|, per coefficient set
         self._cheb_cache = None
         self._cheb_key = None
@@ -240,7 +244,7 @@ class GeometricStructureEmbedding(nn.Module):
             ts = (self.proj_d.weight, self.proj_d.bias, self.proj_a.weight, self.proj_a.bias)
             w_d, b_d, w_a, b_a = [t.detach().contiguous() for t in ts]
             coef = ops.gse_build_cheb(self.embedding.div_term, w_d, b_d, w_a, b_a, self.factor_a)
-            used = [0] + list(range(1, 2 + ops.gse_cheb_max_d_set(self.cheb_d_index_max)))
+            used = range(7)  # the angle set and all six distance sets (cheb_d_index_max may be widened later)
             rep = coef.report()
             bad = [rep[i] for i in used
                    if not rep[i]['max_error'] <= self.cheb_error_budget * max(rep[i]['max_abs_f'], 1e-30)]
@@ -295,13 +299,9 @@ class GeometricStructureEmbedding(nn.Module):
         (E, scores_p): the first 'self' block's additive scores come out of the same kernel."""
         mean = self.reduction_a == 'mean'
         if self._use_cheb(out_dtype, qt):
-            e = ops.gse_embed_cheb(geom, self._cheb_cache, self.sigma_d, self.factor_a, mean, out_dtype,
-                                   ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out)
-            shape = (geom.B, geom.n)
-            if shape not in self._overflow_checked and not torch.cuda.is_current_stream_capturing():
-                self._overflow_checked.add(shape)  # first eager call of a shape: one synchronising read of the flag
-                self.check_overflow()
-            return e
+            return self._cheb_call(geom, lambda: ops.gse_embed_cheb(
+                geom, self._cheb_cache, self.sigma_d, self.factor_a, mean, out_dtype,
+                ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out))
         if self._use_table(out_dtype, qt):
             return ops.gse_embed_table(geom, self._tables(), self.sigma_d, self.factor_a, row_begin, row_count, out)
         if self._use_tensor_cores():
@@ -319,13 +319,26 @@ class GeometricStructureEmbedding(nn.Module):
         if not self._use_cheb(torch.float16, None):
             raise RuntimeError('GeometricStructureEmbedding.scores needs the low-rank embedding kernel (embed_kernel = '
                                "'cheb', hidden_dim 128 / 256)")
-        sc = ops.rpe_scores_cheb(geom, self._cheb_cache, qt, self.sigma_d, self.factor_a, self.reduction_a == 'mean',
-                                 ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out)
-        shape = (geom.B, geom.n)
-        if shape not in self._overflow_checked and not torch.cuda.is_current_stream_capturing():
-            self._overflow_checked.add(shape)
-            self.check_overflow()
-        return sc
+        return self._cheb_call(geom, lambda: ops.rpe_scores_cheb(
+            geom, self._cheb_cache, qt, self.sigma_d, self.factor_a, self.reduction_a == 'mean',
+            ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out))
+
+    def _cheb_call(self, geom, launch):
+        """Runs a K2c / K3r launch; on the first eager call of a shape the overflow flag is read (one synchronisation) and
+        a cloud larger than `cheb_d_index_max` widens the range to the kernels' maximum and repeats the launch."""
+        res = launch()
+        key = (geom.B, geom.n, self.cheb_d_index_max)
+        if key not in self._overflow_checked and not torch.cuda.is_current_stream_capturing():
+            self._overflow_checked.add(key)
+            if int(self._cheb_cache.overflow.item()) != 0:
+                if self.cheb_d_index_max >= 210.0:
+                    self.check_overflow()  # raises
+                warnings.warn(f'ref-geotransformer_b200: a cloud exceeds cheb_d_index_max = {self.cheb_d_index_max:g} index '
+                              'units; widening it to 210 (one CTA per SM for the embedding kernels from now on)')
+                self.cheb_d_index_max = 210.0
+                self._cheb_cache.overflow.zero_()
+                return self._cheb_call(geom, launch)  # the launch reads cheb_d_index_max when it runs
+        return res
 
     def forward(self, points, out_dtype=torch.float32):
         """(B,n,3) -> (B,n,n,C).  Standalone calls return fp32 like the reference; GeometricTransformer asks for
@@ -988,9 +1001,17 @@ class GraphedGeometricTransformer:
             for _ in range(self.warmup):
                 self.model(*self.static_in)
         torch.cuda.current_stream().wait_stream(side)
+        # the embedding kernels' overflow flag (a cloud larger than cheb_d_index_max) travels to pinned host memory at the
+        # end of every replay; the NEXT call reads it there without synchronising
+        emb = getattr(self.model, 'embedding', None)
+        cache = getattr(emb, '_cheb_cache', None)
+        self._flag_dev = cache.overflow if cache is not None else None
+        self._flag_host = torch.zeros(1, dtype=torch.int32).pin_memory() if self._flag_dev is not None else None
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.static_out = self.model(*self.static_in)
+            if self._flag_dev is not None:
+                self._flag_host.copy_(self._flag_dev, non_blocking=True)
 
     @torch.no_grad()
     def __call__(self, ref_points, src_points, ref_feats, src_feats):
@@ -1008,6 +1029,10 @@ class GraphedGeometricTransformer:
         if self.stale():
             torch.cuda.synchronize()
             self.recapture()
+        if self._flag_host is not None and int(self._flag_host[0]) != 0:
+            raise RuntimeError('an earlier replay of this graph saw a cloud larger than the embedding kernels were prepared '
+                               f'for (cheb_d_index_max = {self.model.embedding.cheb_d_index_max:g} index units): its outputs '
+                               'used clamped distances.  Set model.embedding.cheb_d_index_max (<= 210) and recapture()')
         self.graph.replay()
 
 

@@ -655,7 +655,8 @@ def to_half(t):
 
 def _rows2d(t, name, cols):
     """(…, cols) fp32 CUDA tensor whose leading dimensions flatten into equally strided rows -> (rows, row stride)."""
-    _check(t, name, torch.float32)
+    if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.float32 or t.dim() < 1:
+        raise RuntimeError(f'{name} must be a float32 CUDA tensor (ref-geotransformer_b200 has no CPU path)')
     if t.shape[-1] != cols or (cols > 1 and t.stride(-1) != 1):
         raise RuntimeError(f'{name}: last dimension must be dense and of size {cols}, got {tuple(t.shape)} strides {t.stride()}')
     rows = t.numel() // cols

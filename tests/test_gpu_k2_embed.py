@@ -308,16 +308,25 @@ def test_cheb_distance_sets(pkg, oracle, extent, want_set):
 
 
 def test_cheb_overflow_and_guard(pkg, oracle):
-    """(1) A cloud larger than cheb_d_index_max allows: the flag is raised and the first eager call of the shape raises
-    instead of returning clamped values.  (2) Weights scaled x50 and x2000: the measured error of the expansions stays
-    RELATIVE to the weights (a sampled table's would not), the module keeps K2c and still matches the oracle."""
+    """(1) A cloud larger than cheb_d_index_max allows: the kernel raises its overflow flag; the first eager call of the
+    shape reads it, widens the range to the kernels' maximum (210 index units) with a warning and repeats the launch --
+    the caller never sees clamped values; a cloud beyond even that raises.  (2) Weights scaled x50 and x2000: the
+    measured error of the expansions stays RELATIVE to the weights (a sampled table's would not), the module keeps K2c
+    and still matches the oracle."""
     cfg = dict(hidden_dim=128, sigma_d=0.2, sigma_a=15, angle_k=3, reduction_a='max')
     sd = oracle.init_state_dict(8, 8, 128, [], seed=9)
     pts = torch.rand(1, 100, 3, generator=torch.Generator().manual_seed(2)) * 6.0
+    exp = oracle.gse(pts, sd, 'embedding.', cfg['sigma_d'], cfg['sigma_a'], 3, 'max')
     m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
-    m.cheb_d_index_max = 13.0  # set 0 only: 2.6 m
+    assert m.cheb_d_index_max == 64.0
+    m.cheb_d_index_max = 13.0  # set 0 only: 2.6 m of a cloud that spans up to 10 m
+    with pytest.warns(UserWarning, match='cheb_d_index_max'), torch.no_grad():
+        e = m(pts.to(DEV), out_dtype=torch.float16)
+    assert m.cheb_d_index_max == 210.0 and rel(e.float(), exp) <= TOL_CHEB
+    m.check_overflow()  # the flag was cleared before the repeated launch
+    far = torch.rand(1, 90, 3, generator=torch.Generator().manual_seed(3)) * 60.0  # a new shape: its first call is checked
     with pytest.raises(RuntimeError, match='cheb_d_index_max'), torch.no_grad():
-        m(pts.to(DEV), out_dtype=torch.float16)
+        m(far.to(DEV), out_dtype=torch.float16)  # up to 520 index units: beyond every prebuilt set
     for scale in (50.0, 2000.0):
         big = {k: (v * scale if k.endswith(('proj_a.weight', 'proj_d.weight')) else v) for k, v in sd.items()}
         exp = oracle.gse(pts, big, 'embedding.', cfg['sigma_d'], cfg['sigma_a'], 3, 'max')

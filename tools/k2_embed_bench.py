@@ -48,6 +48,15 @@ def timed(fn, reps=10):
 if len(sys.argv) > 1 and sys.argv[1] == 'once':  # for ncu: three launches of one kernel
     kernel, n, C = sys.argv[2], int(sys.argv[3]), int(sys.argv[4])
     m, geom = setup(n, C, kernel)
+    if os.environ.get('K2_SCORES') == '1':  # K3r: scores straight from the geometry
+        qt = torch.randn(1, 4, n, C, device=dev)
+        sc = torch.empty(1, 4, n, n, device=dev)
+        with torch.no_grad():
+            for _ in range(3):
+                m.scores(geom, qt, out=sc)
+        torch.cuda.synchronize()
+        print('ok', float(sc[0, 0, :8].abs().max()))
+        sys.exit(0)
     out = torch.empty(1, n, n, C, dtype=torch.float16, device=dev)
     with torch.no_grad():
         for _ in range(3):
