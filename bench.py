@@ -678,9 +678,10 @@ def run_b200(args):
     d_set = max(host_d_set(pkg, host[0][0], cfg['sigma_d'])[0], host_d_set(pkg, host[0][1], cfg['sigma_d'])[0])
     kd = 16 * KD_TILES[d_set]
 
-    def k3r_flops(geom, coef, qt, *a, **kw):  # flops the kernel EXECUTES: expansions of k angle slots + distance, scores hi + lo
-        rows = geom.n
-        return geom.B * rows * geom.n * (2.0 * C * (k * 16 * coef.ka_tiles + kd) + 2.0 * C * 8 * 2)
+    def k3r_flops(geom, coef, qt, *a, **kw):  # flops the kernel EXECUTES: expansions of the k angle slots, scores hi + lo,
+        rows = geom.n                          # and the distance term (inside E, or split off in coefficient space)
+        dist = 2.0 * kd * 8 * 2 if kw.get('u') is not None else 2.0 * C * kd
+        return geom.B * rows * geom.n * (2.0 * C * (k * 16 * coef.ka_tiles) + dist + 2.0 * C * 8 * 2)
 
     def embed_bytes(geom, out_dtype, row_begin=0, row_count=None, out=None, qt=None):
         rows = geom.n - row_begin if row_count is None else row_count
@@ -949,8 +950,9 @@ def run_b200(args):
         dom = 'rpe_scores_cheb (K3r)'
         if dom in per_kernel:
             roofline = roof_tensor('gse_embed_cheb_kernel<SCORES> (geotx_rpe_scores_cheb, K3r)', per_kernel[dom], step_ms, mma_peak,
-                                   f'executed: per (i,j) pair 2 C (16 k ka + {kd}) for the expansions of the {k} angle slots and the '
-                                   f'distance (distance set {d_set}: {kd} coefficients) + 2 C 8 2 for the folded-query scores (hi + lo)')
+                                   f'executed: per (i,j) pair 2 C 16 k ka for the expansions of the {k} angle slots + 2 C 8 2 for the '
+                                   f'folded-query scores (hi + lo) + the distance term (distance set {d_set}: {kd} coefficients): '
+                                   f'2 {kd} 8 2 in coefficient space (distance split) or 2 C {kd} inside E')
             dtype = 'f16'
         elif 'rpe_scores (K3a)' in per_kernel:
             roofline = roof_hbm('rpe_scores_tc_kernel (geotx_rpe_scores, K3a)', per_kernel['rpe_scores (K3a)'], step_ms,

@@ -334,7 +334,10 @@ int geotx_patch_scores(const float* ref_feats, int64_t n_ref, const float* src_f
  *   geotx_gse_build_cheb   once per weight set: G in fp64 (Gauss-Chebyshev quadrature of the module's own weights and
  *                          div_term), rounded to half, in the kernel's register-image layout (geotx_gse_cheb_bytes bytes);
  *                          stats f32 [7][4] (device; set 0 = angle, 1..6 = distance sets): {largest |expansion - f| found
- *                          at 256 check points per channel, largest |f|, largest |G|, 0} -- the caller's accuracy guard
+ *                          at 256 check points per channel, largest |f|, largest |G|, 0} -- the caller's accuracy guard;
+ *                          plain (optional, else NULL): f32 [geotx_gse_cheb_plain_rows(ka_tiles)][C], the unrounded G of
+ *                          the angle set (16 ka_tiles rows) and of the six distance sets (16, 32, 48, 64, 96, 128 rows),
+ *                          row-major, for host-side folds (see geotx_rpe_scores_cheb: u)
  *   geotx_gse_embed_cheb   E[b,i,j,:] (f16 or bf16) for a slab of query rows, any k <= GEOTX_MAX_ANGLE_K, 'max' or 'mean'.
  *                          The basis values are generated per pair in registers (three-term recurrence, fp32), stored as
  *                          halves in shared memory and contracted with mma.sync.m16n8k16 (fp32 accumulation); the max
@@ -346,8 +349,10 @@ int geotx_patch_scores(const float* ref_feats, int64_t n_ref, const float* src_f
 int geotx_gse_cheb_ka_tiles(float angle_index_max);
 float geotx_gse_cheb_d_range(int d_set);
 int64_t geotx_gse_cheb_bytes(int C, int ka_tiles);
+int64_t geotx_gse_cheb_plain_rows(int ka_tiles);
 int geotx_gse_build_cheb(const float* div_term, const float* w_d, const float* b_d, const float* w_a, const float* b_a,
-                         int C, float angle_index_max, int ka_tiles, void* coef, float* stats, void* stream);
+                         int C, float angle_index_max, int ka_tiles, void* coef, float* stats, float* plain,
+                         void* stream);
 int geotx_gse_embed_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count, const void* coef,
                          int C, float angle_index_max, int ka_tiles, int max_d_set, float sigma_d, float factor_a,
                          int reduce_mean, int out_dtype, void* out, int32_t* overflow, void* stream);
@@ -360,11 +365,19 @@ int geotx_gse_embed_cheb(const void* geometry, int B, int n, int k, int row_begi
  * geotx_rpe_scores), adds the 8 channel blocks' partial scores in shared memory and writes 512-byte rows of scores_p.
  * One launch per 'self' block and cloud replaces one embedding pass (n^2 C 2 B written) plus one HBM read of E per block.
  *   qt f32 addressed as in geotx_rpe_scores (16-byte aligned, strides multiples of 4); H <= 8; scores_p f32 [B,H,n,n]
- *   (only the slab's rows are written); coef / angle_index_max / ka_tiles / max_d_set / overflow as in geotx_gse_embed_cheb. */
+ *   (only the slab's rows are written); coef / angle_index_max / ka_tiles / max_d_set / overflow as in geotx_gse_embed_cheb.
+ *   u (optional, else NULL): the DISTANCE SPLIT.  The distance term of E is linear in its Chebyshev basis, so its share
+ *   of the scores is sum_m u[b,h,i,m] T_m(d_ij) with u[b,h,i,:] = G_d qt[b,h,i,:] -- a K_d-term product per (h,i,j)
+ *   instead of a C-term one, and one third fewer MMAs in the kernel (the embedding contraction then covers the angle
+ *   slots only).  u f32, element (b,h,i,m) at u[b*u_stride_b + h*u_stride_h + i*u_stride_n + m], 80 values per (b,h,i):
+ *   the 32 coefficients of distance set 1 (G rows of `plain`), then the 48 of set 2; 8-byte aligned, even strides.  The
+ *   caller obtains u from the same projection that yields qt (G_d folded into the weights).  Used by the fast instances
+ *   (k = 3, 'max', clouds up to 64 index units); other shapes ignore it (distance term inside E as without u). */
 int geotx_rpe_scores_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count, const void* coef,
                           int C, float angle_index_max, int ka_tiles, int max_d_set, float sigma_d, float factor_a,
                           int reduce_mean, const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n,
-                          int H, float* scores_p, int32_t* overflow, void* stream);
+                          int H, const float* u, int64_t u_stride_b, int64_t u_stride_h, int64_t u_stride_n,
+                          float* scores_p, int32_t* overflow, void* stream);
 
 /* K2t (superseded by K2c, kept as embed_kernel='table'): the embedding by tabulation.  proj_x(sinus(x)) + bias is, per
  * channel, a function of one scalar; geotx_gse_build_tables samples the angle term every h_a index units (row r at

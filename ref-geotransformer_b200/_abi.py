@@ -52,10 +52,11 @@ SIGNATURES = {
     'geotx_gse_cheb_ka_tiles': (_i, [_f]),
     'geotx_gse_cheb_d_range': (_f, [_i]),
     'geotx_gse_cheb_bytes': (_i64, [_i, _i]),
-    'geotx_gse_build_cheb': (_i, [_p, _p, _p, _p, _p, _i, _f, _i, _p, _p, _p]),
+    'geotx_gse_cheb_plain_rows': (_i64, [_i]),
+    'geotx_gse_build_cheb': (_i, [_p, _p, _p, _p, _p, _i, _f, _i, _p, _p, _p, _p]),
     'geotx_gse_embed_cheb': (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _f, _i, _i, _f, _f, _i, _i, _p, _p, _p]),
     'geotx_rpe_scores_cheb': (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _f, _i, _i, _f, _f, _i, _p, _i64, _i64, _i64, _i,
-                                    _p, _p, _p]),
+                                    _p, _i64, _i64, _i64, _p, _p, _p]),
     'geotx_f32_to_f16': (_i, [_p, _p, _i64, _p]),
     'geotx_linear_f16': (_i, [_p, _i64, _i64, _i, _p, _p, _i, _i, _p, _i64, _p]),
     'geotx_post_attention': (_i, [_p, _i64, _p, _i64, _i64, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _f, _p, _i64,

@@ -73,7 +73,7 @@ __host__ inline size_t cheb_set_offset(int C, int ka_tiles, int set /* 0 = angle
 __global__ void __launch_bounds__(CHEB_BUILD_NODES)
 cheb_build_kernel(const float* __restrict__ div_term, const float* __restrict__ w, const float* __restrict__ bias0,
                   const float* __restrict__ bias1, int C, float L, int K, __half* __restrict__ frag,
-                  unsigned int* __restrict__ stats) {
+                  unsigned int* __restrict__ stats, float* __restrict__ plain) {
     __shared__ double F[CHEB_BUILD_NODES];
     __shared__ double Gh[128];
     __shared__ float red[3][CHEB_BUILD_NODES / 32];
@@ -97,6 +97,7 @@ cheb_build_kernel(const float* __restrict__ div_term, const float* __restrict__ 
         for (int j = 0; j < M; ++j) acc += F[j] * cospi((double)q * (j + 0.5) / M);
         acc *= (q == 0 ? 1.0 : 2.0) / M;
         const __half h = __double2half(acc);
+        if (plain) plain[(size_t)q * C + c] = (float)acc;  // row-major [K][C] copy for host-side folds (distance split)
         Gh[q] = (double)__half2float(h);
         gmax = fabsf((float)acc);
         // fragment image: channel c = 32 cb + 8 qq + 2 t + e  <->  n-tile t, B column n = 2 qq + e;  row kk = q % 16 of
@@ -274,6 +275,10 @@ struct ChebArgs {
     const float* qt;
     long long qsb, qsh, qsn;
     int H, key_blocks;
+    // distance split (scores mode, optional): u[b,h,i, u_offset[set] + m] = sum_c qt[b,h,i,c] G_d^{set}[m,c]
+    const float* u;
+    long long usb, ush, usn;
+    int u_offset[CHEB_NUM_D_SETS];
 };
 
 // saturating hi / lo split of two floats into halves (the folded query enters the score contraction as hi + lo, like
@@ -304,9 +309,10 @@ __device__ __forceinline__ void cheb_split(float x, float y, uint32_t& hi, uint3
 //               the tensor pipe never waits for a produce phase
 // Hand-over through named barriers (1, 2: tile buffer b is full; 3, 4: buffer b has been consumed), bar.arrive on the
 // signalling side, bar.sync on the waiting side.
-template <int C, int KA, int KD, bool SCORES, int SL>
+template <int C, int KA, int KD, bool SCORES, int SL, bool SPLIT = false>
 __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned char* smem) {
     constexpr bool FAST = KD > 0 && SL > 0;
+    static_assert(!SPLIT || (SCORES && FAST), "the distance split exists in the fast scores instances only");
     constexpr int NCB = C / 32;                          // 32-channel blocks
     constexpr int MT_PER_WARP = CHEB_MT * NCB / CHEB_CONSUMER_WARPS;  // 8 (C = 256) or 4 (C = 128)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -323,6 +329,10 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     const int partial_floats = NCB * hp * CHEB_TILE;
     const uint32_t qimg = a_base + 2 * buf_bytes + 2 * partial_floats * 4;
     constexpr int QIMG_BYTES = NCB * 32 * 32;
+    // SPLIT: uimg[2][KD][32 lanes][4 words] behind it: the row's distance-score coefficients u[h][m] (see ChebArgs) as mma B
+    // fragments (k = coefficient, n = head), hi | lo halves
+    const uint32_t uimg = qimg + 2 * QIMG_BYTES;
+    constexpr int UIMG_BYTES = (KD > 0 ? KD : 1) * 32 * 16;
     const long long tiles = p.tiles;
     const long long per_b = (long long)p.row_count * p.n;
 
@@ -353,7 +363,8 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     };
 
     if (SCORES) {  // fragment lanes of heads >= H read zeros
-        for (int e = tid; e < 2 * QIMG_BYTES / 16; e += CHEB_THREADS) sts_v4(qimg + e * 16, make_uint4(0u, 0u, 0u, 0u));
+        const int bytes = 2 * QIMG_BYTES + (SPLIT ? 2 * UIMG_BYTES : 0);
+        for (int e = tid; e < bytes / 16; e += CHEB_THREADS) sts_v4(qimg + e * 16, make_uint4(0u, 0u, 0u, 0u));
     }
     __syncthreads();
 
@@ -422,6 +433,22 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                     sts_v4(dst, hi);
                     sts_v4(dst + 16, lo);
                 }
+                if (SPLIT) {
+                    // u[h][m] = sum_c qt[h][c] G_d[m][c] (it arrives with the query: the caller's projection produces it)
+                    // turns the distance term's share of the scores into a K_d-term product with the basis values that
+                    // are in the A tile anyway.  Item = (head, k-tile, q): B rows 2q, 2q+1 | 2q+8, 2q+9 of the k-tile.
+                    constexpr int KD4 = KD > 0 ? KD * 4 : 1;
+                    if (ptid < p.H * KD4) {
+                        const int h = ptid / KD4, rem = ptid - h * KD4, kt = rem >> 2, qq = rem & 3;
+                        const float* src = p.u + b * p.usb + (long long)h * p.ush + (long long)i * p.usn + p.u_offset[d_set] +
+                                           16 * kt + 2 * qq;
+                        const float2 lo2 = __ldg(reinterpret_cast<const float2*>(src)), hi2 = __ldg(reinterpret_cast<const float2*>(src + 8));
+                        uint4 w;  // hi(rows 2q..) | hi(rows 2q+8..) | lo | lo
+                        cheb_split(lo2.x, lo2.y, w.x, w.z);
+                        cheb_split(hi2.x, hi2.y, w.y, w.w);
+                        sts_v4(uimg + buf * UIMG_BYTES + (kt * 32 + h * 4 + qq) * 16, w);
+                    }
+                }
             }
         };
         // the channel blocks' partial scores of a consumed tile -> scores_p[b, h, i, j0 .. j0 + CHEB_TILE - 1]
@@ -477,10 +504,12 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
             for (int kt = 0; kt < KA; ++kt)
 #pragma unroll
                 for (int t = 0; t < 4; ++t) b_a[kt][t] = __ldg(g_a + (kt * NCB * 4 + t) * 32);
+            if (!SPLIT) {
 #pragma unroll
-            for (int kt = 0; kt < KD; ++kt)
+                for (int kt = 0; kt < KD; ++kt)
 #pragma unroll
-                for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(g_d + (kt * NCB * 4 + t) * 32);
+                    for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(g_d + (kt * NCB * 4 + t) * 32);
+            }
         }
         // ldmatrix: lane l addresses row (l & 15) of the m-tile, columns 8 (l >> 4) ..; mma: g = lane / 4 is the fragment
         // row, q = lane % 4 the column pair
@@ -525,20 +554,22 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                             bh[t][1] = sl == 0 ? cur[t][1] : hmax2_u(bh[t][1], cur[t][1]);
                         }
                     }
+                    if (!SPLIT) {
 #pragma unroll
-                    for (int kt = 0; kt < KD; ++kt) {
-                        ldsm4(a, addr + (SL * KA + kt) * 32);
+                        for (int kt = 0; kt < KD; ++kt) {
+                            ldsm4(a, addr + (SL * KA + kt) * 32);
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) {
+                                if (kt == 0) mma_h_new(accd[t], a, b_d[kt][t]);
+                                else mma_h_acc(accd[t], a, b_d[kt][t]);
+                            }
+                        }
 #pragma unroll
                         for (int t = 0; t < 4; ++t) {
-                            if (kt == 0) mma_h_new(accd[t], a, b_d[kt][t]);
-                            else mma_h_acc(accd[t], a, b_d[kt][t]);
+                            bh[t][0] = hadd2_u(bh[t][0], accd[t][0]);
+                            bh[t][1] = hadd2_u(bh[t][1], accd[t][1]);
                         }
-                    }
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        bh[t][0] = hadd2_u(bh[t][0], accd[t][0]);
-                        bh[t][1] = hadd2_u(bh[t][1], accd[t][1]);
-                    }
+                    }  // SPLIT: bh is the angle term alone; the distance term joins the SCORES below
                 } else {
                     // generic instance: fp32 accumulators, runtime loops, G read through L1
                     uint32_t a[4];
@@ -591,6 +622,20 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                     mma_new(sc1, e1, make_uint2(qh.z, qh.w));
                     mma_acc(sc, e0, make_uint2(ql.x, ql.y));
                     mma_acc(sc1, e1, make_uint2(ql.z, ql.w));
+                    if (SPLIT && mt == warp) {
+                        // the distance term's share of this m-tile's scores, once per m-tile (not per channel block):
+                        // sum_m u[h][m] T_m(d_ij), the basis values straight from the A tile, u as hi + lo halves
+#pragma unroll
+                        for (int kt = 0; kt < KD; ++kt) {
+                            uint32_t ad[4];
+                            uint4 ub;
+                            ldsm4(ad, addr + (SL * KA + kt) * 32);
+                            const uint32_t usrc = uimg + buf * UIMG_BYTES + (kt * 32 + lane) * 16;
+                            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ub.x), "=r"(ub.y), "=r"(ub.z), "=r"(ub.w) : "r"(usrc));
+                            mma_acc(sc, ad, make_uint2(ub.x, ub.y));
+                            mma_acc(sc1, ad, make_uint2(ub.z, ub.w));
+                        }
+                    }
                     if (2 * q < hp) {  // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
                         float* dst = partial + (buf * NCB + cb) * hp * CHEB_TILE + (2 * q) * CHEB_TILE + mt * 16 + g;
                         dst[0] = sc[0] + sc1[0];
@@ -631,7 +676,9 @@ __global__ void __launch_bounds__(CHEB_THREADS, CHEB_MIN_CTAS) gse_embed_cheb_ke
     // fast instances: 3 angle slots (k = 3, 'max'), distance sets 1 (also serving set 0: its 32 coefficients cover the
     // shorter range too) and 2; everything else runs the generic instance
     const bool half_out = SCORES || !p.out_bf16;  // the fast instances accumulate in half
-    if (half_out && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3>(p, 1, cheb_smem);
+    if (SCORES && p.u != nullptr && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3, SCORES>(p, 1, cheb_smem);
+    else if (SCORES && p.u != nullptr && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3, SCORES>(p, 2, cheb_smem);
+    else if (half_out && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3>(p, 1, cheb_smem);
     else if (half_out && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3>(p, 2, cheb_smem);
     else cheb_run<C, KA, 0, SCORES, 0>(p, d_set, cheb_smem);
 }
@@ -658,9 +705,16 @@ extern "C" int64_t geotx_gse_cheb_bytes(int C, int ka_tiles) {
     return (int64_t)cheb_set_offset(C, ka_tiles, 1 + CHEB_NUM_D_SETS) * 2;
 }
 
+extern "C" int64_t geotx_gse_cheb_plain_rows(int ka_tiles) {
+    if (ka_tiles != 1 && ka_tiles != 2) return 0;
+    int64_t rows = 16 * ka_tiles;
+    for (int s = 0; s < CHEB_NUM_D_SETS; ++s) rows += 16 * cheb_kd_tiles(s);
+    return rows;
+}
+
 extern "C" int geotx_gse_build_cheb(const float* div_term, const float* w_d, const float* b_d, const float* w_a,
                                     const float* b_a, int C, float angle_index_max, int ka_tiles, void* coef,
-                                    float* stats, void* stream) {
+                                    float* stats, float* plain, void* stream) {
     GEOTX_REQUIRE(div_term && w_d && b_d && w_a && b_a && coef && stats, "geotx_gse_build_cheb: null pointer");
     GEOTX_REQUIRE(cheb_shape_ok(C, ka_tiles), "geotx_gse_build_cheb: C must be 128 or 256, ka_tiles 1 or 2");
     GEOTX_REQUIRE(angle_index_max > 0.f && angle_index_max <= cheb_range(ka_tiles - 1),
@@ -672,11 +726,15 @@ extern "C" int geotx_gse_build_cheb(const float* div_term, const float* w_d, con
     __half* base = (__half*)coef;
     // the angle term carries no bias: max over the slots commutes with adding b_a, which rides with b_d in G_d[0]
     cheb_build_kernel<<<C, CHEB_BUILD_NODES, 0, st>>>(div_term, w_a, nullptr, nullptr, C, angle_index_max, 16 * ka_tiles,
-                                                     base, (unsigned int*)stats);
-    for (int s = 0; s < CHEB_NUM_D_SETS; ++s)
+                                                     base, (unsigned int*)stats, plain);
+    size_t plain_row = 16 * ka_tiles;
+    for (int s = 0; s < CHEB_NUM_D_SETS; ++s) {
         cheb_build_kernel<<<C, CHEB_BUILD_NODES, 0, st>>>(div_term, w_d, b_d, b_a, C, cheb_range(s), 16 * cheb_kd_tiles(s),
                                                          base + cheb_set_offset(C, ka_tiles, 1 + s),
-                                                         (unsigned int*)stats + CHEB_STATS_PER_SET * (1 + s));
+                                                         (unsigned int*)stats + CHEB_STATS_PER_SET * (1 + s),
+                                                         plain ? plain + plain_row * C : nullptr);
+        plain_row += 16 * cheb_kd_tiles(s);
+    }
     return launch_status("geotx_gse_build_cheb");
 }
 
@@ -684,7 +742,8 @@ extern "C" int geotx_gse_build_cheb(const float* div_term, const float* w_d, con
 static int cheb_launch(const char* what, const void* geometry, int B, int n, int k, int row_begin, int row_count,
                        const void* coef, int C, float angle_index_max, int ka_tiles, int max_d_set, float sigma_d,
                        float factor_a, int reduce_mean, int out_dtype, void* out, const float* qt, int64_t qsb,
-                       int64_t qsh, int64_t qsn, int H, int32_t* overflow, void* stream) {
+                       int64_t qsh, int64_t qsn, int H, const float* u, int64_t usb, int64_t ush, int64_t usn,
+                       int32_t* overflow, void* stream) {
     const bool scores = qt != nullptr;
     ChebArgs p;
     p.pts4 = (const float4*)geometry;
@@ -712,12 +771,18 @@ static int cheb_launch(const char* what, const void* geometry, int B, int n, int
     p.qsh = qsh;
     p.qsn = qsn;
     p.H = H;
+    p.u = u;
+    p.usb = usb;
+    p.ush = ush;
+    p.usn = usn;
+    for (int s = 0; s < CHEB_NUM_D_SETS; ++s) p.u_offset[s] = s == 1 ? 0 : s == 2 ? 16 * cheb_kd_tiles(1) : 0;
     p.key_blocks = (n + CHEB_TILE - 1) / CHEB_TILE;
     p.tiles = scores ? (long long)B * row_count * p.key_blocks : (p.pairs_total + CHEB_TILE - 1) / CHEB_TILE;
     GEOTX_REQUIRE(p.tiles < 2147483647LL, "%s: too many tiles", what);
     const int ktot_max = p.slots * 16 * ka_tiles + 16 * cheb_kd_tiles(max_d_set);
     size_t smem = (size_t)2 * CHEB_TILE * (ktot_max * 2 + 16);
-    if (scores) smem += (size_t)2 * (C / 32) * (H <= 4 ? 4 : 8) * CHEB_TILE * sizeof(float) + (size_t)2 * (C / 32) * 32 * 32;
+    if (scores) smem += (size_t)2 * (C / 32) * (H <= 4 ? 4 : 8) * CHEB_TILE * sizeof(float) + (size_t)2 * (C / 32) * 32 * 32 +
+                        (u ? (size_t)2 * 3 * 32 * 16 : 0);
     GEOTX_REQUIRE(smem <= 220 * 1024, "%s: %zu B of shared memory (k=%d, max_d_set=%d) do not fit", what, smem, k, max_d_set);
     int dev = 0, sms = 0;
     int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
@@ -757,13 +822,15 @@ extern "C" int geotx_gse_embed_cheb(const void* geometry, int B, int n, int k, i
     GEOTX_REQUIRE(max_d_set >= 0 && max_d_set < CHEB_NUM_D_SETS, "geotx_gse_embed_cheb: max_d_set outside [0,%d)", CHEB_NUM_D_SETS);
     GEOTX_REQUIRE(angle_index_max > 0.f && sigma_d > 0.f, "geotx_gse_embed_cheb: bad scales");
     return cheb_launch("geotx_gse_embed_cheb", geometry, B, n, k, row_begin, row_count, coef, C, angle_index_max, ka_tiles,
-                       max_d_set, sigma_d, factor_a, reduce_mean, out_dtype, out, nullptr, 0, 0, 0, 0, overflow, stream);
+                       max_d_set, sigma_d, factor_a, reduce_mean, out_dtype, out, nullptr, 0, 0, 0, 0, nullptr, 0, 0, 0, overflow,
+                       stream);
 }
 
 extern "C" int geotx_rpe_scores_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count,
                                      const void* coef, int C, float angle_index_max, int ka_tiles, int max_d_set,
                                      float sigma_d, float factor_a, int reduce_mean, const float* qt,
                                      int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n, int H,
+                                     const float* u, int64_t u_stride_b, int64_t u_stride_h, int64_t u_stride_n,
                                      float* scores_p, int32_t* overflow, void* stream) {
     GEOTX_REQUIRE(geometry && coef && qt && scores_p && overflow, "geotx_rpe_scores_cheb: null pointer");
     GEOTX_REQUIRE(B > 0 && n > 0 && k >= 1 && k <= GEOTX_MAX_ANGLE_K, "geotx_rpe_scores_cheb: bad sizes (B=%d n=%d k=%d)", B, n, k);
@@ -774,7 +841,9 @@ extern "C" int geotx_rpe_scores_cheb(const void* geometry, int B, int n, int k, 
     GEOTX_REQUIRE(H >= 1 && H <= 8, "geotx_rpe_scores_cheb: H=%d outside [1,8]", H);
     GEOTX_REQUIRE(((uintptr_t)qt & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0 && qt_stride_n % 4 == 0,
                   "geotx_rpe_scores_cheb: qt must be 16-byte aligned with strides that are multiples of 4 elements");
+    GEOTX_REQUIRE(!u || (((uintptr_t)u & 7) == 0 && u_stride_b % 2 == 0 && u_stride_h % 2 == 0 && u_stride_n % 2 == 0),
+                  "geotx_rpe_scores_cheb: u must be 8-byte aligned with even strides");
     return cheb_launch("geotx_rpe_scores_cheb", geometry, B, n, k, row_begin, row_count, coef, C, angle_index_max, ka_tiles,
                        max_d_set, sigma_d, factor_a, reduce_mean, GEOTX_F16, scores_p, qt, qt_stride_b, qt_stride_h,
-                       qt_stride_n, H, overflow, stream);
+                       qt_stride_n, H, u, u_stride_b, u_stride_h, u_stride_n, overflow, stream);
 }

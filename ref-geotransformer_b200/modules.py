@@ -313,7 +313,13 @@ class GeometricStructureEmbedding(nn.Module):
                                   self.proj_d.bias.detach(), self.proj_a.weight.detach(), self.proj_a.bias.detach(),
                                   self.sigma_d, self.factor_a, mean, out_dtype, row_begin, row_count, out)
 
-    def scores(self, geom, qt, row_begin=0, row_count=None, out=None):
+    def distance_split_rows(self):
+        """(80, C) Chebyshev coefficients of the distance term (sets 1 and 2) for folding into the query projection."""
+        if self._cheb() is None:
+            raise RuntimeError('the low-rank embedding kernel is not in use for these weights')
+        return self._cheb_cache.distance_split_rows()
+
+    def scores(self, geom, qt, row_begin=0, row_count=None, out=None, u=None):
         """K3r: scores_p[b,h,i,j] = qt[b,h,i,:] . E[b,i,j,:] (rpe_transformer.py:54-56 with proj_p folded into qt) without E
         ever being formed in memory; E enters the contraction rounded to half, exactly like a stored half E."""
         if not self._use_cheb(torch.float16, None):
@@ -321,7 +327,7 @@ class GeometricStructureEmbedding(nn.Module):
                                "'cheb', hidden_dim 128 / 256)")
         return self._cheb_call(geom, lambda: ops.rpe_scores_cheb(
             geom, self._cheb_cache, qt, self.sigma_d, self.factor_a, self.reduction_a == 'mean',
-            ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out))
+            ops.gse_cheb_max_d_set(self.cheb_d_index_max), row_begin, row_count, out, u=u))
 
     def _cheb_call(self, geom, launch):
         """Runs a K2c / K3r launch; on the first eager call of a shape the overflow flag is read (one synchronisation) and
@@ -421,25 +427,35 @@ class RPEMultiHeadAttention(_FusedAttentionBase):
         self.proj_p = nn.Linear(self.d_model, self.d_model)
         self.dropout = build_dropout_layer(dropout)
 
-    def fused_qkvp(self):
+    def fused_qkvp(self, gd=None):
         """One projection for the whole layer: rows [W_q; W_k; W_v; W_qp] with W_qp[h] = W_p[h]^T W_q[h], so that
         x -> (q | k | v | folded query of every head) is a single (C -> 3C + H*C) GEMM.  The fold is exact algebra
-        (formed in fp64, stored fp32); rebuilt whenever one of the source parameters changes."""
+        (formed in fp64, stored fp32); rebuilt whenever one of the source parameters changes.
+        gd (M, C): Chebyshev coefficients G_d of the embedding's distance term (ops.ChebCoefficients.distance_split_rows);
+        then H*M more rows W_u[h] = G_d W_qp[h] follow, so that the same GEMM also yields u = G_d qt, the distance term's
+        share of the scores in coefficient space (K3r's distance split)."""
         ps = (self.proj_q.weight, self.proj_q.bias, self.proj_k.weight, self.proj_k.bias, self.proj_v.weight,
-              self.proj_v.bias, self.proj_p.weight)
+              self.proj_v.bias, self.proj_p.weight) + ((gd,) if gd is not None else ())
         key = tuple((t.data_ptr(), t._version) for t in ps)
         if getattr(self, '_fused_key', None) != key:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError('a weight changed since the fused projection was built; run one forward outside CUDA '
+                                   'graph capture first')
             H, c, C = self.num_heads, self.d_model_per_head, self.d_model
             wp = self.proj_p.weight.detach().double().view(H, c, C)
             wq = self.proj_q.weight.detach().double().view(H, c, C)
             bq = self.proj_q.bias.detach().double().view(H, c)
             w_qp = torch.einsum('hcd,hci->hdi', wp, wq).reshape(H * C, C)
             b_qp = torch.einsum('hcd,hc->hd', wp, bq).reshape(H * C)
-            w = torch.cat([self.proj_q.weight.detach().double(), self.proj_k.weight.detach().double(),
-                           self.proj_v.weight.detach().double(), w_qp]).float().contiguous()
-            b = torch.cat([self.proj_q.bias.detach().double(), self.proj_k.bias.detach().double(),
-                           self.proj_v.bias.detach().double(), b_qp]).float().contiguous()
-            self._fused, self._fused_key = (w, b), key
+            ws = [self.proj_q.weight.detach().double(), self.proj_k.weight.detach().double(),
+                  self.proj_v.weight.detach().double(), w_qp]
+            bs = [self.proj_q.bias.detach().double(), self.proj_k.bias.detach().double(),
+                  self.proj_v.bias.detach().double(), b_qp]
+            if gd is not None:
+                g64 = gd.detach().double()                                           # (M, C)
+                ws.append(torch.einsum('mc,hci->hmi', g64, w_qp.view(H, C, C)).reshape(-1, C))
+                bs.append(torch.einsum('mc,hc->hm', g64, b_qp.view(H, C)).reshape(-1))
+            self._fused, self._fused_key = (torch.cat(ws).float().contiguous(), torch.cat(bs).float().contiguous()), key
         return self._fused
 
     def folded_query(self, q):
@@ -620,9 +636,9 @@ class StreamedEmbedding:
         self.regenerate_bytes = regenerate_bytes
         self._slab = None
 
-    def direct_scores(self, qt):
-        """qt (1,H,n,C) -> scores_p (1,H,n,n) straight from the geometry (K3r); E never exists."""
-        return self.embedding.scores(self.geom, qt)
+    def direct_scores(self, qt, u=None):
+        """qt (1,H,n,C) [, u (1,H,n,80)] -> scores_p (1,H,n,n) straight from the geometry (K3r); E never exists."""
+        return self.embedding.scores(self.geom, qt, u=u)
 
     def regenerated_scores(self, qt):
         """qt (1,H,n,C) -> scores_p (1,H,n,n); E exists one slab at a time."""
@@ -743,8 +759,13 @@ class RPEConditionalTransformer(nn.Module):
             att = layer.attention.attention
             H = att.num_heads
             if block == 'self':
-                w, b = att.fused_qkvp()
-                y = _linear(x, att, 'qkvp', w, b)  # (1, T, 3C + H*C): q | k | v | folded query per head
+                # K3r's distance split: the projection also yields u = G_d qt (80 coefficients per head and token)
+                gd = None
+                if H % 4 == 0 and all(isinstance(e, StreamedEmbedding) and e.direct for e in embs):
+                    gd = embs[0].embedding.distance_split_rows()
+                w, b = att.fused_qkvp(gd)
+                y = _linear(x, att, 'qkvp', w, b)  # (1, T, 3C + H*C [+ H*80]): q | k | v | folded query per head [| u]
+                M = 0 if gd is None else gd.shape[0]
                 hidden = x.new_empty(1, T, C)
                 cur = side = None
                 streamed = any(isinstance(e, StreamedEmbedding) for e in embs)
@@ -756,9 +777,10 @@ class RPEConditionalTransformer(nn.Module):
                     streamed = False
                 for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
                     emb = embs[which]
-                    qt = y[:, lo:hi, 3 * C:].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
+                    qt = y[:, lo:hi, 3 * C:3 * C + H * C].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
                     if isinstance(emb, StreamedEmbedding) and emb.direct:
-                        scores_p = emb.direct_scores(qt)  # K3r: E of this cloud is never formed in memory
+                        u = y[:, lo:hi, 3 * C + H * C:].unflatten(2, (H, M)).permute(0, 2, 1, 3) if M else None
+                        scores_p = emb.direct_scores(qt, u)  # K3r: E of this cloud is never formed in memory
                     elif isinstance(emb, StreamedEmbedding) and emb.regenerate_bytes > 0:
                         scores_p = emb.regenerated_scores(qt)  # E of this cloud is never stored
                     elif isinstance(emb, StreamedEmbedding):

@@ -544,11 +544,17 @@ def gse_embed_table(geom, tables, sigma_d, factor_a, row_begin=0, row_count=None
 
 class ChebCoefficients:
     """Chebyshev coefficients of proj_a(sinus(x)) and proj_d(sinus(x)) + b_d + b_a for geotx_gse_embed_cheb (K2c)."""
-    __slots__ = ('buf', 'C', 'angle_index_max', 'ka_tiles', 'stats', 'overflow', '_report')
+    __slots__ = ('buf', 'C', 'angle_index_max', 'ka_tiles', 'stats', 'overflow', 'plain', '_report')
+    SPLIT_COEFFICIENTS = 80  # distance sets 1 (32 coefficients) and 2 (48): what the distance split of K3r consumes
 
-    def __init__(self, buf, C, angle_index_max, ka_tiles, stats, overflow):
+    def __init__(self, buf, C, angle_index_max, ka_tiles, stats, overflow, plain):
         self.buf, self.C, self.angle_index_max, self.ka_tiles = buf, C, angle_index_max, ka_tiles
-        self.stats, self.overflow, self._report = stats, overflow, None
+        self.stats, self.overflow, self.plain, self._report = stats, overflow, plain, None
+
+    def distance_split_rows(self):
+        """(80, C) fp32: the unrounded Chebyshev coefficients G_d of distance sets 1 and 2, row m = coefficient m."""
+        r0 = 16 * self.ka_tiles + 16  # behind the angle set and distance set 0
+        return self.plain[r0:r0 + self.SPLIT_COEFFICIENTS]
 
     def report(self):
         """One host read per weight set: [{'range', 'coefficients', 'max_error', 'max_abs_f', 'max_abs_g'}, ...] for the
@@ -598,9 +604,10 @@ def gse_build_cheb(div_term, w_d, b_d, w_a, b_a, factor_a):
     buf = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     stats = torch.empty(28, dtype=torch.float32, device=dev)
     overflow = torch.zeros(1, dtype=torch.int32, device=dev)
+    plain = torch.empty(int(lib.geotx_gse_cheb_plain_rows(ka)), C, dtype=torch.float32, device=dev)
     _abi.call('geotx_gse_build_cheb', _p(div_term), _p(w_d.contiguous()), _p(b_d.contiguous()), _p(w_a.contiguous()),
-              _p(b_a.contiguous()), C, angle_index_max, ka, _p(buf), _p(stats), _stream())
-    return ChebCoefficients(buf, C, angle_index_max, ka, stats, overflow)
+              _p(b_a.contiguous()), C, angle_index_max, ka, _p(buf), _p(stats), _p(plain), _stream())
+    return ChebCoefficients(buf, C, angle_index_max, ka, stats, overflow, plain)
 
 
 def gse_embed_cheb(geom, coef, sigma_d, factor_a, reduce_mean, out_dtype, max_d_set=5, row_begin=0, row_count=None,
@@ -621,10 +628,12 @@ def gse_embed_cheb(geom, coef, sigma_d, factor_a, reduce_mean, out_dtype, max_d_
 
 
 def rpe_scores_cheb(geom, coef, qt, sigma_d, factor_a, reduce_mean=False, max_d_set=5, row_begin=0, row_count=None,
-                    out=None):
+                    out=None, u=None):
     """K3r: rpe_transformer.py:54-56 (proj_p folded into qt, see rpe_scores) fused with the embedding
     (geotransformer.py:57-72): scores_p (B,H,n,n) fp32 straight from the geometry; E is rebuilt tile by tile in
-    registers and never stored.  qt: logical (B,H,n,C) fp32 with a dense last dimension (any strides over b, h, i)."""
+    registers and never stored.  qt: logical (B,H,n,C) fp32 with a dense last dimension (any strides over b, h, i).
+    u (optional): logical (B,H,n,80) fp32, u[b,h,i,:] = coef.distance_split_rows() @ qt[b,h,i,:] (the distance split: the
+    distance term's share of the scores becomes a 32 / 48-term product instead of a C-term one)."""
     row_begin, row_count = _slab(geom, row_begin, row_count)
     if not isinstance(qt, torch.Tensor) or not qt.is_cuda or qt.dtype != torch.float32 or qt.dim() != 4:
         raise RuntimeError('qt must be a 4-d float32 CUDA tensor (B,H,n,C)')
@@ -638,9 +647,17 @@ def rpe_scores_cheb(geom, coef, qt, sigma_d, factor_a, reduce_mean=False, max_d_
         _check(out, 'out', torch.float32, 4)
         if tuple(out.shape) != (B, H, n, n):
             raise RuntimeError(f'out must be {(B, H, n, n)}, got {tuple(out.shape)}')
+    us = (0, 0, 0)
+    if u is not None:
+        if not isinstance(u, torch.Tensor) or not u.is_cuda or u.dtype != torch.float32 or \
+                tuple(u.shape) != (B, H, n, coef.SPLIT_COEFFICIENTS) or u.stride(3) != 1:
+            raise RuntimeError(f'u must be a float32 CUDA tensor of logical shape {(B, H, n, coef.SPLIT_COEFFICIENTS)} with a '
+                               f'dense last dimension')
+        us = (int(u.stride(0)), int(u.stride(1)), int(u.stride(2)))
     _abi.call('geotx_rpe_scores_cheb', _p(geom.buf), B, n, geom.k, row_begin, row_count, _p(coef.buf), C,
               coef.angle_index_max, coef.ka_tiles, int(max_d_set), float(sigma_d), float(factor_a), int(bool(reduce_mean)),
-              _p(qt), int(qt.stride(0)), int(qt.stride(1)), int(qt.stride(2)), H, _p(out), _p(coef.overflow), _stream())
+              _p(qt), int(qt.stride(0)), int(qt.stride(1)), int(qt.stride(2)), H, _p(u), us[0], us[1], us[2], _p(out),
+              _p(coef.overflow), _stream())
     return out
 
 

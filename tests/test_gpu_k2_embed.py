@@ -391,11 +391,24 @@ def test_cheb_scores_without_e(pkg, oracle, C, H, n, reduction, k):
         got = m.scores(geom, qt)
         part = torch.full_like(got, -7.0)
         m.scores(geom, qt, row_begin=30, row_count=20, out=part)
+        # the distance split: u = G_d qt in coefficient space replaces the distance term's share of the contraction
+        # (fast instances: k = 3, 'max'; every other shape ignores u and must reproduce `got` bit for bit)
+        gd = m.distance_split_rows()
+        assert tuple(gd.shape) == (80, C)
+        u_wide = torch.zeros(2, n, H * 80 + 8, device=DEV)
+        u_wide[:, :, 8:] = torch.einsum('bhnc,mc->bnhm', qt.double(), gd.double()).float().flatten(2)
+        u = u_wide[:, :, 8:].unflatten(2, (H, 80)).permute(0, 2, 1, 3)  # (B,H,n,80) view of a wider buffer
+        split = m.scores(geom, qt, u=u)
     m.check_overflow()
+    if k == 3 and reduction == 'max':
+        print(f'    distance split vs unsplit {rel(split, got):.3e}, vs oracle (below)')
+        assert rel(split, got) <= 1e-3
+    else:
+        assert torch.equal(split, got)
     exp = torch.einsum('bhic,bijc->bhij', qt.double().cpu(),
                        oracle.gse(pts, sd, 'embedding.', 0.3, 10, k, reduction).double()).float()
     print(f'C={C} H={H} n={n}: K3r vs K2c+K3a {rel(got, want):.3e}, vs oracle {rel(got, exp):.3e}')
     assert rel(got, want) <= 1e-5
-    assert rel(got, exp) <= TOL_CHEB
+    assert rel(got, exp) <= TOL_CHEB and rel(split, exp) <= TOL_CHEB
     assert torch.equal(part[:, :, 30:50], got[:, :, 30:50])
     assert float((part[:, :, :30] + 7.0).abs().max()) == 0.0 and float((part[:, :, 50:] + 7.0).abs().max()) == 0.0

@@ -51,9 +51,10 @@ if len(sys.argv) > 1 and sys.argv[1] == 'once':  # for ncu: three launches of on
     if os.environ.get('K2_SCORES') == '1':  # K3r: scores straight from the geometry
         qt = torch.randn(1, 4, n, C, device=dev)
         sc = torch.empty(1, 4, n, n, device=dev)
+        uu = torch.randn(1, 4, n, 80, device=dev) if os.environ.get('K2_SPLIT', '1') == '1' else None
         with torch.no_grad():
             for _ in range(3):
-                m.scores(geom, qt, out=sc)
+                m.scores(geom, qt, out=sc, u=uu)
         torch.cuda.synchronize()
         print('ok', float(sc[0, 0, :8].abs().max()))
         sys.exit(0)
@@ -95,6 +96,12 @@ for n, C in SIZES:
             kd = 16 * (1, 2, 3, 4, 6, 8)[pkg.ops.gse_cheb_max_d_set(float(torch.cdist(geom_pts(geom), geom_pts(geom)).max()) / m.sigma_d)] \
                 if n <= 4096 else 48
             flops = n * n * (2.0 * C * (3 * 16 + kd) + 2.0 * C * 8 * 2)
+            uu = torch.randn(1, H, n, 80, device=dev)
+            with torch.no_grad():
+                ms_u = timed(lambda: m.scores(geom, qt, out=sc, u=uu))
+            fl_u = n * n * (2.0 * C * (3 * 16) + 2.0 * C * 8 * 2 + 2.0 * kd * 8 * 2)
+            row['cheb_scores_K3r_split'] = {'ms': ms_u, 'executed_tflops': fl_u / ms_u / 1e9,
+                                            'clk_per_pair_per_sm_at_1965MHz': ms_u * 1e-3 * 1.965e9 * 148 / (n * n)}
             row['cheb_scores_K3r'] = {'ms': ms_s, 'executed_tflops': flops / ms_s / 1e9, 'kd': kd,
                                       'hmma_per_pair': ((3 + kd // 16) * 4 + 4) * (C // 32) / 16.0,
                                       'clk_per_pair_per_sm_at_1965MHz': ms_s * 1e-3 * 1.965e9 * 148 / (n * n)}
