@@ -703,13 +703,19 @@ def run_b200(args):
     timers.wrap(pkg.ops, 'gse_knn', 'gse_knn (K1)', lambda points, kk: float(points.shape[0] * points.shape[1] ** 2 * 16))
     timers.wrap(pkg.ops, 'add_layernorm', 'add_layernorm (K4)', None)
 
+    def serial_ms(per_kernel):
+        """One forward's kernels back to back (the probe replays ONE graph instance alone): the denominator of every
+        share_of_step.  The timed region overlaps several instances, so ms_per_step is smaller than this sum."""
+        return sum(sum(d['ms_per_launch']) for d in per_kernel.values())
+
     def kernel_report(per_kernel, step_ms):
         rep = {}
+        whole = serial_ms(per_kernel)
         for name, d in sorted(per_kernel.items()):
             total = sum(d['ms_per_launch'])
             rep[name] = {'launches_per_step': d['launches_per_step'], 'ms_per_step': total,
                          'avg_launch_ms': total / max(d['launches_per_step'], 1),
-                         'share_of_step': total / step_ms if step_ms else None}
+                         'share_of_step': total / whole if whole else None}
         return rep
 
     def roof_tensor(name, d, step_ms, mma_peak, what):
@@ -747,9 +753,9 @@ def run_b200(args):
         try:
             setup()
             with torch.no_grad():
-                model(*resident[0])
+                out = [t.clone() for t in model(*resident[0])]  # compared with the default path on the SAME pair
                 fast = InFlight(pkg, model, resident[0], inflight)
-                ms, out = timed_value(torch, fast, resident, n_pairs, steps, max(3, 2 * inflight))
+                ms, _ = timed_value(torch, fast, resident, n_pairs, steps, max(3, 2 * inflight))
                 del fast
                 res = {'value': steps / (ms * 1e-3), 'unit': UNIT, 'ms_per_step': ms / steps, 'e_storage': model.last_e_mode}
                 if want_kernels:
@@ -768,6 +774,16 @@ def run_b200(args):
         for s in range(3):
             last = model(*resident[s % n_pairs])
         barrier()
+        if args.launch_list:  # the forward's launches, one by one, for `ncu --metrics gpu__time_duration.sum`
+            torch.cuda.synchronize()
+            torch.cuda.profiler.start()
+            for s in range(args.steps):
+                model(*resident[s % n_pairs])
+            torch.cuda.synchronize()
+            torch.cuda.profiler.stop()
+            print(json.dumps({'launch_list': args.workload, 'forwards': args.steps, 'e_storage': model.last_e_mode,
+                              'note': 'not a bench line: run under ncu --profile-from-start off'}))
+            return
         launches0 = pkg._abi.launch_count
         e_start, e_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e_start.record()
@@ -778,6 +794,7 @@ def run_b200(args):
         eager_ms = e_start.elapsed_time(e_stop)
         launches = pkg._abi.launch_count - launches0
         default_mode = model.last_e_mode
+        default_out = [t.clone() for t in model(*resident[0])]  # what the variants below are compared with
 
         # ---- per-kernel times inside the replayed graph of the forward ----
         per_kernel, kernel_timing = probe_kernels(pkg, torch, model, timers, resident, n_pairs, args.steps)
@@ -873,23 +890,23 @@ def run_b200(args):
             v, out = run_variant('stored_e', set_mode(e_mode='store'), reset, vsteps)
             if 'error' not in v:
                 raw = v.pop('_raw')
-                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, last))
+                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, default_out))
                 if 'gse_embed (K2c / K2 / K2t)' in raw:
                     v['embedding_write'] = roof_hbm('gse_embed_cheb_kernel (geotx_gse_embed_cheb, K2c)', raw['gse_embed (K2c / K2 / K2t)'],
-                                                    v['ms_per_step'], 'E written once: n*n*C*2 bytes per launch')
+                                                    serial_ms(raw), 'E written once: n*n*C*2 bytes per launch')
                 if 'rpe_scores (K3a)' in raw:
-                    v['scores_read'] = roof_hbm('rpe_scores_tc_kernel (geotx_rpe_scores, K3a)', raw['rpe_scores (K3a)'], v['ms_per_step'],
+                    v['scores_read'] = roof_hbm('rpe_scores_tc_kernel (geotx_rpe_scores, K3a)', raw['rpe_scores (K3a)'], serial_ms(raw),
                                                 'E read once (n*n*C*2) + scores written (n*n*H*4) per launch')
             variants['stored_e'] = v
             # (b) the full-rank tcgen05 embedding: north_star's "% of tensor-pipe peak" on the formulation it names
             v, out = run_variant('tensor_embedding', set_mode(e_mode='store', kernel='tensor'), reset, vsteps)
             if 'error' not in v:
                 raw = v.pop('_raw')
-                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, last))
+                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, default_out))
                 if 'gse_embed (K2c / K2 / K2t)' in raw:
                     d = dict(raw['gse_embed (K2c / K2 / K2t)'])
                     d['work_per_launch'] = [flops_gse(n if i % 2 == 0 else m, C, k) for i in range(d['launches_per_step'])]
-                    v['embedding_tensor_roof'] = roof_tensor('gse_embed_tc_kernel (geotx_gse_embed, K2, tcgen05)', d, v['ms_per_step'],
+                    v['embedding_tensor_roof'] = roof_tensor('gse_embed_tc_kernel (geotx_gse_embed, K2, tcgen05)', d, serial_ms(raw),
                                                              None, 'SURVEY.md 8d: 2 n^2 C^2 (1+k) per cloud')
                 v['pair_tflops_min'] = flops_pair(n, m, cfg) / 1e12
                 v['pair_tensor_frac'] = flops_pair(n, m, cfg) * v['value'] / 1e12 / peaks['tensor_sustained']
@@ -898,7 +915,7 @@ def run_b200(args):
             # (c) round 1's dense glue (cuBLASLt TF32 GEMMs + K4) under the default embedding / scores
             v, out = run_variant('library_gemm_glue', set_mode(dense='cublas'), reset, vsteps, want_kernels=False)
             if 'error' not in v:
-                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, last))
+                v['rel_diff_of_outputs_vs_default'] = max(float((x - y).norm() / y.norm()) for x, y in zip(out, default_out))
             variants['library_gemm_glue'] = v
 
         # ---- bounded sweep points in the same process (driver-visible): north_star's size and KITTI ----
@@ -947,21 +964,24 @@ def run_b200(args):
         value = world * args.steps / (ms * 1e-3)
         step_ms = ms / args.steps
         kernels = kernel_report(per_kernel, step_ms)
+        serial_step_ms = serial_ms(per_kernel)
         dom = 'rpe_scores_cheb (K3r)'
         if dom in per_kernel:
-            roofline = roof_tensor('gse_embed_cheb_kernel<SCORES> (geotx_rpe_scores_cheb, K3r)', per_kernel[dom], step_ms, mma_peak,
+            roofline = roof_tensor('gse_embed_cheb_kernel<SCORES> (geotx_rpe_scores_cheb, K3r)', per_kernel[dom], serial_ms(per_kernel), mma_peak,
                                    f'executed: per (i,j) pair 2 C 16 k ka for the expansions of the {k} angle slots + 2 C 8 2 for the '
                                    f'folded-query scores (hi + lo) + the distance term (distance set {d_set}: {kd} coefficients): '
                                    f'2 {kd} 8 2 in coefficient space (distance split) or 2 C {kd} inside E')
             dtype = 'f16'
         elif 'rpe_scores (K3a)' in per_kernel:
-            roofline = roof_hbm('rpe_scores_tc_kernel (geotx_rpe_scores, K3a)', per_kernel['rpe_scores (K3a)'], step_ms,
+            roofline = roof_hbm('rpe_scores_tc_kernel (geotx_rpe_scores, K3a)', per_kernel['rpe_scores (K3a)'], serial_ms(per_kernel),
                                 'E read once (n*n*C*2) + scores written (n*n*H*4) per launch')
             dtype = 'f16'
         else:
             roofline, dtype = None, 'f32'
         if roofline is not None:
-            roofline['timing'] = kernel_timing + '; share_of_step = timed launches per step / ms_per_step'
+            roofline['timing'] = kernel_timing + ('; share_of_step = this kernel\'s launches / all launches of one forward, one graph instance replayed alone '
+                                                     '(what an ncu launch list sees); the timed region overlaps several instances, so '
+                                                     'ms_per_step is smaller than the serial sum (serial_ms_per_step)')
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': max(args.warmup, 3), 'ms_per_step': step_ms, 'higher_is_better': True,
@@ -983,6 +1003,7 @@ def run_b200(args):
             'gpu_launches_per_step': launches / args.steps,
             'roofline': roofline,
             'kernels': kernels,
+            'serial_ms_per_step': serial_step_ms,
             'eager_ms_per_step': eager_ms / args.steps,
             'pair_tflops_executed': sum(sum(d['work_per_launch']) for nme, d in per_kernel.items()
                                         if nme.split(' ')[0] in ('rpe_scores_cheb', 'attention', 'post_attention', 'linear_f16')) / 1e12,
@@ -1016,6 +1037,9 @@ def main():
     ap.add_argument('--workload', default='3dmatch_1024', choices=sorted(WORKLOADS))
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-sweep', action='store_true')
+    ap.add_argument('--launch-list', action='store_true',
+                    help='ncu pass (B200_PROFILING.md launch list): warm up, then --steps eager forwards between '
+                         'cudaProfilerStart/Stop (ncu --profile-from-start off) and nothing else; prints no bench line')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

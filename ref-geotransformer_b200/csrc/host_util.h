@@ -14,6 +14,19 @@ inline int check_cuda(cudaError_t e, const char* what) {
     return GEOTX_E_CUDA;
 }
 inline int launch_status(const char* what) { return check_cuda(cudaGetLastError(), what); }
+
+// SM count of the current device (148 on B200), asked once per device: every persistent grid is sized from it.
+inline int sm_count() {
+    static int cached[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int sms = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) return 148;
+        cached[dev] = sms;
+    }
+    return cached[dev];
+}
 }  // namespace geotx
 
 #define GEOTX_REQUIRE(cond, ...)              \

@@ -251,17 +251,18 @@ extern "C" int geotx_grid_subsample(const float* points, const int64_t* host_len
     if (rc) return rc;
     const int nblocks = (int)((max_cells + GS_SCAN_BLOCK - 1) / GS_SCAN_BLOCK);
     int64_t start = 0;
+    const int sms = sm_count();
     for (int b = 0; b < batch; ++b) {
         const int64_t n = host_lengths[b];
         GEOTX_REQUIRE(n > 0 && n < 2147483647LL, "geotx_grid_subsample: batch element %d has %lld points (the reference "
                       "reads points[0] of every element, cloud.cpp:5)", b, (long long)n);
         const float* p = points + 3 * start;
         gs_bounds_kernel<<<1, 1024, 0, st>>>(p, (int)n, voxel_size, (long long)max_cells, w);
-        gs_clear_kernel<<<148 * 8, 256, 0, st>>>(w);
+        gs_clear_kernel<<<sms * 8, 256, 0, st>>>(w);
         gs_accumulate_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(p, (int)n, voxel_size, w);
-        gs_count_kernel<<<148 * 2, GS_SCAN_BLOCK, 0, st>>>(w);
+        gs_count_kernel<<<sms * 2, GS_SCAN_BLOCK, 0, st>>>(w);
         gs_scan_kernel<<<1, 1024, 0, st>>>(nblocks, w, (long long*)s_lengths + b);
-        gs_emit_kernel<<<148 * 2, GS_SCAN_BLOCK, 0, st>>>(w, s_points);
+        gs_emit_kernel<<<sms * 2, GS_SCAN_BLOCK, 0, st>>>(w, s_points);
         gs_advance_kernel<<<1, 1, 0, st>>>(w, (const long long*)s_lengths + b);
         start += n;
     }

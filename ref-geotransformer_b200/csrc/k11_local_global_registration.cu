@@ -536,7 +536,7 @@ extern "C" int geotx_local_global_registration(
                                                        global_scores, num_patches, K, w, ref_corr_points,
                                                        src_corr_points, corr_scores, count_out);
     const int tiles = (int)((cap + LGR_INL_THREADS - 1) / LGR_INL_THREADS);
-    const dim3 inl_grid(tiles < 148 ? tiles : 148, (num_patches + LGR_INL_HYPS - 1) / LGR_INL_HYPS);
+    const dim3 inl_grid(tiles < sm_count() ? tiles : sm_count(), (num_patches + LGR_INL_HYPS - 1) / LGR_INL_HYPS);
     const float d2_max = lgr_d2_max(acceptance_radius);
     lgr_inlier_kernel<<<inl_grid, LGR_INL_THREADS, 0, st>>>(ref_corr_points, src_corr_points, num_patches, d2_max, w);
     lgr_refine_kernel<<<LGR_REF_CTAS, LGR_REF_THREADS, 0, st>>>(ref_corr_points, src_corr_points, corr_scores,

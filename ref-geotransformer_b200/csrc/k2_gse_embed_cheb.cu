@@ -32,6 +32,7 @@
 #include <cuda_fp16.h>
 #include "geotx_common.cuh"
 #include "host_util.h"
+#include "sm100_ptx.cuh"
 
 namespace geotx {
 
@@ -180,12 +181,32 @@ __device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
 
 // named barriers between the producer and the consumer warps (all CHEB_THREADS threads take part: the signalling side
 // arrives, the waiting side syncs)
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+// Producer <-> consumer hand-over of a tile buffer.  Default: four mbarriers in shared memory (full[2]: 128 producer
+// threads arrive, each consumer warp waits on its own; empty[2]: lane 0 of each of the 8 consumer warps arrives, the
+// producers wait).  Nothing makes the consumer warps wait for EACH OTHER: with the named barriers of the first version
+// (bar.sync over all 384 threads; kept under CHEB_NAMED_BARRIERS for A/B timing) every tile restarted the CTA's eight
+// consumer warps in lockstep, and the tensor pipe idled through each ramp-down / ramp-up.
+constexpr int CHEB_BAR_BYTES = 64;
+constexpr int CHEB_PSTRIDE = CHEB_TILE + 8;  // floats between the heads of a channel block's partial scores
 __device__ __forceinline__ void cheb_bar_sync(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(CHEB_THREADS) : "memory"); }
 __device__ __forceinline__ void cheb_bar_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "n"(CHEB_THREADS) : "memory"); }
 
 // 16 * TILES Chebyshev values of t (T_0 = 1, T_1 = t, T_{m+1} = 2 t T_m - T_{m-1}) as halves, to smem at `addr`
 template <int TILES>
 __device__ __forceinline__ void cheb_store(uint32_t addr, float t) {
+    // (measured: the stride-2 form of the recurrence with one packed FFMA2 per half2 instead of two FFMAs is not
+    // faster: n = 4096 1.693 ms against 1.662 ms)
     const float t2 = t + t;
     float a = 1.f, b = t;  // T_m, T_{m+1}
 #pragma unroll
@@ -316,6 +337,8 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     constexpr int NCB = C / 32;                          // 32-channel blocks
     constexpr int MT_PER_WARP = CHEB_MT * NCB / CHEB_CONSUMER_WARPS;  // 8 (C = 256) or 4 (C = 128)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t bar_full = smem_u32(smem), bar_empty = bar_full + 16;  // + 8 * buf
+    smem += CHEB_BAR_BYTES;
     const int slots = FAST ? SL : p.slots;
     const int kd_tiles = FAST ? KD : cheb_kd_tiles(d_set);
     const int ktot = slots * 16 * KA + 16 * kd_tiles;  // halves per A row
@@ -326,7 +349,8 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     // scores) and qimg[2][NCB][32 lanes][8 words]: the tile row's folded query as mma B fragments, hi | lo halves
     const int hp = p.H <= 4 ? 4 : 8;
     float* const partial = reinterpret_cast<float*>(smem + 2 * buf_bytes);
-    const int partial_floats = NCB * hp * CHEB_TILE;
+    constexpr int NSLOT = NCB + (SPLIT ? 1 : 0);  // SPLIT: one more block of partial scores, the distance term's
+    const int partial_floats = NSLOT * hp * CHEB_PSTRIDE;  // head stride 136 floats: the stores of heads 2q | 2q + 2 fall into different banks
     const uint32_t qimg = a_base + 2 * buf_bytes + 2 * partial_floats * 4;
     constexpr int QIMG_BYTES = NCB * 32 * 32;
     // SPLIT: uimg[2][KD][32 lanes][4 words] behind it: the row's distance-score coefficients u[h][m] (see ChebArgs) as mma B
@@ -366,6 +390,13 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         const int bytes = 2 * QIMG_BYTES + (SPLIT ? 2 * UIMG_BYTES : 0);
         for (int e = tid; e < bytes / 16; e += CHEB_THREADS) sts_v4(qimg + e * 16, make_uint4(0u, 0u, 0u, 0u));
     }
+    if (tid == 0) {
+        for (int b = 0; b < 2; ++b) {
+            ptx::mbar_init(bar_full + 8 * b, CHEB_PRODUCER_WARPS * 32);
+            ptx::mbar_init(bar_empty + 8 * b, CHEB_CONSUMER_WARPS);
+        }
+        ptx::fence_barrier_init();
+    }
     __syncthreads();
 
     if (warp >= CHEB_CONSUMER_WARPS) {
@@ -383,6 +414,29 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
             const float4 pi = __ldg(p.pts4 + b * p.n + i), pj = __ldg(p.pts4 + b * p.n + j);
             const float4* refv_i = p.refv + (b * p.n + i) * p.k;
             const uint32_t row = a_base + buf * buf_bytes + ptid * pitch;
+            constexpr int KD4 = KD > 0 ? KD * 4 : 1;
+            if (SCORES) {
+                // The tile row's folded query (and u) come from L2, a different row for every tile of this CTA: fetched
+                // with plain loads at the point of use, that latency sat on the producers' critical path once per tile
+                // (measured: 7 of their 17 clk per pair).  So the raw fp32 values are copied asynchronously, first thing,
+                // into the very slots of the fragment images they will occupy (8 floats = the 32 bytes of hi | lo), and
+                // the same thread converts them in place after the basis values are done.
+                for (int it = ptid; it < p.H * (C / 8); it += CHEB_PRODUCER_WARPS * 32) {
+                    const int h = it / (C / 8), grp = it - h * (C / 8);  // grp = 4 cb + q
+                    const float* src = p.qt + b * p.qsb + (long long)h * p.qsh + (long long)i * p.qsn + grp * 8;
+                    const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * 32;
+                    cp_async16(dst, src);
+                    cp_async16(dst + 16, src + 4);
+                }
+                if (SPLIT && ptid < p.H * KD4) {
+                    const int h = ptid / KD4, rem = ptid - h * KD4, kt = rem >> 2, qq = rem & 3;
+                    const float* src = p.u + b * p.usb + (long long)h * p.ush + (long long)i * p.usn + p.u_offset[d_set] +
+                                       16 * kt + 2 * qq;
+                    const uint32_t dst = uimg + buf * UIMG_BYTES + (kt * 32 + h * 4 + qq) * 16;
+                    cp_async8(dst, src);
+                    cp_async8(dst + 8, src + 8);
+                }
+            }
             if (FAST) {  // k = SL slots, 'max': straight-line code, the recurrences of the slots interleave
 #pragma unroll
                 for (int s = 0; s < SL; ++s) {
@@ -419,51 +473,62 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 // the folded query of the tile's row as B fragments of the score contraction: fragment column n = head;
                 // lane (g = head, q) of channel block cb holds the 8 consecutive channels 32 cb + 8 q .. + 7 (the channel
                 // <-> k-slot assignment of the accumulators that become the A operand), as two half2 pairs per 16-channel
-                // k-tile, hi then lo.  Item = (head, 8-channel group); lanes of heads >= H stay zero.
+                // k-tile, hi then lo.  Item = (head, 8-channel group); lanes of heads >= H stay zero.  The raw values
+                // were copied into the item's own slot above, by this thread.
+                asm volatile("cp.async.wait_all;" ::: "memory");
                 for (int it = ptid; it < p.H * (C / 8); it += CHEB_PRODUCER_WARPS * 32) {
-                    const int h = it / (C / 8), grp = it - h * (C / 8);  // grp = 4 cb + q
-                    const float* src = p.qt + b * p.qsb + (long long)h * p.qsh + (long long)i * p.qsn + grp * 8;
-                    const float4 u = __ldg(reinterpret_cast<const float4*>(src)), v = __ldg(reinterpret_cast<const float4*>(src + 4));
-                    uint4 hi, lo;
-                    cheb_split(u.x, u.y, hi.x, lo.x);
-                    cheb_split(u.z, u.w, hi.y, lo.y);
-                    cheb_split(v.x, v.y, hi.z, lo.z);
-                    cheb_split(v.z, v.w, hi.w, lo.w);
+                    const int h = it / (C / 8), grp = it - h * (C / 8);
                     const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * 32;
+                    const uint4 ua = lds_v4(dst), va = lds_v4(dst + 16);
+                    uint4 hi, lo;
+                    cheb_split(__uint_as_float(ua.x), __uint_as_float(ua.y), hi.x, lo.x);
+                    cheb_split(__uint_as_float(ua.z), __uint_as_float(ua.w), hi.y, lo.y);
+                    cheb_split(__uint_as_float(va.x), __uint_as_float(va.y), hi.z, lo.z);
+                    cheb_split(__uint_as_float(va.z), __uint_as_float(va.w), hi.w, lo.w);
                     sts_v4(dst, hi);
                     sts_v4(dst + 16, lo);
                 }
-                if (SPLIT) {
+                if (SPLIT && ptid < p.H * KD4) {
                     // u[h][m] = sum_c qt[h][c] G_d[m][c] (it arrives with the query: the caller's projection produces it)
                     // turns the distance term's share of the scores into a K_d-term product with the basis values that
                     // are in the A tile anyway.  Item = (head, k-tile, q): B rows 2q, 2q+1 | 2q+8, 2q+9 of the k-tile.
-                    constexpr int KD4 = KD > 0 ? KD * 4 : 1;
-                    if (ptid < p.H * KD4) {
-                        const int h = ptid / KD4, rem = ptid - h * KD4, kt = rem >> 2, qq = rem & 3;
-                        const float* src = p.u + b * p.usb + (long long)h * p.ush + (long long)i * p.usn + p.u_offset[d_set] +
-                                           16 * kt + 2 * qq;
-                        const float2 lo2 = __ldg(reinterpret_cast<const float2*>(src)), hi2 = __ldg(reinterpret_cast<const float2*>(src + 8));
-                        uint4 w;  // hi(rows 2q..) | hi(rows 2q+8..) | lo | lo
-                        cheb_split(lo2.x, lo2.y, w.x, w.z);
-                        cheb_split(hi2.x, hi2.y, w.y, w.w);
-                        sts_v4(uimg + buf * UIMG_BYTES + (kt * 32 + h * 4 + qq) * 16, w);
-                    }
+                    const int h = ptid / KD4, rem = ptid - h * KD4, kt = rem >> 2, qq = rem & 3;
+                    const uint32_t dst = uimg + buf * UIMG_BYTES + (kt * 32 + h * 4 + qq) * 16;
+                    const uint4 raw = lds_v4(dst);  // rows 2q, 2q+1 | rows 2q+8, 2q+9
+                    uint4 w;  // hi(rows 2q..) | hi(rows 2q+8..) | lo | lo
+                    cheb_split(__uint_as_float(raw.x), __uint_as_float(raw.y), w.x, w.z);
+                    cheb_split(__uint_as_float(raw.z), __uint_as_float(raw.w), w.y, w.w);
+                    sts_v4(dst, w);
                 }
             }
         };
-        // the channel blocks' partial scores of a consumed tile -> scores_p[b, h, i, j0 .. j0 + CHEB_TILE - 1]
+        // the channel blocks' partial scores of a consumed tile -> scores_p[b, h, i, j0 .. j0 + CHEB_TILE - 1].  A task is
+        // (head, 4 consecutive keys): NCB 16-byte reads, one 16-byte store (the first version read and added one float per
+        // instruction and spent 37 % of the producers' instructions here)
+        const bool out_vec = (p.n & 3) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0;
         auto reduce = [&](long long tile, int buf) {
             long long b;
             int i, j0;
             locate(tile, 0, b, i, j0);
             const float* src = partial + buf * partial_floats;
             float* const out = reinterpret_cast<float*>(p.out) + (((size_t)b * p.H) * p.n + i) * p.n + j0;
-            for (int e = ptid; e < p.H * CHEB_TILE; e += CHEB_PRODUCER_WARPS * 32) {
-                const int h = e / CHEB_TILE, jl = e & (CHEB_TILE - 1);
-                float v = 0.f;
+            for (int task = ptid; task < p.H * (CHEB_TILE / 4); task += CHEB_PRODUCER_WARPS * 32) {
+                const int h = task / (CHEB_TILE / 4), jl = (task - h * (CHEB_TILE / 4)) * 4;
+                float4 v = *reinterpret_cast<const float4*>(src + h * CHEB_PSTRIDE + jl);
 #pragma unroll
-                for (int w = 0; w < NCB; ++w) v += src[(w * hp + h) * CHEB_TILE + jl];
-                if (j0 + jl < p.n) out[(size_t)h * p.n * p.n + jl] = v;
+                for (int w = 1; w < NSLOT; ++w) {
+                    const float4 t = *reinterpret_cast<const float4*>(src + (w * hp + h) * CHEB_PSTRIDE + jl);
+                    v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+                }
+                float* dst = out + (size_t)h * p.n * p.n + jl;
+                if (out_vec) {  // n % 4 == 0: a group of 4 keys is inside the row or outside it as a whole
+                    if (j0 + jl < p.n) *reinterpret_cast<float4*>(dst) = v;
+                } else {
+                    if (j0 + jl < p.n) dst[0] = v.x;
+                    if (j0 + jl + 1 < p.n) dst[1] = v.y;
+                    if (j0 + jl + 2 < p.n) dst[2] = v.z;
+                    if (j0 + jl + 3 < p.n) dst[3] = v.w;
+                }
             }
         };
 
@@ -472,22 +537,43 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         for (; tile < tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
             if (it >= 2) {
-                cheb_bar_sync(3 + buf);  // the consumers are done with tile it - 2: A[buf] is free, partial[buf] complete
+                // the consumers are done with tile it - 2: A[buf] is free, partial[buf] complete
+#ifdef CHEB_NAMED_BARRIERS
+                cheb_bar_sync(3 + buf);
+#else
+                ptx::mbar_wait(bar_empty + 8 * buf, ((it >> 1) - 1) & 1, 0x100);
+#endif
+#if !defined(CHEB_ABL_NO_REDUCE) && !defined(CHEB_ABL_NO_PRODUCE)  // timing ablations (tools/build_variants.sh), never in the shipped library
                 if (SCORES) reduce(older, buf);
+#endif
             }
+#ifndef CHEB_ABL_NO_PRODUCE
             produce(tile, buf);
+#endif
+#ifdef CHEB_NAMED_BARRIERS
             __threadfence_block();
             cheb_bar_arrive(1 + buf);
+#else
+            ptx::mbar_arrive(bar_full + 8 * buf);  // release: this thread's rows and fragment images are visible to the waiters
+#endif
             older = old;
             old = tile;
         }
         // drain: the last two tiles' scores
         if (it >= 2) {
+#ifdef CHEB_NAMED_BARRIERS
             cheb_bar_sync(3 + (it & 1));
+#else
+            ptx::mbar_wait(bar_empty + 8 * (it & 1), ((it - 2) >> 1) & 1, 0x101);
+#endif
             if (SCORES) reduce(older, it & 1);
         }
         if (it >= 1) {
+#ifdef CHEB_NAMED_BARRIERS
             cheb_bar_sync(3 + ((it + 1) & 1));
+#else
+            ptx::mbar_wait(bar_empty + 8 * ((it + 1) & 1), ((it - 1) >> 1) & 1, 0x102);
+#endif
             if (SCORES) reduce(old, (it + 1) & 1);
         }
         if (clamped) *p.overflow = 1;
@@ -526,6 +612,121 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(qh.x), "=r"(qh.y), "=r"(qh.z), "=r"(qh.w) : "r"(src));
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ql.x), "=r"(ql.y), "=r"(ql.z), "=r"(ql.w) : "r"(src + 16));
             }
+#ifndef CHEB_ABL_NO_TAIL
+            if (SPLIT) {
+                // the distance term's share of the scores, sum_m u[h][m] T_m(d_ij), is owed once per m-tile (not per
+                // channel block): warp w contracts it for m-tile w and leaves it in a block of partial scores of its own
+                // (slot NCB).  Issued FIRST: its dependent chain (ldmatrix -> 2 x KD HMMAs -> add -> store) then runs
+                // in the shadow of the expansions.  (Inside the m-tile loop the test `mt == warp` is if-converted into
+                // predicated-off HMMAs on every iteration, 2 of 10 issue slots per pair; as a read-modify-write of the
+                // warp's own partial after the loop it cost 1.2 clk per pair for 0.25 HMMA per pair.)
+                float sd[4], sd1[4];
+#pragma unroll
+                for (int kt = 0; kt < KD; ++kt) {
+                    uint32_t ad[4];
+                    ldsm4(ad, tile_addr + warp * 16 * pitch + (SL * KA + kt) * 32);
+                    const uint4 ub = lds_v4(uimg + buf * UIMG_BYTES + (kt * 32 + lane) * 16);
+                    if (kt == 0) {
+                        mma_new(sd, ad, make_uint2(ub.x, ub.y));
+                        mma_new(sd1, ad, make_uint2(ub.z, ub.w));
+                    } else {
+                        mma_acc(sd, ad, make_uint2(ub.x, ub.y));
+                        mma_acc(sd1, ad, make_uint2(ub.z, ub.w));
+                    }
+                }
+                if (2 * q < hp) {
+                    float* dst = partial + (buf * NSLOT + NCB) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + warp * 16 + g;
+                    dst[0] = sd[0] + sd1[0];
+                    dst[CHEB_PSTRIDE] = sd[1] + sd1[1];
+                    dst[8] = sd[2] + sd1[2];
+                    dst[CHEB_PSTRIDE + 8] = sd[3] + sd1[3];
+                }
+            }
+#endif
+#ifndef CHEB_NO_PIPELINE  // timing ablation switch (tools/build_variants.sh)
+            constexpr bool PIPELINED = FAST && SCORES;
+#else
+            constexpr bool PIPELINED = false;
+#endif
+            if constexpr (PIPELINED) {
+                // Software-pipelined by one m-tile, fully unrolled: the 12 expansion HMMAs of m-tile t+1 are issued BEFORE
+                // the score contraction of m-tile t, and the partial scores of t are stored one step later still.  Run
+                // back to back (expansions -> max -> two dependent score HMMAs -> add -> store -> next ldmatrix), every
+                // m-tile left the warp ~140 clocks without an HMMA to issue for 128 clocks of HMMA work, and four such
+                // warps kept the pipe 61 % busy with the producers switched off (tools/build_variants.sh ablation).
+                constexpr int AD = SPLIT ? 0 : KD;  // without the split the distance term is expanded into E like the angles
+                uint32_t a[SL * KA + AD][4], c[SL][4][2], cd[4][2];
+                float sc[4], sc1[4], scp[4], sc1p[4];
+                auto load_a = [&](int mt) {
+                    const uint32_t addr = tile_addr + mt * 16 * pitch;
+#pragma unroll
+                    for (int x = 0; x < SL * KA + AD; ++x) ldsm4(a[x], addr + x * 32);
+                };
+                auto expand = [&]() {
+#pragma unroll
+                    for (int sl = 0; sl < SL; ++sl)
+#pragma unroll
+                        for (int kt = 0; kt < KA; ++kt)
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) {
+                                if (kt == 0) mma_h_new(c[sl][t], a[sl * KA + kt], b_a[kt][t]);
+                                else mma_h_acc(c[sl][t], a[sl * KA + kt], b_a[kt][t]);
+                            }
+#pragma unroll
+                    for (int kt = 0; kt < AD; ++kt)
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            if (kt == 0) mma_h_new(cd[t], a[SL * KA + kt], b_d[kt][t]);
+                            else mma_h_acc(cd[t], a[SL * KA + kt], b_d[kt][t]);
+                        }
+                };
+                float sink = 0.f;  // timing ablations only
+                auto store_partial = [&](int mt, const float (&s0)[4], const float (&s1)[4]) {
+#ifdef CHEB_ABL_NO_PSTORE
+                    sink += (s0[0] + s1[0]) + (s0[1] + s1[1]) + (s0[2] + s1[2]) + (s0[3] + s1[3]);
+                    return;
+#endif
+                    if (2 * q < hp) {  // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
+                        float* dst = partial + (buf * NSLOT + cb) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + mt * 16 + g;
+                        dst[0] = s0[0] + s1[0];
+                        dst[CHEB_PSTRIDE] = s0[1] + s1[1];
+                        dst[8] = s0[2] + s1[2];
+                        dst[CHEB_PSTRIDE + 8] = s0[3] + s1[3];
+                    }
+                };
+                load_a(mt0);
+                expand();
+#pragma unroll
+                for (int mi = 0; mi < MT_PER_WARP; ++mi) {
+                    if (mi + 1 < MT_PER_WARP) load_a(mt0 + mi + 1);  // the HMMAs of m-tile mi have read `a` at issue
+                    uint32_t e0[4], e1[4];  // max over the slots (geotransformer.py:66) = the score contraction's A operand
+#pragma unroll
+                    for (int t = 0; t < 4; ++t)
+#pragma unroll
+                        for (int r = 0; r < 2; ++r) {
+                            uint32_t v = c[0][t][r];
+#pragma unroll
+                            for (int sl = 1; sl < SL; ++sl) v = hmax2_u(v, c[sl][t][r]);
+                            if (AD > 0) v = hadd2_u(v, cd[t][r]);  // geotransformer.py:70
+                            (t < 2 ? e0 : e1)[(t & 1) * 2 + r] = v;
+                        }
+                    if (mi + 1 < MT_PER_WARP) expand();
+                    if (mi > 0) store_partial(mt0 + mi - 1, scp, sc1p);
+#ifdef CHEB_ABL_NO_SCORE_MMA
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) { sc[r] = __uint_as_float(e0[r]); sc1[r] = __uint_as_float(e1[r]); }
+#else
+                    mma_new(sc, e0, make_uint2(qh.x, qh.y));
+                    mma_new(sc1, e1, make_uint2(qh.z, qh.w));
+                    mma_acc(sc, e0, make_uint2(ql.x, ql.y));
+                    mma_acc(sc1, e1, make_uint2(ql.z, ql.w));
+#endif
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) { scp[r] = sc[r]; sc1p[r] = sc1[r]; }
+                }
+                store_partial(mt0 + MT_PER_WARP - 1, scp, sc1p);
+                if (sink == 12345.678f) partial[lane] = sink;
+            } else {
             constexpr int kUnroll = FAST ? CHEB_UNROLL : 1;
 #pragma unroll kUnroll
             for (int mi = 0; mi < MT_PER_WARP; ++mi) {
@@ -622,26 +823,12 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                     mma_new(sc1, e1, make_uint2(qh.z, qh.w));
                     mma_acc(sc, e0, make_uint2(ql.x, ql.y));
                     mma_acc(sc1, e1, make_uint2(ql.z, ql.w));
-                    if (SPLIT && mt == warp) {
-                        // the distance term's share of this m-tile's scores, once per m-tile (not per channel block):
-                        // sum_m u[h][m] T_m(d_ij), the basis values straight from the A tile, u as hi + lo halves
-#pragma unroll
-                        for (int kt = 0; kt < KD; ++kt) {
-                            uint32_t ad[4];
-                            uint4 ub;
-                            ldsm4(ad, addr + (SL * KA + kt) * 32);
-                            const uint32_t usrc = uimg + buf * UIMG_BYTES + (kt * 32 + lane) * 16;
-                            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ub.x), "=r"(ub.y), "=r"(ub.z), "=r"(ub.w) : "r"(usrc));
-                            mma_acc(sc, ad, make_uint2(ub.x, ub.y));
-                            mma_acc(sc1, ad, make_uint2(ub.z, ub.w));
-                        }
-                    }
                     if (2 * q < hp) {  // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
-                        float* dst = partial + (buf * NCB + cb) * hp * CHEB_TILE + (2 * q) * CHEB_TILE + mt * 16 + g;
+                        float* dst = partial + (buf * NSLOT + cb) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + mt * 16 + g;
                         dst[0] = sc[0] + sc1[0];
-                        dst[CHEB_TILE] = sc[1] + sc1[1];
+                        dst[CHEB_PSTRIDE] = sc[1] + sc1[1];
                         dst[8] = sc[2] + sc1[2];
-                        dst[CHEB_TILE + 8] = sc[3] + sc1[3];
+                        dst[CHEB_PSTRIDE + 8] = sc[3] + sc1[3];
                     }
                 } else {
                     // thread (g, q): rows g and g + 8 of the m-tile, channels 32 cb + 8 q .. + 7 (n-tile t holds 2 t, 2 t + 1)
@@ -653,15 +840,28 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                     }
                 }
             }
+            }  // !PIPELINED
         };
 
         int it = 0;
         for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
-            cheb_bar_sync(1 + buf);  // the producers have filled A[buf] (and the query image)
+            // the producers have filled A[buf] (and the query image)
+#ifdef CHEB_NAMED_BARRIERS
+            cheb_bar_sync(1 + buf);
+#else
+            ptx::mbar_wait(bar_full + 8 * buf, (it >> 1) & 1, 0x200);
+#endif
+#ifndef CHEB_ABL_NO_CONSUME
             consume(tile, buf);
+#endif
+#ifdef CHEB_NAMED_BARRIERS
             __threadfence_block();
             cheb_bar_arrive(3 + buf);
+#else
+            __syncwarp();  // every lane's reads of A[buf] and partial-score stores are done ...
+            if (lane == 0) ptx::mbar_arrive(bar_empty + 8 * buf);  // ... before the warp's one arrival (release)
+#endif
         }
     }
 }
@@ -780,8 +980,8 @@ static int cheb_launch(const char* what, const void* geometry, int B, int n, int
     p.tiles = scores ? (long long)B * row_count * p.key_blocks : (p.pairs_total + CHEB_TILE - 1) / CHEB_TILE;
     GEOTX_REQUIRE(p.tiles < 2147483647LL, "%s: too many tiles", what);
     const int ktot_max = p.slots * 16 * ka_tiles + 16 * cheb_kd_tiles(max_d_set);
-    size_t smem = (size_t)2 * CHEB_TILE * (ktot_max * 2 + 16);
-    if (scores) smem += (size_t)2 * (C / 32) * (H <= 4 ? 4 : 8) * CHEB_TILE * sizeof(float) + (size_t)2 * (C / 32) * 32 * 32 +
+    size_t smem = CHEB_BAR_BYTES + (size_t)2 * CHEB_TILE * (ktot_max * 2 + 16);
+    if (scores) smem += (size_t)2 * (C / 32 + (u ? 1 : 0)) * (H <= 4 ? 4 : 8) * CHEB_PSTRIDE * sizeof(float) + (size_t)2 * (C / 32) * 32 * 32 +
                         (u ? (size_t)2 * 3 * 32 * 16 : 0);
     GEOTX_REQUIRE(smem <= 220 * 1024, "%s: %zu B of shared memory (k=%d, max_d_set=%d) do not fit", what, smem, k, max_d_set);
     int dev = 0, sms = 0;

@@ -234,7 +234,7 @@ extern "C" int geotx_gse_embed_table(const void* geometry, int B, int n, int k, 
     const float4* pts4 = (const float4*)geometry;
     const float4* refv = pts4 + (size_t)B * n;
     const long long pairs = (long long)B * row_count * n;
-    const int grid = 148 * (smem <= 110 * 1024 ? TBL_CTAS_PER_SM : 1);
+    const int grid = sm_count() * (smem <= 110 * 1024 ? TBL_CTAS_PER_SM : 1);
     auto launch = [&](auto kernel) -> int {
         int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                             "geotx_gse_embed_table: shared memory");

@@ -30,7 +30,6 @@ namespace geotx {
 // for small clouds -- and 8 warps / 128 queries, one CTA per SM -- every K/V tile is fetched from L2 and converted once
 // per CTA, so the larger shape halves that traffic; it is ~8 % faster from n = 2048 up (measured, tools/k3b_bench.py).
 constexpr int ATT_BK = 64;   // keys per tile
-constexpr int ATT_NUM_SMS = 148;
 __host__ __device__ constexpr int att_ctas_per_sm(int warps) { return warps <= 4 ? 2 : 1; }  // ~210 registers / thread
 constexpr int ATT_MAX_SPLITS = 8;      // portable cluster size
 
@@ -381,7 +380,7 @@ static void attention_plan(int B, int H, int n, int m, int warps, int allow_spli
     const int bq = 16 * warps;
     const long long base = (long long)((n + bq - 1) / bq) * B * H;
     const int tiles = (m + ATT_BK - 1) / ATT_BK;
-    const int wave = ATT_NUM_SMS * att_ctas_per_sm(warps);
+    const int wave = sm_count() * att_ctas_per_sm(warps);
     int s = 1;
     if (allow_split)  // stay within one wave: a second, partly filled wave costs more than the split gains
         while (s < ATT_MAX_SPLITS && base * (2 * s) <= wave && 2 * s <= tiles) s *= 2;

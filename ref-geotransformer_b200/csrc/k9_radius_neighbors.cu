@@ -422,7 +422,7 @@ extern "C" int geotx_radius_neighbors_grid(const float* q_points, const float* s
         if (rc) return rc;
         if (s_max > 0) {
             const int blocks = (s_max + 255) / 256;
-            rn_bounds_kernel<<<dim3(blocks < 148 ? blocks : 148, b.n), 256, 0, st>>>(s_points, b, g);
+            rn_bounds_kernel<<<dim3(blocks < sm_count() ? blocks : sm_count(), b.n), 256, 0, st>>>(s_points, b, g);
         }
         rn_params_kernel<<<1, 32, 0, st>>>(radius, b, g);
         if (s_max > 0) rn_build_kernel<<<dim3((s_max + 255) / 256, b.n), 256, 0, st>>>(s_points, b, g);

@@ -775,11 +775,26 @@ class RPEConditionalTransformer(nn.Module):
                     # plain schedule: both embedding kernels back to back, each with the whole GPU to itself
                     embs = [e.materialise() if isinstance(e, StreamedEmbedding) else e for e in embs]
                     streamed = False
+                # E-free mode: the two clouds' chains (K3r -> attention) are independent; the second cloud's runs on a side
+                # stream, so that its persistent K3r fills the SMs the first cloud's K3r drains from and the two short
+                # attention launches share the GPU (GEOTX_PARALLEL_CLOUDS=0: one stream)
+                fork = (self.overlap_attention and os.environ.get('GEOTX_PARALLEL_CLOUDS', '1') != '0' and
+                        all(isinstance(e, StreamedEmbedding) and e.direct for e in embs))
                 for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
                     emb = embs[which]
                     qt = y[:, lo:hi, 3 * C:3 * C + H * C].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
                     if isinstance(emb, StreamedEmbedding) and emb.direct:
                         u = y[:, lo:hi, 3 * C + H * C:].unflatten(2, (H, M)).permute(0, 2, 1, 3) if M else None
+                        if fork and which == 1:
+                            cur = torch.cuda.current_stream(x.device)
+                            side = _side_stream(x.device)
+                            side.wait_stream(cur)
+                            with torch.cuda.stream(side):
+                                scores_p = emb.direct_scores(qt, u)
+                                ops.attention(y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask,
+                                              out=hidden[:, lo:hi])
+                            del scores_p  # allocated and used on the side stream only
+                            continue
                         scores_p = emb.direct_scores(qt, u)  # K3r: E of this cloud is never formed in memory
                     elif isinstance(emb, StreamedEmbedding) and emb.regenerate_bytes > 0:
                         scores_p = emb.regenerated_scores(qt)  # E of this cloud is never stored
