@@ -142,10 +142,13 @@ int geotx_add_layernorm(const float* x, const float* residual, const float* gamm
 /* K13: y = x W^T + b (torch.nn.Linear) for the token-wise projections of the path that are not part of
  * geotx_post_attention's chain: in_proj / out_proj (geotransformer.py:140-141,152-153) and the q | k | v | folded-query
  * projections (rpe_transformer.py:51-53, vanilla_transformer.py:50-52; several Linears of a block are concatenated along
- * N by the caller).  x f32 [T,K] with row stride ld_x (floats), rounded to half on its way into shared memory; w_f16
- * [N][K] IEEE half (geotx_f32_to_f16 of the nn.Linear weight); mma.sync.m16n8k16, fp32 accumulation; y f32 [T,N] with
- * row stride ld_y; bias f32 [N] or NULL; relu != 0 applies max(., 0).  K % 32 == 0, N % 64 == 0. */
+ * N by the caller).  x f32 [T,K] with row stride ld_x (floats), rounded to half on its way into shared memory; w_f16 the
+ * PACKED half image of the nn.Linear weight [N][K] (geotx_pack_linear_weight: K chunks of 32, chunk-major, 16-byte
+ * units XOR-swizzled; streamed by TMA bulk copies); mma.sync.m16n8k16, fp32 accumulation; y f32 [T,N] with row stride
+ * ld_y; bias f32 [N] or NULL; relu != 0 applies max(., 0).  K % 32 == 0, K <= 2048, N % 64 == 0.
+ * geotx_f32_to_f16: plain element-wise conversion (same layout). */
 int geotx_f32_to_f16(const float* src, void* dst, int64_t count, void* stream);
+int geotx_pack_linear_weight(const float* w, int N, int K, void* packed_f16, void* stream);
 int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias, int N,
                      int relu, float* y, int64_t ld_y, void* stream);
 
@@ -153,8 +156,9 @@ int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, const void*
  * vanilla_transformer.py:99-101 followed by output_layer.py:15-21):
  *   x1  = LayerNorm(hidden W_lin^T + b_lin + x_in; gamma1, beta1, eps1)
  *   out = LayerNorm(x1 + (ReLU(x1 W_expand^T + b_expand)) W_squeeze^T + b_squeeze; gamma2, beta2, eps2)
- * hidden, x_in, out f32 [T,C] with row strides in floats (multiples of 4); C = 128 or 256; weights as IEEE half in
- * nn.Linear layout (w_lin [C][C], w_expand [2C][C], w_squeeze [C][2C]); biases and LayerNorm parameters f32.
+ * hidden, x_in, out f32 [T,C] with row strides in floats (multiples of 4); C = 128 or 256; weights as the PACKED half
+ * images (geotx_pack_linear_weight) of the nn.Linear weights w_lin [C][C], w_expand [2C][C], w_squeeze [C][2C]; biases
+ * and LayerNorm parameters f32.
  * A CTA keeps a tile of 32 tokens in shared memory through the whole chain; activations enter the contractions as
  * halves (saturated), accumulation / residuals / LayerNorm are fp32 (torch.nn.LayerNorm semantics). */
 int geotx_post_attention(const float* hidden, int64_t ld_hidden, const float* x_in, int64_t ld_x, int64_t T, int C,

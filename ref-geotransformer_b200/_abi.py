@@ -58,6 +58,7 @@ SIGNATURES = {
     'geotx_rpe_scores_cheb': (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _f, _i, _i, _f, _f, _i, _p, _i64, _i64, _i64, _i,
                                     _p, _i64, _i64, _i64, _p, _p, _p]),
     'geotx_f32_to_f16': (_i, [_p, _p, _i64, _p]),
+    'geotx_pack_linear_weight': (_i, [_p, _i, _i, _p, _p]),
     'geotx_linear_f16': (_i, [_p, _i64, _i64, _i, _p, _p, _i, _i, _p, _i64, _p]),
     'geotx_post_attention': (_i, [_p, _i64, _p, _i64, _i64, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _f, _p, _i64,
                                   _p]),

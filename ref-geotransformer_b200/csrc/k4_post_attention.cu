@@ -3,149 +3,105 @@
 //     out = LayerNorm(x1 + squeeze(ReLU(expand(x1))))              output_layer.py:15-21 (AttentionOutput)
 // The reference (and round 1 of this repo) runs these as 3 library GEMMs + 2 residual/LayerNorm kernels per layer and
 // cloud step: 45 launches of a few microseconds per forward, each one latency-bound at ~2k tokens.  All five steps are
-// token-local (LayerNorm normalises over the channels of ONE token), so a CTA that owns a tile of 32 tokens can run
-// the whole chain without leaving the SM: the three weight matrices stream through a 3-stage cp.async ring in 32-wide
-// K chunks (655 KB of half weights per CTA at C = 256, from L2), the activations live in shared memory between the
-// GEMMs (half as mma A operands, fp32 for the residuals), the contractions run on mma.sync.m16n8k16 (f16 operands --
-// the same 11-bit significand as the TF32 library path it replaces -- fp32 accumulation), LayerNorm is fp32 with warp
-// shuffles (torch.nn.LayerNorm: biased variance, eps inside the root).
+// token-local (LayerNorm normalises over the channels of ONE token), so a CTA that owns a tile of 32 tokens runs the
+// whole chain without leaving the SM: the activations live in shared memory between the GEMMs (half as mma A operands,
+// fp32 for the residuals), the contractions run on mma.sync.m16n8k16 (f16 operands -- the same 11-bit significand as
+// the TF32 library path it replaces -- fp32 accumulation), LayerNorm is fp32 with warp shuffles (torch.nn.LayerNorm:
+// biased variance, eps inside the root).
+//
+// The weights (655 KB of halves per CTA at C = 256, from L2) arrive through the TMA unit: they are packed once per
+// weight set (geotx_pack_linear_weight) into K chunks of 32 whose rows are 64 dense bytes with the 16-byte units
+// XOR-swizzled for conflict-free ldmatrix, so that chunk c of a matrix is ONE contiguous block and ONE cp.async.bulk
+// issued by a dedicated loader warp into a 4-stage ring; the eight compute warps wait on the stage's mbarrier
+// (complete_tx), contract, and hand the stage back with one arrival per warp.  No CTA-wide barrier inside a GEMM.
+// The first version issued 16-byte cp.async from the compute warps themselves and put a __syncthreads around every
+// chunk: the copy-issue phase (64 LSU instructions per chunk) and the mma phase of all eight warps alternated instead of
+// overlapping, 0.9 us per chunk and 32 us per launch for 5 us of tensor work (profiles/r02_launches_3dmatch_1024.csv).
 // Why mma.sync and not tcgen05: at T ~ 2k tokens a 128-token tcgen05 tile gives 16 CTAs on 148 SMs, and every CTA has
-// to pull all three weight matrices through its own L2 port; 32-token tiles put the same chain on 64+ SMs.  The kernel
-// is bound by that weight stream and by the dependent GEMM chain, not by tensor throughput (0.67 GFLOP per call).
+// to pull all three weight matrices through its own L2 port; 32-token tiles put the same chain on 64 SMs.
 #include <cuda_fp16.h>
 #include <type_traits>
 #include "geotx_common.cuh"
 #include "host_util.h"
+#include "sm100_ptx.cuh"
+#include "dense_tile.cuh"
 
 namespace geotx {
-
-constexpr int PA_BM = 32;        // tokens per CTA
-constexpr int PA_THREADS = 256;  // 8 warps: each owns N / 8 output columns of every GEMM
-constexpr int PA_KC = 32;        // K chunk of the weight ring (halves)
-constexpr int PA_STAGES = 3;
-constexpr int PA_WPITCH = PA_KC * 2 + 16;  // bytes per weight row in a stage: 80 = 16 * 5 (odd: conflict-free ldmatrix)
 
 struct PostAttnArgs {
     const float* hidden; long long ld_hidden;   // attention output [T, C]
     const float* x_in; long long ld_x;          // the layer's input tokens (residual) [T, C]
     float* out; long long ld_out;               // [T, C]
-    const __half* w_lin; const float* b_lin;    // [C][C]
+    const __half* w_lin; const float* b_lin;    // packed [C][C]
     const float* g1; const float* be1;          // attention.norm
-    const __half* w_exp; const float* b_exp;    // [2C][C]
-    const __half* w_sq; const float* b_sq;      // [C][2C]
+    const __half* w_exp; const float* b_exp;    // packed [2C][C]
+    const __half* w_sq; const float* b_sq;      // packed [C][2C]
     const float* g2; const float* be2;          // output.norm
     float eps1, eps2;
     int T;
 };
-
-__device__ __forceinline__ void pa_ldsm4(uint32_t (&r)[4], uint32_t addr) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-__device__ __forceinline__ void pa_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-__device__ __forceinline__ uint32_t pa_pack(float lo, float hi) {  // saturating: a stray large activation stays finite
-    uint32_t r;
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-    return r;
-}
-__device__ __forceinline__ void pa_cp16(uint32_t dst, const void* src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
 
 template <int C>
 struct PACfg {
     static constexpr int A_PITCH = C * 2 + 16;        // half A operand [32][C]      (bytes, odd multiple of 16)
     static constexpr int E_PITCH = 2 * C * 2 + 16;    // half A operand [32][2C]
     static constexpr int X_PITCH = C + 4;             // fp32 staging / residual [32][C] (floats)
-    static constexpr int STAGE_BYTES = 2 * C * PA_WPITCH;  // the widest GEMM (N = 2C) sizes a stage
-    static constexpr int OFF_A = 0;
-    static constexpr int OFF_E = OFF_A + PA_BM * A_PITCH;
-    static constexpr int OFF_X = OFF_E + PA_BM * E_PITCH;
-    static constexpr int OFF_W = OFF_X + PA_BM * X_PITCH * 4;
-    static constexpr int SMEM = OFF_W + PA_STAGES * STAGE_BYTES;
+    static constexpr int STAGE_BYTES = 2 * C * DT_ROW_BYTES;  // the widest GEMM (N = 2C) sizes a stage
+    static constexpr int OFF_BAR = 0;                 // full[DT_STAGES], empty[DT_STAGES]
+    static constexpr int OFF_A = 128;
+    static constexpr int OFF_E = OFF_A + DT_BM * A_PITCH;
+    static constexpr int OFF_X = OFF_E + DT_BM * E_PITCH;
+    static constexpr int OFF_W = (OFF_X + DT_BM * X_PITCH * 4 + 127) / 128 * 128;
+    static constexpr int SMEM = OFF_W + DT_STAGES * STAGE_BYTES;
     // chunk schedule: GEMM 0 (linear: N = C, K = C), 1 (expand: N = 2C, K = C), 2 (squeeze: N = C, K = 2C)
-    static constexpr int CH0 = C / PA_KC, CH1 = C / PA_KC, CH2 = 2 * C / PA_KC, CHUNKS = CH0 + CH1 + CH2;
+    static constexpr int CH0 = C / DT_KC, CH1 = C / DT_KC, CH2 = 2 * C / DT_KC, CHUNKS = CH0 + CH1 + CH2;
 };
 
 template <int C>
-__global__ void __launch_bounds__(PA_THREADS, 1) post_attention_kernel(const PostAttnArgs p) {
+__global__ void __launch_bounds__(DT_THREADS, 1) post_attention_kernel(const PostAttnArgs p) {
     using Cfg = PACfg<C>;
-    extern __shared__ __align__(16) unsigned char pa_smem[];
+    extern __shared__ __align__(128) unsigned char pa_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, q = lane & 3;
-    const int row0 = blockIdx.x * PA_BM;
+    const int row0 = blockIdx.x * DT_BM;
     const uint32_t s_base = smem_u32(pa_smem);
-    const uint32_t sA = s_base + Cfg::OFF_A, sE = s_base + Cfg::OFF_E, sW = s_base + Cfg::OFF_W;
+    const uint32_t sA = s_base + Cfg::OFF_A, sE = s_base + Cfg::OFF_E;
     float* const sX = reinterpret_cast<float*>(pa_smem + Cfg::OFF_X);
+    DtRing ring;
+    ring.bar_full = s_base + Cfg::OFF_BAR;
+    ring.bar_empty = ring.bar_full + 8 * DT_STAGES;
+    ring.stages = s_base + Cfg::OFF_W;
+    ring.stage_bytes = Cfg::STAGE_BYTES;
+    ring.init(tid);
+    __syncthreads();
 
-    // weight chunk c of the flat schedule -> ring stage c % 3 (cp.async, 16 B per request)
-    auto issue = [&](int c) {
-        if (c < Cfg::CHUNKS) {
-            const __half* w;
-            int N, K, k0;
-            if (c < Cfg::CH0) { w = p.w_lin; N = C; K = C; k0 = c * PA_KC; }
-            else if (c < Cfg::CH0 + Cfg::CH1) { w = p.w_exp; N = 2 * C; K = C; k0 = (c - Cfg::CH0) * PA_KC; }
-            else { w = p.w_sq; N = C; K = 2 * C; k0 = (c - Cfg::CH0 - Cfg::CH1) * PA_KC; }
-            const uint32_t dst = sW + (c % PA_STAGES) * Cfg::STAGE_BYTES;
-            for (int e = tid; e < N * 4; e += PA_THREADS) {  // 4 x 16 B per weight row
-                const int n = e >> 2, part = e & 3;
-                pa_cp16(dst + n * PA_WPITCH + part * 16, w + (size_t)n * K + k0 + part * 8);
+    if (warp == DT_WARPS) {  // ---- loader: the three matrices' chunks, in schedule order, one bulk copy each ----
+        if (lane == 0) {
+            for (int c = 0; c < Cfg::CHUNKS; ++c) {
+                if (c < Cfg::CH0) ring.load(c, p.w_lin + (size_t)c * C * DT_KC, C * DT_ROW_BYTES);
+                else if (c < Cfg::CH0 + Cfg::CH1) ring.load(c, p.w_exp + (size_t)(c - Cfg::CH0) * 2 * C * DT_KC, 2 * C * DT_ROW_BYTES);
+                else ring.load(c, p.w_sq + (size_t)(c - Cfg::CH0 - Cfg::CH1) * C * DT_KC, C * DT_ROW_BYTES);
             }
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");  // one group per chunk slot, empty past the end
-    };
+        return;
+    }
 
-    issue(0);
-    issue(1);
     // the tile's attention output -> half A operand
-    for (int e = tid; e < PA_BM * (C / 4); e += PA_THREADS) {
+    for (int e = tid; e < DT_BM * (C / 4); e += DT_WARPS * 32) {
         const int r = e / (C / 4), c4 = e % (C / 4);
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (row0 + r < p.T) v = __ldg(reinterpret_cast<const float4*>(p.hidden + (size_t)(row0 + r) * p.ld_hidden) + c4);
-        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(pa_pack(v.x, v.y)),
-                     "r"(pa_pack(v.z, v.w)) : "memory");
+        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(dt_pack(v.x, v.y)),
+                     "r"(dt_pack(v.z, v.w)) : "memory");
     }
-
-    // one GEMM of the chain: acc[mt][nt] (2 m-tiles x NT n-tiles of this warp's N / 8 columns) += A (smem, half) x W^T
-    auto gemm = [&](auto& acc, auto nt_tag, uint32_t a_addr, int a_pitch, int chunk0, int chunks) {
-        constexpr int NT = decltype(nt_tag)::value;
-        const int n_warp = warp * NT * 8;
-        for (int c = 0; c < chunks; ++c) {
-            asm volatile("cp.async.wait_group 1;" ::: "memory");  // chunk (chunk0 + c) has landed
-            __syncthreads();                                      // ... for every thread; stage (c+2) % 3 is free again
-            issue(chunk0 + c + 2);
-            const uint32_t w_addr = sW + ((chunk0 + c) % PA_STAGES) * Cfg::STAGE_BYTES;
-#pragma unroll
-            for (int ks = 0; ks < PA_KC / 16; ++ks) {
-                uint32_t a[2][4];
-#pragma unroll
-                for (int mt = 0; mt < 2; ++mt)
-                    pa_ldsm4(a[mt], a_addr + (mt * 16 + (lane & 15)) * a_pitch + (c * PA_KC + ks * 16 + (lane >> 4) * 8) * 2);
-#pragma unroll
-                for (int np = 0; np < NT / 2; ++np) {  // two n-tiles per ldmatrix.x4
-                    uint32_t b[4];
-                    pa_ldsm4(b, w_addr + (n_warp + np * 16 + (lane & 7) + ((lane >> 4) & 1) * 8) * PA_WPITCH +
-                                    (ks * 16 + ((lane >> 3) & 1) * 8) * 2);
-#pragma unroll
-                    for (int mt = 0; mt < 2; ++mt) {
-                        pa_mma(acc[mt][2 * np], a[mt], b[0], b[1]);
-                        pa_mma(acc[mt][2 * np + 1], a[mt], b[2], b[3]);
-                    }
-                }
-            }
-        }
-    };
+    dt_sync_compute();
 
     // LayerNorm of the 32 rows staged in sX (fp32): warp w normalises rows 4w .. 4w+3, lane owns C / 32 channels
     auto layer_norm = [&](const float* gamma, const float* beta, float eps, bool to_global) {
         constexpr int PER = C / 32;
 #pragma unroll 1
-        for (int rr = 0; rr < PA_BM / 8; ++rr) {
-            const int r = warp * (PA_BM / 8) + rr;
+        for (int rr = 0; rr < DT_BM / 8; ++rr) {
+            const int r = warp * (DT_BM / 8) + rr;
             float* row = sX + r * Cfg::X_PITCH;
             float v[PER];
             float sum = 0.f;
@@ -177,8 +133,8 @@ __global__ void __launch_bounds__(PA_THREADS, 1) post_attention_kernel(const Pos
                     if (row0 + r < p.T) *reinterpret_cast<float4*>(p.out + (size_t)(row0 + r) * p.ld_out + c4 * 4) = o;
                 } else {
                     *reinterpret_cast<float4*>(row + c4 * 4) = o;  // x1 stays in fp32 for the second residual
-                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(pa_pack(o.x, o.y)),
-                                 "r"(pa_pack(o.z, o.w)) : "memory");  // ... and as the expand GEMM's A operand
+                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(dt_pack(o.x, o.y)),
+                                 "r"(dt_pack(o.z, o.w)) : "memory");  // ... and as the expand GEMM's A operand
                 }
             }
         }
@@ -187,7 +143,7 @@ __global__ void __launch_bounds__(PA_THREADS, 1) post_attention_kernel(const Pos
     // ---- GEMM 0: linear(hidden); + bias + residual -> sX; LayerNorm -> x1 (sX fp32, sA half) ----
     {
         float acc[2][C / 64][4] = {};
-        gemm(acc, std::integral_constant<int, C / 64>{}, sA, Cfg::A_PITCH, 0, Cfg::CH0);
+        dt_gemm<C / 64>(acc, ring, 0, Cfg::CH0, sA, Cfg::A_PITCH, warp * (C / 8), lane);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
@@ -204,12 +160,13 @@ __global__ void __launch_bounds__(PA_THREADS, 1) post_attention_kernel(const Pos
                 }
             }
     }
-    __syncthreads();  // all of sX written; every warp is done reading sA (hidden)
+    dt_sync_compute();  // all of sX written; every warp is done reading sA (hidden)
     layer_norm(p.g1, p.be1, p.eps1, false);
-    // ---- GEMM 1: ReLU(expand(x1) + bias) -> sE (half).  Its first barrier orders the LayerNorm's writes ----
+    dt_sync_compute();  // x1 complete in sA / sX
+    // ---- GEMM 1: ReLU(expand(x1) + bias) -> sE (half) ----
     {
         float acc[2][C / 32][4] = {};
-        gemm(acc, std::integral_constant<int, C / 32>{}, sA, Cfg::A_PITCH, Cfg::CH0, Cfg::CH1);
+        dt_gemm<C / 32>(acc, ring, Cfg::CH0, Cfg::CH1, sA, Cfg::A_PITCH, warp * (C / 4), lane);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
@@ -220,15 +177,16 @@ __global__ void __launch_bounds__(PA_THREADS, 1) post_attention_kernel(const Pos
                 for (int h = 0; h < 2; ++h) {
                     const int r = mt * 16 + g + 8 * h;
                     asm volatile("st.shared.b32 [%0], %1;" ::"r"(sE + r * Cfg::E_PITCH + col * 2),
-                                 "r"(pa_pack(fmaxf(acc[mt][nt][2 * h] + bias.x, 0.f), fmaxf(acc[mt][nt][2 * h + 1] + bias.y, 0.f)))
+                                 "r"(dt_pack(fmaxf(acc[mt][nt][2 * h] + bias.x, 0.f), fmaxf(acc[mt][nt][2 * h + 1] + bias.y, 0.f)))
                                  : "memory");
                 }
             }
     }
+    dt_sync_compute();  // sE complete
     // ---- GEMM 2: squeeze(e) + bias + x1 -> sX (in place: each element is read and written by one thread); LayerNorm ----
     {
         float acc[2][C / 64][4] = {};
-        gemm(acc, std::integral_constant<int, C / 64>{}, sE, Cfg::E_PITCH, Cfg::CH0 + Cfg::CH1, Cfg::CH2);
+        dt_gemm<C / 64>(acc, ring, Cfg::CH0 + Cfg::CH1, Cfg::CH2, sE, Cfg::E_PITCH, warp * (C / 8), lane);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
@@ -243,13 +201,30 @@ __global__ void __launch_bounds__(PA_THREADS, 1) post_attention_kernel(const Pos
                 }
             }
     }
-    __syncthreads();
+    dt_sync_compute();
     layer_norm(p.g2, p.be2, p.eps2, true);
 }
 
 __global__ void f32_to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, long long count) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) dst[i] = __float2half_rn(src[i]);
+}
+
+// W [N][K] fp32 -> the packed half image of dense_tile.cuh; one thread per 16-byte unit
+__global__ void pack_linear_weight_kernel(const float* __restrict__ w, int N, int K, uint4* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // = (c * N + r) * 4 + u
+    if (i >= (long long)N * K / 8) return;
+    const int u = (int)(i & 3);
+    const long long cr = i >> 2;
+    const int r = (int)(cr % N), c = (int)(cr / N);
+    const float* src = w + (size_t)r * K + c * DT_KC + u * 8;
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+    uint4 v;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(v.x) : "f"(a.y), "f"(a.x));
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(v.y) : "f"(a.w), "f"(a.z));
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(v.z) : "f"(b.y), "f"(b.x));
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(v.w) : "f"(b.w), "f"(b.z));
+    out[cr * 4 + (u ^ ((r >> 1) & 3))] = v;
 }
 
 }  // namespace geotx
@@ -262,6 +237,16 @@ extern "C" int geotx_f32_to_f16(const float* src, void* dst, int64_t count, void
     GEOTX_REQUIRE(blocks < 2147483647LL, "geotx_f32_to_f16: too many elements");
     f32_to_f16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__half*)dst, count);
     return launch_status("geotx_f32_to_f16");
+}
+
+extern "C" int geotx_pack_linear_weight(const float* w, int N, int K, void* packed_f16, void* stream) {
+    GEOTX_REQUIRE(w && packed_f16, "geotx_pack_linear_weight: null pointer");
+    GEOTX_REQUIRE(N >= 8 && N % 8 == 0 && K >= DT_KC && K % DT_KC == 0,
+                  "geotx_pack_linear_weight: N=%d must be a multiple of 8 and K=%d a multiple of %d", N, K, DT_KC);
+    GEOTX_REQUIRE((((uintptr_t)w | (uintptr_t)packed_f16) & 15) == 0, "geotx_pack_linear_weight: pointers must be 16-byte aligned");
+    const long long units = (long long)N * K / 8;
+    pack_linear_weight_kernel<<<(unsigned)((units + 255) / 256), 256, 0, (cudaStream_t)stream>>>(w, N, K, (uint4*)packed_f16);
+    return launch_status("geotx_pack_linear_weight");
 }
 
 extern "C" int geotx_post_attention(const float* hidden, int64_t ld_hidden, const float* x_in, int64_t ld_x, int64_t T,
@@ -290,12 +275,12 @@ extern "C" int geotx_post_attention(const float* hidden, int64_t ld_hidden, cons
     p.g2 = gamma2; p.be2 = beta2;
     p.eps1 = eps1; p.eps2 = eps2;
     p.T = (int)T;
-    const int grid = (int)((T + PA_BM - 1) / PA_BM);
+    const int grid = (int)((T + DT_BM - 1) / DT_BM);
     auto launch = [&](auto kernel, int smem) -> int {
         int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                             "geotx_post_attention: shared memory");
         if (rc) return rc;
-        kernel<<<grid, PA_THREADS, smem, (cudaStream_t)stream>>>(p);
+        kernel<<<grid, DT_THREADS, smem, (cudaStream_t)stream>>>(p);
         return 0;
     };
     int rc = C == 256 ? launch(post_attention_kernel<256>, PACfg<256>::SMEM) : launch(post_attention_kernel<128>, PACfg<128>::SMEM);

@@ -109,15 +109,19 @@ def _dense_own():
 
 
 def _half_of(owner, name, t):
-    """IEEE-half copy of weight `t`, cached on `owner` and rebuilt when `t` changes (new storage or in-place update)."""
+    """Packed half image (ops.pack_linear: the operand format of K13 / K4f) of weight `t`, cached on `owner` and rebuilt
+    when `t` changes (new storage or in-place update)."""
     cache = owner.__dict__.setdefault('_half_cache', {})
     key = (t.data_ptr(), t._version)
     ent = cache.get(name)
     if ent is None or ent[0] != key:
         if torch.cuda.is_current_stream_capturing():
-            raise RuntimeError('a weight changed since its half copy was made; run one forward outside CUDA graph '
+            raise RuntimeError('a weight changed since its packed half copy was made; run one forward outside CUDA graph '
                                'capture first')
-        ent = (key, ops.to_half(t.detach()))
+        ent = (key, ops.pack_linear(t.detach()))
+        # The copy is made on whatever stream is current (the second cloud's in_proj runs on a side stream) and then
+        # used from every stream: wait for it once, here, instead of ordering every later use.
+        torch.cuda.current_stream(t.device).synchronize()
         cache[name] = ent
     return ent[1]
 

@@ -670,6 +670,20 @@ def to_half(t):
     return out
 
 
+def pack_linear(w):
+    """nn.Linear weight (N, K) fp32 CUDA -> its packed half image for linear_f16 / post_attention: same shape and dtype
+    float16, but the element order is geotx_pack_linear_weight's (K chunks of 32, chunk-major, swizzled 16-byte units;
+    csrc/dense_tile.cuh) -- an opaque operand, not a matrix to index."""
+    _check(w, 'w', torch.float32, 2)
+    w = w.contiguous()
+    N, K = w.shape
+    if N % 8 or K % 32:
+        raise RuntimeError(f'pack_linear: weight {tuple(w.shape)} needs N % 8 == 0 and K % 32 == 0')
+    out = torch.empty(N, K, dtype=torch.float16, device=w.device)
+    _abi.call('geotx_pack_linear_weight', _p(w), N, K, _p(out), _stream())
+    return out
+
+
 def _rows2d(t, name, cols):
     """(…, cols) fp32 CUDA tensor whose leading dimensions flatten into equally strided rows -> (rows, row stride)."""
     if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.float32 or t.dim() < 1:
@@ -686,19 +700,19 @@ def _rows2d(t, name, cols):
 
 
 def linear_supported(K, N):
-    return K >= 32 and K % 32 == 0 and N >= 64 and N % 64 == 0
+    return K >= 32 and K % 32 == 0 and K <= 2048 and N >= 64 and N % 64 == 0
 
 
 def linear_f16(x, w_half, bias, out=None, relu=False):
     """y = x W^T + b (nn.Linear semantics) on the hand-written mma.sync kernel K13: x (..., K) fp32 with equally strided
-    rows, w_half (N, K) IEEE half (`to_half(weight)`), bias (N,) fp32 or None -> (..., N) fp32 (into `out` if given;
-    rows of `out` may be strided).  K % 32 == 0, N % 64 == 0."""
+    rows, w_half (N, K) the PACKED half image of the weight (`pack_linear(weight)`), bias (N,) fp32 or None -> (..., N)
+    fp32 (into `out` if given; rows of `out` may be strided).  K % 32 == 0, K <= 2048, N % 64 == 0."""
     if not isinstance(w_half, torch.Tensor) or not w_half.is_cuda or w_half.dtype != torch.float16 or w_half.dim() != 2 \
             or not w_half.is_contiguous():
         raise RuntimeError('w_half must be a contiguous 2-d float16 CUDA tensor (N, K)')
     N, K = w_half.shape
     if not linear_supported(K, N):
-        raise RuntimeError(f'linear_f16: K={K} must be a multiple of 32 and N={N} a multiple of 64')
+        raise RuntimeError(f'linear_f16: K={K} must be a multiple of 32 (<= 2048) and N={N} a multiple of 64')
     T, ld_x = _rows2d(x, 'x', K)
     if bias is not None:
         _check(bias, 'bias', torch.float32, 1)
@@ -714,7 +728,7 @@ def linear_f16(x, w_half, bias, out=None, relu=False):
 def post_attention(hidden, x_in, w_lin, b_lin, g1, be1, eps1, w_exp, b_exp, w_sq, b_sq, g2, be2, eps2, out=None):
     """K4f: LayerNorm(x1 + squeeze(ReLU(expand(x1)))) with x1 = LayerNorm(linear(hidden) + x_in) in one kernel
     (rpe_transformer.py:101-103 / vanilla_transformer.py:99-101 + output_layer.py:15-21).  hidden, x_in (..., C) fp32
-    with equally strided rows, C in {128, 256}; w_* IEEE-half copies of the nn.Linear weights; the rest fp32."""
+    with equally strided rows, C in {128, 256}; w_* packed half images (`pack_linear`) of the nn.Linear weights; the rest fp32."""
     C = hidden.shape[-1]
     T, ld_h = _rows2d(hidden, 'hidden', C)
     T2, ld_x = _rows2d(x_in, 'x_in', C)

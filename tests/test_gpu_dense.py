@@ -21,8 +21,10 @@ def test_linear_vs_torch(pkg, T, K, N):
     w = torch.randn(N, K, generator=g) / K ** 0.5
     b = torch.randn(N, generator=g)
     exp = torch.nn.functional.linear(x, w, b)
-    wh = pkg.ops.to_half(w.to(DEV))
-    assert wh.dtype == torch.float16 and torch.equal(wh.cpu(), w.half())
+    assert torch.equal(pkg.ops.to_half(w.to(DEV)).cpu(), w.half())
+    wh = pkg.ops.pack_linear(w.to(DEV))  # K13's operand: same halves, chunk-major swizzled order
+    assert wh.dtype == torch.float16 and tuple(wh.shape) == (N, K)
+    assert torch.equal(wh.cpu().flatten().sort().values, w.half().flatten().sort().values)
     got = pkg.ops.linear_f16(x.to(DEV), wh, b.to(DEV))
     assert tuple(got.shape) == (T, N) and rel(got, exp) <= TOL
     assert rel(pkg.ops.linear_f16(x.to(DEV), wh, None), exp - b) <= TOL
@@ -38,16 +40,16 @@ def test_linear_strided_rows_and_slices(pkg):
     b = torch.randn(192, generator=g).to(DEV)
     out_big = torch.full((1, 260, 448), -7.0, device=DEV)
     out = out_big[:, 10:210, 64:256]                # (1, 200, 192) view
-    pkg.ops.linear_f16(x, pkg.ops.to_half(w), b, out=out)
+    pkg.ops.linear_f16(x, pkg.ops.pack_linear(w), b, out=out)
     exp = torch.nn.functional.linear(x, w, b)
     assert rel(out, exp) <= TOL
     mask = torch.ones_like(out_big, dtype=torch.bool)
     mask[:, 10:210, 64:256] = False
     assert float((out_big[mask] + 7.0).abs().max()) == 0.0, 'wrote outside the output view'
     with pytest.raises(RuntimeError):
-        pkg.ops.linear_f16(big[:, :, ::2], pkg.ops.to_half(w), b)  # last dimension not dense
+        pkg.ops.linear_f16(big[:, :, ::2], pkg.ops.pack_linear(w), b)  # last dimension not dense
     with pytest.raises(RuntimeError):
-        pkg.ops.linear_f16(torch.randn(8, 100, device=DEV), pkg.ops.to_half(torch.randn(64, 100, device=DEV)), None)  # K % 32
+        pkg.ops.linear_f16(torch.randn(8, 100, device=DEV), torch.randn(64, 100, device=DEV).half(), None)  # K % 32
 
 
 @pytest.mark.parametrize('C,T', [(256, 2048), (128, 4096), (256, 717), (128, 33), (256, 1)])
@@ -65,7 +67,7 @@ def test_post_attention_vs_oracle(pkg, oracle, C, T):
     x1 = oracle._layer_norm(h + x_in, sd, lp + 'attention.norm.')
     exp = oracle.attention_output(x1, sd, lp + 'output.')
     d = {k: v.to(DEV) for k, v in sd.items()}
-    half = {k: pkg.ops.to_half(d[lp + k]) for k in ('attention.linear.weight', 'output.expand.weight', 'output.squeeze.weight')}
+    half = {k: pkg.ops.pack_linear(d[lp + k]) for k in ('attention.linear.weight', 'output.expand.weight', 'output.squeeze.weight')}
     args = (half['attention.linear.weight'], d[lp + 'attention.linear.bias'], d[lp + 'attention.norm.weight'],
             d[lp + 'attention.norm.bias'], 1e-5, half['output.expand.weight'], d[lp + 'output.expand.bias'],
             half['output.squeeze.weight'], d[lp + 'output.squeeze.bias'], d[lp + 'output.norm.weight'],
