@@ -66,6 +66,12 @@ struct DtRing {
         return stages + s * stage_bytes;
     }
     __device__ __forceinline__ void release(int g, int lane) const {
+        // The stage was read through the generic proxy (ldmatrix) and will be overwritten through the async proxy (the
+        // loader's next bulk copy): the mbarrier hand-over orders generic-proxy accesses only, so every reader fences
+        // its reads against the async proxy first.  Without this fence CTAs of the second wave, starting next to a
+        // running CTA on the same SM, sporadically contracted against partly overwritten weight rows
+        // (tools/dense_stress.py: 14 of 300 calls at N = 1792, every call at N = 2112; none with the fence).
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(bar_empty + 8 * (g % DT_STAGES));
     }

@@ -51,8 +51,12 @@ __global__ void __launch_bounds__(DT_THREADS) linear_tile_kernel(const LinearArg
     const int chunks = p.K / DT_KC;
 
     if (warp == DT_WARPS) {  // ---- loader ----
-        if (lane == 0)
+        if (lane == 0) {
             for (int c = 0; c < chunks; ++c) ring.load(c, p.w + ((size_t)c * p.N + n0) * DT_KC, cols * DT_ROW_BYTES);
+#ifdef DT_LOADER_STAYS
+            for (int c = max(chunks - DT_STAGES, 0); c < chunks; ++c) ring.wait(c);
+#endif
+        }
         return;
     }
 
@@ -121,7 +125,11 @@ extern "C" int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, 
     // the widest column block that still gives every SM a CTA (x is converted once per CTA: wider is cheaper)
     int nt = 4;
     while (nt > 1 && row_tiles * ((N + 64 * nt - 1) / (64 * nt)) < sms) nt >>= 1;
+#ifdef DT_ONE_CTA
+    const size_t smem = 120 * 1024;
+#else
     const size_t smem = (size_t)lin_off_w(K) + (size_t)DT_STAGES * 64 * nt * DT_ROW_BYTES;
+#endif
     const dim3 grid((unsigned)((N + 64 * nt - 1) / (64 * nt)), (unsigned)row_tiles);
     auto launch = [&](auto kernel) -> int {
         int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
