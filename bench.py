@@ -51,8 +51,12 @@ WORKLOADS = {
     '3dmatch_16384': ('3dmatch', 16384, 16384),
 }
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` captures of the SHIPPED kernels
-# (profiles/r02_ncu_*.txt; None until captured)
-NCU_TRAFFIC_BYTES = {}
+# (profiles/r02_forward_3dmatch_1024_ncu_full.txt; None where not captured).  K3r: 5.12 MB read (the folded queries, u
+# and the geometry) and 0 B written INSIDE the launch: its 16.8 MB of scores stay in the 126 MB L2 until the attention
+# kernel that follows has read them (that launch shows 19.9 MB of DRAM reads under ncu's cache flush, ~0 in the step).
+NCU_TRAFFIC_BYTES = {
+    ('gse_embed_cheb_kernel<SCORES> (geotx_rpe_scores_cheb, K3r)', '3dmatch_1024'): 5.12e6,
+}
 METRIC = 'registration pairs/sec (embed+RPE-attn) at N superpoints'
 UNIT = 'pairs/s'
 CONFIGS4_PAIRS = 256
