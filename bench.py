@@ -10,8 +10,9 @@ works on its own pairs (pair sharding, no collective on the path, SURVEY.md 8e);
 steps of all ranks are gathered with one NCCL all_gather inside the timed region (after a warm-up gather).
 Prints ONE JSON line on rank 0.
 
-  value      pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks; up to n = 2048 three CUDA-graph instances
-             of the forward are in flight on three streams (independent pairs overlap; GEOTX_INFLIGHT)
+  value      pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks; up to n = 2048 several CUDA-graph instances
+             of the forward are in flight on their own streams (independent pairs overlap; GEOTX_INFLIGHT, default 4:
+             measured 1040 / 1086 / 1102 / 1097 pairs/s with 2 / 3 / 4 / 5)
   e2e        pairs/s through PipelinedGeometricTransformer.map with HOST (pinned) inputs and a host read of the outputs
   roofline   the dominant kernel of the default path, K3r (geotx_rpe_scores_cheb: low-rank embedding + folded-query
              scores, E never stored), timed by CUDA events captured inside the forward's graph: flops the kernel
@@ -750,7 +751,7 @@ def run_b200(args):
                 'share_of_step': sum(d['ms_per_launch']) / step_ms if step_ms else None}
 
     many = max(n, m) <= 2048
-    inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '3'))) if many else 1
+    inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '4'))) if many else 1
 
     def run_variant(tag, setup, undo, steps, want_kernels=True):
         """The same forward under another configuration: value (graph replay, CUDA events) + its kernel table."""
@@ -847,7 +848,7 @@ def run_b200(args):
 
         # ---- end to end: host (pinned) inputs -> device -> forward -> host outputs, every step, through the serving
         #      API (PipelinedGeometricTransformer: the upload of pair p+1 / download of pair p-1 overlap pair p) ----
-        depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', '3'))) if many else 2)
+        depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', '5'))) if many else 2)
         del fast
         torch.cuda.empty_cache()
         pipe = pkg.PipelinedGeometricTransformer(model, *resident[0], depth=depth)
