@@ -682,6 +682,13 @@ def run_b200(args):
     d2h = (n + m) * cfg['output_dim'] * 4
     d_set = max(host_d_set(pkg, host[0][0], cfg['sigma_d'])[0], host_d_set(pkg, host[0][1], cfg['sigma_d'])[0])
     kd = 16 * KD_TILES[d_set]
+    # the widest cloud of the rotation decides how many distance coefficients the embedding kernel must be prepared for
+    # (the module widens itself on the FIRST call of a shape only; a later pair of the rotation may be wider)
+    widest = max(host_d_set(pkg, pr[c], cfg['sigma_d'])[1] for pr in host for c in (0, 1))
+    if widest > model.embedding.cheb_d_index_max:
+        lib = pkg._abi.load()
+        model.embedding.cheb_d_index_max = next(float(lib.geotx_gse_cheb_d_range(s)) for s in range(6)
+                                                if widest <= float(lib.geotx_gse_cheb_d_range(s)) or s == 5)
 
     def k3r_flops(geom, coef, qt, *a, **kw):  # flops the kernel EXECUTES: expansions of the k angle slots, scores hi + lo,
         rows = geom.n                          # and the distance term (inside E, or split off in coefficient space)
