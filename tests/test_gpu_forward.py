@@ -69,6 +69,27 @@ def test_masks_batch_and_fp32_precision_vs_oracle(pkg, oracle):
         assert r0 <= tol and r1 <= tol
 
 
+@pytest.mark.parametrize('n,m', [(4, 7), (5, 4), (129, 4)])
+def test_smallest_clouds_default_path_vs_oracle(pkg, oracle, n, m):
+    """n = k + 1 (every other point is a neighbour: geotransformer.py:42 takes the k+1 nearest and drops the first) and
+    clouds of a handful of points next to one that crosses a 128-key tile boundary, B = 1, DEFAULT path (K3r scores,
+    own dense kernels): almost every lane of every tile is padding."""
+    cfg = dict(pkg.synth.CONFIGS['3dmatch'])
+    sd = oracle.init_state_dict(cfg['input_dim'], cfg['output_dim'], cfg['hidden_dim'], cfg['blocks'])
+    g = torch.Generator().manual_seed(n * 31 + m)
+    rp, sp = torch.rand(1, n, 3, generator=g) * 2, torch.rand(1, m, 3, generator=g) * 2
+    rf, sf = torch.randn(1, n, cfg['input_dim'], generator=g), torch.randn(1, m, cfg['input_dim'], generator=g)
+    e0, e1 = oracle.geometric_transformer(sd, cfg, rp, sp, rf, sf)
+    model = build_model(pkg, cfg, sd)
+    with torch.no_grad():
+        o0, o1 = model(rp.to(DEV), sp.to(DEV), rf.to(DEV), sf.to(DEV))
+    assert model.last_e_mode == 'scores'
+    assert tuple(o0.shape) == (1, n, cfg['output_dim']) and tuple(o1.shape) == (1, m, cfg['output_dim'])
+    r0, r1 = rel(o0, e0), rel(o1, e1)
+    print(f'n = {n}, m = {m}: {r0:.3e} {r1:.3e}')
+    assert r0 <= 1e-3 and r1 <= 1e-3
+
+
 def test_forward_only_guard_and_cpu_rejection(pkg, oracle):
     cfg = dict(pkg.synth.CONFIGS['modelnet'])
     model = pkg.GeometricTransformer(**cfg).to(DEV)
