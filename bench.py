@@ -932,7 +932,7 @@ def run_b200(args):
 
         # ---- bounded sweep points in the same process (driver-visible): north_star's size and KITTI ----
         if args.workload == '3dmatch_1024' and not args.no_sweep:
-            for wl, ssteps in (('3dmatch_4096', 5), ('kitti_2048', 10)):
+            for wl, ssteps in (('3dmatch_4096', 5), ('kitti_2048', 16)):
                 try:
                     s_shape, s_n, s_m, s_cfg, s_model = build(wl)
                     _, s_res = make_pairs(s_shape, s_n, s_m, 2, pkg.synth.SEED)
@@ -941,12 +941,14 @@ def run_b200(args):
                         for tag, e_mode, kernel in (('default', 'auto', 'cheb'), ('tensor_embedding', 'store', 'tensor')):
                             s_model.e_mode, s_model.embedding.embed_kernel = e_mode, kernel
                             s_model(*s_res[0])
-                            sf = InFlight(pkg, s_model, s_res[0], 1)
-                            s_ms, _ = timed_value(torch, sf, s_res, 2, ssteps, 3)
+                            s_inflight = inflight if max(s_n, s_m) <= 2048 else 1  # the rule of the main line
+                            sf = InFlight(pkg, s_model, s_res[0], s_inflight)
+                            s_ms, _ = timed_value(torch, sf, s_res, 2, ssteps, max(3, 2 * s_inflight))
                             del sf
                             torch.cuda.empty_cache()
                             val = ssteps / (s_ms * 1e-3)
-                            entry[tag] = {'value': val, 'unit': UNIT, 'ms_per_step': s_ms / ssteps, 'e_storage': s_model.last_e_mode}
+                            entry[tag] = {'value': val, 'unit': UNIT, 'ms_per_step': s_ms / ssteps, 'e_storage': s_model.last_e_mode,
+                                          'graph_instances_in_flight': s_inflight}
                             if tag == 'tensor_embedding':
                                 entry[tag]['pair_tflops_min'] = flops_pair(s_n, s_m, s_cfg) / 1e12
                                 entry[tag]['pair_tensor_frac'] = flops_pair(s_n, s_m, s_cfg) * val / 1e12 / peaks['tensor_sustained']

@@ -345,16 +345,20 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     const uint32_t pitch = ktot * 2 + 16;               // bytes: = 16 (mod 32), ldmatrix rows fall into distinct banks
     const uint32_t a_base = smem_u32(smem);
     const uint32_t buf_bytes = CHEB_TILE * pitch;
-    // scores mode, behind the two A tiles: partial[2][NCB][hp][CHEB_TILE] floats (every channel block's share of the
-    // scores) and qimg[2][NCB][32 lanes][8 words]: the tile row's folded query as mma B fragments, hi | lo halves
+    // scores mode, behind the two A tiles.
+    //   plain instances: partial[2][NCB][hp][136] floats (every channel block's share of the scores) and
+    //     qimg[2][NCB][32 lanes][8 words]: the tile row's folded query as mma B fragments, hi | lo halves
+    //   SPLIT instances (H <= 4; a consumer warp owns an m-tile and walks the channel blocks, see consume_rows):
+    //     gimg[KA][NCB][2][32 lanes][4 words]: the angle coefficients as B fragments, two n-tiles per 16 bytes;
+    //     qimg[2][NCB][32 lanes][4 words]: the folded query PACKED -- fragment columns 0-3 = the heads' hi halves,
+    //     columns 4-7 = their lo halves, so that one HMMA contracts both; uimg[2][KD][32 lanes][4 words]: u[h][m]
     const int hp = p.H <= 4 ? 4 : 8;
     float* const partial = reinterpret_cast<float*>(smem + 2 * buf_bytes);
-    constexpr int NSLOT = NCB + (SPLIT ? 1 : 0);  // SPLIT: one more block of partial scores, the distance term's
-    const int partial_floats = NSLOT * hp * CHEB_PSTRIDE;  // head stride 136 floats: the stores of heads 2q | 2q + 2 fall into different banks
-    const uint32_t qimg = a_base + 2 * buf_bytes + 2 * partial_floats * 4;
-    constexpr int QIMG_BYTES = NCB * 32 * 32;
-    // SPLIT: uimg[2][KD][32 lanes][4 words] behind it: the row's distance-score coefficients u[h][m] (see ChebArgs) as mma B
-    // fragments (k = coefficient, n = head), hi | lo halves
+    const int partial_floats = NCB * hp * CHEB_PSTRIDE;  // head stride 136 floats: the stores of heads 2q | 2q + 2 fall into different banks
+    constexpr int GIMG_BYTES = KA * NCB * 2 * 32 * 16;
+    const uint32_t gimg = a_base + 2 * buf_bytes;
+    const uint32_t qimg = SPLIT ? gimg + GIMG_BYTES : a_base + 2 * buf_bytes + 2 * partial_floats * 4;
+    constexpr int QIMG_BYTES = SPLIT ? NCB * 32 * 16 : NCB * 32 * 32;
     const uint32_t uimg = qimg + 2 * QIMG_BYTES;
     constexpr int UIMG_BYTES = (KD > 0 ? KD : 1) * 32 * 16;
     const long long tiles = p.tiles;
@@ -390,6 +394,14 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         const int bytes = 2 * QIMG_BYTES + (SPLIT ? 2 * UIMG_BYTES : 0);
         for (int e = tid; e < bytes / 16; e += CHEB_THREADS) sts_v4(qimg + e * 16, make_uint4(0u, 0u, 0u, 0u));
     }
+    if (SPLIT) {  // the angle coefficients, once per CTA: global image [kt][cb][t][lane] (8 bytes) -> [kt][cb][t / 2][lane] (16 bytes)
+        const uint2* src = reinterpret_cast<const uint2*>(p.coef);
+        for (int e = tid; e < KA * NCB * 4 * 32; e += CHEB_THREADS) {
+            const int l = e & 31, t = (e >> 5) & 3, kc = e >> 7;  // kc = kt * NCB + cb
+            const uint2 v = __ldg(src + e);
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(gimg + ((kc * 2 + (t >> 1)) * 32 + l) * 16 + (t & 1) * 8), "r"(v.x), "r"(v.y) : "memory");
+        }
+    }
     if (tid == 0) {
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(bar_full + 8 * b, CHEB_PRODUCER_WARPS * 32);
@@ -424,9 +436,15 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 for (int it = ptid; it < p.H * (C / 8); it += CHEB_PRODUCER_WARPS * 32) {
                     const int h = it / (C / 8), grp = it - h * (C / 8);  // grp = 4 cb + q
                     const float* src = p.qt + b * p.qsb + (long long)h * p.qsh + (long long)i * p.qsn + grp * 8;
-                    const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * 32;
-                    cp_async16(dst, src);
-                    cp_async16(dst + 16, src + 4);
+                    if (SPLIT) {  // hi slot = lane (g = h, q), lo slot = lane (g = h + 4, q): 16 bytes each
+                        const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * 16;
+                        cp_async16(dst, src);
+                        cp_async16(dst + 256, src + 4);
+                    } else {
+                        const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * 32;
+                        cp_async16(dst, src);
+                        cp_async16(dst + 16, src + 4);
+                    }
                 }
                 if (SPLIT && ptid < p.H * KD4) {
                     const int h = ptid / KD4, rem = ptid - h * KD4, kt = rem >> 2, qq = rem & 3;
@@ -478,15 +496,16 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 for (int it = ptid; it < p.H * (C / 8); it += CHEB_PRODUCER_WARPS * 32) {
                     const int h = it / (C / 8), grp = it - h * (C / 8);
-                    const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * 32;
-                    const uint4 ua = lds_v4(dst), va = lds_v4(dst + 16);
+                    const uint32_t dst = qimg + buf * QIMG_BYTES + ((grp >> 2) * 32 + h * 4 + (grp & 3)) * (SPLIT ? 16 : 32);
+                    const uint32_t dst_lo = dst + (SPLIT ? 256 : 16);
+                    const uint4 ua = lds_v4(dst), va = lds_v4(dst_lo);
                     uint4 hi, lo;
                     cheb_split(__uint_as_float(ua.x), __uint_as_float(ua.y), hi.x, lo.x);
                     cheb_split(__uint_as_float(ua.z), __uint_as_float(ua.w), hi.y, lo.y);
                     cheb_split(__uint_as_float(va.x), __uint_as_float(va.y), hi.z, lo.z);
                     cheb_split(__uint_as_float(va.z), __uint_as_float(va.w), hi.w, lo.w);
                     sts_v4(dst, hi);
-                    sts_v4(dst + 16, lo);
+                    sts_v4(dst_lo, lo);
                 }
                 if (SPLIT && ptid < p.H * KD4) {
                     // u[h][m] = sum_c qt[h][c] G_d[m][c] (it arrives with the query: the caller's projection produces it)
@@ -516,7 +535,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 const int h = task / (CHEB_TILE / 4), jl = (task - h * (CHEB_TILE / 4)) * 4;
                 float4 v = *reinterpret_cast<const float4*>(src + h * CHEB_PSTRIDE + jl);
 #pragma unroll
-                for (int w = 1; w < NSLOT; ++w) {
+                for (int w = 1; w < NCB; ++w) {
                     const float4 t = *reinterpret_cast<const float4*>(src + (w * hp + h) * CHEB_PSTRIDE + jl);
                     v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
                 }
@@ -544,7 +563,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 ptx::mbar_wait(bar_empty + 8 * buf, ((it >> 1) - 1) & 1, 0x100);
 #endif
 #if !defined(CHEB_ABL_NO_REDUCE) && !defined(CHEB_ABL_NO_PRODUCE)  // timing ablations (tools/build_variants.sh), never in the shipped library
-                if (SCORES) reduce(older, buf);
+                if (SCORES && !SPLIT) reduce(older, buf);  // SPLIT: the consumers write scores_p themselves
 #endif
             }
 #ifndef CHEB_ABL_NO_PRODUCE
@@ -566,7 +585,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
 #else
             ptx::mbar_wait(bar_empty + 8 * (it & 1), ((it - 2) >> 1) & 1, 0x101);
 #endif
-            if (SCORES) reduce(older, it & 1);
+            if (SCORES && !SPLIT) reduce(older, it & 1);
         }
         if (it >= 1) {
 #ifdef CHEB_NAMED_BARRIERS
@@ -574,7 +593,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
 #else
             ptx::mbar_wait(bar_empty + 8 * ((it + 1) & 1), ((it - 1) >> 1) & 1, 0x102);
 #endif
-            if (SCORES) reduce(old, (it + 1) & 1);
+            if (SCORES && !SPLIT) reduce(old, (it + 1) & 1);
         }
         if (clamped) *p.overflow = 1;
     } else {
@@ -585,17 +604,15 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         const uint2* const g_a = reinterpret_cast<const uint2*>(p.coef) + cb * 128 + lane;  // + (kt * NCB * 4 + t) * 32
         const uint2* const g_d = reinterpret_cast<const uint2*>(p.coef + p.d_set_offset[d_set]) + cb * 128 + lane;
         uint2 b_a[KA][4], b_d[FAST ? KD : 1][4];
-        if (FAST) {
+        if (FAST && !SPLIT) {
 #pragma unroll
             for (int kt = 0; kt < KA; ++kt)
 #pragma unroll
                 for (int t = 0; t < 4; ++t) b_a[kt][t] = __ldg(g_a + (kt * NCB * 4 + t) * 32);
-            if (!SPLIT) {
 #pragma unroll
-                for (int kt = 0; kt < KD; ++kt)
+            for (int kt = 0; kt < KD; ++kt)
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(g_d + (kt * NCB * 4 + t) * 32);
-            }
+                for (int t = 0; t < 4; ++t) b_d[kt][t] = __ldg(g_d + (kt * NCB * 4 + t) * 32);
         }
         // ldmatrix: lane l addresses row (l & 15) of the m-tile, columns 8 (l >> 4) ..; mma: g = lane / 4 is the fragment
         // row, q = lane % 4 the column pair
@@ -612,39 +629,8 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(qh.x), "=r"(qh.y), "=r"(qh.z), "=r"(qh.w) : "r"(src));
                 asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ql.x), "=r"(ql.y), "=r"(ql.z), "=r"(ql.w) : "r"(src + 16));
             }
-#ifndef CHEB_ABL_NO_TAIL
-            if (SPLIT) {
-                // the distance term's share of the scores, sum_m u[h][m] T_m(d_ij), is owed once per m-tile (not per
-                // channel block): warp w contracts it for m-tile w and leaves it in a block of partial scores of its own
-                // (slot NCB).  Issued FIRST: its dependent chain (ldmatrix -> 2 x KD HMMAs -> add -> store) then runs
-                // in the shadow of the expansions.  (Inside the m-tile loop the test `mt == warp` is if-converted into
-                // predicated-off HMMAs on every iteration, 2 of 10 issue slots per pair; as a read-modify-write of the
-                // warp's own partial after the loop it cost 1.2 clk per pair for 0.25 HMMA per pair.)
-                float sd[4], sd1[4];
-#pragma unroll
-                for (int kt = 0; kt < KD; ++kt) {
-                    uint32_t ad[4];
-                    ldsm4(ad, tile_addr + warp * 16 * pitch + (SL * KA + kt) * 32);
-                    const uint4 ub = lds_v4(uimg + buf * UIMG_BYTES + (kt * 32 + lane) * 16);
-                    if (kt == 0) {
-                        mma_new(sd, ad, make_uint2(ub.x, ub.y));
-                        mma_new(sd1, ad, make_uint2(ub.z, ub.w));
-                    } else {
-                        mma_acc(sd, ad, make_uint2(ub.x, ub.y));
-                        mma_acc(sd1, ad, make_uint2(ub.z, ub.w));
-                    }
-                }
-                if (2 * q < hp) {
-                    float* dst = partial + (buf * NSLOT + NCB) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + warp * 16 + g;
-                    dst[0] = sd[0] + sd1[0];
-                    dst[CHEB_PSTRIDE] = sd[1] + sd1[1];
-                    dst[8] = sd[2] + sd1[2];
-                    dst[CHEB_PSTRIDE + 8] = sd[3] + sd1[3];
-                }
-            }
-#endif
 #ifndef CHEB_NO_PIPELINE  // timing ablation switch (tools/build_variants.sh)
-            constexpr bool PIPELINED = FAST && SCORES;
+            constexpr bool PIPELINED = FAST && SCORES && !SPLIT;
 #else
             constexpr bool PIPELINED = false;
 #endif
@@ -687,7 +673,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                     return;
 #endif
                     if (2 * q < hp) {  // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
-                        float* dst = partial + (buf * NSLOT + cb) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + mt * 16 + g;
+                        float* dst = partial + (buf * NCB + cb) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + mt * 16 + g;
                         dst[0] = s0[0] + s1[0];
                         dst[CHEB_PSTRIDE] = s0[1] + s1[1];
                         dst[8] = s0[2] + s1[2];
@@ -824,7 +810,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                     mma_acc(sc, e0, make_uint2(ql.x, ql.y));
                     mma_acc(sc1, e1, make_uint2(ql.z, ql.w));
                     if (2 * q < hp) {  // thread (g, q): keys 16 mt + g and + 8, heads 2 q and 2 q + 1
-                        float* dst = partial + (buf * NSLOT + cb) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + mt * 16 + g;
+                        float* dst = partial + (buf * NCB + cb) * hp * CHEB_PSTRIDE + (2 * q) * CHEB_PSTRIDE + mt * 16 + g;
                         dst[0] = sc[0] + sc1[0];
                         dst[CHEB_PSTRIDE] = sc[1] + sc1[1];
                         dst[8] = sc[2] + sc1[2];
@@ -843,6 +829,96 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
             }  // !PIPELINED
         };
 
+
+        // SPLIT instances: warp w owns m-tile w of the tile (16 keys) and walks the channel blocks.  Its A fragments
+        // (the basis values) are loaded ONCE per tile instead of once per channel-block warp, the scores accumulate in
+        // registers across the channel blocks (two chains), so there are no partial scores, no reduction pass and no
+        // shared-memory round trip: the warp writes its 16 x H scores straight to scores_p.  Per channel block it reads
+        // 48 bytes per lane of B fragments (G and the packed query) from shared memory.  Per pair: 0.3 ldmatrix + 1.5
+        // LDS.128 instead of 2.5 ldmatrix + 2 STS + the reduction, and 7.25 HMMA instead of 8.25 (hi and lo halves of
+        // the query ride in one HMMA's eight columns).
+        auto consume_rows = [&](long long tile, int buf) {
+            const uint32_t tile_addr = a_base + buf * buf_bytes + ld_off + warp * 16 * pitch;
+            constexpr int SLR = SL > 0 ? SL : 1;  // (the generic instance, SL = 0, never calls this)
+            uint32_t a[SLR * KA][4], c[SLR][4][2];
+#pragma unroll
+            for (int x = 0; x < SL * KA; ++x) ldsm4(a[x], tile_addr + x * 32);
+            // the distance term u . t(d) first: its dependent chain runs in the shadow of the expansions
+            float sc[4] = {0.f, 0.f, 0.f, 0.f}, sc1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int kt = 0; kt < KD; ++kt) {
+                uint32_t ad[4];
+                ldsm4(ad, tile_addr + (SL * KA + kt) * 32);
+                const uint4 ub = lds_v4(uimg + buf * UIMG_BYTES + (kt * 32 + lane) * 16);
+                mma_acc(sc, ad, make_uint2(ub.x, ub.y));
+                mma_acc(sc1, ad, make_uint2(ub.z, ub.w));
+            }
+            uint4 gb[2][KA][2], qc[2];  // B fragments of channel block cb live in slot cb & 1
+            auto load_b = [&](int cb) {
+#pragma unroll
+                for (int kt = 0; kt < KA; ++kt)
+#pragma unroll
+                    for (int tp = 0; tp < 2; ++tp) gb[cb & 1][kt][tp] = lds_v4(gimg + (((kt * NCB + cb) * 2 + tp) * 32 + lane) * 16);
+                qc[cb & 1] = lds_v4(qimg + buf * QIMG_BYTES + (cb * 32 + lane) * 16);
+            };
+            auto expand = [&](int cb) {
+#pragma unroll
+                for (int sl = 0; sl < SL; ++sl)
+#pragma unroll
+                    for (int kt = 0; kt < KA; ++kt)
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            const uint4& w = gb[cb & 1][kt][t >> 1];
+                            const uint2 bb = (t & 1) ? make_uint2(w.z, w.w) : make_uint2(w.x, w.y);
+                            if (kt == 0) mma_h_new(c[sl][t], a[sl * KA + kt], bb);
+                            else mma_h_acc(c[sl][t], a[sl * KA + kt], bb);
+                        }
+            };
+            load_b(0);
+            expand(0);
+#pragma unroll
+            for (int cb = 0; cb < NCB; ++cb) {
+                if (cb + 1 < NCB) load_b(cb + 1);
+                uint32_t e0[4], e1[4];  // max over the slots (geotransformer.py:66) = the score contraction's A operand
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        uint32_t v = c[0][t][r];
+#pragma unroll
+                        for (int sl = 1; sl < SL; ++sl) v = hmax2_u(v, c[sl][t][r]);
+                        (t < 2 ? e0 : e1)[(t & 1) * 2 + r] = v;
+                    }
+                if (cb + 1 < NCB) expand(cb + 1);
+                mma_acc(sc, e0, make_uint2(qc[cb & 1].x, qc[cb & 1].y));
+                mma_acc(sc1, e1, make_uint2(qc[cb & 1].z, qc[cb & 1].w));
+            }
+            // fragment columns 0-3 hold the hi halves' share (and the distance term), columns 4-7 the lo halves': lanes
+            // q and q ^ 2 add up; lanes q < 2 then hold heads 2q, 2q + 1 of keys 16 w + g and + 8
+            float v[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                v[r] = sc[r] + sc1[r];
+                v[r] += __shfl_xor_sync(0xffffffffu, v[r], 2);
+            }
+            long long b;
+            int i, j0;
+            locate(tile, 0, b, i, j0);
+            const int j = j0 + warp * 16 + g;
+            if (q < 2) {
+                float* out = reinterpret_cast<float*>(p.out) + (((size_t)b * p.H + 2 * q) * p.n + i) * p.n + j;
+                const size_t hs = (size_t)p.n * p.n;
+                if (2 * q < p.H) {
+                    if (j < p.n) out[0] = v[0];
+                    if (j + 8 < p.n) out[8] = v[2];
+                }
+                if (2 * q + 1 < p.H) {
+                    if (j < p.n) out[hs] = v[1];
+                    if (j + 8 < p.n) out[hs + 8] = v[3];
+                }
+            }
+        };
+
         int it = 0;
         for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
@@ -853,7 +929,8 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
             ptx::mbar_wait(bar_full + 8 * buf, (it >> 1) & 1, 0x200);
 #endif
 #ifndef CHEB_ABL_NO_CONSUME
-            consume(tile, buf);
+            if constexpr (SPLIT) consume_rows(tile, buf);
+            else consume(tile, buf);
 #endif
 #ifdef CHEB_NAMED_BARRIERS
             __threadfence_block();
@@ -876,8 +953,8 @@ __global__ void __launch_bounds__(CHEB_THREADS, CHEB_MIN_CTAS) gse_embed_cheb_ke
     // fast instances: 3 angle slots (k = 3, 'max'), distance sets 1 (also serving set 0: its 32 coefficients cover the
     // shorter range too) and 2; everything else runs the generic instance
     const bool half_out = SCORES || !p.out_bf16;  // the fast instances accumulate in half
-    if (SCORES && p.u != nullptr && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3, SCORES>(p, 1, cheb_smem);
-    else if (SCORES && p.u != nullptr && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3, SCORES>(p, 2, cheb_smem);
+    if (SCORES && p.u != nullptr && p.H <= 4 && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3, SCORES>(p, 1, cheb_smem);
+    else if (SCORES && p.u != nullptr && p.H <= 4 && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3, SCORES>(p, 2, cheb_smem);
     else if (half_out && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3>(p, 1, cheb_smem);
     else if (half_out && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3>(p, 2, cheb_smem);
     else cheb_run<C, KA, 0, SCORES, 0>(p, d_set, cheb_smem);
