@@ -373,10 +373,12 @@ int geotx_gse_embed_cheb(const void* geometry, int B, int n, int k, int row_begi
  *   u (optional, else NULL): the DISTANCE SPLIT.  The distance term of E is linear in its Chebyshev basis, so its share
  *   of the scores is sum_m u[b,h,i,m] T_m(d_ij) with u[b,h,i,:] = G_d qt[b,h,i,:] -- a K_d-term product per (h,i,j)
  *   instead of a C-term one, and one third fewer MMAs in the kernel (the embedding contraction then covers the angle
- *   slots only).  u f32, element (b,h,i,m) at u[b*u_stride_b + h*u_stride_h + i*u_stride_n + m], 80 values per (b,h,i):
- *   the 32 coefficients of distance set 1 (G rows of `plain`), then the 48 of set 2; 8-byte aligned, even strides.  The
- *   caller obtains u from the same projection that yields qt (G_d folded into the weights).  Used by the fast instances
- *   (k = 3, 'max', clouds up to 64 index units); other shapes ignore it (distance term inside E as without u). */
+ *   slots only).  u f32, element (b,h,i,m) at u[b*u_stride_b + h*u_stride_h + i*u_stride_n + m]; per (b,h,i) the 32
+ *   coefficients of distance set 1 (G rows of `plain`), then the 48 of set 2 (80 values: max_d_set <= 2), then the 64 of
+ *   set 3 (144 values: REQUIRED when max_d_set >= 3); 8-byte aligned, even strides.  The caller obtains u from the same
+ *   projection that yields qt (G_d folded into the weights).  With u the kernel runs its split instances (H <= 4,
+ *   k = 3, 'max', clouds up to 93 index units: a consumer warp owns 16 keys, walks the channel blocks, keeps the scores
+ *   in registers and writes scores_p itself); other shapes ignore u (distance term inside E as without it). */
 int geotx_rpe_scores_cheb(const void* geometry, int B, int n, int k, int row_begin, int row_count, const void* coef,
                           int C, float angle_index_max, int ka_tiles, int max_d_set, float sigma_d, float factor_a,
                           int reduce_mean, const float* qt, int64_t qt_stride_b, int64_t qt_stride_h, int64_t qt_stride_n,

@@ -953,8 +953,12 @@ __global__ void __launch_bounds__(CHEB_THREADS, CHEB_MIN_CTAS) gse_embed_cheb_ke
     // fast instances: 3 angle slots (k = 3, 'max'), distance sets 1 (also serving set 0: its 32 coefficients cover the
     // shorter range too) and 2; everything else runs the generic instance
     const bool half_out = SCORES || !p.out_bf16;  // the fast instances accumulate in half
-    if (SCORES && p.u != nullptr && p.H <= 4 && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3, SCORES>(p, 1, cheb_smem);
-    else if (SCORES && p.u != nullptr && p.H <= 4 && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3, SCORES>(p, 2, cheb_smem);
+    // split instances (the distance term in coefficient space, a consumer warp per m-tile): distance sets <= 3; the host
+    // sized the shared memory for them under the same condition (cheb_launch)
+    const bool split = SCORES && p.u != nullptr && p.H <= 4 && p.slots == 3 && p.max_d_set >= 1;
+    if (split && d_set <= 1) cheb_run<C, KA, 2, SCORES, 3, SCORES>(p, 1, cheb_smem);
+    else if (split && d_set == 2) cheb_run<C, KA, 3, SCORES, 3, SCORES>(p, 2, cheb_smem);
+    else if (split && d_set == 3) cheb_run<C, KA, 4, SCORES, 3, SCORES>(p, 3, cheb_smem);
     else if (half_out && p.slots == 3 && d_set <= 1 && p.max_d_set >= 1) cheb_run<C, KA, 2, SCORES, 3>(p, 1, cheb_smem);
     else if (half_out && p.slots == 3 && d_set == 2) cheb_run<C, KA, 3, SCORES, 3>(p, 2, cheb_smem);
     else cheb_run<C, KA, 0, SCORES, 0>(p, d_set, cheb_smem);
@@ -1052,14 +1056,23 @@ static int cheb_launch(const char* what, const void* geometry, int B, int n, int
     p.usb = usb;
     p.ush = ush;
     p.usn = usn;
-    for (int s = 0; s < CHEB_NUM_D_SETS; ++s) p.u_offset[s] = s == 1 ? 0 : s == 2 ? 16 * cheb_kd_tiles(1) : 0;
+    for (int s = 0; s < CHEB_NUM_D_SETS; ++s)  // u holds sets 1, 2 (, 3) back to back; set 0 uses set 1's coefficients
+        p.u_offset[s] = s == 2 ? 16 * cheb_kd_tiles(1) : s == 3 ? 16 * (cheb_kd_tiles(1) + cheb_kd_tiles(2)) : 0;
     p.key_blocks = (n + CHEB_TILE - 1) / CHEB_TILE;
     p.tiles = scores ? (long long)B * row_count * p.key_blocks : (p.pairs_total + CHEB_TILE - 1) / CHEB_TILE;
     GEOTX_REQUIRE(p.tiles < 2147483647LL, "%s: too many tiles", what);
     const int ktot_max = p.slots * 16 * ka_tiles + 16 * cheb_kd_tiles(max_d_set);
     size_t smem = CHEB_BAR_BYTES + (size_t)2 * CHEB_TILE * (ktot_max * 2 + 16);
-    if (scores) smem += (size_t)2 * (C / 32 + (u ? 1 : 0)) * (H <= 4 ? 4 : 8) * CHEB_PSTRIDE * sizeof(float) + (size_t)2 * (C / 32) * 32 * 32 +
-                        (u ? (size_t)2 * 3 * 32 * 16 : 0);
+    if (scores) smem += (size_t)2 * (C / 32) * (H <= 4 ? 4 : 8) * CHEB_PSTRIDE * sizeof(float) + (size_t)2 * (C / 32) * 32 * 32;
+    if (scores && u && H <= 4 && p.slots == 3 && max_d_set >= 1) {
+        // the split instances' own layout (no partial scores): A tiles for the widest set they handle, the angle
+        // coefficients, the packed query image, u.  Sets 4 and 5 fall back to the generic instance and its layout.
+        const int split_set = max_d_set < 3 ? max_d_set : 3;
+        const size_t split = CHEB_BAR_BYTES + (size_t)2 * CHEB_TILE * ((3 * 16 * ka_tiles + 16 * cheb_kd_tiles(split_set)) * 2 + 16) +
+                             (size_t)ka_tiles * (C / 32) * 2 * 32 * 16 + (size_t)2 * (C / 32) * 32 * 16 +
+                             (size_t)2 * cheb_kd_tiles(split_set) * 32 * 16;
+        smem = max_d_set <= 3 ? split : (split > smem ? split : smem);
+    }
     GEOTX_REQUIRE(smem <= 220 * 1024, "%s: %zu B of shared memory (k=%d, max_d_set=%d) do not fit", what, smem, k, max_d_set);
     int dev = 0, sms = 0;
     int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");

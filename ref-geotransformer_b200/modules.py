@@ -318,10 +318,11 @@ class GeometricStructureEmbedding(nn.Module):
                                   self.sigma_d, self.factor_a, mean, out_dtype, row_begin, row_count, out)
 
     def distance_split_rows(self):
-        """(80, C) Chebyshev coefficients of the distance term (sets 1 and 2) for folding into the query projection."""
+        """(80 | 144, C) Chebyshev coefficients of the distance term (sets 1, 2 and, when `cheb_d_index_max` reaches beyond
+        64, 3) for folding into the query projection."""
         if self._cheb() is None:
             raise RuntimeError('the low-rank embedding kernel is not in use for these weights')
-        return self._cheb_cache.distance_split_rows()
+        return self._cheb_cache.distance_split_rows(ops.gse_cheb_max_d_set(self.cheb_d_index_max))
 
     def scores(self, geom, qt, row_begin=0, row_count=None, out=None, u=None):
         """K3r: scores_p[b,h,i,j] = qt[b,h,i,:] . E[b,i,j,:] (rpe_transformer.py:54-56 with proj_p folded into qt) without E
@@ -440,7 +441,7 @@ class RPEMultiHeadAttention(_FusedAttentionBase):
         share of the scores in coefficient space (K3r's distance split)."""
         ps = (self.proj_q.weight, self.proj_q.bias, self.proj_k.weight, self.proj_k.bias, self.proj_v.weight,
               self.proj_v.bias, self.proj_p.weight) + ((gd,) if gd is not None else ())
-        key = tuple((t.data_ptr(), t._version) for t in ps)
+        key = tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in ps)
         if getattr(self, '_fused_key', None) != key:
             if torch.cuda.is_current_stream_capturing():
                 raise RuntimeError('a weight changed since the fused projection was built; run one forward outside CUDA '
@@ -506,7 +507,7 @@ class MultiHeadAttention(_FusedAttentionBase):
     def fused_kv(self):
         """[W_k; W_v] as one (C -> 2C) projection of the memory tokens."""
         ps = (self.proj_k.weight, self.proj_k.bias, self.proj_v.weight, self.proj_v.bias)
-        key = tuple((t.data_ptr(), t._version) for t in ps)
+        key = tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in ps)
         if getattr(self, '_fused_key', None) != key:
             w = torch.cat([self.proj_k.weight.detach(), self.proj_v.weight.detach()]).contiguous()
             b = torch.cat([self.proj_k.bias.detach(), self.proj_v.bias.detach()]).contiguous()

@@ -551,10 +551,16 @@ class ChebCoefficients:
         self.buf, self.C, self.angle_index_max, self.ka_tiles = buf, C, angle_index_max, ka_tiles
         self.stats, self.overflow, self.plain, self._report = stats, overflow, plain, None
 
-    def distance_split_rows(self):
-        """(80, C) fp32: the unrounded Chebyshev coefficients G_d of distance sets 1 and 2, row m = coefficient m."""
+    @staticmethod
+    def split_columns(max_d_set):
+        """Columns of `u` K3r expects for a call prepared for distance sets up to `max_d_set`: sets 1 and 2 (32 + 48), and
+        set 3 (64 more) when the call may need it."""
+        return 80 if max_d_set <= 2 else 144
+
+    def distance_split_rows(self, max_d_set=2):
+        """(80 | 144, C) fp32: the unrounded Chebyshev coefficients G_d of distance sets 1, 2 (and 3), row m = coefficient m."""
         r0 = 16 * self.ka_tiles + 16  # behind the angle set and distance set 0
-        return self.plain[r0:r0 + self.SPLIT_COEFFICIENTS]
+        return self.plain[r0:r0 + self.split_columns(max_d_set)]
 
     def report(self):
         """One host read per weight set: [{'range', 'coefficients', 'max_error', 'max_abs_f', 'max_abs_g'}, ...] for the
@@ -632,8 +638,9 @@ def rpe_scores_cheb(geom, coef, qt, sigma_d, factor_a, reduce_mean=False, max_d_
     """K3r: rpe_transformer.py:54-56 (proj_p folded into qt, see rpe_scores) fused with the embedding
     (geotransformer.py:57-72): scores_p (B,H,n,n) fp32 straight from the geometry; E is rebuilt tile by tile in
     registers and never stored.  qt: logical (B,H,n,C) fp32 with a dense last dimension (any strides over b, h, i).
-    u (optional): logical (B,H,n,80) fp32, u[b,h,i,:] = coef.distance_split_rows() @ qt[b,h,i,:] (the distance split: the
-    distance term's share of the scores becomes a 32 / 48-term product instead of a C-term one)."""
+    u (optional): logical (B,H,n,M) fp32, u[b,h,i,:] = coef.distance_split_rows(max_d_set) @ qt[b,h,i,:], M = 80 for
+    max_d_set <= 2, else 144 (the distance split: the distance term's share of the scores becomes a 32 / 48 / 64-term
+    product instead of a C-term one; used for H <= 4, k = 3, 'max' and distance sets <= 3, ignored otherwise)."""
     row_begin, row_count = _slab(geom, row_begin, row_count)
     if not isinstance(qt, torch.Tensor) or not qt.is_cuda or qt.dtype != torch.float32 or qt.dim() != 4:
         raise RuntimeError('qt must be a 4-d float32 CUDA tensor (B,H,n,C)')
@@ -650,8 +657,8 @@ def rpe_scores_cheb(geom, coef, qt, sigma_d, factor_a, reduce_mean=False, max_d_
     us = (0, 0, 0)
     if u is not None:
         if not isinstance(u, torch.Tensor) or not u.is_cuda or u.dtype != torch.float32 or \
-                tuple(u.shape) != (B, H, n, coef.SPLIT_COEFFICIENTS) or u.stride(3) != 1:
-            raise RuntimeError(f'u must be a float32 CUDA tensor of logical shape {(B, H, n, coef.SPLIT_COEFFICIENTS)} with a '
+                tuple(u.shape) != (B, H, n, coef.split_columns(int(max_d_set))) or u.stride(3) != 1:
+            raise RuntimeError(f'u must be a float32 CUDA tensor of logical shape {(B, H, n, coef.split_columns(int(max_d_set)))} with a '
                                f'dense last dimension')
         us = (int(u.stride(0)), int(u.stride(1)), int(u.stride(2)))
     _abi.call('geotx_rpe_scores_cheb', _p(geom.buf), B, n, geom.k, row_begin, row_count, _p(coef.buf), C,

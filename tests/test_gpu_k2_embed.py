@@ -412,3 +412,30 @@ def test_cheb_scores_without_e(pkg, oracle, C, H, n, reduction, k):
     assert rel(got, exp) <= TOL_CHEB and rel(split, exp) <= TOL_CHEB
     assert torch.equal(part[:, :, 30:50], got[:, :, 30:50])
     assert float((part[:, :, :30] + 7.0).abs().max()) == 0.0 and float((part[:, :, 50:] + 7.0).abs().max()) == 0.0
+
+
+@pytest.mark.parametrize('C,sigma_d,want_set', [(256, 0.05, 3), (128, 0.05, 3), (256, 0.08, 2)])
+def test_cheb_split_scores_wide_clouds(pkg, oracle, C, sigma_d, want_set):
+    """The split instances of K3r on clouds wider than 64 index units: distance set 3 (64 coefficients, u of 144 columns:
+    sets 1, 2, 3) against the unsplit kernel and the oracle; set 2 through the same wide preparation."""
+    H, n, k = 4, 200, 3
+    cfg = dict(hidden_dim=C, sigma_d=sigma_d, sigma_a=10, angle_k=k, reduction_a='max')
+    sd = oracle.init_state_dict(8, 8, C, [], seed=5)
+    g = torch.Generator().manual_seed(C + want_set)
+    pts = torch.rand(1, n, 3, generator=g) * 2.5
+    qt = torch.randn(1, H, n, C, generator=g).to(DEV)
+    m = _gse(pkg, cfg, sd, 'auto', kernel='cheb')
+    m.cheb_d_index_max = 93.0
+    with torch.no_grad():
+        geom = m.geometry(pts.to(DEV))
+        got = m.scores(geom, qt)
+        gd = m.distance_split_rows()
+        assert tuple(gd.shape) == (144, C)
+        u = torch.einsum('bhnc,mc->bhnm', qt.double(), gd.double()).float().contiguous()
+        split = m.scores(geom, qt, u=u)
+    m.check_overflow()
+    d_max = float(torch.cdist(pts[0].double(), pts[0].double()).max()) / sigma_d
+    assert pkg.ops.gse_cheb_max_d_set(d_max) == want_set, d_max
+    exp = torch.einsum('bhic,bijc->bhij', qt.double().cpu(), oracle.gse(pts, sd, 'embedding.', sigma_d, 10, k, 'max').double()).float()
+    print(f'C={C} set {want_set}: split vs unsplit {rel(split, got):.3e}, split vs oracle {rel(split, exp):.3e}, unsplit vs oracle {rel(got, exp):.3e}')
+    assert rel(split, got) <= 1e-3 and rel(split, exp) <= TOL_CHEB and rel(got, exp) <= TOL_CHEB
