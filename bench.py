@@ -502,8 +502,11 @@ class InFlight:
             o = self.graphs[s % len(self.graphs)](*resident[s % n_pairs])
             if keep is not None:
                 n = o[0].shape[1]
-                keep[s, :n].copy_(o[0][0], non_blocking=True)
-                keep[s, n:].copy_(o[1][0], non_blocking=True)
+                dst = keep.local if hasattr(keep, 'pair_done') else keep
+                dst[s, :n].copy_(o[0][0], non_blocking=True)
+                dst[s, n:].copy_(o[1][0], non_blocking=True)
+                if hasattr(keep, 'pair_done'):
+                    keep.pair_done(s)  # pkg.dist.OverlappedGather: its chunk travels while later steps compute
             return o
         if self.streams[0] is None:
             for s in range(steps):
@@ -692,8 +695,10 @@ def run_b200(args):
 
     def k3r_flops(geom, coef, qt, *a, **kw):  # flops the kernel EXECUTES: expansions of the k angle slots, scores hi + lo,
         rows = geom.n                          # and the distance term (inside E, or split off in coefficient space)
-        dist = 2.0 * kd * 8 * 2 if kw.get('u') is not None else 2.0 * C * kd
-        return geom.B * rows * geom.n * (2.0 * C * (k * 16 * coef.ka_tiles) + dist + 2.0 * C * 8 * 2)
+        split = kw.get('u') is not None and H <= 4
+        dist = 2.0 * kd * 8 * 2 if split else 2.0 * C * kd
+        score = 2.0 * C * 8 * (1 if split else 2)  # split instances: hi and lo halves of the query share one MMA's 8 columns
+        return geom.B * rows * geom.n * (2.0 * C * (k * 16 * coef.ka_tiles) + dist + score)
 
     def embed_bytes(geom, out_dtype, row_begin=0, row_count=None, out=None, qt=None):
         rows = geom.n - row_begin if row_count is None else row_count
@@ -814,11 +819,16 @@ def run_b200(args):
 
         # ---- pass 2 (the timed region of `value`): the forward replayed as one CUDA graph per step ----
         fast = InFlight(pkg, model, resident[0], inflight)
-        keep = torch.empty(args.steps, n + m, cfg['output_dim'], device=dev) if world > 1 else None
+        # N > 1: the outputs of every step of every rank are gathered inside the timed region, in chunks of 4 steps on a
+        # communication stream behind the steps that produce them (pkg.dist.OverlappedGather)
+        shape_out = (n + m, cfg['output_dim'])
         if world > 1:  # warm-up gather: NCCL channel setup and buffer registration stay outside the timed region
-            pkg.dist.gather_pair_outputs(list(torch.zeros(args.steps, n + m, cfg['output_dim'], device=dev)),
-                                         args.steps * world)
+            warm = pkg.dist.OverlappedGather(args.steps * world, shape_out, dev)
+            fast.run(resident, n_pairs, args.steps, keep=warm)
+            warm.finish()
+            del warm
         last = fast.run(resident, n_pairs, max(args.warmup, 3, 2 * inflight))
+        keep = pkg.dist.OverlappedGather(args.steps * world, shape_out, dev) if world > 1 else None
         barrier()
         sampler = ClockSampler(local) if rank == 0 else None
         if sampler:
@@ -827,7 +837,7 @@ def run_b200(args):
         t_start.record()
         last = fast.run(resident, n_pairs, args.steps, keep=keep)
         if world > 1:  # the one collective of the job: every rank ends up with the features of all steps x ranks pairs
-            gathered = pkg.dist.gather_pair_outputs(list(keep), args.steps * world)
+            gathered = keep.finish()
         t_stop.record()
         barrier()
         clocks = sampler.stop() if sampler else None
@@ -839,12 +849,12 @@ def run_b200(args):
         if not big:
             try:
                 mine = pkg.dist.shard_pairs(CONFIGS4_PAIRS, rank, world)
-                keep4 = torch.empty(len(mine), n + m, cfg['output_dim'], device=dev)
+                keep4 = pkg.dist.OverlappedGather(CONFIGS4_PAIRS, shape_out, dev, chunk=8)
                 barrier()
                 c_start, c_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 c_start.record()
                 fast.run(resident, n_pairs, len(mine), keep=keep4)
-                all4 = pkg.dist.gather_pair_outputs(list(keep4), CONFIGS4_PAIRS)
+                all4 = keep4.finish()
                 c_stop.record()
                 barrier()
                 configs4 = {'ms': c_start.elapsed_time(c_stop), 'pairs': CONFIGS4_PAIRS, 'pairs_per_rank': len(mine),
@@ -982,8 +992,8 @@ def run_b200(args):
         dom = 'rpe_scores_cheb (K3r)'
         if dom in per_kernel:
             roofline = roof_tensor('gse_embed_cheb_kernel<SCORES> (geotx_rpe_scores_cheb, K3r)', per_kernel[dom], serial_ms(per_kernel), mma_peak,
-                                   f'executed: per (i,j) pair 2 C 16 k ka for the expansions of the {k} angle slots + 2 C 8 2 for the '
-                                   f'folded-query scores (hi + lo) + the distance term (distance set {d_set}: {kd} coefficients): '
+                                   f'executed: per (i,j) pair 2 C 16 k ka for the expansions of the {k} angle slots + 2 C 8 for the '
+                                   f'folded-query scores (hi | lo halves in the 8 columns of one MMA; 2 C 8 2 without the split) + the distance term (distance set {d_set}: {kd} coefficients): '
                                    f'2 {kd} 8 2 in coefficient space (distance split) or 2 C {kd} inside E')
             dtype = 'f16'
         elif 'rpe_scores (K3a)' in per_kernel:
@@ -1009,7 +1019,7 @@ def run_b200(args):
                 'embed_kernel': model.embedding.embed_kernel, 'dense_glue': os.environ.get('GEOTX_DENSE', 'own'),
                 'l2': f'inputs larger than L2: {n_pairs} distinct pairs ({n_pairs * pair_bytes / 1e6:.0f} MB of inputs) rotated over '
                       f'{inflight} graph instance(s); every step also streams {2 * Ls * n * n * H * 4 / 1e6:.0f} MB of score matrices',
-                'gather': f'all_gather of the outputs of every step of every rank inside the timed region ({gather_bytes / 1e6:.0f} MB), after one warm-up gather' if world > 1 else 'single GPU: nothing to gather'},
+                'gather': f'outputs of every step of every rank gathered inside the timed region ({gather_bytes / 1e6:.0f} MB): chunks of 4 steps on a communication stream behind the steps that produce them (dist.OverlappedGather), after one warm-up pass' if world > 1 else 'single GPU: nothing to gather'},
             'e2e': {'value': world * args.steps / (e2e_ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h,
                     'api': f'PipelinedGeometricTransformer.map over pinned host pairs, depth {depth}, wall clock'},

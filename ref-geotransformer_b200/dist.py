@@ -34,3 +34,64 @@ def gather_pair_outputs(local_outputs, num_pairs, group=None):
     # rank r, slot s  ->  pair s*world + r
     out = gathered.view(world, per, *shape).transpose(0, 1).reshape(world * per, *shape)
     return out[:num_pairs]
+
+
+class OverlappedGather:
+    """The same gather in chunks, overlapped with the computation that produces the pairs.
+
+    `local` (per, *shape) is filled pair by pair by the caller (slot s = the rank's s-th pair, shard_pairs order), in
+    slot order; after writing slot s on some stream the caller calls `pair_done(s)` under that stream.  Every `chunk`
+    pairs one all_gather of that chunk is enqueued on a communication stream behind the events of its pairs, so all
+    chunks but the last travel while later pairs are still being computed.  `finish()` makes the current stream wait
+    for the last chunk and returns the (num_pairs, *shape) tensor with pair p at index p (a view of the gather buffer,
+    which is laid out (slot, rank): no final reordering copy).
+    Works without torch.distributed (world 1: no communication) and with gloo (CPU tensors: synchronous)."""
+
+    def __init__(self, num_pairs, shape, device, dtype=torch.float32, chunk=4, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.per = pairs_per_rank(num_pairs, self.world)
+        self.num_pairs, self.chunk = num_pairs, max(1, int(chunk))
+        self.local = torch.zeros((self.per,) + tuple(shape), dtype=dtype, device=device)
+        # (per, world, *shape): slot s of rank r = pair s * world + r, i.e. flat index s * world + r
+        self.gathered = self.local.new_empty((self.per, self.world) + tuple(shape)) if self.world > 1 else None
+        self.cuda = self.local.is_cuda
+        self.comm = torch.cuda.Stream(device=device) if self.cuda and self.world > 1 else None
+        self._events, self._sent = {}, 0
+
+    def pair_done(self, slot):
+        """Slot `slot` of `local` has been written on the current stream (slots complete in order)."""
+        if self.world == 1:
+            return
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            self._events[slot] = ev
+        if slot + 1 - self._sent >= self.chunk:
+            self._send(self._sent, slot + 1)
+
+    def _send(self, lo, hi):
+        tail = tuple(self.local.shape[1:])
+        stage = self.local.new_empty((self.world * (hi - lo),) + tail)  # all_gather concatenates rank-major along dim 0
+        by_rank = stage.view((self.world, hi - lo) + tail)
+        if self.cuda:
+            with torch.cuda.stream(self.comm):
+                for s in range(lo, hi):
+                    self.comm.wait_event(self._events.pop(s))
+                dist.all_gather_into_tensor(stage, self.local[lo:hi], group=self.group)
+                self.gathered[lo:hi].copy_(by_rank.transpose(0, 1), non_blocking=True)
+            stage.record_stream(self.comm)
+        else:
+            dist.all_gather_into_tensor(stage, self.local[lo:hi].contiguous(), group=self.group)
+            self.gathered[lo:hi].copy_(by_rank.transpose(0, 1))
+        self._sent = hi
+
+    def finish(self):
+        if self.world == 1:
+            return self.local[:self.num_pairs]
+        if self._sent < self.per:
+            self._send(self._sent, self.per)
+        if self.cuda:
+            torch.cuda.current_stream(self.local.device).wait_stream(self.comm)
+        self._events, self._sent = {}, 0
+        return self.gathered.view((self.per * self.world,) + tuple(self.local.shape[1:]))[:self.num_pairs]

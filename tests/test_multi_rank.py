@@ -21,7 +21,15 @@ def _worker(rank, world, port, num_pairs, results):
     outs = [torch.full((3, 4), float(p)) + torch.arange(4.0) for p in mine]
     full = pkg.dist.gather_pair_outputs(outs, num_pairs)
     expect = torch.stack([torch.full((3, 4), float(p)) + torch.arange(4.0) for p in range(num_pairs)])
-    results[rank] = bool(torch.equal(full, expect)) and mine == list(range(rank, num_pairs, world))
+    # the chunked gather that overlaps with the computation (what bench.py times): same result, any chunk size
+    ok = True
+    for chunk in (1, 2, 4):
+        og = pkg.dist.OverlappedGather(num_pairs, (3, 4), torch.device('cpu'), chunk=chunk)
+        for slot, p in enumerate(mine):
+            og.local[slot] = torch.full((3, 4), float(p)) + torch.arange(4.0)
+            og.pair_done(slot)
+        ok = ok and bool(torch.equal(og.finish(), expect))
+    results[rank] = bool(torch.equal(full, expect)) and mine == list(range(rank, num_pairs, world)) and ok
     dist.barrier()
     dist.destroy_process_group()
 
@@ -48,3 +56,8 @@ def test_single_process_gather():
     outs = [torch.ones(2) * p for p in range(3)]
     assert torch.equal(pkg.dist.gather_pair_outputs(outs, 3), torch.stack(outs))
     assert pkg.dist.shard_pairs(7, 1, 4) == [1, 5]
+    og = pkg.dist.OverlappedGather(3, (2,), torch.device('cpu'), chunk=2)
+    for slot in range(3):
+        og.local[slot] = outs[slot]
+        og.pair_done(slot)
+    assert torch.equal(og.finish(), torch.stack(outs))
