@@ -490,6 +490,7 @@ class InFlight:
     def __init__(self, pkg, model, example, count):
         import torch
         self.torch = torch
+        self.joint = pkg.modules._joint_view
         self.graphs = [pkg.GraphedGeometricTransformer(model, *example) for _ in range(count)]
         self.streams = [torch.cuda.Stream() for _ in range(count)] if count > 1 else [None]
 
@@ -503,8 +504,12 @@ class InFlight:
             if keep is not None:
                 n = o[0].shape[1]
                 dst = keep.local if hasattr(keep, 'pair_done') else keep
-                dst[s, :n].copy_(o[0][0], non_blocking=True)
-                dst[s, n:].copy_(o[1][0], non_blocking=True)
+                both = self.joint(o[0], o[1])
+                if both is not None:  # the two outputs are slices of one (1, n+m, C) buffer: one copy
+                    dst[s].copy_(both[0], non_blocking=True)
+                else:
+                    dst[s, :n].copy_(o[0][0], non_blocking=True)
+                    dst[s, n:].copy_(o[1][0], non_blocking=True)
                 if hasattr(keep, 'pair_done'):
                     keep.pair_done(s)  # pkg.dist.OverlappedGather: its chunk travels while later steps compute
             return o
