@@ -14,21 +14,26 @@
 // relative to them, and is measured in fp64 when the coefficients are built), and any angle_k and both reductions are
 // covered ('mean' is linear: the slots' basis vectors are averaged before the contraction).
 //
-// The kernel: a CTA of 8 warps walks tiles of 128 consecutive (i,j) pairs.  Per tile
-//   produce  two threads per pair (in different warps) compute the pair's k+1 arguments (same arithmetic as get_embedding_indices,
-//            geotx_common.cuh), run the three-term recurrence T_{m+1} = 2t T_m - T_{m-1} in fp32 and store the basis
-//            values as IEEE half into a shared-memory A tile [128 pairs][16 (slots + distance tiles)] (double-buffered,
-//            row pitch = 16 (mod 32) bytes: conflict-free for ldmatrix);
-//   consume  warp w owns 32 output channels.  Its B operand (G for those channels, <= 40 registers) never leaves the
-//            register file.  Per 16 pairs: one ldmatrix.x4 + 4 mma.sync.m16n8k16 (f16 x f16 -> f32) per angle slot, a
-//            running max over the slots in registers (geotransformer.py:66), then the distance tiles accumulate ON TOP
-//            of that max (:70; the biases b_d + b_a ride in G_d[0], T_0 = 1), one convert, and each thread stores 16
-//            contiguous bytes of E per row (the channel <-> fragment-column assignment is chosen so that a thread's 8
-//            accumulator columns are 8 consecutive channels).
+// The kernel (one persistent kernel, two outputs: E for K2c, scores_p = qt . E for K3r, where E never leaves the
+// registers): a CTA of 12 warps walks tiles of 128 consecutive (i,j) pairs, two CTAs per SM, two tile buffers per CTA.
+//   4 producer warps (setmaxnreg 48), one thread per pair: the pair's k+1 arguments (the arithmetic of
+//            get_embedding_indices with fast reciprocal square roots and a minimax atan), the three-term recurrence
+//            T_{m+1} = 2t T_m - T_{m-1} in fp32, the basis values as IEEE half into a shared-memory A tile
+//            [128 pairs][16 (slots + distance tiles)] (row pitch = 16 (mod 32) bytes: conflict-free for ldmatrix);
+//            in the scores mode also the query row's folded query (and u) as ready-made mma B fragments, copied
+//            asynchronously first and converted in place last;
+//   8 consumer warps (setmaxnreg 96): nothing but ldmatrix / mma.sync.m16n8k16 (half accumulators) / max.f16x2 /
+//            the score contraction / stores.  The channel <-> fragment-column assignment is chosen so that a thread's 8
+//            accumulator columns are 8 consecutive channels: a 16-byte store of E per row and thread (K2c), or the A
+//            fragment of the score contraction as it stands (K3r).  Two layouts: the split instances of K3r give a
+//            warp one m-tile and let it walk the channel blocks (consume_rows); everything else gives a warp one
+//            channel block of all m-tiles with G in registers and partial scores in shared memory (consume).
+//   hand-over through four mbarriers (full / empty x 2 buffers); the consumer warps never wait for each other.
 // Nothing of size n x n x k x C exists; shared memory carries 160 B per pair instead of K2t's 5 KB of table reads and
 // the accumulators are never read back from TMEM (K2's epilogue moves 4 KB per pair at TMEM's 64 B/clk).
 // The distance range is not known on the host without a synchronisation: geotx_gse_knn leaves the largest squared
 // distance of the cloud behind the geometry scratch, and the kernel picks the coefficient set (K_d) from it.
+// Measurements, ablations and the history of the kernel: DESIGN.md 4.2, profiles/r02_k3r_ablations.txt.
 #include <cuda_fp16.h>
 #include "geotx_common.cuh"
 #include "host_util.h"
