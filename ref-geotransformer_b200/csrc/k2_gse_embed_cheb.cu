@@ -335,6 +335,28 @@ __device__ __forceinline__ void cheb_split(float x, float y, uint32_t& hi, uint3
 //               the tensor pipe never waits for a produce phase
 // Hand-over through named barriers (1, 2: tile buffer b is full; 3, 4: buffer b has been consumed), bar.arrive on the
 // signalling side, bar.sync on the waiting side.
+// Scores mode: a CTA's tiles blockIdx.x, blockIdx.x + gridDim.x, ... as (cloud b, query row i, key block kb), advanced
+// by additions (the two integer divisions of tile -> (b, i, kb) cost ~50 instructions per tile and thread otherwise).
+struct ChebTileWalk {
+    unsigned b, i, kb, kb_step, row_step, key_blocks, row_count;
+    __device__ __forceinline__ void start(const ChebArgs& p) {
+        key_blocks = (unsigned)p.key_blocks;
+        row_count = (unsigned)p.row_count;
+        const unsigned row = blockIdx.x / key_blocks;
+        kb = blockIdx.x - row * key_blocks;
+        b = row / row_count;
+        i = row - b * row_count;
+        row_step = gridDim.x / key_blocks;
+        kb_step = gridDim.x - row_step * key_blocks;
+    }
+    __device__ __forceinline__ void next() {
+        kb += kb_step;
+        i += row_step;
+        if (kb >= key_blocks) { kb -= key_blocks; ++i; }
+        while (i >= row_count) { i -= row_count; ++b; }
+    }
+};
+
 template <int C, int KA, int KD, bool SCORES, int SL, bool SPLIT = false>
 __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned char* smem) {
     constexpr bool FAST = KD > 0 && SL > 0;
@@ -424,10 +446,18 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         const float x_lim_d = cheb_range(d_set) * 1.0001f;
         bool clamped = false;
 
+        ChebTileWalk walk;
+        if (SCORES) walk.start(p);
         auto produce = [&](long long tile, int buf) {
             long long b;
             int i, j;
-            locate(tile, ptid, b, i, j);
+            if (SCORES) {
+                b = walk.b;
+                i = p.row_begin + (int)walk.i;
+                j = min((int)walk.kb * CHEB_TILE + ptid, p.n - 1);
+            } else {
+                locate(tile, ptid, b, i, j);
+            }
             const float4 pi = __ldg(p.pts4 + b * p.n + i), pj = __ldg(p.pts4 + b * p.n + j);
             const float4* refv_i = p.refv + (b * p.n + i) * p.k;
             const uint32_t row = a_base + buf * buf_bytes + ptid * pitch;
@@ -574,6 +604,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
 #ifndef CHEB_ABL_NO_PRODUCE
             produce(tile, buf);
 #endif
+            if (SCORES) walk.next();
 #ifdef CHEB_NAMED_BARRIERS
             __threadfence_block();
             cheb_bar_arrive(1 + buf);
@@ -842,6 +873,8 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         // 48 bytes per lane of B fragments (G and the packed query) from shared memory.  Per pair: 0.3 ldmatrix + 1.5
         // LDS.128 instead of 2.5 ldmatrix + 2 STS + the reduction, and 7.25 HMMA instead of 8.25 (hi and lo halves of
         // the query ride in one HMMA's eight columns).
+        ChebTileWalk cwalk;
+        if (SPLIT) cwalk.start(p);
         auto consume_rows = [&](long long tile, int buf) {
             const uint32_t tile_addr = a_base + buf * buf_bytes + ld_off + warp * 16 * pitch;
             constexpr int SLR = SL > 0 ? SL : 1;  // (the generic instance, SL = 0, never calls this)
@@ -906,10 +939,9 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
                 v[r] = sc[r] + sc1[r];
                 v[r] += __shfl_xor_sync(0xffffffffu, v[r], 2);
             }
-            long long b;
-            int i, j0;
-            locate(tile, 0, b, i, j0);
-            const int j = j0 + warp * 16 + g;
+            const long long b = cwalk.b;
+            const int i = p.row_begin + (int)cwalk.i;
+            const int j = (int)cwalk.kb * CHEB_TILE + warp * 16 + g;
             if (q < 2) {
                 float* out = reinterpret_cast<float*>(p.out) + (((size_t)b * p.H + 2 * q) * p.n + i) * p.n + j;
                 const size_t hs = (size_t)p.n * p.n;
@@ -927,6 +959,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         int it = 0;
         for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const int buf = it & 1;
+            if (SPLIT && it > 0) cwalk.next();
             // the producers have filled A[buf] (and the query image)
 #ifdef CHEB_NAMED_BARRIERS
             cheb_bar_sync(1 + buf);

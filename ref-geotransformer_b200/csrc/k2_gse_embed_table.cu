@@ -1,4 +1,5 @@
-// K2t (experimental, opt-in): GeometricStructureEmbedding by TABULATION instead of by contraction.
+// K2t (round 1's default embedding; since round 2 a variant, GEOTX_EMBED=table -- the default is the low-rank kernel
+// k2_gse_embed_cheb.cu): GeometricStructureEmbedding by TABULATION instead of by contraction.
 //
 // geotransformer.py:57-72 computes E[i,j,:] = proj_d(sinus(d_ij)) + max_k proj_a(sinus(a_ijk)).  Per output channel,
 // proj_x(sinus(x)) + bias is a function of ONE scalar x (positional_embedding.py:28-31 followed by a Linear):
@@ -6,8 +7,9 @@
 // smooth at the scale of one index unit (the highest frequency is 1 rad per unit).  K2 (k2_gse_embed.cu) spends
 // 2 C^2 (1+k) flop per pair on it on the tensor cores; here f_c is tabulated once per weight set (tables fa, fd:
 // rows x C halves, bias folded in) and interpolated out of shared memory: the angle term linearly on a fine grid
-// (step h_a = 1/16: two rows per slot, error <= h^2/8 max|f"| ~ 2e-4), the distance term, whose range is larger, by
-// cubic Lagrange interpolation on a coarse grid (step h_d = 1/4: four rows, error ~ 2e-5).  10 row reads (5 KB) and ~30
+// (the step is the caller's: modules.py ships h_a = 1/8; two rows per slot, error <= h^2/8 max|f"|, i.e. it grows with
+// the weights -- unlike the Chebyshev form, whose error is relative to them), the distance term, whose range is larger, by
+// cubic Lagrange interpolation on a coarse grid (shipped step h_d = 1/2: four rows).  10 row reads (5 KB) and ~30
 // packed half FMAs per pair for C = 256, k = 3: bound by the shared-memory pipe instead of the tensor pipe, and below
 // the fp16 rounding of the stored E (and of K2's bf16 operands).
 //

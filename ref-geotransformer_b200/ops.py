@@ -509,7 +509,7 @@ class EmbeddingTables:
 
 
 def gse_build_tables(div_term, w_d, b_d, w_a, b_a, factor_a, d_index_max, h_a=1.0 / 16, h_d=0.25):
-    """Tables for `gse_embed_table` (experimental): angle arguments lie in [0, pi * factor_a],
+    """Tables for `gse_embed_table` (K2t: round 1's default embedding, now the `GEOTX_EMBED=table` variant): angle arguments lie in [0, pi * factor_a],
     distance arguments in [0, d_index_max] are read from the table, larger ones are evaluated exactly (slowly)."""
     import math
     for name, t in (('div_term', div_term), ('w_d', w_d), ('b_d', b_d), ('w_a', w_a), ('b_a', b_a)):
@@ -529,7 +529,7 @@ def gse_build_tables(div_term, w_d, b_d, w_a, b_a, factor_a, d_index_max, h_a=1.
 
 
 def gse_embed_table(geom, tables, sigma_d, factor_a, row_begin=0, row_count=None, out=None):
-    """Tabulated embedding (experimental): -> E (B,row_count,n,C) f16; tables.overflow becomes 1 if an argument fell
+    """Tabulated embedding (K2t, variant): -> E (B,row_count,n,C) f16; tables.overflow becomes 1 if an argument fell
     outside a table.  geotransformer.py:57-72."""
     row_begin, row_count = _slab(geom, row_begin, row_count)
     if out is None:
