@@ -558,20 +558,21 @@ extern "C" int geotx_gse_pack_weights(const float* w_d, const float* b_d, const 
 template <int C>
 static int launch_k2(const K2Params& prm, cudaStream_t st) {
     using Cfg = K2Cfg<C>;
-    static int num_sms = 0;
     const void* kernels[4] = {(const void*)gse_embed_tc_kernel<C, false, false>, (const void*)gse_embed_tc_kernel<C, true, false>,
                               (const void*)gse_embed_tc_kernel<C, false, true>, (const void*)gse_embed_tc_kernel<C, true, true>};
-    if (num_sms == 0) {
-        int dev = 0;
-        int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
-        if (rc) return rc;
-        rc = check_cuda(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
-        if (rc) return rc;
-        for (int i = 0; i < 4 && !rc; ++i)
-            rc = check_cuda(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES),
-                            "cudaFuncSetAttribute(gse_embed_tc_kernel)");
-        if (rc) { num_sms = 0; return rc; }
+    // the opt-in to > 48 KB of dynamic shared memory belongs to the device's context: once per device, not per process
+    static bool opted_in[64] = {};
+    int dev = 0;
+    int rc0 = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+    if (rc0) return rc0;
+    if (dev < 0 || dev >= 64 || !opted_in[dev]) {
+        for (int i = 0; i < 4 && !rc0; ++i)
+            rc0 = check_cuda(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES),
+                             "cudaFuncSetAttribute(gse_embed_tc_kernel)");
+        if (rc0) return rc0;
+        if (dev >= 0 && dev < 64) opted_in[dev] = true;
     }
+    const int num_sms = sm_count();
     // persistent: one CTA pair per SM pair (cluster of 2, same TPC)
     int clusters = num_sms / 2;
     if (prm.num_tile_pairs < clusters) clusters = prm.num_tile_pairs;

@@ -240,21 +240,22 @@ extern "C" int geotx_rpe_scores(const float* qt, int64_t qt_stride_b, int64_t qt
     const bool fast = e_dtype != GEOTX_F32 && (C == 128 || C == 256) && H <= 8 &&
                       (((uintptr_t)E | (uintptr_t)qt) & 15) == 0 && qt_stride_b % 4 == 0 && qt_stride_h % 4 == 0 && qt_stride_n % 4 == 0;
     if (fast) {
-        static int num_sms = 0;
-        if (num_sms == 0) {
-            int dev = 0;
-            int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
-            if (rc) return rc;
-            rc = check_cuda(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev), "cudaDeviceGetAttribute");
-            if (rc) return rc;
+        // the opt-in to > 48 KB of dynamic shared memory belongs to the device's context: once per device, not per process
+        static bool opted_in[64] = {};
+        int dev = 0;
+        int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+        if (rc) return rc;
+        if (dev < 0 || dev >= 64 || !opted_in[dev]) {
             const void* kernels[4] = {(const void*)rpe_scores_tc_kernel<256, false>, (const void*)rpe_scores_tc_kernel<256, true>,
                                       (const void*)rpe_scores_tc_kernel<128, false>, (const void*)rpe_scores_tc_kernel<128, true>};
             for (int i = 0; i < 4 && !rc; ++i)
                 rc = check_cuda(cudaFuncSetAttribute(kernels[i], cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                      i < 2 ? K3ACfg<256>::SMEM_BYTES : K3ACfg<128>::SMEM_BYTES),
                                 "cudaFuncSetAttribute(rpe_scores_tc_kernel)");
-            if (rc) { num_sms = 0; return rc; }
+            if (rc) return rc;
+            if (dev >= 0 && dev < 64) opted_in[dev] = true;
         }
+        const int num_sms = sm_count();
         // persistent: one CTA per SM, every warp streams a contiguous range of 16-key chunks
         const int chunks_per_row = (m + K3A_KEYS - 1) / K3A_KEYS;
         const long long chunks_total = rows * chunks_per_row;

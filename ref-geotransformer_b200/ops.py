@@ -19,6 +19,7 @@ def _check(t, name, dtype=None, dims=None):
         raise RuntimeError(f'{name} must be a torch.Tensor')
     if not t.is_cuda:
         raise RuntimeError(f'{name} must be a CUDA tensor (ref-geotransformer_b200 has no CPU path)')
+    _same_device(t, name)
     if not t.is_contiguous():
         raise RuntimeError(f'{name} must be contiguous')
     if dtype is not None and t.dtype != dtype:
@@ -26,6 +27,15 @@ def _check(t, name, dtype=None, dims=None):
     if dims is not None and t.dim() != dims:
         raise RuntimeError(f'{name} must have {dims} dims, got shape {tuple(t.shape)}')
     return t
+
+
+def _same_device(t, name):
+    """The C ABI launches on the CURRENT device's current stream: a tensor that lives on another GPU would be addressed
+    from the wrong context.  Fail loudly; the caller wraps the call in `with torch.cuda.device(t.device):`."""
+    cur = torch.cuda.current_device()
+    if t.device.index is not None and t.device.index != cur:
+        raise RuntimeError(f'{name} lives on cuda:{t.device.index} but the current device is cuda:{cur}; call under '
+                           f'`with torch.cuda.device({name}.device):`')
 
 
 def _p(t):
@@ -695,6 +705,7 @@ def _rows2d(t, name, cols):
     """(…, cols) fp32 CUDA tensor whose leading dimensions flatten into equally strided rows -> (rows, row stride)."""
     if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.float32 or t.dim() < 1:
         raise RuntimeError(f'{name} must be a float32 CUDA tensor (ref-geotransformer_b200 has no CPU path)')
+    _same_device(t, name)
     if t.shape[-1] != cols or (cols > 1 and t.stride(-1) != 1):
         raise RuntimeError(f'{name}: last dimension must be dense and of size {cols}, got {tuple(t.shape)} strides {t.stride()}')
     rows = t.numel() // cols
