@@ -767,8 +767,11 @@ def run_b200(args):
                 'avg_launch_ms': ms, 'launches_per_step': d['launches_per_step'],
                 'share_of_step': sum(d['ms_per_launch']) / step_ms if step_ms else None}
 
+    # graph instances in flight (independent pairs overlap): 4 up to n = 2048, 2 at 4096 (measured 91.7 -> 96.5 pairs/s;
+    # 3: 96.2), 1 above
     many = max(n, m) <= 2048
-    inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '4'))) if many else 1
+    mid = not many and max(n, m) <= 4096
+    inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '4' if many else '2'))) if (many or mid) else 1
 
     def run_variant(tag, setup, undo, steps, want_kernels=True):
         """The same forward under another configuration: value (graph replay, CUDA events) + its kernel table."""
@@ -870,7 +873,7 @@ def run_b200(args):
 
         # ---- end to end: host (pinned) inputs -> device -> forward -> host outputs, every step, through the serving
         #      API (PipelinedGeometricTransformer: the upload of pair p+1 / download of pair p-1 overlap pair p) ----
-        depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', '5'))) if many else 2)
+        depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', '5' if many else '3'))) if (many or mid) else 2)
         del fast
         torch.cuda.empty_cache()
         pipe = pkg.PipelinedGeometricTransformer(model, *resident[0], depth=depth)
@@ -956,7 +959,7 @@ def run_b200(args):
                         for tag, e_mode, kernel in (('default', 'auto', 'cheb'), ('tensor_embedding', 'store', 'tensor')):
                             s_model.e_mode, s_model.embedding.embed_kernel = e_mode, kernel
                             s_model(*s_res[0])
-                            s_inflight = inflight if max(s_n, s_m) <= 2048 else 1  # the rule of the main line
+                            s_inflight = (4 if max(s_n, s_m) <= 2048 else 2 if max(s_n, s_m) <= 4096 else 1) if inflight > 1 else 1  # the rule of the main line
                             sf = InFlight(pkg, s_model, s_res[0], s_inflight)
                             s_ms, _ = timed_value(torch, sf, s_res, 2, ssteps, max(3, 2 * s_inflight))
                             del sf

@@ -423,9 +423,15 @@ static int launch_attention(AttParams prm, int B, int allow_split, cudaStream_t 
 
 template <int DH>
 static int launch_attention_shape(const AttParams& prm, int B, int allow_split, cudaStream_t st) {
-    // 128-query CTAs once they alone fill most of the GPU (B * H * n / 128 CTAs), 64-query CTAs for small clouds
+    // 64-query CTAs (4 warps, two per SM) up to n = 2048 at H = 4, 128-query CTAs (8 warps, one per SM) above.  Alone,
+    // the large shape is 2-8 % faster from n = 1024 up (K/V tiles fetched and converted once per 128 queries), but a
+    // serving job keeps several pairs in flight and then SM-time counts: with the small shape the step is 3.5 % / 2 %
+    // shorter at n = 1024 / 2048 (bench.py, 4 graph instances: 0.804 -> 0.777 ms, 2.718 -> 2.666 ms)
     const long long big = (long long)((prm.n + 127) / 128) * B * prm.H;
-    if (big >= 32) return launch_attention<DH, 8>(prm, B, allow_split, st);
+#ifndef ATT_BIG_THRESHOLD
+#define ATT_BIG_THRESHOLD 128  // (B H n / 128 query tiles) from which the 128-query CTA shape is used
+#endif
+    if (big >= ATT_BIG_THRESHOLD) return launch_attention<DH, 8>(prm, B, allow_split, st);
     return launch_attention<DH, 4>(prm, B, allow_split, st);
 }
 
