@@ -18,7 +18,10 @@ constexpr int DT_KC = 32;          // K per chunk (halves)
 constexpr int DT_ROW_BYTES = DT_KC * 2;
 constexpr int DT_WARPS = 8;        // compute warps: each owns 1/8 of the CTA's output columns
 constexpr int DT_THREADS = (DT_WARPS + 1) * 32;  // + the loader warp
-constexpr int DT_STAGES = 4;
+#ifndef DT_STAGES_N
+#define DT_STAGES_N 4  // ring depth (timing experiments: -DDT_STAGES_N=2|3)
+#endif
+constexpr int DT_STAGES = DT_STAGES_N;
 
 __device__ __forceinline__ void dt_ldsm4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"

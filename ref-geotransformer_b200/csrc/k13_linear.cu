@@ -60,14 +60,24 @@ __global__ void __launch_bounds__(DT_THREADS) linear_tile_kernel(const LinearArg
         return;
     }
 
-    // the tile's tokens -> half A operand, once
-    const int k4 = p.K / 4;
-    for (int e = tid; e < DT_BM * k4; e += DT_WARPS * 32) {
-        const int r = e / k4, c4 = e - r * k4;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row0 + r < p.T) v = __ldg(reinterpret_cast<const float4*>(p.x + (size_t)(row0 + r) * p.ld_x) + c4);
-        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * a_pitch + c4 * 8), "r"(dt_pack(v.x, v.y)),
-                     "r"(dt_pack(v.z, v.w)) : "memory");
+    // the tile's tokens -> half A operand, once.  Eight independent 16-byte loads in flight per thread: at K = 1024 the
+    // tile is 128 KB of fp32 from L2 / HBM, and a loop of dependent load -> convert -> store steps is latency-bound
+    const int k4 = p.K / 4, total4 = DT_BM * k4;
+    for (int e0 = tid; e0 < total4; e0 += 8 * DT_WARPS * 32) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int e = e0 + u * DT_WARPS * 32, r = e / k4, c4 = e - r * k4;
+            v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (e < total4 && row0 + r < p.T) v[u] = __ldg(reinterpret_cast<const float4*>(p.x + (size_t)(row0 + r) * p.ld_x) + c4);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int e = e0 + u * DT_WARPS * 32, r = e / k4, c4 = e - r * k4;
+            if (e < total4)
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * a_pitch + c4 * 8), "r"(dt_pack(v[u].x, v[u].y)),
+                             "r"(dt_pack(v[u].z, v[u].w)) : "memory");
+        }
     }
     dt_sync_compute();
 
