@@ -135,6 +135,9 @@ extern "C" int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, 
     // the widest column block that still gives every SM a CTA (x is converted once per CTA: wider is cheaper)
     int nt = 4;
     while (nt > 1 && row_tiles * ((N + 64 * nt - 1) / (64 * nt)) < sms) nt >>= 1;
+#ifdef LIN_SMALL_NT  // timing experiment: column-block width when no width fills the GPU
+    if (row_tiles * ((N + 63) / 64) < sms) nt = N % (64 * LIN_SMALL_NT) == 0 ? LIN_SMALL_NT : 1;
+#endif
 #ifdef DT_ONE_CTA
     const size_t smem = 120 * 1024;
 #else
