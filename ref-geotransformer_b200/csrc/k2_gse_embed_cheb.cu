@@ -203,6 +203,11 @@ __device__ __forceinline__ void cp_async8(uint32_t dst, const void* src) {
 // (bar.sync over all 384 threads; kept under CHEB_NAMED_BARRIERS for A/B timing) every tile restarted the CTA's eight
 // consumer warps in lockstep, and the tensor pipe idled through each ramp-down / ramp-up.
 constexpr int CHEB_BAR_BYTES = 64;
+#ifndef CHEB_SPLIT_BUFFERS
+#define CHEB_SPLIT_BUFFERS 3
+#endif
+// tile buffers of a split instance with kd distance k-tiles: 3 where two CTAs still fit an SM, else 2 (set 3: 240-byte rows)
+__host__ __device__ constexpr int cheb_split_buffers(int kd) { return kd >= 4 ? 2 : CHEB_SPLIT_BUFFERS; }
 constexpr int CHEB_PSTRIDE = CHEB_TILE + 8;  // floats between the heads of a channel block's partial scores
 __device__ __forceinline__ void cheb_bar_sync(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(CHEB_THREADS) : "memory"); }
 __device__ __forceinline__ void cheb_bar_arrive(int id) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "n"(CHEB_THREADS) : "memory"); }
@@ -364,7 +369,11 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     constexpr int NCB = C / 32;                          // 32-channel blocks
     constexpr int MT_PER_WARP = CHEB_MT * NCB / CHEB_CONSUMER_WARPS;  // 8 (C = 256) or 4 (C = 128)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t bar_full = smem_u32(smem), bar_empty = bar_full + 16;  // + 8 * buf
+    // tile buffers in flight: 2, or 3 for the split instances (their shared memory has the room since the partial scores
+    // went: the producers run up to two tiles ahead; measured: producers waited for `empty` a third of their time and the
+    // consumers for `full` 8 % of theirs with two buffers)
+    constexpr int NB = SPLIT ? cheb_split_buffers(KD) : 2;
+    const uint32_t bar_full = smem_u32(smem), bar_empty = bar_full + 8 * NB;  // + 8 * buf
     smem += CHEB_BAR_BYTES;
     const int slots = FAST ? SL : p.slots;
     const int kd_tiles = FAST ? KD : cheb_kd_tiles(d_set);
@@ -380,13 +389,13 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     //     qimg[2][NCB][32 lanes][4 words]: the folded query PACKED -- fragment columns 0-3 = the heads' hi halves,
     //     columns 4-7 = their lo halves, so that one HMMA contracts both; uimg[2][KD][32 lanes][4 words]: u[h][m]
     const int hp = p.H <= 4 ? 4 : 8;
-    float* const partial = reinterpret_cast<float*>(smem + 2 * buf_bytes);
+    float* const partial = reinterpret_cast<float*>(smem + NB * buf_bytes);
     const int partial_floats = NCB * hp * CHEB_PSTRIDE;  // head stride 136 floats: the stores of heads 2q | 2q + 2 fall into different banks
     constexpr int GIMG_BYTES = KA * NCB * 2 * 32 * 16;
-    const uint32_t gimg = a_base + 2 * buf_bytes;
-    const uint32_t qimg = SPLIT ? gimg + GIMG_BYTES : a_base + 2 * buf_bytes + 2 * partial_floats * 4;
+    const uint32_t gimg = a_base + NB * buf_bytes;
+    const uint32_t qimg = SPLIT ? gimg + GIMG_BYTES : a_base + NB * buf_bytes + 2 * partial_floats * 4;
     constexpr int QIMG_BYTES = SPLIT ? NCB * 32 * 16 : NCB * 32 * 32;
-    const uint32_t uimg = qimg + 2 * QIMG_BYTES;
+    const uint32_t uimg = qimg + NB * QIMG_BYTES;
     constexpr int UIMG_BYTES = (KD > 0 ? KD : 1) * 32 * 16;
     const long long tiles = p.tiles;
     const long long per_b = (long long)p.row_count * p.n;
@@ -418,7 +427,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
     };
 
     if (SCORES) {  // fragment lanes of heads >= H read zeros
-        const int bytes = 2 * QIMG_BYTES + (SPLIT ? 2 * UIMG_BYTES : 0);
+        const int bytes = NB * QIMG_BYTES + (SPLIT ? NB * UIMG_BYTES : 0);
         for (int e = tid; e < bytes / 16; e += CHEB_THREADS) sts_v4(qimg + e * 16, make_uint4(0u, 0u, 0u, 0u));
     }
     if (SPLIT) {  // the angle coefficients, once per CTA: global image [kt][cb][t][lane] (8 bytes) -> [kt][cb][t / 2][lane] (16 bytes)
@@ -430,7 +439,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         }
     }
     if (tid == 0) {
-        for (int b = 0; b < 2; ++b) {
+        for (int b = 0; b < NB; ++b) {
             ptx::mbar_init(bar_full + 8 * b, CHEB_PRODUCER_WARPS * 32);
             ptx::mbar_init(bar_empty + 8 * b, CHEB_CONSUMER_WARPS);
         }
@@ -589,13 +598,13 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
         int it = 0;
         long long tile = blockIdx.x, older = 0, old = 0;  // the tiles of the two previous iterations
         for (; tile < tiles; tile += gridDim.x, ++it) {
-            const int buf = it & 1;
-            if (it >= 2) {
-                // the consumers are done with tile it - 2: A[buf] is free, partial[buf] complete
+            const int buf = it % NB;
+            if (it >= NB) {
+                // the consumers are done with tile it - NB: A[buf] is free, partial[buf] complete
 #ifdef CHEB_NAMED_BARRIERS
                 cheb_bar_sync(3 + buf);
 #else
-                ptx::mbar_wait(bar_empty + 8 * buf, ((it >> 1) - 1) & 1, 0x100);
+                ptx::mbar_wait(bar_empty + 8 * buf, ((it / NB) - 1) & 1, 0x100);
 #endif
 #if !defined(CHEB_ABL_NO_REDUCE) && !defined(CHEB_ABL_NO_PRODUCE)  // timing ablations (tools/build_variants.sh), never in the shipped library
                 if (SCORES && !SPLIT) reduce(older, buf);  // SPLIT: the consumers write scores_p themselves
@@ -614,8 +623,8 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
             older = old;
             old = tile;
         }
-        // drain: the last two tiles' scores
-        if (it >= 2) {
+        // drain: the last two tiles' scores (plain instances: NB = 2; the split instances have nothing left to do)
+        if (!SPLIT && it >= 2) {
 #ifdef CHEB_NAMED_BARRIERS
             cheb_bar_sync(3 + (it & 1));
 #else
@@ -623,7 +632,7 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
 #endif
             if (SCORES && !SPLIT) reduce(older, it & 1);
         }
-        if (it >= 1) {
+        if (!SPLIT && it >= 1) {
 #ifdef CHEB_NAMED_BARRIERS
             cheb_bar_sync(3 + ((it + 1) & 1));
 #else
@@ -958,13 +967,13 @@ __device__ __forceinline__ void cheb_run(const ChebArgs& p, int d_set, unsigned 
 
         int it = 0;
         for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
-            const int buf = it & 1;
+            const int buf = it % NB;
             if (SPLIT && it > 0) cwalk.next();
             // the producers have filled A[buf] (and the query image)
 #ifdef CHEB_NAMED_BARRIERS
             cheb_bar_sync(1 + buf);
 #else
-            ptx::mbar_wait(bar_full + 8 * buf, (it >> 1) & 1, 0x200);
+            ptx::mbar_wait(bar_full + 8 * buf, (it / NB) & 1, 0x200);
 #endif
 #ifndef CHEB_ABL_NO_CONSUME
             if constexpr (SPLIT) consume_rows(tile, buf);
@@ -1106,9 +1115,13 @@ static int cheb_launch(const char* what, const void* geometry, int B, int n, int
         // the split instances' own layout (no partial scores): A tiles for the widest set they handle, the angle
         // coefficients, the packed query image, u.  Sets 4 and 5 fall back to the generic instance and its layout.
         const int split_set = max_d_set < 3 ? max_d_set : 3;
-        const size_t split = CHEB_BAR_BYTES + (size_t)2 * CHEB_TILE * ((3 * 16 * ka_tiles + 16 * cheb_kd_tiles(split_set)) * 2 + 16) +
-                             (size_t)ka_tiles * (C / 32) * 2 * 32 * 16 + (size_t)2 * (C / 32) * 32 * 16 +
-                             (size_t)2 * cheb_kd_tiles(split_set) * 32 * 16;
+        size_t split = 0;  // the largest layout among the instances this call may dispatch to (sets 1 .. split_set)
+        for (int s = 1; s <= split_set; ++s) {
+            const size_t kd = cheb_kd_tiles(s), nb = cheb_split_buffers((int)kd);
+            const size_t need = CHEB_BAR_BYTES + nb * CHEB_TILE * ((3 * 16 * ka_tiles + 16 * kd) * 2 + 16) +
+                                (size_t)ka_tiles * (C / 32) * 2 * 32 * 16 + nb * (C / 32) * 32 * 16 + nb * kd * 32 * 16;
+            if (need > split) split = need;
+        }
         smem = max_d_set <= 3 ? split : (split > smem ? split : smem);
     }
     GEOTX_REQUIRE(smem <= 220 * 1024, "%s: %zu B of shared memory (k=%d, max_d_set=%d) do not fit", what, smem, k, max_d_set);
