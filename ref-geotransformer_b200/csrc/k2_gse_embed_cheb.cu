@@ -15,7 +15,7 @@
 // covered ('mean' is linear: the slots' basis vectors are averaged before the contraction).
 //
 // The kernel (one persistent kernel, two outputs: E for K2c, scores_p = qt . E for K3r, where E never leaves the
-// registers): a CTA of 12 warps walks tiles of 128 consecutive (i,j) pairs, two CTAs per SM, two tile buffers per CTA.
+// registers): a CTA of 12 warps walks tiles of 128 consecutive (i,j) pairs, two CTAs per SM, two or three tile buffers per CTA.
 //   4 producer warps (setmaxnreg 48), one thread per pair: the pair's k+1 arguments (the arithmetic of
 //            get_embedding_indices with fast reciprocal square roots and a minimax atan), the three-term recurrence
 //            T_{m+1} = 2t T_m - T_{m-1} in fp32, the basis values as IEEE half into a shared-memory A tile
