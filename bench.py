@@ -831,12 +831,12 @@ def run_b200(args):
         # communication stream behind the steps that produce them (pkg.dist.OverlappedGather)
         shape_out = (n + m, cfg['output_dim'])
         if world > 1:  # warm-up gather: NCCL channel setup and buffer registration stay outside the timed region
-            warm = pkg.dist.OverlappedGather(args.steps * world, shape_out, dev)
+            warm = pkg.dist.make_gather(args.steps * world, shape_out, dev)
             fast.run(resident, n_pairs, args.steps, keep=warm)
             warm.finish()
             del warm
         last = fast.run(resident, n_pairs, max(args.warmup, 3, 2 * inflight))
-        keep = pkg.dist.OverlappedGather(args.steps * world, shape_out, dev) if world > 1 else None
+        keep = pkg.dist.make_gather(args.steps * world, shape_out, dev) if world > 1 else None
         barrier()
         sampler = ClockSampler(local) if rank == 0 else None
         if sampler:
@@ -857,7 +857,7 @@ def run_b200(args):
         if not big:
             try:
                 mine = pkg.dist.shard_pairs(CONFIGS4_PAIRS, rank, world)
-                keep4 = pkg.dist.OverlappedGather(CONFIGS4_PAIRS, shape_out, dev, chunk=8)
+                keep4 = pkg.dist.make_gather(CONFIGS4_PAIRS, shape_out, dev, chunk=8)
                 barrier()
                 c_start, c_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 c_start.record()
@@ -1027,7 +1027,7 @@ def run_b200(args):
                 'embed_kernel': model.embedding.embed_kernel, 'dense_glue': os.environ.get('GEOTX_DENSE', 'own'),
                 'l2': f'inputs larger than L2: {n_pairs} distinct pairs ({n_pairs * pair_bytes / 1e6:.0f} MB of inputs) rotated over '
                       f'{inflight} graph instance(s); every step also streams {2 * Ls * n * n * H * 4 / 1e6:.0f} MB of score matrices',
-                'gather': f'outputs of every step of every rank gathered inside the timed region ({gather_bytes / 1e6:.0f} MB): chunks of 4 steps on a communication stream behind the steps that produce them (dist.OverlappedGather), after one warm-up pass' if world > 1 else 'single GPU: nothing to gather'},
+                'gather': f'outputs of every step of every rank gathered inside the timed region ({gather_bytes / 1e6:.0f} MB): chunks of 4 steps on a communication stream behind the steps that produce them ({type(keep).__name__}: ' + ('copy-engine writes into the peers\' buffers mapped through CUDA IPC, no collective kernel' if type(keep).__name__ == 'PeerGather' else 'NCCL all_gather per chunk') + '), after one warm-up pass' if world > 1 else 'single GPU: nothing to gather'},
             'e2e': {'value': world * args.steps / (e2e_ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h,
                     'api': f'PipelinedGeometricTransformer.map over pinned host pairs, depth {depth}, wall clock'},

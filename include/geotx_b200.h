@@ -39,6 +39,10 @@ extern "C" {
 
 const char* geotx_last_error(void);
 int geotx_abi_version(void);
+/* No reference counterpart: an asynchronous device-to-device copy (copy engines, no kernel) between two pointers valid in
+ * this process, local or peer memory mapped through CUDA IPC.  The multi-GPU gather of the pair outputs
+ * (dist.PeerGather) moves its chunks with it, so that no collective kernel competes with the path's kernels for SMs. */
+int geotx_copy_async(void* dst, const void* src, int64_t bytes, void* stream);
 
 /* Bytes of caller-provided scratch needed by geotx_gse_knn for B clouds of n points and k neighbours
  * (packed float4 points + k reference vectors per point).  The scratch is an OUTPUT of geotx_gse_knn and an

@@ -18,6 +18,7 @@ _i64 = ctypes.c_int64
 SIGNATURES = {
     'geotx_last_error': (ctypes.c_char_p, []),
     'geotx_abi_version': (_i, []),
+    'geotx_copy_async': (_i, [_p, _p, _i64, _p]),
     'geotx_gse_geometry_bytes': (_i64, [_i, _i, _i]),
     'geotx_gse_knn': (_i, [_p, _i, _i, _i, _p, _p, _p]),
     'geotx_gse_indices': (_i, [_p, _i, _i, _i, _f, _f, _p, _p, _p]),
@@ -71,7 +72,8 @@ GEOTX_BF16 = 1
 GEOTX_F16 = 2
 
 # kernels each entry point enqueues (bench.py's gpu_launches is counted from this)
-KERNELS_PER_CALL = {'geotx_gse_knn': 2,  # pack_points + knn
+KERNELS_PER_CALL = {'geotx_copy_async': 0,  # copy engines, no kernel
+                    'geotx_gse_knn': 2,  # pack_points + knn
                     'geotx_superpoint_matching': 10,  # prepare, scores, sums, 6 select passes, collect
                     'geotx_point_to_node_partition': 4,  # assign, offsets, scatter, select
                     'geotx_point_to_node_partition_static': 4,

@@ -2,6 +2,8 @@
 collective: pair p runs on rank p mod W with a full weight replica, and the per-pair outputs are gathered once
 at the end (NCCL all_gather over NVLink on GPUs; gloo in the CPU tests).  The reference itself runs batch size 1
 per GPU under DDP (/root/reference/geotransformer/engine/base_trainer.py:66-72,190-198)."""
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -77,7 +79,9 @@ class OverlappedGather:
         if self.cuda:
             with torch.cuda.stream(self.comm):
                 for s in range(lo, hi):
-                    self.comm.wait_event(self._events.pop(s))
+                    ev = self._events.pop(s, None)  # a rank that owns one pair fewer has no event for the padding slot
+                    if ev is not None:
+                        self.comm.wait_event(ev)
                 dist.all_gather_into_tensor(stage, self.local[lo:hi], group=self.group)
                 self.gathered[lo:hi].copy_(by_rank.transpose(0, 1), non_blocking=True)
             stage.record_stream(self.comm)
@@ -95,3 +99,84 @@ class OverlappedGather:
             torch.cuda.current_stream(self.local.device).wait_stream(self.comm)
         self._events, self._sent = {}, 0
         return self.gathered.view((self.per * self.world,) + tuple(self.local.shape[1:]))[:self.num_pairs]
+
+
+class PeerGather(OverlappedGather):
+    """The chunked gather without a collective kernel: every rank maps the other ranks' gather buffers through CUDA IPC
+    (one node, NVLink / NVSwitch peer access) and WRITES its chunk into each of them with copy-engine copies
+    (geotx_copy_async) on a communication stream, behind the events of the pairs of the chunk.  No NCCL kernel sits on
+    SMs while pairs are being computed.  OPT-IN (GEOTX_GATHER=peer): correct (tools/peer_gather_check.py) but slower than
+    the NCCL chunks as issued from Python today, see make_gather.  One barrier at the end (a 4-byte all_reduce on
+    the communication stream of every rank) tells each rank that all peers' copies into its buffer have completed.
+    CUDA tensors, world > 1, all ranks on one node; `make_gather` falls back to OverlappedGather otherwise."""
+
+    def __init__(self, num_pairs, shape, device, dtype=torch.float32, chunk=4, group=None):
+        super().__init__(num_pairs, shape, device, dtype=dtype, chunk=chunk, group=group)
+        if not (self.cuda and self.world > 1):
+            raise RuntimeError('PeerGather needs CUDA tensors and more than one rank')
+        from . import _abi
+        self._abi = _abi
+        self.rank = dist.get_rank(group)
+        st = self.gathered.untyped_storage()
+        mine = (st._share_cuda_(), self.gathered.storage_offset())
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=group)
+        self.peers, self._keep = [], []
+        for r, (handle, offset) in enumerate(everyone):
+            if r == self.rank:
+                self.peers.append(self.gathered)
+                continue
+            storage = torch.UntypedStorage._new_shared_cuda(*handle)
+            t = torch.empty(0, dtype=dtype, device=storage.device).set_(storage, offset, self.gathered.shape,
+                                                                          self.gathered.stride())
+            self._keep.append(storage)
+            self.peers.append(t)
+        self.slot_bytes = self.local[0].numel() * self.local.element_size()
+        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def _send(self, lo, hi):
+        import ctypes
+        with torch.cuda.stream(self.comm):
+            for s in range(lo, hi):
+                ev = self._events.pop(s, None)
+                if ev is not None:
+                    self.comm.wait_event(ev)
+            stream = ctypes.c_void_p(self.comm.cuda_stream)
+            for r in range(self.world):  # slot s of this rank -> gathered[s, rank] of rank r: one contiguous block each
+                dst = self.peers[(self.rank + r) % self.world]  # start with the own buffer, then spread over the peers
+                for s in range(lo, hi):
+                    self._abi.call('geotx_copy_async', ctypes.c_void_p(dst[s, self.rank].data_ptr()),
+                                   ctypes.c_void_p(self.local[s].data_ptr()), self.slot_bytes, stream)
+        self._sent = hi
+
+    def finish(self):
+        if self._sent < self.per:
+            self._send(self._sent, self.per)
+        with torch.cuda.stream(self.comm):  # all ranks' copy streams meet here: every peer's copies into MY buffer are done
+            dist.all_reduce(self._flag, group=self.group)
+        torch.cuda.current_stream(self.local.device).wait_stream(self.comm)
+        self._events, self._sent = {}, 0
+        return self.gathered.view((self.per * self.world,) + tuple(self.local.shape[1:]))[:self.num_pairs]
+
+
+def make_gather(num_pairs, shape, device, dtype=torch.float32, chunk=4, group=None):
+    """OverlappedGather (NCCL all_gather per chunk: the default), or with GEOTX_GATHER=peer PeerGather where it applies
+    (CUDA, several ranks, peer mapping succeeds on EVERY rank).  Measured, 3DMatch 1024, 20 steps: 2 GPUs 2447 (NCCL) /
+    2413 (peer) pairs/s, 8 GPUs 9403 / 5011: the copy-engine version issues world x chunk copies per chunk from the
+    Python thread that also launches the steps, and loses more there than the collective kernel costs on the SMs."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world > 1 and torch.device(device).type == 'cuda' and os.environ.get('GEOTX_GATHER', 'nccl') == 'peer':
+        g, ok = None, 1
+        try:
+            g = PeerGather(num_pairs, shape, device, dtype=dtype, chunk=chunk, group=group)
+        except Exception as exc:  # no IPC (containers without /dev/shm, several nodes ...): say so once, use NCCL
+            ok = 0
+            if dist.get_rank(group) == 0:
+                import warnings
+                warnings.warn(f'ref-geotransformer_b200: peer-memory gather unavailable ({type(exc).__name__}: {exc}); '
+                              'using NCCL all_gather chunks')
+        flag = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 1:
+            return g
+    return OverlappedGather(num_pairs, shape, device, dtype=dtype, chunk=chunk, group=group)
