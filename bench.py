@@ -830,21 +830,24 @@ def run_b200(args):
         # N > 1: the outputs of every step of every rank are gathered inside the timed region, in chunks of 4 steps on a
         # communication stream behind the steps that produce them (pkg.dist.OverlappedGather)
         shape_out = (n + m, cfg['output_dim'])
+        gather_chunk = max(1, int(os.environ.get('GEOTX_GATHER_CHUNK', '4')))
         if world > 1:  # warm-up gather: NCCL channel setup and buffer registration stay outside the timed region
-            warm = pkg.dist.make_gather(args.steps * world, shape_out, dev)
+            warm = pkg.dist.make_gather(args.steps * world, shape_out, dev, chunk=gather_chunk)
             fast.run(resident, n_pairs, args.steps, keep=warm)
             warm.finish()
             del warm
         last = fast.run(resident, n_pairs, max(args.warmup, 3, 2 * inflight))
-        keep = pkg.dist.make_gather(args.steps * world, shape_out, dev) if world > 1 else None
-        barrier()
+        keep = pkg.dist.make_gather(args.steps * world, shape_out, dev, chunk=gather_chunk) if ((world > 1 and os.environ.get('GEOTX_KEEP') != '0') or os.environ.get('GEOTX_KEEP') == '1') else None
+        # the clock sampler (rank 0 spawns nvidia-smi) starts BEFORE the barrier: started after it, rank 0 entered the timed
+        # region ~0.7 ms late, and with a gather at the end every other rank's time included that wait
         sampler = ClockSampler(local) if rank == 0 else None
         if sampler:
             sampler.start()
         t_start, t_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
         t_start.record()
         last = fast.run(resident, n_pairs, args.steps, keep=keep)
-        if world > 1:  # the one collective of the job: every rank ends up with the features of all steps x ranks pairs
+        if keep is not None:  # the one collective of the job: every rank ends up with the features of all steps x ranks pairs
             gathered = keep.finish()
         t_stop.record()
         barrier()
