@@ -115,6 +115,13 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
+    def wait_ready(self, timeout=5.0):
+        """Blocks until nvidia-smi has printed its first sample: its start-up (fork, NVML initialisation: tens of ms, and it
+        takes driver locks) must be over before the timed region begins."""
+        t0 = time.time()
+        while self.proc is not None and not self.lines and time.time() - t0 < timeout:
+            time.sleep(0.01)
+
     def stop(self):
         if self.proc is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
@@ -838,11 +845,13 @@ def run_b200(args):
             del warm
         last = fast.run(resident, n_pairs, max(args.warmup, 3, 2 * inflight))
         keep = pkg.dist.make_gather(args.steps * world, shape_out, dev, chunk=gather_chunk) if ((world > 1 and os.environ.get('GEOTX_KEEP') != '0') or os.environ.get('GEOTX_KEEP') == '1') else None
-        # the clock sampler (rank 0 spawns nvidia-smi) starts BEFORE the barrier: started after it, rank 0 entered the timed
-        # region ~0.7 ms late, and with a gather at the end every other rank's time included that wait
+        # the clock sampler (rank 0 spawns nvidia-smi) is started, and has delivered its first sample, BEFORE the barrier that
+        # opens the timed region: started after it, rank 0 entered the region ~0.7 ms late (and nvidia-smi initialised
+        # inside it), and with a gather at the end every other rank's time included that wait
         sampler = ClockSampler(local) if rank == 0 else None
         if sampler:
             sampler.start()
+            sampler.wait_ready()
         t_start, t_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         t_start.record()
