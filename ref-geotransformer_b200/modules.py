@@ -1255,7 +1255,8 @@ class LocalGlobalRegistration(nn.Module):
     host-side chunk loop / six Procrustes calls with a host SVD each; the only synchronisation is the read of C that
     sizes the returned views (`ops.local_global_registration` is the fixed-capacity form without it).
     use_dustbin = True and correspondence_limit are not shipped by any configuration (experiments/*/config.py:116-125)
-    and raise."""
+    and raise; the reference's own dustbin branch cannot run either (local_global_registration.py:78-79 slices the
+    correspondence matrix to (B, 1) before the (B, K, K) mask is applied)."""
 
     def __init__(self, k, acceptance_radius, mutual=True, confidence_threshold=0.05, use_dustbin=False,
                  use_global_score=False, correspondence_threshold=3, correspondence_limit=None,
@@ -1304,10 +1305,21 @@ def radius_search(q_points, s_points, q_lengths, s_lengths, radius, neighbor_lim
     the GPU: same arguments, same result -- (N, min(max_count, neighbor_limit)) int64, filled with M.  The reference
     runs nanoflann on the host inside the data loader; here the width of the result depends on device data, so this
     wrapper reads one integer back (the only synchronisation); `ops.radius_neighbors` returns the fixed-width form
-    without it.  neighbor_limit <= 0 (the reference's "no truncation") is not supported."""
+    without it.  neighbor_limit <= 0 is the reference's "no truncation" (radius_search.py:25): the search runs once to
+    learn the widest neighbourhood and, when that exceeds the first guess, once more at that width; the kernel keeps
+    at most GEOTX_MAX_NEIGHBOR_LIMIT = 512 neighbours per query and a wider neighbourhood is an error."""
+    q_points, s_points = q_points.contiguous(), s_points.contiguous()
     if neighbor_limit <= 0:
-        raise RuntimeError('radius_search: neighbor_limit must be positive on the GPU path')
-    neighbors, _, max_count = ops.radius_neighbors(q_points.contiguous(), s_points.contiguous(), q_lengths, s_lengths,
+        guess = 64
+        neighbors, _, max_count = ops.radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, guess)
+        width = int(max_count.item())
+        if width > ops.MAX_NEIGHBOR_LIMIT:
+            raise RuntimeError(f'radius_search: a query has {width} neighbours within radius={radius}; the GPU path '
+                               f'keeps at most {ops.MAX_NEIGHBOR_LIMIT} per query -- pass a neighbor_limit')
+        if width > guess:
+            neighbors, _, _ = ops.radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, width)
+        return neighbors[:, :width]
+    neighbors, _, max_count = ops.radius_neighbors(q_points, s_points, q_lengths, s_lengths,
                                                    radius, neighbor_limit)
     width = min(int(max_count.item()), int(neighbor_limit))
     return neighbors[:, :width] if width < neighbor_limit else neighbors

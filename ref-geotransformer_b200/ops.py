@@ -365,6 +365,7 @@ def _host_lengths(lengths, name):
 
 
 _RN_WORK = {}
+MAX_NEIGHBOR_LIMIT = 512  # GEOTX_MAX_NEIGHBOR_LIMIT (include/geotx_b200.h): neighbours K9 keeps per query
 
 
 def radius_neighbors(q_points, s_points, q_lengths, s_lengths, radius, neighbor_limit, method='grid', max_cells=1 << 20):

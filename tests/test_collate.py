@@ -140,6 +140,24 @@ def test_gpu_full_size_vs_reference_operator(pkg, sizes, radius, limit):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize('sizes,radius', [((3000, 2500), 0.5), ((900, 1, 700), 0.8), ((40, 33), 10.0)])
+def test_gpu_no_truncation_vs_reference_operator(pkg, sizes, radius):
+    """neighbor_limit <= 0: the reference returns the operator's full-width result (radius_search.py:24-26); so does
+    the GPU wrapper (one search to learn the width, a second one when it exceeds the first guess of 64: widths 129, 106 and 40 here)."""
+    if not ref_cpu.available():
+        pytest.skip('oracle/_ref not built and /root/reference absent')
+    from gpu_common import DEV
+    s = torch.cat([pkg.synth.make_dense_cloud(n, 3.0, 700 + b) for b, n in enumerate(sizes)])
+    full = ref_cpu.radius_neighbors(s.numpy(), s.numpy(), list(sizes), list(sizes), radius)
+    for limit in (0, -1):
+        got = pkg.radius_search(s.to(DEV), s.to(DEV), list(sizes), list(sizes), radius, limit).cpu().numpy()
+        assert_same_neighbors(got, full, s.numpy(), s.numpy(), s.shape[0])
+    crowd = pkg.synth.make_dense_cloud(600, 3.0, 77).to(DEV)  # 600 points within reach of each other
+    with pytest.raises(RuntimeError, match='at most 512'):
+        pkg.radius_search(crowd, crowd, [600], [600], 100.0, 0)
+
+
+@pytest.mark.gpu
 def test_gpu_empty_batch_element(pkg):
     """Our own semantics for an empty element: it contributes no queries and no neighbours, the others are unaffected."""
     from gpu_common import DEV
