@@ -137,6 +137,14 @@ int geotx_attention(const float* q, const float* k, const float* v, const float*
                     const uint8_t* key_mask, int B, int H, int n, int m, int c, int ld_q, int ld_k, int ld_v,
                     float scale, float* out, int split_keys, void* stream);
 
+/* geotx_attention for q, k, v that are already IEEE half (geotx_linear_f16_mixed): same contract and arithmetic (the
+ * fp32 entry rounds q, k, v to half itself), ld_q / ld_k / ld_v in halves (multiples of 8), q/k/v 16-byte aligned.
+ * K and V tiles and the additive-score tile of the CTA's queries arrive through one 3- or 4-stage cp.async pipeline
+ * (one block barrier per 64-key tile, no conversion pass).  scale must be positive. */
+int geotx_attention_f16(const void* q, const void* k, const void* v, const float* scores_p, const uint8_t* key_mask,
+                        int B, int H, int n, int m, int c, int ld_q, int ld_k, int ld_v, float scale, float* out,
+                        int split_keys, void* stream);
+
 /* out = LayerNorm(x + residual) over the last dimension (rpe_transformer.py:103, vanilla_transformer.py:101,
  * output_layer.py:20; torch.nn.LayerNorm semantics: biased variance, eps inside the root).  residual may be NULL.
  *   x, residual, out f32 [rows, C]; gamma, beta f32 [C]; C a multiple of 4, <= 1024. */
@@ -155,6 +163,13 @@ int geotx_f32_to_f16(const float* src, void* dst, int64_t count, void* stream);
 int geotx_pack_linear_weight(const float* w, int N, int K, void* packed_f16, void* stream);
 int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias, int N,
                      int relu, float* y, int64_t ld_y, void* stream);
+/* The same Linear with a two-part result: output columns [0, half_cols) are written as IEEE half (round to nearest,
+ * saturated to +-65504) to y_half [T, half_cols] (row stride ld_yh halves, multiple of 8), columns [half_cols, N) as fp32
+ * to y [T, N - half_cols] (y may be NULL when half_cols == N).  half_cols % 64 == 0.  The q | k | v blocks of a fused
+ * projection are consumed by geotx_attention_f16 only, which contracts in half anyway: writing them as half removes the
+ * attention kernel's conversion pass and halves their traffic, with bit-identical operands. */
+int geotx_linear_f16_mixed(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias, int N,
+                           int relu, void* y_half, int64_t ld_yh, int half_cols, float* y, int64_t ld_y, void* stream);
 
 /* K4f: everything a transformer layer does after its attention core, in one kernel (rpe_transformer.py:101-103 /
  * vanilla_transformer.py:99-101 followed by output_layer.py:15-21):

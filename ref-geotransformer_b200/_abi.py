@@ -30,6 +30,7 @@ SIGNATURES = {
     'geotx_gse_embed_fp32': (_i, [_p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _i, _f, _f, _i, _i, _p, _p]),
     'geotx_rpe_scores': (_i, [_p, _i64, _i64, _i64, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
     'geotx_attention': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _f, _p, _i, _p]),
+    'geotx_attention_f16': (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _f, _p, _i, _p]),
     'geotx_add_layernorm': (_i, [_p, _p, _p, _p, _i64, _i, _f, _p, _p]),
     'geotx_spm_workspace_bytes': (_i64, [_i, _i, _i, _i]),
     'geotx_superpoint_matching': (_i, [_p, _p, _i, _i, _i, _p, _p, _i, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
@@ -61,6 +62,7 @@ SIGNATURES = {
     'geotx_f32_to_f16': (_i, [_p, _p, _i64, _p]),
     'geotx_pack_linear_weight': (_i, [_p, _i, _i, _p, _p]),
     'geotx_linear_f16': (_i, [_p, _i64, _i64, _i, _p, _p, _i, _i, _p, _i64, _p]),
+    'geotx_linear_f16_mixed': (_i, [_p, _i64, _i64, _i, _p, _p, _i, _i, _p, _i64, _i, _p, _i64, _p]),
     'geotx_post_attention': (_i, [_p, _i64, _p, _i64, _i64, _i, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _p, _f, _p, _i64,
                                   _p]),
     'geotx_mma_sync_probe': (_i, [_i, _i, _p, _p]),

@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB_DIR = os.path.join(HERE, 'lib')
 LIB_PATH = os.path.join(LIB_DIR, 'libgeotx_b200.so')
-SOURCES = ['abi.cu', 'k0_probe.cu', 'k1_knn.cu', 'k2_gse_embed_fp32.cu', 'k2_gse_embed.cu', 'k3_rpe_scores.cu', 'k3_attention.cu',
+SOURCES = ['abi.cu', 'k0_probe.cu', 'k1_knn.cu', 'k2_gse_embed_fp32.cu', 'k2_gse_embed.cu', 'k3_rpe_scores.cu', 'k3_attention.cu', 'k3_attention_f16.cu',
            'k4_add_layernorm.cu', 'k5_superpoint_matching.cu', 'k6_point_to_node.cu',
            'k7_log_optimal_transport.cu', 'k8_weighted_procrustes.cu',
            'k9_radius_neighbors.cu', 'k10_grid_subsample.cu', 'k11_local_global_registration.cu', 'k12_patch_scores.cu', 'k2_gse_embed_table.cu', 'k2_gse_embed_cheb.cu', 'k4_post_attention.cu', 'k13_linear.cu']

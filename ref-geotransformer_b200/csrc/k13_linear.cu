@@ -24,6 +24,8 @@ struct LinearArgs {
     const float* bias;   // [N] or null
     float* y; long long ld_y;
     int T, K, N, relu;
+    __half* yh; long long ld_yh;  // geotx_linear_f16_mixed: output columns < half_cols go here as half ...
+    int half_cols;                // ... and column c >= half_cols to y[.., c - half_cols] (0: everything fp32 into y)
 };
 
 constexpr int LIN_OFF_A = 128;
@@ -104,7 +106,10 @@ __global__ void __launch_bounds__(DT_THREADS) linear_tile_kernel(const LinearArg
                 if (r < p.T) {
                     float2 o = make_float2(acc[mt][nt][2 * h] + b.x, acc[mt][nt][2 * h + 1] + b.y);
                     if (p.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); }
-                    *reinterpret_cast<float2*>(p.y + (size_t)r * p.ld_y + col) = o;
+                    if (col < p.half_cols)  // uniform per 64-column block: half_cols is a multiple of 64
+                        *reinterpret_cast<uint32_t*>(p.yh + (size_t)r * p.ld_yh + col) = dt_pack(o.x, o.y);
+                    else
+                        *reinterpret_cast<float2*>(p.y + (size_t)r * p.ld_y + (col - p.half_cols)) = o;
                 }
             }
     }
@@ -114,14 +119,34 @@ __global__ void __launch_bounds__(DT_THREADS) linear_tile_kernel(const LinearArg
 
 using namespace geotx;
 
+static int linear_launch(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias, int N, int relu,
+                         float* y, int64_t ld_y, void* y_half, int64_t ld_yh, int half_cols, void* stream);
+
 extern "C" int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias,
                                 int N, int relu, float* y, int64_t ld_y, void* stream) {
-    GEOTX_REQUIRE(x && w_f16 && y, "geotx_linear_f16: null pointer");
+    GEOTX_REQUIRE(y, "geotx_linear_f16: null pointer");
+    return linear_launch(x, ld_x, T, K, w_f16, bias, N, relu, y, ld_y, nullptr, 0, 0, stream);
+}
+
+extern "C" int geotx_linear_f16_mixed(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias,
+                                      int N, int relu, void* y_half, int64_t ld_yh, int half_cols, float* y, int64_t ld_y,
+                                      void* stream) {
+    GEOTX_REQUIRE(half_cols > 0 && half_cols <= N && half_cols % 64 == 0,
+                  "geotx_linear_f16_mixed: half_cols=%d must be a multiple of 64 in (0, N=%d]", half_cols, N);
+    GEOTX_REQUIRE(y_half && ((uintptr_t)y_half & 15) == 0 && ld_yh >= half_cols && ld_yh % 8 == 0,
+                  "geotx_linear_f16_mixed: y_half must be 16-byte aligned with a row stride >= half_cols, multiple of 8 halves");
+    GEOTX_REQUIRE(half_cols == N || y, "geotx_linear_f16_mixed: y is null but %d fp32 columns remain", N - half_cols);
+    return linear_launch(x, ld_x, T, K, w_f16, bias, N, relu, y, ld_y, y_half, ld_yh, half_cols, stream);
+}
+
+static int linear_launch(const float* x, int64_t ld_x, int64_t T, int K, const void* w_f16, const float* bias, int N, int relu,
+                         float* y, int64_t ld_y, void* y_half, int64_t ld_yh, int half_cols, void* stream) {
+    GEOTX_REQUIRE(x && w_f16, "geotx_linear_f16: null pointer");
     GEOTX_REQUIRE(T > 0 && T < 2147483647LL / 2, "geotx_linear_f16: bad token count");
     GEOTX_REQUIRE(K >= DT_KC && K % DT_KC == 0 && K <= 2048 && N >= 64 && N % 64 == 0,
                   "geotx_linear_f16: K=%d must be a multiple of %d (<= 2048) and N=%d a multiple of 64", K, DT_KC, N);
-    GEOTX_REQUIRE(ld_x >= K && ld_x % 4 == 0 && ld_y >= N && ld_y % 2 == 0,
-                  "geotx_linear_f16: row strides (x: multiple of 4 floats >= K, y: even >= N)");
+    GEOTX_REQUIRE(ld_x >= K && ld_x % 4 == 0 && (half_cols == N || (ld_y >= N - half_cols && ld_y % 2 == 0)),
+                  "geotx_linear_f16: row strides (x: multiple of 4 floats >= K, y: even >= its column count)");
     GEOTX_REQUIRE((((uintptr_t)x | (uintptr_t)w_f16) & 15) == 0 && (((uintptr_t)y | (uintptr_t)bias) & 7) == 0,
                   "geotx_linear_f16: x, w must be 16-byte aligned, y and bias 8-byte aligned");
     LinearArgs p;
@@ -130,6 +155,7 @@ extern "C" int geotx_linear_f16(const float* x, int64_t ld_x, int64_t T, int K, 
     p.bias = bias;
     p.y = y; p.ld_y = ld_y;
     p.T = (int)T; p.K = K; p.N = N; p.relu = relu;
+    p.yh = (__half*)y_half; p.ld_yh = ld_yh; p.half_cols = half_cols;
     const int sms = sm_count();
     const long long row_tiles = (T + DT_BM - 1) / DT_BM;
     // the widest column block that still gives every SM a CTA (x is converted once per CTA: wider is cheaper)

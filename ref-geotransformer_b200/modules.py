@@ -126,16 +126,30 @@ def _half_of(owner, name, t):
     return ent[1]
 
 
-def _linear(x, owner, name, weight, bias, out=None):
-    """nn.Linear on K13 when the shape fits its tiles and GEOTX_DENSE allows it, else F.linear."""
+def _linear(x, owner, name, weight, bias, out=None, half_cols=0):
+    """nn.Linear on K13 when the shape fits its tiles and GEOTX_DENSE allows it, else F.linear.  half_cols > 0: returns
+    (the first half_cols output columns as float16 -- the q | k | v operands of the attention kernel --, the remaining
+    columns as fp32 or None), see ops.linear_f16."""
     N, K = weight.shape
-    if _dense_own() and x.is_cuda and x.dtype == torch.float32 and ops.linear_supported(K, N) and x.stride(-1) == 1:
-        return ops.linear_f16(x, _half_of(owner, name, weight), bias, out=out)
+    if _dense_own() and x.is_cuda and x.dtype == torch.float32 and ops.linear_supported(K, N) and x.stride(-1) == 1 \
+            and half_cols % 64 == 0:
+        return ops.linear_f16(x, _half_of(owner, name, weight), bias, out=out, half_cols=half_cols)
     y = F.linear(x, weight, bias)
+    if half_cols:
+        return y[..., :half_cols].clamp(-65504.0, 65504.0).to(torch.float16), (y[..., half_cols:] if half_cols < N else None)
     if out is not None:
         out.copy_(y)
         return out
     return y
+
+
+def _attention_f16():
+    """GEOTX_ATT: 'f16' (default) has the fused schedule's projections write q | k | v as half for the pipelined
+    attention kernel K3h (geotx_attention_f16); 'f32' keeps fp32 q | k | v and K3b, which rounds them itself."""
+    mode = os.environ.get('GEOTX_ATT', 'f16')
+    if mode not in ('f16', 'f32'):
+        raise ValueError(f"GEOTX_ATT must be 'f16' or 'f32', got {mode!r}")
+    return mode == 'f16'
 
 
 class SinusoidalPositionalEmbedding(nn.Module):
@@ -769,7 +783,14 @@ class RPEConditionalTransformer(nn.Module):
                 if H % 4 == 0 and all(isinstance(e, StreamedEmbedding) and e.direct for e in embs):
                     gd = embs[0].embedding.distance_split_rows()
                 w, b = att.fused_qkvp(gd)
-                y = _linear(x, att, 'qkvp', w, b)  # (1, T, 3C + H*C [+ H*80]): q | k | v | folded query per head [| u]
+                # one projection: q | k | v | folded query per head [| u].  (1, T, 3C + H*C [+ H*80]) fp32, or the q | k | v
+                # block as half (what the attention kernel contracts in) and the rest as fp32
+                if _attention_f16():
+                    qkv, y = _linear(x, att, 'qkvp', w, b, half_cols=3 * C)
+                    off = 0
+                else:
+                    qkv = y = _linear(x, att, 'qkvp', w, b)
+                    off = 3 * C
                 M = 0 if gd is None else gd.shape[0]
                 hidden = x.new_empty(1, T, C)
                 cur = side = None
@@ -787,17 +808,17 @@ class RPEConditionalTransformer(nn.Module):
                         all(isinstance(e, StreamedEmbedding) and e.direct for e in embs))
                 for which, (lo, hi, mask) in enumerate(((0, N, masks0), (N, T, masks1))):
                     emb = embs[which]
-                    qt = y[:, lo:hi, 3 * C:3 * C + H * C].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
+                    qt = y[:, lo:hi, off:off + H * C].unflatten(2, (H, C)).permute(0, 2, 1, 3)  # (1, H, n, C) view
                     if isinstance(emb, StreamedEmbedding) and emb.direct:
-                        u = y[:, lo:hi, 3 * C + H * C:].unflatten(2, (H, M)).permute(0, 2, 1, 3) if M else None
+                        u = y[:, lo:hi, off + H * C:].unflatten(2, (H, M)).permute(0, 2, 1, 3) if M else None
                         if fork and which == 1:
                             cur = torch.cuda.current_stream(x.device)
                             side = _side_stream(x.device)
                             side.wait_stream(cur)
                             with torch.cuda.stream(side):
                                 scores_p = emb.direct_scores(qt, u)
-                                ops.attention(y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask,
-                                              out=hidden[:, lo:hi])
+                                ops.attention(qkv[:, lo:hi, 0:C], qkv[:, lo:hi, C:2 * C], qkv[:, lo:hi, 2 * C:3 * C], H, scores_p,
+                                              mask, out=hidden[:, lo:hi])
                             del scores_p  # allocated and used on the side stream only
                             continue
                         scores_p = emb.direct_scores(qt, u)  # K3r: E of this cloud is never formed in memory
@@ -808,7 +829,7 @@ class RPEConditionalTransformer(nn.Module):
                         embs[which] = emb.E
                     else:
                         scores_p = ops.rpe_scores(qt, emb.contiguous())
-                    att_args = (y[:, lo:hi, 0:C], y[:, lo:hi, C:2 * C], y[:, lo:hi, 2 * C:3 * C], H, scores_p, mask)
+                    att_args = (qkv[:, lo:hi, 0:C], qkv[:, lo:hi, C:2 * C], qkv[:, lo:hi, 2 * C:3 * C], H, scores_p, mask)
                     if which == 0 and self.overlap_attention and not streamed:
                         # the first cloud's attention core (a short, latency-bound launch) runs on a side stream
                         # underneath the second cloud's HBM-bound scores kernel
@@ -830,12 +851,14 @@ class RPEConditionalTransformer(nn.Module):
                 # (parallel=True reads the old one: no second projection at all).
                 x_new = torch.empty_like(x)
                 w3, b3 = att.fused_qkv()
-                y = _linear(x, att, 'qkv', w3, b3)  # (1, T, 3C): q | k | v
+                f16 = _attention_f16()
+                y = _linear(x, att, 'qkv', w3, b3, half_cols=3 * C)[0] if f16 else _linear(x, att, 'qkv', w3, b3)  # (1, T, 3C)
                 order = ((0, N, N, T, masks1), (N, T, 0, N, masks0))  # (query cloud, memory cloud, memory mask)
                 for step, (qlo, qhi, mlo, mhi, mask) in enumerate(order):
                     if step == 1 and not self.parallel:
                         wkv, bkv = att.fused_kv()
-                        kv = _linear(x_new[:, mlo:mhi], att, 'kv', wkv, bkv)
+                        kv = _linear(x_new[:, mlo:mhi], att, 'kv', wkv, bkv, half_cols=2 * C)[0] if f16 else \
+                            _linear(x_new[:, mlo:mhi], att, 'kv', wkv, bkv)
                         k_mem, v_mem = kv[:, :, :C], kv[:, :, C:]
                     else:
                         k_mem, v_mem = y[:, mlo:mhi, C:2 * C], y[:, mlo:mhi, 2 * C:]

@@ -149,13 +149,15 @@ def gse_embed_fp32(geom, div_term, w_d, b_d, w_a, b_a, sigma_d, factor_a, reduce
     return out
 
 
-def _row_strided(t, name):
-    """(B, tokens, D) fp32 CUDA view with unit channel stride, 16-byte aligned rows: returns (tensor, row stride).
-    Column blocks of a fused projection output qualify; anything else is made contiguous."""
-    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.dim() == 3):
-        raise RuntimeError(f'{name} must be a 3-d fp32 CUDA tensor (ref-geotransformer_b200 has no CPU path)')
+def _row_strided(t, name, dtype=torch.float32):
+    """(B, tokens, D) fp32 (or half) CUDA view with unit channel stride, 16-byte aligned rows: returns (tensor, row
+    stride).  Column blocks of a fused projection output qualify; anything else is made contiguous."""
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == dtype and t.dim() == 3):
+        raise RuntimeError(f'{name} must be a 3-d {dtype} CUDA tensor (ref-geotransformer_b200 has no CPU path)')
+    _same_device(t, name)
     B, n, D = t.shape
-    ok = t.stride(2) == 1 and t.stride(1) % 4 == 0 and t.stride(1) >= D and t.data_ptr() % 16 == 0 and \
+    unit = 16 // t.element_size()
+    ok = t.stride(2) == 1 and t.stride(1) % unit == 0 and t.stride(1) >= D and t.data_ptr() % 16 == 0 and \
         (B == 1 or t.stride(0) == n * t.stride(1))
     if not ok:
         t = t.contiguous()
@@ -187,10 +189,15 @@ def rpe_scores(qt, E, n=None, row_begin=0, out=None):
 
 def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None, split_keys=True, out=None):
     """q (B,n,H*c), k,v (B,m,H*c) fp32 token-major (dense or column blocks of a wider row-major matrix)
-    -> (B,n,H*c) dense.  softmax((q k^T + scores_p)*scale) v.  rpe_transformer.py:57-70, vanilla_transformer.py:54-68."""
-    q, ldq = _row_strided(q, 'q')
-    k, ldk = _row_strided(k, 'k')
-    v, ldv = _row_strided(v, 'v')
+    -> (B,n,H*c) dense.  softmax((q k^T + scores_p)*scale) v.  rpe_transformer.py:57-70, vanilla_transformer.py:54-68.
+    q, k, v may also be float16 (all three: what `linear_f16(..., half_cols=)` writes): the fp32 kernel (K3b) rounds them
+    to half itself, the half kernel (K3h, geotx_attention_f16) takes them as they are -- same operands, same result up to
+    fp32 summation order."""
+    half = isinstance(q, torch.Tensor) and q.dtype == torch.float16
+    dt = torch.float16 if half else torch.float32
+    q, ldq = _row_strided(q, 'q', dt)
+    k, ldk = _row_strided(k, 'k', dt)
+    v, ldv = _row_strided(v, 'v', dt)
     B, n, D = q.shape
     m = k.shape[1]
     c = D // num_heads
@@ -208,8 +215,8 @@ def attention(q, k, v, num_heads, scores_p=None, key_mask=None, scale=None, spli
         out = torch.empty(B, n, D, dtype=torch.float32, device=q.device)
     elif tuple(_check(out, 'out', torch.float32, 3).shape) != (B, n, D):
         raise RuntimeError(f'out must be {(B, n, D)}, got {tuple(out.shape)}')
-    _abi.call('geotx_attention', _p(q), _p(k), _p(v), _p(scores_p), _p(mask_u8), B, num_heads, n, m, c, ldq, ldk, ldv,
-              float(scale), _p(out), int(bool(split_keys)), _stream())
+    _abi.call('geotx_attention_f16' if half else 'geotx_attention', _p(q), _p(k), _p(v), _p(scores_p), _p(mask_u8), B,
+              num_heads, n, m, c, ldq, ldk, ldv, float(scale), _p(out), int(bool(split_keys)), _stream())
     return out
 
 
@@ -722,10 +729,13 @@ def linear_supported(K, N):
     return K >= 32 and K % 32 == 0 and K <= 2048 and N >= 64 and N % 64 == 0
 
 
-def linear_f16(x, w_half, bias, out=None, relu=False):
+def linear_f16(x, w_half, bias, out=None, relu=False, half_cols=0):
     """y = x W^T + b (nn.Linear semantics) on the hand-written mma.sync kernel K13: x (..., K) fp32 with equally strided
     rows, w_half (N, K) the PACKED half image of the weight (`pack_linear(weight)`), bias (N,) fp32 or None -> (..., N)
-    fp32 (into `out` if given; rows of `out` may be strided).  K % 32 == 0, K <= 2048, N % 64 == 0."""
+    fp32 (into `out` if given; rows of `out` may be strided).  K % 32 == 0, K <= 2048, N % 64 == 0.
+    half_cols > 0 (a multiple of 64; geotx_linear_f16_mixed): returns (y_half (..., half_cols) float16, y (..., N -
+    half_cols) fp32 or None when nothing is left) -- the first output columns rounded to half (saturating), for
+    `attention`, the rest as usual."""
     if not isinstance(w_half, torch.Tensor) or not w_half.is_cuda or w_half.dtype != torch.float16 or w_half.dim() != 2 \
             or not w_half.is_contiguous():
         raise RuntimeError('w_half must be a contiguous 2-d float16 CUDA tensor (N, K)')
@@ -735,6 +745,14 @@ def linear_f16(x, w_half, bias, out=None, relu=False):
     T, ld_x = _rows2d(x, 'x', K)
     if bias is not None:
         _check(bias, 'bias', torch.float32, 1)
+    if half_cols:
+        if out is not None or half_cols % 64 or not 0 < half_cols <= N:
+            raise RuntimeError(f'linear_f16: half_cols={half_cols} must be a multiple of 64 in (0, {N}] and excludes out=')
+        y_half = torch.empty(*x.shape[:-1], half_cols, dtype=torch.float16, device=x.device)
+        rest = torch.empty(*x.shape[:-1], N - half_cols, dtype=torch.float32, device=x.device) if half_cols < N else None
+        _abi.call('geotx_linear_f16_mixed', _p(x), ld_x, T, K, _p(w_half), _p(bias), N, int(bool(relu)), _p(y_half),
+                  half_cols, half_cols, _p(rest), N - half_cols, _stream())
+        return y_half, rest
     if out is None:
         out = torch.empty(*x.shape[:-1], N, dtype=torch.float32, device=x.device)
     T_out, ld_y = _rows2d(out, 'out', N)

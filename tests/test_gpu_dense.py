@@ -31,6 +31,30 @@ def test_linear_vs_torch(pkg, T, K, N):
     assert rel(pkg.ops.linear_f16(x.to(DEV), wh, b.to(DEV), relu=True), exp.clamp_min(0)) <= TOL
 
 
+@pytest.mark.parametrize('T,K,N,hc', [(2048, 256, 1792, 768), (717, 256, 768, 768), (50, 128, 896, 384), (1, 64, 128, 64)])
+def test_linear_mixed_half_and_fp32_columns(pkg, T, K, N, hc):
+    """geotx_linear_f16_mixed: the first hc columns of the result as half (exactly the rounding K3b applies to fp32
+    q | k | v: round to nearest, saturating), the rest as fp32 -- both bit-identical to the plain call."""
+    g = torch.Generator().manual_seed(T + K + N + hc)
+    x = torch.randn(T, K, generator=g).to(DEV)
+    w = torch.randn(N, K, generator=g) / K ** 0.5
+    wh = pkg.ops.pack_linear(w.to(DEV))
+    b = torch.randn(N, generator=g)
+    b[0], b[1] = 1e6, -1e6  # columns 0 and 1 overflow half: must saturate to +-65504, not inf
+    b = b.to(DEV)
+    full = pkg.ops.linear_f16(x, wh, b)
+    yh, rest = pkg.ops.linear_f16(x, wh, b, half_cols=hc)
+    assert yh.dtype == torch.float16 and tuple(yh.shape) == (T, hc)
+    assert torch.equal(yh, full[:, :hc].clamp(-65504.0, 65504.0).to(torch.float16))
+    assert torch.isfinite(yh).all()
+    if hc < N:
+        assert rest.dtype == torch.float32 and torch.equal(rest, full[:, hc:])
+    else:
+        assert rest is None
+    with pytest.raises(RuntimeError, match='half_cols'):
+        pkg.ops.linear_f16(x, wh, b, half_cols=32)
+
+
 def test_linear_strided_rows_and_slices(pkg):
     """Inputs / outputs that are column blocks and row slices of larger token buffers (how the fused schedule calls it)."""
     g = torch.Generator().manual_seed(4)

@@ -67,6 +67,56 @@ def test_attention_vs_torch(pkg, oracle, c, H, n, m, with_p, with_mask):
     assert rel(one, exp) <= 2e-3 and rel(one, got) <= 1e-3  # P is rounded to TF32 against a different running max
 
 
+@pytest.mark.parametrize('c,H,n,m', [(64, 4, 200, 160), (32, 4, 77, 300), (64, 4, 64, 64), (16, 2, 33, 65), (64, 4, 1024, 1024),
+                                     (64, 1, 130, 1000), (32, 4, 2100, 1900)])
+@pytest.mark.parametrize('with_p,with_mask', [(False, False), (True, False), (True, True), (False, True)])
+def test_attention_half_operands_vs_torch(pkg, c, H, n, m, with_p, with_mask):
+    """K3h (geotx_attention_f16): q, k, v handed over as half.  Against torch fp32 on the SAME half-rounded operands the
+    only differences are P's rounding to half and the fp32 summation order -> 1e-3; against K3b (fp32 entry, which rounds
+    to half itself) likewise.  Shapes: ragged tiles, key counts that are / are not multiples of 4 (16-byte / 4-byte
+    score copies), both CTA shapes (the last case has >= 128 query tiles of 128), cluster splits 1..8."""
+    g = torch.Generator().manual_seed(c * 1000 + n + m)
+    B, D = (2, H * c) if n < 1000 else (1, H * c)
+    q, k, v = (_rand(g, B, r, D).to(torch.float16) for r in (n, m, m))
+    sp = _rand(g, B, H, n, m) * 3.0 if with_p else None
+    mask = (torch.rand(B, m, generator=g) < 0.3) if with_mask else None
+    if mask is not None:
+        mask[:, 0] = False
+    qh, kh, vh = (t.float().view(B, -1, H, c).permute(0, 2, 1, 3) for t in (q, k, v))
+    s = torch.einsum('bhnc,bhmc->bhnm', qh, kh)
+    if sp is not None:
+        s = s + sp
+    s = s / c ** 0.5
+    if mask is not None:
+        s = s.masked_fill(mask[:, None, None], float('-inf'))
+    exp = torch.matmul(torch.softmax(s, -1), vh).permute(0, 2, 1, 3).reshape(B, n, D)
+    dev = lambda t: None if t is None else t.to(DEV)  # noqa: E731
+    got = pkg.ops.attention(dev(q), dev(k), dev(v), H, dev(sp), dev(mask))
+    assert got.dtype == torch.float32 and rel(got, exp) <= 1e-3
+    one = pkg.ops.attention(dev(q), dev(k), dev(v), H, dev(sp), dev(mask), split_keys=False)
+    assert rel(one, exp) <= 1e-3
+    old = pkg.ops.attention(dev(q.float()), dev(k.float()), dev(v.float()), H, dev(sp), dev(mask))
+    assert rel(got, old) <= 1e-3
+
+
+def test_attention_half_column_blocks_and_edge_cases(pkg):
+    """q | k | v as column blocks of one half matrix (what linear_f16(half_cols=) writes); all keys masked -> NaN like
+    torch; mixed dtypes and a non-positive scale are refused."""
+    g = torch.Generator().manual_seed(11)
+    n, H, c = 300, 4, 64
+    C = H * c
+    y = torch.randn(1, n, 3 * C, generator=g).to(DEV).to(torch.float16)
+    q, k, v = y[:, :, :C], y[:, :, C:2 * C], y[:, :, 2 * C:]
+    got = pkg.ops.attention(q, k, v, H)
+    assert torch.equal(got, pkg.ops.attention(q.contiguous(), k.contiguous(), v.contiguous(), H))
+    nan = pkg.ops.attention(q, k, v, H, None, torch.ones(1, n, dtype=torch.bool, device=DEV))
+    assert torch.isnan(nan).all()
+    with pytest.raises(RuntimeError, match='float16'):
+        pkg.ops.attention(q, k.float(), v, H)
+    with pytest.raises(RuntimeError, match='scale must be positive'):
+        pkg.ops.attention(q, k, v, H, scale=-1.0)
+
+
 def test_attention_all_keys_masked_is_nan_like_torch(pkg):
     q = torch.randn(1, 8, 64)
     got = pkg.ops.attention(q.to(DEV), q.to(DEV), q.to(DEV), 2, None, torch.ones(1, 8, dtype=torch.bool).to(DEV))
