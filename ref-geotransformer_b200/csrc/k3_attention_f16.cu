@@ -14,6 +14,7 @@
 //   * 3 stages (4 without scores): tile t+2 is requested before tile t is consumed, ONE block barrier per tile;
 //   * the softmax works on raw logits (max first, then one FFMA + EX2 per weight).
 // Key ranges are split over a thread-block cluster exactly as in K3b (partials merged through distributed shared memory).
+#include <cstdlib>
 #include <cuda_fp16.h>
 #include "geotx_common.cuh"
 #include "sm100_ptx.cuh"
@@ -358,6 +359,13 @@ attention_f16_kernel(const __grid_constant__ AhParams prm) {
 
 using namespace geotx;
 
+static int env_int(const char* name, int dflt, int lo, int hi) {
+    const char* e = getenv(name);
+    if (!e || !*e) return dflt;
+    const int v = atoi(e);
+    return v < lo ? lo : v > hi ? hi : v;
+}
+
 // Key-range splits (= cluster size): the largest power of two <= 8 that keeps the grid within one wave and leaves
 // every CTA at least one 64-key tile (the rule of K3b).
 static void ah_plan(int B, int H, int n, int m, int warps, bool scores, int allow_split, int* splits, int* tiles_per_split) {
@@ -365,9 +373,10 @@ static void ah_plan(int B, int H, int n, int m, int warps, bool scores, int allo
     const long long base = (long long)((n + bq - 1) / bq) * B * H;
     const int tiles = (m + AH_BK - 1) / AH_BK;
     const int wave = sm_count() * ah_ctas_per_sm(warps, scores);
+    static const int max_splits = env_int("GEOTX_ATT_MAX_SPLITS", AH_MAX_SPLITS, 1, AH_MAX_SPLITS);  // timing experiments
     int s = 1;
     if (allow_split)
-        while (s < AH_MAX_SPLITS && base * (2 * s) <= wave && 2 * s <= tiles) s *= 2;
+        while (s < max_splits && base * (2 * s) <= wave && 2 * s <= tiles) s *= 2;
     *tiles_per_split = (tiles + s - 1) / s;
     while (s > 1 && (s - 1) * *tiles_per_split >= tiles) {  // no CTA of the cluster may be left without keys
         s /= 2;
@@ -411,13 +420,17 @@ static int ah_launch(AhParams prm, int B, int allow_split, cudaStream_t st) {
 
 template <int DH>
 static int ah_launch_shape(const AhParams& prm, int B, int allow_split, cudaStream_t st) {
-    // 64-query CTAs (4 warps, two or three per SM) while there are fewer than AH_BIG_THRESHOLD 128-query tiles,
-    // 128-query CTAs (8 warps, one per SM: every K/V tile is fetched once per 128 queries) from there on -- K3b's rule
+    // split_keys != 0 (one forward at a time): 64-query CTAs (4 warps, two or three per SM) while there are fewer than
+    // AH_BIG_THRESHOLD 128-query tiles, 128-query CTAs (8 warps, one per SM: every K/V tile is fetched once per 128
+    // queries) from there on -- K3b's rule.  split_keys == 0 (several forwards in flight, SM-time counts): always the
+    // 64-query shape (3DMatch 4096, 2 graph instances in flight: 103.7 -> 105.6 pairs/s; 1024 without key splits,
+    // 4 in flight: 1363 -> 1407)
     const long long big = (long long)((prm.n + 127) / 128) * B * prm.H;
 #ifndef AH_BIG_THRESHOLD
 #define AH_BIG_THRESHOLD 128
 #endif
-    if (big >= AH_BIG_THRESHOLD)
+    static const int big_threshold = env_int("GEOTX_ATT_BIG", AH_BIG_THRESHOLD, 1, 1 << 30);  // timing experiments
+    if (allow_split && big >= big_threshold)
         return prm.scores_p ? ah_launch<DH, 8, true>(prm, B, allow_split, st) : ah_launch<DH, 8, false>(prm, B, allow_split, st);
     return prm.scores_p ? ah_launch<DH, 4, true>(prm, B, allow_split, st) : ah_launch<DH, 4, false>(prm, B, allow_split, st);
 }

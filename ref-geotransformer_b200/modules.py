@@ -724,6 +724,11 @@ class RPEConditionalTransformer(nn.Module):
         self.return_attention_scores = return_attention_scores
         self.parallel = parallel
         self.overlap_attention = os.environ.get('GEOTX_OVERLAP_ATTENTION', '1') != '0'
+        # False (default): one forward at a time -- a small attention grid is spread over the GPU by splitting the keys
+        # over thread-block clusters (shortest latency).  True: several forwards are in flight (GraphedGeometricTransformer
+        # (throughput=True), PipelinedGeometricTransformer) -- SM-time counts, not latency: one lean CTA per 64 queries
+        # walks all keys (no split / merge overhead).  Same results up to fp32 summation order.
+        self.throughput = False
 
     # ---- fused schedule (same math, fewer and larger launches) ------------------------------------------------
     # Both clouds share every layer's weights, so all token-wise work of a 'self' block (one fused q|k|v|folded-query
@@ -773,6 +778,7 @@ class RPEConditionalTransformer(nn.Module):
         if x is None:
             x = torch.cat([feats0, feats1], dim=1)  # (1, N+M, C); cloud slices of it are contiguous views
         T = x.shape[1]
+        split = not self.throughput
         for i, block in enumerate(self.blocks):
             layer = self.layers[i]
             att = layer.attention.attention
@@ -818,7 +824,7 @@ class RPEConditionalTransformer(nn.Module):
                             with torch.cuda.stream(side):
                                 scores_p = emb.direct_scores(qt, u)
                                 ops.attention(qkv[:, lo:hi, 0:C], qkv[:, lo:hi, C:2 * C], qkv[:, lo:hi, 2 * C:3 * C], H, scores_p,
-                                              mask, out=hidden[:, lo:hi])
+                                              mask, split_keys=split, out=hidden[:, lo:hi])
                             del scores_p  # allocated and used on the side stream only
                             continue
                         scores_p = emb.direct_scores(qt, u)  # K3r: E of this cloud is never formed in memory
@@ -837,10 +843,10 @@ class RPEConditionalTransformer(nn.Module):
                         side = _side_stream(x.device)
                         side.wait_stream(cur)
                         with torch.cuda.stream(side):
-                            ops.attention(*att_args, out=hidden[:, lo:hi])
+                            ops.attention(*att_args, split_keys=split, out=hidden[:, lo:hi])
                         scores_p.record_stream(side)
                     else:
-                        ops.attention(*att_args, out=hidden[:, lo:hi])
+                        ops.attention(*att_args, split_keys=split, out=hidden[:, lo:hi])
                 if side is not None:
                     cur.wait_stream(side)
                 x = self._post_attention(layer, hidden, x)
@@ -862,7 +868,7 @@ class RPEConditionalTransformer(nn.Module):
                         k_mem, v_mem = kv[:, :, :C], kv[:, :, C:]
                     else:
                         k_mem, v_mem = y[:, mlo:mhi, C:2 * C], y[:, mlo:mhi, 2 * C:]
-                    hidden = ops.attention(y[:, qlo:qhi, :C], k_mem, v_mem, H, None, mask)
+                    hidden = ops.attention(y[:, qlo:qhi, :C], k_mem, v_mem, H, None, mask, split_keys=split)
                     self._post_attention(layer, hidden, x[:, qlo:qhi], out=x_new[:, qlo:qhi])
                 x = x_new
         return x[:, :N], x[:, N:]
@@ -1040,8 +1046,9 @@ class GraphedGeometricTransformer:
         ref_out, src_out = fast(ref_points, src_points, ref_feats, src_feats)    # any inputs of the same shapes
     """
 
-    def __init__(self, model, ref_points, src_points, ref_feats, src_feats, warmup=2):
+    def __init__(self, model, ref_points, src_points, ref_feats, src_feats, warmup=2, throughput=False):
         self.model = model
+        self.throughput = bool(throughput)  # captured with the transformer's throughput schedule (several graphs in flight)
         self.static_in = [torch.empty_like(t) for t in (ref_points, src_points, ref_feats, src_feats)]
         for s, t in zip(self.static_in, (ref_points, src_points, ref_feats, src_feats)):
             s.copy_(t)
@@ -1060,6 +1067,17 @@ class GraphedGeometricTransformer:
         self._weights = list(self.model.parameters()) + list(self.model.buffers())
         self._captured_versions = self._weight_versions()
         self.captures = getattr(self, 'captures', 0) + 1
+        sched = getattr(self.model, 'transformer', None)
+        previous = getattr(sched, 'throughput', None)
+        if previous is not None:
+            sched.throughput = self.throughput
+        try:
+            self._capture()
+        finally:
+            if previous is not None:
+                sched.throughput = previous
+
+    def _capture(self):
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):  # warm-up off the capture: lazy cuBLAS / function-attribute initialisation
@@ -1114,7 +1132,8 @@ class PipelinedGeometricTransformer:
             ...                                          # pinned host tensors, valid until the NEXT result is requested
                                                          # (their slot is re-enqueued then): clone what must outlive it
 
-    Results come back in order and are bit-identical to `model(...)` on the same inputs."""
+    Results come back in order and are bit-identical to `model(...)` on the same inputs under the same schedule
+    (`model.transformer.throughput = True`, which the slots' graphs are captured with when they overlap)."""
 
     def __init__(self, model, ref_points, src_points, ref_feats, src_feats, depth=2, overlap_compute=None):
         if depth < 1:
@@ -1127,7 +1146,8 @@ class PipelinedGeometricTransformer:
         self.compute_streams = [torch.cuda.Stream() for _ in range(depth)] if overlap_compute and depth > 1 else None
         self.slots = []
         for _ in range(depth):
-            g = GraphedGeometricTransformer(model, ref_points, src_points, ref_feats, src_feats)
+            g = GraphedGeometricTransformer(model, ref_points, src_points, ref_feats, src_feats,
+                                            throughput=self.compute_streams is not None)
             host_out = tuple(torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in g.static_out)
             ev = {k: torch.cuda.Event() for k in ('h2d', 'compute', 'd2h')}
             self.slots.append((g, host_out, ev))

@@ -28,6 +28,7 @@ def main():
     ap.add_argument('--workload', default='3dmatch_1024')
     ap.add_argument('--steps', type=int, default=60)
     ap.add_argument('--inflight', type=int, default=0)
+    ap.add_argument('--full-only', action='store_true', help='time the full step only (A/B runs of environment knobs)')
     args = ap.parse_args()
     import torch
     import pkgpath
@@ -59,7 +60,7 @@ def main():
         real_call(name, *a)
     pkg._abi.call = call
     base = None
-    for tag, names in FAMILIES:
+    for tag, names in (FAMILIES[:1] if args.full_only else FAMILIES):
         skip.clear()
         skip.update(names)
         with torch.no_grad():
