@@ -6,13 +6,26 @@
 // What changed against K3b, and why.  K3b's step over one 64-key tile was: wait for the raw fp32 K/V tile, barrier,
 // convert it to half in a second buffer, barrier, Q K^T, softmax, P V -- with the additive scores of the tile loaded
 // straight from global memory into registers one tile ahead.  Measured inside the pipelined step (tools/ablate_step.py)
-// the attention launches cost 17 % of the step at every cloud size while running at 23 % of the mma.sync peak: the
-// conversion pass, two barriers per tile and the HBM latency of the score loads were all exposed.  Here
+// the attention launches cost 17 % of the step at every cloud size while running at 23 % of the mma.sync peak.  Here
 //   * K and V tiles are copied as they are (cp.async, 16 bytes) into padded half tiles: no conversion, half the bytes;
-//   * the additive scores of the CTA's queries x the tile's keys travel through the SAME multi-stage pipeline into a
-//     padded fp32 tile, and seed the accumulators of Q K^T (C operand) instead of being added afterwards;
-//   * 3 stages (4 without scores): tile t+2 is requested before tile t is consumed, ONE block barrier per tile;
+//   * the additive scores of the CTA's queries x the tile's keys travel through the SAME rings into a padded fp32
+//     tile, and seed the accumulators of Q K^T (C operand) instead of being added afterwards;
+//   * two 3-slot rings (K + scores + mask bias | V; 6 slots without scores): the copies of a tile are requested two
+//     steps before its Q K^T, ONE block barrier per tile, the per-thread copy pattern worked out once outside the loop
+//     (the first version spent 420 of its 850 instructions per tile on copy addressing);
+//   * software pipelining inside the warp: a step issues Q K^T of tile t+1 and then softmax + P V of tile t, two
+//     independent instruction streams in one basic block -- ptxas interleaves the HMMAs with the MUFU.EX2 / FFMA /
+//     FMNMX of the softmax (two tiles' logits live: ~240 registers, two 4-warp CTAs per SM);
 //   * the softmax works on raw logits (max first, then one FFMA + EX2 per weight).
+// Stand-alone (tools/att_time.py, graph replays, us per launch, with / without scores), H = 4, c = 64:
+//            n = 1024            n = 2048         n = 4096
+//   K3b      29.4 / 25.8         58.0 / 49.1      166.9 / 118.6      (one CTA per query tile walks all keys)
+//   K3h      16.1 / 13.0         30.3 / 23.8       80.6 /  64.9      (213 / 265 TFLOP/s at n = 4096)
+//   K3h, keys split over clusters (one forward at a time): 11.1 / 10.3 at n = 1024.
+// ncu at n = 1024 without key split (64 CTAs, one warp per scheduler): 493 instructions per warp and tile at 0.27 per
+// clock -- fixed-latency dependency stalls of a lone warp; 2.4 us of the launch are fixed, 0.87 us goes per tile.
+// Not kept (profiles/r02_k3h_notes.txt): deeper rings (2, 3 and 5 slots time the same), two warp groups per CTA on
+// alternate tiles (15.3 us against 16.0, slower inside the step), the 128-query / 8-warp CTA shape.
 // Key ranges are split over a thread-block cluster exactly as in K3b (partials merged through distributed shared memory).
 #include <cstdlib>
 #include <cuda_fp16.h>
@@ -25,6 +38,12 @@ namespace geotx {
 constexpr int AH_BK = 64;        // keys per tile
 constexpr int AH_SPITCH = 72;    // floats per row of the staged score tile: 8-byte fragment reads are conflict-free
 constexpr int AH_MAX_SPLITS = 8;
+#ifndef AH_SLOTS_SCORES
+#define AH_SLOTS_SCORES 3  // ring depth with a score tile per slot (27.9 KB + 9.2 KB per slot at c = 64, 64 queries)
+#endif
+#ifndef AH_SLOTS_PLAIN
+#define AH_SLOTS_PLAIN 6   // ring depth without scores (9.5 KB + 9.2 KB per slot)
+#endif
 
 __device__ __forceinline__ void ah_mma(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
     asm volatile(
@@ -65,13 +84,16 @@ struct AhSmem {
     static constexpr int HP = DH + 8;  // halves per K / V row: 16-byte aligned, pitch / 16 B odd -> ldmatrix conflict-free
     static constexpr int KV_BYTES = AH_BK * HP * 2;
     static constexpr int S_BYTES = SCORES ? BQ * AH_SPITCH * 4 : 0;
-    static constexpr int OFF_V = KV_BYTES, OFF_S = 2 * KV_BYTES, OFF_MB = OFF_S + S_BYTES;
-    static constexpr int STAGE = OFF_MB + AH_BK * 4;
-    static constexpr int STAGES = SCORES ? 3 : 4;
-    static constexpr int PO_PITCH = DH + 4;  // key-split merge: partial O [BQ][PO_PITCH] + (max, sum)[BQ] reuse the stages
+    // K ring slot: K tile | score tile | mask bias; SLOTS of them, then the V ring's SLOTS slots
+    static constexpr int OFF_S = KV_BYTES, OFF_MB = OFF_S + S_BYTES;
+    static constexpr int KS_STAGE = OFF_MB + AH_BK * 4;
+    static constexpr int SLOTS = SCORES ? AH_SLOTS_SCORES : AH_SLOTS_PLAIN;  // K ring and V ring depth
+    static constexpr int OFF_VRING = SLOTS * KS_STAGE;
+    static constexpr int RING_BYTES = OFF_VRING + SLOTS * KV_BYTES;
+    static constexpr int PO_PITCH = DH + 4;  // key-split merge: partial O [BQ][PO_PITCH] + (max, sum)[BQ] reuse the rings
     static constexpr int MERGE_BYTES = (BQ * PO_PITCH + BQ * 2) * 4;
-    static constexpr int BYTES = STAGES * STAGE > MERGE_BYTES ? STAGES * STAGE : MERGE_BYTES;
-    static_assert(STAGE % 16 == 0, "stage alignment");
+    static constexpr int BYTES = RING_BYTES > MERGE_BYTES ? RING_BYTES : MERGE_BYTES;
+    static_assert(KS_STAGE % 16 == 0, "slot alignment");
 };
 
 struct AhParams {
@@ -86,22 +108,25 @@ struct AhParams {
     int tiles_per_split;
 };
 
-// CTAs per SM the launch bounds ask for: the 4-warp shape with scores is limited to 2 by shared memory (3 x 37 KB each);
-// without scores 3 fit (4 x 18.7 KB and <= 168 registers)
-__host__ __device__ constexpr int ah_ctas_per_sm(int warps, bool scores) { return warps <= 4 ? (scores ? 2 : 3) : 1; }
+// CTAs per SM the launch bounds ask for: two of the 4-warp shape (111 KB of shared memory each with scores; ~220
+// registers: two tiles' logits are live at a time), one of the 8-warp shape
+__host__ __device__ constexpr int ah_ctas_per_sm(int warps, bool scores) {
+    return warps <= 4 && (scores ? AH_SLOTS_SCORES : AH_SLOTS_PLAIN) <= (scores ? 3 : 6) ? 2 : 1;
+}
 
 template <int DH, int WARPS, bool SCORES>
 __global__ void __launch_bounds__(32 * WARPS, ah_ctas_per_sm(WARPS, SCORES))
 attention_f16_kernel(const __grid_constant__ AhParams prm) {
     using SM = AhSmem<DH, WARPS, SCORES>;
-    constexpr int BQ = SM::BQ, THREADS = 32 * WARPS, HP = SM::HP, STAGES = SM::STAGES;
+    constexpr int BQ = SM::BQ, THREADS = 32 * WARPS, HP = SM::HP;
     constexpr int KS = DH / 16;  // k16 steps of q.k^T
     constexpr int NT = DH / 8;   // 8-wide n-tiles of the output
     constexpr int CH = DH / 8;   // 16-byte chunks per K / V row
     extern __shared__ __align__(16) uint8_t ah_smem[];
+    const int tid = threadIdx.x;
     const uint32_t smem0 = smem_u32(ah_smem);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
     const int H = prm.H, n = prm.n, m = prm.m;
     const int bh = blockIdx.y;
@@ -111,50 +136,80 @@ attention_f16_kernel(const __grid_constant__ AhParams prm) {
     const int ld = H * DH;
     const int r0 = q0 + g, r1 = q0 + g + 8;  // the two query rows this thread holds fragments of
     const int num_tiles = (m + AH_BK - 1) / AH_BK;
-    const int tile_begin = blockIdx.z * prm.tiles_per_split;
-    const int tile_end = min(num_tiles, tile_begin + prm.tiles_per_split);
+    const int tile_first = blockIdx.z * prm.tiles_per_split;
+    const int tile_end = min(num_tiles, tile_first + prm.tiles_per_split);
     const bool sp_vec = (m & 3) == 0;  // 16-byte copies need 16-byte aligned score rows
 
-    auto issue_tile = [&](int tile, int stage) {
+    // Tile requests, kept lean (one or two warps per scheduler run this between two tiles' math): every thread copies the
+    // same (row, 16-byte chunk) positions of every tile, so the positions are worked out once, here.
+    constexpr int KV_CHUNKS = AH_BK * CH;                         // 16-byte chunks of one K (or V) tile
+    constexpr int KV_ROWS_PER_IT = THREADS / CH;                  // rows between a thread's successive chunks
+    constexpr int KV_IT = (KV_CHUNKS + THREADS - 1) / THREADS;
+    constexpr int S_ROWS_PER_IT = THREADS / (AH_BK / 4);          // score tile: 16 chunks per row
+    constexpr int S_IT = BQ / S_ROWS_PER_IT;                      // = 8
+    static_assert(THREADS % CH == 0 && BQ % S_ROWS_PER_IT == 0, "copy pattern");
+    const int kv_c8 = tid % CH, kv_row = tid / CH;
+    const __half* const k_col = prm.k + (size_t)b * m * prm.ldk + h * DH + 8 * kv_c8;
+    const __half* const v_col = prm.v + (size_t)b * m * prm.ldv + h * DH + 8 * kv_c8;
+    const uint32_t kv_dst = (kv_row * HP + 8 * kv_c8) * 2;
+    const int s_c4 = tid % (AH_BK / 4), s_row = tid / (AH_BK / 4);
+    const float* const sp_head = SCORES ? prm.scores_p + ((size_t)b * H + h) * n * (size_t)m : nullptr;
+    const uint32_t s_dst = SM::OFF_S + (s_row * AH_SPITCH + 4 * s_c4) * 4;
+
+    // one K (or V) tile: rows past the end of the cloud are zero-filled
+    auto issue_rows = [&](const __half* col, int ld_rows, int tile, uint32_t dst) {
         const int j0 = tile * AH_BK;
-        const uint32_t base = smem0 + stage * SM::STAGE;
-        for (int idx = threadIdx.x; idx < AH_BK * CH; idx += THREADS) {
-            const int row = idx / CH, c8 = idx - row * CH;
-            const int j = j0 + row;
-            const size_t tok = (size_t)b * m + min(j, m - 1);
-            const uint32_t nbytes = j < m ? 16u : 0u;
-            const uint32_t off = (row * HP + 8 * c8) * 2;
-            ah_cp16(base + off, prm.k + tok * prm.ldk + h * DH + 8 * c8, nbytes);
-            ah_cp16(base + SM::OFF_V + off, prm.v + tok * prm.ldv + h * DH + 8 * c8, nbytes);
+        const int last = m - 1 - j0;  // tile-local index of the cloud's last key (>= 63 for a full tile)
+        const __half* const src = col + (size_t)j0 * ld_rows;
+#pragma unroll
+        for (int it = 0; it < KV_IT; ++it) {
+            const int row = kv_row + it * KV_ROWS_PER_IT;
+            if (KV_CHUNKS % THREADS == 0 || row < AH_BK)
+                ah_cp16(dst + kv_dst + it * (KV_ROWS_PER_IT * HP * 2), src + min(row, last) * ld_rows, row <= last ? 16u : 0u);
         }
+    };
+    // K tile + the additive scores of the CTA's queries against its keys + the keys' mask bias -> slot of the K ring
+    auto issue_ks = [&](int tile, int slot) {
+        if (tile >= tile_end) return;
+        const uint32_t base = smem0 + slot * SM::KS_STAGE;
+        const int j0 = tile * AH_BK;
+        const int last = m - 1 - j0;
+        issue_rows(k_col, prm.ldk, tile, base);
         if (SCORES) {
-            const float* sp = prm.scores_p + ((size_t)b * H + h) * n * (size_t)m;
             if (sp_vec) {
-                for (int idx = threadIdx.x; idx < BQ * (AH_BK / 4); idx += THREADS) {
-                    const int row = idx / (AH_BK / 4), c4 = idx - row * (AH_BK / 4);
-                    const int j = j0 + 4 * c4;
-                    ah_cp16(base + SM::OFF_S + (row * AH_SPITCH + 4 * c4) * 4,
-                            sp + (size_t)min(qbase + row, n - 1) * m + min(j, m - 4), j < m ? 16u : 0u);
+                const int jc = 4 * s_c4;  // m % 4 == 0: a 4-key chunk is inside the cloud or outside, never across its end
+                const float* const sp_tile = sp_head + j0 + min(jc, last - 3);
+                const uint32_t nbytes = jc <= last ? 16u : 0u;
+#pragma unroll
+                for (int it = 0; it < S_IT; ++it) {
+                    const int qr = min(qbase + s_row + it * S_ROWS_PER_IT, n - 1);
+                    ah_cp16(base + s_dst + it * (S_ROWS_PER_IT * AH_SPITCH * 4), sp_tile + (size_t)qr * m, nbytes);
                 }
             } else {
-                for (int idx = threadIdx.x; idx < BQ * AH_BK; idx += THREADS) {
+                for (int idx = tid; idx < BQ * AH_BK; idx += THREADS) {
                     const int row = idx / AH_BK, c = idx - row * AH_BK;
-                    const int j = j0 + c;
-                    ah_cp4(base + SM::OFF_S + (row * AH_SPITCH + c) * 4, sp + (size_t)min(qbase + row, n - 1) * m + min(j, m - 1),
-                           j < m ? 4u : 0u);
+                    ah_cp4(base + SM::OFF_S + (row * AH_SPITCH + c) * 4,
+                           sp_head + (size_t)min(qbase + row, n - 1) * m + j0 + min(c, last), c <= last ? 4u : 0u);
                 }
             }
         }
-        if (threadIdx.x < AH_BK) {
-            const int j = j0 + threadIdx.x;
-            const bool dead = j >= m || (prm.key_mask && prm.key_mask[(size_t)b * m + j]);
-            asm volatile("st.shared.f32 [%0], %1;" ::"r"(base + SM::OFF_MB + threadIdx.x * 4), "f"(dead ? -INFINITY : 0.f) : "memory");
+        if (tid < AH_BK) {
+            const bool dead = tid > last || (prm.key_mask && prm.key_mask[(size_t)b * m + j0 + tid]);
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(base + SM::OFF_MB + tid * 4), "f"(dead ? -INFINITY : 0.f) : "memory");
         }
     };
+    auto issue_v = [&](int tile, int slot) {
+        if (tile < tile_end) issue_rows(v_col, prm.ldv, tile, smem0 + SM::OFF_VRING + slot * SM::KV_BYTES);
+    };
 
+    // cp.async groups (N = SLOTS): G(g) = {K/S(g), V(g)} for g <= N-2, G(N-1) = {K/S(N-1)}, then iteration i commits
+    // G(N+i) = {K/S(i+N), V(i+N-1)}: everything iteration i needs (K/S(i+1), V(i)) is in groups <= i+1, and N+i groups
+    // have been committed by then: wait_group N-2
+    constexpr int N = SM::SLOTS;
 #pragma unroll
-    for (int s = 0; s < STAGES - 1; ++s) {
-        if (tile_begin + s < tile_end) issue_tile(tile_begin + s, s);
+    for (int g2 = 0; g2 < N; ++g2) {
+        issue_ks(tile_first + g2, g2);
+        if (g2 < N - 1) issue_v(tile_first + g2, g2);
         ah_commit();
     }
 
@@ -178,55 +233,73 @@ attention_f16_kernel(const __grid_constant__ AhParams prm) {
     const float scale_log2e = prm.scale_log2e;
     const bool any_mask = prm.key_mask != nullptr;
 
-    for (int tile = tile_begin; tile < tile_end; ++tile) {
-        const int i = tile - tile_begin;
-        ah_wait<STAGES - 2>();  // this thread's copies of tile i have landed ...
-        __syncthreads();        // ... everybody's have; and every warp is done with tile i-1, whose stage is refilled now
-        if (tile + STAGES - 1 < tile_end) issue_tile(tile + STAGES - 1, (i + STAGES - 1) % STAGES);
-        ah_commit();
-        const uint32_t base = smem0 + (i % STAGES) * SM::STAGE;
-        const uint32_t Kh = base, Vh = base + SM::OFF_V;
-
-        // ---- S = scores_p tile + Q K^T : 8 key n-tiles x KS k-steps.  B frag (k = channel, n = key) straight from the
-        //      row-major half tile: ldmatrix matrix j = channels 8j..8j+7 of keys 8nt..8nt+7 ----
-        float s[AH_BK / 8][4];
+    // ---- S = scores_p tile + Q K^T : 8 key n-tiles x KS k-steps.  The staged scores seed the accumulators (C operand).
+    //      B frag (k = channel, n = key) straight from the row-major half tile: ldmatrix matrix j = channels 8j..8j+7 of
+    //      keys 8nt..8nt+7 ----
+    auto qk = [&](float (&s)[AH_BK / 8][4], uint32_t ks_base) {
 #pragma unroll
         for (int nt = 0; nt < AH_BK / 8; ++nt) {
             if (SCORES) {  // C frag: (g, 2t) (g, 2t+1) (g+8, 2t) (g+8, 2t+1)
-                const uint32_t a = base + SM::OFF_S + ((warp * 16 + g) * AH_SPITCH + nt * 8 + 2 * t) * 4;
+                const uint32_t a = ks_base + SM::OFF_S + ((warp * 16 + g) * AH_SPITCH + nt * 8 + 2 * t) * 4;
                 asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(s[nt][0]), "=f"(s[nt][1]) : "r"(a));
                 asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(s[nt][2]), "=f"(s[nt][3]) : "r"(a + 8 * AH_SPITCH * 4));
             } else {
                 s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
             }
-            if (KS >= 2) {
+        }
+        if (KS >= 2) {  // k-step outer, key n-tile inner: eight independent accumulator chains in flight
 #pragma unroll
-                for (int ks2 = 0; ks2 < KS / 2; ++ks2) {
+            for (int ks2 = 0; ks2 < KS / 2; ++ks2) {
+#pragma unroll
+                for (int nt = 0; nt < AH_BK / 8; ++nt) {
                     uint32_t b0, b1, b2, b3;
-                    ah_ldsm4(Kh + ((nt * 8 + (lane & 7)) * HP + 32 * ks2 + 8 * (lane >> 3)) * 2, b0, b1, b2, b3);
+                    ah_ldsm4(ks_base + ((nt * 8 + (lane & 7)) * HP + 32 * ks2 + 8 * (lane >> 3)) * 2, b0, b1, b2, b3);
                     ah_mma(s[nt], qa[2 * ks2], b0, b1);
                     ah_mma(s[nt], qa[(2 * ks2 + 1) % KS], b2, b3);
                 }
-            } else {
+            }
+        } else {
+#pragma unroll
+            for (int nt = 0; nt < AH_BK / 8; ++nt) {
                 uint32_t b0, b1;
-                ah_ldsm2(Kh + ((nt * 8 + (lane & 7)) * HP + 8 * ((lane >> 3) & 1)) * 2, b0, b1);
+                ah_ldsm2(ks_base + ((nt * 8 + (lane & 7)) * HP + 8 * ((lane >> 3) & 1)) * 2, b0, b1);
                 ah_mma(s[nt], qa[0], b0, b1);
             }
         }
-        // ---- mask (only tiles that have dead keys pay for it), running max on the raw logits ----
-        if (any_mask || tile * AH_BK + AH_BK > m) {
+    };
+    // dead keys -> -inf (only tiles that have some pay for it)
+    auto mask_add = [&](float (&s)[AH_BK / 8][4], uint32_t ks_base, int tile) {
+        if (tile < tile_end && (any_mask || tile * AH_BK + AH_BK > m)) {
 #pragma unroll
             for (int nt = 0; nt < AH_BK / 8; ++nt) {
                 float mb0, mb1;
-                asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(mb0), "=f"(mb1) : "r"(base + SM::OFF_MB + (nt * 8 + 2 * t) * 4));
+                asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(mb0), "=f"(mb1) : "r"(ks_base + SM::OFF_MB + (nt * 8 + 2 * t) * 4));
                 s[nt][0] += mb0; s[nt][1] += mb1; s[nt][2] += mb0; s[nt][3] += mb1;
             }
         }
+    };
+
+    // One tile step.  `cur` holds the raw logits of tile `tile` (computed one step earlier); the step computes the logits
+    // of tile + 1 into `nxt` -- independent tensor-pipe work that overlaps this tile's softmax (FMNMX / FFMA / MUFU.EX2)
+    // in the same basic block -- then O += P V.  The K ring holds K/S(tile+1 .. tile+N-1) [the later ones in flight], the
+    // slot of K/S(tile) is refilled with tile + N; the V ring holds V(tile .. tile+N-2) and refills V(tile-1)'s slot.
+    auto step = [&](float (&cur)[AH_BK / 8][4], float (&nxt)[AH_BK / 8][4], int tile, int r) {
+        const int r1 = r == N - 1 ? 0 : r + 1, rp = r == 0 ? N - 1 : r - 1;
+        ah_wait<N - 2>();  // this thread's copies of K/S(next tile) and V(tile) have landed ...
+        __syncthreads();   // ... everybody's have; and every warp is done with K/S(tile) and V(previous tile)
+        issue_ks(tile + N, r);
+        issue_v(tile + N - 1, rp);
+        ah_commit();
+        const uint32_t ks_next = smem0 + r1 * SM::KS_STAGE;
+        const uint32_t Vh = smem0 + SM::OFF_VRING + r * SM::KV_BYTES;
+        qk(nxt, ks_next);  // past the last tile this reads a stale slot: finite work on garbage, discarded
+
+        // ---- running max on the raw logits, weights, running sum ----
         float tmax0 = -INFINITY, tmax1 = -INFINITY;
 #pragma unroll
         for (int nt = 0; nt < AH_BK / 8; ++nt) {
-            tmax0 = fmaxf(tmax0, fmaxf(s[nt][0], s[nt][1]));
-            tmax1 = fmaxf(tmax1, fmaxf(s[nt][2], s[nt][3]));
+            tmax0 = fmaxf(tmax0, fmaxf(cur[nt][0], cur[nt][1]));
+            tmax1 = fmaxf(tmax1, fmaxf(cur[nt][2], cur[nt][3]));
         }
         tmax0 = fmaxf(tmax0, __shfl_xor_sync(0xffffffffu, tmax0, 1));
         tmax0 = fmaxf(tmax0, __shfl_xor_sync(0xffffffffu, tmax0, 2));
@@ -240,10 +313,10 @@ attention_f16_kernel(const __grid_constant__ AhParams prm) {
         float ps0 = 0.f, ps1 = 0.f;
 #pragma unroll
         for (int nt = 0; nt < AH_BK / 8; ++nt) {
-            s[nt][0] = ah_exp2(fmaf(s[nt][0], scale_log2e, -sub0)); s[nt][1] = ah_exp2(fmaf(s[nt][1], scale_log2e, -sub0));
-            s[nt][2] = ah_exp2(fmaf(s[nt][2], scale_log2e, -sub1)); s[nt][3] = ah_exp2(fmaf(s[nt][3], scale_log2e, -sub1));
-            ps0 += s[nt][0] + s[nt][1];
-            ps1 += s[nt][2] + s[nt][3];
+            cur[nt][0] = ah_exp2(fmaf(cur[nt][0], scale_log2e, -sub0)); cur[nt][1] = ah_exp2(fmaf(cur[nt][1], scale_log2e, -sub0));
+            cur[nt][2] = ah_exp2(fmaf(cur[nt][2], scale_log2e, -sub1)); cur[nt][3] = ah_exp2(fmaf(cur[nt][3], scale_log2e, -sub1));
+            ps0 += cur[nt][0] + cur[nt][1];
+            ps1 += cur[nt][2] + cur[nt][3];
         }
         sum0 = sum0 * corr0 + ps0;
         sum1 = sum1 * corr1 + ps1;
@@ -257,10 +330,10 @@ attention_f16_kernel(const __grid_constant__ AhParams prm) {
         for (int kk = 0; kk < AH_BK / 16; ++kk) {
             uint32_t pf[4];
             {
-                const __half2 h0 = __floats2half2_rn(s[2 * kk][0], s[2 * kk][1]);
-                const __half2 h1 = __floats2half2_rn(s[2 * kk][2], s[2 * kk][3]);
-                const __half2 h2 = __floats2half2_rn(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-                const __half2 h3 = __floats2half2_rn(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+                const __half2 h0 = __floats2half2_rn(cur[2 * kk][0], cur[2 * kk][1]);
+                const __half2 h1 = __floats2half2_rn(cur[2 * kk][2], cur[2 * kk][3]);
+                const __half2 h2 = __floats2half2_rn(cur[2 * kk + 1][0], cur[2 * kk + 1][1]);
+                const __half2 h3 = __floats2half2_rn(cur[2 * kk + 1][2], cur[2 * kk + 1][3]);
                 pf[0] = *(const uint32_t*)&h0; pf[1] = *(const uint32_t*)&h1;
                 pf[2] = *(const uint32_t*)&h2; pf[3] = *(const uint32_t*)&h3;
             }
@@ -272,6 +345,23 @@ attention_f16_kernel(const __grid_constant__ AhParams prm) {
                 ah_mma(o[2 * nt2], pf, b0, b1);
                 ah_mma(o[2 * nt2 + 1], pf, b2, b3);
             }
+        }
+        mask_add(nxt, ks_next, tile + 1);
+    };
+
+    float sA[AH_BK / 8][4], sB[AH_BK / 8][4];
+    ah_wait<N - 1>();  // G0: K/S and V of the first tile
+    __syncthreads();
+    qk(sA, smem0);
+    mask_add(sA, smem0, tile_first);
+    {
+        int r = 0;
+        for (int tile = tile_first; tile < tile_end; tile += 2) {
+            step(sA, sB, tile, r);
+            r = r == N - 1 ? 0 : r + 1;
+            if (tile + 1 >= tile_end) break;
+            step(sB, sA, tile + 1, r);
+            r = r == N - 1 ? 0 : r + 1;
         }
     }
     ah_wait<0>();
@@ -388,13 +478,15 @@ static void ah_plan(int B, int H, int n, int m, int warps, bool scores, int allo
 template <int DH, int WARPS, bool SCORES>
 static int ah_launch(AhParams prm, int B, int allow_split, cudaStream_t st) {
     using SM = AhSmem<DH, WARPS, SCORES>;
+    constexpr int SMEM_BYTES = SM::BYTES;
     static bool opted_in[64] = {};
     int dev = 0;
     int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
     if (rc) return rc;
     if (dev < 0 || dev >= 64 || !opted_in[dev]) {
-        rc = check_cuda(cudaFuncSetAttribute(attention_f16_kernel<DH, WARPS, SCORES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             SM::BYTES), "cudaFuncSetAttribute(attention_f16_kernel)");
+        rc = check_cuda(cudaFuncSetAttribute(attention_f16_kernel<DH, WARPS, SCORES>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES),
+                        "cudaFuncSetAttribute(attention_f16_kernel)");
         if (rc) return rc;
         if (dev >= 0 && dev < 64) opted_in[dev] = true;
     }
@@ -404,7 +496,7 @@ static int ah_launch(AhParams prm, int B, int allow_split, cudaStream_t st) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((prm.n + 16 * WARPS - 1) / (16 * WARPS), B * prm.H, splits);
     cfg.blockDim = dim3(32 * WARPS, 1, 1);
-    cfg.dynamicSmemBytes = SM::BYTES;
+    cfg.dynamicSmemBytes = SMEM_BYTES;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -412,26 +504,18 @@ static int ah_launch(AhParams prm, int B, int allow_split, cudaStream_t st) {
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = splits;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    rc = check_cuda(cudaLaunchKernelEx(&cfg, attention_f16_kernel<DH, WARPS, SCORES>, prm), "cudaLaunchKernelEx(attention_f16_kernel)");
+    cfg.numAttrs = splits > 1 ? 1 : 0;  // a plain launch when nothing is split
+    rc = check_cuda(cudaLaunchKernelEx(&cfg, attention_f16_kernel<DH, WARPS, SCORES>, prm),
+                    "cudaLaunchKernelEx(attention_f16_kernel)");
     if (rc) return rc;
     return launch_status("geotx_attention_f16");
 }
 
 template <int DH>
 static int ah_launch_shape(const AhParams& prm, int B, int allow_split, cudaStream_t st) {
-    // split_keys != 0 (one forward at a time): 64-query CTAs (4 warps, two or three per SM) while there are fewer than
-    // AH_BIG_THRESHOLD 128-query tiles, 128-query CTAs (8 warps, one per SM: every K/V tile is fetched once per 128
-    // queries) from there on -- K3b's rule.  split_keys == 0 (several forwards in flight, SM-time counts): always the
-    // 64-query shape (3DMatch 4096, 2 graph instances in flight: 103.7 -> 105.6 pairs/s; 1024 without key splits,
-    // 4 in flight: 1363 -> 1407)
-    const long long big = (long long)((prm.n + 127) / 128) * B * prm.H;
-#ifndef AH_BIG_THRESHOLD
-#define AH_BIG_THRESHOLD 128
-#endif
-    static const int big_threshold = env_int("GEOTX_ATT_BIG", AH_BIG_THRESHOLD, 1, 1 << 30);  // timing experiments
-    if (allow_split && big >= big_threshold)
-        return prm.scores_p ? ah_launch<DH, 8, true>(prm, B, allow_split, st) : ah_launch<DH, 8, false>(prm, B, allow_split, st);
+    // One CTA shape: 64 queries, 4 warps, two CTAs per SM.  K3b's 128-query / 8-warp shape (every K/V tile fetched once
+    // per 128 queries) lost here: stand-alone at n = 4096, 92.6 us against 80.6 us (tools/att_time.py) -- K and V are
+    // half the bytes and L2-resident, while two independent CTAs per SM desynchronise their barrier / softmax phases.
     return prm.scores_p ? ah_launch<DH, 4, true>(prm, B, allow_split, st) : ah_launch<DH, 4, false>(prm, B, allow_split, st);
 }
 
