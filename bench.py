@@ -11,8 +11,8 @@ steps of all ranks are gathered with one NCCL all_gather inside the timed region
 Prints ONE JSON line on rank 0.
 
   value      pairs/s, inputs resident in HBM, CUDA-event timed, max over ranks; up to n = 2048 several CUDA-graph instances
-             of the forward are in flight on their own streams (independent pairs overlap; GEOTX_INFLIGHT, default 4:
-             measured 1040 / 1086 / 1102 / 1097 pairs/s with 2 / 3 / 4 / 5)
+             of the forward are in flight on their own streams (independent pairs overlap; GEOTX_INFLIGHT, default 6 up
+             to n = 1024: measured 1390 / 1436 / 1447 / 1455 / 1454 pairs/s with 3 / 4 / 5 / 6 / 8; 4 at 2048, 3 at 4096)
   e2e        pairs/s through PipelinedGeometricTransformer.map with HOST (pinned) inputs and a host read of the outputs
   roofline   the dominant kernel of the default path, K3r (geotx_rpe_scores_cheb: low-rank embedding + folded-query
              scores, E never stored), timed by CUDA events captured inside the forward's graph: flops the kernel
@@ -610,6 +610,11 @@ def measure_mma_sync_peak(pkg, torch, dev):
         return None
 
 
+def default_inflight(n):
+    """CUDA-graph instances of the forward kept in flight at cloud size n (measured, see run_b200)."""
+    return 6 if n <= 1024 else 4 if n <= 2048 else 3 if n <= 4096 else 1
+
+
 def timed_value(torch, fast, resident, n_pairs, steps, warm):
     fast.run(resident, n_pairs, warm)
     torch.cuda.synchronize()
@@ -774,11 +779,11 @@ def run_b200(args):
                 'avg_launch_ms': ms, 'launches_per_step': d['launches_per_step'],
                 'share_of_step': sum(d['ms_per_launch']) / step_ms if step_ms else None}
 
-    # graph instances in flight (independent pairs overlap): 4 up to n = 2048, 2 at 4096 (measured 91.7 -> 96.5 pairs/s;
-    # 3: 96.2), 1 above
+    # graph instances in flight (independent pairs overlap; tools/ablate_step.py --inflight): 6 up to n = 1024 (1436 ->
+    # 1455 pairs/s against 4), 4 at 2048 (6: the same), 3 at 4096 (105.8 -> 108.0 against 2; 4: 108.0), 1 above
     many = max(n, m) <= 2048
     mid = not many and max(n, m) <= 4096
-    inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', '4' if many else '2'))) if (many or mid) else 1
+    inflight = max(1, int(os.environ.get('GEOTX_INFLIGHT', str(default_inflight(max(n, m)))))) if (many or mid) else 1
 
     def run_variant(tag, setup, undo, steps, want_kernels=True):
         """The same forward under another configuration: value (graph replay, CUDA events) + its kernel table."""
@@ -887,7 +892,7 @@ def run_b200(args):
 
         # ---- end to end: host (pinned) inputs -> device -> forward -> host outputs, every step, through the serving
         #      API (PipelinedGeometricTransformer: the upload of pair p+1 / download of pair p-1 overlap pair p) ----
-        depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', '5' if many else '3'))) if (many or mid) else 2)
+        depth = 1 if big else (max(1, int(os.environ.get('GEOTX_PIPE_DEPTH', str(inflight + 1)))) if (many or mid) else 2)
         del fast
         torch.cuda.empty_cache()
         pipe = pkg.PipelinedGeometricTransformer(model, *resident[0], depth=depth)
@@ -973,7 +978,7 @@ def run_b200(args):
                         for tag, e_mode, kernel in (('default', 'auto', 'cheb'), ('tensor_embedding', 'store', 'tensor')):
                             s_model.e_mode, s_model.embedding.embed_kernel = e_mode, kernel
                             s_model(*s_res[0])
-                            s_inflight = (4 if max(s_n, s_m) <= 2048 else 2 if max(s_n, s_m) <= 4096 else 1) if inflight > 1 else 1  # the rule of the main line
+                            s_inflight = default_inflight(max(s_n, s_m)) if inflight > 1 else 1  # the rule of the main line
                             sf = InFlight(pkg, s_model, s_res[0], s_inflight)
                             s_ms, _ = timed_value(torch, sf, s_res, 2, ssteps, max(3, 2 * s_inflight))
                             del sf

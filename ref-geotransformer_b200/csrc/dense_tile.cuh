@@ -82,14 +82,19 @@ struct DtRing {
 
 // One GEMM of a token tile: acc[mt][nt] (2 m-tiles x NT n-tiles: the 8 NT columns of this warp that start at row
 // `n_warp` of the staged chunk) += A (shared memory, half, row pitch a_pitch bytes, K from column 0) x W^T, over
-// `chunks` K chunks whose flat numbers start at g0.
-template <int NT>
-__device__ __forceinline__ void dt_gemm(float (&acc)[2][NT][4], const DtRing& ring, int g0, int chunks, uint32_t a_addr,
-                                        int a_pitch, int n_warp, int lane) {
+// `entries` ring entries whose flat numbers start at g0.  A ring entry holds SUB consecutive K chunks of the packed
+// weight (they are contiguous in memory: one bulk copy), `sub_bytes` apart: one wait / fence / release per entry.
+template <int NT, int SUB = 1>
+__device__ __forceinline__ void dt_gemm(float (&acc)[2][NT][4], const DtRing& ring, int g0, int entries, uint32_t a_addr,
+                                        int a_pitch, int n_warp, int lane, uint32_t sub_bytes = 0) {
     const int brow = n_warp + (lane & 7) + ((lane >> 4) & 1) * 8;  // + 16 np: this lane's row of an n-tile pair
     const int bunit = (lane >> 3) & 1;                             // + 2 ks: its 16-byte unit
-    for (int c = 0; c < chunks; ++c) {
-        const uint32_t w_addr = ring.wait(g0 + c);
+    for (int c0 = 0; c0 < entries; ++c0) {
+      const uint32_t w_entry = ring.wait(g0 + c0);
+#pragma unroll
+      for (int sub = 0; sub < SUB; ++sub) {
+        const int c = c0 * SUB + sub;  // K chunk
+        const uint32_t w_addr = w_entry + sub * sub_bytes;
 #pragma unroll
         for (int ks = 0; ks < DT_KC / 16; ++ks) {
             uint32_t a[2][4];
@@ -115,7 +120,8 @@ __device__ __forceinline__ void dt_gemm(float (&acc)[2][NT][4], const DtRing& ri
                 for (int mt = 0; mt < 2; ++mt) dt_mma(acc[mt][NT - 1], a[mt], b[0], b[1]);
             }
         }
-        ring.release(g0 + c, lane);
+      }
+      ring.release(g0 + c0, lane);
     }
 }
 

@@ -62,19 +62,20 @@ __global__ void __launch_bounds__(DT_THREADS) linear_tile_kernel(const LinearArg
         return;
     }
 
-    // the tile's tokens -> half A operand, once.  Eight independent 16-byte loads in flight per thread: at K = 1024 the
+    // the tile's tokens -> half A operand, once.  Sixteen independent 16-byte loads in flight per thread: at K = 1024 the
     // tile is 128 KB of fp32 from L2 / HBM, and a loop of dependent load -> convert -> store steps is latency-bound
     const int k4 = p.K / 4, total4 = DT_BM * k4;
-    for (int e0 = tid; e0 < total4; e0 += 8 * DT_WARPS * 32) {
-        float4 v[8];
+    constexpr int U = 16;  // loads in flight per thread (8: in_proj's tile, 32 float4 per thread, paid four round trips)
+    for (int e0 = tid; e0 < total4; e0 += U * DT_WARPS * 32) {
+        float4 v[U];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < U; ++u) {
             const int e = e0 + u * DT_WARPS * 32, r = e / k4, c4 = e - r * k4;
             v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (e < total4 && row0 + r < p.T) v[u] = __ldg(reinterpret_cast<const float4*>(p.x + (size_t)(row0 + r) * p.ld_x) + c4);
         }
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < U; ++u) {
             const int e = e0 + u * DT_WARPS * 32, r = e / k4, c4 = e - r * k4;
             if (e < total4)
                 asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * a_pitch + c4 * 8), "r"(dt_pack(v[u].x, v[u].y)),
@@ -92,12 +93,16 @@ __global__ void __launch_bounds__(DT_THREADS) linear_tile_kernel(const LinearArg
         return;
     }
     float acc[2][NT][4] = {};
-    dt_gemm<NT>(acc, ring, 0, chunks, sA, a_pitch, n_warp, lane);
     const int g = lane >> 2, q = lane & 3;
+    float2 bias_r[NT];  // fetched before the GEMM (their L2 latency used to sit in front of the epilogue)
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+        bias_r[nt] = p.bias ? __ldg(reinterpret_cast<const float2*>(p.bias + n0 + n_warp + nt * 8 + 2 * q)) : make_float2(0.f, 0.f);
+    dt_gemm<NT>(acc, ring, 0, chunks, sA, a_pitch, n_warp, lane);
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
         const int col = n0 + n_warp + nt * 8 + 2 * q;
-        const float2 b = p.bias ? __ldg(reinterpret_cast<const float2*>(p.bias + col)) : make_float2(0.f, 0.f);
+        const float2 b = bias_r[nt];
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll

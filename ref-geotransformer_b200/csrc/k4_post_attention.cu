@@ -53,9 +53,18 @@ struct PACfg {
     static constexpr int OFF_X = OFF_E + DT_BM * E_PITCH;
     static constexpr int OFF_W = (OFF_X + DT_BM * X_PITCH * 4 + 127) / 128 * 128;
     static constexpr int SMEM = OFF_W + DT_STAGES * STAGE_BYTES;
-    // chunk schedule: GEMM 0 (linear: N = C, K = C), 1 (expand: N = 2C, K = C), 2 (squeeze: N = C, K = 2C)
-    static constexpr int CH0 = C / DT_KC, CH1 = C / DT_KC, CH2 = 2 * C / DT_KC, CHUNKS = CH0 + CH1 + CH2;
+    // ring schedule: GEMM 0 (linear: N = C, K = C), 1 (expand: N = 2C, K = C), 2 (squeeze: N = C, K = 2C).  A ring entry
+    // is one stage = 2C rows x one K chunk for GEMM 1, C rows x TWO K chunks for GEMMs 0 and 2 (same bytes, half the
+    // waits / fences / releases: a chunk of an N = C GEMM cost 500 clocks against 256 of HMMA, tools/k4f_phases.py)
+    static constexpr int CH0 = C / DT_KC / 2, CH1 = C / DT_KC, CH2 = 2 * C / DT_KC / 2, CHUNKS = CH0 + CH1 + CH2;
 };
+
+#ifdef PA_PHASE_CLOCKS  // timing experiment: clock64 of CTA 0 / warp 0 at the phase boundaries (tools/k4f_phases.py)
+__device__ long long pa_phase_clock[16];
+#define PA_MARK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) pa_phase_clock[i] = clock64(); } while (0)
+#else
+#define PA_MARK(i) do { } while (0)
+#endif
 
 template <int C>
 __global__ void __launch_bounds__(DT_THREADS, 1) post_attention_kernel(const PostAttnArgs p) {
@@ -72,63 +81,111 @@ __global__ void __launch_bounds__(DT_THREADS, 1) post_attention_kernel(const Pos
     ring.bar_empty = ring.bar_full + 8 * DT_STAGES;
     ring.stages = s_base + Cfg::OFF_W;
     ring.stage_bytes = Cfg::STAGE_BYTES;
+    PA_MARK(0);
     ring.init(tid);
     __syncthreads();
 
     if (warp == DT_WARPS) {  // ---- loader: the three matrices' chunks, in schedule order, one bulk copy each ----
         if (lane == 0) {
             for (int c = 0; c < Cfg::CHUNKS; ++c) {
-                if (c < Cfg::CH0) ring.load(c, p.w_lin + (size_t)c * C * DT_KC, C * DT_ROW_BYTES);
+                if (c < Cfg::CH0) ring.load(c, p.w_lin + (size_t)c * 2 * C * DT_KC, 2 * C * DT_ROW_BYTES);
                 else if (c < Cfg::CH0 + Cfg::CH1) ring.load(c, p.w_exp + (size_t)(c - Cfg::CH0) * 2 * C * DT_KC, 2 * C * DT_ROW_BYTES);
-                else ring.load(c, p.w_sq + (size_t)(c - Cfg::CH0 - Cfg::CH1) * C * DT_KC, C * DT_ROW_BYTES);
+                else ring.load(c, p.w_sq + (size_t)(c - Cfg::CH0 - Cfg::CH1) * 2 * C * DT_KC, 2 * C * DT_ROW_BYTES);
             }
         }
         return;
     }
 
-    // the tile's attention output -> half A operand
-    for (int e = tid; e < DT_BM * (C / 4); e += DT_WARPS * 32) {
-        const int r = e / (C / 4), c4 = e % (C / 4);
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row0 + r < p.T) v = __ldg(reinterpret_cast<const float4*>(p.hidden + (size_t)(row0 + r) * p.ld_hidden) + c4);
-        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(dt_pack(v.x, v.y)),
-                     "r"(dt_pack(v.z, v.w)) : "memory");
+    // Prologue, one L2 round trip for everything: the residual rows x_in go straight into sX (cp.async; GEMM 0's epilogue
+    // adds them there), and the tile's attention output is fetched with all of a thread's loads in flight before the first
+    // conversion to the half A operand (a load -> convert -> store loop pays the L2 latency once per iteration: 14 % of
+    // the kernel's stall samples sat on its first F2FP).
+    constexpr int C4 = C / 4, PER_THREAD = DT_BM * C4 / (DT_WARPS * 32);
+    static_assert(DT_BM * C4 % (DT_WARPS * 32) == 0, "tile loads divide evenly over the compute threads");
+#pragma unroll
+    for (int u = 0; u < PER_THREAD; ++u) {
+        const int e = tid + u * DT_WARPS * 32, r = e / C4, c4 = e - r * C4;
+        const int rr = min(row0 + r, p.T - 1);  // rows past the end: any valid row (their results are never stored)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s_base + Cfg::OFF_X + (r * Cfg::X_PITCH + c4 * 4) * 4),
+                     "l"(p.x_in + (size_t)rr * p.ld_x + c4 * 4) : "memory");
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    {
+        float4 v[PER_THREAD];
+#pragma unroll
+        for (int u = 0; u < PER_THREAD; ++u) {
+            const int e = tid + u * DT_WARPS * 32, r = e / C4, c4 = e - r * C4;
+            v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row0 + r < p.T) v[u] = __ldg(reinterpret_cast<const float4*>(p.hidden + (size_t)(row0 + r) * p.ld_hidden) + c4);
+        }
+#pragma unroll
+        for (int u = 0; u < PER_THREAD; ++u) {
+            const int e = tid + u * DT_WARPS * 32, r = e / C4, c4 = e - r * C4;
+            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sA + r * Cfg::A_PITCH + c4 * 8), "r"(dt_pack(v[u].x, v[u].y)),
+                         "r"(dt_pack(v[u].z, v[u].w)) : "memory");
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     dt_sync_compute();
+    PA_MARK(1);
 
-    // LayerNorm of the 32 rows staged in sX (fp32): warp w normalises rows 4w .. 4w+3, lane owns C / 32 channels
-    auto layer_norm = [&](const float* gamma, const float* beta, float eps, bool to_global) {
-        constexpr int PER = C / 32;
-#pragma unroll 1
-        for (int rr = 0; rr < DT_BM / 8; ++rr) {
-            const int r = warp * (DT_BM / 8) + rr;
-            float* row = sX + r * Cfg::X_PITCH;
-            float v[PER];
-            float sum = 0.f;
+    // LayerNorm of the 32 rows staged in sX (fp32): warp w normalises rows 4w .. 4w+3, lane owns C / 32 channels.  The
+    // four rows go through their two shuffle reductions TOGETHER (four independent chains per level instead of one: the
+    // row-at-a-time form cost 2500 clocks per LayerNorm, 18 % of the CTA's time, tools/k4f_phases.py), and gamma / beta
+    // are fetched once per LayerNorm, BEFORE the GEMM in front of it (ln_load), so that their L2 latency is not paid here.
+    constexpr int PER = C / 32, ROWS = DT_BM / 8;
+    struct LnW { float4 gm[PER / 4], bt[PER / 4]; };
+    auto ln_load = [&](const float* gamma, const float* beta, LnW& w) {
+#pragma unroll
+        for (int i = 0; i < PER / 4; ++i) {
+            w.gm[i] = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
+            w.bt[i] = __ldg(reinterpret_cast<const float4*>(beta) + lane + 32 * i);
+        }
+    };
+    auto layer_norm = [&](const LnW& w, float eps, bool to_global) {
+        const float4 (&gm)[PER / 4] = w.gm;
+        const float4 (&bt)[PER / 4] = w.bt;
+        float v[ROWS][PER], sum[ROWS], sq[ROWS];
+#pragma unroll
+        for (int rr = 0; rr < ROWS; ++rr) {
+            const float* row = sX + (warp * ROWS + rr) * Cfg::X_PITCH;
+            sum[rr] = 0.f;
 #pragma unroll
             for (int i = 0; i < PER / 4; ++i) {
                 const float4 t = *reinterpret_cast<const float4*>(row + (lane + 32 * i) * 4);
-                v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-                sum += (t.x + t.y) + (t.z + t.w);
+                v[rr][4 * i] = t.x; v[rr][4 * i + 1] = t.y; v[rr][4 * i + 2] = t.z; v[rr][4 * i + 3] = t.w;
+                sum[rr] += (t.x + t.y) + (t.z + t.w);
             }
+        }
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
-            const float mean = sum / (float)C;
-            float sq = 0.f;
+        for (int off = 16; off > 0; off >>= 1)
 #pragma unroll
-            for (int i = 0; i < PER; ++i) sq += (v[i] - mean) * (v[i] - mean);
+            for (int rr = 0; rr < ROWS; ++rr) sum[rr] += __shfl_xor_sync(0xffffffffu, sum[rr], off);
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, off);
-            const float rstd = rsqrtf(sq / (float)C + eps);
+        for (int rr = 0; rr < ROWS; ++rr) {
+            sum[rr] = sum[rr] / (float)C;  // mean
+            sq[rr] = 0.f;
+#pragma unroll
+            for (int i = 0; i < PER; ++i) sq[rr] += (v[rr][i] - sum[rr]) * (v[rr][i] - sum[rr]);
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+            for (int rr = 0; rr < ROWS; ++rr) sq[rr] += __shfl_xor_sync(0xffffffffu, sq[rr], off);
+#pragma unroll
+        for (int rr = 0; rr < ROWS; ++rr) {
+            const int r = warp * ROWS + rr;
+            float* row = sX + r * Cfg::X_PITCH;
+            const float mean = sum[rr];
+            const float rstd = rsqrtf(sq[rr] / (float)C + eps);
 #pragma unroll
             for (int i = 0; i < PER / 4; ++i) {
                 const int c4 = lane + 32 * i;
-                const float4 gm = __ldg(reinterpret_cast<const float4*>(gamma) + c4), bt = __ldg(reinterpret_cast<const float4*>(beta) + c4);
                 float4 o;
-                o.x = (v[4 * i] - mean) * rstd * gm.x + bt.x;
-                o.y = (v[4 * i + 1] - mean) * rstd * gm.y + bt.y;
-                o.z = (v[4 * i + 2] - mean) * rstd * gm.z + bt.z;
-                o.w = (v[4 * i + 3] - mean) * rstd * gm.w + bt.w;
+                o.x = (v[rr][4 * i] - mean) * rstd * gm[i].x + bt[i].x;
+                o.y = (v[rr][4 * i + 1] - mean) * rstd * gm[i].y + bt[i].y;
+                o.z = (v[rr][4 * i + 2] - mean) * rstd * gm[i].z + bt[i].z;
+                o.w = (v[rr][4 * i + 3] - mean) * rstd * gm[i].w + bt[i].w;
                 if (to_global) {
                     if (row0 + r < p.T) *reinterpret_cast<float4*>(p.out + (size_t)(row0 + r) * p.ld_out + c4 * 4) = o;
                 } else {
@@ -141,38 +198,48 @@ __global__ void __launch_bounds__(DT_THREADS, 1) post_attention_kernel(const Pos
     };
 
     // ---- GEMM 0: linear(hidden); + bias + residual -> sX; LayerNorm -> x1 (sX fp32, sA half) ----
+    LnW ln1, ln2;
     {
+        ln_load(p.g1, p.be1, ln1);
         float acc[2][C / 64][4] = {};
-        dt_gemm<C / 64>(acc, ring, 0, Cfg::CH0, sA, Cfg::A_PITCH, warp * (C / 8), lane);
+        float2 bias_r[C / 64];  // fetched before the GEMM: their L2 latency used to sit in front of every epilogue
+#pragma unroll
+        for (int nt = 0; nt < C / 64; ++nt) bias_r[nt] = __ldg(reinterpret_cast<const float2*>(p.b_lin + warp * (C / 8) + nt * 8 + 2 * q));
+        dt_gemm<C / 64, 2>(acc, ring, 0, Cfg::CH0, sA, Cfg::A_PITCH, warp * (C / 8), lane, C * DT_ROW_BYTES);
+        PA_MARK(2);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < C / 64; ++nt) {
                 const int col = warp * (C / 8) + nt * 8 + 2 * q;
-                const float2 bias = __ldg(reinterpret_cast<const float2*>(p.b_lin + col));
+                const float2 bias = bias_r[nt];
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int r = mt * 16 + g + 8 * h;
-                    float2 res = make_float2(0.f, 0.f);
-                    if (row0 + r < p.T) res = __ldg(reinterpret_cast<const float2*>(p.x_in + (size_t)(row0 + r) * p.ld_x + col));
-                    *reinterpret_cast<float2*>(sX + r * Cfg::X_PITCH + col) =
-                        make_float2(acc[mt][nt][2 * h] + bias.x + res.x, acc[mt][nt][2 * h + 1] + bias.y + res.y);
+                for (int h = 0; h < 2; ++h) {  // in place: each element of sX is read and written by one thread
+                    float2* x = reinterpret_cast<float2*>(sX + (mt * 16 + g + 8 * h) * Cfg::X_PITCH + col);
+                    const float2 res = *x;
+                    *x = make_float2(acc[mt][nt][2 * h] + bias.x + res.x, acc[mt][nt][2 * h + 1] + bias.y + res.y);
                 }
             }
     }
     dt_sync_compute();  // all of sX written; every warp is done reading sA (hidden)
-    layer_norm(p.g1, p.be1, p.eps1, false);
+    PA_MARK(3);
+    layer_norm(ln1, p.eps1, false);
     dt_sync_compute();  // x1 complete in sA / sX
+    PA_MARK(4);
     // ---- GEMM 1: ReLU(expand(x1) + bias) -> sE (half) ----
     {
         float acc[2][C / 32][4] = {};
+        float2 bias_r[C / 32];
+#pragma unroll
+        for (int nt = 0; nt < C / 32; ++nt) bias_r[nt] = __ldg(reinterpret_cast<const float2*>(p.b_exp + warp * (C / 4) + nt * 8 + 2 * q));
         dt_gemm<C / 32>(acc, ring, Cfg::CH0, Cfg::CH1, sA, Cfg::A_PITCH, warp * (C / 4), lane);
+        PA_MARK(5);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < C / 32; ++nt) {
                 const int col = warp * (C / 4) + nt * 8 + 2 * q;
-                const float2 bias = __ldg(reinterpret_cast<const float2*>(p.b_exp + col));
+                const float2 bias = bias_r[nt];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const int r = mt * 16 + g + 8 * h;
@@ -183,16 +250,22 @@ __global__ void __launch_bounds__(DT_THREADS, 1) post_attention_kernel(const Pos
             }
     }
     dt_sync_compute();  // sE complete
+    PA_MARK(6);
     // ---- GEMM 2: squeeze(e) + bias + x1 -> sX (in place: each element is read and written by one thread); LayerNorm ----
     {
+        ln_load(p.g2, p.be2, ln2);
         float acc[2][C / 64][4] = {};
-        dt_gemm<C / 64>(acc, ring, Cfg::CH0 + Cfg::CH1, Cfg::CH2, sE, Cfg::E_PITCH, warp * (C / 8), lane);
+        float2 bias_r[C / 64];
+#pragma unroll
+        for (int nt = 0; nt < C / 64; ++nt) bias_r[nt] = __ldg(reinterpret_cast<const float2*>(p.b_sq + warp * (C / 8) + nt * 8 + 2 * q));
+        dt_gemm<C / 64, 2>(acc, ring, Cfg::CH0 + Cfg::CH1, Cfg::CH2, sE, Cfg::E_PITCH, warp * (C / 8), lane, C * DT_ROW_BYTES);
+        PA_MARK(7);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int nt = 0; nt < C / 64; ++nt) {
                 const int col = warp * (C / 8) + nt * 8 + 2 * q;
-                const float2 bias = __ldg(reinterpret_cast<const float2*>(p.b_sq + col));
+                const float2 bias = bias_r[nt];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     float2* x = reinterpret_cast<float2*>(sX + (mt * 16 + g + 8 * h) * Cfg::X_PITCH + col);
@@ -202,7 +275,9 @@ __global__ void __launch_bounds__(DT_THREADS, 1) post_attention_kernel(const Pos
             }
     }
     dt_sync_compute();
-    layer_norm(p.g2, p.be2, p.eps2, true);
+    PA_MARK(8);
+    layer_norm(ln2, p.eps2, true);
+    PA_MARK(9);
 }
 
 __global__ void f32_to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, long long count) {
@@ -230,6 +305,12 @@ __global__ void pack_linear_weight_kernel(const float* __restrict__ w, int N, in
 }  // namespace geotx
 
 using namespace geotx;
+
+#ifdef PA_PHASE_CLOCKS
+extern "C" int geotx_debug_k4f_phases(long long* host16) {
+    return check_cuda(cudaMemcpyFromSymbol(host16, pa_phase_clock, sizeof(long long) * 16), "geotx_debug_k4f_phases");
+}
+#endif
 
 extern "C" int geotx_f32_to_f16(const float* src, void* dst, int64_t count, void* stream) {
     GEOTX_REQUIRE(src && dst && count > 0, "geotx_f32_to_f16: bad arguments");

@@ -47,7 +47,7 @@ def main():
         lib = pkg._abi.load()
         model.embedding.cheb_d_index_max = next(float(lib.geotx_gse_cheb_d_range(s)) for s in range(6)
                                                 if widest <= float(lib.geotx_gse_cheb_d_range(s)) or s == 5)
-    inflight = args.inflight or (4 if max(n, m) <= 2048 else 2 if max(n, m) <= 4096 else 1)
+    inflight = args.inflight or bench.default_inflight(max(n, m))
     with torch.no_grad():
         model(*resident[0])  # packs the weights, builds the coefficient tables
     torch.cuda.synchronize()
