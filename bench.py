@@ -728,7 +728,7 @@ def run_b200(args):
     timers.wrap(pkg.ops, 'rpe_scores_cheb', 'rpe_scores_cheb (K3r)', k3r_flops)
     timers.wrap(pkg.ops, 'rpe_scores', 'rpe_scores (K3a)', k3a_bytes)
     timers.wrap(model.embedding, 'embed', 'gse_embed (K2c / K2 / K2t)', embed_bytes)
-    timers.wrap(pkg.ops, 'attention', 'attention (K3b)',
+    timers.wrap(pkg.ops, 'attention', 'attention (K3h)',
                 lambda q, kk, v, heads, *a, **kw: 4.0 * q.shape[0] * q.shape[1] * kk.shape[1] * q.shape[2])
     timers.wrap(pkg.ops, 'post_attention', 'post_attention (K4f)',
                 lambda hidden, *a, **kw: 2.0 * (hidden.numel() // hidden.shape[-1]) * 5 * hidden.shape[-1] ** 2)
