@@ -220,3 +220,29 @@ def test_joint_view_only_inside_one_storage(pkg):
     a = torch.from_numpy(raw[:1024]).view(1, 4, 256)
     b = torch.from_numpy(raw[1024:]).view(1, 4, 256)
     assert a.data_ptr() + a.numel() * 4 == b.data_ptr() and jv(a, b) is None
+
+
+def test_attention_operand_switch_and_projection_fallback(pkg, monkeypatch):
+    """GEOTX_ATT selects the attention core's operand form (half q | k | v written by the projection kernel, or fp32);
+    `_linear(..., half_cols=)` on a shape / device K13 does not take falls back to F.linear and rounds the leading
+    columns exactly as the kernel's epilogue does (round to nearest, SATURATING: a stray large activation stays finite)."""
+    import torch
+    m = pkg.modules
+    assert m._attention_f16()
+    monkeypatch.setenv('GEOTX_ATT', 'f32')
+    assert not m._attention_f16()
+    monkeypatch.setenv('GEOTX_ATT', 'int8')
+    with pytest.raises(ValueError):
+        m._attention_f16()
+    g = torch.Generator().manual_seed(3)
+    x, w, b = torch.randn(5, 64, generator=g), torch.randn(192, 64, generator=g), torch.randn(192, generator=g)
+    b[0], b[1] = 1e6, -1e6
+    full = torch.nn.functional.linear(x, w, b)
+    yh, rest = m._linear(x, torch.nn.Module(), 'w', w, b, half_cols=128)  # CPU tensors: the F.linear branch
+    assert yh.dtype == torch.float16 and tuple(yh.shape) == (5, 128) and torch.isfinite(yh).all()
+    assert float(yh[0, 0]) == 65504.0 and float(yh[0, 1]) == -65504.0
+    assert torch.equal(yh[:, 2:], full[:, 2:128].to(torch.float16)) and torch.equal(rest, full[:, 128:])
+    yh, rest = m._linear(x, torch.nn.Module(), 'w', w, b, half_cols=192)
+    assert rest is None and tuple(yh.shape) == (5, 192)
+    sched = pkg.RPEConditionalTransformer(['self', 'cross'], 64, 4)
+    assert sched.throughput is False  # one forward at a time unless a graph in flight asks for the other schedule
