@@ -1,4 +1,6 @@
-// K3b: flash-style multi-head attention with an additive pre-softmax score term.
+// K3b: flash-style multi-head attention with an additive pre-softmax score term, for fp32 q, k, v.
+// (The fused schedule of modules.py hands q, k, v over as IEEE half and runs K3h, k3_attention_f16.cu; this kernel
+// serves direct callers with fp32 operands and GEOTX_ATT=f32.  Same arithmetic: it rounds q, k, v to half itself.)
 //
 // Replaces /root/reference/geotransformer/modules/transformer/rpe_transformer.py:57-70 (self blocks, scores_p from
 // K3a) and /root/reference/geotransformer/modules/transformer/vanilla_transformer.py:54-68 (cross blocks,
